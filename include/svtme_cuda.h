@@ -1,0 +1,298 @@
+/*
+ * svtme_cuda.h -- C ABI of the B200-native open-loop motion-estimation library
+ * (libsvtme_cuda.so).
+ *
+ * This is the drop-in boundary for SVT-AV1's open-loop ME hot path.  Every
+ * entry point cites the reference interface it replaces (paths relative to the
+ * SVT-AV1 v3.0.2 tree).  Only plain C types cross the boundary: pointers,
+ * sizes, and the POD structs declared here.  No torch / CUDA types.
+ *
+ * Return codes reuse the numeric values of the reference's EbErrorType
+ * (Source/API/EbSvtAv1.h:121-135).
+ */
+#ifndef SVTME_CUDA_H
+#define SVTME_CUDA_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVTME_OK                       0            /* EB_ErrorNone */
+#define SVTME_ERR_INSUFFICIENT         ((int32_t)0x80001000) /* EB_ErrorInsufficientResources */
+#define SVTME_ERR_UNDEFINED            ((int32_t)0x80001001) /* EB_ErrorUndefined (CUDA failure) */
+#define SVTME_ERR_BAD_PARAMETER        ((int32_t)0x80001005) /* EB_ErrorBadParameter */
+
+#define SVTME_MAX_LISTS          2   /* MAX_NUM_OF_REF_PIC_LIST, definitions.h:2337 */
+#define SVTME_MAX_REFS_PER_LIST  4   /* REF_LIST_MAX_DEPTH / MAX_REF_IDX, EbSvtAv1Enc.h:36, definitions.h:2352 */
+#define SVTME_SQUARE_PU_COUNT    85  /* SQUARE_PU_COUNT, me_sb_results.h:24 */
+#define SVTME_PU_COUNT_NO_8X8    21  /* MAX_SB64_PU_COUNT_NO_8X8, me_sb_results.h:25 */
+#define SVTME_PU_COUNT_WO_16X16  5   /* MAX_SB64_PU_COUNT_WO_16X16, me_sb_results.h:26 */
+#define SVTME_MAX_SAD_VALUE      (128u * 128u * 255u) /* motion_estimation.h:85 */
+
+/* EbInputResolution classes, definitions.h:2076-2086 */
+enum {
+    SVTME_INPUT_SIZE_240p = 0, SVTME_INPUT_SIZE_360p = 1, SVTME_INPUT_SIZE_480p = 2,
+    SVTME_INPUT_SIZE_720p = 3, SVTME_INPUT_SIZE_1080p = 4, SVTME_INPUT_SIZE_4K = 5,
+    SVTME_INPUT_SIZE_8K = 6
+};
+
+/* SearchArea / SearchAreaMinMax, me_context.h:321-328 */
+typedef struct SvtMeArea {
+    uint16_t width;
+    uint16_t height;
+} SvtMeArea;
+typedef struct SvtMeAreaMinMax {
+    SvtMeArea sa_min;
+    SvtMeArea sa_max;
+} SvtMeAreaMinMax;
+
+/*
+ * SvtMeKnobs -- the flattened, derived ME configuration of ONE picture.
+ *
+ * It is the union of
+ *  (a) the MeContext knob fields written by svt_aom_sig_deriv_me
+ *      (enc_mode_config.c:671-808; struct at me_context.h:366-509),
+ *  (b) the per-picture fields me_process.c copies into MeContext
+ *      (me_process.c:216-227), and
+ *  (c) the PictureParentControlSet / SequenceControlSet fields that
+ *      motion_estimation.c reads directly.
+ * The encoder keeps deriving these on the CPU exactly as today; the shim only
+ * copies them out of MeContext/pcs.
+ */
+typedef struct SvtMeKnobs {
+    /* (c) pcs / scs fields */
+    uint64_t picture_number;          /* pcs->picture_number */
+    uint8_t  hierarchical_levels;     /* pcs->hierarchical_levels   (motion_estimation.c:2419) */
+    uint8_t  similar_brightness_refs; /* pcs->similar_brightness_refs (:2420) */
+    uint8_t  input_resolution;        /* scs->input_resolution class (:2851, :2998) */
+    uint8_t  enable_me_8x8;           /* pcs->enable_me_8x8  (pcs.c:1392) */
+    uint8_t  enable_me_16x16;         /* pcs->enable_me_16x16 (pcs.c:1389) */
+    uint8_t  max_number_of_pus_per_sb;/* pcs->max_number_of_pus_per_sb, always 85 (resource_coordination_process.c:425) */
+    uint8_t  gm_enabled;              /* pcs->gm_ctrls.enabled (:3149) */
+    uint8_t  gm_use_distance_based_active_th; /* pcs->gm_ctrls.use_distance_based_active_th (:2879) */
+    uint8_t  only_l_bwd;              /* scs->mrp_ctrls.only_l_bwd (:2783) */
+    uint8_t  max_cand;                /* pa_me_data->max_cand (pd_process.c:3517) */
+    uint8_t  max_refs;                /* pa_me_data->max_refs */
+    uint8_t  max_l0;                  /* pa_me_data->max_l0 */
+
+    /* (b) per-picture MeContext fields, me_process.c:219-227 */
+    uint8_t  num_of_list_to_search;
+    uint8_t  num_of_ref_pic_to_search[SVTME_MAX_LISTS];
+    uint8_t  temporal_layer_index;
+    uint8_t  is_ref;
+
+    /* (a) derived MeContext knobs */
+    uint8_t  hme_search_method;       /* 0 = SUB_SAD_SEARCH, 1 = FULL_SAD_SEARCH (definitions.h) */
+    uint8_t  me_search_method;
+    uint8_t  enable_hme_flag;
+    uint8_t  enable_hme_level0_flag;
+    uint8_t  enable_hme_level1_flag;
+    uint8_t  enable_hme_level2_flag;
+    uint16_t num_hme_sa_w;            /* always 2 */
+    uint16_t num_hme_sa_h;            /* always 2 */
+    SvtMeAreaMinMax hme_l0_sa;
+    SvtMeArea       hme_l1_sa;
+    SvtMeArea       hme_l2_sa;
+    SvtMeAreaMinMax me_sa;
+    /* MeHmeRefPruneCtrls, me_context.h:280-290 */
+    uint8_t  enable_me_hme_ref_pruning;
+    uint16_t prune_ref_if_hme_sad_dev_bigger_than_th;
+    uint16_t prune_ref_if_me_sad_dev_bigger_than_th;
+    uint32_t zz_sad_th;
+    uint16_t zz_sad_pct;
+    uint32_t phme_sad_th;
+    uint16_t phme_sad_pct;
+    /* MeSrCtrls, me_context.h:292-305 */
+    uint8_t  enable_me_sr_adjustment;
+    uint16_t reduce_me_sr_based_on_mv_length_th;
+    uint16_t stationary_hme_sad_abs_th;
+    uint16_t stationary_me_sr_divisor;
+    uint16_t reduce_me_sr_based_on_hme_sad_abs_th;
+    uint16_t me_sr_divisor_for_low_hme_sad;
+    uint8_t  distance_based_hme_resizing;
+    /* Me8x8VarCtrls, me_context.h:310-319 */
+    uint8_t  me_8x8_var_enabled;
+    uint32_t me_sr_div4_th;
+    uint32_t me_sr_div2_th;
+    uint32_t me_sr_mult2_th;
+    /* MvBasedSearchAdj, me_context.h:356-364 */
+    uint8_t  mv_sa_adj_enabled;
+    uint8_t  mv_sa_adj_nearest_ref_only;
+    uint16_t mv_sa_adj_mv_size_th;
+    uint16_t mv_sa_adj_sa_multiplier;
+    /* PreHmeCtrls, me_context.h:336-341 */
+    uint8_t  prehme_enable;
+    SvtMeAreaMinMax prehme_sa_cfg[2];
+    uint8_t  prehme_skip_search_line;
+    uint8_t  prehme_l1_early_exit;
+    /* scalars, me_context.h:491-508 */
+    int32_t  prune_me_candidates_th;
+    uint8_t  use_best_unipred_cand_only;
+    uint8_t  reduce_hme_l0_sr_th_min;
+    uint8_t  reduce_hme_l0_sr_th_max;
+    uint32_t me_early_exit_th;
+    uint32_t me_safe_limit_zz_th;
+    uint32_t prev_me_stage_based_exit_th;
+} SvtMeKnobs;
+
+/*
+ * Preset-level inputs of svt_aom_sig_deriv_me (enc_mode_config.c:671) and of
+ * the pcs/scs fields around it.  svtme_derive_knobs() is a convenience mirror
+ * of that derivation for callers that do not run the encoder (tests, bench);
+ * an integrated encoder copies its own derived MeContext instead.
+ */
+typedef struct SvtMePresetCfg {
+    int8_t   enc_mode;             /* ENC_MR(-1) .. ENC_M13, EbSvtAv1Enc.h:45-61 */
+    uint8_t  rtc_tune;             /* pred_structure == SVT_AV1_PRED_LOW_DELAY_B */
+    uint8_t  sc_class1;            /* screen-content class */
+    uint8_t  rate_control_vbr;     /* rate_control_mode == VBR (mrp level, enc_handle.c:4163) */
+    uint8_t  fast_decode;          /* static_config.fast_decode */
+    uint32_t qp;                   /* static_config.qp (default 35, enc_settings.h:22) */
+    uint32_t frame_rate_q16;       /* scs->frame_rate (Q16), enc_mode_config.c:335 */
+    uint16_t width;                /* luma width  (multiple of 8) */
+    uint16_t height;               /* luma height (multiple of 8) */
+    uint8_t  hierarchical_levels;  /* pcs->hierarchical_levels */
+    /* per picture */
+    uint64_t picture_number;
+    uint8_t  temporal_layer_index;
+    uint8_t  is_ref;
+    uint8_t  slice_type_b;         /* 1 = B_SLICE (two lists), 0 = P_SLICE */
+    uint8_t  similar_brightness_refs;
+    uint8_t  ref_list0_count_try;  /* 0 => take the mrp default for this layer */
+    uint8_t  ref_list1_count_try;
+} SvtMePresetCfg;
+
+/*
+ * Host result buffers of one picture, caller-owned.  They are the flat,
+ * picture-level form of the per-SB MeSbResults arrays (me_sb_results.h:44-51,
+ * allocated at pcs.c:98-119) plus the eight per-SB pcs statistics written by
+ * compute_distortion / perform_gm_detection (motion_estimation.c:2964-3007,
+ * 2838-2961).  pu_count = 85 / 21 / 5 as at pcs.c:106-110.
+ *
+ * Entries the reference leaves unwritten (MVs of pruned references,
+ * candidates beyond total_me_candidate_index) are 0 here.
+ */
+typedef struct SvtMePictureResults {
+    uint32_t  b64_total_count;             /* in: capacity check; picture width/height in 64x64 blocks multiplied */
+    uint32_t  pu_count;                    /* in: 85, 21 or 5 */
+    uint32_t *me_mv;                       /* [b64][pu_count][max_refs]  MvCandidate.as_int = (y<<16)|(x&0xffff), full-pel */
+    uint8_t  *me_cand;                     /* [b64][pu_count][max_cand]  MeCandidate bit-fields: dir:2 | ref_idx_l0:2<<2 | ref_idx_l1:2<<4 | ref0_list<<6 | ref1_list<<7 */
+    uint8_t  *total_me_candidate_index;    /* [b64][pu_count] */
+    uint32_t *me_64x64_distortion;         /* [b64] */
+    uint32_t *me_32x32_distortion;
+    uint32_t *me_16x16_distortion;
+    uint32_t *me_8x8_distortion;
+    uint32_t *me_8x8_cost_variance;
+    uint32_t *rc_me_distortion;
+    uint8_t  *stationary_block_present_sb;
+    uint8_t  *rc_me_allow_gm;
+    /* Optional (may be NULL): MeContext state at the end of each SB, for parity checks of SADs and selected refs. */
+    uint32_t *sb_best_sad;                 /* [b64][2][4][85] p_sb_best_sad, tier-zero PU order; MAX_SAD_VALUE where the ref was not searched */
+    uint32_t *sb_best_mv;                  /* [b64][2][4][85] p_sb_best_mv */
+    uint8_t  *do_ref;                      /* [b64][2][4]  search_results[l][r].do_ref after me_prune_ref */
+    int16_t  *hme_sc;                      /* [b64][2][4][2] search_results[l][r].hme_sc_x / hme_sc_y */
+} SvtMePictureResults;
+
+typedef struct SvtMeDeviceCfg {
+    int32_t  device;            /* CUDA device ordinal */
+    uint32_t max_width;         /* largest luma width that will be registered */
+    uint32_t max_height;
+    uint32_t max_pictures;      /* device picture slots (source + references in flight); 0 => 64 */
+    uint32_t max_inflight;      /* concurrent picture searches (streams); 0 => 4 */
+} SvtMeDeviceCfg;
+
+typedef struct SvtMeHandle SvtMeHandle;   /* opaque */
+typedef struct SvtMePic    SvtMePic;      /* opaque: one picture's full / quarter / sixteenth luma planes in HBM */
+
+/* Library/device bring-up.  Replaces: the allocation of PA reference objects
+ * (reference_object.c:217-345) and ME contexts (enc_handle.c:2102-2110). */
+int32_t svtme_init(const SvtMeDeviceCfg *cfg, SvtMeHandle **out);
+void    svtme_destroy(SvtMeHandle *h);
+
+/* Mirror of svt_aom_sig_deriv_me + set_hme/me_search_params (enc_mode_config.c:136-808),
+ * HME flags (:1608-1619), enable_me_8x8 (:76-96), gm level (:103-129, 1821-1903),
+ * mrp controls (enc_handle.c:3347-3640, 4141-4176), max_cand/max_refs (pcs.c:91-96). Pure host code. */
+int32_t svtme_derive_knobs(const SvtMePresetCfg *cfg, SvtMeKnobs *out);
+
+/* Upload one 8-bit luma plane, then build the padded full / quarter / sixteenth
+ * planes on the device.  Replaces: copy_frame_buffer's luma memcpy
+ * (enc_handle.c:4920-4925), svt_aom_pad_input_pictures (pic_analysis_process.c:2004),
+ * svt_aom_downsample_filtering_input_picture (:1945-2002) incl. RTCD downsample_2d
+ * (aom_dsp_rtcd.c:509) and svt_aom_generate_padding (pic_operators.c:338).
+ * `luma` points at pixel (0,0); width/height must be multiples of 8.
+ * Asynchronous: the host buffer must stay valid until svtme_picture_wait(). */
+int32_t svtme_picture_register(SvtMeHandle *h, uint64_t picture_number, const uint8_t *luma, uint32_t stride,
+                               uint32_t width, uint32_t height, SvtMePic **out);
+/* 10-bit input: ME sees the 8-bit MSB plane (in16 >> 2), as svt_unpack_and_2bcompress
+ * does (pack_unpack_c.c:77-117, enc_handle.c:4964-4972).  stride in samples. */
+int32_t svtme_picture_register16(SvtMeHandle *h, uint64_t picture_number, const uint16_t *luma16, uint32_t stride,
+                                 uint32_t width, uint32_t height, SvtMePic **out);
+/* Same, from a luma plane that is already in device memory (device pointer). */
+int32_t svtme_picture_register_device(SvtMeHandle *h, uint64_t picture_number, const void *d_luma, uint32_t stride,
+                                      uint32_t width, uint32_t height, SvtMePic **out);
+/* Wait until the planes of `pic` are built. */
+int32_t svtme_picture_wait(SvtMeHandle *h, SvtMePic *pic);
+/* Copy a padded plane back (level 0 = full, 1 = quarter, 2 = sixteenth) for the
+ * CPU users of the decimated planes (temporal filter, DG detector) and for tests.
+ * dst receives (width>>level) x (height>>level) pixels plus `pad` replicated
+ * pixels on every side (pad <= 64 >> level); dst_stride >= (width>>level)+2*pad. Synchronous. */
+int32_t svtme_picture_read_plane(SvtMeHandle *h, SvtMePic *pic, int32_t level, uint32_t pad, uint8_t *dst,
+                                 uint32_t dst_stride);
+int32_t svtme_picture_release(SvtMeHandle *h, SvtMePic *pic);
+
+/* Open-loop ME of every 64x64 block of `cur` against refs[list][idx].
+ * Replaces: the segment/SB loop of svt_aom_motion_estimation_kernel
+ * (me_process.c:174-290) and svt_aom_motion_estimation_b64
+ * (motion_estimation.c:3076-3153) for all b64 of the picture.
+ * Asynchronous; `out` buffers are filled when svtme_search_wait() returns.
+ * Unused refs[][] entries may be NULL. */
+int32_t svtme_picture_search(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
+                             const SvtMeKnobs *knobs, SvtMePictureResults *out, uint64_t *ticket);
+int32_t svtme_search_wait(SvtMeHandle *h, uint64_t ticket);
+/* Device-resident variant for throughput measurement: results stay in HBM
+ * (no D2H); used by bench.py for `value`.  Returns device time of the last
+ * completed search of this ticket in milliseconds via svtme_search_elapsed_ms. */
+int32_t svtme_picture_search_device(SvtMeHandle *h, SvtMePic *cur,
+                                    SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
+                                    const SvtMeKnobs *knobs, uint64_t *ticket);
+int32_t svtme_search_elapsed_ms(SvtMeHandle *h, uint64_t ticket, float *ms);
+/* Kernel launches issued by this handle so far (bench.py's gpu_launches). */
+uint64_t svtme_launch_count(SvtMeHandle *h);
+/* Last CUDA error string of this handle (for diagnostics). */
+const char *svtme_last_error(SvtMeHandle *h);
+
+/*
+ * RTCD-level entry points (host pointers, synchronous).  Signatures are those
+ * of the reference's function-pointer table so the reference's kernel unit
+ * tests (test/SadTest.cc, test/PictureOperatorTest.cc) can be pointed at them;
+ * a per-call offload is NOT the fast path.
+ */
+/* aom_dsp_rtcd.h:779 svt_sad_loop_kernel */
+void svtme_cuda_sad_loop_kernel(SvtMeHandle *h, const uint8_t *src, uint32_t src_stride, const uint8_t *ref,
+                                uint32_t ref_stride, uint32_t block_height, uint32_t block_width, uint64_t *best_sad,
+                                int16_t *x_search_center, int16_t *y_search_center, uint32_t src_stride_raw,
+                                uint8_t skip_search_line, int16_t search_area_width, int16_t search_area_height);
+/* aom_dsp_rtcd.h:841 downsample_2d */
+void svtme_cuda_downsample_2d(SvtMeHandle *h, const uint8_t *input_samples, uint32_t input_stride,
+                              uint32_t input_area_width, uint32_t input_area_height, uint8_t *decim_samples,
+                              uint32_t decim_stride, uint32_t decim_step);
+/* aom_dsp_rtcd.h:856 svt_nxm_sad_kernel */
+uint32_t svtme_cuda_nxm_sad_kernel(SvtMeHandle *h, const uint8_t *src, uint32_t src_stride, const uint8_t *ref,
+                                   uint32_t ref_stride, uint32_t height, uint32_t width);
+/* open_loop_me_fullpel_search_sblock (motion_estimation.c:781-817) = the fused
+ * svt_initialize_buffer_32bits + svt_ext_all_sad_calculation_8x8_16x16 +
+ * svt_ext_eight_sad_calculation_32x32_64x64 + svt_ext_sad_calculation_* loop
+ * (aom_dsp_rtcd.h:842-853) for one 64x64 block and one search window.
+ * best_sad/best_mv: [85] in tier-zero order, initialised by the caller. */
+void svtme_cuda_fullpel_search_sblock(SvtMeHandle *h, const uint8_t *src, uint32_t src_stride, const uint8_t *ref,
+                                      uint32_t ref_stride, int16_t x_search_area_origin, int16_t y_search_area_origin,
+                                      uint32_t search_area_width, uint32_t search_area_height, uint8_t sub_sad,
+                                      uint32_t *best_sad, uint32_t *best_mv);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVTME_CUDA_H */

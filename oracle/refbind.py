@@ -1,0 +1,144 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes binding of oracle/_ref/libsvtref.so (the compiled reference) and of
+oracle/libsvtme_oracle.so (our C restatement).  Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline
+legs may import this module."""
+import ctypes as C
+import importlib.util
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+_pkg = os.path.join(ROOT, "svt-av1-mirror_b200")
+if _pkg not in sys.path:
+    sys.path.insert(0, _pkg)
+from svtme import abi  # noqa: E402
+
+
+class RefPlane(C.Structure):
+    _fields_ = [("buf", C.c_void_p), ("stride", C.c_uint32), ("width", C.c_uint32), ("height", C.c_uint32),
+                ("org_x", C.c_uint32), ("org_y", C.c_uint32)]
+
+
+class RefPic(C.Structure):
+    _fields_ = [("lvl", RefPlane * 3), ("picture_number", C.c_uint64)]
+
+
+# Reference geometry: full-res pad 72 (enc_handle.c:4057-4070), quarter 32, sixteenth 16 (reference_object.c:267-295)
+PADS = (72, 32, 16)
+
+
+class PaddedPicture:
+    """Three padded luma planes laid out as the reference's EbPaReferenceObject has them."""
+
+    def __init__(self, luma, picture_number):
+        h, w = luma.shape
+        assert w % 8 == 0 and h % 8 == 0
+        self.width, self.height, self.picture_number = w, h, picture_number
+        self.planes = []
+        for lvl, pad in enumerate(PADS):
+            pw, ph = w >> lvl, h >> lvl
+            self.planes.append(np.zeros((ph + 2 * pad, pw + 2 * pad), np.uint8))
+        p = PADS[0]
+        self.planes[0][p:p + h, p:p + w] = luma
+        self.struct = RefPic()
+        self.struct.picture_number = picture_number
+        for lvl, pad in enumerate(PADS):
+            pl = self.struct.lvl[lvl]
+            pl.buf = self.planes[lvl].ctypes.data
+            pl.stride = self.planes[lvl].shape[1]
+            pl.width, pl.height = w >> lvl, h >> lvl
+            pl.org_x = pl.org_y = pad
+
+    def interior(self, lvl):
+        pad = PADS[lvl]
+        return self.planes[lvl][pad:pad + (self.height >> lvl), pad:pad + (self.width >> lvl)]
+
+
+def _load(path, what):
+    if not os.path.exists(path):
+        raise RuntimeError("%s not built: %s (run `make -C oracle`)" % (what, path))
+    return C.CDLL(path)
+
+
+class _Binding:
+    """Common call surface of the compiled reference (prefix svtref_) and the oracle restatement (svtorc_)."""
+
+    def __init__(self, lib, prefix):
+        self.lib, self.prefix = lib, prefix
+        f = self._f
+        f("derive_knobs").argtypes = [C.POINTER(abi.PresetCfg), C.POINTER(abi.Knobs)]
+        f("me_picture").argtypes = [C.POINTER(abi.Knobs), C.POINTER(RefPic), C.POINTER(RefPic),
+                                    C.POINTER(abi.PictureResults), C.c_int]
+        f("build_planes").argtypes = [C.POINTER(RefPic), C.c_int]
+        f("build_planes").restype = None
+        f("sad_loop_kernel").argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                         C.POINTER(C.c_uint64), C.POINTER(C.c_int16), C.POINTER(C.c_int16),
+                                         C.c_uint32, C.c_uint8, C.c_int16, C.c_int16]
+        f("sad_loop_kernel").restype = None
+        f("nxm_sad_kernel").argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
+        f("nxm_sad_kernel").restype = C.c_uint32
+        f("downsample_2d").argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32,
+                                       C.c_uint32]
+        f("downsample_2d").restype = None
+        f("generate_padding").argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+        f("generate_padding").restype = None
+        f("fullpel_search_sblock").argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_int16, C.c_int16,
+                                               C.c_uint32, C.c_uint32, C.c_uint8, C.c_void_p, C.c_void_p]
+        f("fullpel_search_sblock").restype = None
+
+    def _f(self, name):
+        return getattr(self.lib, self.prefix + name)
+
+    def derive_knobs(self, **kw):
+        cfg = abi.PresetCfg()
+        for k, v in kw.items():
+            setattr(cfg, k, v)
+        k = abi.Knobs()
+        rc = self._f("derive_knobs")(C.byref(cfg), C.byref(k))
+        if rc != 0:
+            raise RuntimeError("derive_knobs failed: %d" % rc)
+        return k
+
+    def build_planes(self, pic, hme_level1=1):
+        self._f("build_planes")(C.byref(pic.struct), hme_level1)
+
+    def me_picture(self, knobs, cur, refs, n_threads=1, extended=True):
+        """refs: {(list, idx): PaddedPicture}. Returns abi.ResultBuffers."""
+        n_b64 = ((cur.width + 63) // 64) * ((cur.height + 63) // 64)
+        out = abi.ResultBuffers(n_b64, knobs, extended=extended)
+        arr = (RefPic * 8)()
+        for (li, ri), p in refs.items():
+            arr[li * 4 + ri] = p.struct
+        rc = self._f("me_picture")(C.byref(knobs), C.byref(cur.struct), arr, C.byref(out.struct), n_threads)
+        if rc != 0:
+            raise RuntimeError("me_picture failed: %d" % rc)
+        out._keep = (arr, refs, cur)
+        return out
+
+    def sad_loop_kernel(self, src, src_off, src_stride, ref, ref_off, ref_stride, bh, bw, raw_stride, skip, sa_w, sa_h):
+        best = C.c_uint64(0)
+        x = C.c_int16(-12345)
+        y = C.c_int16(-12345)
+        self._f("sad_loop_kernel")(src.ctypes.data + src_off, src_stride, ref.ctypes.data + ref_off, ref_stride, bh, bw,
+                                   C.byref(best), C.byref(x), C.byref(y), raw_stride, skip, sa_w, sa_h)
+        return best.value, x.value, y.value
+
+
+class Reference(_Binding):
+    def __init__(self):
+        super().__init__(_load(os.path.join(HERE, "_ref", "libsvtref.so"), "compiled reference"), "svtref_")
+        self.lib.svtref_set_isa.argtypes = [C.c_int]
+
+    def set_isa(self, isa):
+        return self.lib.svtref_set_isa(isa)
+
+
+class Oracle(_Binding):
+    def __init__(self):
+        super().__init__(_load(os.path.join(HERE, "libsvtme_oracle.so"), "oracle restatement"), "svtorc_")
+
+
+def have_reference():
+    return os.path.exists(os.path.join(HERE, "_ref", "libsvtref.so"))
