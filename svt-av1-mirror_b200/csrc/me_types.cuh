@@ -1,0 +1,145 @@
+// me_types.cuh -- device-side data structures of the open-loop ME path.
+//
+// Names follow the reference's domain: a picture has three luma planes (full, quarter, sixteenth);
+// a 64x64 block ("b64"/SB) is searched against up to 2x4 reference pictures; results are per
+// square PU (85 per SB, "tier-zero" order, me_context.h:52-138).
+#pragma once
+#include <stdint.h>
+#include "../../include/svtme_cuda.h"
+
+#if defined(__CUDACC__)
+#define SVTME_HD __host__ __device__ __forceinline__
+#define SVTME_D __device__ __forceinline__
+#else
+#define SVTME_HD inline
+#define SVTME_D inline
+#endif
+
+namespace svtme {
+
+constexpr int kMaxLists = SVTME_MAX_LISTS;
+constexpr int kMaxRefs  = SVTME_MAX_REFS_PER_LIST;
+constexpr int kPus      = SVTME_SQUARE_PU_COUNT;
+constexpr uint32_t kMaxU32 = 0xFFFFFFFFu;
+
+// One padded luma plane in HBM.  `org` points at pixel (0,0); at least `pad_x`/`pad_y` replicated
+// pixels exist on every side.  `ref_org` is the origin (= padding) the REFERENCE's buffer of this
+// level has (72 / 32 / 16: enc_handle.c:4057-4070, reference_object.c:267-295); the HME window
+// clipping depends on it (pad_width = org_x - 1, motion_estimation.c:838-839), independent of how
+// much padding the device buffer really has.
+struct DevPlane {
+    const uint8_t *org;
+    int32_t        stride;
+    int32_t        width, height;
+    int32_t        ref_org;
+};
+
+struct DevPic {
+    DevPlane lvl[3];  // 0 full, 1 quarter, 2 sixteenth
+    uint64_t picture_number;
+};
+
+// Device result buffers of one picture (same layout as SvtMePictureResults).
+struct DevResults {
+    uint32_t *me_mv;
+    uint8_t  *me_cand;
+    uint8_t  *total_me_candidate_index;
+    uint32_t *me_64x64_distortion, *me_32x32_distortion, *me_16x16_distortion, *me_8x8_distortion;
+    uint32_t *me_8x8_cost_variance, *rc_me_distortion;
+    uint8_t  *stationary_block_present_sb, *rc_me_allow_gm;
+    uint32_t *sb_best_sad, *sb_best_mv;  // optional
+    uint8_t  *do_ref;                    // optional
+    int16_t  *hme_sc;                    // optional
+};
+
+struct MeParams {
+    SvtMeKnobs k;
+    DevPic     cur;
+    DevPic     refs[kMaxLists][kMaxRefs];
+    DevResults out;
+    uint32_t   wb, hb;      // picture size in 64x64 blocks
+    uint32_t   pu_count;    // 85 / 21 / 5
+    uint32_t  *work_counter;  // persistent-CTA SB queue
+};
+
+// ---- work descriptors produced by the per-SB control code and consumed by the search engines ----
+
+// One svt_sad_loop_kernel call (compute_sad_c.c:58): block (block_w x rows, rows at blk_stride) against every
+// position of an sa_w x sa_h window whose rows are raw_stride apart; block rows sample the reference at ref_stride.
+struct SadJob {
+    const uint8_t *blk;
+    const uint8_t *ref;
+    int32_t        blk_stride, ref_stride, raw_stride;
+    int16_t        rows, block_w;
+    int16_t        sa_w, sa_h;
+    int16_t        sa_ox, sa_oy;  // window origin relative to the block position (added to the result)
+    uint8_t        skip_line;     // search odd candidate rows only (16-wide blocks of <= 16 rows)
+    uint8_t        mv_scale;      // 4 / 2 / 1
+    uint8_t        level, li, ri, qw, qh;  // destination: HME level (3 = pre-HME, qw = search region)
+    uint8_t        found;
+    uint32_t       best_sad;  // raw (not doubled)
+    int16_t        bx, by;    // raw argmin inside the window
+};
+
+// One svt_nxm_sad_kernel call (compute_sad_c.c:209)
+struct NxmJob {
+    const uint8_t *src;
+    const uint8_t *ref;
+    int32_t        src_stride, ref_stride;
+    int16_t        rows, width;
+    uint8_t        li, ri, kind;
+    uint32_t       sad;
+};
+
+// One open_loop_me_fullpel_search_sblock call (motion_estimation.c:781)
+struct FpJob {
+    const uint8_t *ref;  // reference pixel under the block's top-left for MV (xo, yo)
+    int32_t        ref_stride;
+    int16_t        xo, yo;
+    int16_t        w, h;
+    uint8_t        li, ri;
+};
+
+struct PreHme {
+    uint64_t sad;
+    uint16_t sa_w, sa_h;
+    int16_t  mv_x, mv_y;
+    uint8_t  valid;
+};
+
+constexpr int kMaxSadJobs = 32;
+constexpr int kMaxNxmJobs = 16;
+constexpr int kMaxFpJobs  = 8;
+
+// SB-scoped part of the reference's MeContext (me_context.h:366-509); lives in shared memory on the device.
+struct SbState {
+    uint64_t lsad[3][kMaxLists][kMaxRefs][2][2];  // hme_level{0,1,2}_sad[l][r][w][h]
+    uint64_t hme_sad[kMaxLists][kMaxRefs];
+    PreHme   prehme[kMaxLists][kMaxRefs][2];
+    int16_t  lx[3][kMaxLists][kMaxRefs][2][2], ly[3][kMaxLists][kMaxRefs][2][2];
+    int16_t  hme_sc_x[kMaxLists][kMaxRefs], hme_sc_y[kMaxLists][kMaxRefs];
+    uint32_t divisor[kMaxLists][kMaxRefs];
+    uint32_t zz_sad[kMaxLists][kMaxRefs];
+    uint32_t best_sad[kMaxLists][kMaxRefs][kPus], best_mv[kMaxLists][kMaxRefs][kPus];
+    uint32_t me_distortion[kPus];
+    uint8_t  do_ref[kMaxLists][kMaxRefs];
+    uint8_t  performed_phme[kMaxLists][kMaxRefs][2];
+    SvtMeAreaMinMax hme_l0_sa;
+    uint32_t org_x, org_y, b64_w, b64_h, b64_index;
+    const uint8_t *src;  // b64_src_ptr
+    int32_t  src_stride;
+    // integer-search scratch per reference
+    int16_t  isc_x[kMaxLists][kMaxRefs], isc_y[kMaxLists][kMaxRefs];    // search centre after check_00_center
+    int16_t  isa_w[kMaxLists][kMaxRefs], isa_h[kMaxLists][kMaxRefs];    // search area
+    int16_t  isa_w0[kMaxLists][kMaxRefs], isa_h0[kMaxLists][kMaxRefs];  // before SR reduction
+    uint32_t c00_sad[kMaxLists][kMaxRefs];
+    uint8_t  c00_done[kMaxLists][kMaxRefs];
+    uint8_t  probe[kMaxLists][kMaxRefs];
+    // job lists
+    SadJob   sad_jobs[kMaxSadJobs];
+    NxmJob   nxm_jobs[kMaxNxmJobs];
+    FpJob    fp_jobs[kMaxFpJobs];
+    int32_t  n_sad, n_nxm, n_fp;
+};
+
+}  // namespace svtme
