@@ -202,6 +202,8 @@ typedef struct SvtMeDeviceCfg {
     uint32_t max_height;
     uint32_t max_pictures;      /* device picture slots (source + references in flight); 0 => 64 */
     uint32_t max_inflight;      /* concurrent picture searches (streams); 0 => 4 */
+    uint32_t sixteenth_from_full; /* 1: HME level 1 is off, the sixteenth plane is decimated from the full plane with
+                                   * step 4 (pic_analysis_process.c:1981-1992); 0: from the quarter plane with step 2 */
 } SvtMeDeviceCfg;
 
 typedef struct SvtMeHandle SvtMeHandle;   /* opaque */

@@ -1,0 +1,634 @@
+// abi.cu -- the extern "C" boundary of libsvtme_cuda.so (include/svtme_cuda.h).
+//
+// Host-side runtime of the library: device picture pool (three padded luma planes per picture in HBM),
+// per-search result arenas (device + pinned host mirror), a stream per in-flight picture, and the RTCD-level
+// single-call entry points.  There is NO CPU implementation behind any entry point: every call either runs
+// the CUDA kernels or returns an error code.
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/svtme_cuda.h"
+#include "me_launch.h"
+
+using namespace svtme;
+
+namespace {
+
+// Device plane geometry: padding >= the reference's (72 / 32 / 16: enc_handle.c:4057-4070, reference_object.c:267-295)
+// rounded so that pixel (0,0) and every row start are 16-byte aligned and aligned vector loads of a search window
+// never leave the allocation.
+constexpr int kPad[3]    = {96, 48, 32};
+constexpr int kRefOrg[3] = {72, 32, 16};
+
+struct PlaneGeom {
+    int    w, h, pad, stride;
+    size_t offset, bytes;
+};
+
+struct PicBuffer {
+    uint8_t    *base = nullptr;
+    size_t      bytes = 0;
+    uint32_t    w = 0, h = 0;
+    cudaEvent_t last_use = nullptr;  // last search that read this buffer
+    bool        used_once = false;
+};
+
+}  // namespace
+
+struct SvtMePic {
+    uint64_t    picture_number;
+    uint32_t    width, height;
+    PicBuffer   buf;
+    DevPic      dev;
+    PlaneGeom   geom[3];
+    cudaEvent_t ready;
+    cudaStream_t stream;
+    uint16_t   *staging16;
+};
+
+namespace {
+
+struct ResultLayout {
+    size_t   off[15];
+    size_t   bytes[15];
+    size_t   total;
+};
+enum { R_MV, R_CAND, R_COUNT, R_D64, R_D32, R_D16, R_D8, R_VAR, R_RC, R_STAT, R_GM, R_SAD, R_BMV, R_DOREF, R_HMESC, R_N };
+
+struct Inflight {
+    cudaStream_t        stream = nullptr;
+    cudaEvent_t         ev_start = nullptr, ev_kernel = nullptr, ev_done = nullptr;
+    uint8_t            *d_res = nullptr, *h_res = nullptr;
+    size_t              cap = 0;
+    uint32_t           *d_counter = nullptr;
+    ResultLayout        lay{};
+    SvtMePictureResults user{};
+    bool                to_host = false, busy = false;
+    uint64_t            ticket = 0;
+    float               ms = 0.f;
+};
+
+}  // namespace
+
+struct SvtMeHandle {
+    SvtMeDeviceCfg         cfg;
+    std::mutex             mu;
+    std::vector<PicBuffer> free_bufs;
+    std::vector<Inflight>  slots;
+    std::vector<cudaStream_t> up_streams;
+    size_t                 next_up = 0;
+    uint64_t               next_ticket = 1;
+    uint64_t               launches = 0;
+    int                    sm_count = 0, ctas_per_sm = 0;
+    std::string            err;
+    // RTCD-level scratch
+    uint8_t               *d_scratch = nullptr;
+    size_t                 scratch_bytes = 0;
+    uint32_t              *d_small = nullptr;
+    float                  last_ms = 0.f;
+};
+
+namespace {
+
+int fail(SvtMeHandle *h, int code, const char *what, cudaError_t e = cudaSuccess) {
+    if (h) {
+        h->err = what;
+        if (e != cudaSuccess) { h->err += ": "; h->err += cudaGetErrorString(e); }
+    }
+    return code;
+}
+#define CK(call)                                                                  \
+    do {                                                                          \
+        cudaError_t e_ = (call);                                                  \
+        if (e_ != cudaSuccess) return fail(h, SVTME_ERR_UNDEFINED, #call, e_);    \
+    } while (0)
+
+void plane_geometry(uint32_t w, uint32_t h, PlaneGeom g[3], size_t *total) {
+    size_t off = 0;
+    for (int l = 0; l < 3; l++) {
+        g[l].w = (int)(w >> l); g[l].h = (int)(h >> l); g[l].pad = kPad[l];
+        g[l].stride = (g[l].w + 2 * g[l].pad + 127) & ~127;
+        g[l].offset = off;
+        g[l].bytes  = (size_t)g[l].stride * (g[l].h + 2 * g[l].pad) + 256;  // slack for aligned over-reads of the last row
+        off += (g[l].bytes + 255) & ~size_t(255);
+    }
+    *total = off;
+}
+
+int set_device(SvtMeHandle *h) {
+    CK(cudaSetDevice(h->cfg.device));
+    return SVTME_OK;
+}
+
+int acquire_buffer(SvtMeHandle *h, uint32_t w, uint32_t hgt, size_t bytes, PicBuffer *out) {
+    for (size_t i = 0; i < h->free_bufs.size(); i++)
+        if (h->free_bufs[i].bytes >= bytes && h->free_bufs[i].bytes <= bytes + bytes / 4) {
+            *out = h->free_bufs[i];
+            h->free_bufs.erase(h->free_bufs.begin() + i);
+            out->w = w; out->h = hgt;
+            return SVTME_OK;
+        }
+    PicBuffer b;
+    cudaError_t e = cudaMalloc(&b.base, bytes);
+    if (e != cudaSuccess) return fail(h, SVTME_ERR_INSUFFICIENT, "cudaMalloc(picture planes)", e);
+    b.bytes = bytes; b.w = w; b.h = hgt;
+    e = cudaEventCreateWithFlags(&b.last_use, cudaEventDisableTiming);
+    if (e != cudaSuccess) { cudaFree(b.base); return fail(h, SVTME_ERR_UNDEFINED, "cudaEventCreate", e); }
+    *out = b;
+    return SVTME_OK;
+}
+
+int make_pic(SvtMeHandle *h, uint64_t picture_number, uint32_t width, uint32_t height, SvtMePic **out) {
+    if (!h || !out || width == 0 || height == 0 || (width & 7) || (height & 7)) return fail(h, SVTME_ERR_BAD_PARAMETER, "width/height must be non-zero multiples of 8");
+    if (width > 16384 || height > 16384) return fail(h, SVTME_ERR_BAD_PARAMETER, "picture too large (int16 MV arithmetic)");
+    int rc = set_device(h);
+    if (rc) return rc;
+    SvtMePic *p = new SvtMePic();
+    p->picture_number = picture_number; p->width = width; p->height = height; p->staging16 = nullptr;
+    size_t total;
+    plane_geometry(width, height, p->geom, &total);
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        rc = acquire_buffer(h, width, height, total, &p->buf);
+        p->stream = h->up_streams[h->next_up++ % h->up_streams.size()];
+    }
+    if (rc) { delete p; return rc; }
+    for (int l = 0; l < 3; l++) {
+        const PlaneGeom &g = p->geom[l];
+        p->dev.lvl[l].org     = p->buf.base + g.offset + (size_t)g.pad * g.stride + g.pad;
+        p->dev.lvl[l].stride  = g.stride;
+        p->dev.lvl[l].width   = g.w;
+        p->dev.lvl[l].height  = g.h;
+        p->dev.lvl[l].ref_org = kRefOrg[l];
+    }
+    p->dev.picture_number = picture_number;
+    cudaError_t e = cudaEventCreateWithFlags(&p->ready, cudaEventDisableTiming);
+    if (e != cudaSuccess) { delete p; return fail(h, SVTME_ERR_UNDEFINED, "cudaEventCreate", e); }
+    // a recycled buffer may still be read by a search in flight
+    if (p->buf.used_once) cudaStreamWaitEvent(p->stream, p->buf.last_use, 0);
+    *out = p;
+    return SVTME_OK;
+}
+
+// pad the full plane, build quarter + sixteenth (+ padding), signal `ready`
+int build_planes(SvtMeHandle *h, SvtMePic *p) {
+    uint8_t *org = const_cast<uint8_t *>(p->dev.lvl[0].org);
+    CK(launch_pad_plane(org, p->geom[0].stride, p->geom[0].w, p->geom[0].h, p->geom[0].pad, p->stream));
+    CK(launch_decimate(p->dev, p->geom[1].pad, p->geom[2].pad, h->cfg.sixteenth_from_full ? 1 : 0, p->stream));
+    CK(cudaEventRecord(p->ready, p->stream));
+    std::lock_guard<std::mutex> lk(h->mu);
+    h->launches += 2;
+    return SVTME_OK;
+}
+
+void result_layout(uint32_t n_b64, uint32_t pu_count, const SvtMeKnobs &k, bool extended, ResultLayout *L) {
+    const size_t n = n_b64;
+    size_t sz[R_N] = {n * pu_count * k.max_refs * 4, n * pu_count * k.max_cand, n * pu_count, n * 4, n * 4, n * 4, n * 4,
+                      n * 4, n * 4, n, n, extended ? n * 680 * 4 : 0, extended ? n * 680 * 4 : 0, extended ? n * 8 : 0,
+                      extended ? n * 16 * 2 : 0};
+    size_t off = 0;
+    for (int i = 0; i < R_N; i++) {
+        L->off[i] = off; L->bytes[i] = sz[i];
+        off += (sz[i] + 255) & ~size_t(255);
+    }
+    L->total = off;
+}
+
+int validate_knobs(SvtMeHandle *h, const SvtMeKnobs *k, uint32_t pu_count) {
+    if (k->num_of_list_to_search < 1 || k->num_of_list_to_search > SVTME_MAX_LISTS) return fail(h, SVTME_ERR_BAD_PARAMETER, "num_of_list_to_search");
+    for (int l = 0; l < SVTME_MAX_LISTS; l++)
+        if (k->num_of_ref_pic_to_search[l] > SVTME_MAX_REFS_PER_LIST) return fail(h, SVTME_ERR_BAD_PARAMETER, "num_of_ref_pic_to_search");
+    if (k->num_of_ref_pic_to_search[0] < 1) return fail(h, SVTME_ERR_BAD_PARAMETER, "list 0 needs at least one reference");
+    if (k->num_hme_sa_w < 1 || k->num_hme_sa_w > 2 || k->num_hme_sa_h < 1 || k->num_hme_sa_h > 2) return fail(h, SVTME_ERR_BAD_PARAMETER, "num_hme_sa_w/h");
+    if (k->max_number_of_pus_per_sb != SVTME_SQUARE_PU_COUNT) return fail(h, SVTME_ERR_BAD_PARAMETER, "max_number_of_pus_per_sb must be 85");
+    const uint32_t want = k->enable_me_16x16 ? (k->enable_me_8x8 ? 85u : 21u) : 5u;
+    if (pu_count != want) return fail(h, SVTME_ERR_BAD_PARAMETER, "pu_count does not match enable_me_8x8/16x16");
+    if (k->max_refs == 0 || k->max_cand == 0) return fail(h, SVTME_ERR_BAD_PARAMETER, "max_refs/max_cand");
+    const uint32_t n0 = k->num_of_ref_pic_to_search[0], n1 = k->num_of_list_to_search > 1 ? k->num_of_ref_pic_to_search[1] : 0;
+    if (k->max_l0 < n0 || (uint32_t)k->max_l0 + n1 > k->max_refs) return fail(h, SVTME_ERR_BAD_PARAMETER, "max_l0/max_refs too small for the reference lists");
+    const uint32_t need_cand = (n0 == 1 && n1 <= 1) ? (n1 ? 3u : 1u) : n0 + n1 + n0 * n1 + (n0 ? n0 - 1 : 0) + (n1 == 3 ? 1 : 0);
+    if (k->max_cand < need_cand) return fail(h, SVTME_ERR_BAD_PARAMETER, "max_cand too small for the reference lists");
+    return SVTME_OK;
+}
+
+int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
+                const SvtMeKnobs *knobs, SvtMePictureResults *out, uint32_t pu_count_dev, bool extended, uint64_t *ticket) {
+    if (!h || !cur || !refs || !knobs || !ticket) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    const uint32_t wb = (cur->width + 63) / 64, hb = (cur->height + 63) / 64, n_b64 = wb * hb;
+    const uint32_t pu_count = out ? out->pu_count : pu_count_dev;
+    int rc = validate_knobs(h, knobs, pu_count);
+    if (rc) return rc;
+    if (out && out->b64_total_count < n_b64) return fail(h, SVTME_ERR_BAD_PARAMETER, "b64_total_count too small");
+    for (int l = 0; l < knobs->num_of_list_to_search; l++)
+        for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) {
+            if (!refs[l][r]) return fail(h, SVTME_ERR_BAD_PARAMETER, "missing reference picture");
+            if (refs[l][r]->width != cur->width || refs[l][r]->height != cur->height) return fail(h, SVTME_ERR_BAD_PARAMETER, "reference size differs");
+        }
+    rc = set_device(h);
+    if (rc) return rc;
+
+    // pick a slot (wait for the oldest if all are busy)
+    Inflight *sl = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        for (auto &s : h->slots)
+            if (!s.busy) { sl = &s; break; }
+        if (!sl) return fail(h, SVTME_ERR_INSUFFICIENT, "all search slots in flight: call svtme_search_wait first");
+        sl->busy = true;
+        sl->ticket = h->next_ticket++;
+    }
+    auto release_slot = [&](int code) { std::lock_guard<std::mutex> lk(h->mu); sl->busy = false; return code; };
+    result_layout(n_b64, pu_count, *knobs, extended, &sl->lay);
+    if (sl->cap < sl->lay.total) {
+        if (sl->d_res) cudaFree(sl->d_res);
+        if (sl->h_res) cudaFreeHost(sl->h_res);
+        sl->d_res = nullptr; sl->h_res = nullptr; sl->cap = 0;
+        cudaError_t e = cudaMalloc(&sl->d_res, sl->lay.total);
+        if (e == cudaSuccess) e = cudaMallocHost(&sl->h_res, sl->lay.total);
+        if (e != cudaSuccess) return release_slot(fail(h, SVTME_ERR_INSUFFICIENT, "result arena", e));
+        sl->cap = sl->lay.total;
+    }
+    MeParams p;
+    memset(&p, 0, sizeof(p));
+    p.k   = *knobs;
+    p.cur = cur->dev;
+    for (int l = 0; l < knobs->num_of_list_to_search; l++)
+        for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) p.refs[l][r] = refs[l][r]->dev;
+    p.wb = wb; p.hb = hb; p.pu_count = pu_count; p.work_counter = sl->d_counter;
+    uint8_t *d = sl->d_res;
+    const ResultLayout &L = sl->lay;
+    p.out.me_mv = (uint32_t *)(d + L.off[R_MV]); p.out.me_cand = d + L.off[R_CAND]; p.out.total_me_candidate_index = d + L.off[R_COUNT];
+    p.out.me_64x64_distortion = (uint32_t *)(d + L.off[R_D64]); p.out.me_32x32_distortion = (uint32_t *)(d + L.off[R_D32]);
+    p.out.me_16x16_distortion = (uint32_t *)(d + L.off[R_D16]); p.out.me_8x8_distortion = (uint32_t *)(d + L.off[R_D8]);
+    p.out.me_8x8_cost_variance = (uint32_t *)(d + L.off[R_VAR]); p.out.rc_me_distortion = (uint32_t *)(d + L.off[R_RC]);
+    p.out.stationary_block_present_sb = d + L.off[R_STAT]; p.out.rc_me_allow_gm = d + L.off[R_GM];
+    if (extended) {
+        p.out.sb_best_sad = (uint32_t *)(d + L.off[R_SAD]); p.out.sb_best_mv = (uint32_t *)(d + L.off[R_BMV]);
+        p.out.do_ref = d + L.off[R_DOREF]; p.out.hme_sc = (int16_t *)(d + L.off[R_HMESC]);
+    }
+    cudaStream_t st = sl->stream;
+    cudaError_t  e  = cudaStreamWaitEvent(st, cur->ready, 0);
+    for (int l = 0; l < knobs->num_of_list_to_search && e == cudaSuccess; l++)
+        for (int r = 0; r < knobs->num_of_ref_pic_to_search[l] && e == cudaSuccess; r++) e = cudaStreamWaitEvent(st, refs[l][r]->ready, 0);
+    if (e == cudaSuccess) e = cudaMemsetAsync(sl->d_counter, 0, 4, st);
+    if (e == cudaSuccess) e = cudaEventRecord(sl->ev_start, st);
+    const int grid = (int)std::min<uint32_t>(n_b64, (uint32_t)(h->sm_count * h->ctas_per_sm));
+    if (e == cudaSuccess) e = launch_me_picture(p, grid, st);
+    if (e == cudaSuccess) e = cudaEventRecord(sl->ev_kernel, st);
+    sl->to_host = out != nullptr;
+    if (out) {
+        sl->user = *out;
+        if (e == cudaSuccess) e = cudaMemcpyAsync(sl->h_res, sl->d_res, L.total, cudaMemcpyDeviceToHost, st);
+    }
+    if (e == cudaSuccess) e = cudaEventRecord(sl->ev_done, st);
+    // the planes must outlive this search
+    if (e == cudaSuccess) e = cudaEventRecord(cur->buf.last_use, st);
+    cur->buf.used_once = true;
+    for (int l = 0; l < knobs->num_of_list_to_search && e == cudaSuccess; l++)
+        for (int r = 0; r < knobs->num_of_ref_pic_to_search[l] && e == cudaSuccess; r++) {
+            e = cudaEventRecord(refs[l][r]->buf.last_use, st);
+            refs[l][r]->buf.used_once = true;
+        }
+    if (e != cudaSuccess) return release_slot(fail(h, SVTME_ERR_UNDEFINED, "search launch", e));
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        h->launches += 1;
+    }
+    *ticket = sl->ticket;
+    return SVTME_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t svtme_init(const SvtMeDeviceCfg *cfg, SvtMeHandle **out) {
+    if (!cfg || !out) return SVTME_ERR_BAD_PARAMETER;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) return SVTME_ERR_UNDEFINED;  // no CUDA device: no fallback
+    if (cfg->device < 0 || cfg->device >= n) return SVTME_ERR_BAD_PARAMETER;
+    SvtMeHandle *h = new SvtMeHandle();
+    h->cfg = *cfg;
+    if (h->cfg.max_pictures == 0) h->cfg.max_pictures = 64;
+    if (h->cfg.max_inflight == 0) h->cfg.max_inflight = 4;
+    const uint32_t inflight = h->cfg.max_inflight;
+    cudaError_t e = cudaSetDevice(cfg->device);
+    cudaDeviceProp prop;
+    if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, cfg->device);
+    if (e == cudaSuccess && prop.major < 10) { delete h; return SVTME_ERR_UNDEFINED; }  // built for sm_100a only
+    if (e == cudaSuccess) {
+        h->sm_count    = prop.multiProcessorCount;
+        h->ctas_per_sm = me_max_ctas_per_sm();
+        if (h->ctas_per_sm < 1) e = cudaErrorInvalidConfiguration;
+    }
+    h->slots.resize(inflight);
+    for (auto &s : h->slots) {
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreate(&s.ev_start);
+        if (e == cudaSuccess) e = cudaEventCreate(&s.ev_kernel);
+        if (e == cudaSuccess) e = cudaEventCreate(&s.ev_done);
+        if (e == cudaSuccess) e = cudaMalloc(&s.d_counter, 256);
+    }
+    h->up_streams.resize(std::max<uint32_t>(2, inflight));
+    for (auto &s : h->up_streams)
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_small, 4096);
+    if (e != cudaSuccess) { fprintf(stderr, "svtme_init: %s\n", cudaGetErrorString(e)); svtme_destroy(h); return SVTME_ERR_UNDEFINED; }
+    *out = h;
+    return SVTME_OK;
+}
+
+void svtme_destroy(SvtMeHandle *h) {
+    if (!h) return;
+    cudaSetDevice(h->cfg.device);
+    cudaDeviceSynchronize();
+    for (auto &s : h->slots) {
+        if (s.stream) cudaStreamDestroy(s.stream);
+        if (s.ev_start) cudaEventDestroy(s.ev_start);
+        if (s.ev_kernel) cudaEventDestroy(s.ev_kernel);
+        if (s.ev_done) cudaEventDestroy(s.ev_done);
+        if (s.d_res) cudaFree(s.d_res);
+        if (s.h_res) cudaFreeHost(s.h_res);
+        if (s.d_counter) cudaFree(s.d_counter);
+    }
+    for (auto &s : h->up_streams)
+        if (s) cudaStreamDestroy(s);
+    for (auto &b : h->free_bufs) { cudaFree(b.base); cudaEventDestroy(b.last_use); }
+    if (h->d_scratch) cudaFree(h->d_scratch);
+    if (h->d_small) cudaFree(h->d_small);
+    delete h;
+}
+
+int32_t svtme_picture_register(SvtMeHandle *h, uint64_t picture_number, const uint8_t *luma, uint32_t stride, uint32_t width,
+                               uint32_t height, SvtMePic **out) {
+    if (!luma || stride < width) return fail(h, SVTME_ERR_BAD_PARAMETER, "luma/stride");
+    SvtMePic *p = nullptr;
+    int rc = make_pic(h, picture_number, width, height, &p);
+    if (rc) return rc;
+    cudaError_t e = cudaMemcpy2DAsync(const_cast<uint8_t *>(p->dev.lvl[0].org), p->geom[0].stride, luma, stride, width, height,
+                                      cudaMemcpyHostToDevice, p->stream);
+    if (e != cudaSuccess) { svtme_picture_release(h, p); return fail(h, SVTME_ERR_UNDEFINED, "cudaMemcpy2DAsync(luma)", e); }
+    rc = build_planes(h, p);
+    if (rc) { svtme_picture_release(h, p); return rc; }
+    *out = p;
+    return SVTME_OK;
+}
+
+int32_t svtme_picture_register_device(SvtMeHandle *h, uint64_t picture_number, const void *d_luma, uint32_t stride, uint32_t width,
+                                      uint32_t height, SvtMePic **out) {
+    if (!d_luma || stride < width) return fail(h, SVTME_ERR_BAD_PARAMETER, "luma/stride");
+    SvtMePic *p = nullptr;
+    int rc = make_pic(h, picture_number, width, height, &p);
+    if (rc) return rc;
+    cudaError_t e = cudaMemcpy2DAsync(const_cast<uint8_t *>(p->dev.lvl[0].org), p->geom[0].stride, d_luma, stride, width, height,
+                                      cudaMemcpyDeviceToDevice, p->stream);
+    if (e != cudaSuccess) { svtme_picture_release(h, p); return fail(h, SVTME_ERR_UNDEFINED, "cudaMemcpy2DAsync(device luma)", e); }
+    rc = build_planes(h, p);
+    if (rc) { svtme_picture_release(h, p); return rc; }
+    *out = p;
+    return SVTME_OK;
+}
+
+int32_t svtme_picture_register16(SvtMeHandle *h, uint64_t picture_number, const uint16_t *luma16, uint32_t stride, uint32_t width,
+                                 uint32_t height, SvtMePic **out) {
+    if (!luma16 || stride < width) return fail(h, SVTME_ERR_BAD_PARAMETER, "luma/stride");
+    SvtMePic *p = nullptr;
+    int rc = make_pic(h, picture_number, width, height, &p);
+    if (rc) return rc;
+    cudaError_t e = cudaMalloc(&p->staging16, (size_t)width * height * 2);
+    if (e == cudaSuccess)
+        e = cudaMemcpy2DAsync(p->staging16, (size_t)width * 2, luma16, (size_t)stride * 2, (size_t)width * 2, height, cudaMemcpyHostToDevice, p->stream);
+    if (e == cudaSuccess)
+        e = launch_unpack16(p->staging16, (int)width, const_cast<uint8_t *>(p->dev.lvl[0].org), p->geom[0].stride, (int)width, (int)height, p->stream);
+    if (e != cudaSuccess) { svtme_picture_release(h, p); return fail(h, SVTME_ERR_UNDEFINED, "10-bit upload", e); }
+    { std::lock_guard<std::mutex> lk(h->mu); h->launches += 1; }
+    rc = build_planes(h, p);
+    if (rc) { svtme_picture_release(h, p); return rc; }
+    *out = p;
+    return SVTME_OK;
+}
+
+int32_t svtme_picture_wait(SvtMeHandle *h, SvtMePic *pic) {
+    if (!h || !pic) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    CK(cudaEventSynchronize(pic->ready));
+    return SVTME_OK;
+}
+
+int32_t svtme_picture_read_plane(SvtMeHandle *h, SvtMePic *pic, int32_t level, uint32_t pad, uint8_t *dst, uint32_t dst_stride) {
+    if (!h || !pic || !dst || level < 0 || level > 2) return fail(h, SVTME_ERR_BAD_PARAMETER, "argument");
+    const PlaneGeom &g = pic->geom[level];
+    if ((int)pad > g.pad || dst_stride < (uint32_t)g.w + 2 * pad) return fail(h, SVTME_ERR_BAD_PARAMETER, "pad/dst_stride");
+    int rc = set_device(h);
+    if (rc) return rc;
+    CK(cudaEventSynchronize(pic->ready));
+    const uint8_t *src = pic->dev.lvl[level].org - (size_t)pad * g.stride - pad;
+    CK(cudaMemcpy2D(dst, dst_stride, src, g.stride, g.w + 2 * pad, g.h + 2 * pad, cudaMemcpyDeviceToHost));
+    return SVTME_OK;
+}
+
+int32_t svtme_picture_release(SvtMeHandle *h, SvtMePic *pic) {
+    if (!h || !pic) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    cudaSetDevice(h->cfg.device);
+    if (pic->staging16) { cudaEventSynchronize(pic->ready); cudaFree(pic->staging16); }
+    // the buffer goes back to the pool; its next user waits on `last_use` (searches still reading it) on its own stream
+    cudaStreamWaitEvent(pic->stream, pic->ready, 0);
+    cudaEventDestroy(pic->ready);
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        if (h->free_bufs.size() < h->cfg.max_pictures) h->free_bufs.push_back(pic->buf);
+        else { cudaEventSynchronize(pic->buf.last_use); cudaFree(pic->buf.base); cudaEventDestroy(pic->buf.last_use); }
+    }
+    delete pic;
+    return SVTME_OK;
+}
+
+int32_t svtme_picture_search(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
+                             const SvtMeKnobs *knobs, SvtMePictureResults *out, uint64_t *ticket) {
+    if (!out || !out->me_mv || !out->me_cand || !out->total_me_candidate_index || !out->me_64x64_distortion ||
+        !out->me_32x32_distortion || !out->me_16x16_distortion || !out->me_8x8_distortion || !out->me_8x8_cost_variance ||
+        !out->rc_me_distortion || !out->stationary_block_present_sb || !out->rc_me_allow_gm)
+        return fail(h, SVTME_ERR_BAD_PARAMETER, "result buffers");
+    const bool extended = out->sb_best_sad || out->sb_best_mv || out->do_ref || out->hme_sc;
+    return search_impl(h, cur, refs, knobs, out, 0, extended, ticket);
+}
+
+int32_t svtme_picture_search_device(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
+                                    const SvtMeKnobs *knobs, uint64_t *ticket) {
+    if (!knobs) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    const uint32_t pu = knobs->enable_me_16x16 ? (knobs->enable_me_8x8 ? 85u : 21u) : 5u;
+    return search_impl(h, cur, refs, knobs, nullptr, pu, false, ticket);
+}
+
+static Inflight *find_slot(SvtMeHandle *h, uint64_t ticket) {
+    for (auto &s : h->slots)
+        if (s.ticket == ticket) return &s;
+    return nullptr;
+}
+
+int32_t svtme_search_wait(SvtMeHandle *h, uint64_t ticket) {
+    if (!h) return SVTME_ERR_BAD_PARAMETER;
+    Inflight *sl;
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        sl = find_slot(h, ticket);
+        if (!sl || !sl->busy) return fail(h, SVTME_ERR_BAD_PARAMETER, "unknown ticket");
+    }
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaEventSynchronize(sl->ev_done));
+    cudaEventElapsedTime(&sl->ms, sl->ev_start, sl->ev_kernel);
+    if (sl->to_host) {
+        const ResultLayout &L = sl->lay;
+        const SvtMePictureResults &u = sl->user;
+        void *dst[R_N] = {u.me_mv, u.me_cand, u.total_me_candidate_index, u.me_64x64_distortion, u.me_32x32_distortion,
+                          u.me_16x16_distortion, u.me_8x8_distortion, u.me_8x8_cost_variance, u.rc_me_distortion,
+                          u.stationary_block_present_sb, u.rc_me_allow_gm, u.sb_best_sad, u.sb_best_mv, u.do_ref, u.hme_sc};
+        for (int i = 0; i < R_N; i++)
+            if (dst[i] && L.bytes[i]) memcpy(dst[i], sl->h_res + L.off[i], L.bytes[i]);
+    }
+    std::lock_guard<std::mutex> lk(h->mu);
+    h->last_ms = sl->ms;
+    sl->busy = false;
+    return SVTME_OK;
+}
+
+int32_t svtme_search_elapsed_ms(SvtMeHandle *h, uint64_t ticket, float *ms) {
+    if (!h || !ms) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> lk(h->mu);
+    Inflight *sl = find_slot(h, ticket);
+    if (!sl || sl->busy) return fail(h, SVTME_ERR_BAD_PARAMETER, "ticket not completed (call svtme_search_wait first)");
+    *ms = sl->ms;
+    return SVTME_OK;
+}
+
+uint64_t svtme_launch_count(SvtMeHandle *h) {
+    if (!h) return 0;
+    std::lock_guard<std::mutex> lk(h->mu);
+    return h->launches;
+}
+
+const char *svtme_last_error(SvtMeHandle *h) { return h ? h->err.c_str() : "null handle"; }
+
+// ---- RTCD-level entry points: host pointers, synchronous.  Inputs are copied into an aligned device scratch. ----
+static uint8_t *scratch(SvtMeHandle *h, size_t bytes) {
+    if (h->scratch_bytes < bytes) {
+        if (h->d_scratch) cudaFree(h->d_scratch);
+        h->d_scratch = nullptr; h->scratch_bytes = 0;
+        if (cudaMalloc(&h->d_scratch, bytes) != cudaSuccess) return nullptr;
+        h->scratch_bytes = bytes;
+    }
+    return h->d_scratch;
+}
+static inline size_t al(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+void svtme_cuda_sad_loop_kernel(SvtMeHandle *h, const uint8_t *src, uint32_t src_stride, const uint8_t *ref, uint32_t ref_stride,
+                                uint32_t block_height, uint32_t block_width, uint64_t *best_sad, int16_t *x_search_center,
+                                int16_t *y_search_center, uint32_t src_stride_raw, uint8_t skip_search_line, int16_t search_area_width,
+                                int16_t search_area_height) {
+    *best_sad = 0xffffff;  // compute_sad_c.c:71
+    if (!h || block_width == 0 || block_height == 0 || block_width > 64 || block_height > 64 || search_area_width <= 0 || search_area_height <= 0) return;
+    if (src_stride_raw == 0 || ref_stride % src_stride_raw) { h->err = "ref_stride must be a multiple of src_stride_raw"; return; }
+    std::lock_guard<std::mutex> lk(h->mu);
+    cudaSetDevice(h->cfg.device);
+    // reference rows touched: (sa_h - 1) * raw + (bh - 1) * ref_stride + sa_w + bw - 1 bytes from `ref`
+    const size_t ref_rows  = (size_t)(search_area_height - 1) + (size_t)(block_height - 1) * (ref_stride / src_stride_raw) + 1;
+    const size_t ref_w     = (size_t)search_area_width + block_width - 1;
+    const size_t d_rstride = al(ref_w + 64, 128), d_sstride = 128;
+    const size_t need      = d_rstride * (ref_rows + 1) + d_sstride * block_height + 512;
+    uint8_t     *d         = scratch(h, need);
+    if (!d) { h->err = "scratch alloc"; return; }
+    uint8_t *d_ref = d, *d_src = d + al(d_rstride * (ref_rows + 1), 256);
+    cudaMemsetAsync(d, 0, need, 0);
+    cudaMemcpy2DAsync(d_ref, d_rstride, ref, src_stride_raw, ref_w, ref_rows, cudaMemcpyHostToDevice, 0);
+    cudaMemcpy2DAsync(d_src, d_sstride, src, src_stride, block_width, block_height, cudaMemcpyHostToDevice, 0);
+    SadJob j;
+    memset(&j, 0, sizeof(j));
+    j.blk = d_src; j.blk_stride = (int32_t)d_sstride;
+    j.ref = d_ref; j.raw_stride = (int32_t)d_rstride; j.ref_stride = (int32_t)(d_rstride * (ref_stride / src_stride_raw));
+    j.rows = (int16_t)block_height; j.block_w = (int16_t)block_width;
+    j.sa_w = search_area_width; j.sa_h = search_area_height; j.skip_line = skip_search_line; j.mv_scale = 1;
+    j.best_sad = 0xffffff;
+    uint32_t res[4] = {0, 0, 0, 0};
+    cudaError_t e = launch_rtcd_sad_loop(j, h->d_small, 0);
+    if (e == cudaSuccess) e = cudaMemcpy(res, h->d_small, sizeof(res), cudaMemcpyDeviceToHost);
+    h->launches++;
+    if (e != cudaSuccess) { h->err = cudaGetErrorString(e); return; }
+    if (res[0]) { *best_sad = res[1]; *x_search_center = (int16_t)(int32_t)res[2]; *y_search_center = (int16_t)(int32_t)res[3]; }
+}
+
+void svtme_cuda_downsample_2d(SvtMeHandle *h, const uint8_t *input_samples, uint32_t input_stride, uint32_t input_area_width,
+                              uint32_t input_area_height, uint8_t *decim_samples, uint32_t decim_stride, uint32_t decim_step) {
+    if (!h || decim_step < 2 || !input_area_width || !input_area_height) return;
+    std::lock_guard<std::mutex> lk(h->mu);
+    cudaSetDevice(h->cfg.device);
+    const size_t in_stride = al(input_area_width, 128);
+    const uint32_t ow = (input_area_width - (decim_step >> 1) + decim_step - 1) / decim_step;
+    const uint32_t oh = (input_area_height - (decim_step >> 1) + decim_step - 1) / decim_step;
+    const size_t out_stride = al(ow, 128);
+    uint8_t *d = scratch(h, in_stride * input_area_height + out_stride * oh + 512);
+    if (!d) { h->err = "scratch alloc"; return; }
+    uint8_t *d_in = d, *d_out = d + al(in_stride * input_area_height, 256);
+    cudaMemcpy2DAsync(d_in, in_stride, input_samples, input_stride, input_area_width, input_area_height, cudaMemcpyHostToDevice, 0);
+    cudaError_t e = launch_downsample_generic(d_in, (int)in_stride, (int)input_area_width, (int)input_area_height, d_out, (int)out_stride,
+                                              (int)decim_step, 0);
+    if (e == cudaSuccess) e = cudaMemcpy2D(decim_samples, decim_stride, d_out, out_stride, ow, oh, cudaMemcpyDeviceToHost);
+    h->launches++;
+    if (e != cudaSuccess) h->err = cudaGetErrorString(e);
+}
+
+uint32_t svtme_cuda_nxm_sad_kernel(SvtMeHandle *h, const uint8_t *src, uint32_t src_stride, const uint8_t *ref, uint32_t ref_stride,
+                                   uint32_t height, uint32_t width) {
+    if (!h || !width || !height) return 0;
+    std::lock_guard<std::mutex> lk(h->mu);
+    cudaSetDevice(h->cfg.device);
+    const size_t st = al(width, 128);
+    uint8_t *d = scratch(h, 2 * st * height + 512);
+    if (!d) { h->err = "scratch alloc"; return 0; }
+    uint8_t *d_src = d, *d_ref = d + al(st * height, 256);
+    cudaMemcpy2DAsync(d_src, st, src, src_stride, width, height, cudaMemcpyHostToDevice, 0);
+    cudaMemcpy2DAsync(d_ref, st, ref, ref_stride, width, height, cudaMemcpyHostToDevice, 0);
+    NxmJob j;
+    memset(&j, 0, sizeof(j));
+    j.src = d_src; j.ref = d_ref; j.src_stride = (int32_t)st; j.ref_stride = (int32_t)st; j.rows = (int16_t)height; j.width = (int16_t)width;
+    uint32_t res = 0;
+    cudaError_t e = launch_rtcd_nxm(j, h->d_small, 0);
+    if (e == cudaSuccess) e = cudaMemcpy(&res, h->d_small, 4, cudaMemcpyDeviceToHost);
+    h->launches++;
+    if (e != cudaSuccess) h->err = cudaGetErrorString(e);
+    return res;
+}
+
+void svtme_cuda_fullpel_search_sblock(SvtMeHandle *h, const uint8_t *src, uint32_t src_stride, const uint8_t *ref, uint32_t ref_stride,
+                                      int16_t x_search_area_origin, int16_t y_search_area_origin, uint32_t search_area_width,
+                                      uint32_t search_area_height, uint8_t sub_sad, uint32_t *best_sad, uint32_t *best_mv) {
+    if (!h || !search_area_width || !search_area_height || search_area_width > 32767 || search_area_height > 32767) return;
+    std::lock_guard<std::mutex> lk(h->mu);
+    cudaSetDevice(h->cfg.device);
+    const size_t ref_w = search_area_width + 63, ref_rows = search_area_height + 63;
+    const size_t d_rstride = al(ref_w + 64, 128);
+    const size_t need = d_rstride * (ref_rows + 1) + 128 * 64 + 2 * 85 * 4 + 1024;
+    uint8_t *d = scratch(h, need);
+    if (!d) { h->err = "scratch alloc"; return; }
+    uint8_t  *d_ref = d, *d_src = d + al(d_rstride * (ref_rows + 1), 256);
+    uint32_t *d_bs = (uint32_t *)(d_src + 128 * 64), *d_bm = d_bs + 88;
+    cudaMemsetAsync(d, 0, need, 0);
+    cudaMemcpy2DAsync(d_ref, d_rstride, ref, ref_stride, ref_w, ref_rows, cudaMemcpyHostToDevice, 0);
+    cudaMemcpy2DAsync(d_src, 128, src, src_stride, 64, 64, cudaMemcpyHostToDevice, 0);
+    cudaMemcpyAsync(d_bs, best_sad, 85 * 4, cudaMemcpyHostToDevice, 0);
+    cudaMemcpyAsync(d_bm, best_mv, 85 * 4, cudaMemcpyHostToDevice, 0);
+    FpJob j;
+    memset(&j, 0, sizeof(j));
+    j.ref = d_ref; j.ref_stride = (int32_t)d_rstride; j.xo = x_search_area_origin; j.yo = y_search_area_origin;
+    j.w = (int16_t)search_area_width; j.h = (int16_t)search_area_height;
+    cudaError_t e = launch_rtcd_fullpel(d_src, 128, j, sub_sad ? 1 : 0, d_bs, d_bm, 0);
+    if (e == cudaSuccess) e = cudaMemcpy(best_sad, d_bs, 85 * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(best_mv, d_bm, 85 * 4, cudaMemcpyDeviceToHost);
+    h->launches++;
+    if (e != cudaSuccess) h->err = cudaGetErrorString(e);
+}
+
+}  // extern "C"

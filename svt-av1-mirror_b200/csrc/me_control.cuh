@@ -139,6 +139,7 @@ SVTME_HD void sb_init(B &be, const MeParams &p, SbState &s, uint32_t b64_index) 
     be.sync();
     for (uint32_t i = be.tid(); i < kMaxLists * kMaxRefs * kPus; i += be.nthreads()) bs[i] = SVTME_MAX_SAD_VALUE;
     be.sync();
+    be.stage_src(s);  // engines keep the 64x64 source block on chip for the whole SB
 }
 
 #define SVTME_FOR_REFS(k, li, ri)                                \

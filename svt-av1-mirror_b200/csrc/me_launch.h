@@ -1,0 +1,19 @@
+// me_launch.h -- host-callable launch wrappers of the device kernels (me_kernel.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include "me_types.cuh"
+
+namespace svtme {
+size_t      me_smem_bytes();
+int         me_max_ctas_per_sm();
+cudaError_t launch_me_picture(const MeParams &p, int grid, cudaStream_t st);
+cudaError_t launch_pad_plane(uint8_t *org, int stride, int w, int h, int pad, cudaStream_t st);
+cudaError_t launch_decimate(const DevPic &pic, int pad_q, int pad_s, int sixteenth_from_full, cudaStream_t st);
+cudaError_t launch_unpack16(const uint16_t *in, int in_stride, uint8_t *out, int out_stride, int w, int h, cudaStream_t st);
+cudaError_t launch_downsample_generic(const uint8_t *in, int in_stride, int w, int h, uint8_t *out, int out_stride, int step,
+                                      cudaStream_t st);
+cudaError_t launch_rtcd_sad_loop(const SadJob &job, uint32_t *d_out, cudaStream_t st);
+cudaError_t launch_rtcd_nxm(const NxmJob &job, uint32_t *d_out, cudaStream_t st);
+cudaError_t launch_rtcd_fullpel(const uint8_t *src, int src_stride, const FpJob &job, int sub_sad, uint32_t *d_best_sad,
+                                uint32_t *d_best_mv, cudaStream_t st);
+}  // namespace svtme

@@ -8,7 +8,7 @@
 #include "../../include/svtme_cuda.h"
 
 #if defined(__CUDACC__)
-#define SVTME_HD __host__ __device__ __forceinline__
+#define SVTME_HD __device__ __forceinline__
 #define SVTME_D __device__ __forceinline__
 #else
 #define SVTME_HD inline

@@ -145,6 +145,7 @@ class DeviceCfg(C.Structure):
         ("max_height", C.c_uint32),
         ("max_pictures", C.c_uint32),
         ("max_inflight", C.c_uint32),
+        ("sixteenth_from_full", C.c_uint32),
     ]
 
 

@@ -17,6 +17,7 @@ struct ScalarBackend {
     void     sync() const {}
     uint32_t tid() const { return 0; }
     uint32_t nthreads() const { return 1; }
+    void     stage_src(const SbState &) const {}
 
     static uint32_t sad(const uint8_t *a, int as, const uint8_t *b, int bs, int rows, int w) {
         uint32_t s = 0;

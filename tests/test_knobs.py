@@ -1,0 +1,53 @@
+"""svtme_derive_knobs (csrc/knobs.cc, host code of the product) against the reference's own svt_aom_sig_deriv_me +
+MRP tables driven through oracle/_ref, over the preset / resolution / layer / mode grid.  CPU only."""
+import ctypes as C
+import itertools
+
+import pytest
+
+from svtme import api
+
+Q16 = 1 << 16
+SIZES = [(320, 192), (640, 360), (832, 480), (1280, 720), (1920, 1080), (3840, 2160), (7680, 4320)]
+
+
+def _bytes(k):
+    return bytes(C.string_at(C.addressof(k), C.sizeof(k)))
+
+
+def _diff(a, b):
+    da, db = a.as_dict(), b.as_dict()
+    return {n: (da[n], db[n]) for n in da if da[n] != db[n]}
+
+
+@pytest.mark.parametrize("enc_mode", list(range(-1, 14)))
+def test_knobs_match_reference(reference, enc_mode):
+    n = 0
+    for (w, h), tl, hl, rtc, sc, vbr, fd, qp in itertools.product(SIZES, [0, 1, 3], [3, 4], [0, 1], [0, 1], [0, 1], [0, 2],
+                                                                 [20, 35, 63]):
+        if (vbr and (rtc or sc)) or (fd and (rtc or sc or qp != 35)) or (hl == 4 and qp != 35):
+            continue
+        for b_slice in ((1, 0) if (tl == 1 and qp == 35) else (1,)):
+            kw = dict(enc_mode=enc_mode, rtc_tune=rtc, sc_class1=sc, rate_control_vbr=vbr, fast_decode=fd, qp=qp,
+                      frame_rate_q16=30 * Q16, width=w, height=h, hierarchical_levels=hl, picture_number=8,
+                      temporal_layer_index=tl, is_ref=1 if tl < hl else 0, slice_type_b=b_slice)
+            a = reference.derive_knobs(**kw)
+            b = api.derive_knobs(**kw)
+            assert _bytes(a) == _bytes(b), "%s: %s" % (kw, _diff(a, b))
+            n += 1
+    assert n > 100
+
+
+def test_knobs_misc(reference):
+    for kw in (dict(enc_mode=6, frame_rate_q16=0), dict(enc_mode=4, ref_list0_count_try=1, ref_list1_count_try=0),
+               dict(enc_mode=8, ref_list0_count_try=2, ref_list1_count_try=1, similar_brightness_refs=1)):
+        kw = dict(dict(qp=35, frame_rate_q16=60 * Q16, width=1920, height=1080, hierarchical_levels=4, picture_number=3,
+                       temporal_layer_index=2, is_ref=1, slice_type_b=1), **kw)
+        assert _bytes(reference.derive_knobs(**kw)) == _bytes(api.derive_knobs(**kw)), kw
+
+
+def test_bad_preset_rejected():
+    with pytest.raises(api.SvtMeError):
+        api.derive_knobs(enc_mode=14, width=64, height=64)
+    with pytest.raises(api.SvtMeError):
+        api.derive_knobs(enc_mode=3, width=0, height=64)

@@ -1,0 +1,88 @@
+// sadrate.cu -- microbenchmark: peak issue rate of the packed-byte SAD instruction (VABSDIFF4.U8.ACC) on B200,
+// alone and mixed with the funnel shifts / shared-memory loads a SAD search needs.  Gives the INT-roofline
+// denominator P_sad.  Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o sadrate sadrate.cu
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+__device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) k(uint32_t *out, int iters, uint32_t seed) {
+    __shared__ uint32_t sm[2048];
+    for (int i = threadIdx.x; i < 2048; i += blockDim.x) sm[i] = i * 2654435761u + seed;
+    __syncthreads();
+    uint32_t a[8], acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { a[i] = seed * (i + 1) + threadIdx.x; acc[i] = 0; }
+    uint32_t b = seed ^ threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                if (MODE == 0) acc[i] = sad4(a[i], b, acc[i]);                       // pure SAD
+                if (MODE == 1) { acc[i] = sad4(__funnelshift_r(a[i], a[(i + 1) & 7], 8), b, acc[i]); }  // SHF + SAD
+                if (MODE == 2) acc[i] = acc[i] + (a[i] ^ b);                          // LOP3 + IADD (alu baseline)
+                if (MODE == 3) acc[i] = sad4(sm[(lane + i * 32 + u * 256 + it) & 2047], b, acc[i]);  // LDS + SAD
+                if (MODE == 4) { uint32_t w = sm[(lane + i * 32 + u * 256 + it) & 2047];
+                                 acc[i] = sad4(w, b, acc[i]); acc[(i + 1) & 7] = sad4(w, a[i], acc[(i + 1) & 7]);
+                                 acc[(i + 2) & 7] = sad4(w, a[(i + 3) & 7], acc[(i + 2) & 7]);
+                                 acc[(i + 3) & 7] = sad4(w, a[(i + 5) & 7], acc[(i + 3) & 7]); }  // 1 LDS : 4 SAD
+                if (MODE == 5) acc[i] = __sad(a[i], b, acc[i]);                      // scalar SAD (VABSDIFF)
+                if (MODE == 6) acc[i] = __dp4a(a[i], b, acc[i]);                     // IDP4A for comparison
+            }
+            b += acc[0] & 1;
+        }
+    }
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) r += acc[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+
+template <int MODE>
+void run(const char *name, int ops_per_inner, int ctas_per_sm) {
+    int dev = 0, sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    uint32_t *out;
+    const int grid = sms * ctas_per_sm, iters = 20000;
+    cudaMalloc(&out, (size_t)grid * 256 * 4);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    k<MODE><<<grid, 256>>>(out, 100, 1);
+    cudaDeviceSynchronize();
+    float best = 1e30f;
+    for (int r = 0; r < 5; r++) {
+        cudaEventRecord(e0);
+        k<MODE><<<grid, 256>>>(out, iters, r + 2);
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        if (ms < best) best = ms;
+    }
+    const double sads = (double)grid * 256 * iters * 32.0 * ops_per_inner;
+    printf("{\"bench\":\"%s\",\"ctas_per_sm\":%d,\"ms\":%.3f,\"Gsad4_per_s\":%.1f,\"Tpx_per_s\":%.2f,\"per_sm_per_clk_at_1965MHz\":%.2f}\n", name,
+           ctas_per_sm, best, sads / best / 1e6, sads * 4 / best / 1e9, sads / best / 1e3 / sms / 1965e3);
+    cudaFree(out);
+}
+
+int main() {
+    cudaDeviceProp p; cudaGetDeviceProperties(&p, 0);
+    printf("{\"gpu\":\"%s\",\"sms\":%d,\"clock_khz\":%d}\n", p.name, p.multiProcessorCount, p.clockRate);
+    for (int c = 1; c <= 4; c *= 2) {
+        run<0>("vabsdiff4.acc", 1, c);
+        run<1>("shf+vabsdiff4.acc", 1, c);
+        run<2>("lop3+iadd", 1, c);
+        run<3>("lds+vabsdiff4.acc", 1, c);
+        run<4>("lds+4xvabsdiff4.acc", 4, c);
+        run<5>("sad.u32", 1, c);
+        run<6>("dp4a", 1, c);
+    }
+    return 0;
+}
