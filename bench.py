@@ -1,0 +1,324 @@
+#!/usr/bin/env python
+"""bench.py -- open-loop ME pictures/s at 4K (BASELINE.json configs[2]: 3840x2160 8-bit, preset 6).
+
+One STEP = the hot path over one mini-GOP per GPU: every picture of the mini-GOP is decimated (quarter + sixteenth
+planes + padding) and every non-intra picture is searched against its reference lists (pre-HME, HME L0/L1/L2, full-pel
+64x64 search, pruning, candidates, per-SB statistics).  Pictures are independent objects: with N GPUs every rank runs
+its own mini-GOPs (weak scaling, no data-path collective).
+
+  value     device-resident: luma planes already in HBM, results stay in HBM
+  e2e       through the public C ABI with HOST buffers: H2D of every luma plane and D2H of every result inside the
+            timed region
+  roofline  dominant kernel (me_picture_kernel): algorithmic pixel-compares / kernel time against the measured
+            VABSDIFF4 issue peak (INT pipe -- SAD is not a tensor-core op), plus the HBM view of the same kernel
+  cpu_baseline / --impl reference: the UNMODIFIED reference C/AVX2 ME (oracle/_ref/libsvtref.so, compiled from the
+            reference's own sources) on the host cores, on a bounded sample of the same workload
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "svt-av1-mirror_b200"))
+
+import numpy as np  # noqa: E402
+
+Q16 = 1 << 16
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=6)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--width", type=int, default=3840)
+    ap.add_argument("--height", type=int, default=2160)
+    ap.add_argument("--preset", type=int, default=6)
+    ap.add_argument("--hier-levels", type=int, default=5, help="mini-GOP = 2^levels pictures")
+    ap.add_argument("--inflight", type=int, default=4)
+    ap.add_argument("--cpu-sample", type=int, default=3, help="pictures of the workload timed on the host cores")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class Workload:
+    """A synthetic 8-bit clip of one mini-GOP (+ its leading base picture) and its prediction structure."""
+
+    def __init__(self, args, seed):
+        from svtme import api, synth
+        self.w, self.h, self.hl = args.width, args.height, args.hier_levels
+        self.gop = 1 << self.hl
+        self.n_frames = self.gop + 1
+        self.frames = synth.make_clip(self.w, self.h, self.n_frames, seed=seed, kind="pan")
+        k0 = api.derive_knobs(enc_mode=args.preset, qp=35, frame_rate_q16=60 * Q16, width=self.w, height=self.h,
+                              hierarchical_levels=self.hl, picture_number=1, temporal_layer_index=1, is_ref=1, slice_type_b=1)
+        self.pics = []  # decode order
+        for e in synth.minigop_structure(self.n_frames, self.hl, k0.max_l0, max(1, k0.max_refs - k0.max_l0)):
+            k = api.derive_knobs(enc_mode=args.preset, qp=35, frame_rate_q16=60 * Q16, width=self.w, height=self.h,
+                                 hierarchical_levels=self.hl, picture_number=e["poc"], temporal_layer_index=e["temporal_layer"],
+                                 is_ref=e["is_ref"], slice_type_b=1, ref_list0_count_try=len(e["list0"]),
+                                 ref_list1_count_try=len(e["list1"]))
+            l0 = e["list0"][:k.num_of_ref_pic_to_search[0]]
+            l1 = e["list1"][:k.num_of_ref_pic_to_search[1]]
+            self.pics.append((e["poc"], k, l0, l1))
+        self.name = "%dx%d 8-bit 4:2:0 synthetic, preset M%d, mini-GOP %d (hier. levels %d), refs<=%d+%d" % (
+            self.w, self.h, args.preset, self.gop, self.hl, k0.max_l0, k0.max_refs - k0.max_l0)
+
+
+class ClockSampler(threading.Thread):
+    """SM clock + throttle reasons of one GPU sampled through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self._stop = index, [], set(), None, threading.Event()
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {getattr(nv, n): n[len("nvmlClocksThrottleReason"):] for n in dir(nv)
+                     if n.startswith("nvmlClocksThrottleReason") and n not in ("nvmlClocksThrottleReasonAll", "nvmlClocksThrottleReasonNone")}
+            while not self._stop.is_set():
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, n in names.items():
+                    if bit and (r & bit) and n != "GpuIdle":
+                        self.reasons.add(n)
+                time.sleep(0.05)
+        except Exception as ex:  # NVML missing: report that rather than invent clocks
+            self.reasons.add("nvml_unavailable:%s" % type(ex).__name__)
+
+    def stop(self):
+        self._stop.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def run_step_device(dev, wl, d_luma, inflight):
+    """Device-resident step: register every picture from HBM-resident luma, search in decode order, results stay in HBM."""
+    w, h = wl.w, wl.h
+    pics = {i: dev.register_device(d_luma.data_ptr() + i * w * h, w, w, h, i) for i in range(wl.n_frames)}
+    pending = []
+    for poc, k, l0, l1 in wl.pics:
+        refs = {(0, i): pics[p] for i, p in enumerate(l0)}
+        refs.update({(1, i): pics[p] for i, p in enumerate(l1)})
+        if len(pending) >= inflight:
+            dev.wait(pending.pop(0))
+        pending.append(dev.search_device_async(k, pics[poc], refs))
+    for t in pending:
+        dev.wait(t)
+    for p in pics.values():
+        p.release()
+
+
+def run_step_host(dev, wl, h_luma, outs, inflight):
+    """End-to-end step through the C ABI with host buffers: H2D of each luma plane, D2H of each picture's results."""
+    w, h = wl.w, wl.h
+    base = h_luma.data_ptr()
+    pics = {i: dev.register_ptr(base + i * w * h, w, w, h, i) for i in range(wl.n_frames)}
+    pending = []
+    for n, (poc, k, l0, l1) in enumerate(wl.pics):
+        refs = {(0, i): pics[p] for i, p in enumerate(l0)}
+        refs.update({(1, i): pics[p] for i, p in enumerate(l1)})
+        if len(pending) >= inflight:
+            dev.wait(pending.pop(0))
+        pending.append(dev.search_async(k, pics[poc], refs, out=outs[n])[0])
+    for t in pending:
+        dev.wait(t)
+    for p in pics.values():
+        p.release()
+
+
+def reference_arm(wl, n_pictures, steps, warmup):
+    """The reference's own CPU ME (oracle/_ref/libsvtref.so: its unmodified C sources + AVX2 twins) on the host cores.
+    One step = decimation + ME of `n_pictures` pictures of the workload (spread over the temporal layers)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refbind
+    kind = "reference"
+    if refbind.have_reference():
+        ref = refbind.Reference()
+        isa = ref.set_isa(1)
+        what = "reference C sources compiled by oracle/Makefile, %s kernels" % ("AVX2" if isa == 1 else "C")
+    else:
+        ref, kind, what = refbind.Oracle(), "port", "oracle restatement (oracle/_ref not built)"
+    cores = os.cpu_count() or 1
+    # sample: evenly spaced entries of the decode-order list (covers base, middle and top temporal layers)
+    idx = sorted(set(int(round(i * (len(wl.pics) - 1) / max(1, n_pictures - 1))) for i in range(n_pictures)))
+    sample = [wl.pics[i] for i in idx]
+    need = sorted(set(p for poc, k, l0, l1 in sample for p in [poc] + l0 + l1))
+    padded = {p: refbind.PaddedPicture(wl.frames[p], p) for p in need}
+    for p in need:
+        ref.build_planes(padded[p], 1)
+
+    def step():
+        for poc, k, l0, l1 in sample:
+            ref.build_planes(padded[poc], 1)  # decimation of the current picture is part of the path
+            refs = {(0, i): padded[p] for i, p in enumerate(l0)}
+            refs.update({(1, i): padded[p] for i, p in enumerate(l1)})
+            ref.me_picture(k, padded[poc], refs, n_threads=cores, extended=False)
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = time.perf_counter() - t0
+    pps = len(sample) * steps / dt
+    return {"value": pps, "unit": "pictures/s", "cores": cores, "kind": kind,
+            "sample": "%d pictures (decode-order %s) of the workload x %d steps, %s, %d threads" % (len(sample), idx, steps, what, cores)}, dt
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        wl = Workload(args, seed=100)
+        steps, warmup = max(1, min(args.steps, 3)), min(args.warmup, 1)
+        cb, dt = reference_arm(wl, args.cpu_sample, steps, warmup)
+        line = {"impl": "reference", "metric": "ME pictures/sec at 4K", "value": cb["value"], "unit": "pictures/s",
+                "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": wl.name, "l2": "inputs larger than L2"},
+                "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": "pictures/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    from svtme import abi, api
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    wl = Workload(args, seed=100 + rank)
+    dev = api.MeDevice(device=local_rank, max_inflight=args.inflight, max_pictures=2 * wl.n_frames)
+    w, h, nf = wl.w, wl.h, wl.n_frames
+    h_luma = torch.empty((nf, h, w), dtype=torch.uint8).pin_memory()
+    h_luma.numpy()[:] = np.stack(wl.frames)
+    d_luma = h_luma.cuda(non_blocking=False)
+    n_b64 = ((w + 63) // 64) * ((h + 63) // 64)
+    keep = []
+
+    def pinned(shape, dt):
+        t = torch.zeros(tuple(shape), dtype=getattr(torch, np.dtype(dt).name)).pin_memory()
+        keep.append(t)
+        return t.numpy()
+
+    outs = [abi.ResultBuffers(n_b64, k, extended=False, pinned_alloc=pinned) for _, k, _, _ in wl.pics]
+    d2h = sum(o.nbytes() for o in outs)
+    h2d = nf * w * h
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()  # every step ends with all of its searches waited for
+        torch.cuda.synchronize()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        barrier()
+        if dist is not None:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    step_dev = lambda: run_step_device(dev, wl, d_luma, args.inflight)  # noqa: E731
+    step_host = lambda: run_step_host(dev, wl, h_luma, outs, args.inflight)  # noqa: E731
+
+    for _ in range(max(3, args.warmup)):
+        step_dev()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    l0 = dev.launch_count()
+    ms_dev = timed(step_dev, args.steps)
+    launches = dev.launch_count() - l0
+    clocks = sampler.stop()
+    step_host()
+    ms_host = timed(step_host, args.steps)
+
+    # per-launch view of the dominant kernel: serialised launches, CUDA events around each (svtme_search_elapsed_ms)
+    px_total, ms_total, n_launch = 0, 0.0, 0
+    pics = {i: dev.register_device(d_luma.data_ptr() + i * w * h, w, w, h, i) for i in range(nf)}
+    for rep in range(2):
+        for poc, k, l0_, l1_ in wl.pics:
+            refs = {(0, i): pics[p] for i, p in enumerate(l0_)}
+            refs.update({(1, i): pics[p] for i, p in enumerate(l1_)})
+            t = dev.search_device_async(k, pics[poc], refs)
+            dev.wait(t)
+            if rep == 1:
+                px_total += dev.px_compares(t)
+                ms_total += dev.elapsed_ms(t)
+                n_launch += 1
+    for p in pics.values():
+        p.release()
+
+    pictures = wl.gop * args.steps * world
+    value = pictures / (ms_dev * 1e-3)
+    e2e = pictures / (ms_host * 1e-3)
+    if rank != 0:
+        return 0
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    sad_peak = dev.measure_sad_peak() * 4 / 1e3  # T pixel-compares/s
+    refs_avg = sum(len(l0_) + len(l1_) for _, _, l0_, l1_ in wl.pics) / len(wl.pics)
+    # compulsory HBM bytes of one search launch: source + every reference, three planes each (1.3125 B/px) + results
+    alg_bytes = (1 + refs_avg) * 1.3125 * w * h + d2h / len(wl.pics)
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["me_picture_kernel_dram_bytes_per_launch"]
+    except Exception:
+        pass
+    ach = px_total / (ms_total * 1e-3) / 1e12
+    roofline = {"bound": "int", "kernel": "me_picture_kernel", "achieved": ach, "peak": sad_peak, "unit": "Tpx-compares/s",
+                "frac": ach / sad_peak, "traffic": traffic,
+                "peak_source": "VABSDIFF4.U8.ACC issue rate measured in this run (svtme_measure_sad_peak) x 4 px",
+                "px_compares_per_launch": px_total / n_launch, "avg_launch_ms": ms_total / n_launch,
+                "hbm": {"achieved": alg_bytes / (ms_total / n_launch * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": alg_bytes / (ms_total / n_launch * 1e-3) / 1e9 / hbm_peak, "algorithmic_bytes_per_launch": alg_bytes,
+                        "peak_source": hbm_src}}
+    line = {"metric": "ME pictures/sec at 4K", "value": value, "unit": "pictures/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": wl.name, "pictures_per_step_per_gpu": wl.gop, "parallelism": "pictures sharded by mini-GOP, %d rank(s)" % world,
+                       "l2": "inputs larger than L2 (%.0f MB of planes per step)" % (nf * w * h * 1.55 / 1e6), "inflight": args.inflight},
+            "e2e": {"value": e2e, "unit": "pictures/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_host / args.steps},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline}
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"], _ = reference_arm(wl, args.cpu_sample, 1, 0)
+    print(json.dumps(line))
+    dev.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -261,6 +261,12 @@ int32_t svtme_picture_search_device(SvtMeHandle *h, SvtMePic *cur,
                                     SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
                                     const SvtMeKnobs *knobs, uint64_t *ticket);
 int32_t svtme_search_elapsed_ms(SvtMeHandle *h, uint64_t ticket, float *ms);
+/* Algorithmic work of a completed search: pixel-compares (block pixels x candidate positions summed over every SAD
+ * evaluation the reference's svt_sad_loop_kernel / svt_nxm_sad_kernel / full-pel scan would perform). */
+int32_t svtme_search_px_compares(SvtMeHandle *h, uint64_t ticket, uint64_t *px_compares);
+/* Diagnostic: measured peak issue rate of the packed-byte SAD instruction (VABSDIFF4.U8.ACC, 4 pixel-compares per
+ * lane) on this device, in 1e9 instructions per second; the INT-roofline denominator of DESIGN.md. */
+int32_t svtme_measure_sad_peak(SvtMeHandle *h, double *gsad4_per_s);
 /* Kernel launches issued by this handle so far (bench.py's gpu_launches). */
 uint64_t svtme_launch_count(SvtMeHandle *h);
 /* Last CUDA error string of this handle (for diagnostics). */

@@ -138,6 +138,11 @@ class Reference(_Binding):
 class Oracle(_Binding):
     def __init__(self):
         super().__init__(_load(os.path.join(HERE, "libsvtme_oracle.so"), "oracle restatement"), "svtorc_")
+        self.lib.svtorc_last_px_compares.restype = C.c_uint64
+
+    def last_px_compares(self):
+        """Pixel-compares of the last me_picture call (the algorithmic work C_alg of SURVEY.md section 8d)."""
+        return int(self.lib.svtorc_last_px_compares())
 
 
 def have_reference():

@@ -71,6 +71,8 @@ struct Inflight {
     bool                to_host = false, busy = false;
     uint64_t            ticket = 0;
     float               ms = 0.f;
+    unsigned long long *h_px = nullptr;  // pinned
+    unsigned long long  px = 0;
 };
 
 }  // namespace
@@ -260,6 +262,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     for (int l = 0; l < knobs->num_of_list_to_search; l++)
         for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) p.refs[l][r] = refs[l][r]->dev;
     p.wb = wb; p.hb = hb; p.pu_count = pu_count; p.work_counter = sl->d_counter;
+    p.px_counter = reinterpret_cast<unsigned long long *>(sl->d_counter + 2);
     uint8_t *d = sl->d_res;
     const ResultLayout &L = sl->lay;
     p.out.me_mv = (uint32_t *)(d + L.off[R_MV]); p.out.me_cand = d + L.off[R_CAND]; p.out.total_me_candidate_index = d + L.off[R_COUNT];
@@ -275,11 +278,12 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     cudaError_t  e  = cudaStreamWaitEvent(st, cur->ready, 0);
     for (int l = 0; l < knobs->num_of_list_to_search && e == cudaSuccess; l++)
         for (int r = 0; r < knobs->num_of_ref_pic_to_search[l] && e == cudaSuccess; r++) e = cudaStreamWaitEvent(st, refs[l][r]->ready, 0);
-    if (e == cudaSuccess) e = cudaMemsetAsync(sl->d_counter, 0, 4, st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(sl->d_counter, 0, 16, st);
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_start, st);
     const int grid = (int)std::min<uint32_t>(n_b64, (uint32_t)(h->sm_count * h->ctas_per_sm));
     if (e == cudaSuccess) e = launch_me_picture(p, grid, st);
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_kernel, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sl->h_px, sl->d_counter + 2, 8, cudaMemcpyDeviceToHost, st);
     sl->to_host = out != nullptr;
     if (out) {
         sl->user = *out;
@@ -333,6 +337,7 @@ int32_t svtme_init(const SvtMeDeviceCfg *cfg, SvtMeHandle **out) {
         if (e == cudaSuccess) e = cudaEventCreate(&s.ev_kernel);
         if (e == cudaSuccess) e = cudaEventCreate(&s.ev_done);
         if (e == cudaSuccess) e = cudaMalloc(&s.d_counter, 256);
+        if (e == cudaSuccess) e = cudaMallocHost(&s.h_px, 64);
     }
     h->up_streams.resize(std::max<uint32_t>(2, inflight));
     for (auto &s : h->up_streams)
@@ -355,6 +360,7 @@ void svtme_destroy(SvtMeHandle *h) {
         if (s.d_res) cudaFree(s.d_res);
         if (s.h_res) cudaFreeHost(s.h_res);
         if (s.d_counter) cudaFree(s.d_counter);
+        if (s.h_px) cudaFreeHost(s.h_px);
     }
     for (auto &s : h->up_streams)
         if (s) cudaStreamDestroy(s);
@@ -481,6 +487,7 @@ int32_t svtme_search_wait(SvtMeHandle *h, uint64_t ticket) {
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaEventSynchronize(sl->ev_done));
     cudaEventElapsedTime(&sl->ms, sl->ev_start, sl->ev_kernel);
+    sl->px = *sl->h_px;
     if (sl->to_host) {
         const ResultLayout &L = sl->lay;
         const SvtMePictureResults &u = sl->user;
@@ -505,10 +512,46 @@ int32_t svtme_search_elapsed_ms(SvtMeHandle *h, uint64_t ticket, float *ms) {
     return SVTME_OK;
 }
 
+int32_t svtme_search_px_compares(SvtMeHandle *h, uint64_t ticket, uint64_t *px) {
+    if (!h || !px) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> lk(h->mu);
+    Inflight *sl = find_slot(h, ticket);
+    if (!sl || sl->busy) return fail(h, SVTME_ERR_BAD_PARAMETER, "ticket not completed (call svtme_search_wait first)");
+    *px = sl->px;
+    return SVTME_OK;
+}
+
 uint64_t svtme_launch_count(SvtMeHandle *h) {
     if (!h) return 0;
     std::lock_guard<std::mutex> lk(h->mu);
     return h->launches;
+}
+
+int32_t svtme_measure_sad_peak(SvtMeHandle *h, double *gsad4_per_s) {
+    if (!h || !gsad4_per_s) return SVTME_ERR_BAD_PARAMETER;
+    std::lock_guard<std::mutex> lk(h->mu);
+    CK(cudaSetDevice(h->cfg.device));
+    const int grid = h->sm_count * 4, iters = 4000;
+    uint32_t *d = nullptr;
+    CK(cudaMalloc(&d, (size_t)grid * 256 * 4));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    float best = 1e30f;
+    cudaError_t e = cudaSuccess;
+    for (int r = 0; r < 6 && e == cudaSuccess; r++) {  // first pass is the warm-up
+        cudaEventRecord(e0, 0);
+        e = launch_sad_peak(d, grid, iters, 0);
+        cudaEventRecord(e1, 0);
+        if (e == cudaSuccess) e = cudaEventSynchronize(e1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (r > 0 && ms < best) best = ms;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    h->launches += 6;
+    if (e != cudaSuccess) return fail(h, SVTME_ERR_UNDEFINED, "sad peak probe", e);
+    *gsad4_per_s = (double)grid * 256 * iters * 32.0 / (best * 1e-3) / 1e9;
+    return SVTME_OK;
 }
 
 const char *svtme_last_error(SvtMeHandle *h) { return h ? h->err.c_str() : "null handle"; }

@@ -48,6 +48,7 @@ struct EngineShared {
     uint32_t           n_items;
     int32_t            cur_job, cur_x, cur_y;  // planning cursor
     uint32_t           next_sb;                // persistent-CTA work queue broadcast
+    unsigned long long px;                     // pixel-compares of this SB (algorithmic work, same definition as the oracle's)
     unsigned long long sad_key[kMaxSadJobs];
     unsigned long long fp_key[kMaxFpJobs][kPus];
     uint32_t           blk[64 * 16];   // HME source block of the current phase: [row][word], zero past block_w
@@ -76,6 +77,8 @@ struct CudaBackend {
     // ---------------------------------------------------------------------------------------------
     __device__ void run_nxm(SbState &s) const {
         const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+        if (threadIdx.x == 0)
+            for (int ji = 0; ji < s.n_nxm; ji++) sh->px += (unsigned long long)s.nxm_jobs[ji].rows * s.nxm_jobs[ji].width;
         for (int ji = warp; ji < s.n_nxm; ji += nwarps) {
             NxmJob        &j  = s.nxm_jobs[ji];
             const int      nw = (j.width + 3) >> 2;
@@ -175,7 +178,15 @@ struct CudaBackend {
             e.blk[r * 16 + c] = a;
         }
         for (int i = threadIdx.x; i < s.n_sad; i += blockDim.x) e.sad_key[i] = ~0ull;
-        if (threadIdx.x == 0) { e.cur_job = 0; e.cur_x = 0; e.cur_y = 0; }
+        if (threadIdx.x == 0) {
+            e.cur_job = 0; e.cur_x = 0; e.cur_y = 0;
+            for (int ji = 0; ji < s.n_sad; ji++) {
+                const SadJob &j = s.sad_jobs[ji];
+                if (j.sa_w <= 0 || j.sa_h <= 0) continue;
+                const bool skip = j.skip_line && j.block_w == 16 && j.rows <= 16;
+                e.px += (unsigned long long)j.sa_w * (skip ? (j.sa_h >> 1) : j.sa_h) * j.rows * j.block_w;
+            }
+        }
         __syncthreads();
 
         auto geom = [&](int ji) {
@@ -267,7 +278,11 @@ struct CudaBackend {
         EngineShared &e = *sh;
         constexpr int RSTEP = SUB ? 2 : 1;
         for (int i = threadIdx.x; i < s.n_fp * kPus; i += blockDim.x) (&e.fp_key[0][0])[i] = ~0ull;
-        if (threadIdx.x == 0) { e.cur_job = 0; e.cur_x = 0; e.cur_y = 0; }
+        if (threadIdx.x == 0) {
+            e.cur_job = 0; e.cur_x = 0; e.cur_y = 0;
+            for (int ji = 0; ji < s.n_fp; ji++)
+                if (s.fp_jobs[ji].w > 0 && s.fp_jobs[ji].h > 0) e.px += (unsigned long long)s.fp_jobs[ji].w * s.fp_jobs[ji].h * (SUB ? 64 * 32 : 64 * 64);
+        }
         __syncthreads();
         auto geom = [&](int ji) {
             const FpJob &j = s.fp_jobs[ji];

@@ -38,7 +38,9 @@ __global__ void __launch_bounds__(kThreads, 2) me_picture_kernel(const __grid_co
         __syncthreads();
         const uint32_t sb = cs->eng.next_sb;
         if (sb >= n_sb) break;
+        if (threadIdx.x == 0) cs->eng.px = 0;
         me_sb(be, p, cs->sb, sb);
+        if (threadIdx.x == 0 && p.px_counter) atomicAdd(p.px_counter, cs->eng.px);
     }
 }
 
@@ -179,6 +181,31 @@ __global__ void __launch_bounds__(kThreads) rtcd_fullpel_kernel(const uint8_t *s
     else be.run_fullpel_t<false>(s);
     __syncthreads();
     for (int i = threadIdx.x; i < kPus; i += blockDim.x) { best_sad[i] = s.best_sad[0][0][i]; best_mv[i] = s.best_mv[0][0][i]; }
+}
+
+// ---- INT-pipe peak probe: 8 independent VABSDIFF4.U8.ACC chains per thread, nothing else in the loop ----
+__global__ void __launch_bounds__(256) sad_peak_kernel(uint32_t *out, int iters, uint32_t seed) {
+    uint32_t a[8], acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { a[i] = seed * (i + 1) + threadIdx.x; acc[i] = 0; }
+    uint32_t b = seed ^ threadIdx.x;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) acc[i] = sad4(a[i], b, acc[i]);
+            b += acc[0] & 1;
+        }
+    }
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) r += acc[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+
+cudaError_t launch_sad_peak(uint32_t *d_out, int grid, int iters, cudaStream_t st) {
+    sad_peak_kernel<<<grid, 256, 0, st>>>(d_out, iters, 12345u);
+    return cudaGetLastError();
 }
 
 // ---- launch wrappers (host) ----

@@ -16,4 +16,5 @@ cudaError_t launch_rtcd_sad_loop(const SadJob &job, uint32_t *d_out, cudaStream_
 cudaError_t launch_rtcd_nxm(const NxmJob &job, uint32_t *d_out, cudaStream_t st);
 cudaError_t launch_rtcd_fullpel(const uint8_t *src, int src_stride, const FpJob &job, int sub_sad, uint32_t *d_best_sad,
                                 uint32_t *d_best_mv, cudaStream_t st);
+cudaError_t launch_sad_peak(uint32_t *d_out, int grid, int iters, cudaStream_t st);
 }  // namespace svtme

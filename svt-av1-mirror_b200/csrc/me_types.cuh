@@ -60,6 +60,7 @@ struct MeParams {
     uint32_t   wb, hb;      // picture size in 64x64 blocks
     uint32_t   pu_count;    // 85 / 21 / 5
     uint32_t  *work_counter;  // persistent-CTA SB queue
+    unsigned long long *px_counter;  // optional: algorithmic pixel-compares of the picture (roofline numerator)
 };
 
 // ---- work descriptors produced by the per-SB control code and consumed by the search engines ----

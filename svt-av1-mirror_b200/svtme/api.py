@@ -21,7 +21,7 @@ EXPORTS = [
     "svtme_init", "svtme_destroy", "svtme_derive_knobs", "svtme_picture_register", "svtme_picture_register16",
     "svtme_picture_register_device", "svtme_picture_wait", "svtme_picture_read_plane", "svtme_picture_release",
     "svtme_picture_search", "svtme_search_wait", "svtme_picture_search_device", "svtme_search_elapsed_ms",
-    "svtme_launch_count", "svtme_last_error", "svtme_cuda_sad_loop_kernel", "svtme_cuda_downsample_2d",
+    "svtme_search_px_compares", "svtme_measure_sad_peak", "svtme_launch_count", "svtme_last_error", "svtme_cuda_sad_loop_kernel", "svtme_cuda_downsample_2d",
     "svtme_cuda_nxm_sad_kernel", "svtme_cuda_fullpel_search_sblock",
 ]
 
@@ -66,6 +66,8 @@ def load_library():
     lib.svtme_picture_search_device.argtypes = [vp, vp, refs_t, C.POINTER(abi.Knobs), C.POINTER(u64)]
     lib.svtme_search_wait.argtypes = [vp, u64]
     lib.svtme_search_elapsed_ms.argtypes = [vp, u64, C.POINTER(C.c_float)]
+    lib.svtme_search_px_compares.argtypes = [vp, u64, C.POINTER(u64)]
+    lib.svtme_measure_sad_peak.argtypes = [vp, C.POINTER(C.c_double)]
     lib.svtme_launch_count.argtypes = [vp]
     lib.svtme_launch_count.restype = u64
     lib.svtme_last_error.argtypes = [vp]
@@ -211,11 +213,24 @@ class MeDevice:
         self._check(self.lib.svtme_search_elapsed_ms(self.h, ticket, C.byref(ms)), "svtme_search_elapsed_ms")
         return ms.value
 
+    def px_compares(self, ticket):
+        px = C.c_uint64()
+        self._check(self.lib.svtme_search_px_compares(self.h, ticket, C.byref(px)), "svtme_search_px_compares")
+        return px.value
+
     def me_picture(self, knobs, cur, refs, extended=True):
         """Synchronous picture search: the call the reference's ME kernel thread makes per picture."""
         t, out = self.search_async(knobs, cur, refs, extended=extended)
         self.wait(t)
+        out.px_compares = self.px_compares(t)
+        out.kernel_ms = self.elapsed_ms(t)
         return out
+
+    def measure_sad_peak(self):
+        """Peak VABSDIFF4 rate of this GPU in 1e9 instructions/s (x4 = pixel-compares)."""
+        v = C.c_double()
+        self._check(self.lib.svtme_measure_sad_peak(self.h, C.byref(v)), "svtme_measure_sad_peak")
+        return v.value
 
     def launch_count(self):
         return int(self.lib.svtme_launch_count(self.h))

@@ -73,7 +73,7 @@ def test_10bit_input_uses_msb_plane(oracle, dev):
     b.release()
 
 
-@pytest.mark.parametrize("size,step", itertools.product([(176, 144), (88, 72), (960, 540)], [2, 4, 8]))
+@pytest.mark.parametrize("size,step", list(itertools.product([(176, 144), (88, 72), (960, 540)], [2, 4, 8])))
 def test_rtcd_downsample_2d(oracle, dev, size, step):
     """test/PictureOperatorTest.cc:236-333 grid (sizes x steps, random data)."""
     w, h = size
@@ -186,8 +186,10 @@ def _run_case(oracle, dev, po, pd, cfg, cur, w, h, n_frames):
                          slice_type_b=cfg.pop("slice_type_b", 1), **cfg)
     l0, l1 = H.ref_lists(cur, n_frames, k.num_of_ref_pic_to_search[0], k.num_of_ref_pic_to_search[1])
     a = oracle.me_picture(k, po[cur], H.refs_dict(po, l0, l1), n_threads=8)
+    px = oracle.last_px_compares()
     b = dev.me_picture(k, pd[cur], H.refs_dict(pd, l0, l1), extended=True)
     H.assert_same(a, b, "M%d tl%d %s" % (em, tl, cfg))
+    assert b.px_compares == px, "algorithmic work counter differs: %d vs oracle %d" % (b.px_compares, px)
 
 
 @pytest.mark.parametrize("cfg", CASES, ids=lambda c: "-".join("%s%s" % kv for kv in c.items()))
