@@ -74,7 +74,7 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.samples, self.reasons, self.max_mhz, self._stop = index, [], set(), None, threading.Event()
+        self.index, self.samples, self.reasons, self.max_mhz, self._halt = index, [], set(), None, threading.Event()
 
     def run(self):
         try:
@@ -84,7 +84,7 @@ class ClockSampler(threading.Thread):
             self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
             names = {getattr(nv, n): n[len("nvmlClocksThrottleReason"):] for n in dir(nv)
                      if n.startswith("nvmlClocksThrottleReason") and n not in ("nvmlClocksThrottleReasonAll", "nvmlClocksThrottleReasonNone")}
-            while not self._stop.is_set():
+            while not self._halt.is_set():
                 self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
                 for bit, n in names.items():
@@ -95,7 +95,7 @@ class ClockSampler(threading.Thread):
             self.reasons.add("nvml_unavailable:%s" % type(ex).__name__)
 
     def stop(self):
-        self._stop.set()
+        self._halt.set()
         self.join(timeout=2)
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}

@@ -51,8 +51,8 @@ struct EngineShared {
     unsigned long long px;                     // pixel-compares of this SB (algorithmic work, same definition as the oracle's)
     unsigned long long sad_key[kMaxSadJobs];
     unsigned long long fp_key[kMaxFpJobs][kPus];
-    uint32_t           blk[64 * 16];   // HME source block of the current phase: [row][word], zero past block_w
-    uint32_t           src64[64 * 16]; // 64x64 source block of this SB: [row][word]
+    alignas(16) uint32_t blk[64 * 16];   // HME source block of the current phase: [row][word], zero past block_w
+    alignas(16) uint32_t src64[64 * 16]; // 64x64 source block of this SB: [row][word]
 };
 
 __device__ __forceinline__ uint32_t sad4(uint32_t a, uint32_t b, uint32_t c) {

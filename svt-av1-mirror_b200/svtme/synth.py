@@ -58,6 +58,7 @@ def minigop_structure(n_frames, hierarchical_levels, max_l0, max_l1):
     references.  Returns a list of dicts for pictures 1..n-1 in decode order."""
     gop = 1 << hierarchical_levels
     out = []
+    decoded = {0}
 
     def layer_of(poc):
         if poc % gop == 0:
@@ -84,18 +85,20 @@ def minigop_structure(n_frames, hierarchical_levels, max_l0, max_l1):
         visit(base, end, 1)
         for poc in order:
             tl = layer_of(poc) if end - base == gop else min(hierarchical_levels, layer_of(poc))
-            past = [p for p in range(poc - 1, -1, -1) if layer_of(p) <= max(tl - 1, 0) or p % gop == 0]
             if tl == 0:
                 past = [p for p in range(poc - gop, -1, -gop)] or [base]
-                fut = list(past)  # base-layer list 1 repeats past pictures (low-delay-like), pd_process.c
+                fut = list(past)  # base-layer list 1 repeats past pictures (pd_process.c: no future base picture exists yet)
             else:
-                step = 1 << (hierarchical_levels - tl)
-                past = [p for p in range(poc - step, max(base - gop, 0) - 1, -step) if p >= 0]
-                fut = [p for p in range(poc + step, end + 1, step)]
+                # references = reference pictures already decoded (decode order), nearest first
+                lo = max(base - gop, 0)
+                past = [p for p in range(poc - 1, lo - 1, -1) if p in decoded]
+                fut = [p for p in range(poc + 1, end + 1) if p in decoded]
             l0 = past[:max_l0] or [base]
             l1 = fut[:max_l1]
             out.append({"poc": poc, "temporal_layer": tl, "list0": l0, "list1": l1,
                         "is_ref": 1 if tl < hierarchical_levels else 0})
+            if tl < hierarchical_levels:
+                decoded.add(poc)
         base = end
         if end == n_frames - 1:
             break
