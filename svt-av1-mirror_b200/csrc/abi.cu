@@ -14,6 +14,7 @@
 
 #include "../../include/svtme_cuda.h"
 #include "me_launch.h"
+#include "me_control.cuh"
 
 using namespace svtme;
 
@@ -261,6 +262,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     p.cur = cur->dev;
     for (int l = 0; l < knobs->num_of_list_to_search; l++)
         for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) p.refs[l][r] = refs[l][r]->dev;
+    p.n_steps = build_program(p.k, p.prog);
     p.wb = wb; p.hb = hb; p.pu_count = pu_count; p.work_counter = sl->d_counter;
     p.px_counter = reinterpret_cast<unsigned long long *>(sl->d_counter + 2);
     uint8_t *d = sl->d_res;

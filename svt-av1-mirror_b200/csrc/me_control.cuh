@@ -139,7 +139,6 @@ SVTME_HD void sb_init(B &be, const MeParams &p, SbState &s, uint32_t b64_index) 
     be.sync();
     for (uint32_t i = be.tid(); i < kMaxLists * kMaxRefs * kPus; i += be.nthreads()) bs[i] = SVTME_MAX_SAD_VALUE;
     be.sync();
-    be.stage_src(s);  // engines keep the 64x64 source block on chip for the whole SB
 }
 
 #define SVTME_FOR_REFS(k, li, ri)                                \
@@ -160,40 +159,34 @@ SVTME_HD void make_nxm_job(const MeParams &p, SbState &s, int li, int ri, int16_
     j.li = (uint8_t)li; j.ri = (uint8_t)ri; j.kind = kind; j.sad = 0;
 }
 
-// ---- init_zz_sad (:2382-2437) ----
-template <class B>
-SVTME_HD void phase_zz(B &be, const MeParams &p, SbState &s) {
+// ---- init_zz_sad (:2382-2437): make the zero-MV SAD jobs / fold them and prune ----
+SVTME_HD void zz_make(const MeParams &p, SbState &s) {
     const SvtMeKnobs &k = p.k;
-    if (be.leader()) {
-        s.n_nxm = 0;
-        SVTME_FOR_REFS(k, li, ri) if (hme_active(k, li)) make_nxm_job(p, s, li, ri, 0, 0, 0);
+    s.n_nxm = 0;
+    SVTME_FOR_REFS(k, li, ri) if (hme_active(k, li)) make_nxm_job(p, s, li, ri, 0, 0, 0);
+}
+SVTME_HD void zz_fold(const MeParams &p, SbState &s) {
+    const SvtMeKnobs &k = p.k;
+    uint32_t best = kMaxU32;
+    for (int i = 0; i < s.n_nxm; i++) {
+        const NxmJob &j = s.nxm_jobs[i];
+        uint32_t zz = j.sad << 1;
+        zz = (zz * 64 * 64) / (s.b64_w * s.b64_h);  // normalise incomplete b64 (:2395)
+        s.zz_sad[j.li][j.ri] = zz;
+        best = SVTME_MIN(best, zz);
     }
-    be.sync();
-    be.run_nxm(s);
-    be.sync();
-    if (be.leader()) {
-        uint32_t best = kMaxU32;
-        for (int i = 0; i < s.n_nxm; i++) {
-            const NxmJob &j = s.nxm_jobs[i];
-            uint32_t zz = j.sad << 1;
-            zz = (zz * 64 * 64) / (s.b64_w * s.b64_h);  // normalise incomplete b64 (:2395)
-            s.zz_sad[j.li][j.ri] = zz;
-            best = SVTME_MIN(best, zz);
-        }
-        if (k.temporal_layer_index > 0 && best < k.zz_sad_th) {
-            SVTME_FOR_REFS(k, li, ri) {
-                if (ri == 0) continue;
-                if ((s.zz_sad[li][ri] - best) * 100 > ((uint32_t)k.zz_sad_pct * best)) s.do_ref[li][ri] = 0;  // u32 wrap (:2409)
-            }
-        }
-        if (k.me_safe_limit_zz_th) {
-            const bool safe = k.hierarchical_levels > 0 && k.num_of_list_to_search == 2 &&
-                k.temporal_layer_index >= k.hierarchical_levels && k.similar_brightness_refs &&
-                s.zz_sad[0][0] < k.me_safe_limit_zz_th && s.zz_sad[1][0] < k.me_safe_limit_zz_th;
-            SVTME_FOR_REFS(k, li, ri) if (safe && ri > 0) s.do_ref[li][ri] = 0;
+    if (k.temporal_layer_index > 0 && best < k.zz_sad_th) {
+        SVTME_FOR_REFS(k, li, ri) {
+            if (ri == 0) continue;
+            if ((s.zz_sad[li][ri] - best) * 100 > ((uint32_t)k.zz_sad_pct * best)) s.do_ref[li][ri] = 0;  // u32 wrap (:2409)
         }
     }
-    be.sync();
+    if (k.me_safe_limit_zz_th) {
+        const bool safe = k.hierarchical_levels > 0 && k.num_of_list_to_search == 2 &&
+            k.temporal_layer_index >= k.hierarchical_levels && k.similar_brightness_refs &&
+            s.zz_sad[0][0] < k.me_safe_limit_zz_th && s.zz_sad[1][0] < k.me_safe_limit_zz_th;
+        SVTME_FOR_REFS(k, li, ri) if (safe && ri > 0) s.do_ref[li][ri] = 0;
+    }
 }
 
 // ---- prehme_b64 (:1722-1796) with check_prehme_early_exit (:1693-1719) and prehme_core (:1568-1666) ----
@@ -235,49 +228,40 @@ SVTME_HD void prehme_make_jobs(const MeParams &p, SbState &s, int li) {
     }
 }
 
-template <class B>
-SVTME_HD void phase_prehme(B &be, const MeParams &p, SbState &s) {
+// `arg`: 0 = list 0 only, 1 = list 1 only (its early exit reads the list-0 results, :1706-1717), 2 = both lists.
+// List 1 of a base-layer picture mirrors list 0 (:1769-1777) and has no searches of its own.
+SVTME_HD void prehme_make(const MeParams &p, SbState &s, int arg) {
     const SvtMeKnobs &k = p.k;
-    // List 1 of a base-layer picture mirrors list 0 (:1769-1777) and has no searches of its own.  List 1 of other
-    // pictures may early-exit on the list-0 result (l1_early_exit), so it runs as a second sub-phase then.
     const bool l1_active = k.num_of_list_to_search > 1 && hme_active(k, 1);
-    const bool split     = l1_active && k.prehme_l1_early_exit;
-    for (int pass = 0; pass < (split ? 2 : 1); pass++) {
-        if (be.leader()) {
-            s.n_sad = 0;
-            if (pass == 0) prehme_make_jobs(p, s, 0);
-            if (l1_active && (pass == 1 || !split)) prehme_make_jobs(p, s, 1);
+    s.n_sad = 0;
+    if (arg == 0 || arg == 2) prehme_make_jobs(p, s, 0);
+    if (l1_active && (arg == 1 || arg == 2)) prehme_make_jobs(p, s, 1);
+}
+SVTME_HD void sad_fold(const MeParams &p, SbState &s) {
+    for (int i = 0; i < s.n_sad; i++) fold_sad_job(p, s, s.sad_jobs[i]);
+}
+SVTME_HD void prehme_final(const MeParams &p, SbState &s) {
+    const SvtMeKnobs &k = p.k;
+    uint32_t best_sad = kMaxU32;
+    SVTME_FOR_REFS(k, li, ri) {
+        if (hme_active(k, li)) {
+            const uint32_t m = (uint32_t)SVTME_MIN(s.prehme[li][ri][0].sad, s.prehme[li][ri][1].sad);
+            best_sad         = SVTME_MIN(best_sad, m);
+        } else {
+            for (int sr = 0; sr < 2; sr++) {
+                s.prehme[1][ri][sr].mv_x = (int16_t)-s.prehme[0][ri][sr].mv_x;
+                s.prehme[1][ri][sr].mv_y = (int16_t)-s.prehme[0][ri][sr].mv_y;
+                s.prehme[1][ri][sr].sad  = s.prehme[0][ri][sr].sad;
+            }
         }
-        be.sync();
-        be.run_sad(s);
-        be.sync();
-        if (be.leader())
-            for (int i = 0; i < s.n_sad; i++) fold_sad_job(p, s, s.sad_jobs[i]);
-        be.sync();
     }
-    if (be.leader()) {
-        uint32_t best_sad = kMaxU32;
+    if (k.temporal_layer_index > 0 && best_sad < k.phme_sad_th) {
         SVTME_FOR_REFS(k, li, ri) {
-            if (hme_active(k, li)) {
-                const uint32_t m = (uint32_t)SVTME_MIN(s.prehme[li][ri][0].sad, s.prehme[li][ri][1].sad);
-                best_sad         = SVTME_MIN(best_sad, m);
-            } else {
-                for (int sr = 0; sr < 2; sr++) {
-                    s.prehme[1][ri][sr].mv_x = (int16_t)-s.prehme[0][ri][sr].mv_x;
-                    s.prehme[1][ri][sr].mv_y = (int16_t)-s.prehme[0][ri][sr].mv_y;
-                    s.prehme[1][ri][sr].sad  = s.prehme[0][ri][sr].sad;
-                }
-            }
-        }
-        if (k.temporal_layer_index > 0 && best_sad < k.phme_sad_th) {
-            SVTME_FOR_REFS(k, li, ri) {
-                if (!s.do_ref[li][ri] || ri == 0) continue;
-                const uint32_t m = (uint32_t)SVTME_MIN(s.prehme[li][ri][0].sad, s.prehme[li][ri][1].sad);
-                if ((m - best_sad) * 100 > ((uint32_t)k.phme_sad_pct * best_sad)) s.do_ref[li][ri] = 0;  // u32 wrap (:1790)
-            }
+            if (!s.do_ref[li][ri] || ri == 0) continue;
+            const uint32_t m = (uint32_t)SVTME_MIN(s.prehme[li][ri][0].sad, s.prehme[li][ri][1].sad);
+            if ((m - best_sad) * 100 > ((uint32_t)k.phme_sad_pct * best_sad)) s.do_ref[li][ri] = 0;  // u32 wrap (:1790)
         }
     }
-    be.sync();
 }
 
 // ---- get_hme_l0_search_area (:1800-1867); works on a private copy of hme_l0_sa, which is what the reference's
@@ -359,99 +343,71 @@ SVTME_HD void hme_l0_replace_worst(const SvtMeKnobs &k, SbState &s, int li, int 
     }
 }
 
-template <class B>
-SVTME_HD void phase_hme_l0(B &be, const MeParams &p, SbState &s) {
+// `arg`: 0 = reference (0,0) only, 1 = all others (they read the (0,0) level-0 centre, :1804-1825), 2 = all.
+SVTME_HD void l0_make(const MeParams &p, SbState &s, int arg) {
     const SvtMeKnobs &k = p.k;
-    // refs other than (0,0) read the (0,0) level-0 centre only in this configuration (:1804-1825)
-    const bool dep = k.enable_me_sr_adjustment && k.distance_based_hme_resizing && k.reduce_hme_l0_sr_th_min &&
-        k.reduce_hme_l0_sr_th_max;
-    for (int pass = 0; pass < (dep ? 2 : 1); pass++) {
-        if (be.leader()) {
-            s.n_sad = 0;
-            uint32_t searched = 0;  // bit li*4+ri
-            SVTME_FOR_REFS(k, li, ri) {
-                const bool first = (li == 0 && ri == 0);
-                if (dep && (first != (pass == 0))) continue;
-                if (hme_l0_make_jobs(p, s, li, ri)) searched |= 1u << (li * 4 + ri);
-            }
-            s.n_nxm = (int32_t)searched;  // scratch: remembered across the collective call
-        }
-        be.sync();
-        be.run_sad(s);
-        be.sync();
-        if (be.leader()) {
-            for (int i = 0; i < s.n_sad; i++) fold_sad_job(p, s, s.sad_jobs[i]);
-            const uint32_t searched = (uint32_t)s.n_nxm;
-            SVTME_FOR_REFS(k, li, ri) if (searched & (1u << (li * 4 + ri))) hme_l0_replace_worst(k, s, li, ri);
-        }
-        be.sync();
+    s.n_sad = 0;
+    uint32_t searched = 0;  // bit li*4+ri
+    SVTME_FOR_REFS(k, li, ri) {
+        const bool first = (li == 0 && ri == 0);
+        if (arg != 2 && (first != (arg == 0))) continue;
+        if (hme_l0_make_jobs(p, s, li, ri)) searched |= 1u << (li * 4 + ri);
     }
+    s.l0_searched = searched;
+}
+SVTME_HD void l0_fold(const MeParams &p, SbState &s) {
+    const SvtMeKnobs &k = p.k;
+    for (int i = 0; i < s.n_sad; i++) fold_sad_job(p, s, s.sad_jobs[i]);
+    const uint32_t searched = s.l0_searched;
+    SVTME_FOR_REFS(k, li, ri) if (searched & (1u << (li * 4 + ri))) hme_l0_replace_worst(k, s, li, ri);
 }
 
 // ---- hme_level1_b64 (:2041-2122) + hme_level_1 (:923-1022) ----
-template <class B>
-SVTME_HD void phase_hme_l1(B &be, const MeParams &p, SbState &s) {
+SVTME_HD void l1_make(const MeParams &p, SbState &s) {
     const SvtMeKnobs &k = p.k;
-    if (be.leader()) {
-        s.n_sad = 0;
-        SVTME_FOR_REFS(k, li, ri) {
-            if (!hme_active(k, li)) continue;
-            if (k.me_early_exit_th && s.zz_sad[li][ri] < (k.me_early_exit_th >> 2)) { set_quadrants(k, s, 1, li, ri, 0, 0, 0); continue; }
-            if (!s.do_ref[li][ri]) { set_quadrants(k, s, 1, li, ri, 0, 0, kMaxU32); continue; }
-            const DevPlane &rp = p.refs[li][ri].lvl[1];
-            for (int qh = 0; qh < k.num_hme_sa_h; qh++)
-                for (int qw = 0; qw < k.num_hme_sa_w; qw++) {
-                    if (k.prev_me_stage_based_exit_th && s.lsad[0][li][ri][qw][qh] < (k.prev_me_stage_based_exit_th >> 5)) {
-                        s.lx[1][li][ri][qw][qh] = s.lx[0][li][ri][qw][qh]; s.ly[1][li][ri][qw][qh] = s.ly[0][li][ri][qw][qh];
-                        s.lsad[1][li][ri][qw][qh] = s.lsad[0][li][ri][qw][qh];
-                        continue;
-                    }
-                    int16_t w = (int16_t)(((int16_t)k.hme_l1_sa.width + 7) & ~0x07), h = (int16_t)k.hme_l1_sa.height;
-                    const int16_t cx = (int16_t)(s.lx[0][li][ri][qw][qh] >> 1), cy = (int16_t)(s.ly[0][li][ri][qw][qh] >> 1);
-                    int16_t ox = (int16_t)(-(w >> 1) + cx), oy = (int16_t)(-(h >> 1) + cy);
-                    clip_window((int16_t)(((int16_t)s.org_x) >> 1), (int16_t)(((int16_t)s.org_y) >> 1), (int16_t)(rp.ref_org - 1),
-                                (int16_t)(rp.ref_org - 1), (int16_t)rp.width, (int16_t)rp.height, ox, oy, w, h, true);
-                    make_sad_job(p, s, 1, li, ri, ox, oy, w, h, 0, 1, (uint8_t)qw, (uint8_t)qh);
+    s.n_sad = 0;
+    SVTME_FOR_REFS(k, li, ri) {
+        if (!hme_active(k, li)) continue;
+        if (k.me_early_exit_th && s.zz_sad[li][ri] < (k.me_early_exit_th >> 2)) { set_quadrants(k, s, 1, li, ri, 0, 0, 0); continue; }
+        if (!s.do_ref[li][ri]) { set_quadrants(k, s, 1, li, ri, 0, 0, kMaxU32); continue; }
+        const DevPlane &rp = p.refs[li][ri].lvl[1];
+        for (int qh = 0; qh < k.num_hme_sa_h; qh++)
+            for (int qw = 0; qw < k.num_hme_sa_w; qw++) {
+                if (k.prev_me_stage_based_exit_th && s.lsad[0][li][ri][qw][qh] < (k.prev_me_stage_based_exit_th >> 5)) {
+                    s.lx[1][li][ri][qw][qh] = s.lx[0][li][ri][qw][qh]; s.ly[1][li][ri][qw][qh] = s.ly[0][li][ri][qw][qh];
+                    s.lsad[1][li][ri][qw][qh] = s.lsad[0][li][ri][qw][qh];
+                    continue;
                 }
-        }
+                int16_t w = (int16_t)(((int16_t)k.hme_l1_sa.width + 7) & ~0x07), h = (int16_t)k.hme_l1_sa.height;
+                const int16_t cx = (int16_t)(s.lx[0][li][ri][qw][qh] >> 1), cy = (int16_t)(s.ly[0][li][ri][qw][qh] >> 1);
+                int16_t ox = (int16_t)(-(w >> 1) + cx), oy = (int16_t)(-(h >> 1) + cy);
+                clip_window((int16_t)(((int16_t)s.org_x) >> 1), (int16_t)(((int16_t)s.org_y) >> 1), (int16_t)(rp.ref_org - 1),
+                            (int16_t)(rp.ref_org - 1), (int16_t)rp.width, (int16_t)rp.height, ox, oy, w, h, true);
+                make_sad_job(p, s, 1, li, ri, ox, oy, w, h, 0, 1, (uint8_t)qw, (uint8_t)qh);
+            }
     }
-    be.sync();
-    be.run_sad(s);
-    be.sync();
-    if (be.leader())
-        for (int i = 0; i < s.n_sad; i++) fold_sad_job(p, s, s.sad_jobs[i]);
-    be.sync();
 }
 
 // ---- hme_level2_b64 (:2127-2177) + hme_level_2 (:1025-1113; pad is BLOCK_SIZE_64-1 regardless of the buffer) ----
-template <class B>
-SVTME_HD void phase_hme_l2(B &be, const MeParams &p, SbState &s) {
+SVTME_HD void l2_make(const MeParams &p, SbState &s) {
     const SvtMeKnobs &k = p.k;
-    if (be.leader()) {
-        s.n_sad = 0;
-        SVTME_FOR_REFS(k, li, ri) {
-            if (!hme_active(k, li)) continue;
-            const DevPlane &rp = p.refs[li][ri].lvl[0];
-            for (int qh = 0; qh < k.num_hme_sa_h; qh++)
-                for (int qw = 0; qw < k.num_hme_sa_w; qw++) {
-                    if (k.prev_me_stage_based_exit_th && s.lsad[1][li][ri][qw][qh] < (k.prev_me_stage_based_exit_th >> 2)) {
-                        s.lx[2][li][ri][qw][qh] = s.lx[1][li][ri][qw][qh]; s.ly[2][li][ri][qw][qh] = s.ly[1][li][ri][qw][qh];
-                        s.lsad[2][li][ri][qw][qh] = s.lsad[1][li][ri][qw][qh];
-                        continue;
-                    }
-                    int16_t w = (int16_t)(((int16_t)k.hme_l2_sa.width + 7) & ~0x07), h = (int16_t)k.hme_l2_sa.height;
-                    int16_t ox = (int16_t)(-(w >> 1) + s.lx[1][li][ri][qw][qh]), oy = (int16_t)(-(h >> 1) + s.ly[1][li][ri][qw][qh]);
-                    clip_window((int16_t)s.org_x, (int16_t)s.org_y, 63, 63, (int16_t)rp.width, (int16_t)rp.height, ox, oy, w, h, true);
-                    make_sad_job(p, s, 0, li, ri, ox, oy, w, h, 0, 2, (uint8_t)qw, (uint8_t)qh);
+    s.n_sad = 0;
+    SVTME_FOR_REFS(k, li, ri) {
+        if (!hme_active(k, li)) continue;
+        const DevPlane &rp = p.refs[li][ri].lvl[0];
+        for (int qh = 0; qh < k.num_hme_sa_h; qh++)
+            for (int qw = 0; qw < k.num_hme_sa_w; qw++) {
+                if (k.prev_me_stage_based_exit_th && s.lsad[1][li][ri][qw][qh] < (k.prev_me_stage_based_exit_th >> 2)) {
+                    s.lx[2][li][ri][qw][qh] = s.lx[1][li][ri][qw][qh]; s.ly[2][li][ri][qw][qh] = s.ly[1][li][ri][qw][qh];
+                    s.lsad[2][li][ri][qw][qh] = s.lsad[1][li][ri][qw][qh];
+                    continue;
                 }
-        }
+                int16_t w = (int16_t)(((int16_t)k.hme_l2_sa.width + 7) & ~0x07), h = (int16_t)k.hme_l2_sa.height;
+                int16_t ox = (int16_t)(-(w >> 1) + s.lx[1][li][ri][qw][qh]), oy = (int16_t)(-(h >> 1) + s.ly[1][li][ri][qw][qh]);
+                clip_window((int16_t)s.org_x, (int16_t)s.org_y, 63, 63, (int16_t)rp.width, (int16_t)rp.height, ox, oy, w, h, true);
+                make_sad_job(p, s, 0, li, ri, ox, oy, w, h, 0, 2, (uint8_t)qw, (uint8_t)qh);
+            }
     }
-    be.sync();
-    be.run_sad(s);
-    be.sync();
-    if (be.leader())
-        for (int i = 0; i < s.n_sad; i++) fold_sad_job(p, s, s.sad_jobs[i]);
-    be.sync();
 }
 
 // ---- set_final_seach_centre_sb (:2182-2380) followed by hme_prune_ref_and_adjust_sr (:2477-2518); leader only ----
@@ -621,52 +577,44 @@ SVTME_HD void isearch_final_job(const MeParams &p, SbState &s, int li, int ri) {
     make_fp_job(p, s, li, ri, xo, yo, w, h);
 }
 
-template <class B>
-SVTME_HD void phase_isearch(B &be, const MeParams &p, SbState &s) {
+// `arg`: 0 = reference (0,0) only, 1 = the others (SR adjustment level 2 lets p_sb_best_sad[0][0][0] of THIS SB steer
+// them, :1355-1364), 2 = all references.
+SVTME_HD bool is_in_pass(const SbState &s, int li, int ri, int arg) {
+    return s.do_ref[li][ri] && (arg == 2 || ((li == 0 && ri == 0) == (arg == 0)));
+}
+// A: area from distance / MV / divisor, and the zero-MV / HME-centre SAD jobs of check_00_center
+SVTME_HD void is_a(const MeParams &p, SbState &s, int arg) {
     const SvtMeKnobs &k = p.k;
-    // p_sb_best_sad[0][0][0] of THIS SB steers the other references only with SR adjustment level 2 (:1355-1364)
-    const bool dep = (k.enable_me_sr_adjustment == 2) && !k.me_early_exit_th;
-    for (int pass = 0; pass < (dep ? 2 : 1); pass++) {
-#define SVTME_IN_PASS(li, ri) (s.do_ref[li][ri] && (!dep || (((li) == 0 && (ri) == 0) == (pass == 0))))
-        if (be.leader()) {
-            s.n_nxm = 0;
-            SVTME_FOR_REFS(k, li, ri) {
-                if (!SVTME_IN_PASS(li, ri)) continue;
-                isearch_area(p, s, li, ri);
-                if (!k.me_early_exit_th && (s.isc_x[li][ri] != 0 || s.isc_y[li][ri] != 0) && k.is_ref) isearch_c00_jobs(p, s, li, ri);
-            }
-        }
-        be.sync();
-        be.run_nxm(s);
-        be.sync();
-        if (be.leader()) {
-            s.n_fp = 0;
-            SVTME_FOR_REFS(k, li, ri) {
-                if (!SVTME_IN_PASS(li, ri)) continue;
-                uint32_t zero_raw = s.zz_sad[li][ri], hme_raw = 0;  // zz_sad stands in for the zero-MV SAD when early exit is on
-                for (int i = 0; i < s.n_nxm; i++) {
-                    const NxmJob &j = s.nxm_jobs[i];
-                    if (j.li != li || j.ri != ri) continue;
-                    if (j.kind == 1) zero_raw = j.sad;
-                    if (j.kind == 2) hme_raw = j.sad;
-                }
-                isearch_adjust(p, s, li, ri, zero_raw, hme_raw);
-                // 1x1 probe at the search centre BEFORE the main scan, on the same best arrays (:1391-1412)
-                if (s.probe[li][ri]) make_fp_job(p, s, li, ri, s.isc_x[li][ri], s.isc_y[li][ri], 1, 1);
-            }
-        }
-        be.sync();
-        be.run_fullpel(s);
-        be.sync();
-        if (be.leader()) {
-            s.n_fp = 0;
-            SVTME_FOR_REFS(k, li, ri) if (SVTME_IN_PASS(li, ri)) isearch_final_job(p, s, li, ri);
-        }
-        be.sync();
-        be.run_fullpel(s);
-        be.sync();
-#undef SVTME_IN_PASS
+    s.n_nxm = 0;
+    SVTME_FOR_REFS(k, li, ri) {
+        if (!is_in_pass(s, li, ri, arg)) continue;
+        isearch_area(p, s, li, ri);
+        if (!k.me_early_exit_th && (s.isc_x[li][ri] != 0 || s.isc_y[li][ri] != 0) && k.is_ref) isearch_c00_jobs(p, s, li, ri);
     }
+}
+// B: early exit / SR adjustment; queue the 1x1 probe at the search centre, which runs BEFORE the main scan on the
+// same best arrays (:1391-1412)
+SVTME_HD void is_b(const MeParams &p, SbState &s, int arg) {
+    const SvtMeKnobs &k = p.k;
+    s.n_fp = 0;
+    SVTME_FOR_REFS(k, li, ri) {
+        if (!is_in_pass(s, li, ri, arg)) continue;
+        uint32_t zero_raw = s.zz_sad[li][ri], hme_raw = 0;  // zz_sad stands in for the zero-MV SAD when early exit is on
+        for (int i = 0; i < s.n_nxm; i++) {
+            const NxmJob &j = s.nxm_jobs[i];
+            if (j.li != li || j.ri != ri) continue;
+            if (j.kind == 1) zero_raw = j.sad;
+            if (j.kind == 2) hme_raw = j.sad;
+        }
+        isearch_adjust(p, s, li, ri, zero_raw, hme_raw);
+        if (s.probe[li][ri]) make_fp_job(p, s, li, ri, s.isc_x[li][ri], s.isc_y[li][ri], 1, 1);
+    }
+}
+// C: 8x8-variance scaling, clipping, the main scan
+SVTME_HD void is_c(const MeParams &p, SbState &s, int arg) {
+    const SvtMeKnobs &k = p.k;
+    s.n_fp = 0;
+    SVTME_FOR_REFS(k, li, ri) if (is_in_pass(s, li, ri, arg)) isearch_final_job(p, s, li, ri);
 }
 
 // ---- me_prune_ref (:1522-1565); leader only ----
@@ -877,23 +825,70 @@ SVTME_HD void gm_detection(const MeParams &p, const SbState &s, const SbOut &o) 
                     if (cnt[l][r][c][q] > (tot / 2)) p.out.rc_me_allow_gm[s.b64_index] = 1;
 }
 
-// ---- svt_aom_motion_estimation_b64 (:3076-3153) for ME_OPEN_LOOP, hme_b64 (:2441-2475) inlined ----
-template <class B>
-SVTME_HD void me_sb(B &be, const MeParams &p, SbState &s, uint32_t b64_index) {
-    const SvtMeKnobs &k = p.k;
-    sb_init(be, p, s, b64_index);
-    if (k.me_early_exit_th || k.me_safe_limit_zz_th) phase_zz(be, p, s);
-    if (k.prehme_enable) phase_prehme(be, p, s);
-    if (k.enable_hme_flag) {
-        if (k.enable_hme_level0_flag) phase_hme_l0(be, p, s);
-        if (k.enable_hme_level1_flag) phase_hme_l1(be, p, s);
-        if (k.enable_hme_level2_flag) phase_hme_l2(be, p, s);
-    }
-    if (be.leader()) final_centre_and_prune(p, s);
-    be.sync();
-    phase_isearch(be, p, s);
-    if (be.leader() && k.enable_hme_flag && k.enable_me_hme_ref_pruning) me_prune_ref(p, s);
+// ---- the step program: svt_aom_motion_estimation_b64 (:3076-3153) for ME_OPEN_LOOP with hme_b64 (:2441-2475) and
+// integer_search_b64 (:1249-1516) unrolled into control steps (scalar, per SB) and engine steps (data parallel) ----
+enum StepKind : uint8_t { STEP_CTL = 0, STEP_NXM = 1, STEP_SAD = 2, STEP_FP = 3 };
+enum CtlOp : uint8_t {
+    C_ZZ_MAKE, C_ZZ_FOLD, C_PREHME_MAKE, C_SAD_FOLD, C_PREHME_FINAL, C_L0_MAKE, C_L0_FOLD, C_L1_MAKE, C_L2_MAKE,
+    C_FINAL_CENTRE, C_IS_A, C_IS_B, C_IS_C, C_PRUNE
+};
 
+SVTME_HDX int build_program(const SvtMeKnobs &k, Step *st) {
+    int n = 0;
+    auto ctl = [&](uint8_t op, uint8_t arg) { st[n].kind = STEP_CTL; st[n].op = op; st[n].arg = arg; n++; };
+    auto eng = [&](uint8_t kind) { st[n].kind = kind; st[n].op = 0; st[n].arg = 0; n++; };
+    const bool l1_hme = k.temporal_layer_index > 0;  // hme_active(k, 1)
+    if (k.me_early_exit_th || k.me_safe_limit_zz_th) { ctl(C_ZZ_MAKE, 0); eng(STEP_NXM); ctl(C_ZZ_FOLD, 0); }
+    if (k.prehme_enable) {
+        const bool split = k.num_of_list_to_search > 1 && l1_hme && k.prehme_l1_early_exit;
+        for (int pass = 0; pass < (split ? 2 : 1); pass++) { ctl(C_PREHME_MAKE, (uint8_t)(split ? pass : 2)); eng(STEP_SAD); ctl(C_SAD_FOLD, 0); }
+        ctl(C_PREHME_FINAL, 0);
+    }
+    if (k.enable_hme_flag) {
+        if (k.enable_hme_level0_flag) {
+            const bool dep = k.enable_me_sr_adjustment && k.distance_based_hme_resizing && k.reduce_hme_l0_sr_th_min &&
+                k.reduce_hme_l0_sr_th_max;
+            for (int pass = 0; pass < (dep ? 2 : 1); pass++) { ctl(C_L0_MAKE, (uint8_t)(dep ? pass : 2)); eng(STEP_SAD); ctl(C_L0_FOLD, 0); }
+        }
+        if (k.enable_hme_level1_flag) { ctl(C_L1_MAKE, 0); eng(STEP_SAD); ctl(C_SAD_FOLD, 0); }
+        if (k.enable_hme_level2_flag) { ctl(C_L2_MAKE, 0); eng(STEP_SAD); ctl(C_SAD_FOLD, 0); }
+    }
+    ctl(C_FINAL_CENTRE, 0);
+    {
+        const bool dep = (k.enable_me_sr_adjustment == 2) && !k.me_early_exit_th;
+        for (int pass = 0; pass < (dep ? 2 : 1); pass++) {
+            const uint8_t a = (uint8_t)(dep ? pass : 2);
+            ctl(C_IS_A, a); eng(STEP_NXM); ctl(C_IS_B, a); eng(STEP_FP); ctl(C_IS_C, a); eng(STEP_FP);
+        }
+    }
+    if (k.enable_hme_flag && k.enable_me_hme_ref_pruning) ctl(C_PRUNE, 0);
+    return n;
+}
+
+SVTME_HD void ctl_step(const MeParams &p, SbState &s, uint8_t op, uint8_t arg) {
+    switch (op) {
+    case C_ZZ_MAKE: zz_make(p, s); break;
+    case C_ZZ_FOLD: zz_fold(p, s); break;
+    case C_PREHME_MAKE: prehme_make(p, s, arg); break;
+    case C_SAD_FOLD: sad_fold(p, s); break;
+    case C_PREHME_FINAL: prehme_final(p, s); break;
+    case C_L0_MAKE: l0_make(p, s, arg); break;
+    case C_L0_FOLD: l0_fold(p, s); break;
+    case C_L1_MAKE: l1_make(p, s); break;
+    case C_L2_MAKE: l2_make(p, s); break;
+    case C_FINAL_CENTRE: final_centre_and_prune(p, s); break;
+    case C_IS_A: is_a(p, s, arg); break;
+    case C_IS_B: is_b(p, s, arg); break;
+    case C_IS_C: is_c(p, s, arg); break;
+    case C_PRUNE: me_prune_ref(p, s); break;
+    default: break;
+    }
+}
+
+// ---- results of one SB: candidates (one PU per thread), distortion statistics, GM detection, optional exports ----
+template <class B>
+SVTME_HD void sb_finish(B &be, const MeParams &p, SbState &s, uint32_t b64_index) {
+    const SvtMeKnobs &k = p.k;
     SbOut o;
     o.mv    = p.out.me_mv + (size_t)b64_index * p.pu_count * k.max_refs;
     o.cand  = p.out.me_cand + (size_t)b64_index * p.pu_count * k.max_cand;
@@ -928,6 +923,26 @@ SVTME_HD void me_sb(B &be, const MeParams &p, SbState &s, uint32_t b64_index) {
             }
     }
     be.sync();
+}
+
+// ---- one CTA (or the scalar test backend) runs the whole program for one SB ----
+template <class B>
+SVTME_HD void me_sb(B &be, const MeParams &p, SbState &s, uint32_t b64_index) {
+    sb_init(be, p, s, b64_index);
+    be.stage_src(s);  // engines keep the 64x64 source block on chip for the whole SB
+    for (int i = 0; i < p.n_steps; i++) {
+        const Step st = p.prog[i];
+        switch (st.kind) {
+        case STEP_CTL:
+            if (be.leader()) ctl_step(p, s, st.op, st.arg);
+            break;
+        case STEP_NXM: be.run_nxm(s); break;
+        case STEP_SAD: be.run_sad(s); break;
+        default: be.run_fullpel(s); break;
+        }
+        be.sync();
+    }
+    sb_finish(be, p, s, b64_index);
 }
 
 }  // namespace svtme

@@ -24,9 +24,18 @@
 
 namespace svtme {
 
-constexpr int      kThreads   = 256;
+#ifndef SVTME_THREADS
+#define SVTME_THREADS 256
+#endif
+#ifndef SVTME_WIN_KB
+#define SVTME_WIN_KB 64
+#endif
+#ifndef SVTME_MIN_CTAS
+#define SVTME_MIN_CTAS 2
+#endif
+constexpr int      kThreads   = SVTME_THREADS;
 constexpr int      kMaxTiles  = 48;
-constexpr uint32_t kWinBytes  = 64 * 1024;
+constexpr uint32_t kWinBytes  = SVTME_WIN_KB * 1024;
 constexpr int      kTileMaxNx = 128;  // candidates per tile row
 
 struct Tile {

@@ -28,7 +28,7 @@ __device__ __forceinline__ CudaBackend make_backend(const MeParams *p, unsigned 
     return be;
 }
 
-__global__ void __launch_bounds__(kThreads, 2) me_picture_kernel(const __grid_constant__ MeParams p) {
+__global__ void __launch_bounds__(kThreads, SVTME_MIN_CTAS) me_picture_kernel(const __grid_constant__ MeParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     CtaShared  *cs = reinterpret_cast<CtaShared *>(smem);
     CudaBackend be = make_backend(&p, smem);

@@ -9,9 +9,11 @@
 
 #if defined(__CUDACC__)
 #define SVTME_HD __device__ __forceinline__
+#define SVTME_HDX __host__ __device__ inline
 #define SVTME_D __device__ __forceinline__
 #else
 #define SVTME_HD inline
+#define SVTME_HDX inline
 #define SVTME_D inline
 #endif
 
@@ -52,6 +54,14 @@ struct DevResults {
     int16_t  *hme_sc;                    // optional
 };
 
+// One step of the per-SB program (me_control.cuh: build_program)
+struct Step {
+    uint8_t kind, op, arg;
+};
+constexpr int kMaxSteps = 48;
+
+struct SbState;
+
 struct MeParams {
     SvtMeKnobs k;
     DevPic     cur;
@@ -61,6 +71,9 @@ struct MeParams {
     uint32_t   pu_count;    // 85 / 21 / 5
     uint32_t  *work_counter;  // persistent-CTA SB queue
     unsigned long long *px_counter;  // optional: algorithmic pixel-compares of the picture (roofline numerator)
+    SbState   *states;        // staged pipeline: one SbState per 64x64 block in HBM/L2
+    int32_t    n_steps;
+    Step       prog[kMaxSteps];
 };
 
 // ---- work descriptors produced by the per-SB control code and consumed by the search engines ----
@@ -141,6 +154,7 @@ struct SbState {
     NxmJob   nxm_jobs[kMaxNxmJobs];
     FpJob    fp_jobs[kMaxFpJobs];
     int32_t  n_sad, n_nxm, n_fp;
+    uint32_t l0_searched;  // references whose HME-L0 quadrants were searched in the current pass (bit li*4+ri)
 };
 
 }  // namespace svtme

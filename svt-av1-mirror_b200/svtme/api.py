@@ -14,7 +14,7 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsvtme_cuda.so")
+LIB_PATH = os.environ.get("SVTME_LIB") or os.path.join(_HERE, "libsvtme_cuda.so")  # SVTME_LIB: tuning variants
 _PKG_DIR = os.path.dirname(_HERE)
 
 EXPORTS = [
