@@ -67,6 +67,8 @@ struct Inflight {
     uint8_t            *d_res = nullptr, *h_res = nullptr;
     size_t              cap = 0;
     uint32_t           *d_counter = nullptr;
+    uint8_t            *d_states = nullptr;
+    size_t              states_cap = 0;
     ResultLayout        lay{};
     SvtMePictureResults user{};
     bool                to_host = false, busy = false;
@@ -256,6 +258,13 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
         if (e != cudaSuccess) return release_slot(fail(h, SVTME_ERR_INSUFFICIENT, "result arena", e));
         sl->cap = sl->lay.total;
     }
+    if (h->cfg.pipeline == 0 && sl->states_cap < staged_state_bytes(n_b64)) {
+        if (sl->d_states) cudaFree(sl->d_states);
+        sl->d_states = nullptr; sl->states_cap = 0;
+        cudaError_t e = cudaMalloc(&sl->d_states, staged_state_bytes(n_b64));
+        if (e != cudaSuccess) return release_slot(fail(h, SVTME_ERR_INSUFFICIENT, "block state arena", e));
+        sl->states_cap = staged_state_bytes(n_b64);
+    }
     MeParams p;
     memset(&p, 0, sizeof(p));
     p.k   = *knobs;
@@ -265,6 +274,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     p.n_steps = build_program(p.k, p.prog);
     p.wb = wb; p.hb = hb; p.pu_count = pu_count; p.work_counter = sl->d_counter;
     p.px_counter = reinterpret_cast<unsigned long long *>(sl->d_counter + 2);
+    p.states = reinterpret_cast<SbState *>(sl->d_states);
     uint8_t *d = sl->d_res;
     const ResultLayout &L = sl->lay;
     p.out.me_mv = (uint32_t *)(d + L.off[R_MV]); p.out.me_cand = d + L.off[R_CAND]; p.out.total_me_candidate_index = d + L.off[R_COUNT];
@@ -283,7 +293,8 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     if (e == cudaSuccess) e = cudaMemsetAsync(sl->d_counter, 0, 16, st);
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_start, st);
     const int grid = (int)std::min<uint32_t>(n_b64, (uint32_t)(h->sm_count * h->ctas_per_sm));
-    if (e == cudaSuccess) e = launch_me_picture(p, grid, st);
+    int n_launch = 1;
+    if (e == cudaSuccess) e = h->cfg.pipeline == 0 ? launch_me_picture_staged(p, st, &n_launch) : launch_me_picture(p, grid, st);
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_kernel, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(sl->h_px, sl->d_counter + 2, 8, cudaMemcpyDeviceToHost, st);
     sl->to_host = out != nullptr;
@@ -303,7 +314,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     if (e != cudaSuccess) return release_slot(fail(h, SVTME_ERR_UNDEFINED, "search launch", e));
     {
         std::lock_guard<std::mutex> lk(h->mu);
-        h->launches += 1;
+        h->launches += (uint64_t)n_launch;
     }
     *ticket = sl->ticket;
     return SVTME_OK;
@@ -362,6 +373,7 @@ void svtme_destroy(SvtMeHandle *h) {
         if (s.d_res) cudaFree(s.d_res);
         if (s.h_res) cudaFreeHost(s.h_res);
         if (s.d_counter) cudaFree(s.d_counter);
+        if (s.d_states) cudaFree(s.d_states);
         if (s.h_px) cudaFreeHost(s.h_px);
     }
     for (auto &s : h->up_streams)

@@ -18,3 +18,8 @@ cudaError_t launch_rtcd_fullpel(const uint8_t *src, int src_stride, const FpJob 
                                 uint32_t *d_best_mv, cudaStream_t st);
 cudaError_t launch_sad_peak(uint32_t *d_out, int grid, int iters, cudaStream_t st);
 }  // namespace svtme
+namespace svtme {
+// staged (picture-wide kernels) execution of the step program; p.states must hold staged_state_bytes(n_sb) bytes
+cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_launches);
+size_t      staged_state_bytes(uint32_t n_sb);
+}  // namespace svtme

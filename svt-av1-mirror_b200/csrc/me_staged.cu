@@ -1,0 +1,501 @@
+// me_staged.cu -- the picture-wide ("staged") execution of the per-SB step program.
+//
+// The v1 kernel (me_kernel.cu: one persistent CTA runs the whole program of a 64x64 block) is latency bound: a single
+// leader thread executes the scalar control steps while the rest of the CTA waits at barriers (ncu: 56 % of warp
+// time in barrier stalls, 7.5x more instructions than SADs).  Here every step of the program becomes ONE KERNEL OVER
+// THE WHOLE PICTURE:
+//     control steps : one thread per 64x64 block (all 2040 blocks of a 4K picture advance together)
+//     engine steps  : one CTA per block, one WARP per search job -- no block barriers inside a job, windows staged in
+//                     warp-private shared memory, minima reduced with warp shuffles
+// Block state (SbState, the SB-scoped part of the reference's MeContext) lives in HBM/L2 between kernels.  Kernel
+// launches of one picture are stream ordered; several pictures are in flight on different streams, so the small
+// control kernels of one picture overlap the engine kernels of another.
+#include <cuda_runtime.h>
+#include "me_engines.cuh"
+#include "me_launch.h"
+
+namespace svtme {
+
+constexpr int kStThreads  = 128;             // 4 warps per block CTA
+constexpr int kStWarps    = kStThreads / 32;
+constexpr int kSadWarpWin = 8 * 1024;        // HME window bytes per warp
+constexpr int kFpWarpWin  = 16 * 1024;       // full-pel window bytes per warp (64 block rows + candidates)
+
+// cooperative helpers of a block CTA working on global state
+struct StBackend {
+    __device__ __forceinline__ bool     leader() const { return threadIdx.x == 0; }
+    __device__ __forceinline__ void     sync() const { __syncthreads(); }
+    __device__ __forceinline__ uint32_t tid() const { return threadIdx.x; }
+    __device__ __forceinline__ uint32_t nthreads() const { return blockDim.x; }
+};
+
+__global__ void __launch_bounds__(kStThreads) st_init_kernel(const __grid_constant__ MeParams p) {
+    StBackend be;
+    sb_init(be, p, p.states[blockIdx.x], blockIdx.x);
+}
+
+// control steps [first, first + count) of the program, one thread per 64x64 block
+__global__ void __launch_bounds__(64) st_ctl_kernel(const __grid_constant__ MeParams p, int first, int count) {
+    const uint32_t sb = blockIdx.x * blockDim.x + threadIdx.x;
+    if (sb >= p.wb * p.hb) return;
+    SbState &s = p.states[sb];
+    for (int i = first; i < first + count; i++) ctl_step(p, s, p.prog[i].op, p.prog[i].arg);
+}
+
+__global__ void __launch_bounds__(kStThreads) st_finish_kernel(const __grid_constant__ MeParams p) {
+    StBackend be;
+    sb_finish(be, p, p.states[blockIdx.x], blockIdx.x);
+    if (threadIdx.x == 0 && p.px_counter) atomicAdd(p.px_counter, p.states[blockIdx.x].px);
+}
+
+// ---- svt_nxm_sad_kernel jobs: one warp per job, straight from global memory (2 KB per operand) ----
+__global__ void __launch_bounds__(kStThreads) st_nxm_kernel(const __grid_constant__ MeParams p) {
+    SbState  &s    = p.states[blockIdx.x];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n    = s.n_nxm;
+    if (threadIdx.x == 0) {
+        unsigned long long px = 0;
+        for (int ji = 0; ji < n; ji++) px += (unsigned long long)s.nxm_jobs[ji].rows * s.nxm_jobs[ji].width;
+        s.px += px;
+    }
+    for (int ji = warp; ji < n; ji += kStWarps) {
+        NxmJob        &j   = s.nxm_jobs[ji];
+        const int      nw  = (j.width + 3) >> 2, rows = j.rows, width = j.width;
+        const uint8_t *src = j.src, *ref = j.ref;
+        const int      sst = j.src_stride, rst = j.ref_stride;
+        const uint32_t tail = (width & 3) ? ((1u << (8 * (width & 3))) - 1u) : 0xffffffffu;
+        uint32_t       acc = 0;
+        if ((((uintptr_t)src | (uint32_t)sst) & 3) == 0) {
+            // source rows are word aligned (always so on the ME path); reference words come from two aligned loads
+            const int sh = (int)((uintptr_t)ref & 3);
+            for (int i = lane; i < rows * nw; i += 32) {
+                const int       r = i / nw, c = i - r * nw;
+                const uint32_t  a = *reinterpret_cast<const uint32_t *>(src + (int64_t)r * sst + 4 * c);
+                const uint8_t  *rp = ref + (int64_t)r * rst + 4 * c;
+                const uint32_t *ra = reinterpret_cast<const uint32_t *>(rp - ((uintptr_t)rp & 3));
+                const uint32_t  lo = ra[0], hi = (((uintptr_t)rp & 3) ? ra[1] : 0u);
+                uint32_t        b  = __funnelshift_r(lo, hi, 8 * (int)((uintptr_t)rp & 3));
+                (void)sh;
+                const uint32_t m = (c == nw - 1) ? tail : 0xffffffffu;
+                acc = sad4(a & m, b & m, acc);
+            }
+        } else {
+            for (int i = lane; i < rows * nw; i += 32) {
+                const int      r = i / nw, c = i - r * nw;
+                const uint8_t *sp = src + (int64_t)r * sst + 4 * c, *rp = ref + (int64_t)r * rst + 4 * c;
+                const int      nb = min(4, width - 4 * c);
+                uint32_t       a = 0, b = 0;
+                for (int q = 0; q < nb; q++) { a |= (uint32_t)sp[q] << (8 * q); b |= (uint32_t)rp[q] << (8 * q); }
+                acc = sad4(a, b, acc);
+            }
+        }
+        for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) j.sad = acc;
+    }
+}
+
+// ---- svt_sad_loop_kernel jobs (pre-HME, HME level 0/1/2): one warp per job ----
+// A lane evaluates 4 x-adjacent candidates (they share shared-memory words; alignments 1..3 by funnel shift).  When a
+// job has fewer than 32 such items, the block rows of an item are split over L = 2^k lanes and summed by xor shuffles,
+// so that 8x3 refinement windows still fill the warp.
+template <int NW>
+__device__ __forceinline__ void sad_rows(const uint32_t *rowp, uint32_t row_step_w, const uint32_t *blk, int r0, int rstride, int rows,
+                                         int nw, uint32_t tailmask, uint32_t &a0, uint32_t &a1, uint32_t &a2, uint32_t &a3) {
+    for (int r = r0; r < rows; r += rstride) {
+        const uint32_t *rp = rowp + (uint32_t)r * row_step_w;
+        const uint32_t *bp = blk + r * 16;
+        uint32_t        w0 = rp[0];
+        if (NW > 0) {
+#pragma unroll
+            for (int c = 0; c < NW; c++) {
+                const uint32_t w1 = rp[c + 1], sw = bp[c];
+                a0 = sad4(w0, sw, a0);
+                a1 = sad4(fsr(w0, w1, 1), sw, a1);
+                a2 = sad4(fsr(w0, w1, 2), sw, a2);
+                a3 = sad4(fsr(w0, w1, 3), sw, a3);
+                w0 = w1;
+            }
+        } else {
+            const int nwfull = (tailmask == 0xffffffffu) ? nw : nw - 1;
+            for (int c = 0; c < nwfull; c++) {
+                const uint32_t w1 = rp[c + 1], sw = bp[c];
+                a0 = sad4(w0, sw, a0);
+                a1 = sad4(fsr(w0, w1, 1), sw, a1);
+                a2 = sad4(fsr(w0, w1, 2), sw, a2);
+                a3 = sad4(fsr(w0, w1, 3), sw, a3);
+                w0 = w1;
+            }
+            if (nwfull != nw) {
+                const uint32_t w1 = rp[nw], sw = bp[nwfull];
+                a0 = sad4(w0 & tailmask, sw, a0);
+                a1 = sad4(fsr(w0, w1, 1) & tailmask, sw, a1);
+                a2 = sad4(fsr(w0, w1, 2) & tailmask, sw, a2);
+                a3 = sad4(fsr(w0, w1, 3) & tailmask, sw, a3);
+            }
+        }
+    }
+}
+
+template <int NW>
+__device__ void warp_sad_job(SadJob &j, const uint32_t *blk, uint8_t *win, int lane, int rows, int bw, int rstep) {
+    const int W = j.sa_w, H = j.sa_h;
+    if (W <= 0 || H <= 0) return;
+    const bool     skip     = j.skip_line && bw == 16 && rows <= 16;
+    const int      nw       = (bw + 3) >> 2;
+    const uint32_t tailmask = (bw & 3) ? ((1u << (8 * (bw & 3))) - 1u) : 0xffffffffu;
+    const int      ext_y    = (rows - 1) * rstep;
+    const uint8_t *ref      = j.ref;
+    const int      raw      = j.raw_stride;
+    unsigned long long best = ~0ull;
+    // widest tile whose rows (a few candidate rows + the block extent) still fit the warp's window buffer
+    int nx_cap = (((kSadWarpWin / (ext_y + min(H, 8))) & ~15) - 16) - 15 - (bw - 1) - 8;
+    nx_cap     = max(4, min(nx_cap, kTileMaxNx));
+    for (int x0 = 0; x0 < W; x0 += nx_cap) {
+        const int      nx    = min(W - x0, nx_cap);
+        const uint32_t mis   = (uint32_t)((uintptr_t)(ref + x0) & 15);
+        uint32_t       pitch = (mis + nx + bw - 1 + 8 + 15) & ~15u;
+        if (((pitch >> 4) & 1) == 0) pitch += 16;
+        const int rows_fit = max(1, kSadWarpWin / (int)pitch - ext_y);  // >= 1 by the choice of nx_cap
+        const int ngroups  = (int)(((mis & 3) + nx + 3) >> 2);
+        const uint32_t pitchw = pitch >> 2, nvec = pitch >> 4;
+        for (int y0 = 0; y0 < H; y0 += rows_fit) {
+            const int ny = min(H - y0, rows_fit);
+            // stage rows y0 .. y0 + ny - 1 + ext_y of the window: 16-byte vectors from 16-byte aligned addresses
+            const uint8_t *row0  = ref + (int64_t)y0 * raw + x0 - mis;
+            const uint32_t total = nvec * (uint32_t)(ny + ext_y);
+            __syncwarp();
+            for (uint32_t i = lane; i < total; i += 32) {
+                const uint32_t r = i / nvec, v = i - r * nvec;
+                *reinterpret_cast<uint4 *>(win + r * pitch + (v << 4)) = __ldg(reinterpret_cast<const uint4 *>(row0 + (int64_t)r * raw) + v);
+            }
+            __syncwarp();
+            const int nyeff = skip ? ((ny + (y0 & 1)) >> 1) : ny;  // odd candidate rows only
+            const int items = nyeff * ngroups;
+            int       L     = 1;
+            while (L < 32 && items * (L * 2) <= 32 && L * 2 <= rows) L *= 2;
+            const int per_round = 32 / L;
+            const int slice = lane & (L - 1), sub = lane / L;
+            for (int base = 0; base < items; base += per_round) {
+                const int  item   = base + sub;
+                const bool active = item < items;
+                const int  yi = active ? item / ngroups : 0, g = active ? item - yi * ngroups : 0;
+                const int  yy = skip ? (2 * yi + ((y0 & 1) ? 0 : 1)) : yi;
+                uint32_t   a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+                if (active) {
+                    const uint32_t *rowp = reinterpret_cast<const uint32_t *>(win) + (uint32_t)yy * pitchw + (mis >> 2) + g;
+                    sad_rows<NW>(rowp, (uint32_t)rstep * pitchw, blk, slice, L, rows, nw, tailmask, a0, a1, a2, a3);
+                }
+                for (int o = L >> 1; o; o >>= 1) {
+                    a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+                    a2 += __shfl_xor_sync(0xffffffffu, a2, o); a3 += __shfl_xor_sync(0xffffffffu, a3, o);
+                }
+                if (active && slice == 0) {
+                    const int      xb = x0 + 4 * g - (int)(mis & 3), y = y0 + yy;
+                    const uint32_t acc[4] = {a0, a1, a2, a3};
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const int x = xb + c;
+                        if (x >= x0 && x < x0 + nx) {
+                            const unsigned long long key = ((unsigned long long)acc[c] << 32) | ((uint32_t)y << 16) | (uint32_t)x;
+                            best = key < best ? key : best;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    for (int o = 16; o; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+        best = other < best ? other : best;
+    }
+    if (lane == 0 && best != ~0ull && (uint32_t)(best >> 32) < 0xffffffu) {  // strict '<' against the 0xffffff start value
+        j.found = 1; j.best_sad = (uint32_t)(best >> 32);
+        j.by = (int16_t)((best >> 16) & 0xffff); j.bx = (int16_t)(best & 0xffff);
+    }
+}
+
+__global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constant__ MeParams p) {
+    __shared__ __align__(16) uint32_t blk[64 * 16];
+    __shared__ __align__(16) uint8_t  win[kStWarps][kSadWarpWin];
+    SbState  &s = p.states[blockIdx.x];
+    const int n = s.n_sad;
+    if (n == 0) return;
+    const SadJob &j0   = s.sad_jobs[0];
+    const int     rows = j0.rows, bw = j0.block_w, nw = (bw + 3) >> 2;
+    const int     rstep = j0.ref_stride / j0.raw_stride;
+    {   // the source block of this phase (same for every job of the SB), zero beyond block_w
+        const uint8_t *b0 = j0.blk;
+        const int      bs = j0.blk_stride;
+        for (int i = threadIdx.x; i < rows * nw; i += blockDim.x) {
+            const int      r = i / nw, c = i - r * nw;
+            const uint8_t *sp = b0 + (int64_t)r * bs + 4 * c;
+            uint32_t       a;
+            if (4 * c + 4 <= bw && (((uintptr_t)sp) & 3) == 0) a = *reinterpret_cast<const uint32_t *>(sp);
+            else {
+                a = 0;
+                for (int q = 0; q < min(4, bw - 4 * c); q++) a |= (uint32_t)sp[q] << (8 * q);
+            }
+            blk[r * 16 + c] = a;
+        }
+        if (threadIdx.x == 0) {
+            unsigned long long px = 0;
+            for (int ji = 0; ji < n; ji++) {
+                const SadJob &j = s.sad_jobs[ji];
+                if (j.sa_w <= 0 || j.sa_h <= 0) continue;
+                const bool skip = j.skip_line && j.block_w == 16 && j.rows <= 16;
+                px += (unsigned long long)j.sa_w * (skip ? (j.sa_h >> 1) : j.sa_h) * j.rows * j.block_w;
+            }
+            s.px += px;
+        }
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int ji = warp; ji < n; ji += kStWarps) {
+        SadJob &j = s.sad_jobs[ji];
+        if (bw == 16) warp_sad_job<4>(j, blk, win[warp], lane, rows, bw, rstep);
+        else if (bw == 32) warp_sad_job<8>(j, blk, win[warp], lane, rows, bw, rstep);
+        else if (bw == 64) warp_sad_job<16>(j, blk, win[warp], lane, rows, bw, rstep);
+        else warp_sad_job<0>(j, blk, win[warp], lane, rows, bw, rstep);
+    }
+}
+
+// ---- open_loop_me_fullpel_search_sblock jobs: one warp per unit (a strip of candidate rows of one job) ----
+struct FpUnit {
+    int16_t job, x0, y0, nx, ny;
+};
+constexpr int kFpTileNx = 64;
+
+template <bool SUB>
+__global__ void __launch_bounds__(kStThreads) st_fp_kernel(const __grid_constant__ MeParams p) {
+    __shared__ __align__(16) uint32_t src64[64 * 16];
+    extern __shared__ __align__(16) uint8_t win_dyn[];  // kStWarps x kFpWarpWin
+    __shared__ unsigned long long     fp_key[kMaxFpJobs][kPus];
+    __shared__ int                    u_base[kMaxFpJobs + 1], u_strips[kMaxFpJobs], u_ny[kMaxFpJobs];
+    constexpr int RSTEP = SUB ? 2 : 1;
+    SbState  &s = p.states[blockIdx.x];
+    const int n = s.n_fp;
+    if (n == 0) return;
+    for (int i = threadIdx.x; i < 64 * 4; i += blockDim.x) {
+        const int r = i >> 2, v = i & 3;
+        *reinterpret_cast<uint4 *>(&src64[r * 16 + 4 * v]) = __ldg(reinterpret_cast<const uint4 *>(s.src + (int64_t)r * s.src_stride) + v);
+    }
+    for (int i = threadIdx.x; i < n * kPus; i += blockDim.x) (&fp_key[0][0])[i] = ~0ull;
+    if (threadIdx.x == 0) {
+        // units = (job, 64-candidate-wide column, strip of candidate rows): a strip's window (ny + 63 rows) fits the
+        // warp buffer and holds <= 512 candidates, so that the warps of the CTA share a big job
+        int                nu = 0;
+        unsigned long long px = 0;
+        for (int ji = 0; ji < n; ji++) {
+            const FpJob &j = s.fp_jobs[ji];
+            u_base[ji] = nu; u_strips[ji] = 0; u_ny[ji] = 1;
+            if (j.w <= 0 || j.h <= 0) continue;
+            px += (unsigned long long)j.w * j.h * (SUB ? 64 * 32 : 64 * 64);
+            const int      nx    = min((int)j.w, kFpTileNx);
+            const uint32_t pitch = ((15 + nx + 63 + 8 + 15) & ~15u) + 16;  // upper bound of the pitch used below
+            const int      fit   = max(1, kFpWarpWin / (int)pitch - 63);
+            u_ny[ji]     = max(1, min(fit, 512 / nx));
+            u_strips[ji] = (j.h + u_ny[ji] - 1) / u_ny[ji];
+            nu += u_strips[ji] * ((j.w + kFpTileNx - 1) / kFpTileNx);
+        }
+        u_base[n] = nu;
+        s.px += px;
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = lane & 15, half = lane >> 4;
+    const int bx = ((b >> 2) & 1) * 2 + (b & 1), by = (b >> 3) * 2 + ((b >> 1) & 1);
+    uint8_t  *w8 = win_dyn + warp * kFpWarpWin;
+    const int n_units = u_base[n];
+
+    for (int pass = 0; pass < (SUB ? 1 : 2); pass++) {
+        uint32_t sreg[8][4];
+#pragma unroll
+        for (int r = 0; r < 8; r++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) sreg[r][c] = src64[(16 * by + (SUB ? 2 * r : 8 * pass + r)) * 16 + 4 * bx + c];
+        for (int u = warp; u < n_units; u += kStWarps) {
+            int uj = 0;
+            while (uj + 1 < n && u >= u_base[uj + 1]) uj++;
+            const FpJob &j = s.fp_jobs[uj];
+            FpUnit       un;
+            {
+                const int local = u - u_base[uj], xt = local / u_strips[uj], st = local - xt * u_strips[uj];
+                un.job = (int16_t)uj; un.x0 = (int16_t)(xt * kFpTileNx); un.y0 = (int16_t)(st * u_ny[uj]);
+                un.nx = (int16_t)min(j.w - un.x0, kFpTileNx); un.ny = (int16_t)min(j.h - un.y0, u_ny[uj]);
+            }
+            const uint8_t *ref = j.ref + (int64_t)un.y0 * j.ref_stride + un.x0;
+            const uint32_t mis = (uint32_t)((uintptr_t)ref & 15);
+            uint32_t       pitch = (mis + un.nx + 63 + 8 + 15) & ~15u;
+            if (((pitch >> 4) & 1) == 0) pitch += 16;
+            const uint32_t pitchw = pitch >> 2, nvec = pitch >> 4, total = nvec * (uint32_t)(un.ny + 63);
+            const uint8_t *row0 = ref - mis;
+            __syncwarp();
+            for (uint32_t i = lane; i < total; i += 32) {
+                const uint32_t r = i / nvec, v = i - r * nvec;
+                *reinterpret_cast<uint4 *>(w8 + r * pitch + (v << 4)) = __ldg(reinterpret_cast<const uint4 *>(row0 + (int64_t)r * j.ref_stride) + v);
+            }
+            __syncwarp();
+            const int ngroups = (int)(((mis & 3) + un.nx + 3) >> 2);
+            const int items = un.ny * ngroups, rounds = (items + 1) >> 1;
+            uint32_t           best8[4] = {~0u, ~0u, ~0u, ~0u}, best16 = ~0u;
+            unsigned long long best32 = ~0ull, best64 = ~0ull;
+            for (int it = 0; it < rounds; it++) {
+                const int  item   = 2 * it + half;
+                const bool active = item < items;
+                const int  yy = active ? item / ngroups : 0, g = active ? item - yy * ngroups : 0;
+                uint32_t   acc[4][4];
+#pragma unroll
+                for (int c = 0; c < 4; c++) acc[c][0] = acc[c][1] = acc[c][2] = acc[c][3] = 0;
+                if (active) {
+                    const uint32_t *rowp = reinterpret_cast<const uint32_t *>(w8) + (uint32_t)(yy + 16 * by + (SUB ? 0 : 8 * pass)) * pitchw +
+                        (mis >> 2) + g + 4 * bx;
+#pragma unroll
+                    for (int r = 0; r < 8; r++) {
+                        const uint32_t *rp = rowp + (uint32_t)(r * RSTEP) * pitchw;
+                        uint32_t        w[5];
+#pragma unroll
+                        for (int c = 0; c < 5; c++) w[c] = rp[c];
+#pragma unroll
+                        for (int c = 0; c < 4; c++) {
+                            const int      q  = SUB ? ((r >> 2) * 2 + (c >> 1)) : (c >> 1);
+                            const uint32_t sw = sreg[r][c];
+                            acc[0][q] = sad4(w[c], sw, acc[0][q]);
+                            acc[1][q] = sad4(fsr(w[c], w[c + 1], 1), sw, acc[1][q]);
+                            acc[2][q] = sad4(fsr(w[c], w[c + 1], 2), sw, acc[2][q]);
+                            acc[3][q] = sad4(fsr(w[c], w[c + 1], 3), sw, acc[3][q]);
+                        }
+                    }
+                }
+                const int xb = 4 * g - (int)(mis & 3);
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    const int      xx    = xb + c;
+                    const bool     valid = active && xx >= 0 && xx < un.nx;
+                    const uint32_t ord   = (uint32_t)yy * (uint32_t)un.nx + (uint32_t)xx;  // < 65536
+                    if (SUB) {
+                        uint32_t s16 = 0;
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            if (valid) best8[q] = min(best8[q], (acc[c][q] << 16) | ord);
+                            s16 += acc[c][q];
+                        }
+                        if (valid) best16 = min(best16, (s16 << 16) | ord);
+                        uint32_t s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 1);
+                        s32 += __shfl_xor_sync(0xffffffffu, s32, 2);
+                        uint32_t s64 = s32 + __shfl_xor_sync(0xffffffffu, s32, 4);
+                        s64 += __shfl_xor_sync(0xffffffffu, s64, 8);
+                        if (valid) {
+                            best32 = min(best32, ((unsigned long long)s32 << 32) | ord);
+                            best64 = min(best64, ((unsigned long long)s64 << 32) | ord);
+                        }
+                    } else if (valid) {
+                        best8[0] = min(best8[0], (acc[c][0] << 16) | ord);
+                        best8[1] = min(best8[1], (acc[c][1] << 16) | ord);
+                    }
+                }
+            }
+            // fold this lane's minima of the unit into the job's keys: (SAD, raster index inside the job's window)
+            auto gk = [&](uint32_t sad, uint32_t ord) {
+                const uint32_t yy = ord / (uint32_t)un.nx, xx = ord - yy * (uint32_t)un.nx;
+                return ((unsigned long long)(SUB ? sad << 1 : sad) << 32) | (uint32_t)((un.y0 + yy) * j.w + un.x0 + xx);
+            };
+            if (SUB) {
+#pragma unroll
+                for (int q = 0; q < 4; q++)
+                    if (best8[q] != ~0u) atomicMin(&fp_key[un.job][21 + 4 * b + q], gk(best8[q] >> 16, best8[q] & 0xffff));
+                if (best16 != ~0u) atomicMin(&fp_key[un.job][5 + b], gk(best16 >> 16, best16 & 0xffff));
+                if ((b & 3) == 0 && best32 != ~0ull) atomicMin(&fp_key[un.job][1 + (b >> 2)], gk((uint32_t)(best32 >> 32), (uint32_t)best32));
+                if (b == 0 && best64 != ~0ull) atomicMin(&fp_key[un.job][0], gk((uint32_t)(best64 >> 32), (uint32_t)best64));
+            } else {
+#pragma unroll
+                for (int q = 0; q < 2; q++)
+                    if (best8[q] != ~0u) atomicMin(&fp_key[un.job][21 + 4 * b + 2 * pass + q], gk(best8[q] >> 16, best8[q] & 0xffff));
+            }
+        }
+    }
+    if (!SUB) {
+        // FULL SAD (off the open-loop hot path): 16x16 and larger PUs straight from global memory, lane = 16x16 block
+        for (int ji = 0; ji < n; ji++) {
+            const FpJob   &j     = s.fp_jobs[ji];
+            const uint32_t ncand = (uint32_t)max(0, (int)j.w) * (uint32_t)max(0, (int)j.h);
+            const uint32_t nsub = 2 * kStWarps, subi = warp * 2 + half, rounds = (ncand + nsub - 1) / nsub;
+            unsigned long long b16 = ~0ull, b32 = ~0ull, b64 = ~0ull;
+            for (uint32_t it = 0; it < rounds; it++) {
+                const uint32_t i = it * nsub + subi;
+                const bool     active = i < ncand;
+                uint32_t       s16 = 0;
+                if (active) {
+                    const uint32_t y = i / (uint32_t)j.w, x = i - y * (uint32_t)j.w;
+                    const uint8_t *rp = j.ref + (int64_t)(y + 16 * by) * j.ref_stride + x + 16 * bx;
+                    for (int r = 0; r < 16; r++)
+                        for (int c = 0; c < 4; c++) {
+                            uint32_t v = 0;
+                            for (int q = 0; q < 4; q++) v |= (uint32_t)rp[(int64_t)r * j.ref_stride + 4 * c + q] << (8 * q);
+                            s16 = sad4(v, src64[(16 * by + r) * 16 + 4 * bx + c], s16);
+                        }
+                }
+                uint32_t s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 1);
+                s32 += __shfl_xor_sync(0xffffffffu, s32, 2);
+                uint32_t s64 = s32 + __shfl_xor_sync(0xffffffffu, s32, 4);
+                s64 += __shfl_xor_sync(0xffffffffu, s64, 8);
+                if (active) {
+                    b16 = min(b16, ((unsigned long long)s16 << 32) | i);
+                    b32 = min(b32, ((unsigned long long)s32 << 32) | i);
+                    b64 = min(b64, ((unsigned long long)s64 << 32) | i);
+                }
+            }
+            if (b16 != ~0ull) atomicMin(&fp_key[ji][5 + b], b16);
+            if ((b & 3) == 0 && b32 != ~0ull) atomicMin(&fp_key[ji][1 + (b >> 2)], b32);
+            if (b == 0 && b64 != ~0ull) atomicMin(&fp_key[ji][0], b64);
+        }
+    }
+    __syncthreads();
+    // fold the window minima into the running best of the reference (strict '<': earlier results win ties)
+    for (int i = threadIdx.x; i < n * kPus; i += blockDim.x) {
+        const int                ji = i / kPus, pu = i - ji * kPus;
+        const FpJob             &j  = s.fp_jobs[ji];
+        const unsigned long long key = fp_key[ji][pu];
+        if (key == ~0ull) continue;
+        const uint32_t sad = (uint32_t)(key >> 32), ord = (uint32_t)key;
+        if (sad < s.best_sad[j.li][j.ri][pu]) {
+            const int32_t y = (int32_t)(ord / (uint32_t)j.w), x = (int32_t)(ord - (uint32_t)y * (uint32_t)j.w);
+            s.best_sad[j.li][j.ri][pu] = sad;
+            s.best_mv[j.li][j.ri][pu]  = ((uint32_t)(y + j.yo) << 16) | (uint16_t)(x + j.xo);
+        }
+    }
+}
+
+// ---- host: run the program of one picture as a stream-ordered sequence of picture-wide kernels ----
+cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_launches) {
+    static cudaError_t attr = [] {
+        cudaError_t e = cudaFuncSetAttribute(st_fp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStWarps * kFpWarpWin);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStWarps * kFpWarpWin);
+        return e;
+    }();
+    if (attr != cudaSuccess) return attr;
+    const int n_sb = (int)(p.wb * p.hb);
+    int       nl   = 0;
+    st_init_kernel<<<n_sb, kStThreads, 0, st>>>(p); nl++;
+    for (int i = 0; i < p.n_steps;) {
+        if (p.prog[i].kind == STEP_CTL) {
+            int c = 1;
+            while (i + c < p.n_steps && p.prog[i + c].kind == STEP_CTL) c++;
+            st_ctl_kernel<<<(n_sb + 63) / 64, 64, 0, st>>>(p, i, c);
+            i += c;
+        } else {
+            if (p.prog[i].kind == STEP_NXM) st_nxm_kernel<<<n_sb, kStThreads, 0, st>>>(p);
+            else if (p.prog[i].kind == STEP_SAD) st_sad_kernel<<<n_sb, kStThreads, 0, st>>>(p);
+            else if (p.k.me_search_method == 0) st_fp_kernel<true><<<n_sb, kStThreads, kStWarps * kFpWarpWin, st>>>(p);
+            else st_fp_kernel<false><<<n_sb, kStThreads, kStWarps * kFpWarpWin, st>>>(p);
+            i++;
+        }
+        nl++;
+    }
+    st_finish_kernel<<<n_sb, kStThreads, 0, st>>>(p); nl++;
+    if (n_launches) *n_launches = nl;
+    return cudaGetLastError();
+}
+
+size_t staged_state_bytes(uint32_t n_sb) { return (size_t)n_sb * sizeof(SbState); }
+
+}  // namespace svtme

@@ -154,6 +154,7 @@ struct SbState {
     NxmJob   nxm_jobs[kMaxNxmJobs];
     FpJob    fp_jobs[kMaxFpJobs];
     int32_t  n_sad, n_nxm, n_fp;
+    unsigned long long px;  // algorithmic pixel-compares of this SB so far (staged pipeline)
     uint32_t l0_searched;  // references whose HME-L0 quadrants were searched in the current pass (bit li*4+ri)
 };
 

@@ -146,6 +146,7 @@ class DeviceCfg(C.Structure):
         ("max_pictures", C.c_uint32),
         ("max_inflight", C.c_uint32),
         ("sixteenth_from_full", C.c_uint32),
+        ("pipeline", C.c_uint32),
     ]
 
 

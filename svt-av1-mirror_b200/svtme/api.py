@@ -114,9 +114,12 @@ class Picture:
 class MeDevice:
     """One library handle bound to one CUDA device (SvtMeHandle*)."""
 
-    def __init__(self, device=0, max_width=0, max_height=0, max_pictures=0, max_inflight=0, sixteenth_from_full=0):
+    def __init__(self, device=0, max_width=0, max_height=0, max_pictures=0, max_inflight=0, sixteenth_from_full=0,
+                 pipeline=None):
         self.lib = load_library()
-        cfg = abi.DeviceCfg(device, max_width, max_height, max_pictures, max_inflight, sixteenth_from_full)
+        if pipeline is None:
+            pipeline = int(os.environ.get("SVTME_PIPELINE", "0"))
+        cfg = abi.DeviceCfg(device, max_width, max_height, max_pictures, max_inflight, sixteenth_from_full, pipeline)
         h = C.c_void_p()
         rc = self.lib.svtme_init(C.byref(cfg), C.byref(h))
         if rc != 0:
