@@ -836,22 +836,22 @@ enum CtlOp : uint8_t {
 SVTME_HDX int build_program(const SvtMeKnobs &k, Step *st) {
     int n = 0;
     auto ctl = [&](uint8_t op, uint8_t arg) { st[n].kind = STEP_CTL; st[n].op = op; st[n].arg = arg; n++; };
-    auto eng = [&](uint8_t kind) { st[n].kind = kind; st[n].op = 0; st[n].arg = 0; n++; };
+    auto eng = [&](uint8_t kind, uint8_t arg = 0) { st[n].kind = kind; st[n].op = 0; st[n].arg = arg; n++; };  // SAD steps: arg = plane level
     const bool l1_hme = k.temporal_layer_index > 0;  // hme_active(k, 1)
     if (k.me_early_exit_th || k.me_safe_limit_zz_th) { ctl(C_ZZ_MAKE, 0); eng(STEP_NXM); ctl(C_ZZ_FOLD, 0); }
     if (k.prehme_enable) {
         const bool split = k.num_of_list_to_search > 1 && l1_hme && k.prehme_l1_early_exit;
-        for (int pass = 0; pass < (split ? 2 : 1); pass++) { ctl(C_PREHME_MAKE, (uint8_t)(split ? pass : 2)); eng(STEP_SAD); ctl(C_SAD_FOLD, 0); }
+        for (int pass = 0; pass < (split ? 2 : 1); pass++) { ctl(C_PREHME_MAKE, (uint8_t)(split ? pass : 2)); eng(STEP_SAD, 2); ctl(C_SAD_FOLD, 0); }
         ctl(C_PREHME_FINAL, 0);
     }
     if (k.enable_hme_flag) {
         if (k.enable_hme_level0_flag) {
             const bool dep = k.enable_me_sr_adjustment && k.distance_based_hme_resizing && k.reduce_hme_l0_sr_th_min &&
                 k.reduce_hme_l0_sr_th_max;
-            for (int pass = 0; pass < (dep ? 2 : 1); pass++) { ctl(C_L0_MAKE, (uint8_t)(dep ? pass : 2)); eng(STEP_SAD); ctl(C_L0_FOLD, 0); }
+            for (int pass = 0; pass < (dep ? 2 : 1); pass++) { ctl(C_L0_MAKE, (uint8_t)(dep ? pass : 2)); eng(STEP_SAD, 2); ctl(C_L0_FOLD, 0); }
         }
-        if (k.enable_hme_level1_flag) { ctl(C_L1_MAKE, 0); eng(STEP_SAD); ctl(C_SAD_FOLD, 0); }
-        if (k.enable_hme_level2_flag) { ctl(C_L2_MAKE, 0); eng(STEP_SAD); ctl(C_SAD_FOLD, 0); }
+        if (k.enable_hme_level1_flag) { ctl(C_L1_MAKE, 0); eng(STEP_SAD, 1); ctl(C_SAD_FOLD, 0); }
+        if (k.enable_hme_level2_flag) { ctl(C_L2_MAKE, 0); eng(STEP_SAD, 0); ctl(C_SAD_FOLD, 0); }
     }
     ctl(C_FINAL_CENTRE, 0);
     {

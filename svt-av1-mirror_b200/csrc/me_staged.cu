@@ -11,6 +11,8 @@
 // launches of one picture are stream ordered; several pictures are in flight on different streams, so the small
 // control kernels of one picture overlap the engine kernels of another.
 #include <cuda_runtime.h>
+#include <cstdio>
+#include <cstdlib>
 #include "me_engines.cuh"
 #include "me_launch.h"
 
@@ -34,10 +36,12 @@ __global__ void __launch_bounds__(kStThreads) st_init_kernel(const __grid_consta
     sb_init(be, p, p.states[blockIdx.x], blockIdx.x);
 }
 
-// control steps [first, first + count) of the program, one thread per 64x64 block
-__global__ void __launch_bounds__(64) st_ctl_kernel(const __grid_constant__ MeParams p, int first, int count) {
-    const uint32_t sb = blockIdx.x * blockDim.x + threadIdx.x;
-    if (sb >= p.wb * p.hb) return;
+// control steps [first, first + count) of the program: one WARP per 64x64 block with a single active lane -- the code is
+// a long scalar dependency chain with block-dependent branches, so 32 blocks per warp would serialise their paths;
+// one block per warp keeps every chain independent (2040 warps in flight at 4K).
+__global__ void __launch_bounds__(kStThreads) st_ctl_kernel(const __grid_constant__ MeParams p, int first, int count) {
+    const uint32_t sb = blockIdx.x * kStWarps + (threadIdx.x >> 5);
+    if (sb >= p.wb * p.hb || (threadIdx.x & 31) != 0) return;
     SbState &s = p.states[sb];
     for (int i = first; i < first + count; i++) ctl_step(p, s, p.prog[i].op, p.prog[i].arg);
 }
@@ -56,7 +60,7 @@ __global__ void __launch_bounds__(kStThreads) st_nxm_kernel(const __grid_constan
     if (threadIdx.x == 0) {
         unsigned long long px = 0;
         for (int ji = 0; ji < n; ji++) px += (unsigned long long)s.nxm_jobs[ji].rows * s.nxm_jobs[ji].width;
-        s.px += px;
+        if (px) atomicAdd(&s.px, px);
     }
     for (int ji = warp; ji < n; ji += kStWarps) {
         NxmJob        &j   = s.nxm_jobs[ji];
@@ -137,7 +141,7 @@ __device__ __forceinline__ void sad_rows(const uint32_t *rowp, uint32_t row_step
 }
 
 template <int NW>
-__device__ void warp_sad_job(SadJob &j, const uint32_t *blk, uint8_t *win, int lane, int rows, int bw, int rstep) {
+__device__ void warp_sad_job(const SadJob &j, SadJob &jout, const uint32_t *blk, uint8_t *win, int lane, int rows, int bw, int rstep) {
     const int W = j.sa_w, H = j.sa_h;
     if (W <= 0 || H <= 0) return;
     const bool     skip     = j.skip_line && bw == 16 && rows <= 16;
@@ -209,23 +213,264 @@ __device__ void warp_sad_job(SadJob &j, const uint32_t *blk, uint8_t *win, int l
         best = other < best ? other : best;
     }
     if (lane == 0 && best != ~0ull && (uint32_t)(best >> 32) < 0xffffffu) {  // strict '<' against the 0xffffff start value
-        j.found = 1; j.best_sad = (uint32_t)(best >> 32);
-        j.by = (int16_t)((best >> 16) & 0xffff); j.bx = (int16_t)(best & 0xffff);
+        jout.found = 1; jout.best_sad = (uint32_t)(best >> 32);
+        jout.by = (int16_t)((best >> 16) & 0xffff); jout.bx = (int16_t)(best & 0xffff);
     }
 }
 
-__global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constant__ MeParams p) {
+// Window staging for the specialised paths.  Rows are staged word by word (4-byte cp.async, all copies of the warp in
+// flight together) with an ODD row pitch in words, and -- when the block samples every second reference row
+// (sub-sampled SAD) -- with even and odd window rows in two separate planes, so that the rows a candidate reads are
+// consecutive in shared memory.  Lanes that read the same column of different block rows then hit 32 different banks
+// (a 16-byte aligned pitch gave 4- to 8-way conflicts: ncu l1tex__data_bank_conflicts of the first staged version).
+struct WinLayout {
+    uint32_t S;            // row pitch in words (odd)
+    uint32_t plane_words;  // offset of the odd-row plane (0 when rows are not split)
+    int      a;            // byte offset of candidate x0 inside the first staged word
+};
+__device__ __forceinline__ uint32_t win_row_word(const WinLayout &wl, int R, bool split) {
+    return split ? (uint32_t)(R & 1) * wl.plane_words + (uint32_t)(R >> 1) * wl.S : (uint32_t)R * wl.S;
+}
+__device__ __forceinline__ void warp_stage_words(uint32_t *win, const uint8_t *start, int raw_stride, int nrows, int nwords,
+                                                 const WinLayout &wl, bool split, int lane) {
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(win);
+    const uint32_t total = (uint32_t)nrows * (uint32_t)nwords;
+    uint32_t       R = (uint32_t)lane / (uint32_t)nwords, wd = (uint32_t)lane - R * (uint32_t)nwords;
+    const uint32_t dR = 32u / (uint32_t)nwords, dw = 32u - dR * (uint32_t)nwords;
+    for (uint32_t i = lane; i < total; i += 32) {
+        const uint8_t *g = start + (int64_t)R * raw_stride + (wd << 2);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sbase + ((win_row_word(wl, (int)R, split) + wd) << 2)), "l"(g));
+        R += dR; wd += dw;
+        if (wd >= (uint32_t)nwords) { wd -= (uint32_t)nwords; R++; }
+    }
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+}
+
+// Full-size blocks (every SB that does not touch the right/bottom picture edge): block words of the lane live in
+// registers, the row loop is fully unrolled.  L lanes share an item (4 x-adjacent candidates):
+//   sixteenth plane 16x8 rows : L = 1  (windows are large: >= 32 items)         32 source words per lane
+//   quarter plane  32x16 rows : L = 16 (8x3 refinement windows: 6..9 items)      8 source words per lane (one row)
+//   full plane     64x32 rows : L = 32                                          16 source words per lane (one row)
+template <int NW, int ROWS, int L>
+__device__ void warp_sad_job_fast(const SadJob &j, SadJob &jout, const uint32_t *blk, uint32_t *win, int lane, int rstep) {
+    constexpr int RPL = ROWS / L, PER_ROUND = 32 / L;
+    const int W = j.sa_w, H = j.sa_h;
+    if (W <= 0 || H <= 0) return;
+    constexpr int bw = NW * 4;
+    const bool     skip  = j.skip_line && bw == 16 && ROWS <= 16;
+    const bool     split = rstep == 2;
+    const int      ext_y = (ROWS - 1) * rstep;
+    const uint8_t *ref   = j.ref;
+    const int      raw   = j.raw_stride;
+    const int      slice = lane & (L - 1), sub = lane / L;
+    uint32_t       sreg[RPL][NW];
+#pragma unroll
+    for (int k = 0; k < RPL; k++)
+#pragma unroll
+        for (int c = 0; c < NW; c++) sreg[k][c] = blk[(slice + L * k) * 16 + c];
+    unsigned long long best = ~0ull;
+    constexpr int kWinWords = kSadWarpWin / 4;
+    // widest tile whose rows (a few candidate rows + the block extent) still fit the warp's window buffer
+    int nx_cap = (kWinWords / (ext_y + min(H, 8) + 1) - 3) * 4 - bw - 8;
+    nx_cap     = max(4, min(nx_cap, kTileMaxNx));
+    for (int x0 = 0; x0 < W; x0 += nx_cap) {
+        const int nx = min(W - x0, nx_cap);
+        WinLayout wl;
+        wl.a = (int)((uintptr_t)(ref + x0) & 3);
+        const int nwords  = (wl.a + nx + bw - 1 + 3) / 4 + 1;  // +1: the shifted loads touch one word past the last candidate
+        wl.S              = (uint32_t)nwords | 1u;
+        const int rows_fit = max(1, (kWinWords / (int)wl.S) - ext_y - 2);
+        const int ngroups  = (wl.a + nx + 3) >> 2;
+        const float inv_ng = 1.0f / (float)ngroups;
+        for (int y0 = 0; y0 < H; y0 += rows_fit) {
+            const int ny = min(H - y0, rows_fit), nrows = ny + ext_y;
+            wl.plane_words = split ? (uint32_t)((nrows + 1) >> 1) * wl.S : 0u;
+            __syncwarp();
+            warp_stage_words(win, ref + (int64_t)y0 * raw + x0 - wl.a, raw, nrows, nwords, wl, split, lane);
+            const int nyeff = skip ? ((ny + (y0 & 1)) >> 1) : ny;
+            const int items = nyeff * ngroups;
+            for (int base = 0; base < items; base += PER_ROUND) {
+                const int  item   = base + sub;
+                const bool active = item < items;
+                const int  yi = active ? (int)(((float)item + 0.5f) * inv_ng) : 0, g = active ? item - yi * ngroups : 0;
+                const int  yy = skip ? (2 * yi + ((y0 & 1) ? 0 : 1)) : yi;
+                uint32_t   a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+                if (active) {
+                    // block row r of candidate row yy is window row yy + r * rstep: consecutive rows of one plane
+                    const uint32_t row_step = split ? wl.S : (uint32_t)rstep * wl.S;
+                    const uint32_t *rowp = win + win_row_word(wl, yy, split) + (uint32_t)slice * row_step + g;
+#pragma unroll
+                    for (int k = 0; k < RPL; k++) {
+                        const uint32_t *rp = rowp + (uint32_t)(L * k) * row_step;
+                        uint32_t        w[NW + 1];
+#pragma unroll
+                        for (int c = 0; c <= NW; c++) w[c] = rp[c];
+#pragma unroll
+                        for (int c = 0; c < NW; c++) {
+                            const uint32_t sw = sreg[k][c];
+                            a0 = sad4(w[c], sw, a0);
+                            a1 = sad4(fsr(w[c], w[c + 1], 1), sw, a1);
+                            a2 = sad4(fsr(w[c], w[c + 1], 2), sw, a2);
+                            a3 = sad4(fsr(w[c], w[c + 1], 3), sw, a3);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int o = L >> 1; o; o >>= 1) {
+                    a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+                    a2 += __shfl_xor_sync(0xffffffffu, a2, o); a3 += __shfl_xor_sync(0xffffffffu, a3, o);
+                }
+                if (active && slice == 0) {
+                    const int      xb = x0 + 4 * g - wl.a;
+                    const uint32_t yk = (uint32_t)(y0 + yy) << 16;
+                    const uint32_t acc[4] = {a0, a1, a2, a3};
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const int x = xb + c;
+                        if (x >= x0 && x < x0 + nx) {
+                            const unsigned long long key = ((unsigned long long)acc[c] << 32) | yk | (uint32_t)x;
+                            best = key < best ? key : best;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    for (int o = 16; o; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+        best = other < best ? other : best;
+    }
+    if (lane == 0 && best != ~0ull && (uint32_t)(best >> 32) < 0xffffffu) {
+        jout.found = 1; jout.best_sad = (uint32_t)(best >> 32);
+        jout.by = (int16_t)((best >> 16) & 0xffff); jout.bx = (int16_t)(best & 0xffff);
+    }
+}
+
+// Refinement windows (HME level 1 / 2: at most 8 candidates wide, a few rows high) on big blocks: lane = one block row.
+// The lane pulls its window row into registers ONCE per candidate row, normalises the byte alignment with one funnel
+// shift per word, and evaluates all 8 x-candidates from registers; the 8 partial SADs are summed over the rows with
+// a transposing butterfly (9 shuffles instead of 40).  ROWS lanes form a group; 32 / ROWS candidate rows run at once.
+template <int NW, int ROWS>
+__device__ void warp_sad_job_rows(const SadJob &j, SadJob &jout, const uint32_t *blk, uint32_t *win, int lane, int rstep) {
+    constexpr int SUBS = 32 / ROWS, MAXW = NW + 3;
+    const int W = j.sa_w, H = j.sa_h;  // W <= 8
+    if (W <= 0 || H <= 0) return;
+    constexpr int bw = NW * 4;
+    const bool     split = rstep == 2;
+    const int      ext_y = (ROWS - 1) * rstep;
+    const uint8_t *ref   = j.ref;
+    const int      raw   = j.raw_stride;
+    const int      slice = lane & (ROWS - 1), sub = lane / ROWS;
+    uint32_t       sreg[NW];
+#pragma unroll
+    for (int c = 0; c < NW; c++) sreg[c] = blk[slice * 16 + c];
+    unsigned long long best = ~0ull;
+    constexpr int kWinWords = kSadWarpWin / 4;
+    WinLayout wl;
+    wl.a = (int)((uintptr_t)ref & 3);
+    constexpr int nwords = MAXW + 1;  // bytes a .. a + 7 + bw - 1, plus the word the alignment shift pulls in
+    wl.S = (uint32_t)nwords | 1u;
+    const int rows_fit = max(1, (kWinWords / (int)wl.S) - ext_y - 2);
+    const int shift = 8 * wl.a;
+    // which of the 8 candidates this lane owns after the transposing reduction
+    const int own = ROWS == 32 ? (((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1))
+                               : (((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1));
+    for (int y0 = 0; y0 < H; y0 += rows_fit) {
+        const int ny = min(H - y0, rows_fit), nrows = ny + ext_y;
+        wl.plane_words = split ? (uint32_t)((nrows + 1) >> 1) * wl.S : 0u;
+        __syncwarp();
+        warp_stage_words(win, ref + (int64_t)y0 * raw - wl.a, raw, nrows, nwords, wl, split, lane);
+        for (int yb = 0; yb < ny; yb += SUBS) {
+            const int  yy     = yb + sub;
+            const bool active = yy < ny;
+            uint32_t   acc[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) acc[i] = 0;
+            if (active) {
+                const uint32_t *rp = win + win_row_word(wl, yy, split) + (uint32_t)slice * wl.S;
+                uint32_t        w[MAXW + 1];
+#pragma unroll
+                for (int c = 0; c <= MAXW; c++) w[c] = rp[c];
+#pragma unroll
+                for (int c = 0; c < MAXW; c++) w[c] = __funnelshift_r(w[c], w[c + 1], shift);  // candidate 0 now starts at byte 0
+#pragma unroll
+                for (int g = 0; g < 2; g++)
+#pragma unroll
+                    for (int c = 0; c < NW; c++) {
+                        const uint32_t sw = sreg[c], lo = w[g + c], hi = w[g + c + 1];
+                        acc[4 * g + 0] = sad4(lo, sw, acc[4 * g + 0]);
+                        acc[4 * g + 1] = sad4(fsr(lo, hi, 1), sw, acc[4 * g + 1]);
+                        acc[4 * g + 2] = sad4(fsr(lo, hi, 2), sw, acc[4 * g + 2]);
+                        acc[4 * g + 3] = sad4(fsr(lo, hi, 3), sw, acc[4 * g + 3]);
+                    }
+            }
+            // transposing butterfly over the ROWS lanes of the group: 8 -> 4 -> 2 -> 1 values per lane, then plain sums
+            uint32_t v4[4], v2[2], v1;
+            {
+                const bool up = lane & (ROWS / 2);
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const uint32_t send = up ? acc[i] : acc[4 + i], keep = up ? acc[4 + i] : acc[i];
+                    v4[i] = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 2);
+                }
+            }
+            {
+                const bool up = lane & (ROWS / 4);
+#pragma unroll
+                for (int i = 0; i < 2; i++) {
+                    const uint32_t send = up ? v4[i] : v4[2 + i], keep = up ? v4[2 + i] : v4[i];
+                    v2[i] = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 4);
+                }
+            }
+            {
+                const bool     up   = lane & (ROWS / 8);
+                const uint32_t send = up ? v2[0] : v2[1], keep = up ? v2[1] : v2[0];
+                v1 = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 8);
+            }
+#pragma unroll
+            for (int o = ROWS / 16; o; o >>= 1) v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+            if (active && own < W && (lane & (ROWS / 8 - 1)) == 0) {
+                const unsigned long long key = ((unsigned long long)v1 << 32) | ((uint32_t)(y0 + yy) << 16) | (uint32_t)own;
+                best = key < best ? key : best;
+            }
+        }
+    }
+    for (int o = 16; o; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+        best = other < best ? other : best;
+    }
+    if (lane == 0 && best != ~0ull && (uint32_t)(best >> 32) < 0xffffffu) {
+        jout.found = 1; jout.best_sad = (uint32_t)(best >> 32);
+        jout.by = (int16_t)((best >> 16) & 0xffff); jout.bx = (int16_t)(best & 0xffff);
+    }
+}
+
+// `lvl`: plane of this phase (2 sixteenth: pre-HME / level 0, 1 quarter: level 1, 0 full: level 2).  The source block is
+// derived from the block index alone, so its staging overlaps the fetch of the job descriptors.
+__global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constant__ MeParams p, int lvl) {
     __shared__ __align__(16) uint32_t blk[64 * 16];
     __shared__ __align__(16) uint8_t  win[kStWarps][kSadWarpWin];
+    __shared__ __align__(16) SadJob   jobs[kMaxSadJobs];
+    static_assert(sizeof(SadJob) % 8 == 0, "SadJob is copied as 64-bit words");
     SbState  &s = p.states[blockIdx.x];
     const int n = s.n_sad;
-    if (n == 0) return;
-    const SadJob &j0   = s.sad_jobs[0];
-    const int     rows = j0.rows, bw = j0.block_w, nw = (bw + 3) >> 2;
-    const int     rstep = j0.ref_stride / j0.raw_stride;
+    {
+        const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.sad_jobs[0]);
+        unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
+        for (int i = threadIdx.x; i < (int)(kMaxSadJobs * sizeof(SadJob) / 8); i += blockDim.x) dst[i] = src[i];
+    }
+    // block geometry as in make_sad_job (me_control.cuh)
+    const DevPlane &cp   = p.cur.lvl[lvl];
+    const bool      full = p.k.hme_search_method == 1;
+    const uint32_t  aw = (uint32_t)((p.cur.lvl[0].width + 7) & ~7), ah = (uint32_t)((p.cur.lvl[0].height + 7) & ~7);
+    const uint32_t  org_x = (blockIdx.x % p.wb) * 64, org_y = (blockIdx.x / p.wb) * 64;
+    const uint32_t  b64_w = min(64u, aw - org_x), b64_h = min(64u, ah - org_y);
+    const int       bw = (int)(b64_w >> lvl), rows = (int)(full ? (b64_h >> lvl) : ((b64_h >> lvl) >> 1)), nw = (bw + 3) >> 2;
+    const int       rstep = full ? 1 : 2;
     {   // the source block of this phase (same for every job of the SB), zero beyond block_w
-        const uint8_t *b0 = j0.blk;
-        const int      bs = j0.blk_stride;
+        const uint8_t *b0 = cp.org + (int64_t)(org_y >> lvl) * cp.stride + (org_x >> lvl);
+        const int      bs = full ? cp.stride : cp.stride * 2;
         for (int i = threadIdx.x; i < rows * nw; i += blockDim.x) {
             const int      r = i / nw, c = i - r * nw;
             const uint8_t *sp = b0 + (int64_t)r * bs + 4 * c;
@@ -237,26 +482,30 @@ __global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constan
             }
             blk[r * 16 + c] = a;
         }
-        if (threadIdx.x == 0) {
-            unsigned long long px = 0;
-            for (int ji = 0; ji < n; ji++) {
-                const SadJob &j = s.sad_jobs[ji];
-                if (j.sa_w <= 0 || j.sa_h <= 0) continue;
-                const bool skip = j.skip_line && j.block_w == 16 && j.rows <= 16;
-                px += (unsigned long long)j.sa_w * (skip ? (j.sa_h >> 1) : j.sa_h) * j.rows * j.block_w;
-            }
-            s.px += px;
-        }
     }
+    if (n == 0) return;
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    unsigned long long px = 0;
     for (int ji = warp; ji < n; ji += kStWarps) {
-        SadJob &j = s.sad_jobs[ji];
-        if (bw == 16) warp_sad_job<4>(j, blk, win[warp], lane, rows, bw, rstep);
-        else if (bw == 32) warp_sad_job<8>(j, blk, win[warp], lane, rows, bw, rstep);
-        else if (bw == 64) warp_sad_job<16>(j, blk, win[warp], lane, rows, bw, rstep);
-        else warp_sad_job<0>(j, blk, win[warp], lane, rows, bw, rstep);
+        const SadJob &j  = jobs[ji];
+        SadJob       &jo = s.sad_jobs[ji];
+        uint32_t     *w32 = reinterpret_cast<uint32_t *>(win[warp]);
+        if (j.sa_w > 0 && j.sa_h > 0) {
+            const bool skip = j.skip_line && bw == 16 && rows <= 16;
+            px += (unsigned long long)j.sa_w * (skip ? (j.sa_h >> 1) : j.sa_h) * rows * bw;
+        }
+        if (bw == 16 && rows == 8) warp_sad_job_fast<4, 8, 1>(j, jo, blk, w32, lane, rstep);
+        else if (bw == 32 && rows == 16 && j.sa_w <= 8 && j.sa_h <= 16) warp_sad_job_rows<8, 16>(j, jo, blk, w32, lane, rstep);
+        else if (bw == 64 && rows == 32 && j.sa_w <= 8 && j.sa_h <= 16) warp_sad_job_rows<16, 32>(j, jo, blk, w32, lane, rstep);
+        else if (bw == 32 && rows == 16 && j.sa_w * j.sa_h <= 64) warp_sad_job_fast<8, 16, 16>(j, jo, blk, w32, lane, rstep);
+        else if (bw == 64 && rows == 32 && j.sa_w * j.sa_h <= 64) warp_sad_job_fast<16, 32, 32>(j, jo, blk, w32, lane, rstep);
+        else if (bw == 16) warp_sad_job<4>(j, jo, blk, win[warp], lane, rows, bw, rstep);
+        else if (bw == 32) warp_sad_job<8>(j, jo, blk, win[warp], lane, rows, bw, rstep);
+        else if (bw == 64) warp_sad_job<16>(j, jo, blk, win[warp], lane, rows, bw, rstep);
+        else warp_sad_job<0>(j, jo, blk, win[warp], lane, rows, bw, rstep);
     }
+    if (lane == 0 && px) atomicAdd(&s.px, px);
 }
 
 // ---- open_loop_me_fullpel_search_sblock jobs: one warp per unit (a strip of candidate rows of one job) ----
@@ -270,23 +519,34 @@ __global__ void __launch_bounds__(kStThreads) st_fp_kernel(const __grid_constant
     __shared__ __align__(16) uint32_t src64[64 * 16];
     extern __shared__ __align__(16) uint8_t win_dyn[];  // kStWarps x kFpWarpWin
     __shared__ unsigned long long     fp_key[kMaxFpJobs][kPus];
+    __shared__ __align__(16) FpJob    jobs[kMaxFpJobs];
     __shared__ int                    u_base[kMaxFpJobs + 1], u_strips[kMaxFpJobs], u_ny[kMaxFpJobs];
+    static_assert(sizeof(FpJob) % 8 == 0, "FpJob is copied as 64-bit words");
     constexpr int RSTEP = SUB ? 2 : 1;
     SbState  &s = p.states[blockIdx.x];
     const int n = s.n_fp;
     if (n == 0) return;
-    for (int i = threadIdx.x; i < 64 * 4; i += blockDim.x) {
-        const int r = i >> 2, v = i & 3;
-        *reinterpret_cast<uint4 *>(&src64[r * 16 + 4 * v]) = __ldg(reinterpret_cast<const uint4 *>(s.src + (int64_t)r * s.src_stride) + v);
+    {
+        const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.fp_jobs[0]);
+        unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
+        for (int i = threadIdx.x; i < (int)(kMaxFpJobs * sizeof(FpJob) / 8); i += blockDim.x) dst[i] = src[i];
+        // the 64x64 source block: its address follows from the block index (sb_init)
+        const DevPlane &f   = p.cur.lvl[0];
+        const uint8_t  *sp0 = f.org + (int64_t)((blockIdx.x / p.wb) * 64) * f.stride + (blockIdx.x % p.wb) * 64;
+        for (int i = threadIdx.x; i < 64 * 4; i += blockDim.x) {
+            const int r = i >> 2, v = i & 3;
+            *reinterpret_cast<uint4 *>(&src64[r * 16 + 4 * v]) = __ldg(reinterpret_cast<const uint4 *>(sp0 + (int64_t)r * f.stride) + v);
+        }
     }
     for (int i = threadIdx.x; i < n * kPus; i += blockDim.x) (&fp_key[0][0])[i] = ~0ull;
+    __syncthreads();
     if (threadIdx.x == 0) {
         // units = (job, 64-candidate-wide column, strip of candidate rows): a strip's window (ny + 63 rows) fits the
         // warp buffer and holds <= 512 candidates, so that the warps of the CTA share a big job
         int                nu = 0;
         unsigned long long px = 0;
         for (int ji = 0; ji < n; ji++) {
-            const FpJob &j = s.fp_jobs[ji];
+            const FpJob &j = jobs[ji];
             u_base[ji] = nu; u_strips[ji] = 0; u_ny[ji] = 1;
             if (j.w <= 0 || j.h <= 0) continue;
             px += (unsigned long long)j.w * j.h * (SUB ? 64 * 32 : 64 * 64);
@@ -298,7 +558,7 @@ __global__ void __launch_bounds__(kStThreads) st_fp_kernel(const __grid_constant
             nu += u_strips[ji] * ((j.w + kFpTileNx - 1) / kFpTileNx);
         }
         u_base[n] = nu;
-        s.px += px;
+        if (px) atomicAdd(&s.px, px);
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -316,7 +576,7 @@ __global__ void __launch_bounds__(kStThreads) st_fp_kernel(const __grid_constant
         for (int u = warp; u < n_units; u += kStWarps) {
             int uj = 0;
             while (uj + 1 < n && u >= u_base[uj + 1]) uj++;
-            const FpJob &j = s.fp_jobs[uj];
+            const FpJob &j = jobs[uj];
             FpUnit       un;
             {
                 const int local = u - u_base[uj], xt = local / u_strips[uj], st = local - xt * u_strips[uj];
@@ -416,7 +676,7 @@ __global__ void __launch_bounds__(kStThreads) st_fp_kernel(const __grid_constant
     if (!SUB) {
         // FULL SAD (off the open-loop hot path): 16x16 and larger PUs straight from global memory, lane = 16x16 block
         for (int ji = 0; ji < n; ji++) {
-            const FpJob   &j     = s.fp_jobs[ji];
+            const FpJob   &j     = jobs[ji];
             const uint32_t ncand = (uint32_t)max(0, (int)j.w) * (uint32_t)max(0, (int)j.h);
             const uint32_t nsub = 2 * kStWarps, subi = warp * 2 + half, rounds = (ncand + nsub - 1) / nsub;
             unsigned long long b16 = ~0ull, b32 = ~0ull, b64 = ~0ull;
@@ -453,7 +713,7 @@ __global__ void __launch_bounds__(kStThreads) st_fp_kernel(const __grid_constant
     // fold the window minima into the running best of the reference (strict '<': earlier results win ties)
     for (int i = threadIdx.x; i < n * kPus; i += blockDim.x) {
         const int                ji = i / kPus, pu = i - ji * kPus;
-        const FpJob             &j  = s.fp_jobs[ji];
+        const FpJob             &j  = jobs[ji];
         const unsigned long long key = fp_key[ji][pu];
         if (key == ~0ull) continue;
         const uint32_t sad = (uint32_t)(key >> 32), ord = (uint32_t)key;
@@ -475,23 +735,47 @@ cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_
     if (attr != cudaSuccess) return attr;
     const int n_sb = (int)(p.wb * p.hb);
     int       nl   = 0;
-    st_init_kernel<<<n_sb, kStThreads, 0, st>>>(p); nl++;
+    // SVTME_TRACE=1: per-step device times of every picture on stderr (serialises the stream; diagnostics only)
+    static const bool trace = getenv("SVTME_TRACE") != nullptr;
+    cudaEvent_t ev[kMaxSteps + 4];
+    const char *nm[kMaxSteps + 4];
+    int         ne = 0;
+    auto mark = [&](const char *name) {
+        if (!trace) return;
+        cudaEventCreate(&ev[ne]); cudaEventRecord(ev[ne], st); nm[ne] = name; ne++;
+    };
+    mark("start");
+    st_init_kernel<<<n_sb, kStThreads, 0, st>>>(p); nl++; mark("init");
     for (int i = 0; i < p.n_steps;) {
         if (p.prog[i].kind == STEP_CTL) {
             int c = 1;
             while (i + c < p.n_steps && p.prog[i + c].kind == STEP_CTL) c++;
-            st_ctl_kernel<<<(n_sb + 63) / 64, 64, 0, st>>>(p, i, c);
-            i += c;
+            st_ctl_kernel<<<(n_sb + kStWarps - 1) / kStWarps, kStThreads, 0, st>>>(p, i, c);
+            i += c; mark("ctl");
         } else {
             if (p.prog[i].kind == STEP_NXM) st_nxm_kernel<<<n_sb, kStThreads, 0, st>>>(p);
-            else if (p.prog[i].kind == STEP_SAD) st_sad_kernel<<<n_sb, kStThreads, 0, st>>>(p);
+            else if (p.prog[i].kind == STEP_SAD) st_sad_kernel<<<n_sb, kStThreads, 0, st>>>(p, (int)p.prog[i].arg);
             else if (p.k.me_search_method == 0) st_fp_kernel<true><<<n_sb, kStThreads, kStWarps * kFpWarpWin, st>>>(p);
             else st_fp_kernel<false><<<n_sb, kStThreads, kStWarps * kFpWarpWin, st>>>(p);
+            mark(p.prog[i].kind == STEP_NXM ? "nxm" : p.prog[i].kind == STEP_SAD ? "sad" : "fp");
             i++;
         }
         nl++;
     }
-    st_finish_kernel<<<n_sb, kStThreads, 0, st>>>(p); nl++;
+    st_finish_kernel<<<n_sb, kStThreads, 0, st>>>(p); nl++; mark("finish");
+    if (trace) {
+        cudaStreamSynchronize(st);
+        float tot = 0.f;
+        fprintf(stderr, "[svtme trace] tl=%d refs=%d+%d:", p.k.temporal_layer_index, p.k.num_of_ref_pic_to_search[0], p.k.num_of_ref_pic_to_search[1]);
+        for (int i = 1; i < ne; i++) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, ev[i - 1], ev[i]);
+            tot += ms;
+            fprintf(stderr, " %s %.1f", nm[i], ms * 1e3f);
+        }
+        fprintf(stderr, " | total %.1f us\n", tot * 1e3f);
+        for (int i = 0; i < ne; i++) cudaEventDestroy(ev[i]);
+    }
     if (n_launches) *n_launches = nl;
     return cudaGetLastError();
 }

@@ -1,4 +1,4 @@
-for pl in 0 1; do echo "== pipeline $pl"; SVTME_PIPELINE=$pl python bench.py --steps 3 --warmup 3 --no-cpu-baseline 2>&1 | python -c "
+for pl in ${PIPES:-0 1}; do echo "== pipeline $pl"; SVTME_PIPELINE=$pl python bench.py --steps 3 --warmup 3 --no-cpu-baseline ${BENCH_ARGS} 2>&1 | python -c "
 import sys,json
 for l in sys.stdin:
     if l.startswith('{'):
