@@ -69,9 +69,20 @@ __global__ void __launch_bounds__(kStThreads) st_nxm_kernel(const __grid_constan
         const int      sst = j.src_stride, rst = j.ref_stride;
         const uint32_t tail = (width & 3) ? ((1u << (8 * (width & 3))) - 1u) : 0xffffffffu;
         uint32_t       acc = 0;
-        if ((((uintptr_t)src | (uint32_t)sst) & 3) == 0) {
+        if (width == 64 && (((uintptr_t)src | (uint32_t)sst | (uint32_t)rst) & 3) == 0) {
+            // the common case (64 x 32 sub-sampled rows): lane = (column word, row parity); the loads of 8 rows are
+            // independent and issued together.  The second reference word is read even when the row is word aligned --
+            // it lies inside the padded plane -- so that the loop has no data-dependent branch.
+            const int       c  = lane & 15, sh = 8 * (int)((uintptr_t)ref & 3);
+            const uint8_t  *sp = src + (int64_t)(lane >> 4) * sst + 4 * c;
+            const uint32_t *rp = reinterpret_cast<const uint32_t *>(ref - ((uintptr_t)ref & 3) + (int64_t)(lane >> 4) * rst) + c;
+#pragma unroll 8
+            for (int r = lane >> 4; r < rows; r += 2, sp += 2 * (int64_t)sst, rp += (int64_t)rst >> 1) {
+                const uint32_t a = *reinterpret_cast<const uint32_t *>(sp), lo = rp[0], hi = rp[1];
+                acc = sad4(a, __funnelshift_r(lo, hi, sh), acc);
+            }
+        } else if ((((uintptr_t)src | (uint32_t)sst) & 3) == 0) {
             // source rows are word aligned (always so on the ME path); reference words come from two aligned loads
-            const int sh = (int)((uintptr_t)ref & 3);
             for (int i = lane; i < rows * nw; i += 32) {
                 const int       r = i / nw, c = i - r * nw;
                 const uint32_t  a = *reinterpret_cast<const uint32_t *>(src + (int64_t)r * sst + 4 * c);
@@ -79,7 +90,6 @@ __global__ void __launch_bounds__(kStThreads) st_nxm_kernel(const __grid_constan
                 const uint32_t *ra = reinterpret_cast<const uint32_t *>(rp - ((uintptr_t)rp & 3));
                 const uint32_t  lo = ra[0], hi = (((uintptr_t)rp & 3) ? ra[1] : 0u);
                 uint32_t        b  = __funnelshift_r(lo, hi, 8 * (int)((uintptr_t)rp & 3));
-                (void)sh;
                 const uint32_t m = (c == nw - 1) ? tail : 0xffffffffu;
                 acc = sad4(a & m, b & m, acc);
             }
@@ -234,14 +244,29 @@ __device__ __forceinline__ uint32_t win_row_word(const WinLayout &wl, int R, boo
 __device__ __forceinline__ void warp_stage_words(uint32_t *win, const uint8_t *start, int raw_stride, int nrows, int nwords,
                                                  const WinLayout &wl, bool split, int lane) {
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(win);
-    const uint32_t total = (uint32_t)nrows * (uint32_t)nwords;
-    uint32_t       R = (uint32_t)lane / (uint32_t)nwords, wd = (uint32_t)lane - R * (uint32_t)nwords;
-    const uint32_t dR = 32u / (uint32_t)nwords, dw = 32u - dR * (uint32_t)nwords;
-    for (uint32_t i = lane; i < total; i += 32) {
-        const uint8_t *g = start + (int64_t)R * raw_stride + (wd << 2);
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sbase + ((win_row_word(wl, (int)R, split) + wd) << 2)), "l"(g));
-        R += dR; wd += dw;
-        if (wd >= (uint32_t)nwords) { wd -= (uint32_t)nwords; R++; }
+    // 2^q lanes per row (smallest power of two >= nwords, at most 32): a copy instruction covers 32 >> q rows, and the
+    // per-copy address arithmetic is a handful of adds (no divisions, no 64-bit multiplies)
+    int q = 5;
+    while (q > 0 && (1 << (q - 1)) >= nwords) q--;
+    const int rpi = 32 >> q, lr = lane >> q, lw = lane & ((1 << q) - 1);
+    const int64_t gstep = (int64_t)rpi * raw_stride;
+    for (int wd = lw; wd < nwords; wd += 32) {  // a second pass only for rows wider than 32 words
+        const uint8_t *g = start + (int64_t)lr * raw_stride + 4 * wd;
+        if (!split) {
+            uint32_t sa = sbase + 4u * ((uint32_t)lr * wl.S + (uint32_t)wd);
+            for (int R = lr; R < nrows; R += rpi, g += gstep, sa += 4u * (uint32_t)rpi * wl.S)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(g));
+        } else if (rpi >= 2) {  // the parity of the lane's rows is fixed
+            uint32_t sa = sbase + 4u * ((uint32_t)(lr & 1) * wl.plane_words + (uint32_t)(lr >> 1) * wl.S + (uint32_t)wd);
+            for (int R = lr; R < nrows; R += rpi, g += gstep, sa += 4u * (uint32_t)(rpi >> 1) * wl.S)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(g));
+        } else {
+            uint32_t sa = sbase + 4u * (uint32_t)wd;
+            for (int R = 0; R < nrows; R += 2, g += 2 * gstep, sa += 4u * wl.S) {
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(g));
+                if (R + 1 < nrows) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa + 4u * wl.plane_words), "l"(g + gstep));
+            }
+        }
     }
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
     __syncwarp();
@@ -347,92 +372,122 @@ __device__ void warp_sad_job_fast(const SadJob &j, SadJob &jout, const uint32_t 
     }
 }
 
-// Refinement windows (HME level 1 / 2: at most 8 candidates wide, a few rows high) on big blocks: lane = one block row.
-// The lane pulls its window row into registers ONCE per candidate row, normalises the byte alignment with one funnel
-// shift per word, and evaluates all 8 x-candidates from registers; the 8 partial SADs are summed over the rows with
-// a transposing butterfly (9 shuffles instead of 40).  ROWS lanes form a group; 32 / ROWS candidate rows run at once.
+// ---- HME level 1 / 2 refinement windows (8x3 candidates on 32x16 / 64x32 sub-sampled blocks): lane = one block row ----
+// The search job is tiny (24 candidates) but every candidate touches the whole block, and each window row is used by
+// at most two candidate rows -- so shared memory is only the transposer between coalesced global rows and "one row
+// per lane".  The lane pulls its window row into registers ONCE per candidate row, normalises the byte alignment with
+// one funnel shift per word and evaluates 8 x-candidates from registers; the 8 partial SADs are summed over the rows
+// with a transposing butterfly (9 shuffles instead of 40).  ROWS lanes form a group; 32 / ROWS candidate rows run at
+// once.  Sub-sampled SAD only (block row r = window row 2r): even and odd window rows live in two planes with an odd
+// word pitch, so the 32 rows read by a warp fall into 32 different banks.
 template <int NW, int ROWS>
-__device__ void warp_sad_job_rows(const SadJob &j, SadJob &jout, const uint32_t *blk, uint32_t *win, int lane, int rstep) {
+struct RowsCfg {
+    static constexpr int kNWords  = NW + 4;                      // window words per row: bytes a .. a+7+bw-1, +1 for the shift
+    static constexpr int kS       = kNWords | 1;                 // odd pitch
+    static constexpr int kExtY    = (ROWS - 1) * 2;
+    static constexpr int kNy      = 4;                           // candidate rows per staged chunk
+    static constexpr int kRowsPad = (kNy + kExtY + 7) & ~7;      // staged in groups of 8 rows
+    static constexpr int kPlaneW  = (kRowsPad / 2) * kS;         // words per parity plane
+    static constexpr int kWinW    = 2 * kPlaneW;
+    static constexpr int kK       = kNWords / 4;                 // cp.async per lane per 8 rows
+    static_assert(kNWords % 4 == 0, "8 rows x kNWords words must be a whole number of warp-wide copies");
+};
+
+template <int NW, int ROWS, bool FULLW>
+__device__ __forceinline__ void rows_job(const SadJob &j, SadJob &jout, const uint32_t (&sreg)[NW], uint32_t *win, int lane,
+                                         int rows, int nw_eff) {
+    using C = RowsCfg<NW, ROWS>;
     constexpr int SUBS = 32 / ROWS, MAXW = NW + 3;
-    const int W = j.sa_w, H = j.sa_h;  // W <= 8
+    const int W = j.sa_w, H = j.sa_h;
     if (W <= 0 || H <= 0) return;
-    constexpr int bw = NW * 4;
-    const bool     split = rstep == 2;
-    const int      ext_y = (ROWS - 1) * rstep;
     const uint8_t *ref   = j.ref;
     const int      raw   = j.raw_stride;
     const int      slice = lane & (ROWS - 1), sub = lane / ROWS;
-    uint32_t       sreg[NW];
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(win);
+    // staging map of this lane: copy k of an 8-row group moves word wk of row rk
+    uint32_t gofs[C::kK], sofs[C::kK];
 #pragma unroll
-    for (int c = 0; c < NW; c++) sreg[c] = blk[slice * 16 + c];
-    unsigned long long best = ~0ull;
-    constexpr int kWinWords = kSadWarpWin / 4;
-    WinLayout wl;
-    wl.a = (int)((uintptr_t)ref & 3);
-    constexpr int nwords = MAXW + 1;  // bytes a .. a + 7 + bw - 1, plus the word the alignment shift pulls in
-    wl.S = (uint32_t)nwords | 1u;
-    const int rows_fit = max(1, (kWinWords / (int)wl.S) - ext_y - 2);
-    const int shift = 8 * wl.a;
+    for (int k = 0; k < C::kK; k++) {
+        const int idx = lane + 32 * k, R = idx / C::kNWords, w = idx - R * C::kNWords;
+        gofs[k] = (uint32_t)(R * raw + 4 * w);
+        sofs[k] = (uint32_t)(((R & 1) * C::kPlaneW + (R >> 1) * C::kS + w) * 4);
+    }
     // which of the 8 candidates this lane owns after the transposing reduction
     const int own = ROWS == 32 ? (((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1))
                                : (((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1));
-    for (int y0 = 0; y0 < H; y0 += rows_fit) {
-        const int ny = min(H - y0, rows_fit), nrows = ny + ext_y;
-        wl.plane_words = split ? (uint32_t)((nrows + 1) >> 1) * wl.S : 0u;
-        __syncwarp();
-        warp_stage_words(win, ref + (int64_t)y0 * raw - wl.a, raw, nrows, nwords, wl, split, lane);
-        for (int yb = 0; yb < ny; yb += SUBS) {
-            const int  yy     = yb + sub;
-            const bool active = yy < ny;
-            uint32_t   acc[8];
+    unsigned long long best = ~0ull;
+    for (int x0 = 0; x0 < W; x0 += 8) {
+        const int a = (int)((uintptr_t)(ref + x0) & 3), shift = 8 * a, wx = min(8, W - x0);
+        for (int y0 = 0; y0 < H; y0 += C::kNy) {
+            const int      ny = min(H - y0, C::kNy);
+            const uint8_t *g0 = ref + (int64_t)y0 * raw + x0 - a;
+            __syncwarp();
+            // always the full kRowsPad rows: the few rows below a short window are inside the plane's physical padding
+            // (96 / 48 rows against the 72 / 32 the search may touch), and the copy loop unrolls to immediates
 #pragma unroll
-            for (int i = 0; i < 8; i++) acc[i] = 0;
-            if (active) {
-                const uint32_t *rp = win + win_row_word(wl, yy, split) + (uint32_t)slice * wl.S;
-                uint32_t        w[MAXW + 1];
+            for (int G = 0; G < C::kRowsPad / 8; G++) {
 #pragma unroll
-                for (int c = 0; c <= MAXW; c++) w[c] = rp[c];
+                for (int k = 0; k < C::kK; k++)
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sbase + sofs[k] + (uint32_t)(G * 4 * C::kS * 4)), "l"(g0 + gofs[k]));
+                g0 += 8 * (int64_t)raw;
+            }
+            asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+            __syncwarp();
+            for (int yb = 0; yb < ny; yb += SUBS) {
+                const int  yy     = yb + sub;
+                const bool active = yy < ny && slice < rows;
+                uint32_t   acc[8];
 #pragma unroll
-                for (int c = 0; c < MAXW; c++) w[c] = __funnelshift_r(w[c], w[c + 1], shift);  // candidate 0 now starts at byte 0
+                for (int i = 0; i < 8; i++) acc[i] = 0;
+                if (active) {
+                    const uint32_t *rp = win + (yy & 1) * C::kPlaneW + ((yy >> 1) + slice) * C::kS;
+                    uint32_t        w[MAXW + 1];
 #pragma unroll
-                for (int g = 0; g < 2; g++)
+                    for (int c = 0; c <= MAXW; c++) w[c] = rp[c];
 #pragma unroll
-                    for (int c = 0; c < NW; c++) {
-                        const uint32_t sw = sreg[c], lo = w[g + c], hi = w[g + c + 1];
-                        acc[4 * g + 0] = sad4(lo, sw, acc[4 * g + 0]);
-                        acc[4 * g + 1] = sad4(fsr(lo, hi, 1), sw, acc[4 * g + 1]);
-                        acc[4 * g + 2] = sad4(fsr(lo, hi, 2), sw, acc[4 * g + 2]);
-                        acc[4 * g + 3] = sad4(fsr(lo, hi, 3), sw, acc[4 * g + 3]);
+                    for (int c = 0; c < MAXW; c++) w[c] = __funnelshift_r(w[c], w[c + 1], shift);  // candidate 0 now starts at byte 0
+#pragma unroll
+                    for (int g = 0; g < 2; g++)
+#pragma unroll
+                        for (int c = 0; c < NW; c++) {
+                            if (FULLW || c < nw_eff) {
+                                const uint32_t sw = sreg[c], lo = w[g + c], hi = w[g + c + 1];
+                                acc[4 * g + 0] = sad4(lo, sw, acc[4 * g + 0]);
+                                acc[4 * g + 1] = sad4(fsr(lo, hi, 1), sw, acc[4 * g + 1]);
+                                acc[4 * g + 2] = sad4(fsr(lo, hi, 2), sw, acc[4 * g + 2]);
+                                acc[4 * g + 3] = sad4(fsr(lo, hi, 3), sw, acc[4 * g + 3]);
+                            }
+                        }
+                }
+                // transposing butterfly over the ROWS lanes of the group: 8 -> 4 -> 2 -> 1 values per lane, then plain sums
+                uint32_t v4[4], v2[2], v1;
+                {
+                    const bool up = lane & (ROWS / 2);
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const uint32_t send = up ? acc[i] : acc[4 + i], keep = up ? acc[4 + i] : acc[i];
+                        v4[i] = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 2);
                     }
-            }
-            // transposing butterfly over the ROWS lanes of the group: 8 -> 4 -> 2 -> 1 values per lane, then plain sums
-            uint32_t v4[4], v2[2], v1;
-            {
-                const bool up = lane & (ROWS / 2);
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const uint32_t send = up ? acc[i] : acc[4 + i], keep = up ? acc[4 + i] : acc[i];
-                    v4[i] = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 2);
                 }
-            }
-            {
-                const bool up = lane & (ROWS / 4);
+                {
+                    const bool up = lane & (ROWS / 4);
 #pragma unroll
-                for (int i = 0; i < 2; i++) {
-                    const uint32_t send = up ? v4[i] : v4[2 + i], keep = up ? v4[2 + i] : v4[i];
-                    v2[i] = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 4);
+                    for (int i = 0; i < 2; i++) {
+                        const uint32_t send = up ? v4[i] : v4[2 + i], keep = up ? v4[2 + i] : v4[i];
+                        v2[i] = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 4);
+                    }
                 }
-            }
-            {
-                const bool     up   = lane & (ROWS / 8);
-                const uint32_t send = up ? v2[0] : v2[1], keep = up ? v2[1] : v2[0];
-                v1 = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 8);
-            }
+                {
+                    const bool     up   = lane & (ROWS / 8);
+                    const uint32_t send = up ? v2[0] : v2[1], keep = up ? v2[1] : v2[0];
+                    v1 = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 8);
+                }
 #pragma unroll
-            for (int o = ROWS / 16; o; o >>= 1) v1 += __shfl_xor_sync(0xffffffffu, v1, o);
-            if (active && own < W && (lane & (ROWS / 8 - 1)) == 0) {
-                const unsigned long long key = ((unsigned long long)v1 << 32) | ((uint32_t)(y0 + yy) << 16) | (uint32_t)own;
-                best = key < best ? key : best;
+                for (int o = ROWS / 16; o; o >>= 1) v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+                if (yy < ny && own < wx && (lane & (ROWS / 8 - 1)) == 0) {
+                    const unsigned long long key = ((unsigned long long)v1 << 32) | ((uint32_t)(y0 + yy) << 16) | (uint32_t)(x0 + own);
+                    best = key < best ? key : best;
+                }
             }
         }
     }
@@ -440,10 +495,54 @@ __device__ void warp_sad_job_rows(const SadJob &j, SadJob &jout, const uint32_t 
         const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
         best = other < best ? other : best;
     }
-    if (lane == 0 && best != ~0ull && (uint32_t)(best >> 32) < 0xffffffu) {
+    if (lane == 0 && best != ~0ull && (uint32_t)(best >> 32) < 0xffffffu) {  // strict '<' against the 0xffffff start value
         jout.found = 1; jout.best_sad = (uint32_t)(best >> 32);
         jout.by = (int16_t)((best >> 16) & 0xffff); jout.bx = (int16_t)(best & 0xffff);
     }
+}
+
+// `lvl` 1: quarter plane, <8, 16>; `lvl` 0: full plane, <16, 32>.  Launched only when hme_search_method is sub-sampled.
+template <int NW, int ROWS>
+__global__ void __launch_bounds__(kStThreads) st_sad_rows_kernel(const __grid_constant__ MeParams p, int lvl) {
+    using C = RowsCfg<NW, ROWS>;
+    constexpr int kBlkPitch = 17;  // odd: lane = row reads are conflict free
+    __shared__ uint32_t              blk[ROWS * kBlkPitch];
+    __shared__ uint32_t              win[kStWarps][C::kWinW];
+    __shared__ __align__(16) SadJob  jobs[kMaxSadJobs];
+    SbState  &s = p.states[blockIdx.x];
+    const int n = s.n_sad;
+    if (n == 0) return;
+    {
+        const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.sad_jobs[0]);
+        unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
+        for (int i = threadIdx.x; i < n * (int)(sizeof(SadJob) / 8); i += blockDim.x) dst[i] = src[i];
+    }
+    // block geometry as in make_sad_job (me_control.cuh)
+    const DevPlane &cp = p.cur.lvl[lvl];
+    const uint32_t  aw = (uint32_t)((p.cur.lvl[0].width + 7) & ~7), ah = (uint32_t)((p.cur.lvl[0].height + 7) & ~7);
+    const uint32_t  org_x = (blockIdx.x % p.wb) * 64, org_y = (blockIdx.x / p.wb) * 64;
+    const uint32_t  b64_w = min(64u, aw - org_x), b64_h = min(64u, ah - org_y);
+    const int       bw = (int)(b64_w >> lvl), rows = (int)((b64_h >> lvl) >> 1), nw_eff = bw >> 2;  // bw is a multiple of 4
+    {   // every second row of the source block (same for every job of the SB)
+        const uint8_t *b0 = cp.org + (int64_t)(org_y >> lvl) * cp.stride + (org_x >> lvl);
+        for (int i = threadIdx.x; i < ROWS * NW; i += blockDim.x) {
+            const int r = i / NW, c = i - r * NW;
+            blk[r * kBlkPitch + c] = (r < rows && c < nw_eff) ? __ldg(reinterpret_cast<const uint32_t *>(b0 + (int64_t)(2 * r) * cp.stride) + c) : 0u;
+        }
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t  sreg[NW];
+#pragma unroll
+    for (int c = 0; c < NW; c++) sreg[c] = blk[(lane & (ROWS - 1)) * kBlkPitch + c];
+    unsigned long long px = 0;
+    for (int ji = warp; ji < n; ji += kStWarps) {
+        const SadJob &j = jobs[ji];
+        if (j.sa_w > 0 && j.sa_h > 0) px += (uint32_t)(j.sa_w * j.sa_h) * (uint32_t)(rows * bw);
+        if (nw_eff == NW) rows_job<NW, ROWS, true>(j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff);
+        else rows_job<NW, ROWS, false>(j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff);
+    }
+    if (lane == 0 && px) atomicAdd(&s.px, px);
 }
 
 // `lvl`: plane of this phase (2 sixteenth: pre-HME / level 0, 1 quarter: level 1, 0 full: level 2).  The source block is
@@ -496,8 +595,6 @@ __global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constan
             px += (unsigned long long)j.sa_w * (skip ? (j.sa_h >> 1) : j.sa_h) * rows * bw;
         }
         if (bw == 16 && rows == 8) warp_sad_job_fast<4, 8, 1>(j, jo, blk, w32, lane, rstep);
-        else if (bw == 32 && rows == 16 && j.sa_w <= 8 && j.sa_h <= 16) warp_sad_job_rows<8, 16>(j, jo, blk, w32, lane, rstep);
-        else if (bw == 64 && rows == 32 && j.sa_w <= 8 && j.sa_h <= 16) warp_sad_job_rows<16, 32>(j, jo, blk, w32, lane, rstep);
         else if (bw == 32 && rows == 16 && j.sa_w * j.sa_h <= 64) warp_sad_job_fast<8, 16, 16>(j, jo, blk, w32, lane, rstep);
         else if (bw == 64 && rows == 32 && j.sa_w * j.sa_h <= 64) warp_sad_job_fast<16, 32, 32>(j, jo, blk, w32, lane, rstep);
         else if (bw == 16) warp_sad_job<4>(j, jo, blk, win[warp], lane, rows, bw, rstep);
@@ -725,11 +822,241 @@ __global__ void __launch_bounds__(kStThreads) st_fp_kernel(const __grid_constant
     }
 }
 
+// ---- sub-sampled full-pel search (the open-loop hot path): CTA-wide windows, balanced rounds ----
+// All windows of the block's jobs are staged TOGETHER into shared memory with asynchronous 4-byte copies (one exposed
+// memory latency per CTA); the candidates of all windows then form one flat list of ROUNDS dealt to the 4 warps.
+// A round = one group of 4 x-adjacent candidates for FOUR candidate rows 4k .. 4k+3: half-warp `half` takes rows
+// 4k + half and 4k + half + 2.  Those two rows share 7 of their 8 sub-sampled reference rows, so 9 window rows
+// (loads + funnel shifts) serve 8 candidates -- LDS and SHF per SAD are nearly halved against one row per item.
+// lane & 15 = a 16x16 block of the 64x64 (z-order), its 8 source rows (32 words) live in registers.
+// Layout of a window: even and odd rows in two planes (offset = 16 mod 32 words), row i of a plane at
+// i * P + (i >> 3) with P = 0 mod 4: the 32 lanes of a load hit banks 16 * half + by + 4 * bx + const -- no conflicts.
+// Minima: 32-bit keys (sad << 12 | candidate index inside the <= 64 x 64 sub-window); 32x32 / 64x64 sums by a
+// transposing butterfly (8 shuffles for 8 candidates).
+constexpr int kFpBufWords = 11 * 1024;  // 44 KB of windows per CTA
+constexpr int kFpMaxSub   = 16;
+struct FpSub {
+    int16_t job, x0, y0, nx, ny, a, ngroups, P;
+    int32_t off, plane_words, rbase, rounds;
+};
+
+__global__ void __launch_bounds__(kStThreads, 4) st_fp_sub_kernel(const __grid_constant__ MeParams p) {
+    __shared__ __align__(16) uint32_t src64[64 * 16];
+    extern __shared__ __align__(16) uint32_t fp_win[];  // kFpBufWords
+    __shared__ unsigned long long     fp_key[kMaxFpJobs][kPus];
+    __shared__ __align__(16) FpJob    jobs[kMaxFpJobs];
+    __shared__ FpSub                  subs[kFpMaxSub];
+    __shared__ int                    n_sub, cur_job, cur_xt, cur_st;
+    SbState  &s = p.states[blockIdx.x];
+    const int n = s.n_fp;
+    if (n == 0) return;
+    {
+        const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.fp_jobs[0]);
+        unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
+        for (int i = threadIdx.x; i < n * (int)(sizeof(FpJob) / 8); i += blockDim.x) dst[i] = src[i];
+        // the 64x64 source block: its address follows from the block index (sb_init)
+        const DevPlane &f   = p.cur.lvl[0];
+        const uint8_t  *sp0 = f.org + (int64_t)((blockIdx.x / p.wb) * 64) * f.stride + (blockIdx.x % p.wb) * 64;
+        for (int i = threadIdx.x; i < 64 * 4; i += blockDim.x) {
+            const int r = i >> 2, v = i & 3;
+            *reinterpret_cast<uint4 *>(&src64[r * 16 + 4 * v]) = __ldg(reinterpret_cast<const uint4 *>(sp0 + (int64_t)r * f.stride) + v);
+        }
+        for (int i = threadIdx.x; i < n * kPus; i += blockDim.x) (&fp_key[0][0])[i] = ~0ull;
+        if (threadIdx.x == 0) { cur_job = 0; cur_xt = 0; cur_st = 0; }
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = lane & 15, half = lane >> 4;
+    const int bx = ((b >> 2) & 1) * 2 + (b & 1), by = (b >> 3) * 2 + ((b >> 1) & 1);
+    uint32_t  sreg[8][4];  // every second row of the lane's 16x16 block
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) sreg[r][c] = src64[(16 * by + 2 * r) * 16 + 4 * bx + c];
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(fp_win);
+
+    for (;;) {
+        if (threadIdx.x == 0) {
+            // next batch of sub-windows (job, 64-wide column, 64-high strip) that fits the buffer
+            int                ns = 0, used = 0, rb = 0;
+            unsigned long long px = 0;
+            while (cur_job < n && ns < kFpMaxSub) {
+                const FpJob &j = jobs[cur_job];
+                if (j.w <= 0 || j.h <= 0) { cur_job++; continue; }
+                const int nxt = (j.w + 63) >> 6, nst = (j.h + 63) >> 6;
+                const int x0 = cur_xt * 64, y0 = cur_st * 64, nx = min(64, j.w - x0), ny = min(64, j.h - y0);
+                const int a = (int)((uintptr_t)(j.ref + x0) & 3);
+                const int ngroups = (a + nx + 3) >> 2, P = (ngroups + 16 + 3) & ~3;
+                const int nyp = (ny + 3) & ~3, PR = ((nyp + 62 + 1) >> 1) + 1;
+                int       plane = PR * P + (PR >> 3) + 1;
+                plane           = ((plane + 15) & ~31) + 16;  // = 16 mod 32
+                if (used + 2 * plane > kFpBufWords) break;    // a single sub-window always fits (<= 4.8 K words)
+                FpSub &u = subs[ns++];
+                u.job = (int16_t)cur_job; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
+                u.a = (int16_t)a; u.ngroups = (int16_t)ngroups; u.P = (int16_t)P;
+                u.off = used; u.plane_words = plane; u.rbase = rb; u.rounds = (nyp >> 2) * ngroups;
+                used += 2 * plane; rb += u.rounds;
+                if (cur_xt == 0 && cur_st == 0) px += (unsigned long long)j.w * j.h * (64 * 32);
+                if (++cur_st == nst) { cur_st = 0; if (++cur_xt == nxt) { cur_xt = 0; cur_job++; } }
+            }
+            n_sub = ns;
+            if (px) atomicAdd(&s.px, px);
+        }
+        __syncthreads();
+        const int ns = n_sub;
+        if (ns == 0) break;
+        // stage: warp w copies rows w, w + 4, ... (fixed parity), lane = word of the row
+        for (int si = 0; si < ns; si++) {
+            const FpSub   &u = subs[si];
+            const FpJob   &j = jobs[u.job];
+            const int      nrows = ((u.ny + 3) & ~3) + 62, nwords = u.ngroups + 16, raw = j.ref_stride;
+            const uint8_t *g0 = j.ref + (int64_t)u.y0 * raw + u.x0 - u.a;
+            const uint32_t pbase = sbase + 4u * (uint32_t)(u.off + (warp & 1) * u.plane_words);
+            for (int wd = lane; wd < nwords; wd += 32) {
+                const uint8_t *g = g0 + (int64_t)warp * raw + 4 * wd;
+                for (int R = warp; R < nrows; R += kStWarps, g += (int64_t)kStWarps * raw) {
+                    const int i = R >> 1;
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(pbase + 4u * (uint32_t)(i * u.P + (i >> 3) + wd)), "l"(g));
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+        for (int si = 0; si < ns; si++) {
+            const FpSub &u = subs[si];
+            const int    first = (warp - u.rbase) & (kStWarps - 1);
+            if (first >= u.rounds) continue;
+            const int ngroups = u.ngroups, nx = u.nx, ny = u.ny, P = u.P;
+            int       k = first / ngroups, g = first - k * ngroups;
+            uint32_t  best8[4] = {~0u, ~0u, ~0u, ~0u}, best16 = ~0u, best32 = ~0u, best64 = ~0u;
+            const uint32_t *wbase = fp_win + u.off + half * u.plane_words + 4 * bx + (8 * by) * P + by;
+            for (int local = first; local < u.rounds; local += kStWarps) {
+                const int  yy = 4 * k + half;
+                const bool active = yy < ny;
+                uint32_t   acc[2][4][4];
+#pragma unroll
+                for (int y2 = 0; y2 < 2; y2++)
+#pragma unroll
+                    for (int c = 0; c < 4; c++) acc[y2][c][0] = acc[y2][c][1] = acc[y2][c][2] = acc[y2][c][3] = 0;
+                if (active) {
+                    const uint32_t *rowp = wbase + g;
+#pragma unroll
+                    for (int rr = 0; rr < 9; rr++) {
+                        const int       i  = 2 * k + rr;  // + 8 * by is in wbase, and (i + 8 by) >> 3 = by + (i >> 3)
+                        const uint32_t *rp = rowp + i * P + (i >> 3);
+                        uint32_t        w[5];
+#pragma unroll
+                        for (int c = 0; c < 5; c++) w[c] = rp[c];
+#pragma unroll
+                        for (int c = 0; c < 4; c++) {
+                            const uint32_t s0 = w[c], s1 = fsr(w[c], w[c + 1], 1), s2 = fsr(w[c], w[c + 1], 2), s3 = fsr(w[c], w[c + 1], 3);
+                            if (rr < 8) {
+                                const int      q  = (rr >> 2) * 2 + (c >> 1);
+                                const uint32_t sw = sreg[rr][c];
+                                acc[0][0][q] = sad4(s0, sw, acc[0][0][q]); acc[0][1][q] = sad4(s1, sw, acc[0][1][q]);
+                                acc[0][2][q] = sad4(s2, sw, acc[0][2][q]); acc[0][3][q] = sad4(s3, sw, acc[0][3][q]);
+                            }
+                            if (rr >= 1) {
+                                const int      q  = ((rr - 1) >> 2) * 2 + (c >> 1);
+                                const uint32_t sw = sreg[rr - 1][c];
+                                acc[1][0][q] = sad4(s0, sw, acc[1][0][q]); acc[1][1][q] = sad4(s1, sw, acc[1][1][q]);
+                                acc[1][2][q] = sad4(s2, sw, acc[1][2][q]); acc[1][3][q] = sad4(s3, sw, acc[1][3][q]);
+                            }
+                        }
+                    }
+                }
+                const int xb = 4 * g - u.a;
+                uint32_t  s16[8];
+#pragma unroll
+                for (int y2 = 0; y2 < 2; y2++)
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const int      xx = xb + c, y = yy + 2 * y2;
+                        const bool     valid = y < ny && xx >= 0 && xx < nx;
+                        const uint32_t ord = (uint32_t)(y * nx + xx);  // < 4096
+                        uint32_t       t = 0;
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            if (valid) best8[q] = min(best8[q], acc[y2][c][q] * 4096u + ord);
+                            t += acc[y2][c][q];
+                        }
+                        if (valid) best16 = min(best16, t * 4096u + ord);
+                        s16[y2 * 4 + c] = t;
+                    }
+                // transposing butterfly over the 4 lanes of a 32x32 block, then over the 4 blocks: candidate e = y2 * 4 + c
+                uint32_t t4[4], t2[2], t1;
+                {
+                    const bool up = b & 1;  // keeps y2 = b0
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const uint32_t send = up ? s16[i] : s16[4 + i], keep = up ? s16[4 + i] : s16[i];
+                        t4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+                    }
+                }
+                {
+                    const bool up = b & 2;  // keeps c >> 1 = b1
+#pragma unroll
+                    for (int i = 0; i < 2; i++) {
+                        const uint32_t send = up ? t4[i] : t4[2 + i], keep = up ? t4[2 + i] : t4[i];
+                        t2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+                    }
+                }
+                const int  y32 = yy + 2 * (b & 1), x32 = xb + (b & 2);
+                const bool yok = y32 < ny;
+#pragma unroll
+                for (int i = 0; i < 2; i++) {
+                    const int xx = x32 + i;
+                    if (yok && xx >= 0 && xx < nx) best32 = min(best32, t2[i] * 4096u + (uint32_t)(y32 * nx + xx));
+                }
+                {
+                    const bool     up   = b & 4;  // keeps c & 1 = b2
+                    const uint32_t send = up ? t2[0] : t2[1], keep = up ? t2[1] : t2[0];
+                    t1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+                }
+                t1 += __shfl_xor_sync(0xffffffffu, t1, 8);
+                {
+                    const int xx = x32 + ((b >> 2) & 1);
+                    if (yok && xx >= 0 && xx < nx) best64 = min(best64, t1 * 4096u + (uint32_t)(y32 * nx + xx));
+                }
+                g += kStWarps;
+                while (g >= ngroups) { g -= ngroups; k++; }
+            }
+            // fold this lane's minima into the job's keys: (doubled SAD, raster index inside the job's window)
+            const FpJob &j = jobs[u.job];
+            auto gk = [&](uint32_t key) {
+                const uint32_t sad = key >> 12, ord = key & 4095u, y = ord / (uint32_t)nx, x = ord - y * (uint32_t)nx;
+                return ((unsigned long long)(sad << 1) << 32) | (uint32_t)((u.y0 + y) * j.w + u.x0 + x);
+            };
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                if (best8[q] != ~0u) atomicMin(&fp_key[u.job][21 + 4 * b + q], gk(best8[q]));
+            if (best16 != ~0u) atomicMin(&fp_key[u.job][5 + b], gk(best16));
+            if (best32 != ~0u) atomicMin(&fp_key[u.job][1 + (b >> 2)], gk(best32));
+            if (b < 8 && best64 != ~0u) atomicMin(&fp_key[u.job][0], gk(best64));
+        }
+        __syncthreads();  // the windows are reused by the next batch
+    }
+    // fold the window minima into the running best of the reference (strict '<': earlier results win ties)
+    for (int i = threadIdx.x; i < n * kPus; i += blockDim.x) {
+        const int                ji = i / kPus, pu = i - ji * kPus;
+        const FpJob             &j  = jobs[ji];
+        const unsigned long long key = fp_key[ji][pu];
+        if (key == ~0ull) continue;
+        const uint32_t sad = (uint32_t)(key >> 32), ord = (uint32_t)key;
+        if (sad < s.best_sad[j.li][j.ri][pu]) {
+            const int32_t y = (int32_t)(ord / (uint32_t)j.w), x = (int32_t)(ord - (uint32_t)y * (uint32_t)j.w);
+            s.best_sad[j.li][j.ri][pu] = sad;
+            s.best_mv[j.li][j.ri][pu]  = ((uint32_t)(y + j.yo) << 16) | (uint16_t)(x + j.xo);
+        }
+    }
+}
+
 // ---- host: run the program of one picture as a stream-ordered sequence of picture-wide kernels ----
 cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_launches) {
     static cudaError_t attr = [] {
         cudaError_t e = cudaFuncSetAttribute(st_fp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStWarps * kFpWarpWin);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStWarps * kFpWarpWin);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_sub_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpBufWords * 4);
         return e;
     }();
     if (attr != cudaSuccess) return attr;
@@ -737,6 +1064,7 @@ cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_
     int       nl   = 0;
     // SVTME_TRACE=1: per-step device times of every picture on stderr (serialises the stream; diagnostics only)
     static const bool trace = getenv("SVTME_TRACE") != nullptr;
+    static const bool fp_old = getenv("SVTME_FP_OLD") != nullptr;  // A/B switch of the full-pel kernel (diagnostics only)
     cudaEvent_t ev[kMaxSteps + 4];
     const char *nm[kMaxSteps + 4];
     int         ne = 0;
@@ -754,7 +1082,13 @@ cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_
             i += c; mark("ctl");
         } else {
             if (p.prog[i].kind == STEP_NXM) st_nxm_kernel<<<n_sb, kStThreads, 0, st>>>(p);
-            else if (p.prog[i].kind == STEP_SAD) st_sad_kernel<<<n_sb, kStThreads, 0, st>>>(p, (int)p.prog[i].arg);
+            else if (p.prog[i].kind == STEP_SAD) {
+                const int lvl = (int)p.prog[i].arg;
+                if (lvl == 1 && p.k.hme_search_method == 0) st_sad_rows_kernel<8, 16><<<n_sb, kStThreads, 0, st>>>(p, lvl);
+                else if (lvl == 0 && p.k.hme_search_method == 0) st_sad_rows_kernel<16, 32><<<n_sb, kStThreads, 0, st>>>(p, lvl);
+                else st_sad_kernel<<<n_sb, kStThreads, 0, st>>>(p, lvl);
+            }
+            else if (p.k.me_search_method == 0 && !fp_old) st_fp_sub_kernel<<<n_sb, kStThreads, kFpBufWords * 4, st>>>(p);
             else if (p.k.me_search_method == 0) st_fp_kernel<true><<<n_sb, kStThreads, kStWarps * kFpWarpWin, st>>>(p);
             else st_fp_kernel<false><<<n_sb, kStThreads, kStWarps * kFpWarpWin, st>>>(p);
             mark(p.prog[i].kind == STEP_NXM ? "nxm" : p.prog[i].kind == STEP_SAD ? "sad" : "fp");
