@@ -151,7 +151,8 @@ __device__ __forceinline__ void sad_rows(const uint32_t *rowp, uint32_t row_step
 }
 
 template <int NW>
-__device__ void warp_sad_job(const SadJob &j, SadJob &jout, const uint32_t *blk, uint8_t *win, int lane, int rows, int bw, int rstep) {
+__device__ void warp_sad_job(const SadJob &j, SadJob &jout, const uint32_t *blk, uint8_t *win, int lane, int rows, int bw, int rstep,
+                             int win_bytes = kSadWarpWin) {
     const int W = j.sa_w, H = j.sa_h;
     if (W <= 0 || H <= 0) return;
     const bool     skip     = j.skip_line && bw == 16 && rows <= 16;
@@ -162,14 +163,14 @@ __device__ void warp_sad_job(const SadJob &j, SadJob &jout, const uint32_t *blk,
     const int      raw      = j.raw_stride;
     unsigned long long best = ~0ull;
     // widest tile whose rows (a few candidate rows + the block extent) still fit the warp's window buffer
-    int nx_cap = (((kSadWarpWin / (ext_y + min(H, 8))) & ~15) - 16) - 15 - (bw - 1) - 8;
+    int nx_cap = (((win_bytes / (ext_y + min(H, 8))) & ~15) - 16) - 15 - (bw - 1) - 8;
     nx_cap     = max(4, min(nx_cap, kTileMaxNx));
     for (int x0 = 0; x0 < W; x0 += nx_cap) {
         const int      nx    = min(W - x0, nx_cap);
         const uint32_t mis   = (uint32_t)((uintptr_t)(ref + x0) & 15);
         uint32_t       pitch = (mis + nx + bw - 1 + 8 + 15) & ~15u;
         if (((pitch >> 4) & 1) == 0) pitch += 16;
-        const int rows_fit = max(1, kSadWarpWin / (int)pitch - ext_y);  // >= 1 by the choice of nx_cap
+        const int rows_fit = max(1, win_bytes / (int)pitch - ext_y);  // >= 1 by the choice of nx_cap
         const int ngroups  = (int)(((mis & 3) + nx + 3) >> 2);
         const uint32_t pitchw = pitch >> 2, nvec = pitch >> 4;
         for (int y0 = 0; y0 < H; y0 += rows_fit) {
@@ -603,6 +604,258 @@ __global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constan
         else warp_sad_job<0>(j, jo, blk, win[warp], lane, rows, bw, rstep);
     }
     if (lane == 0 && px) atomicAdd(&s.px, px);
+}
+
+// ---- pre-HME / HME level 0 on the sixteenth plane (16x16 blocks, 8 sub-sampled rows): CTA-wide windows, lane = item ----
+// The windows of a batch of (job, column tile, row strip) sub-windows are staged together with asynchronous copies,
+// and ALL their items form one flat list dealt to the 128 lanes -- HME level 0 has ~20 tiny windows per block (8x8
+// candidates when the reference is close), which per-warp or per-window scheduling leaves mostly idle.
+// An item = 4 x-adjacent candidates on the two candidate rows y and y + 2, which share 7 of their 8 reference rows:
+// 9 window rows (45 LDS, 108 SHF) per 256 SADs.  With prehme_skip_search_line only odd candidate rows exist
+// (y = 4k + 1 and 4k + 3).  Even / odd window rows are kept in two planes with an odd pitch.  A lane keeps the
+// minimum of its current sub-window as (sad << 16 | candidate index) and folds it into the job's 64-bit key
+// (sad, y, x) when it moves on.  Blocks cut by the picture edge take the generic per-warp path.
+constexpr int kS16BufWords = 7 * 1024;
+constexpr int kS16MaxSub   = 64;
+struct S16Sub {
+    int16_t job, x0, y0, nx, ny, a, ngroups, P;
+    int32_t plane_words, items, off, ibase;  // off / ibase: words / items before this sub-window inside its batch
+    float   inv_ng, inv_nx;
+    int16_t hsel, q;                          // hsel 1: odd rows only; q: log2 lanes per staged row
+};
+
+__global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_constant__ MeParams p) {
+    extern __shared__ __align__(16) uint32_t s16_win[];  // kS16BufWords
+    __shared__ __align__(16) SadJob        jobs[kMaxSadJobs];
+    __shared__ unsigned long long          job_key[kMaxSadJobs];
+    __shared__ S16Sub                      subs[kS16MaxSub];
+    __shared__ uint32_t                    sub_key[kS16MaxSub];
+    __shared__ int16_t                     j_cnt[kMaxSadJobs], j_base[kMaxSadJobs], j_nst[kMaxSadJobs], j_nycap[kMaxSadJobs];
+    __shared__ int                         n_sub_all, n_batch, b_start[kS16MaxSub + 1], b_items[kS16MaxSub];
+    SbState  &s = p.states[blockIdx.x];
+    const int n = s.n_sad;
+    if (n == 0) return;
+    {
+        const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.sad_jobs[0]);
+        unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
+        for (int i = threadIdx.x; i < n * (int)(sizeof(SadJob) / 8); i += blockDim.x) dst[i] = src[i];
+        if (threadIdx.x < kMaxSadJobs) job_key[threadIdx.x] = ~0ull;
+        if (threadIdx.x < kS16MaxSub) sub_key[threadIdx.x] = ~0u;
+    }
+    // block geometry as in make_sad_job (me_control.cuh)
+    const DevPlane &cp = p.cur.lvl[2];
+    const uint32_t  aw = (uint32_t)((p.cur.lvl[0].width + 7) & ~7), ah = (uint32_t)((p.cur.lvl[0].height + 7) & ~7);
+    const uint32_t  org_x = (blockIdx.x % p.wb) * 64, org_y = (blockIdx.x / p.wb) * 64;
+    const uint32_t  b64_w = min(64u, aw - org_x), b64_h = min(64u, ah - org_y);
+    const int       bw = (int)(b64_w >> 2), rows = (int)((b64_h >> 2) >> 1);
+    const int       warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint8_t  *b0 = cp.org + (int64_t)(org_y >> 2) * cp.stride + (org_x >> 2);
+    __syncthreads();
+    // ---- decomposition, in parallel: per job (tiles x strips), then per sub-window ----
+    if ((int)threadIdx.x < kMaxSadJobs) {
+        const int ji = threadIdx.x;
+        int       cnt = 0, nst = 1, ny_cap = 16;
+        if (ji < n && jobs[ji].sa_w > 0 && jobs[ji].sa_h > 0) {
+            const int W = jobs[ji].sa_w, H = jobs[ji].sa_h;
+            const int pmax = (((3 + min(128, W) + 3) >> 2) + 4) | 1;
+            ny_cap = max(16, min(512, 4096 / pmax - 16)) & ~3;  // a sub-window: <= ~4 K words, < 64 K candidates
+            nst    = (H + ny_cap - 1) / ny_cap;
+            cnt    = ((W + 127) >> 7) * nst;
+        }
+        int incl = cnt;  // threads 0..31 are warp 0
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        j_cnt[ji] = (int16_t)cnt; j_base[ji] = (int16_t)(incl - cnt); j_nst[ji] = (int16_t)nst; j_nycap[ji] = (int16_t)ny_cap;
+        if (ji == 31) n_sub_all = incl;
+    }
+    __syncthreads();
+    const int S = n_sub_all;
+    if (bw != 16 || rows != 8 || S > kS16MaxSub) {
+        // generic path: block words in shared memory, one warp per job, warp-private windows carved from the buffer
+        uint32_t *blk = s16_win;
+        const int nw = (bw + 3) >> 2;
+        for (int i = threadIdx.x; i < rows * nw; i += blockDim.x) {
+            const int      r = i / nw, c = i - r * nw;
+            const uint8_t *sp = b0 + (int64_t)r * (cp.stride * 2) + 4 * c;
+            uint32_t       a = 0;
+            for (int q = 0; q < min(4, bw - 4 * c); q++) a |= (uint32_t)sp[q] << (8 * q);
+            blk[r * 16 + c] = a;
+        }
+        __syncthreads();
+        unsigned long long px = 0;
+        for (int ji = warp; ji < n; ji += kStWarps) {
+            const SadJob &j = jobs[ji];
+            if (j.sa_w > 0 && j.sa_h > 0) {
+                const bool skip = j.skip_line && bw == 16 && rows <= 16;
+                px += (unsigned long long)j.sa_w * (skip ? (j.sa_h >> 1) : j.sa_h) * rows * bw;
+            }
+            constexpr int kWin = (kS16BufWords - 1024) / kStWarps * 4;  // bytes per warp
+            uint8_t      *w8   = reinterpret_cast<uint8_t *>(s16_win + 1024) + warp * kWin;
+            if (bw == 16) warp_sad_job<4>(j, s.sad_jobs[ji], blk, w8, lane, rows, bw, 2, kWin);
+            else warp_sad_job<0>(j, s.sad_jobs[ji], blk, w8, lane, rows, bw, 2, kWin);
+        }
+        if (lane == 0 && px) atomicAdd(&s.px, px);
+        return;
+    }
+    if ((int)threadIdx.x < S) {
+        int ji = 0;
+        for (int q = 0; q < n; q++)
+            if ((int)threadIdx.x >= j_base[q] && (int)threadIdx.x < j_base[q] + j_cnt[q]) ji = q;
+        const SadJob &j = jobs[ji];
+        const int     local = threadIdx.x - j_base[ji], nst = j_nst[ji], ny_cap = j_nycap[ji];
+        const int     xt = local / nst, st = local - xt * nst;
+        const int     x0 = xt * 128, nx = min(128, j.sa_w - x0), y0 = st * ny_cap, ny = min(ny_cap, j.sa_h - y0);
+        const int     a = (int)((uintptr_t)(j.ref + x0) & 3);
+        const int     ngroups = (a + nx + 3) >> 2, P = (ngroups + 4) | 1;  // 4 block words + the shifted-in word
+        const int     nyp = (ny + 3) & ~3, PR = ((nyp + 14 + 1) >> 1) + 1;
+        S16Sub       &u = subs[threadIdx.x];
+        u.job = (int16_t)ji; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
+        u.a = (int16_t)a; u.ngroups = (int16_t)ngroups; u.P = (int16_t)P;
+        u.plane_words = ((PR * P + 15) & ~31) + 16;  // = 16 mod 32
+        u.hsel  = j.skip_line ? 1 : 0;
+        u.items = (nyp >> 2) * (j.skip_line ? 1 : 2) * ngroups;
+        u.inv_ng = 1.0f / (float)ngroups; u.inv_nx = 1.0f / (float)nx;
+        int q = 5;
+        while (q > 0 && (1 << (q - 1)) >= ngroups + 4) q--;
+        u.q = (int16_t)q;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // batches: maximal runs of sub-windows that fit the buffer
+        int                nb = 0, used = 0, items = 0;
+        unsigned long long px = 0;
+        b_start[0] = 0;
+        for (int i = 0; i < S; i++) {
+            S16Sub   &u = subs[i];
+            const int w2 = 2 * u.plane_words;
+            if (used + w2 > kS16BufWords) { b_items[nb] = items; b_start[++nb] = i; used = 0; items = 0; }
+            u.off = used; u.ibase = items;
+            used += w2; items += u.items;
+        }
+        b_items[nb] = items; b_start[++nb] = S;
+        n_batch = nb;
+        for (int ji = 0; ji < n; ji++) {
+            const SadJob &j = jobs[ji];
+            if (j.sa_w > 0 && j.sa_h > 0) px += (unsigned long long)j.sa_w * (j.skip_line ? (j.sa_h >> 1) : j.sa_h) * (8 * 16);
+        }
+        if (px) atomicAdd(&s.px, px);
+    }
+    uint32_t sreg[8][4];  // rows 0, 2, .. 14 of the 16x16 block (same for every lane: broadcast loads)
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(b0 + (int64_t)(2 * r) * cp.stride));
+        sreg[r][0] = v.x; sreg[r][1] = v.y; sreg[r][2] = v.z; sreg[r][3] = v.w;
+    }
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(s16_win);
+    __syncthreads();
+    const int nb = n_batch;
+    for (int bi = 0; bi < nb; bi++) {
+        const int s_lo = b_start[bi], s_hi = b_start[bi + 1];
+        // stage: one warp per sub-window, 2^q lanes per window row
+        for (int si = s_lo + warp; si < s_hi; si += kStWarps) {
+            const S16Sub  &u = subs[si];
+            const SadJob  &j = jobs[u.job];
+            const int      nrows = ((u.ny + 3) & ~3) + 14, nwords = u.ngroups + 4, raw = j.raw_stride, q = u.q;
+            const int      rpi = 32 >> q, lr = lane >> q, lw = lane & ((1 << q) - 1);
+            const uint8_t *g0 = j.ref + (int64_t)u.y0 * raw + u.x0 - u.a;
+            const uint32_t w0 = sbase + 4u * (uint32_t)u.off, pw = 4u * (uint32_t)u.plane_words, P4 = 4u * (uint32_t)u.P;
+            for (int wd = lw; wd < nwords; wd += 32) {
+                const uint8_t *g = g0 + (int64_t)lr * raw + 4 * wd;
+                if (rpi >= 2) {  // the parity of the lane's rows is fixed
+                    uint32_t sa = w0 + (lr & 1) * pw + (uint32_t)(lr >> 1) * P4 + 4u * (uint32_t)wd;
+                    for (int R = lr; R < nrows; R += rpi, g += (int64_t)rpi * raw, sa += (uint32_t)(rpi >> 1) * P4)
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(g));
+                } else {
+                    uint32_t sa = w0 + 4u * (uint32_t)wd;
+                    for (int R = 0; R < nrows; R += 2, g += 2 * (int64_t)raw, sa += P4) {
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(g));
+                        if (R + 1 < nrows) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa + pw), "l"(g + raw));
+                    }
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+        // compute: flat item list of the batch, lane f takes items f, f + 128, ...
+        {
+            const int T = b_items[bi];
+            int       si = s_lo - 1, next_base = 0;  // items [ibase, next_base) belong to sub-window si
+            uint32_t  best = ~0u;
+            int       u_ng = 1, u_nx = 1, u_ny = 0, u_P = 1, u_a = 0, u_hsel = 0, u_ibase = 0;
+            float     u_inv_ng = 1.f;
+            const uint32_t *u_win = s16_win;
+            uint32_t        u_pw = 0;
+            auto flush = [&]() {
+                if (best != ~0u) { atomicMin(&sub_key[si], best); best = ~0u; }
+            };
+            for (int f = threadIdx.x; f < T; f += kStThreads) {
+                if (f >= next_base) {
+                    flush();
+                    do { si++; next_base = subs[si].ibase + subs[si].items; } while (f >= next_base);
+                    const S16Sub &u = subs[si];
+                    u_ng = u.ngroups; u_nx = u.nx; u_ny = u.ny; u_P = u.P; u_a = u.a; u_hsel = u.hsel; u_ibase = u.ibase;
+                    u_inv_ng = u.inv_ng; u_win = s16_win + u.off; u_pw = (uint32_t)u.plane_words;
+                }
+                const int item = f - u_ibase;
+                const int kh = (int)(((float)item + 0.5f) * u_inv_ng), g = item - kh * u_ng;
+                const int k = u_hsel ? kh : (kh >> 1), h = u_hsel ? 1 : (kh & 1);
+                const int yy = 4 * k + h;
+                uint32_t  acc[2][4];
+#pragma unroll
+                for (int c = 0; c < 4; c++) acc[0][c] = acc[1][c] = 0;
+                const uint32_t *rowp = u_win + h * u_pw + (2 * k) * u_P + g;
+#pragma unroll
+                for (int rr = 0; rr < 9; rr++) {
+                    const uint32_t *rp = rowp + rr * u_P;
+                    uint32_t        w[5];
+#pragma unroll
+                    for (int c = 0; c < 5; c++) w[c] = rp[c];
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const uint32_t s0 = w[c], s1 = fsr(w[c], w[c + 1], 1), s2 = fsr(w[c], w[c + 1], 2), s3 = fsr(w[c], w[c + 1], 3);
+                        if (rr < 8) {
+                            const uint32_t sw = sreg[rr][c];
+                            acc[0][0] = sad4(s0, sw, acc[0][0]); acc[0][1] = sad4(s1, sw, acc[0][1]);
+                            acc[0][2] = sad4(s2, sw, acc[0][2]); acc[0][3] = sad4(s3, sw, acc[0][3]);
+                        }
+                        if (rr >= 1) {
+                            const uint32_t sw = sreg[rr - 1][c];
+                            acc[1][0] = sad4(s0, sw, acc[1][0]); acc[1][1] = sad4(s1, sw, acc[1][1]);
+                            acc[1][2] = sad4(s2, sw, acc[1][2]); acc[1][3] = sad4(s3, sw, acc[1][3]);
+                        }
+                    }
+                }
+                const int xb = 4 * g - u_a;
+#pragma unroll
+                for (int y2 = 0; y2 < 2; y2++)
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const int xx = xb + c, y = yy + 2 * y2;
+                        if (y < u_ny && xx >= 0 && xx < u_nx) best = min(best, (acc[y2][c] << 16) | (uint32_t)(y * u_nx + xx));
+                    }
+            }
+            flush();
+        }
+        __syncthreads();  // the windows are reused by the next batch
+    }
+    // sub-window minima -> job keys (sad, y, x): raster order inside the job decides ties between sub-windows
+    if ((int)threadIdx.x < S && sub_key[threadIdx.x] != ~0u) {
+        const S16Sub  &u = subs[threadIdx.x];
+        const uint32_t key = sub_key[threadIdx.x], sad = key >> 16, ord = key & 0xffffu;
+        const uint32_t y = (uint32_t)(((float)ord + 0.5f) * u.inv_nx), x = ord - y * (uint32_t)u.nx;
+        atomicMin(&job_key[u.job], ((unsigned long long)sad << 32) | ((uint32_t)(u.y0 + y) << 16) | (uint32_t)(u.x0 + x));
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < n) {
+        const unsigned long long key = job_key[threadIdx.x];
+        if (key != ~0ull && (uint32_t)(key >> 32) < 0xffffffu) {  // strict '<' against the 0xffffff start value
+            SadJob &jo = s.sad_jobs[threadIdx.x];
+            jo.found = 1; jo.best_sad = (uint32_t)(key >> 32);
+            jo.by = (int16_t)((key >> 16) & 0xffff); jo.bx = (int16_t)(key & 0xffff);
+        }
+    }
 }
 
 // ---- open_loop_me_fullpel_search_sblock jobs: one warp per unit (a strip of candidate rows of one job) ----
@@ -1056,6 +1309,7 @@ cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_
     static cudaError_t attr = [] {
         cudaError_t e = cudaFuncSetAttribute(st_fp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStWarps * kFpWarpWin);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStWarps * kFpWarpWin);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(st_sad16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kS16BufWords * 4);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_sub_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpBufWords * 4);
         return e;
     }();
@@ -1064,6 +1318,7 @@ cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_
     int       nl   = 0;
     // SVTME_TRACE=1: per-step device times of every picture on stderr (serialises the stream; diagnostics only)
     static const bool trace = getenv("SVTME_TRACE") != nullptr;
+    static const bool sad_old = getenv("SVTME_SAD_OLD") != nullptr;
     static const bool fp_old = getenv("SVTME_FP_OLD") != nullptr;  // A/B switch of the full-pel kernel (diagnostics only)
     cudaEvent_t ev[kMaxSteps + 4];
     const char *nm[kMaxSteps + 4];
@@ -1086,6 +1341,7 @@ cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_
                 const int lvl = (int)p.prog[i].arg;
                 if (lvl == 1 && p.k.hme_search_method == 0) st_sad_rows_kernel<8, 16><<<n_sb, kStThreads, 0, st>>>(p, lvl);
                 else if (lvl == 0 && p.k.hme_search_method == 0) st_sad_rows_kernel<16, 32><<<n_sb, kStThreads, 0, st>>>(p, lvl);
+                else if (lvl == 2 && p.k.hme_search_method == 0 && !sad_old) st_sad16_kernel<<<n_sb, kStThreads, kS16BufWords * 4, st>>>(p);
                 else st_sad_kernel<<<n_sb, kStThreads, 0, st>>>(p, lvl);
             }
             else if (p.k.me_search_method == 0 && !fp_old) st_fp_sub_kernel<<<n_sb, kStThreads, kFpBufWords * 4, st>>>(p);

@@ -17,7 +17,9 @@ for r in rows:
     if r[0].isdigit():
         try: n = int(r[len(r) - off])
         except ValueError: continue
-        lines.append((n, cur, r[0], ','.join(r[1:len(r) - len(hdr) + 2])[:110]))
+        try: smp = int(r[len(r) - off - 1])
+        except ValueError: smp = 0
+        lines.append((n, cur, r[0], ','.join(r[1:len(r) - len(hdr) + 2])[:110], smp))
     elif r[0] == '' and len(r) > 3 and r[2].startswith('0x'):
         try: n = int(r[len(r) - off])
         except ValueError: continue
@@ -28,3 +30,6 @@ print('total warp instructions', tot)
 for k, v in ops.most_common(16): print('  %-10s %10d %5.1f%%' % (k, v, 100.0 * v / max(tot, 1)))
 lines.sort(reverse=True)
 for l in lines[:28]: print(l)
+print('--- by stall samples')
+tots = sum(l[4] for l in lines)
+for l in sorted(lines, key=lambda l: -l[4])[:22]: print('%5.1f%%' % (100.0 * l[4] / max(tots, 1)), l[1], l[2], l[3][:100])
