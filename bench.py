@@ -9,8 +9,9 @@ its own mini-GOPs (weak scaling, no data-path collective).
   value     device-resident: luma planes already in HBM, results stay in HBM
   e2e       through the public C ABI with HOST buffers: H2D of every luma plane and D2H of every result inside the
             timed region
-  roofline  dominant kernel (me_picture_kernel): algorithmic pixel-compares / kernel time against the measured
-            VABSDIFF4 issue peak (INT pipe -- SAD is not a tensor-core op), plus the HBM view of the same kernel
+  roofline  the search of one picture (the stream-ordered st_* kernels of csrc/me_staged.cu, launched serialised with
+            CUDA events around them): algorithmic pixel-compares / device time against the measured VABSDIFF4 issue
+            peak (INT pipe -- SAD is not a tensor-core op), plus the HBM view of the same launches
   cpu_baseline / --impl reference: the UNMODIFIED reference C/AVX2 ME (oracle/_ref/libsvtref.so, compiled from the
             reference's own sources) on the host cores, on a bounded sample of the same workload
 """
@@ -39,7 +40,7 @@ def parse():
     ap.add_argument("--height", type=int, default=2160)
     ap.add_argument("--preset", type=int, default=6)
     ap.add_argument("--hier-levels", type=int, default=5, help="mini-GOP = 2^levels pictures")
-    ap.add_argument("--inflight", type=int, default=4)
+    ap.add_argument("--inflight", type=int, default=8, help="searches in flight (one stream each)")
     ap.add_argument("--cpu-sample", type=int, default=3, help="pictures of the workload timed on the host cores")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -258,7 +259,7 @@ def main():
     step_host()
     ms_host = timed(step_host, args.steps)
 
-    # per-launch view of the dominant kernel: serialised launches, CUDA events around each (svtme_search_elapsed_ms)
+    # per-launch view: one picture's search at a time, CUDA events on its stream around it (svtme_search_elapsed_ms)
     px_total, ms_total, n_launch = 0, 0.0, 0
     pics = {i: dev.register_device(d_luma.data_ptr() + i * w * h, w, w, h, i) for i in range(nf)}
     for rep in range(2):
@@ -292,11 +293,11 @@ def main():
     alg_bytes = (1 + refs_avg) * 1.3125 * w * h + d2h / len(wl.pics)
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["me_picture_kernel_dram_bytes_per_launch"]
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["search_dram_bytes_per_picture"]
     except Exception:
         pass
     ach = px_total / (ms_total * 1e-3) / 1e12
-    roofline = {"bound": "int", "kernel": "me_picture_kernel", "achieved": ach, "peak": sad_peak, "unit": "Tpx-compares/s",
+    roofline = {"bound": "int", "kernel": "picture search = st_init/ctl/nxm/sad16/sad_rows/fp_sub/finish kernels (me_staged.cu)", "achieved": ach, "peak": sad_peak, "unit": "Tpx-compares/s",
                 "frac": ach / sad_peak, "traffic": traffic,
                 "peak_source": "VABSDIFF4.U8.ACC issue rate measured in this run (svtme_measure_sad_peak) x 4 px",
                 "px_compares_per_launch": px_total / n_launch, "avg_launch_ms": ms_total / n_launch,

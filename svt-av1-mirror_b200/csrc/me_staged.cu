@@ -504,7 +504,7 @@ __device__ __forceinline__ void rows_job(const SadJob &j, SadJob &jout, const ui
 
 // `lvl` 1: quarter plane, <8, 16>; `lvl` 0: full plane, <16, 32>.  Launched only when hme_search_method is sub-sampled.
 template <int NW, int ROWS>
-__global__ void __launch_bounds__(kStThreads) st_sad_rows_kernel(const __grid_constant__ MeParams p, int lvl) {
+__global__ void __launch_bounds__(kStThreads, 6) st_sad_rows_kernel(const __grid_constant__ MeParams p, int lvl) {
     using C = RowsCfg<NW, ROWS>;
     constexpr int kBlkPitch = 17;  // odd: lane = row reads are conflict free
     __shared__ uint32_t              blk[ROWS * kBlkPitch];
@@ -1086,16 +1086,16 @@ __global__ void __launch_bounds__(kStThreads) st_fp_kernel(const __grid_constant
 // i * P + (i >> 3) with P = 0 mod 4: the 32 lanes of a load hit banks 16 * half + by + 4 * bx + const -- no conflicts.
 // Minima: 32-bit keys (sad << 12 | candidate index inside the <= 64 x 64 sub-window); 32x32 / 64x64 sums by a
 // transposing butterfly (8 shuffles for 8 candidates).
-constexpr int kFpBufWords = 11 * 1024;  // 44 KB of windows per CTA
-constexpr int kFpMaxSub   = 16;
+constexpr int kFpBufWords = 8 * 1024;  // 44 KB of windows per CTA
+constexpr int kFpMaxSub   = 12;
 struct FpSub {
     int16_t job, x0, y0, nx, ny, a, ngroups, P;
     int32_t off, plane_words, rbase, rounds;
 };
 
-__global__ void __launch_bounds__(kStThreads, 4) st_fp_sub_kernel(const __grid_constant__ MeParams p) {
-    __shared__ __align__(16) uint32_t src64[64 * 16];
+__global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_constant__ MeParams p) {
     extern __shared__ __align__(16) uint32_t fp_win[];  // kFpBufWords
+    __shared__ uint32_t               sub_key[kFpMaxSub][kPus];  // (sad << 12 | candidate) minima of the batch's sub-windows
     __shared__ unsigned long long     fp_key[kMaxFpJobs][kPus];
     __shared__ __align__(16) FpJob    jobs[kMaxFpJobs];
     __shared__ FpSub                  subs[kFpMaxSub];
@@ -1107,13 +1107,6 @@ __global__ void __launch_bounds__(kStThreads, 4) st_fp_sub_kernel(const __grid_c
         const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.fp_jobs[0]);
         unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
         for (int i = threadIdx.x; i < n * (int)(sizeof(FpJob) / 8); i += blockDim.x) dst[i] = src[i];
-        // the 64x64 source block: its address follows from the block index (sb_init)
-        const DevPlane &f   = p.cur.lvl[0];
-        const uint8_t  *sp0 = f.org + (int64_t)((blockIdx.x / p.wb) * 64) * f.stride + (blockIdx.x % p.wb) * 64;
-        for (int i = threadIdx.x; i < 64 * 4; i += blockDim.x) {
-            const int r = i >> 2, v = i & 3;
-            *reinterpret_cast<uint4 *>(&src64[r * 16 + 4 * v]) = __ldg(reinterpret_cast<const uint4 *>(sp0 + (int64_t)r * f.stride) + v);
-        }
         for (int i = threadIdx.x; i < n * kPus; i += blockDim.x) (&fp_key[0][0])[i] = ~0ull;
         if (threadIdx.x == 0) { cur_job = 0; cur_xt = 0; cur_st = 0; }
     }
@@ -1121,11 +1114,16 @@ __global__ void __launch_bounds__(kStThreads, 4) st_fp_sub_kernel(const __grid_c
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = lane & 15, half = lane >> 4;
     const int bx = ((b >> 2) & 1) * 2 + (b & 1), by = (b >> 3) * 2 + ((b >> 1) & 1);
-    uint32_t  sreg[8][4];  // every second row of the lane's 16x16 block
+    uint32_t  sreg[8][4];  // every second row of the lane's 16x16 block, straight from the source picture (sb_init geometry)
+    {
+        const DevPlane &f   = p.cur.lvl[0];
+        const uint8_t  *sp0 = f.org + (int64_t)((blockIdx.x / p.wb) * 64 + 16 * by) * f.stride + (blockIdx.x % p.wb) * 64 + 16 * bx;
 #pragma unroll
-    for (int r = 0; r < 8; r++)
-#pragma unroll
-        for (int c = 0; c < 4; c++) sreg[r][c] = src64[(16 * by + 2 * r) * 16 + 4 * bx + c];
+        for (int r = 0; r < 8; r++) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(sp0 + (int64_t)(2 * r) * f.stride));
+            sreg[r][0] = v.x; sreg[r][1] = v.y; sreg[r][2] = v.z; sreg[r][3] = v.w;
+        }
+    }
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(fp_win);
 
     for (;;) {
@@ -1140,7 +1138,7 @@ __global__ void __launch_bounds__(kStThreads, 4) st_fp_sub_kernel(const __grid_c
                 const int x0 = cur_xt * 64, y0 = cur_st * 64, nx = min(64, j.w - x0), ny = min(64, j.h - y0);
                 const int a = (int)((uintptr_t)(j.ref + x0) & 3);
                 const int ngroups = (a + nx + 3) >> 2, P = (ngroups + 16 + 3) & ~3;
-                const int nyp = (ny + 3) & ~3, PR = ((nyp + 62 + 1) >> 1) + 1;
+                const int nyp = (ny + 3) & ~3, PR = ((nyp + 62 + 7) & ~7) >> 1;  // staged in groups of 8 rows
                 int       plane = PR * P + (PR >> 3) + 1;
                 plane           = ((plane + 15) & ~31) + 16;  // = 16 mod 32
                 if (used + 2 * plane > kFpBufWords) break;    // a single sub-window always fits (<= 4.8 K words)
@@ -1158,18 +1156,24 @@ __global__ void __launch_bounds__(kStThreads, 4) st_fp_sub_kernel(const __grid_c
         __syncthreads();
         const int ns = n_sub;
         if (ns == 0) break;
-        // stage: warp w copies rows w, w + 4, ... (fixed parity), lane = word of the row
+        for (int i = threadIdx.x; i < ns * kPus; i += blockDim.x) (&sub_key[0][0])[i] = ~0u;
+        // stage: warp w copies rows w, w + 4, ... (fixed parity), lane = word of the row.  Rows go in groups of 8
+        // (2 per warp): inside a group the skew (i >> 3) is constant, so the addresses are plain strides.  The rows
+        // past the window (< 8 + 3) are inside the plane's physical padding (96 rows against the 72 a search uses).
         for (int si = 0; si < ns; si++) {
             const FpSub   &u = subs[si];
             const FpJob   &j = jobs[u.job];
-            const int      nrows = ((u.ny + 3) & ~3) + 62, nwords = u.ngroups + 16, raw = j.ref_stride;
-            const uint8_t *g0 = j.ref + (int64_t)u.y0 * raw + u.x0 - u.a;
-            const uint32_t pbase = sbase + 4u * (uint32_t)(u.off + (warp & 1) * u.plane_words);
+            const int      ngrp = (((u.ny + 3) & ~3) + 62 + 7) >> 3, nwords = u.ngroups + 16, raw = j.ref_stride;
+            const uint8_t *g0 = j.ref + (int64_t)u.y0 * raw + u.x0 - u.a + (int64_t)warp * raw;
+            const uint32_t P4 = 4u * (uint32_t)u.P;
+            const uint32_t pbase = sbase + 4u * (uint32_t)(u.off + (warp & 1) * u.plane_words) + (uint32_t)(warp >> 1) * P4;
             for (int wd = lane; wd < nwords; wd += 32) {
-                const uint8_t *g = g0 + (int64_t)warp * raw + 4 * wd;
-                for (int R = warp; R < nrows; R += kStWarps, g += (int64_t)kStWarps * raw) {
-                    const int i = R >> 1;
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(pbase + 4u * (uint32_t)(i * u.P + (i >> 3) + wd)), "l"(g));
+                const uint8_t *g  = g0 + 4 * wd;
+                uint32_t       sa = pbase + 4u * (uint32_t)wd;
+                for (int G = 0; G < ngrp; G++, g += 8 * (int64_t)raw, sa += 4u * P4 + ((G & 1) ? 0u : 4u)) {
+                    // rows warp + 8G and warp + 8G + 4: plane rows i = (warp >> 1) + 4G + {0, 2}, skew i >> 3 = G >> 1
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(g));
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa + 2u * P4), "l"(g + 4 * (int64_t)raw));
                 }
             }
         }
@@ -1274,18 +1278,23 @@ __global__ void __launch_bounds__(kStThreads, 4) st_fp_sub_kernel(const __grid_c
                 g += kStWarps;
                 while (g >= ngroups) { g -= ngroups; k++; }
             }
-            // fold this lane's minima into the job's keys: (doubled SAD, raster index inside the job's window)
-            const FpJob &j = jobs[u.job];
-            auto gk = [&](uint32_t key) {
-                const uint32_t sad = key >> 12, ord = key & 4095u, y = ord / (uint32_t)nx, x = ord - y * (uint32_t)nx;
-                return ((unsigned long long)(sad << 1) << 32) | (uint32_t)((u.y0 + y) * j.w + u.x0 + x);
-            };
+            // this lane's minima -> the sub-window's keys (native 32-bit shared atomics)
 #pragma unroll
             for (int q = 0; q < 4; q++)
-                if (best8[q] != ~0u) atomicMin(&fp_key[u.job][21 + 4 * b + q], gk(best8[q]));
-            if (best16 != ~0u) atomicMin(&fp_key[u.job][5 + b], gk(best16));
-            if (best32 != ~0u) atomicMin(&fp_key[u.job][1 + (b >> 2)], gk(best32));
-            if (b < 8 && best64 != ~0u) atomicMin(&fp_key[u.job][0], gk(best64));
+                if (best8[q] != ~0u) atomicMin(&sub_key[si][21 + 4 * b + q], best8[q]);
+            if (best16 != ~0u) atomicMin(&sub_key[si][5 + b], best16);
+            if (best32 != ~0u) atomicMin(&sub_key[si][1 + (b >> 2)], best32);
+            if (b < 8 && best64 != ~0u) atomicMin(&sub_key[si][0], best64);
+        }
+        __syncthreads();
+        // sub-window keys -> job keys: (doubled SAD, raster index inside the job's window)
+        for (int i = threadIdx.x; i < ns * kPus; i += blockDim.x) {
+            const int      si = i / kPus, pu = i - si * kPus;
+            const uint32_t key = sub_key[si][pu];
+            if (key == ~0u) continue;
+            const FpSub   &u = subs[si];
+            const uint32_t sad = key >> 12, ord = key & 4095u, y = ord / (uint32_t)u.nx, x = ord - y * (uint32_t)u.nx;
+            atomicMin(&fp_key[u.job][pu], ((unsigned long long)(sad << 1) << 32) | (uint32_t)((u.y0 + y) * jobs[u.job].w + u.x0 + x));
         }
         __syncthreads();  // the windows are reused by the next batch
     }
