@@ -197,7 +197,7 @@ def main():
         return 0
 
     import torch
-    from svtme import abi, api
+    from svtme import abi, api, shard
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
     torch.cuda.set_device(local_rank)
@@ -206,7 +206,9 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    wl = Workload(args, seed=100 + rank)
+    # weak scaling: one mini-GOP per rank and step; rank r owns mini-GOP r of the job (svtme/shard.py), its own clip
+    my_gops = list(shard.shard_minigops(world, rank, world))
+    wl = Workload(args, seed=100 + my_gops[0])
     dev = api.MeDevice(device=local_rank, max_inflight=args.inflight, max_pictures=2 * wl.n_frames)
     w, h, nf = wl.w, wl.h, wl.n_frames
     h_luma = torch.empty((nf, h, w), dtype=torch.uint8).pin_memory()
@@ -239,11 +241,10 @@ def main():
         torch.cuda.synchronize()
         e1.record()
         torch.cuda.synchronize()
-        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        ms = e0.elapsed_time(e1)
         barrier()
-        if dist is not None:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item())
+        # whole job: SUM of the pictures of all ranks, MAX of their device times (svtme/shard.py)
+        return shard.reduce_job(wl.gop * steps, ms, dist, device="cuda")
 
     step_dev = lambda: run_step_device(dev, wl, d_luma, args.inflight)  # noqa: E731
     step_host = lambda: run_step_host(dev, wl, h_luma, outs, args.inflight)  # noqa: E731
@@ -253,11 +254,11 @@ def main():
     sampler = ClockSampler(local_rank)
     sampler.start()
     l0 = dev.launch_count()
-    ms_dev = timed(step_dev, args.steps)
+    pictures, ms_dev = timed(step_dev, args.steps)
     launches = dev.launch_count() - l0
     clocks = sampler.stop()
     step_host()
-    ms_host = timed(step_host, args.steps)
+    _, ms_host = timed(step_host, args.steps)
 
     # per-launch view: one picture's search at a time, CUDA events on its stream around it (svtme_search_elapsed_ms)
     px_total, ms_total, n_launch = 0, 0.0, 0
@@ -275,7 +276,6 @@ def main():
     for p in pics.values():
         p.release()
 
-    pictures = wl.gop * args.steps * world
     value = pictures / (ms_dev * 1e-3)
     e2e = pictures / (ms_host * 1e-3)
     if rank != 0:

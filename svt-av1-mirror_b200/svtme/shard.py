@@ -1,0 +1,35 @@
+"""Multi-GPU host logic: the open-loop ME path shards by picture -- one process per GPU, every
+rank owns whole mini-GOPs (its pictures and their references live on that GPU), no data-path collective.  The only
+communication is the job-level bookkeeping below: a barrier around the timed region, MAX of the device times and SUM
+of the pictures (torch.distributed; NCCL on GPUs, gloo in the CPU tests)."""
+
+
+def shard_minigops(n_minigops, rank, world):
+    """Contiguous, balanced partition of mini-GOP indices 0..n-1: rank r gets [lo, hi).  Contiguous ranges keep the
+    reference pictures a mini-GOP needs from its predecessor (the leading base picture) on one rank."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError("bad rank/world: %r/%r" % (rank, world))
+    base, extra = divmod(n_minigops, world)
+    lo = rank * base + min(rank, extra)
+    return range(lo, lo + base + (1 if rank < extra else 0))
+
+
+def pictures_of(minigops, gop_size):
+    """Picture numbers (display order) a rank must hold for its mini-GOPs: the GOP's pictures plus the leading base
+    picture of the previous mini-GOP (the only cross-mini-GOP reference of a hierarchical structure)."""
+    pics = set()
+    for g in minigops:
+        pics.update(range(g * gop_size, (g + 1) * gop_size + 1))
+    return sorted(pics)
+
+
+def reduce_job(pictures_local, ms_local, dist=None, device="cpu"):
+    """Whole-job numbers from per-rank ones: (sum of pictures, max of milliseconds)."""
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return pictures_local, ms_local
+    import torch
+    t = torch.tensor([float(pictures_local)], dtype=torch.float64, device=device)
+    m = torch.tensor([float(ms_local)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    dist.all_reduce(m, op=dist.ReduceOp.MAX)
+    return int(round(t.item())), float(m.item())

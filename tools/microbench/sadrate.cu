@@ -46,6 +46,77 @@ __global__ void __launch_bounds__(256) k(uint32_t *out, int iters, uint32_t seed
     out[blockIdx.x * blockDim.x + threadIdx.x] = r;
 }
 
+// MODE 7: the inner body of the search kernels -- per window row 5 LDS, 12 SHF, 32 SAD (two candidate rows share it);
+// MODE 8: the same plus 12 integer ops per row (address / key arithmetic), the measured in-kernel mix.
+template <int MODE>
+__global__ void __launch_bounds__(128) kmix(uint32_t *out, int iters, uint32_t seed) {
+    __shared__ uint32_t sm[4096];
+    for (int i = threadIdx.x; i < 4096; i += blockDim.x) sm[i] = i * 2654435761u + seed;
+    __syncthreads();
+    uint32_t sreg[8][4], acc[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}}, junk = seed;
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) sreg[r][c] = seed * (r * 4 + c + 1) + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    for (int it = 0; it < iters; it++) {
+        const uint32_t *rowp = sm + ((lane + it * 37) & 1023);
+#pragma unroll
+        for (int rr = 0; rr < 9; rr++) {
+            const uint32_t *rp = rowp + rr * 33;
+            uint32_t        w[5];
+#pragma unroll
+            for (int c = 0; c < 5; c++) w[c] = rp[c];
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const uint32_t s0 = w[c], s1 = __funnelshift_r(w[c], w[c + 1], 8), s2 = __funnelshift_r(w[c], w[c + 1], 16),
+                               s3 = __funnelshift_r(w[c], w[c + 1], 24);
+                if (rr < 8) {
+                    const uint32_t sw = sreg[rr][c];
+                    acc[0][0] = sad4(s0, sw, acc[0][0]); acc[0][1] = sad4(s1, sw, acc[0][1]);
+                    acc[0][2] = sad4(s2, sw, acc[0][2]); acc[0][3] = sad4(s3, sw, acc[0][3]);
+                }
+                if (rr >= 1) {
+                    const uint32_t sw = sreg[rr - 1][c];
+                    acc[1][0] = sad4(s0, sw, acc[1][0]); acc[1][1] = sad4(s1, sw, acc[1][1]);
+                    acc[1][2] = sad4(s2, sw, acc[1][2]); acc[1][3] = sad4(s3, sw, acc[1][3]);
+                }
+                if (MODE == 8) { junk = junk * 5u + w[c]; junk ^= junk >> 3; junk += s1 & 7u; }
+            }
+        }
+    }
+    uint32_t r = junk;
+#pragma unroll
+    for (int i = 0; i < 4; i++) r += acc[0][i] + acc[1][i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+
+template <int MODE>
+void runmix(const char *name, int ctas_per_sm) {
+    int dev = 0, sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    uint32_t *out;
+    const int grid = sms * ctas_per_sm, iters = 4000;
+    cudaMalloc(&out, (size_t)grid * 128 * 4);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    kmix<MODE><<<grid, 128>>>(out, 100, 1);
+    cudaDeviceSynchronize();
+    float best = 1e30f;
+    for (int r = 0; r < 5; r++) {
+        cudaEventRecord(e0);
+        kmix<MODE><<<grid, 128>>>(out, iters, r + 2);
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        if (ms < best) best = ms;
+    }
+    const double sads = (double)grid * 128 * iters * 256.0;
+    printf("{\"bench\":\"%s\",\"warps_per_sm\":%d,\"ms\":%.3f,\"Gsad4_per_s\":%.1f,\"Tpx_per_s\":%.2f,\"per_sm_per_clk_at_1965MHz\":%.2f}\n", name,
+           ctas_per_sm * 4, best, sads / best / 1e6, sads * 4 / best / 1e9, sads / best / 1e3 / sms / 1965e3);
+    cudaFree(out);
+}
+
 template <int MODE>
 void run(const char *name, int ops_per_inner, int ctas_per_sm) {
     int dev = 0, sms = 0;
@@ -83,6 +154,10 @@ int main() {
         run<4>("lds+4xvabsdiff4.acc", 4, c);
         run<5>("sad.u32", 1, c);
         run<6>("dp4a", 1, c);
+    }
+    for (int c = 2; c <= 12; c += 2) {
+        runmix<7>("search-body 5LDS+12SHF+32SAD", c);
+        runmix<8>("search-body + 12 int ops/row", c);
     }
     return 0;
 }
