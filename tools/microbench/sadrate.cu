@@ -91,6 +91,100 @@ __global__ void __launch_bounds__(128) kmix(uint32_t *out, int iters, uint32_t s
     out[blockIdx.x * blockDim.x + threadIdx.x] = r;
 }
 
+// fsr by k bytes on the FMA pipe: (lo >> 8k) | (hi << (32 - 8k)) = mulhi(lo, 2^(32-8k)) + hi * 2^(32-8k)
+template <int K>
+__device__ __forceinline__ uint32_t fsr_mad(uint32_t lo, uint32_t hi) {
+    constexpr uint32_t C = 1u << (32 - 8 * K);
+    return hi * C + __umulhi(lo, C);
+}
+
+// MODE 9: the search body with the alignment shifts on the FMA pipe (2 IMAD per shifted word) instead of SHF
+// MODE 10..13: pipe probes (8 independent chains): 10 IMAD, 11 IMAD.HI, 12 SAD + IMAD 1:1, 13 SHF (non-hoistable)
+template <int MODE>
+__global__ void __launch_bounds__(128) kmix2(uint32_t *out, int iters, uint32_t seed) {
+    __shared__ uint32_t sm[4096];
+    for (int i = threadIdx.x; i < 4096; i += blockDim.x) sm[i] = i * 2654435761u + seed;
+    __syncthreads();
+    uint32_t sreg[8][4], acc[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) sreg[r][c] = seed * (r * 4 + c + 1) + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    if (MODE == 9) {
+        for (int it = 0; it < iters; it++) {
+            const uint32_t *rowp = sm + ((lane + it * 37) & 1023);
+#pragma unroll
+            for (int rr = 0; rr < 9; rr++) {
+                const uint32_t *rp = rowp + rr * 33;
+                uint32_t        w[5];
+#pragma unroll
+                for (int c = 0; c < 5; c++) w[c] = rp[c];
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    const uint32_t s0 = w[c], s1 = fsr_mad<1>(w[c], w[c + 1]), s2 = fsr_mad<2>(w[c], w[c + 1]), s3 = fsr_mad<3>(w[c], w[c + 1]);
+                    if (rr < 8) {
+                        const uint32_t sw = sreg[rr][c];
+                        acc[0][0] = sad4(s0, sw, acc[0][0]); acc[0][1] = sad4(s1, sw, acc[0][1]);
+                        acc[0][2] = sad4(s2, sw, acc[0][2]); acc[0][3] = sad4(s3, sw, acc[0][3]);
+                    }
+                    if (rr >= 1) {
+                        const uint32_t sw = sreg[rr - 1][c];
+                        acc[1][0] = sad4(s0, sw, acc[1][0]); acc[1][1] = sad4(s1, sw, acc[1][1]);
+                        acc[1][2] = sad4(s2, sw, acc[1][2]); acc[1][3] = sad4(s3, sw, acc[1][3]);
+                    }
+                }
+            }
+        }
+    } else {
+        uint32_t a[8], b = seed ^ threadIdx.x;
+#pragma unroll
+        for (int i = 0; i < 8; i++) a[i] = seed * (i + 3) + threadIdx.x;
+        for (int it = 0; it < iters; it++) {
+#pragma unroll
+            for (int u = 0; u < 32; u++) {
+                const int i = u & 7;
+                if (MODE == 10) a[i] = a[i] * 3u + b;
+                if (MODE == 11) a[i] = __umulhi(a[i], 0x01000000u) + b;
+                if (MODE == 12) { a[i] = a[i] * 3u + b; acc[i >> 2][i & 3] = sad4(a[(i + 4) & 7], b, acc[i >> 2][i & 3]); }
+                if (MODE == 13) a[i] = __funnelshift_r(a[i], a[(i + 1) & 7], 8);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i++) acc[0][0] += a[i];
+    }
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) r += acc[0][i] + acc[1][i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+
+template <int MODE>
+void runmix2(const char *name, int ctas_per_sm, double ops_per_iter) {
+    int dev = 0, sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    uint32_t *out;
+    const int grid = sms * ctas_per_sm, iters = 4000;
+    cudaMalloc(&out, (size_t)grid * 128 * 4);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    kmix2<MODE><<<grid, 128>>>(out, 100, 1);
+    cudaDeviceSynchronize();
+    float best = 1e30f;
+    for (int r = 0; r < 5; r++) {
+        cudaEventRecord(e0);
+        kmix2<MODE><<<grid, 128>>>(out, iters, r + 2);
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        if (ms < best) best = ms;
+    }
+    const double ops = (double)grid * 128 * iters * ops_per_iter;
+    printf("{\"bench\":\"%s\",\"warps_per_sm\":%d,\"ms\":%.3f,\"Gops_per_s\":%.1f,\"warp_ops_per_clk_per_smsp_at_1965MHz\":%.3f}\n", name,
+           ctas_per_sm * 4, best, ops / best / 1e6, ops / best / 1e3 / 32 / (sms * 4) / 1965e3);
+    cudaFree(out);
+}
+
 template <int MODE>
 void runmix(const char *name, int ctas_per_sm) {
     int dev = 0, sms = 0;
@@ -154,6 +248,13 @@ int main() {
         run<4>("lds+4xvabsdiff4.acc", 4, c);
         run<5>("sad.u32", 1, c);
         run<6>("dp4a", 1, c);
+    }
+    for (int c = 4; c <= 8; c += 4) {
+        runmix2<9>("search-body, shifts as IMAD pairs (SAD count)", c, 256.0);
+        runmix2<10>("imad", c, 32.0);
+        runmix2<11>("imad.hi", c, 32.0);
+        runmix2<12>("imad+sad (pairs)", c, 32.0);
+        runmix2<13>("shf", c, 32.0);
     }
     for (int c = 2; c <= 12; c += 2) {
         runmix<7>("search-body 5LDS+12SHF+32SAD", c);
