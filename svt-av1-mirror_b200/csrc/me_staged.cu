@@ -13,10 +13,22 @@
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include "me_engines.cuh"
 #include "me_launch.h"
 
 namespace svtme {
+
+// -DSVTME_PHASES: thread 0 of every CTA accumulates the clocks it spends in each phase of the engine kernels
+// (diagnostics; printed per search by SVTME_TRACE=1)
+#ifdef SVTME_PHASES
+__device__ unsigned long long g_phase[2][12];
+#define PH_DECL unsigned long long ph_t = clock64();
+#define PH(k, i) if (threadIdx.x == 0) { const unsigned long long ph_n = clock64(); atomicAdd(&g_phase[k][i], ph_n - ph_t); ph_t = ph_n; }
+#else
+#define PH_DECL
+#define PH(k, i)
+#endif
 
 constexpr int kStThreads  = 128;             // 4 warps per block CTA
 constexpr int kStWarps    = kStThreads / 32;
@@ -621,7 +633,7 @@ struct S16Sub {
     int16_t job, x0, y0, nx, ny, a, ngroups, P;
     int32_t plane_words, items, off, ibase;  // off / ibase: words / items before this sub-window inside its batch
     float   inv_ng, inv_nx;
-    int16_t hsel, q;                          // hsel 1: odd rows only; q: log2 lanes per staged row
+    int16_t hsel, q, wo, chunks;             // hsel 1: odd rows only; q: log2 lanes per staged row; wo: first word of group 0
 };
 
 __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_constant__ MeParams p) {
@@ -630,8 +642,8 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
     __shared__ unsigned long long          job_key[kMaxSadJobs];
     __shared__ S16Sub                      subs[kS16MaxSub];
     __shared__ uint32_t                    sub_key[kS16MaxSub];
-    __shared__ int16_t                     j_cnt[kMaxSadJobs], j_base[kMaxSadJobs], j_nst[kMaxSadJobs], j_nycap[kMaxSadJobs];
     __shared__ int                         n_sub_all, n_batch, b_start[kS16MaxSub + 1], b_items[kS16MaxSub];
+    PH_DECL
     SbState  &s = p.states[blockIdx.x];
     const int n = s.n_sad;
     if (n == 0) return;
@@ -650,25 +662,74 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
     const int       bw = (int)(b64_w >> 2), rows = (int)((b64_h >> 2) >> 1);
     const int       warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint8_t  *b0 = cp.org + (int64_t)(org_y >> 2) * cp.stride + (org_x >> 2);
+    uint32_t        sreg[8][4];  // rows 0, 2, .. 14 of the 16x16 block (same for every lane: broadcast loads), in flight early
+    if (bw == 16 && rows == 8) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(b0 + (int64_t)(2 * r) * cp.stride));
+            sreg[r][0] = v.x; sreg[r][1] = v.y; sreg[r][2] = v.z; sreg[r][3] = v.w;
+        }
+    }
     __syncthreads();
-    // ---- decomposition, in parallel: per job (tiles x strips), then per sub-window ----
-    if ((int)threadIdx.x < kMaxSadJobs) {
-        const int ji = threadIdx.x;
+    PH(1, 0)  // job fetch
+    // ---- decomposition by warp 0: lane = job.  Sub-windows = (column tile of <= 128 candidates) x (row strip) ----
+    if (warp == 0) {
+        const int ji = lane;
         int       cnt = 0, nst = 1, ny_cap = 16;
+        uint32_t  px = 0;
         if (ji < n && jobs[ji].sa_w > 0 && jobs[ji].sa_h > 0) {
             const int W = jobs[ji].sa_w, H = jobs[ji].sa_h;
-            const int pmax = (((3 + min(128, W) + 3) >> 2) + 4) | 1;
-            ny_cap = max(16, min(512, 4096 / pmax - 16)) & ~3;  // a sub-window: <= ~4 K words, < 64 K candidates
+            const int pmax = (((15 + min(128, W) + 3) >> 2) + 4 + 3) & ~3;  // widest row pitch of a tile, in words
+            ny_cap = max(16, min(512, 3584 / pmax - 16)) & ~3;               // a sub-window: <= ~3.6 K words, < 64 K candidates
             nst    = (H + ny_cap - 1) / ny_cap;
             cnt    = ((W + 127) >> 7) * nst;
+            px     = (uint32_t)W * (uint32_t)(jobs[ji].skip_line ? (H >> 1) : H) * (8 * 16);
         }
-        int incl = cnt;  // threads 0..31 are warp 0
+        int incl = cnt;
         for (int o = 1; o < 32; o <<= 1) {
             const int v = __shfl_up_sync(0xffffffffu, incl, o);
             if (lane >= o) incl += v;
         }
-        j_cnt[ji] = (int16_t)cnt; j_base[ji] = (int16_t)(incl - cnt); j_nst[ji] = (int16_t)nst; j_nycap[ji] = (int16_t)ny_cap;
-        if (ji == 31) n_sub_all = incl;
+        for (int o = 16; o; o >>= 1) px += __shfl_xor_sync(0xffffffffu, px, o);  // < 2^32: 32 jobs x 400 x 400 x 128
+        const int S = __shfl_sync(0xffffffffu, incl, 31);
+        if (lane == 0) { n_sub_all = S; if (px) atomicAdd(&s.px, (unsigned long long)px); }
+        if (S <= kS16MaxSub && cnt > 0) {
+            const SadJob &j = jobs[ji];
+            for (int local = 0, xt = 0, st = 0; local < cnt; local++) {
+                const int x0 = xt * 128, nx = min(128, j.sa_w - x0), y0 = st * ny_cap, ny = min(ny_cap, j.sa_h - y0);
+                const int a16 = (int)((uintptr_t)(j.ref + x0) & 15), a = a16 & 3, wo = a16 >> 2;
+                const int ngroups = (a + nx + 3) >> 2;
+                int       chunks = (wo + ngroups + 4 + 3) >> 2;  // 16-byte copies per row: groups + 4 block words + shifted-in word
+                chunks |= 1;                                      // pitch = 4 * odd words: candidate rows k, k+1 .. fall 8 banks apart
+                const int P = 4 * chunks, nyp = (ny + 3) & ~3, PR = ((nyp + 14 + 1) >> 1) + 1;
+                S16Sub   &u = subs[incl - cnt + local];
+                u.job = (int16_t)ji; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
+                u.a = (int16_t)a; u.wo = (int16_t)wo; u.chunks = (int16_t)chunks; u.ngroups = (int16_t)ngroups; u.P = (int16_t)P;
+                u.plane_words = ((PR * P + 15) & ~31) + 16;  // = 16 mod 32
+                u.hsel  = j.skip_line ? 1 : 0;
+                u.items = (nyp >> 2) * (j.skip_line ? 1 : 2) * ngroups;
+                u.inv_ng = 1.0f / (float)ngroups; u.inv_nx = 1.0f / (float)nx;
+                int q = 4;
+                while (q > 0 && (1 << (q - 1)) >= chunks) q--;
+                u.q = (int16_t)q;
+                if (++st == nst) { st = 0; xt++; }
+            }
+        }
+        __syncwarp();
+        // batches: maximal runs of sub-windows that fit the buffer (lane 0; a handful of adds per sub-window)
+        if (lane == 0 && S <= kS16MaxSub) {
+            int nb = 0, used = 0, items = 0;
+            b_start[0] = 0;
+            for (int i = 0; i < S; i++) {
+                S16Sub   &u = subs[i];
+                const int w2 = 2 * u.plane_words;
+                if (used + w2 > kS16BufWords) { b_items[nb] = items; b_start[++nb] = i; used = 0; items = 0; }
+                u.off = used; u.ibase = items;
+                used += w2; items += u.items;
+            }
+            b_items[nb] = items; b_start[++nb] = S;
+            n_batch = nb;
+        }
     }
     __syncthreads();
     const int S = n_sub_all;
@@ -684,100 +745,65 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
             blk[r * 16 + c] = a;
         }
         __syncthreads();
-        unsigned long long px = 0;
         for (int ji = warp; ji < n; ji += kStWarps) {
             const SadJob &j = jobs[ji];
-            if (j.sa_w > 0 && j.sa_h > 0) {
-                const bool skip = j.skip_line && bw == 16 && rows <= 16;
-                px += (unsigned long long)j.sa_w * (skip ? (j.sa_h >> 1) : j.sa_h) * rows * bw;
-            }
             constexpr int kWin = (kS16BufWords - 1024) / kStWarps * 4;  // bytes per warp
             uint8_t      *w8   = reinterpret_cast<uint8_t *>(s16_win + 1024) + warp * kWin;
             if (bw == 16) warp_sad_job<4>(j, s.sad_jobs[ji], blk, w8, lane, rows, bw, 2, kWin);
             else warp_sad_job<0>(j, s.sad_jobs[ji], blk, w8, lane, rows, bw, 2, kWin);
         }
-        if (lane == 0 && px) atomicAdd(&s.px, px);
+        {
+            // the work counter of partial blocks: rows x width of THIS block (the decomposition above counted 8 x 16)
+            if (threadIdx.x == 0) {
+                long long px = 0;
+                for (int ji = 0; ji < n; ji++) {
+                    const SadJob &j = jobs[ji];
+                    if (j.sa_w > 0 && j.sa_h > 0) {
+                        const bool skip = j.skip_line && bw == 16 && rows <= 16;
+                        px += (long long)j.sa_w * (skip ? (j.sa_h >> 1) : j.sa_h) * rows * bw;
+                        px -= (long long)j.sa_w * (j.skip_line ? (j.sa_h >> 1) : j.sa_h) * (8 * 16);
+                    }
+                }
+                if (px) atomicAdd(&s.px, (unsigned long long)px);
+            }
+        }
         return;
     }
-    if ((int)threadIdx.x < S) {
-        int ji = 0;
-        for (int q = 0; q < n; q++)
-            if ((int)threadIdx.x >= j_base[q] && (int)threadIdx.x < j_base[q] + j_cnt[q]) ji = q;
-        const SadJob &j = jobs[ji];
-        const int     local = threadIdx.x - j_base[ji], nst = j_nst[ji], ny_cap = j_nycap[ji];
-        const int     xt = local / nst, st = local - xt * nst;
-        const int     x0 = xt * 128, nx = min(128, j.sa_w - x0), y0 = st * ny_cap, ny = min(ny_cap, j.sa_h - y0);
-        const int     a = (int)((uintptr_t)(j.ref + x0) & 3);
-        const int     ngroups = (a + nx + 3) >> 2, P = (ngroups + 4) | 1;  // 4 block words + the shifted-in word
-        const int     nyp = (ny + 3) & ~3, PR = ((nyp + 14 + 1) >> 1) + 1;
-        S16Sub       &u = subs[threadIdx.x];
-        u.job = (int16_t)ji; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
-        u.a = (int16_t)a; u.ngroups = (int16_t)ngroups; u.P = (int16_t)P;
-        u.plane_words = ((PR * P + 15) & ~31) + 16;  // = 16 mod 32
-        u.hsel  = j.skip_line ? 1 : 0;
-        u.items = (nyp >> 2) * (j.skip_line ? 1 : 2) * ngroups;
-        u.inv_ng = 1.0f / (float)ngroups; u.inv_nx = 1.0f / (float)nx;
-        int q = 5;
-        while (q > 0 && (1 << (q - 1)) >= ngroups + 4) q--;
-        u.q = (int16_t)q;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        // batches: maximal runs of sub-windows that fit the buffer
-        int                nb = 0, used = 0, items = 0;
-        unsigned long long px = 0;
-        b_start[0] = 0;
-        for (int i = 0; i < S; i++) {
-            S16Sub   &u = subs[i];
-            const int w2 = 2 * u.plane_words;
-            if (used + w2 > kS16BufWords) { b_items[nb] = items; b_start[++nb] = i; used = 0; items = 0; }
-            u.off = used; u.ibase = items;
-            used += w2; items += u.items;
-        }
-        b_items[nb] = items; b_start[++nb] = S;
-        n_batch = nb;
-        for (int ji = 0; ji < n; ji++) {
-            const SadJob &j = jobs[ji];
-            if (j.sa_w > 0 && j.sa_h > 0) px += (unsigned long long)j.sa_w * (j.skip_line ? (j.sa_h >> 1) : j.sa_h) * (8 * 16);
-        }
-        if (px) atomicAdd(&s.px, px);
-    }
-    uint32_t sreg[8][4];  // rows 0, 2, .. 14 of the 16x16 block (same for every lane: broadcast loads)
-#pragma unroll
-    for (int r = 0; r < 8; r++) {
-        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(b0 + (int64_t)(2 * r) * cp.stride));
-        sreg[r][0] = v.x; sreg[r][1] = v.y; sreg[r][2] = v.z; sreg[r][3] = v.w;
-    }
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(s16_win);
-    __syncthreads();
+    PH(1, 1)  // decomposition
     const int nb = n_batch;
     for (int bi = 0; bi < nb; bi++) {
         const int s_lo = b_start[bi], s_hi = b_start[bi + 1];
-        // stage: one warp per sub-window, 2^q lanes per window row
+        // stage: one warp per sub-window, 16-byte copies, 2^q lanes per window row.  The rounded-up rows may read a few
+        // bytes past the window: inside the plane's padding / the allocation's slack, never used.
         for (int si = s_lo + warp; si < s_hi; si += kStWarps) {
             const S16Sub  &u = subs[si];
             const SadJob  &j = jobs[u.job];
-            const int      nrows = ((u.ny + 3) & ~3) + 14, nwords = u.ngroups + 4, raw = j.raw_stride, q = u.q;
-            const int      rpi = 32 >> q, lr = lane >> q, lw = lane & ((1 << q) - 1);
-            const uint8_t *g0 = j.ref + (int64_t)u.y0 * raw + u.x0 - u.a;
-            const uint32_t w0 = sbase + 4u * (uint32_t)u.off, pw = 4u * (uint32_t)u.plane_words, P4 = 4u * (uint32_t)u.P;
-            for (int wd = lw; wd < nwords; wd += 32) {
-                const uint8_t *g = g0 + (int64_t)lr * raw + 4 * wd;
+            const int      nrows = ((u.ny + 3) & ~3) + 14, chunks = u.chunks, q = u.q;
+            const uint32_t raw = (uint32_t)j.raw_stride;
+            const int      rpi = 32 >> q, lr = lane >> q, lc = lane & ((1 << q) - 1);
+            if (lc < chunks) {
+                const uint8_t *g0 = j.ref + (int64_t)u.y0 * (int64_t)raw + u.x0 - (u.a + 4 * u.wo) + 16 * lc;
+                const uint32_t P4 = 4u * (uint32_t)u.P;
+                const uint32_t w0 = sbase + 4u * (uint32_t)u.off + 16u * (uint32_t)lc, pw = 4u * (uint32_t)u.plane_words;
                 if (rpi >= 2) {  // the parity of the lane's rows is fixed
-                    uint32_t sa = w0 + (lr & 1) * pw + (uint32_t)(lr >> 1) * P4 + 4u * (uint32_t)wd;
-                    for (int R = lr; R < nrows; R += rpi, g += (int64_t)rpi * raw, sa += (uint32_t)(rpi >> 1) * P4)
-                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(g));
+                    const uint32_t sa0 = w0 + (uint32_t)(lr & 1) * pw;
+#pragma unroll 4
+                    for (int R = lr; R < nrows; R += rpi)
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa0 + (uint32_t)(R >> 1) * P4),
+                                     "l"(g0 + (uint64_t)(uint32_t)R * (uint64_t)raw));
                 } else {
-                    uint32_t sa = w0 + 4u * (uint32_t)wd;
-                    for (int R = 0; R < nrows; R += 2, g += 2 * (int64_t)raw, sa += P4) {
-                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(g));
-                        if (R + 1 < nrows) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa + pw), "l"(g + raw));
-                    }
+#pragma unroll 4
+                    for (int R = 0; R < nrows; R++)
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(w0 + (uint32_t)(R & 1) * pw + (uint32_t)(R >> 1) * P4),
+                                     "l"(g0 + (uint64_t)(uint32_t)R * (uint64_t)raw));
                 }
             }
         }
+        PH(1, 2)  // copy issue
         asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
         __syncthreads();
+        PH(1, 3)  // copy wait
         // compute: flat item list of the batch, lane f takes items f, f + 128, ...
         {
             const int T = b_items[bi];
@@ -796,7 +822,7 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
                     do { si++; next_base = subs[si].ibase + subs[si].items; } while (f >= next_base);
                     const S16Sub &u = subs[si];
                     u_ng = u.ngroups; u_nx = u.nx; u_ny = u.ny; u_P = u.P; u_a = u.a; u_hsel = u.hsel; u_ibase = u.ibase;
-                    u_inv_ng = u.inv_ng; u_win = s16_win + u.off; u_pw = (uint32_t)u.plane_words;
+                    u_inv_ng = u.inv_ng; u_win = s16_win + u.off + u.wo; u_pw = (uint32_t)u.plane_words;
                 }
                 const int item = f - u_ibase;
                 const int kh = (int)(((float)item + 0.5f) * u_inv_ng), g = item - kh * u_ng;
@@ -829,16 +855,20 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
                 }
                 const int xb = 4 * g - u_a;
 #pragma unroll
-                for (int y2 = 0; y2 < 2; y2++)
+                for (int y2 = 0; y2 < 2; y2++) {
+                    const int  y = yy + 2 * y2;
+                    const bool yok = y < u_ny;
+                    const uint32_t ybase = (uint32_t)(y * u_nx + xb);
 #pragma unroll
-                    for (int c = 0; c < 4; c++) {
-                        const int xx = xb + c, y = yy + 2 * y2;
-                        if (y < u_ny && xx >= 0 && xx < u_nx) best = min(best, (acc[y2][c] << 16) | (uint32_t)(y * u_nx + xx));
-                    }
+                    for (int c = 0; c < 4; c++)
+                        if (yok && (uint32_t)(xb + c) < (uint32_t)u_nx) best = min(best, acc[y2][c] * 65536u + ybase + (uint32_t)c);
+                }
             }
             flush();
         }
+        PH(1, 4)  // search (this thread)
         __syncthreads();  // the windows are reused by the next batch
+        PH(1, 5)  // waiting for the other warps
     }
     // sub-window minima -> job keys (sad, y, x): raster order inside the job decides ties between sub-windows
     if ((int)threadIdx.x < S && sub_key[threadIdx.x] != ~0u) {
@@ -856,6 +886,7 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
             jo.by = (int16_t)((key >> 16) & 0xffff); jo.bx = (int16_t)(key & 0xffff);
         }
     }
+    PH(1, 6)  // results to the block state
 }
 
 // ---- open_loop_me_fullpel_search_sblock jobs: one warp per unit (a strip of candidate rows of one job) ----
@@ -1100,6 +1131,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
     __shared__ __align__(16) FpJob    jobs[kMaxFpJobs];
     __shared__ FpSub                  subs[kFpMaxSub];
     __shared__ int                    n_sub, cur_job, cur_xt, cur_st;
+    PH_DECL
     SbState  &s = p.states[blockIdx.x];
     const int n = s.n_fp;
     if (n == 0) return;
@@ -1125,6 +1157,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
         }
     }
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(fp_win);
+    PH(0, 0)  // job fetch + source rows
 
     for (;;) {
         if (threadIdx.x == 0) {
@@ -1154,6 +1187,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
             if (px) atomicAdd(&s.px, px);
         }
         __syncthreads();
+        PH(0, 1)  // batch planning
         const int ns = n_sub;
         if (ns == 0) break;
         for (int i = threadIdx.x; i < ns * kPus; i += blockDim.x) (&sub_key[0][0])[i] = ~0u;
@@ -1177,8 +1211,10 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
                 }
             }
         }
+        PH(0, 2)  // copy issue
         asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
         __syncthreads();
+        PH(0, 3)  // copy wait
         for (int si = 0; si < ns; si++) {
             const FpSub &u = subs[si];
             const int    first = (warp - u.rbase) & (kStWarps - 1);
@@ -1286,7 +1322,9 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
             if (best32 != ~0u) atomicMin(&sub_key[si][1 + (b >> 2)], best32);
             if (b < 8 && best64 != ~0u) atomicMin(&sub_key[si][0], best64);
         }
+        PH(0, 4)  // search (this warp)
         __syncthreads();
+        PH(0, 5)  // waiting for the other warps
         // sub-window keys -> job keys: (doubled SAD, raster index inside the job's window)
         for (int i = threadIdx.x; i < ns * kPus; i += blockDim.x) {
             const int      si = i / kPus, pu = i - si * kPus;
@@ -1297,6 +1335,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
             atomicMin(&fp_key[u.job][pu], ((unsigned long long)(sad << 1) << 32) | (uint32_t)((u.y0 + y) * jobs[u.job].w + u.x0 + x));
         }
         __syncthreads();  // the windows are reused by the next batch
+        PH(0, 6)  // key fold
     }
     // fold the window minima into the running best of the reference (strict '<': earlier results win ties)
     for (int i = threadIdx.x; i < n * kPus; i += blockDim.x) {
@@ -1311,6 +1350,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
             s.best_mv[j.li][j.ri][pu]  = ((uint32_t)(y + j.yo) << 16) | (uint16_t)(x + j.xo);
         }
     }
+    PH(0, 7)  // results to the block state
 }
 
 // ---- host: run the program of one picture as a stream-ordered sequence of picture-wide kernels ----
@@ -1373,6 +1413,21 @@ cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_
             fprintf(stderr, " %s %.1f", nm[i], ms * 1e3f);
         }
         fprintf(stderr, " | total %.1f us\n", tot * 1e3f);
+#ifdef SVTME_PHASES
+        {
+            unsigned long long ph[2][12];
+            cudaMemcpyFromSymbol(ph, g_phase, sizeof(ph));
+            for (int k = 0; k < 2; k++) {
+                unsigned long long sum = 0;
+                for (int i = 0; i < 12; i++) sum += ph[k][i];
+                fprintf(stderr, "[svtme phases] %s:", k == 0 ? "fp_sub" : "sad16");
+                for (int i = 0; i < 12; i++) if (ph[k][i]) fprintf(stderr, " p%d %.1f%%", i, 100.0 * (double)ph[k][i] / (double)sum);
+                fprintf(stderr, " | %.1f kclk per CTA\n", (double)sum / 1e3 / (double)(n_sb * (k == 0 ? 2 : 2)));
+            }
+            memset(ph, 0, sizeof(ph));
+            cudaMemcpyToSymbol(g_phase, ph, sizeof(ph));
+        }
+#endif
         for (int i = 0; i < ne; i++) cudaEventDestroy(ev[i]);
     }
     if (n_launches) *n_launches = nl;
