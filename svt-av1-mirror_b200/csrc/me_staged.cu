@@ -645,15 +645,21 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
     __shared__ int                         n_sub_all, n_batch, b_start[kS16MaxSub + 1], b_items[kS16MaxSub];
     PH_DECL
     SbState  &s = p.states[blockIdx.x];
-    const int n = s.n_sad;
-    if (n == 0) return;
     {
+        // the whole job table is fetched together with the job count (one memory round trip instead of two)
+        constexpr int kWords = kMaxSadJobs * (int)sizeof(SadJob) / 8;
+        static_assert(kWords <= 2 * kStThreads, "two 64-bit words per thread");
         const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.sad_jobs[0]);
         unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
-        for (int i = threadIdx.x; i < n * (int)(sizeof(SadJob) / 8); i += blockDim.x) dst[i] = src[i];
+        const int                 i0 = threadIdx.x, i1 = threadIdx.x + kStThreads;
+        const unsigned long long  v0 = src[i0], v1 = i1 < kWords ? src[i1] : 0ull;
+        if (s.n_sad == 0) return;
+        dst[i0] = v0;
+        if (i1 < kWords) dst[i1] = v1;
         if (threadIdx.x < kMaxSadJobs) job_key[threadIdx.x] = ~0ull;
         if (threadIdx.x < kS16MaxSub) sub_key[threadIdx.x] = ~0u;
     }
+    const int n = s.n_sad;
     // block geometry as in make_sad_job (me_control.cuh)
     const DevPlane &cp = p.cur.lvl[2];
     const uint32_t  aw = (uint32_t)((p.cur.lvl[0].width + 7) & ~7), ah = (uint32_t)((p.cur.lvl[0].height + 7) & ~7);
@@ -674,61 +680,97 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
     PH(1, 0)  // job fetch
     // ---- decomposition by warp 0: lane = job.  Sub-windows = (column tile of <= 128 candidates) x (row strip) ----
     if (warp == 0) {
-        const int ji = lane;
-        int       cnt = 0, nst = 1, ny_cap = 16;
-        uint32_t  px = 0;
-        if (ji < n && jobs[ji].sa_w > 0 && jobs[ji].sa_h > 0) {
+        const int  ji    = lane;
+        const bool valid = ji < n && jobs[ji].sa_w > 0 && jobs[ji].sa_h > 0;
+        int        cnt = 0, nst = 1, ny_cap = 16;
+        uint32_t   px = 0;
+        if (valid) {
             const int W = jobs[ji].sa_w, H = jobs[ji].sa_h;
-            const int pmax = (((15 + min(128, W) + 3) >> 2) + 4 + 3) & ~3;  // widest row pitch of a tile, in words
-            ny_cap = max(16, min(512, 3584 / pmax - 16)) & ~3;               // a sub-window: <= ~3.6 K words, < 64 K candidates
-            nst    = (H + ny_cap - 1) / ny_cap;
+            const int pmax = (((15 + min(128, W) + 3) >> 2) + 4 + 3) & ~3;  // widest row pitch of a tile, in words (8 .. 40)
+            ny_cap = max(16, min(512, (int)(3584.0f / (float)pmax) - 16)) & ~3;  // a sub-window: <= ~5.5 K words, < 64 K candidates
+            nst    = H <= ny_cap ? 1 : (H + ny_cap - 1) / ny_cap;
             cnt    = ((W + 127) >> 7) * nst;
             px     = (uint32_t)W * (uint32_t)(jobs[ji].skip_line ? (H >> 1) : H) * (8 * 16);
         }
-        int incl = cnt;
-        for (int o = 1; o < 32; o <<= 1) {
-            const int v = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += v;
-        }
         for (int o = 16; o; o >>= 1) px += __shfl_xor_sync(0xffffffffu, px, o);  // < 2^32: 32 jobs x 400 x 400 x 128
-        const int S = __shfl_sync(0xffffffffu, incl, 31);
-        if (lane == 0) { n_sub_all = S; if (px) atomicAdd(&s.px, (unsigned long long)px); }
-        if (S <= kS16MaxSub && cnt > 0) {
+        if (lane == 0 && px) atomicAdd(&s.px, (unsigned long long)px);
+        // one sub-window per job in the common case: everything below is then lane-parallel
+        auto fill = [&](S16Sub &u, int x0, int y0, int nx, int ny, int &words) {
             const SadJob &j = jobs[ji];
-            for (int local = 0, xt = 0, st = 0; local < cnt; local++) {
-                const int x0 = xt * 128, nx = min(128, j.sa_w - x0), y0 = st * ny_cap, ny = min(ny_cap, j.sa_h - y0);
-                const int a16 = (int)((uintptr_t)(j.ref + x0) & 15), a = a16 & 3, wo = a16 >> 2;
-                const int ngroups = (a + nx + 3) >> 2;
-                int       chunks = (wo + ngroups + 4 + 3) >> 2;  // 16-byte copies per row: groups + 4 block words + shifted-in word
-                chunks |= 1;                                      // pitch = 4 * odd words: candidate rows k, k+1 .. fall 8 banks apart
-                const int P = 4 * chunks, nyp = (ny + 3) & ~3, PR = ((nyp + 14 + 1) >> 1) + 1;
-                S16Sub   &u = subs[incl - cnt + local];
-                u.job = (int16_t)ji; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
-                u.a = (int16_t)a; u.wo = (int16_t)wo; u.chunks = (int16_t)chunks; u.ngroups = (int16_t)ngroups; u.P = (int16_t)P;
-                u.plane_words = ((PR * P + 15) & ~31) + 16;  // = 16 mod 32
-                u.hsel  = j.skip_line ? 1 : 0;
-                u.items = (nyp >> 2) * (j.skip_line ? 1 : 2) * ngroups;
-                u.inv_ng = 1.0f / (float)ngroups; u.inv_nx = 1.0f / (float)nx;
-                int q = 4;
-                while (q > 0 && (1 << (q - 1)) >= chunks) q--;
-                u.q = (int16_t)q;
-                if (++st == nst) { st = 0; xt++; }
+            const int     a16 = (int)((uintptr_t)(j.ref + x0) & 15), a = a16 & 3, wo = a16 >> 2;
+            const int     ngroups = (a + nx + 3) >> 2;
+            int           chunks = (wo + ngroups + 4 + 3) >> 2;  // 16-byte copies per row: groups + 4 block words + shifted-in word
+            chunks |= 1;                                          // pitch = 4 * odd words: candidate rows k, k+1 .. fall 8 banks apart
+            const int P = 4 * chunks, nyp = (ny + 3) & ~3, PR = ((nyp + 14 + 1) >> 1) + 1;
+            u.job = (int16_t)ji; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
+            u.a = (int16_t)a; u.wo = (int16_t)wo; u.chunks = (int16_t)chunks; u.ngroups = (int16_t)ngroups; u.P = (int16_t)P;
+            u.plane_words = ((PR * P + 15) & ~31) + 16;  // = 16 mod 32
+            u.hsel  = j.skip_line ? 1 : 0;
+            u.items = (nyp >> 2) * (j.skip_line ? 1 : 2) * ngroups;
+            u.inv_ng = __fdividef(1.0f, (float)ngroups) * 1.0000001f; u.inv_nx = __fdividef(1.0f, (float)nx) * 1.0000001f;
+            u.q = (int16_t)(chunks <= 2 ? 1 : chunks <= 4 ? 2 : chunks <= 8 ? 3 : 4);
+            words = 2 * u.plane_words;
+        };
+        const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+        if (__all_sync(0xffffffffu, cnt <= 1)) {
+            const int S = __popc(vmask), idx = __popc(vmask & ((1u << lane) - 1u));
+            int       words = 0, items = 0;
+            if (valid) { fill(subs[idx], 0, 0, jobs[ji].sa_w, jobs[ji].sa_h, words); items = subs[idx].items; }
+            int cw = words, ci = items;  // inclusive sums over the lanes (invalid lanes contribute 0)
+            for (int o = 1; o < 32; o <<= 1) {
+                const int vw = __shfl_up_sync(0xffffffffu, cw, o), vi = __shfl_up_sync(0xffffffffu, ci, o);
+                if (lane >= o) { cw += vw; ci += vi; }
             }
-        }
-        __syncwarp();
-        // batches: maximal runs of sub-windows that fit the buffer (lane 0; a handful of adds per sub-window)
-        if (lane == 0 && S <= kS16MaxSub) {
-            int nb = 0, used = 0, items = 0;
-            b_start[0] = 0;
-            for (int i = 0; i < S; i++) {
-                S16Sub   &u = subs[i];
-                const int w2 = 2 * u.plane_words;
-                if (used + w2 > kS16BufWords) { b_items[nb] = items; b_start[++nb] = i; used = 0; items = 0; }
-                u.off = used; u.ibase = items;
-                used += w2; items += u.items;
+            // greedy batches: a lane whose window would overflow the buffer starts the next batch
+            int base_w = 0, base_i = 0, nb = 0;
+            if (lane == 0) b_start[0] = 0;
+            for (;;) {
+                const unsigned over = __ballot_sync(0xffffffffu, valid && cw - base_w > kS16BufWords);
+                if (!over) break;
+                const int first = __ffs(over) - 1;
+                const int fw = __shfl_sync(0xffffffffu, cw - words, first), fi = __shfl_sync(0xffffffffu, ci - items, first);
+                const int fidx = __shfl_sync(0xffffffffu, idx, first);
+                // items of the batch that ends here = fi - (items before the batch); every lane >= first moves its base
+                const int prev_base_i = __shfl_sync(0xffffffffu, base_i, first);
+                if (lane == 0) { b_items[nb] = fi - prev_base_i; b_start[nb + 1] = fidx; }
+                nb++;
+                if (lane >= first) { base_w = fw; base_i = fi; }
             }
-            b_items[nb] = items; b_start[++nb] = S;
-            n_batch = nb;
+            if (valid) { subs[idx].off = cw - words - base_w; subs[idx].ibase = ci - items - base_i; }
+            const int tot_i = __shfl_sync(0xffffffffu, ci, 31), last_base_i = __shfl_sync(0xffffffffu, base_i, 31);
+            if (lane == 0) { b_items[nb] = tot_i - last_base_i; b_start[nb + 1] = S; n_batch = S ? nb + 1 : 0; n_sub_all = S; }
+        } else {
+            int incl = cnt;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const int S = __shfl_sync(0xffffffffu, incl, 31);
+            if (lane == 0) n_sub_all = S;
+            if (S <= kS16MaxSub && cnt > 0) {
+                const SadJob &j = jobs[ji];
+                for (int local = 0, xt = 0, st = 0; local < cnt; local++) {
+                    const int x0 = xt * 128, y0 = st * ny_cap;
+                    int       words;
+                    fill(subs[incl - cnt + local], x0, y0, min(128, j.sa_w - x0), min(ny_cap, j.sa_h - y0), words);
+                    if (++st == nst) { st = 0; xt++; }
+                }
+            }
+            __syncwarp();
+            // batches: maximal runs of sub-windows that fit the buffer (lane 0; a handful of adds per sub-window)
+            if (lane == 0 && S <= kS16MaxSub) {
+                int nb = 0, used = 0, items = 0;
+                b_start[0] = 0;
+                for (int i = 0; i < S; i++) {
+                    S16Sub   &u = subs[i];
+                    const int w2 = 2 * u.plane_words;
+                    if (used + w2 > kS16BufWords) { b_items[nb] = items; b_start[++nb] = i; used = 0; items = 0; }
+                    u.off = used; u.ibase = items;
+                    used += w2; items += u.items;
+                }
+                b_items[nb] = items; b_start[++nb] = S;
+                n_batch = nb;
+            }
         }
     }
     __syncthreads();
