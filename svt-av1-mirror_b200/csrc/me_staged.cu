@@ -1174,16 +1174,20 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
     __shared__ FpSub                  subs[kFpMaxSub];
     __shared__ int                    n_sub, cur_job, cur_xt, cur_st;
     PH_DECL
+    __shared__ int                    b_lo[kFpMaxSub + 1], fast_nb;
     SbState  &s = p.states[blockIdx.x];
-    const int n = s.n_fp;
-    if (n == 0) return;
     {
+        // the job table is fetched together with the job count (one memory round trip instead of two)
+        constexpr int kWords = kMaxFpJobs * (int)sizeof(FpJob) / 8;
+        static_assert(kWords <= kStThreads, "one 64-bit word per thread");
         const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.fp_jobs[0]);
-        unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
-        for (int i = threadIdx.x; i < n * (int)(sizeof(FpJob) / 8); i += blockDim.x) dst[i] = src[i];
-        for (int i = threadIdx.x; i < n * kPus; i += blockDim.x) (&fp_key[0][0])[i] = ~0ull;
+        const unsigned long long  v = (int)threadIdx.x < kWords ? src[threadIdx.x] : 0ull;
+        if (s.n_fp == 0) return;
+        if ((int)threadIdx.x < kWords) reinterpret_cast<unsigned long long *>(&jobs[0])[threadIdx.x] = v;
+        for (int i = threadIdx.x; i < kMaxFpJobs * kPus; i += blockDim.x) (&fp_key[0][0])[i] = ~0ull;
         if (threadIdx.x == 0) { cur_job = 0; cur_xt = 0; cur_st = 0; }
     }
+    const int n = s.n_fp;
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = lane & 15, half = lane >> 4;
@@ -1198,45 +1202,106 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
             sreg[r][0] = v.x; sreg[r][1] = v.y; sreg[r][2] = v.z; sreg[r][3] = v.w;
         }
     }
+    // the running best SADs this thread will compare against at the end: requested now, needed last
+    constexpr int kFoldPer = (kMaxFpJobs * kPus + kStThreads - 1) / kStThreads;
+    uint32_t      prev_best[kFoldPer];
+#pragma unroll
+    for (int t = 0; t < kFoldPer; t++) {
+        const int i = threadIdx.x + t * kStThreads, ji = i / kPus, pu = i - ji * kPus;
+        prev_best[t] = i < n * kPus ? s.best_sad[jobs[ji].li][jobs[ji].ri][pu] : 0u;
+    }
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(fp_win);
     PH(0, 0)  // job fetch + source rows
-
-    for (;;) {
-        if (threadIdx.x == 0) {
-            // next batch of sub-windows (job, 64-wide column, 64-high strip) that fits the buffer
-            int                ns = 0, used = 0, rb = 0;
-            unsigned long long px = 0;
-            while (cur_job < n && ns < kFpMaxSub) {
-                const FpJob &j = jobs[cur_job];
-                if (j.w <= 0 || j.h <= 0) { cur_job++; continue; }
-                const int nxt = (j.w + 63) >> 6, nst = (j.h + 63) >> 6;
-                const int x0 = cur_xt * 64, y0 = cur_st * 64, nx = min(64, j.w - x0), ny = min(64, j.h - y0);
-                const int a = (int)((uintptr_t)(j.ref + x0) & 3);
-                const int ngroups = (a + nx + 3) >> 2, P = (ngroups + 16 + 3) & ~3;
-                const int nyp = (ny + 3) & ~3, PR = ((nyp + 62 + 7) & ~7) >> 1;  // staged in groups of 8 rows
-                int       plane = PR * P + (PR >> 3) + 1;
-                plane           = ((plane + 15) & ~31) + 16;  // = 16 mod 32
-                if (used + 2 * plane > kFpBufWords) break;    // a single sub-window always fits (<= 4.8 K words)
-                FpSub &u = subs[ns++];
-                u.job = (int16_t)cur_job; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
-                u.a = (int16_t)a; u.ngroups = (int16_t)ngroups; u.P = (int16_t)P;
-                u.off = used; u.plane_words = plane; u.rbase = rb; u.rounds = (nyp >> 2) * ngroups;
-                used += 2 * plane; rb += u.rounds;
-                if (cur_xt == 0 && cur_st == 0) px += (unsigned long long)j.w * j.h * (64 * 32);
-                if (++cur_st == nst) { cur_st = 0; if (++cur_xt == nxt) { cur_xt = 0; cur_job++; } }
+    // ---- common case: every window is one sub-window (<= 64 x 64 candidates): all batches planned at once by warp 0,
+    //      lane = job; otherwise thread 0 walks a cursor over (job, column, strip) batch by batch ----
+    auto sub_geometry = [&](const FpJob &j, int x0, int y0, int nx, int ny, FpSub &u) {
+        const int a = (int)((uintptr_t)(j.ref + x0) & 3);
+        const int ngroups = (a + nx + 3) >> 2, P = (ngroups + 16 + 3) & ~3;
+        const int nyp = (ny + 3) & ~3, PR = ((nyp + 62 + 7) & ~7) >> 1;  // staged in groups of 8 rows
+        int       plane = PR * P + (PR >> 3) + 1;
+        plane           = ((plane + 15) & ~31) + 16;  // = 16 mod 32
+        u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
+        u.a = (int16_t)a; u.ngroups = (int16_t)ngroups; u.P = (int16_t)P;
+        u.plane_words = plane; u.rounds = (nyp >> 2) * ngroups;
+    };
+    if (warp == 0) {
+        const bool valid = lane < n && jobs[lane].w > 0 && jobs[lane].h > 0;
+        const bool fast  = __all_sync(0xffffffffu, !valid || (jobs[lane].w <= 64 && jobs[lane].h <= 64));
+        if (fast) {
+            const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+            const int      S = __popc(vmask), idx = __popc(vmask & ((1u << lane) - 1u));
+            int            words = 0, rounds = 0;
+            uint32_t       px = 0;
+            if (valid) {
+                FpSub &u = subs[idx];
+                sub_geometry(jobs[lane], 0, 0, jobs[lane].w, jobs[lane].h, u);
+                u.job = (int16_t)lane;
+                words = 2 * u.plane_words; rounds = u.rounds;
+                px    = (uint32_t)(jobs[lane].w * jobs[lane].h) * (64u * 32u);  // <= 64 * 64 * 2048
             }
-            n_sub = ns;
-            if (px) atomicAdd(&s.px, px);
+            int cw = words, cr = rounds;
+            for (int o = 1; o < 8; o <<= 1) {  // jobs live in lanes 0..7
+                const int vw = __shfl_up_sync(0xffffffffu, cw, o), vr = __shfl_up_sync(0xffffffffu, cr, o);
+                if (lane >= o) { cw += vw; cr += vr; }
+            }
+            for (int o = 4; o; o >>= 1) px += __shfl_xor_sync(0xffffffffu, px, o);
+            if (lane == 0 && px) atomicAdd(&s.px, (unsigned long long)px);
+            int base_w = 0, nb = 0;
+            if (lane == 0) b_lo[0] = 0;
+            for (;;) {
+                const unsigned over = __ballot_sync(0xffffffffu, valid && cw - base_w > kFpBufWords);
+                if (!over) break;
+                const int first = __ffs(over) - 1;
+                const int fw = __shfl_sync(0xffffffffu, cw - words, first), fidx = __shfl_sync(0xffffffffu, idx, first);
+                nb++;
+                if (lane == 0) b_lo[nb] = fidx;
+                if (lane >= first) base_w = fw;
+            }
+            if (valid) { subs[idx].off = cw - words - base_w; subs[idx].rbase = cr - rounds; }
+            if (lane == 0) { b_lo[nb + 1] = S; fast_nb = S ? nb + 1 : 0; }
+        } else if (lane == 0) fast_nb = -1;
+    }
+    __syncthreads();
+    const int nb_fast = fast_nb;
+
+    for (int bi = 0;; bi++) {
+        int s_lo = 0, s_hi = 0;
+        if (nb_fast >= 0) {
+            if (bi >= nb_fast) break;
+            s_lo = b_lo[bi]; s_hi = b_lo[bi + 1];
+        } else {
+            if (threadIdx.x == 0) {
+                // next batch of sub-windows (job, 64-wide column, 64-high strip) that fits the buffer
+                int                ns = 0, used = 0, rb = 0;
+                unsigned long long px = 0;
+                while (cur_job < n && ns < kFpMaxSub) {
+                    const FpJob &j = jobs[cur_job];
+                    if (j.w <= 0 || j.h <= 0) { cur_job++; continue; }
+                    const int nxt = (j.w + 63) >> 6, nst = (j.h + 63) >> 6;
+                    const int x0 = cur_xt * 64, y0 = cur_st * 64;
+                    FpSub     u;
+                    sub_geometry(j, x0, y0, min(64, j.w - x0), min(64, j.h - y0), u);
+                    if (used + 2 * u.plane_words > kFpBufWords) break;  // a single sub-window always fits (<= 4.8 K words)
+                    u.job = (int16_t)cur_job; u.off = used; u.rbase = rb;
+                    subs[ns++] = u;
+                    used += 2 * u.plane_words; rb += u.rounds;
+                    if (cur_xt == 0 && cur_st == 0) px += (unsigned long long)j.w * j.h * (64 * 32);
+                    if (++cur_st == nst) { cur_st = 0; if (++cur_xt == nxt) { cur_xt = 0; cur_job++; } }
+                }
+                n_sub = ns;
+                if (px) atomicAdd(&s.px, px);
+            }
+            __syncthreads();
+            s_hi = n_sub;
+            if (s_hi == 0) break;
         }
-        __syncthreads();
         PH(0, 1)  // batch planning
-        const int ns = n_sub;
-        if (ns == 0) break;
-        for (int i = threadIdx.x; i < ns * kPus; i += blockDim.x) (&sub_key[0][0])[i] = ~0u;
+        const int ns = s_hi - s_lo;
+        for (int i = threadIdx.x; i < ns * kPus; i += blockDim.x) (&sub_key[s_lo][0])[i] = ~0u;
         // stage: warp w copies rows w, w + 4, ... (fixed parity), lane = word of the row.  Rows go in groups of 8
         // (2 per warp): inside a group the skew (i >> 3) is constant, so the addresses are plain strides.  The rows
         // past the window (< 8 + 3) are inside the plane's physical padding (96 rows against the 72 a search uses).
-        for (int si = 0; si < ns; si++) {
+        for (int si = s_lo; si < s_hi; si++) {
             const FpSub   &u = subs[si];
             const FpJob   &j = jobs[u.job];
             const int      ngrp = (((u.ny + 3) & ~3) + 62 + 7) >> 3, nwords = u.ngroups + 16, raw = j.ref_stride;
@@ -1257,7 +1322,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
         asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
         __syncthreads();
         PH(0, 3)  // copy wait
-        for (int si = 0; si < ns; si++) {
+        for (int si = s_lo; si < s_hi; si++) {
             const FpSub &u = subs[si];
             const int    first = (warp - u.rbase) & (kStWarps - 1);
             if (first >= u.rounds) continue;
@@ -1369,7 +1434,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
         PH(0, 5)  // waiting for the other warps
         // sub-window keys -> job keys: (doubled SAD, raster index inside the job's window)
         for (int i = threadIdx.x; i < ns * kPus; i += blockDim.x) {
-            const int      si = i / kPus, pu = i - si * kPus;
+            const int      si = s_lo + i / kPus, pu = i - (i / kPus) * kPus;
             const uint32_t key = sub_key[si][pu];
             if (key == ~0u) continue;
             const FpSub   &u = subs[si];
@@ -1380,13 +1445,16 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
         PH(0, 6)  // key fold
     }
     // fold the window minima into the running best of the reference (strict '<': earlier results win ties)
-    for (int i = threadIdx.x; i < n * kPus; i += blockDim.x) {
+#pragma unroll
+    for (int t = 0; t < kFoldPer; t++) {
+        const int i = threadIdx.x + t * kStThreads;
+        if (i >= n * kPus) break;
         const int                ji = i / kPus, pu = i - ji * kPus;
         const FpJob             &j  = jobs[ji];
         const unsigned long long key = fp_key[ji][pu];
         if (key == ~0ull) continue;
         const uint32_t sad = (uint32_t)(key >> 32), ord = (uint32_t)key;
-        if (sad < s.best_sad[j.li][j.ri][pu]) {
+        if (sad < prev_best[t]) {
             const int32_t y = (int32_t)(ord / (uint32_t)j.w), x = (int32_t)(ord - (uint32_t)y * (uint32_t)j.w);
             s.best_sad[j.li][j.ri][pu] = sad;
             s.best_mv[j.li][j.ri][pu]  = ((uint32_t)(y + j.yo) << 16) | (uint16_t)(x + j.xo);
