@@ -395,112 +395,129 @@ __device__ void warp_sad_job_fast(const SadJob &j, SadJob &jout, const uint32_t 
 // word pitch, so the 32 rows read by a warp fall into 32 different banks.
 template <int NW, int ROWS>
 struct RowsCfg {
-    static constexpr int kNWords  = NW + 4;                      // window words per row: bytes a .. a+7+bw-1, +1 for the shift
-    static constexpr int kS       = kNWords | 1;                 // odd pitch
+    // a window row = 16-byte chunks from the 16-byte aligned address below the first candidate:
+    // misalignment (<= 15) + 7 more candidates + block width, rounded up
+    static constexpr int kChunks  = (15 + 7 + 4 * NW + 15) / 16;  // 6 (64-wide blocks) / 4 (32-wide)
+    static constexpr int kSlots   = kChunks <= 4 ? 4 : 8;         // lanes per staged row
+    static constexpr int kRpi     = 32 / kSlots;                  // rows per copy instruction (even: a lane keeps its row parity)
+    static constexpr int kS       = 4 * (kChunks | 1);            // pitch in words, an ODD number of chunks: 8 consecutive rows
+                                                                  // of a plane start in 8 different 16-byte bank groups
     static constexpr int kExtY    = (ROWS - 1) * 2;
-    static constexpr int kNy      = 4;                           // candidate rows per staged chunk
-    static constexpr int kRowsPad = (kNy + kExtY + 7) & ~7;      // staged in groups of 8 rows
-    static constexpr int kPlaneW  = (kRowsPad / 2) * kS;         // words per parity plane
+    static constexpr int kNy      = 4;                            // candidate rows per staged chunk
+    static constexpr int kRowsPad = (kNy + kExtY + 7) & ~7;       // staged in groups of 8 rows
+    static constexpr int kPlaneW  = (kRowsPad / 2) * kS;          // words per parity plane
     static constexpr int kWinW    = 2 * kPlaneW;
-    static constexpr int kK       = kNWords / 4;                 // cp.async per lane per 8 rows
-    static_assert(kNWords % 4 == 0, "8 rows x kNWords words must be a whole number of warp-wide copies");
+    static_assert(kRowsPad % kRpi == 0 && kRpi % 2 == 0, "copy groups");
 };
+
+// WO = (address of candidate 0) / 4 mod 4: which word of the 16-byte aligned row holds candidate 0 (static register indexing)
+template <int NW, int ROWS, bool FULLW, int WO>
+__device__ __forceinline__ void rows_unit(const uint32_t (&sreg)[NW], const uint32_t *win, int lane, int rows, int nw_eff, int a,
+                                          int x0, int y0, int wx, int ny, unsigned long long &best) {
+    using C = RowsCfg<NW, ROWS>;
+    constexpr int SUBS = 32 / ROWS, MAXW = NW + 3;
+    static_assert(WO + MAXW < 4 * C::kChunks, "the shifted-in word is inside the staged chunks");
+    const int slice = lane & (ROWS - 1), sub = lane / ROWS, shift = 8 * a;
+    // which of the 8 candidates this lane owns after the transposing reduction
+    const int own = ROWS == 32 ? (((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1))
+                               : (((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1));
+    for (int yb = 0; yb < ny; yb += SUBS) {
+        const int  yy     = yb + sub;
+        const bool active = yy < ny && slice < rows;
+        uint32_t   acc[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) acc[i] = 0;
+        if (active) {
+            const uint4 *rp = reinterpret_cast<const uint4 *>(win + (yy & 1) * C::kPlaneW + ((yy >> 1) + slice) * C::kS);
+            uint32_t     v[4 * C::kChunks];
+#pragma unroll
+            for (int c = 0; c < C::kChunks; c++) {
+                const uint4 q = rp[c];
+                v[4 * c] = q.x; v[4 * c + 1] = q.y; v[4 * c + 2] = q.z; v[4 * c + 3] = q.w;
+            }
+            uint32_t w[MAXW + 1];
+#pragma unroll
+            for (int c = 0; c < MAXW; c++) w[c] = __funnelshift_r(v[WO + c], v[WO + c + 1], shift);  // candidate 0 now starts at byte 0
+            w[MAXW] = 0;
+#pragma unroll
+            for (int g = 0; g < 2; g++)
+#pragma unroll
+                for (int c = 0; c < NW; c++) {
+                    if (FULLW || c < nw_eff) {
+                        const uint32_t sw = sreg[c], lo = w[g + c], hi = w[g + c + 1];
+                        acc[4 * g + 0] = sad4(lo, sw, acc[4 * g + 0]);
+                        acc[4 * g + 1] = sad4(fsr(lo, hi, 1), sw, acc[4 * g + 1]);
+                        acc[4 * g + 2] = sad4(fsr(lo, hi, 2), sw, acc[4 * g + 2]);
+                        acc[4 * g + 3] = sad4(fsr(lo, hi, 3), sw, acc[4 * g + 3]);
+                    }
+                }
+        }
+        // transposing butterfly over the ROWS lanes of the group: 8 -> 4 -> 2 -> 1 values per lane, then plain sums
+        uint32_t v4[4], v2[2], v1;
+        {
+            const bool up = lane & (ROWS / 2);
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint32_t send = up ? acc[i] : acc[4 + i], keep = up ? acc[4 + i] : acc[i];
+                v4[i] = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 2);
+            }
+        }
+        {
+            const bool up = lane & (ROWS / 4);
+#pragma unroll
+            for (int i = 0; i < 2; i++) {
+                const uint32_t send = up ? v4[i] : v4[2 + i], keep = up ? v4[2 + i] : v4[i];
+                v2[i] = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 4);
+            }
+        }
+        {
+            const bool     up   = lane & (ROWS / 8);
+            const uint32_t send = up ? v2[0] : v2[1], keep = up ? v2[1] : v2[0];
+            v1 = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 8);
+        }
+#pragma unroll
+        for (int o = ROWS / 16; o; o >>= 1) v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+        if (yy < ny && own < wx && (lane & (ROWS / 8 - 1)) == 0) {
+            const unsigned long long key = ((unsigned long long)v1 << 32) | ((uint32_t)(y0 + yy) << 16) | (uint32_t)(x0 + own);
+            best = key < best ? key : best;
+        }
+    }
+}
 
 template <int NW, int ROWS, bool FULLW>
 __device__ __forceinline__ void rows_job(const SadJob &j, SadJob &jout, const uint32_t (&sreg)[NW], uint32_t *win, int lane,
                                          int rows, int nw_eff) {
     using C = RowsCfg<NW, ROWS>;
-    constexpr int SUBS = 32 / ROWS, MAXW = NW + 3;
     const int W = j.sa_w, H = j.sa_h;
     if (W <= 0 || H <= 0) return;
     const uint8_t *ref   = j.ref;
-    const int      raw   = j.raw_stride;
-    const int      slice = lane & (ROWS - 1), sub = lane / ROWS;
+    const uint32_t raw   = (uint32_t)j.raw_stride;
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(win);
-    // staging map of this lane: copy k of an 8-row group moves word wk of row rk
-    uint32_t gofs[C::kK], sofs[C::kK];
-#pragma unroll
-    for (int k = 0; k < C::kK; k++) {
-        const int idx = lane + 32 * k, R = idx / C::kNWords, w = idx - R * C::kNWords;
-        gofs[k] = (uint32_t)(R * raw + 4 * w);
-        sofs[k] = (uint32_t)(((R & 1) * C::kPlaneW + (R >> 1) * C::kS + w) * 4);
-    }
-    // which of the 8 candidates this lane owns after the transposing reduction
-    const int own = ROWS == 32 ? (((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1))
-                               : (((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1));
+    // staging map of this lane: row lr of every group of kRpi rows, chunk lc (16-byte copies)
+    const int      lr = lane / C::kSlots, lc = lane % C::kSlots;
+    const uint32_t sofs = (uint32_t)(((lr & 1) * C::kPlaneW + (lr >> 1) * C::kS) * 4 + 16 * lc);
     unsigned long long best = ~0ull;
     for (int x0 = 0; x0 < W; x0 += 8) {
-        const int a = (int)((uintptr_t)(ref + x0) & 3), shift = 8 * a, wx = min(8, W - x0);
+        const int a16 = (int)((uintptr_t)(ref + x0) & 15), a = a16 & 3, wo = a16 >> 2, wx = min(8, W - x0);
         for (int y0 = 0; y0 < H; y0 += C::kNy) {
             const int      ny = min(H - y0, C::kNy);
-            const uint8_t *g0 = ref + (int64_t)y0 * raw + x0 - a;
+            const uint8_t *g0 = ref + (int64_t)y0 * (int64_t)raw + x0 - a16 + 16 * lc;
             __syncwarp();
             // always the full kRowsPad rows: the few rows below a short window are inside the plane's physical padding
             // (96 / 48 rows against the 72 / 32 the search may touch), and the copy loop unrolls to immediates
+            if (lc < C::kChunks) {
 #pragma unroll
-            for (int G = 0; G < C::kRowsPad / 8; G++) {
-#pragma unroll
-                for (int k = 0; k < C::kK; k++)
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sbase + sofs[k] + (uint32_t)(G * 4 * C::kS * 4)), "l"(g0 + gofs[k]));
-                g0 += 8 * (int64_t)raw;
+                for (int G = 0; G < C::kRowsPad / C::kRpi; G++)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sbase + sofs + (uint32_t)(G * (C::kRpi / 2) * C::kS * 4)),
+                                 "l"(g0 + (uint64_t)(uint32_t)(G * C::kRpi + lr) * (uint64_t)raw));
             }
             asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
             __syncwarp();
-            for (int yb = 0; yb < ny; yb += SUBS) {
-                const int  yy     = yb + sub;
-                const bool active = yy < ny && slice < rows;
-                uint32_t   acc[8];
-#pragma unroll
-                for (int i = 0; i < 8; i++) acc[i] = 0;
-                if (active) {
-                    const uint32_t *rp = win + (yy & 1) * C::kPlaneW + ((yy >> 1) + slice) * C::kS;
-                    uint32_t        w[MAXW + 1];
-#pragma unroll
-                    for (int c = 0; c <= MAXW; c++) w[c] = rp[c];
-#pragma unroll
-                    for (int c = 0; c < MAXW; c++) w[c] = __funnelshift_r(w[c], w[c + 1], shift);  // candidate 0 now starts at byte 0
-#pragma unroll
-                    for (int g = 0; g < 2; g++)
-#pragma unroll
-                        for (int c = 0; c < NW; c++) {
-                            if (FULLW || c < nw_eff) {
-                                const uint32_t sw = sreg[c], lo = w[g + c], hi = w[g + c + 1];
-                                acc[4 * g + 0] = sad4(lo, sw, acc[4 * g + 0]);
-                                acc[4 * g + 1] = sad4(fsr(lo, hi, 1), sw, acc[4 * g + 1]);
-                                acc[4 * g + 2] = sad4(fsr(lo, hi, 2), sw, acc[4 * g + 2]);
-                                acc[4 * g + 3] = sad4(fsr(lo, hi, 3), sw, acc[4 * g + 3]);
-                            }
-                        }
-                }
-                // transposing butterfly over the ROWS lanes of the group: 8 -> 4 -> 2 -> 1 values per lane, then plain sums
-                uint32_t v4[4], v2[2], v1;
-                {
-                    const bool up = lane & (ROWS / 2);
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const uint32_t send = up ? acc[i] : acc[4 + i], keep = up ? acc[4 + i] : acc[i];
-                        v4[i] = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 2);
-                    }
-                }
-                {
-                    const bool up = lane & (ROWS / 4);
-#pragma unroll
-                    for (int i = 0; i < 2; i++) {
-                        const uint32_t send = up ? v4[i] : v4[2 + i], keep = up ? v4[2 + i] : v4[i];
-                        v2[i] = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 4);
-                    }
-                }
-                {
-                    const bool     up   = lane & (ROWS / 8);
-                    const uint32_t send = up ? v2[0] : v2[1], keep = up ? v2[1] : v2[0];
-                    v1 = keep + __shfl_xor_sync(0xffffffffu, send, ROWS / 8);
-                }
-#pragma unroll
-                for (int o = ROWS / 16; o; o >>= 1) v1 += __shfl_xor_sync(0xffffffffu, v1, o);
-                if (yy < ny && own < wx && (lane & (ROWS / 8 - 1)) == 0) {
-                    const unsigned long long key = ((unsigned long long)v1 << 32) | ((uint32_t)(y0 + yy) << 16) | (uint32_t)(x0 + own);
-                    best = key < best ? key : best;
-                }
+            switch (wo) {
+            case 0: rows_unit<NW, ROWS, FULLW, 0>(sreg, win, lane, rows, nw_eff, a, x0, y0, wx, ny, best); break;
+            case 1: rows_unit<NW, ROWS, FULLW, 1>(sreg, win, lane, rows, nw_eff, a, x0, y0, wx, ny, best); break;
+            case 2: rows_unit<NW, ROWS, FULLW, 2>(sreg, win, lane, rows, nw_eff, a, x0, y0, wx, ny, best); break;
+            default: rows_unit<NW, ROWS, FULLW, 3>(sreg, win, lane, rows, nw_eff, a, x0, y0, wx, ny, best); break;
             }
         }
     }
@@ -519,17 +536,23 @@ template <int NW, int ROWS>
 __global__ void __launch_bounds__(kStThreads, 6) st_sad_rows_kernel(const __grid_constant__ MeParams p, int lvl) {
     using C = RowsCfg<NW, ROWS>;
     constexpr int kBlkPitch = 17;  // odd: lane = row reads are conflict free
-    __shared__ uint32_t              blk[ROWS * kBlkPitch];
-    __shared__ uint32_t              win[kStWarps][C::kWinW];
-    __shared__ __align__(16) SadJob  jobs[kMaxSadJobs];
+    __shared__ uint32_t                    blk[ROWS * kBlkPitch];
+    __shared__ __align__(16) uint32_t      win[kStWarps][C::kWinW];
+    __shared__ __align__(16) SadJob        jobs[kMaxSadJobs];
     SbState  &s = p.states[blockIdx.x];
-    const int n = s.n_sad;
-    if (n == 0) return;
     {
+        // the whole job table is fetched together with the job count (one memory round trip instead of two)
+        constexpr int kWords = kMaxSadJobs * (int)sizeof(SadJob) / 8;
+        static_assert(kWords <= 2 * kStThreads, "two 64-bit words per thread");
         const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.sad_jobs[0]);
         unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
-        for (int i = threadIdx.x; i < n * (int)(sizeof(SadJob) / 8); i += blockDim.x) dst[i] = src[i];
+        const int                 i0 = threadIdx.x, i1 = threadIdx.x + kStThreads;
+        const unsigned long long  v0 = src[i0], v1 = i1 < kWords ? src[i1] : 0ull;
+        if (s.n_sad == 0) return;
+        dst[i0] = v0;
+        if (i1 < kWords) dst[i1] = v1;
     }
+    const int n = s.n_sad;
     // block geometry as in make_sad_job (me_control.cuh)
     const DevPlane &cp = p.cur.lvl[lvl];
     const uint32_t  aw = (uint32_t)((p.cur.lvl[0].width + 7) & ~7), ah = (uint32_t)((p.cur.lvl[0].height + 7) & ~7);
@@ -548,14 +571,14 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad_rows_kernel(const __grid
     uint32_t  sreg[NW];
 #pragma unroll
     for (int c = 0; c < NW; c++) sreg[c] = blk[(lane & (ROWS - 1)) * kBlkPitch + c];
-    unsigned long long px = 0;
+    uint32_t px = 0;
     for (int ji = warp; ji < n; ji += kStWarps) {
         const SadJob &j = jobs[ji];
         if (j.sa_w > 0 && j.sa_h > 0) px += (uint32_t)(j.sa_w * j.sa_h) * (uint32_t)(rows * bw);
         if (nw_eff == NW) rows_job<NW, ROWS, true>(j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff);
         else rows_job<NW, ROWS, false>(j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff);
     }
-    if (lane == 0 && px) atomicAdd(&s.px, px);
+    if (lane == 0 && px) atomicAdd(&s.px, (unsigned long long)px);
 }
 
 // `lvl`: plane of this phase (2 sixteenth: pre-HME / level 0, 1 quarter: level 1, 0 full: level 2).  The source block is
