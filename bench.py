@@ -120,17 +120,28 @@ def run_step_device(dev, wl, d_luma, inflight):
 
 
 def run_step_host(dev, wl, h_luma, outs, inflight):
-    """End-to-end step through the C ABI with host buffers: H2D of each luma plane, D2H of each picture's results."""
+    """End-to-end step through the C ABI with host buffers: H2D of each luma plane, D2H of each picture's results.
+    Pictures are registered (uploaded + decimated, asynchronously) in the order the searches need them, so the uploads
+    of later pictures overlap the searches of earlier ones; every picture of the step is uploaded exactly once."""
     w, h = wl.w, wl.h
     base = h_luma.data_ptr()
-    pics = {i: dev.register_ptr(base + i * w * h, w, w, h, i) for i in range(wl.n_frames)}
+    pics = {}
+
+    def pic(i):
+        if i not in pics:
+            pics[i] = dev.register_ptr(base + i * w * h, w, w, h, i)
+        return pics[i]
+
     pending = []
     for n, (poc, k, l0, l1) in enumerate(wl.pics):
-        refs = {(0, i): pics[p] for i, p in enumerate(l0)}
-        refs.update({(1, i): pics[p] for i, p in enumerate(l1)})
+        refs = {(0, i): pic(p) for i, p in enumerate(l0)}
+        refs.update({(1, i): pic(p) for i, p in enumerate(l1)})
+        cur = pic(poc)
         if len(pending) >= inflight:
             dev.wait(pending.pop(0))
-        pending.append(dev.search_async(k, pics[poc], refs, out=outs[n])[0])
+        pending.append(dev.search_async(k, cur, refs, out=outs[n])[0])
+    for i in range(wl.n_frames):  # a picture no search touched (none in a closed mini-GOP) still counts as uploaded
+        pic(i)
     for t in pending:
         dev.wait(t)
     for p in pics.values():
@@ -259,6 +270,17 @@ def main():
     clocks = sampler.stop()
     step_host()
     _, ms_host = timed(step_host, args.steps)
+    # context for the end-to-end number: what the host link alone sustains for one step's uploads (pinned -> HBM)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    scratch = torch.empty_like(d_luma)
+    scratch.copy_(h_luma, non_blocking=True)
+    torch.cuda.synchronize()
+    e0.record()
+    scratch.copy_(h_luma, non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize()
+    h2d_only_ms = e0.elapsed_time(e1)
+    del scratch
 
     # per-launch view: one picture's search at a time, CUDA events on its stream around it (svtme_search_elapsed_ms)
     px_total, ms_total, n_launch = 0, 0.0, 0
@@ -310,7 +332,8 @@ def main():
             "config": {"workload": wl.name, "pictures_per_step_per_gpu": wl.gop, "parallelism": "pictures sharded by mini-GOP, %d rank(s)" % world,
                        "l2": "inputs larger than L2 (%.0f MB of planes per step)" % (nf * w * h * 1.55 / 1e6), "inflight": args.inflight},
             "e2e": {"value": e2e, "unit": "pictures/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_host / args.steps},
+                    "ms_per_step": ms_host / args.steps, "h2d_copy_alone_ms_per_step": h2d_only_ms,
+                    "h2d_link_gbs": h2d / h2d_only_ms / 1e6},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline}
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"], _ = reference_arm(wl, args.cpu_sample, 1, 0)

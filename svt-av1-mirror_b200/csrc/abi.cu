@@ -72,6 +72,7 @@ struct Inflight {
     ResultLayout        lay{};
     SvtMePictureResults user{};
     bool                to_host = false, busy = false;
+    bool                direct[32] = {};  // result array i went straight into the caller's (page-locked) buffer
     uint64_t            ticket = 0;
     float               ms = 0.f;
     unsigned long long *h_px = nullptr;  // pinned
@@ -300,7 +301,24 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     sl->to_host = out != nullptr;
     if (out) {
         sl->user = *out;
-        if (e == cudaSuccess) e = cudaMemcpyAsync(sl->h_res, sl->d_res, L.total, cudaMemcpyDeviceToHost, st);
+        // Large arrays whose destination is page-locked host memory are copied straight into it; the rest goes
+        // through the slot's pinned arena (one copy of the covering range) and is scattered by svtme_search_wait.
+        void *dst[R_N] = {out->me_mv, out->me_cand, out->total_me_candidate_index, out->me_64x64_distortion, out->me_32x32_distortion,
+                          out->me_16x16_distortion, out->me_8x8_distortion, out->me_8x8_cost_variance, out->rc_me_distortion,
+                          out->stationary_block_present_sb, out->rc_me_allow_gm, out->sb_best_sad, out->sb_best_mv, out->do_ref, out->hme_sc};
+        size_t lo = L.total, hi = 0;
+        for (int i = 0; i < R_N && e == cudaSuccess; i++) {
+            sl->direct[i] = false;
+            if (!dst[i] || !L.bytes[i]) continue;
+            if (L.bytes[i] >= (64u << 10)) {
+                cudaPointerAttributes pa;
+                if (cudaPointerGetAttributes(&pa, dst[i]) == cudaSuccess && pa.type == cudaMemoryTypeHost) sl->direct[i] = true;
+                else (void)cudaGetLastError();
+            }
+            if (sl->direct[i]) e = cudaMemcpyAsync(dst[i], sl->d_res + L.off[i], L.bytes[i], cudaMemcpyDeviceToHost, st);
+            else { lo = std::min(lo, L.off[i]); hi = std::max(hi, L.off[i] + L.bytes[i]); }
+        }
+        if (e == cudaSuccess && hi > lo) e = cudaMemcpyAsync(sl->h_res + lo, sl->d_res + lo, hi - lo, cudaMemcpyDeviceToHost, st);
     }
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_done, st);
     // the planes must outlive this search
@@ -509,7 +527,7 @@ int32_t svtme_search_wait(SvtMeHandle *h, uint64_t ticket) {
                           u.me_16x16_distortion, u.me_8x8_distortion, u.me_8x8_cost_variance, u.rc_me_distortion,
                           u.stationary_block_present_sb, u.rc_me_allow_gm, u.sb_best_sad, u.sb_best_mv, u.do_ref, u.hme_sc};
         for (int i = 0; i < R_N; i++)
-            if (dst[i] && L.bytes[i]) memcpy(dst[i], sl->h_res + L.off[i], L.bytes[i]);
+            if (dst[i] && L.bytes[i] && !sl->direct[i]) memcpy(dst[i], sl->h_res + L.off[i], L.bytes[i]);
     }
     std::lock_guard<std::mutex> lk(h->mu);
     h->last_ms = sl->ms;
