@@ -727,7 +727,7 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
             const int P = 4 * chunks, nyp = (ny + 3) & ~3, PR = ((nyp + 14 + 1) >> 1) + 1;
             u.job = (int16_t)ji; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
             u.a = (int16_t)a; u.wo = (int16_t)wo; u.chunks = (int16_t)chunks; u.ngroups = (int16_t)ngroups; u.P = (int16_t)P;
-            u.plane_words = ((PR * P + 15) & ~31) + 16;  // = 16 mod 32
+            u.plane_words = ((PR * P + 27) & ~31) + 4;   // = 4 mod 32: rows k (8 banks apart) of the two planes interleave
             u.hsel  = j.skip_line ? 1 : 0;
             u.items = (nyp >> 2) * (j.skip_line ? 1 : 2) * ngroups;
             u.inv_ng = __fdividef(1.0f, (float)ngroups) * 1.0000001f; u.inv_nx = __fdividef(1.0f, (float)nx) * 1.0000001f;
