@@ -30,6 +30,25 @@ __device__ unsigned long long g_phase[2][12];
 #define PH(k, i)
 #endif
 
+// -DSVTME_BOUNDS: every staged copy checks that its source bytes lie inside the reference plane's allocation
+// (physical padding 96 / 48 / 32 + 256 bytes of slack, csrc/abi.cu plane_geometry); a violation prints and traps.
+#ifdef SVTME_BOUNDS
+__device__ __forceinline__ void check_src(const MeParams &p, int lvl, int li, int ri, const uint8_t *g, int bytes, int site) {
+    const DevPlane &pl = p.refs[li][ri].lvl[lvl];
+    const int       pad = lvl == 0 ? 96 : lvl == 1 ? 48 : 32;
+    const uint8_t  *lo = pl.org - (int64_t)pad * pl.stride - pad;
+    const uint8_t  *hi = lo + (int64_t)pl.stride * (pl.height + 2 * pad) + 256;
+    if (g < lo || g + bytes > hi) {
+        printf("svtme bounds: site %d lvl %d ref %d/%d: %lld bytes before / %lld past the plane\n", site, lvl, li, ri,
+               (long long)(lo - g), (long long)(g + bytes - hi));
+        __trap();
+    }
+}
+#define CHECK_SRC(p, lvl, li, ri, g, bytes, site) check_src(p, lvl, li, ri, reinterpret_cast<const uint8_t *>(g), bytes, site)
+#else
+#define CHECK_SRC(p, lvl, li, ri, g, bytes, site)
+#endif
+
 constexpr int kStThreads  = 128;             // 4 warps per block CTA
 constexpr int kStWarps    = kStThreads / 32;
 constexpr int kSadWarpWin = 8 * 1024;        // HME window bytes per warp
@@ -485,8 +504,8 @@ __device__ __forceinline__ void rows_unit(const uint32_t (&sreg)[NW], const uint
 }
 
 template <int NW, int ROWS, bool FULLW>
-__device__ __forceinline__ void rows_job(const SadJob &j, SadJob &jout, const uint32_t (&sreg)[NW], uint32_t *win, int lane,
-                                         int rows, int nw_eff) {
+__device__ __forceinline__ void rows_job(const MeParams &p, int lvl, const SadJob &j, SadJob &jout, const uint32_t (&sreg)[NW],
+                                         uint32_t *win, int lane, int rows, int nw_eff) {
     using C = RowsCfg<NW, ROWS>;
     const int W = j.sa_w, H = j.sa_h;
     if (W <= 0 || H <= 0) return;
@@ -507,9 +526,11 @@ __device__ __forceinline__ void rows_job(const SadJob &j, SadJob &jout, const ui
             // (96 / 48 rows against the 72 / 32 the search may touch), and the copy loop unrolls to immediates
             if (lc < C::kChunks) {
 #pragma unroll
-                for (int G = 0; G < C::kRowsPad / C::kRpi; G++)
+                for (int G = 0; G < C::kRowsPad / C::kRpi; G++) {
+                    CHECK_SRC(p, lvl, j.li, j.ri, g0 + (uint64_t)(uint32_t)(G * C::kRpi + lr) * (uint64_t)raw, 16, 1);
                     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sbase + sofs + (uint32_t)(G * (C::kRpi / 2) * C::kS * 4)),
                                  "l"(g0 + (uint64_t)(uint32_t)(G * C::kRpi + lr) * (uint64_t)raw));
+                }
             }
             asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
             __syncwarp();
@@ -575,8 +596,8 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad_rows_kernel(const __grid
     for (int ji = warp; ji < n; ji += kStWarps) {
         const SadJob &j = jobs[ji];
         if (j.sa_w > 0 && j.sa_h > 0) px += (uint32_t)(j.sa_w * j.sa_h) * (uint32_t)(rows * bw);
-        if (nw_eff == NW) rows_job<NW, ROWS, true>(j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff);
-        else rows_job<NW, ROWS, false>(j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff);
+        if (nw_eff == NW) rows_job<NW, ROWS, true>(p, lvl, j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff);
+        else rows_job<NW, ROWS, false>(p, lvl, j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff);
     }
     if (lane == 0 && px) atomicAdd(&s.px, (unsigned long long)px);
 }
@@ -854,9 +875,11 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
                 if (rpi >= 2) {  // the parity of the lane's rows is fixed
                     const uint32_t sa0 = w0 + (uint32_t)(lr & 1) * pw;
 #pragma unroll 4
-                    for (int R = lr; R < nrows; R += rpi)
+                    for (int R = lr; R < nrows; R += rpi) {
+                        CHECK_SRC(p, 2, j.li, j.ri, g0 + (uint64_t)(uint32_t)R * (uint64_t)raw, 16, 2);
                         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa0 + (uint32_t)(R >> 1) * P4),
                                      "l"(g0 + (uint64_t)(uint32_t)R * (uint64_t)raw));
+                    }
                 } else {
 #pragma unroll 4
                     for (int R = 0; R < nrows; R++)
@@ -1336,6 +1359,8 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
                 uint32_t       sa = pbase + 4u * (uint32_t)wd;
                 for (int G = 0; G < ngrp; G++, g += 8 * (int64_t)raw, sa += 4u * P4 + ((G & 1) ? 0u : 4u)) {
                     // rows warp + 8G and warp + 8G + 4: plane rows i = (warp >> 1) + 4G + {0, 2}, skew i >> 3 = G >> 1
+                    CHECK_SRC(p, 0, j.li, j.ri, g, 4, 3);
+                    CHECK_SRC(p, 0, j.li, j.ri, g + 4 * (int64_t)raw, 4, 3);
                     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(g));
                     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa + 2u * P4), "l"(g + 4 * (int64_t)raw));
                 }
