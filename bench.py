@@ -49,12 +49,13 @@ def parse():
 class Workload:
     """A synthetic 8-bit clip of one mini-GOP (+ its leading base picture) and its prediction structure."""
 
-    def __init__(self, args, seed):
+    def __init__(self, args, seed, minigop=0):
         from svtme import api, synth
         self.w, self.h, self.hl = args.width, args.height, args.hier_levels
         self.gop = 1 << self.hl
         self.n_frames = self.gop + 1
-        self.frames = synth.make_clip(self.w, self.h, self.n_frames, seed=seed, kind="pan")
+        # mini-GOP `minigop` of the clip: its 2^levels pictures plus the leading base picture it shares with its predecessor
+        self.frames = synth.make_clip(self.w, self.h, self.n_frames, seed=seed, kind="pan", first=minigop * self.gop)
         k0 = api.derive_knobs(enc_mode=args.preset, qp=35, frame_rate_q16=60 * Q16, width=self.w, height=self.h,
                               hierarchical_levels=self.hl, picture_number=1, temporal_layer_index=1, is_ref=1, slice_type_b=1)
         self.pics = []  # decode order
@@ -102,10 +103,13 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def run_step_device(dev, wl, d_luma, inflight):
-    """Device-resident step: register every picture from HBM-resident luma, search in decode order, results stay in HBM."""
+def run_step_device(dev, wl, d_luma, inflight, handoff=None):
+    """Device-resident step: register every picture from HBM-resident luma, search in decode order, results stay in HBM.
+    With several ranks the leading base picture first arrives from the previous rank (handoff)."""
     w, h = wl.w, wl.h
-    pics = {i: dev.register_device(d_luma.data_ptr() + i * w * h, w, w, h, i) for i in range(wl.n_frames)}
+    first = handoff() if handoff else None
+    pics = {i: dev.register_device((first if (i == 0 and first) else d_luma.data_ptr() + i * w * h), w, w, h, i)
+            for i in range(wl.n_frames)}
     pending = []
     for poc, k, l0, l1 in wl.pics:
         refs = {(0, i): pics[p] for i, p in enumerate(l0)}
@@ -119,13 +123,16 @@ def run_step_device(dev, wl, d_luma, inflight):
         p.release()
 
 
-def run_step_host(dev, wl, h_luma, outs, inflight):
+def run_step_host(dev, wl, h_luma, outs, inflight, handoff=None):
     """End-to-end step through the C ABI with host buffers: H2D of each luma plane, D2H of each picture's results.
     Pictures are registered (uploaded + decimated, asynchronously) in the order the searches need them, so the uploads
     of later pictures overlap the searches of earlier ones; every picture of the step is uploaded exactly once."""
     w, h = wl.w, wl.h
     base = h_luma.data_ptr()
     pics = {}
+    first = handoff() if handoff else None  # the shared base picture comes over NVLink, not over the host link
+    if first:
+        pics[0] = dev.register_device(first, w, w, h, 0)
 
     def pic(i):
         if i not in pics:
@@ -219,7 +226,7 @@ def main():
 
     # weak scaling: one mini-GOP per rank and step; rank r owns mini-GOP r of the job (svtme/shard.py), its own clip
     my_gops = list(shard.shard_minigops(world, rank, world))
-    wl = Workload(args, seed=100 + my_gops[0])
+    wl = Workload(args, seed=100, minigop=my_gops[0])
     dev = api.MeDevice(device=local_rank, max_inflight=args.inflight, max_pictures=2 * wl.n_frames)
     w, h, nf = wl.w, wl.h, wl.n_frames
     h_luma = torch.empty((nf, h, w), dtype=torch.uint8).pin_memory()
@@ -257,8 +264,22 @@ def main():
         # whole job: SUM of the pictures of all ranks, MAX of their device times (svtme/shard.py)
         return shard.reduce_job(wl.gop * steps, ms, dist, device="cuda")
 
-    step_dev = lambda: run_step_device(dev, wl, d_luma, args.inflight)  # noqa: E731
-    step_host = lambda: run_step_host(dev, wl, h_luma, outs, args.inflight)  # noqa: E731
+    # the picture consecutive mini-GOPs share (last of rank r = leading base picture of rank r + 1) moves GPU to GPU
+    # every step: NCCL point-to-point over NVLink; the receiver decimates it locally
+    d_recv = torch.empty((h, w), dtype=torch.uint8, device="cuda") if world > 1 else None
+
+    def handoff():
+        got = shard.handoff_boundary(dist, d_luma[nf - 1], d_recv)
+        torch.cuda.current_stream().synchronize()  # the library's upload streams read the buffer next
+        return d_recv.data_ptr() if got else None
+
+    hand = handoff if world > 1 else None
+    step_dev = lambda: run_step_device(dev, wl, d_luma, args.inflight, hand)  # noqa: E731
+    step_host = lambda: run_step_host(dev, wl, h_luma, outs, args.inflight, hand)  # noqa: E731
+    if world > 1:
+        handoff()
+        if rank > 0 and not torch.equal(d_recv, d_luma[0]):
+            raise SystemExit("rank %d: the base picture received from rank %d differs from the clip's" % (rank, rank - 1))
 
     for _ in range(max(3, args.warmup)):
         step_dev()
@@ -329,7 +350,8 @@ def main():
     line = {"metric": "ME pictures/sec at 4K", "value": value, "unit": "pictures/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": wl.name, "pictures_per_step_per_gpu": wl.gop, "parallelism": "pictures sharded by mini-GOP, %d rank(s)" % world,
+            "config": {"workload": wl.name, "pictures_per_step_per_gpu": wl.gop, "parallelism": "pictures sharded by mini-GOP, %d rank(s)%s" % (
+                           world, "; shared base picture handed rank r -> r+1 by NCCL p2p every step (verified equal)" if world > 1 else ""),
                        "l2": "inputs larger than L2 (%.0f MB of planes per step)" % (nf * w * h * 1.55 / 1e6), "inflight": args.inflight},
             "e2e": {"value": e2e, "unit": "pictures/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_host / args.steps, "h2d_copy_alone_ms_per_step": h2d_only_ms,

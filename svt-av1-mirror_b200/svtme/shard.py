@@ -23,6 +23,24 @@ def pictures_of(minigops, gop_size):
     return sorted(pics)
 
 
+def handoff_boundary(dist, last_picture, recv_buf):
+    """The one picture consecutive mini-GOPs share: the last (base-layer) picture of mini-GOP g is the leading
+    reference of mini-GOP g + 1.  Rank r sends the luma of its last picture to rank r + 1 and receives rank r - 1's into
+    `recv_buf` (point-to-point: NVLink under NCCL); the receiver decimates locally -- cheaper than moving the 1.33x
+    planes.  Returns True when `recv_buf` was filled (every rank but 0)."""
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return False
+    rank, world = dist.get_rank(), dist.get_world_size()
+    ops = []
+    if rank + 1 < world:
+        ops.append(dist.P2POp(dist.isend, last_picture, rank + 1))
+    if rank > 0:
+        ops.append(dist.P2POp(dist.irecv, recv_buf, rank - 1))
+    for r in dist.batch_isend_irecv(ops):  # one NCCL group: all pairs move at once, no chain of blocking sends
+        r.wait()
+    return rank > 0
+
+
 def reduce_job(pictures_local, ms_local, dist=None, device="cpu"):
     """Whole-job numbers from per-rank ones: (sum of pictures, max of milliseconds)."""
     if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:

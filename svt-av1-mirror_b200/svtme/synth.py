@@ -21,8 +21,11 @@ def _smooth_canvas(rng, h, w):
     return np.clip(img, 0, 255).astype(np.uint8)
 
 
-def make_clip(width, height, n_frames, seed=0, kind="pan", max_mv=48, n_patches=16):
-    """Returns a list of (height, width) uint8 arrays."""
+def make_clip(width, height, n_frames, seed=0, kind="pan", max_mv=48, n_patches=16, first=0):
+    """Returns a list of (height, width) uint8 arrays: frames first .. first + n_frames - 1 of the clip `seed`
+    (a clip is one deterministic sequence; `first` lets every rank of a multi-GPU job cut its own mini-GOPs out of it)."""
+    if first:
+        return make_clip(width, height, first + n_frames, seed, kind, max_mv, n_patches)[first:]
     rng = np.random.default_rng(seed)
     if kind == "zero":
         return [np.zeros((height, width), np.uint8) for _ in range(n_frames)]

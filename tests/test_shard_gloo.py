@@ -13,7 +13,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 import helpers as H
-from svtme import api, shard
+from svtme import api, shard, synth
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 W, HH, GOP, NGOP = 128, 128, 2, 3
@@ -50,6 +50,14 @@ def _worker(rank, world, port, outdir):
         res = _search_minigops(refbind.Oracle(), mine)
         assert set(res).issubset(set(need))
         dist.barrier()
+        # the picture consecutive mini-GOPs share travels rank r -> r + 1
+        frames = synth.make_clip(W, HH, len(mine) * GOP + 1, seed=5, kind="pan", first=mine[0] * GOP)
+        last = torch.from_numpy(np.ascontiguousarray(frames[-1]))
+        recv = torch.zeros_like(last)
+        got = shard.handoff_boundary(dist, last, recv)
+        assert got == (rank > 0)
+        if got:
+            assert torch.equal(recv, torch.from_numpy(np.ascontiguousarray(frames[0]))), "handed-over picture differs"
         pictures, ms = shard.reduce_job(len(res), 10.0 * (rank + 1), dist)
         with open(os.path.join(outdir, "rank%d.pkl" % rank), "wb") as f:
             pickle.dump({"gops": list(mine), "res": res, "pictures": pictures, "ms": ms}, f)
