@@ -344,6 +344,11 @@ def main():
                 "frac": ach / sad_peak, "traffic": traffic,
                 "peak_source": "VABSDIFF4.U8.ACC issue rate measured in this run (svtme_measure_sad_peak) x 4 px",
                 "px_compares_per_launch": px_total / n_launch, "avg_launch_ms": ms_total / n_launch,
+                "launch": "one picture's search (~21 stream-ordered kernels), launched alone",
+                # the same work over the timed (pipelined, 8 searches in flight) region, per GPU: grid tails of one picture's
+                # kernels are filled by the next picture's
+                "achieved_pipelined": (px_total / n_launch) * (value / world) / 1e12,
+                "frac_pipelined": (px_total / n_launch) * (value / world) / 1e12 / sad_peak,
                 "hbm": {"achieved": alg_bytes / (ms_total / n_launch * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": alg_bytes / (ms_total / n_launch * 1e-3) / 1e9 / hbm_peak, "algorithmic_bytes_per_launch": alg_bytes,
                         "peak_source": hbm_src}}
