@@ -41,7 +41,8 @@ def parse():
     ap.add_argument("--preset", type=int, default=6)
     ap.add_argument("--hier-levels", type=int, default=5, help="mini-GOP = 2^levels pictures")
     ap.add_argument("--inflight", type=int, default=8, help="searches in flight (one stream each)")
-    ap.add_argument("--cpu-sample", type=int, default=3, help="pictures of the workload timed on the host cores")
+    ap.add_argument("--cpu-sample", type=int, default=32, help="pictures of the workload timed on the host cores per step")
+    ap.add_argument("--cpu-seconds", type=float, default=8.0, help="CPU-baseline budget of the default run (about this much work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -155,9 +156,10 @@ def run_step_host(dev, wl, h_luma, outs, inflight, handoff=None):
         p.release()
 
 
-def reference_arm(wl, n_pictures, steps, warmup):
+def reference_arm(wl, n_pictures, steps, warmup, seconds=None):
     """The reference's own CPU ME (oracle/_ref/libsvtref.so: its unmodified C sources + AVX2 twins) on the host cores.
-    One step = decimation + ME of `n_pictures` pictures of the workload (spread over the temporal layers)."""
+    One step = decimation + ME of `n_pictures` pictures of the workload (all of the mini-GOP by default, else spread
+    over the temporal layers).  With `seconds` the steps repeat until about that much time has been spent."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import refbind
     kind = "reference"
@@ -186,12 +188,16 @@ def reference_arm(wl, n_pictures, steps, warmup):
     for _ in range(warmup):
         step()
     t0 = time.perf_counter()
-    for _ in range(steps):
+    done = 0
+    while done < steps or (seconds is not None and time.perf_counter() - t0 < seconds):
         step()
+        done += 1
+    steps = done
     dt = time.perf_counter() - t0
     pps = len(sample) * steps / dt
     return {"value": pps, "unit": "pictures/s", "cores": cores, "kind": kind,
-            "sample": "%d pictures (decode-order %s) of the workload x %d steps, %s, %d threads" % (len(sample), idx, steps, what, cores)}, dt
+            "sample": "%d pictures (decode-order %s) of the workload x %d steps = %.1f s, %s, %d threads" % (
+                len(sample), "all" if len(sample) == len(wl.pics) else idx, steps, dt, what, cores)}, dt
 
 
 def main():
@@ -204,7 +210,7 @@ def main():
         if rank != 0:
             return 0
         wl = Workload(args, seed=100)
-        steps, warmup = max(1, min(args.steps, 3)), min(args.warmup, 1)
+        steps, warmup = max(1, min(args.steps, 40)), min(args.warmup, 2)  # a step = the whole mini-GOP, ~0.2 s on 16 cores
         cb, dt = reference_arm(wl, args.cpu_sample, steps, warmup)
         line = {"impl": "reference", "metric": "ME pictures/sec at 4K", "value": cb["value"], "unit": "pictures/s",
                 "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True,
@@ -363,7 +369,7 @@ def main():
                     "h2d_link_gbs": h2d / h2d_only_ms / 1e6},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline}
     if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"], _ = reference_arm(wl, args.cpu_sample, 1, 0)
+        line["cpu_baseline"], _ = reference_arm(wl, args.cpu_sample, 1, 1, seconds=args.cpu_seconds)
     print(json.dumps(line))
     dev.close()
     if dist is not None:
