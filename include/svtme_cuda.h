@@ -62,6 +62,11 @@ typedef struct SvtMeAreaMinMax {
  * The encoder keeps deriving these on the CPU exactly as today; the shim only
  * copies them out of MeContext/pcs.
  */
+/* SvtMeKnobs.me_type.  0 keeps a zero-initialised knob block on the open-loop path; the shim maps
+ * EbMeType (me_context.h:45-50) ME_OPEN_LOOP(3) -> 0 (me_process.c:216) and ME_MCTF(1) -> 1 (temporal_filtering.c:296). */
+#define SVTME_ME_OPEN_LOOP 0
+#define SVTME_ME_MCTF      1
+
 typedef struct SvtMeKnobs {
     /* (c) pcs / scs fields */
     uint64_t picture_number;          /* pcs->picture_number */
@@ -136,6 +141,10 @@ typedef struct SvtMeKnobs {
     uint32_t me_early_exit_th;
     uint32_t me_safe_limit_zz_th;
     uint32_t prev_me_stage_based_exit_th;
+    /* temporal-filter mode (SVTME_ME_MCTF): the caller is produce_temporally_filtered_pic
+     * (temporal_filtering.c:3129-3174); one list, one reference = the neighbouring picture of the window */
+    uint8_t  me_type;                 /* SVTME_ME_OPEN_LOOP / SVTME_ME_MCTF, MeContext.me_type (me_context.h EbMeType) */
+    uint32_t tf_me_exit_th;           /* MeContext.tf_me_exit_th = pcs->tf_ctrls.me_exit_th (temporal_filtering.c:3158) */
 } SvtMeKnobs;
 
 /*
@@ -194,6 +203,12 @@ typedef struct SvtMePictureResults {
     uint32_t *sb_best_mv;                  /* [b64][2][4][85] p_sb_best_mv */
     uint8_t  *do_ref;                      /* [b64][2][4]  search_results[l][r].do_ref after me_prune_ref */
     int16_t  *hme_sc;                      /* [b64][2][4][2] search_results[l][r].hme_sc_x / hme_sc_y */
+    /* Optional, temporal-filter mode only (NULL otherwise).  In that mode the outputs the filter consumes are
+     * sb_best_mv / sb_best_sad of [0][0] (p_best_mv64x64 .. 16x16, temporal_filtering.c:1866-2114, 2685),
+     * hme_sc of [0][0], and these two: */
+    uint8_t  *tf_exit_sb;                  /* [b64] 1: search_results[0][0].hme_sad < tf_me_exit_th, the integer search
+                                            * was skipped and tf_use_pred_64x64_only_th = 0xFF (motion_estimation.c:3109) */
+    uint32_t *tf_blk_counts;               /* [2] tf_tot_horz_blks, tf_tot_vert_blks of this picture pair (:2469-2474) */
 } SvtMePictureResults;
 
 typedef struct SvtMeDeviceCfg {
@@ -220,6 +235,30 @@ void    svtme_destroy(SvtMeHandle *h);
  * HME flags (:1608-1619), enable_me_8x8 (:76-96), gm level (:103-129, 1821-1903),
  * mrp controls (enc_handle.c:3347-3640, 4141-4176), max_cand/max_refs (pcs.c:91-96). Pure host code. */
 int32_t svtme_derive_knobs(const SvtMePresetCfg *cfg, SvtMeKnobs *out);
+
+/*
+ * Temporal-filter (alt-ref) motion search: the knobs of one (centre picture, neighbouring picture) pair as
+ * produce_temporally_filtered_pic sets them up before svt_aom_motion_estimation_b64
+ * (temporal_filtering.c:3129-3174): me_type = ME_MCTF (:296), HME always full-SAD (:316), one list / one
+ * reference (:3140-3142), hme_l0_sa = hme_l0_sa_default_tf (set_hme_search_params_mctf level 0, :2759-2767),
+ * tf_me_exit_th = tf_ctrls.me_exit_th (:3158).  The inputs are the TfControls fields the derivation reads
+ * (definitions.h:172-260; per-preset values at enc_handle.c:2560-3160).
+ */
+typedef struct SvtMeTfCfg {
+    uint8_t  hme_me_level;         /* tf_ctrls.hme_me_level 0..4: search areas (enc_mode_config.c:588-653), HME levels (:1620-1643) */
+    uint8_t  qp_opt;               /* tf_ctrls.qp_opt: modulate the ME area by qp (:656-663) */
+    uint32_t me_exit_th;           /* tf_ctrls.me_exit_th */
+    uint32_t qp;                   /* scs->static_config.qp */
+    uint16_t width;                /* luma size: input_resolution class for hme_me_level 2 */
+    uint16_t height;
+    uint64_t picture_number;       /* of the centre picture */
+    uint8_t  temporal_layer_index; /* of the centre picture (temporal_filtering.c:3143-3146) */
+    uint8_t  is_ref;
+} SvtMeTfCfg;
+
+/* Mirror of svt_aom_sig_deriv_me_tf + tf_set_me_hme_params_oq (enc_mode_config.c:588-663, 814-854) and the
+ * per-call overrides listed above.  Pure host code. */
+int32_t svtme_derive_tf_knobs(const SvtMeTfCfg *cfg, SvtMeKnobs *out);
 
 /* Upload one 8-bit luma plane, then build the padded full / quarter / sixteenth
  * planes on the device.  Replaces: copy_frame_buffer's luma memcpy

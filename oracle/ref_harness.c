@@ -183,6 +183,8 @@ static void knobs_from_ctx(SvtMeKnobs *k, const MeContext *c) {
     k->me_early_exit_th            = c->me_early_exit_th;
     k->me_safe_limit_zz_th         = c->me_safe_limit_zz_th;
     k->prev_me_stage_based_exit_th = c->prev_me_stage_based_exit_th;
+    k->me_type                     = c->me_type == ME_MCTF ? SVTME_ME_MCTF : SVTME_ME_OPEN_LOOP;
+    k->tf_me_exit_th               = c->tf_me_exit_th;
 }
 
 static void ctx_from_knobs(MeContext *c, const SvtMeKnobs *k) {
@@ -236,7 +238,8 @@ static void ctx_from_knobs(MeContext *c, const SvtMeKnobs *k) {
     c->me_early_exit_th             = k->me_early_exit_th;
     c->me_safe_limit_zz_th          = k->me_safe_limit_zz_th;
     c->prev_me_stage_based_exit_th  = k->prev_me_stage_based_exit_th;
-    c->me_type                      = ME_OPEN_LOOP; /* me_process.c:216 */
+    c->me_type       = k->me_type == SVTME_ME_MCTF ? ME_MCTF : ME_OPEN_LOOP; /* temporal_filtering.c:296 / me_process.c:216 */
+    c->tf_me_exit_th = k->tf_me_exit_th;
     c->num_of_list_to_search        = k->num_of_list_to_search;
     c->num_of_ref_pic_to_search[0]  = k->num_of_ref_pic_to_search[0];
     c->num_of_ref_pic_to_search[1]  = k->num_of_ref_pic_to_search[1];
@@ -333,6 +336,45 @@ int svtref_derive_knobs(const SvtMePresetCfg *cfg, SvtMeKnobs *k) {
     return 0;
 }
 
+/* Temporal-filter knobs: the reference's own svt_aom_sig_deriv_me_tf on a pcs carrying the given TfControls, then the
+ * per-block overrides of produce_temporally_filtered_pic (temporal_filtering.c:296, 316, 2759-2767, 3140-3158). */
+int svtref_derive_tf_knobs(const SvtMeTfCfg *cfg, SvtMeKnobs *k) {
+    SequenceControlSet      *scs = (SequenceControlSet *)calloc(1, sizeof(*scs));
+    PictureParentControlSet *pcs = (PictureParentControlSet *)calloc(1, sizeof(*pcs));
+    MeContext               *ctx = (MeContext *)calloc(1, sizeof(*ctx));
+    if (!scs || !pcs || !ctx) return -1;
+    memset(k, 0, sizeof(*k));
+    pcs->scs                  = scs;
+    scs->static_config.qp     = cfg->qp;
+    svt_aom_derive_input_resolution(&scs->input_resolution, (uint32_t)cfg->width * cfg->height);
+    pcs->tf_ctrls.hme_me_level = cfg->hme_me_level;
+    pcs->tf_ctrls.qp_opt       = cfg->qp_opt;
+    pcs->tf_ctrls.me_exit_th   = cfg->me_exit_th;
+    /* enc_mode_config.c:1620-1643 (inside svt_aom_sig_deriv_multi_processes, too entangled to call) */
+    pcs->tf_enable_hme_flag        = 1;
+    pcs->tf_enable_hme_level0_flag = 1;
+    pcs->tf_enable_hme_level1_flag = cfg->hme_me_level <= 2;
+    pcs->tf_enable_hme_level2_flag = cfg->hme_me_level == 0;
+    svt_aom_sig_deriv_me_tf(pcs, ctx);
+    ctx->me_type           = ME_MCTF;                  /* temporal_filtering.c:296 */
+    ctx->hme_search_method = FULL_SAD_SEARCH;          /* :316 */
+    ctx->hme_l0_sa         = ctx->hme_l0_sa_default_tf; /* set_hme_search_params_mctf(ctx, 0), :2759-2767 */
+    ctx->tf_me_exit_th     = pcs->tf_ctrls.me_exit_th; /* :3158 */
+    knobs_from_ctx(k, ctx);
+    k->num_of_list_to_search       = 1; /* :3140-3142 */
+    k->num_of_ref_pic_to_search[0] = 1;
+    k->temporal_layer_index        = cfg->temporal_layer_index;
+    k->is_ref                      = cfg->is_ref;
+    k->picture_number              = cfg->picture_number;
+    k->input_resolution            = scs->input_resolution;
+    k->enable_me_8x8 = 1; k->enable_me_16x16 = 1; k->max_number_of_pus_per_sb = SQUARE_PU_COUNT;
+    k->max_cand = 1; k->max_refs = 1; k->max_l0 = 1;
+    free(ctx);
+    free(pcs);
+    free(scs);
+    return 0;
+}
+
 /* ---- picture-level driver: the SB loop of me_process.c:174-290 over the whole picture ---- */
 typedef struct RefJob {
     const SvtMeKnobs        *k;
@@ -397,18 +439,22 @@ static void *ref_worker(void *arg) {
         }
         /* the knob block is re-derived per message in the encoder (me_process.c:121); areas mutated
          * by get_hme_l0_search_area are restored by the reference itself (:1999-2003). */
-        ctx->me_type = ME_OPEN_LOOP;
+        ctx->me_type = k->me_type == SVTME_ME_MCTF ? ME_MCTF : ME_OPEN_LOOP;
+        ctx->tf_use_pred_64x64_only_th = 1; /* any value but 0xFF: the reference overwrites it per block (temporal_filtering.c:3161) */
         /* harness convention (header of svtme_cuda.h): unsearched refs report MAX_SAD_VALUE, unwritten outputs 0 */
         for (int li = 0; li < 2; li++)
             for (int ri = 0; ri < 4; ri++)
                 for (int p = 0; p < SQUARE_PU_COUNT; p++) ctx->p_sb_best_sad[li][ri][p] = MAX_SAD_VALUE;
-        MeSbResults *r = pcs->pa_me_data->me_results[sb];
-        memset(r->me_mv_array, 0, sizeof(MvCandidate) * pus * mr);
-        memset(r->me_candidate_array, 0, sizeof(MeCandidate) * pus * mc);
-        memset(r->total_me_candidate_index, 0, pus);
+        if (k->me_type != SVTME_ME_MCTF) {
+            MeSbResults *r = pcs->pa_me_data->me_results[sb];
+            memset(r->me_mv_array, 0, sizeof(MvCandidate) * pus * mr);
+            memset(r->me_candidate_array, 0, sizeof(MeCandidate) * pus * mc);
+            memset(r->total_me_candidate_index, 0, pus);
+        }
 
         svt_aom_motion_estimation_b64(pcs, sb, x, y, ctx, &cur_d[0]);
 
+        if (out->tf_exit_sb) out->tf_exit_sb[sb] = ctx->tf_use_pred_64x64_only_th == (uint8_t)~0;
         if (out->sb_best_sad) memcpy(out->sb_best_sad + (size_t)sb * 2 * 4 * 85, ctx->p_sb_best_sad, sizeof(uint32_t) * 2 * 4 * 85);
         if (out->sb_best_mv) memcpy(out->sb_best_mv + (size_t)sb * 2 * 4 * 85, ctx->p_sb_best_mv, sizeof(uint32_t) * 2 * 4 * 85);
         for (int li = 0; li < 2; li++)
@@ -420,6 +466,10 @@ static void *ref_worker(void *arg) {
                     out->hme_sc[((size_t)sb * 8 + li * 4 + ri) * 2 + 1] = used ? ctx->search_results[li][ri].hme_sc_y : 0;
                 }
             }
+    }
+    if (out->tf_blk_counts) { /* temporal_filtering.c:4224-4227: per-segment counters summed into the centre pcs */
+        __sync_fetch_and_add(&out->tf_blk_counts[0], ctx->tf_tot_horz_blks);
+        __sync_fetch_and_add(&out->tf_blk_counts[1], ctx->tf_tot_vert_blks);
     }
     free(ctx);
     return NULL;
@@ -477,6 +527,7 @@ int svtref_me_picture(const SvtMeKnobs *k, const SvtRefPic *cur, const SvtRefPic
     pcs->stationary_block_present_sb = out->stationary_block_present_sb;
     pcs->rc_me_allow_gm              = out->rc_me_allow_gm;
 
+    if (out->tf_blk_counts) out->tf_blk_counts[0] = out->tf_blk_counts[1] = 0;
     RefJob job;
     memset(&job, 0, sizeof(job));
     job.k = k; job.cur = cur; job.refs = refs; job.out = out; job.pcs = pcs;

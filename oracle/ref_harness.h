@@ -10,6 +10,7 @@ extern "C" {
 int      svtref_set_isa(int isa); /* 0 = C kernels, 1 = AVX2 twins (if built and supported); returns what was bound */
 int      svtref_get_isa(void);
 int      svtref_derive_knobs(const SvtMePresetCfg *cfg, SvtMeKnobs *out);
+int      svtref_derive_tf_knobs(const SvtMeTfCfg *cfg, SvtMeKnobs *out);
 int      svtref_me_picture(const SvtMeKnobs *k, const SvtRefPic *cur, const SvtRefPic *refs /*[2][4]*/,
                            SvtMePictureResults *out, int n_threads);
 void     svtref_build_planes(const SvtRefPic *pic, int hme_level1);

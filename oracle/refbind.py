@@ -69,6 +69,8 @@ class _Binding:
         self.lib, self.prefix = lib, prefix
         f = self._f
         f("derive_knobs").argtypes = [C.POINTER(abi.PresetCfg), C.POINTER(abi.Knobs)]
+        if hasattr(lib, prefix + "derive_tf_knobs"):
+            f("derive_tf_knobs").argtypes = [C.POINTER(abi.TfCfg), C.POINTER(abi.Knobs)]
         f("me_picture").argtypes = [C.POINTER(abi.Knobs), C.POINTER(RefPic), C.POINTER(RefPic),
                                     C.POINTER(abi.PictureResults), C.c_int]
         f("build_planes").argtypes = [C.POINTER(RefPic), C.c_int]
@@ -99,6 +101,16 @@ class _Binding:
         rc = self._f("derive_knobs")(C.byref(cfg), C.byref(k))
         if rc != 0:
             raise RuntimeError("derive_knobs failed: %d" % rc)
+        return k
+
+    def derive_tf_knobs(self, **kw):
+        cfg = abi.TfCfg()
+        for k, v in kw.items():
+            setattr(cfg, k, v)
+        k = abi.Knobs()
+        rc = self._f("derive_tf_knobs")(C.byref(cfg), C.byref(k))
+        if rc != 0:
+            raise RuntimeError("derive_tf_knobs failed: %d" % rc)
         return k
 
     def build_planes(self, pic, hme_level1=1):

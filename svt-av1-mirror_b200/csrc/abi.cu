@@ -55,11 +55,11 @@ struct SvtMePic {
 namespace {
 
 struct ResultLayout {
-    size_t   off[15];
-    size_t   bytes[15];
+    size_t   off[17];
+    size_t   bytes[17];
     size_t   total;
 };
-enum { R_MV, R_CAND, R_COUNT, R_D64, R_D32, R_D16, R_D8, R_VAR, R_RC, R_STAT, R_GM, R_SAD, R_BMV, R_DOREF, R_HMESC, R_N };
+enum { R_MV, R_CAND, R_COUNT, R_D64, R_D32, R_D16, R_D8, R_VAR, R_RC, R_STAT, R_GM, R_SAD, R_BMV, R_DOREF, R_HMESC, R_TFEXIT, R_TFCNT, R_N };
 
 struct Inflight {
     cudaStream_t        stream = nullptr;
@@ -196,7 +196,12 @@ void result_layout(uint32_t n_b64, uint32_t pu_count, const SvtMeKnobs &k, bool 
     const size_t n = n_b64;
     size_t sz[R_N] = {n * pu_count * k.max_refs * 4, n * pu_count * k.max_cand, n * pu_count, n * 4, n * 4, n * 4, n * 4,
                       n * 4, n * 4, n, n, extended ? n * 680 * 4 : 0, extended ? n * 680 * 4 : 0, extended ? n * 8 : 0,
-                      extended ? n * 16 * 2 : 0};
+                      extended ? n * 16 * 2 : 0, 0, 0};
+    if (k.me_type == SVTME_ME_MCTF) {
+        // the temporal filter reads no candidates or statistics (motion_estimation.c:3126): only MVs / SADs / centres
+        for (int i = R_MV; i <= R_GM; i++) sz[i] = 0;
+        sz[R_TFEXIT] = n; sz[R_TFCNT] = 8;
+    }
     size_t off = 0;
     for (int i = 0; i < R_N; i++) {
         L->off[i] = off; L->bytes[i] = sz[i];
@@ -214,6 +219,12 @@ int validate_knobs(SvtMeHandle *h, const SvtMeKnobs *k, uint32_t pu_count) {
     if (k->max_number_of_pus_per_sb != SVTME_SQUARE_PU_COUNT) return fail(h, SVTME_ERR_BAD_PARAMETER, "max_number_of_pus_per_sb must be 85");
     const uint32_t want = k->enable_me_16x16 ? (k->enable_me_8x8 ? 85u : 21u) : 5u;
     if (pu_count != want) return fail(h, SVTME_ERR_BAD_PARAMETER, "pu_count does not match enable_me_8x8/16x16");
+    if (k->me_type == SVTME_ME_MCTF) {  // one neighbouring picture per call, no candidate arrays (temporal_filtering.c:3140-3142)
+        if (k->num_of_list_to_search != 1 || k->num_of_ref_pic_to_search[0] != 1)
+            return fail(h, SVTME_ERR_BAD_PARAMETER, "temporal-filter mode searches exactly one reference");
+        return SVTME_OK;
+    }
+    if (k->me_type != SVTME_ME_OPEN_LOOP) return fail(h, SVTME_ERR_BAD_PARAMETER, "me_type");
     if (k->max_refs == 0 || k->max_cand == 0) return fail(h, SVTME_ERR_BAD_PARAMETER, "max_refs/max_cand");
     const uint32_t n0 = k->num_of_ref_pic_to_search[0], n1 = k->num_of_list_to_search > 1 ? k->num_of_ref_pic_to_search[1] : 0;
     if (k->max_l0 < n0 || (uint32_t)k->max_l0 + n1 > k->max_refs) return fail(h, SVTME_ERR_BAD_PARAMETER, "max_l0/max_refs too small for the reference lists");
@@ -287,11 +298,15 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
         p.out.sb_best_sad = (uint32_t *)(d + L.off[R_SAD]); p.out.sb_best_mv = (uint32_t *)(d + L.off[R_BMV]);
         p.out.do_ref = d + L.off[R_DOREF]; p.out.hme_sc = (int16_t *)(d + L.off[R_HMESC]);
     }
+    if (knobs->me_type == SVTME_ME_MCTF) {
+        p.out.tf_exit_sb = d + L.off[R_TFEXIT]; p.out.tf_blk_counts = (uint32_t *)(d + L.off[R_TFCNT]);
+    }
     cudaStream_t st = sl->stream;
     cudaError_t  e  = cudaStreamWaitEvent(st, cur->ready, 0);
     for (int l = 0; l < knobs->num_of_list_to_search && e == cudaSuccess; l++)
         for (int r = 0; r < knobs->num_of_ref_pic_to_search[l] && e == cudaSuccess; r++) e = cudaStreamWaitEvent(st, refs[l][r]->ready, 0);
     if (e == cudaSuccess) e = cudaMemsetAsync(sl->d_counter, 0, 16, st);
+    if (e == cudaSuccess && p.out.tf_blk_counts) e = cudaMemsetAsync(p.out.tf_blk_counts, 0, 8, st);
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_start, st);
     const int grid = (int)std::min<uint32_t>(n_b64, (uint32_t)(h->sm_count * h->ctas_per_sm));
     int n_launch = 1;
@@ -305,7 +320,8 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
         // through the slot's pinned arena (one copy of the covering range) and is scattered by svtme_search_wait.
         void *dst[R_N] = {out->me_mv, out->me_cand, out->total_me_candidate_index, out->me_64x64_distortion, out->me_32x32_distortion,
                           out->me_16x16_distortion, out->me_8x8_distortion, out->me_8x8_cost_variance, out->rc_me_distortion,
-                          out->stationary_block_present_sb, out->rc_me_allow_gm, out->sb_best_sad, out->sb_best_mv, out->do_ref, out->hme_sc};
+                          out->stationary_block_present_sb, out->rc_me_allow_gm, out->sb_best_sad, out->sb_best_mv, out->do_ref, out->hme_sc,
+                          out->tf_exit_sb, out->tf_blk_counts};
         size_t lo = L.total, hi = 0;
         for (int i = 0; i < R_N && e == cudaSuccess; i++) {
             sl->direct[i] = false;
@@ -487,6 +503,11 @@ int32_t svtme_picture_release(SvtMeHandle *h, SvtMePic *pic) {
 
 int32_t svtme_picture_search(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
                              const SvtMeKnobs *knobs, SvtMePictureResults *out, uint64_t *ticket) {
+    if (out && knobs && knobs->me_type == SVTME_ME_MCTF) {
+        if (!out->sb_best_mv || !out->sb_best_sad || !out->hme_sc || !out->tf_exit_sb || !out->tf_blk_counts)
+            return fail(h, SVTME_ERR_BAD_PARAMETER, "temporal-filter mode needs sb_best_mv, sb_best_sad, hme_sc, tf_exit_sb and tf_blk_counts");
+        return search_impl(h, cur, refs, knobs, out, 0, true, ticket);
+    }
     if (!out || !out->me_mv || !out->me_cand || !out->total_me_candidate_index || !out->me_64x64_distortion ||
         !out->me_32x32_distortion || !out->me_16x16_distortion || !out->me_8x8_distortion || !out->me_8x8_cost_variance ||
         !out->rc_me_distortion || !out->stationary_block_present_sb || !out->rc_me_allow_gm)
@@ -499,7 +520,7 @@ int32_t svtme_picture_search_device(SvtMeHandle *h, SvtMePic *cur, SvtMePic *con
                                     const SvtMeKnobs *knobs, uint64_t *ticket) {
     if (!knobs) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
     const uint32_t pu = knobs->enable_me_16x16 ? (knobs->enable_me_8x8 ? 85u : 21u) : 5u;
-    return search_impl(h, cur, refs, knobs, nullptr, pu, false, ticket);
+    return search_impl(h, cur, refs, knobs, nullptr, pu, knobs->me_type == SVTME_ME_MCTF, ticket);
 }
 
 static Inflight *find_slot(SvtMeHandle *h, uint64_t ticket) {
@@ -525,7 +546,8 @@ int32_t svtme_search_wait(SvtMeHandle *h, uint64_t ticket) {
         const SvtMePictureResults &u = sl->user;
         void *dst[R_N] = {u.me_mv, u.me_cand, u.total_me_candidate_index, u.me_64x64_distortion, u.me_32x32_distortion,
                           u.me_16x16_distortion, u.me_8x8_distortion, u.me_8x8_cost_variance, u.rc_me_distortion,
-                          u.stationary_block_present_sb, u.rc_me_allow_gm, u.sb_best_sad, u.sb_best_mv, u.do_ref, u.hme_sc};
+                          u.stationary_block_present_sb, u.rc_me_allow_gm, u.sb_best_sad, u.sb_best_mv, u.do_ref, u.hme_sc,
+                          u.tf_exit_sb, u.tf_blk_counts};
         for (int i = 0; i < R_N; i++)
             if (dst[i] && L.bytes[i] && !sl->direct[i]) memcpy(dst[i], sl->h_res + L.off[i], L.bytes[i]);
     }

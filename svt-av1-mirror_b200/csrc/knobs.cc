@@ -296,3 +296,75 @@ extern "C" int32_t svtme_derive_knobs(const SvtMePresetCfg *cfg, SvtMeKnobs *out
     k.only_l_bwd = mrp.only_l_bwd;
     return SVTME_OK;
 }
+
+// Temporal-filter knobs: svt_aom_sig_deriv_me_tf (enc_mode_config.c:814-854), tf_set_me_hme_params_oq (:588-663),
+// the TF HME level flags (:1620-1643) and the per-call overrides of produce_temporally_filtered_pic
+// (temporal_filtering.c:296, 316, 2759-2767, 3140-3158).
+extern "C" int32_t svtme_derive_tf_knobs(const SvtMeTfCfg *cfg, SvtMeKnobs *out) {
+    if (!cfg || !out || cfg->hme_me_level > 4 || cfg->width == 0 || cfg->height == 0) return SVTME_ERR_BAD_PARAMETER;
+    SvtMeKnobs &k = *out;
+    memset(&k, 0, sizeof(k));
+    const int lvl = cfg->hme_me_level;
+    const int res = input_resolution_class((uint32_t)cfg->width * cfg->height);
+    k.num_hme_sa_w = 2;
+    k.num_hme_sa_h = 2;
+    switch (lvl) {
+    case 0:
+        k.hme_l0_sa.sa_min = A(30, 30); k.hme_l0_sa.sa_max = A(60, 60);
+        k.hme_l1_sa = A(16, 16); k.hme_l2_sa = A(16, 16);
+        k.me_sa.sa_min = A(60, 60); k.me_sa.sa_max = A(120, 120);
+        break;
+    case 1:
+        k.hme_l0_sa.sa_min = A(16, 16); k.hme_l0_sa.sa_max = A(32, 32);
+        k.hme_l1_sa = A(16, 16); k.hme_l2_sa = A(16, 16);
+        k.me_sa.sa_min = A(16, 16); k.me_sa.sa_max = A(32, 32);
+        break;
+    case 2:
+        if (res <= SVTME_INPUT_SIZE_360p) { k.hme_l0_sa.sa_min = A(8, 8); k.hme_l0_sa.sa_max = A(8, 8); k.hme_l1_sa = A(8, 8); }
+        else if (res <= SVTME_INPUT_SIZE_480p) { k.hme_l0_sa.sa_min = A(8, 8); k.hme_l0_sa.sa_max = A(16, 16); k.hme_l1_sa = A(8, 8); }
+        else { k.hme_l0_sa.sa_min = A(16, 16); k.hme_l0_sa.sa_max = A(32, 32); k.hme_l1_sa = A(16, 16); }
+        k.hme_l2_sa = A(16, 16);
+        k.me_sa.sa_min = A(8, 8); k.me_sa.sa_max = A(8, 8);
+        break;
+    case 3:
+        k.hme_l0_sa.sa_min = A(8, 8); k.hme_l0_sa.sa_max = A(8, 8);
+        k.hme_l1_sa = A(8, 8); k.hme_l2_sa = A(8, 8);
+        k.me_sa.sa_min = A(8, 8); k.me_sa.sa_max = A(8, 8);
+        break;
+    default:
+        k.hme_l0_sa.sa_min = A(4, 4); k.hme_l0_sa.sa_max = A(4, 4);
+        k.hme_l1_sa = A(8, 8); k.hme_l2_sa = A(8, 8);
+        k.me_sa.sa_min = A(8, 8); k.me_sa.sa_max = A(8, 8);
+        break;
+    }
+    if (cfg->qp_opt) {  // :656-663
+        const int q = clip3(250, 1000, (int)(8 * cfg->qp) - 125);
+        auto mod = [q](uint16_t v) { const int r = (v * q) / 1000; return (uint16_t)(r > 8 ? r : 8); };
+        k.me_sa.sa_min.width = mod(k.me_sa.sa_min.width); k.me_sa.sa_min.height = mod(k.me_sa.sa_min.height);
+        k.me_sa.sa_max.width = mod(k.me_sa.sa_max.width); k.me_sa.sa_max.height = mod(k.me_sa.sa_max.height);
+    }
+    k.enable_hme_flag        = 1;
+    k.enable_hme_level0_flag = 1;
+    k.enable_hme_level1_flag = lvl <= 2 ? 1 : 0;
+    k.enable_hme_level2_flag = lvl == 0 ? 1 : 0;
+    k.hme_search_method = 1;                 // FULL_SAD_SEARCH, forced per block (temporal_filtering.c:316)
+    k.me_search_method  = lvl <= 2 ? 1 : 0;  // :822-834
+    prehme_ctrls(0, k);
+    prune_ctrls(0, k);
+    sr_adjust_ctrls(0, k);
+    // mv-based SA adjustment and 8x8-variance control are level 0 = off (:844-846)
+    k.me_early_exit_th            = lvl <= 1 ? 0 : 64 * 64 * 4;
+    k.prev_me_stage_based_exit_th = lvl <= 1 ? 0 : 64 * 64 * 4;
+    k.me_type       = SVTME_ME_MCTF;
+    k.tf_me_exit_th = cfg->me_exit_th;
+    k.num_of_list_to_search       = 1;
+    k.num_of_ref_pic_to_search[0] = 1;
+    k.temporal_layer_index        = cfg->temporal_layer_index;
+    k.is_ref                      = cfg->is_ref;
+    k.picture_number              = cfg->picture_number;
+    k.input_resolution            = (uint8_t)res;
+    // only read by the candidate / statistics stage, which this mode skips; kept at the encoder's constants
+    k.enable_me_8x8 = 1; k.enable_me_16x16 = 1; k.max_number_of_pus_per_sb = SVTME_SQUARE_PU_COUNT;
+    k.max_cand = 1; k.max_refs = 1; k.max_l0 = 1;
+    return SVTME_OK;
+}

@@ -442,6 +442,12 @@ SVTME_HD void final_centre_and_prune(const MeParams &p, SbState &s) {
         }
         s.hme_sc_x[li][ri] = sx; s.hme_sc_y[li][ri] = sy; s.hme_sad[li][ri] = hme_mv_sad;
     }
+    if (k.me_type == SVTME_ME_MCTF) {
+        // temporal-filter mode: no reference pruning or SR adjustment (:3103); a block whose HME SAD is already under
+        // the threshold skips the integer search altogether (:3109-3113)
+        s.tf_exit = s.hme_sad[0][0] < k.tf_me_exit_th;
+        return;
+    }
     if (!k.enable_hme_flag) return;  // prune_ref = enable_hme_flag && me_type != ME_MCTF (:3103, 3115)
     const uint16_t th = k.prune_ref_if_hme_sad_dev_bigger_than_th;
     if (k.enable_me_hme_ref_pruning && th != (uint16_t)~0) {
@@ -472,7 +478,7 @@ SVTME_HD void isearch_area(const MeParams &p, SbState &s, int li, int ri) {
     const SvtMeKnobs &k = p.k;
     int16_t xc = s.hme_sc_x[li][ri], yc = s.hme_sc_y[li][ri];
     int16_t w = (int16_t)k.me_sa.sa_min.width, h = (int16_t)k.me_sa.sa_min.height;
-    const uint16_t dist = scaled_dist(ref_dist(p, li, ri));  // me_type != ME_MCTF
+    const uint16_t dist = k.me_type == SVTME_ME_MCTF ? ref_dist(p, li, ri) : scaled_dist(ref_dist(p, li, ri));  // :1300
     w = (int16_t)SVTME_MIN((w * dist), (int)k.me_sa.sa_max.width);
     h = (int16_t)SVTME_MIN((h * dist), (int)k.me_sa.sa_max.height);
     if (k.mv_sa_adj_enabled && (!k.mv_sa_adj_nearest_ref_only || ri == 0)) {
@@ -580,7 +586,7 @@ SVTME_HD void isearch_final_job(const MeParams &p, SbState &s, int li, int ri) {
 // `arg`: 0 = reference (0,0) only, 1 = the others (SR adjustment level 2 lets p_sb_best_sad[0][0][0] of THIS SB steer
 // them, :1355-1364), 2 = all references.
 SVTME_HD bool is_in_pass(const SbState &s, int li, int ri, int arg) {
-    return s.do_ref[li][ri] && (arg == 2 || ((li == 0 && ri == 0) == (arg == 0)));
+    return s.do_ref[li][ri] && !s.tf_exit && (arg == 2 || ((li == 0 && ri == 0) == (arg == 0)));
 }
 // A: area from distance / MV / divisor, and the zero-MV / HME-centre SAD jobs of check_00_center
 SVTME_HD void is_a(const MeParams &p, SbState &s, int arg) {
@@ -861,7 +867,7 @@ SVTME_HDX int build_program(const SvtMeKnobs &k, Step *st) {
             ctl(C_IS_A, a); eng(STEP_NXM); ctl(C_IS_B, a); eng(STEP_FP); ctl(C_IS_C, a); eng(STEP_FP);
         }
     }
-    if (k.enable_hme_flag && k.enable_me_hme_ref_pruning) ctl(C_PRUNE, 0);
+    if (k.enable_hme_flag && k.enable_me_hme_ref_pruning && k.me_type != SVTME_ME_MCTF) ctl(C_PRUNE, 0);
     return n;
 }
 
@@ -885,9 +891,9 @@ SVTME_HD void ctl_step(const MeParams &p, SbState &s, uint8_t op, uint8_t arg) {
     }
 }
 
-// ---- results of one SB: candidates (one PU per thread), distortion statistics, GM detection, optional exports ----
+// candidates (one PU per thread), distortion statistics and GM detection of one SB (:3126-3151)
 template <class B>
-SVTME_HD void sb_finish(B &be, const MeParams &p, SbState &s, uint32_t b64_index) {
+SVTME_HD void sb_results(B &be, const MeParams &p, SbState &s, uint32_t b64_index) {
     const SvtMeKnobs &k = p.k;
     SbOut o;
     o.mv    = p.out.me_mv + (size_t)b64_index * p.pu_count * k.max_refs;
@@ -907,6 +913,27 @@ SVTME_HD void sb_finish(B &be, const MeParams &p, SbState &s, uint32_t b64_index
         p.out.stationary_block_present_sb[b64_index] = 0;
         p.out.rc_me_allow_gm[b64_index]              = 0;
         if (k.gm_enabled) gm_detection(p, s, o);
+    }
+}
+
+// ---- results of one SB: candidates (one PU per thread), distortion statistics, GM detection, optional exports ----
+template <class B>
+SVTME_HD void sb_finish(B &be, const MeParams &p, SbState &s, uint32_t b64_index) {
+    const SvtMeKnobs &k = p.k;
+    const uint8_t *nr     = k.num_of_ref_pic_to_search;
+    if (k.me_type == SVTME_ME_MCTF) {
+        // no candidates, distortions or GM for the temporal filter (:3126); it reads the best MVs / SADs below
+        if (be.leader()) {
+            p.out.tf_exit_sb[b64_index] = s.tf_exit;
+            uint32_t *cnt = p.out.tf_blk_counts + (SVTME_ABS(s.hme_sc_x[0][0]) > SVTME_ABS(s.hme_sc_y[0][0]) ? 0 : 1);  // :2469-2474
+#ifdef __CUDA_ARCH__
+            atomicAdd(cnt, 1u);
+#else
+            ++*cnt;
+#endif
+        }
+    } else {
+        sb_results(be, p, s, b64_index);
     }
     // optional MeContext state for parity checks
     if (p.out.sb_best_sad)

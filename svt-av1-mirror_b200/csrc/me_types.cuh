@@ -52,6 +52,8 @@ struct DevResults {
     uint32_t *sb_best_sad, *sb_best_mv;  // optional
     uint8_t  *do_ref;                    // optional
     int16_t  *hme_sc;                    // optional
+    uint8_t  *tf_exit_sb;                // temporal-filter mode only
+    uint32_t *tf_blk_counts;             // temporal-filter mode only: [horz, vert]
 };
 
 // One step of the per-SB program (me_control.cuh: build_program)
@@ -138,6 +140,7 @@ struct SbState {
     uint32_t me_distortion[kPus];
     uint8_t  do_ref[kMaxLists][kMaxRefs];
     uint8_t  performed_phme[kMaxLists][kMaxRefs][2];
+    uint8_t  tf_exit;  // temporal-filter mode: HME SAD under tf_me_exit_th, no integer search (motion_estimation.c:3109)
     SvtMeAreaMinMax hme_l0_sa;
     uint32_t org_x, org_y, b64_w, b64_h, b64_index;
     const uint8_t *src;  // b64_src_ptr

@@ -8,6 +8,8 @@ MAX_LISTS = 2
 MAX_REFS_PER_LIST = 4
 SQUARE_PU_COUNT = 85
 MAX_SAD_VALUE = 128 * 128 * 255
+ME_OPEN_LOOP = 0  # SVTME_ME_OPEN_LOOP
+ME_MCTF = 1       # SVTME_ME_MCTF
 
 
 class Area(C.Structure):
@@ -82,6 +84,8 @@ class Knobs(C.Structure):
         ("me_early_exit_th", C.c_uint32),
         ("me_safe_limit_zz_th", C.c_uint32),
         ("prev_me_stage_based_exit_th", C.c_uint32),
+        ("me_type", C.c_uint8),
+        ("tf_me_exit_th", C.c_uint32),
     ]
 
     def as_dict(self):
@@ -116,6 +120,21 @@ class PresetCfg(C.Structure):
     ]
 
 
+class TfCfg(C.Structure):
+    """SvtMeTfCfg: the TfControls fields the temporal-filter knob derivation reads."""
+    _fields_ = [
+        ("hme_me_level", C.c_uint8),
+        ("qp_opt", C.c_uint8),
+        ("me_exit_th", C.c_uint32),
+        ("qp", C.c_uint32),
+        ("width", C.c_uint16),
+        ("height", C.c_uint16),
+        ("picture_number", C.c_uint64),
+        ("temporal_layer_index", C.c_uint8),
+        ("is_ref", C.c_uint8),
+    ]
+
+
 class PictureResults(C.Structure):
     _fields_ = [
         ("b64_total_count", C.c_uint32),
@@ -135,6 +154,8 @@ class PictureResults(C.Structure):
         ("sb_best_mv", C.POINTER(C.c_uint32)),
         ("do_ref", C.POINTER(C.c_uint8)),
         ("hme_sc", C.POINTER(C.c_int16)),
+        ("tf_exit_sb", C.POINTER(C.c_uint8)),
+        ("tf_blk_counts", C.POINTER(C.c_uint32)),
     ]
 
 
@@ -186,6 +207,9 @@ class ResultBuffers:
             self.arrays["sb_best_mv"] = alloc((n_b64, 2, 4, 85), np.uint32)
             self.arrays["do_ref"] = alloc((n_b64, 2, 4), np.uint8)
             self.arrays["hme_sc"] = alloc((n_b64, 2, 4, 2), np.int16)
+            if knobs.me_type == ME_MCTF:
+                self.arrays["tf_exit_sb"] = alloc((n_b64,), np.uint8)
+                self.arrays["tf_blk_counts"] = alloc((2,), np.uint32)
         s = PictureResults()
         s.b64_total_count = n_b64
         s.pu_count = self.pu_count

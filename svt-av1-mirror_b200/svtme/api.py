@@ -18,7 +18,7 @@ LIB_PATH = os.environ.get("SVTME_LIB") or os.path.join(_HERE, "libsvtme_cuda.so"
 _PKG_DIR = os.path.dirname(_HERE)
 
 EXPORTS = [
-    "svtme_init", "svtme_destroy", "svtme_derive_knobs", "svtme_picture_register", "svtme_picture_register16",
+    "svtme_init", "svtme_destroy", "svtme_derive_knobs", "svtme_derive_tf_knobs", "svtme_picture_register", "svtme_picture_register16",
     "svtme_picture_register_device", "svtme_picture_wait", "svtme_picture_read_plane", "svtme_picture_release",
     "svtme_picture_search", "svtme_search_wait", "svtme_picture_search_device", "svtme_search_elapsed_ms",
     "svtme_search_px_compares", "svtme_measure_sad_peak", "svtme_launch_count", "svtme_last_error", "svtme_cuda_sad_loop_kernel", "svtme_cuda_downsample_2d",
@@ -55,6 +55,7 @@ def load_library():
     lib.svtme_destroy.argtypes = [vp]
     lib.svtme_destroy.restype = None
     lib.svtme_derive_knobs.argtypes = [C.POINTER(abi.PresetCfg), C.POINTER(abi.Knobs)]
+    lib.svtme_derive_tf_knobs.argtypes = [C.POINTER(abi.TfCfg), C.POINTER(abi.Knobs)]
     lib.svtme_picture_register.argtypes = [vp, u64, u8p, u32, u32, u32, C.POINTER(vp)]
     lib.svtme_picture_register16.argtypes = [vp, u64, u8p, u32, u32, u32, C.POINTER(vp)]
     lib.svtme_picture_register_device.argtypes = [vp, u64, vp, u32, u32, u32, C.POINTER(vp)]
@@ -95,6 +96,18 @@ def derive_knobs(**kw):
     rc = load_library().svtme_derive_knobs(C.byref(cfg), C.byref(out))
     if rc != 0:
         raise SvtMeError("svtme_derive_knobs: 0x%x" % (rc & 0xffffffff))
+    return out
+
+
+def derive_tf_knobs(**kw):
+    """svtme_derive_tf_knobs: TfControls fields -> SvtMeKnobs of one temporal-filter search (pure host code)."""
+    cfg = abi.TfCfg()
+    for k, v in kw.items():
+        setattr(cfg, k, v)
+    out = abi.Knobs()
+    rc = load_library().svtme_derive_tf_knobs(C.byref(cfg), C.byref(out))
+    if rc != 0:
+        raise SvtMeError("svtme_derive_tf_knobs: 0x%x" % (rc & 0xffffffff))
     return out
 
 

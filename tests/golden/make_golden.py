@@ -22,6 +22,9 @@ import refbind  # noqa: E402
 import helpers as H  # noqa: E402
 
 W, HH, N = 192, 136, 7
+# temporal-filter mode: (tf hme_me_level, me_exit_th, centre picture, neighbouring picture)
+TF_CASES = [(0, 0, 3, 2), (1, 256, 3, 5), (2, 256, 3, 4), (4, 3000, 3, 1)]
+TF_ARRAYS = ("sb_best_sad", "sb_best_mv", "hme_sc", "do_ref", "tf_exit_sb", "tf_blk_counts")
 # (enc_mode, temporal layer, picture, extra preset fields)
 CASES = [(6, 0, 4, {}), (6, 2, 3, {}), (10, 1, 2, {}), (2, 2, 3, {}), (13, 0, 4, {}), (8, 1, 2, {"slice_type_b": 0})]
 
@@ -43,6 +46,14 @@ def main():
         out["case%d_meta" % n] = np.array([em, tl, cur, len(l0), len(l1)] + l0 + l1, dtype=np.int32)
         for name, arr in res.arrays.items():
             out["case%d_%s" % (n, name)] = arr.copy()
+    for n, (lvl, th, cur, nb) in enumerate(TF_CASES):
+        k = ref.derive_tf_knobs(hme_me_level=lvl, qp_opt=1, me_exit_th=th, qp=35, width=W, height=HH,
+                                picture_number=cur, temporal_layer_index=0, is_ref=1)
+        res = ref.me_picture(k, pics[cur], {(0, 0): pics[nb]}, n_threads=1, extended=True)
+        out["tf%d_knobs" % n] = np.frombuffer(bytes(k), dtype=np.uint8).copy()
+        out["tf%d_meta" % n] = np.array([lvl, th, cur, nb], dtype=np.int32)
+        for name in TF_ARRAYS:
+            out["tf%d_%s" % (n, name)] = res.arrays[name].copy()
     path = os.path.join(HERE, "me_golden.npz")
     np.savez_compressed(path, **out)
     print("wrote %s: %d arrays, %.1f KB" % (path, len(out), os.path.getsize(path) / 1e3))

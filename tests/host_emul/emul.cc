@@ -116,6 +116,8 @@ extern "C" int svtemu_me_picture(const SvtMeKnobs *k, const SvtRefPic *cur, cons
     p.out.me_8x8_cost_variance = out->me_8x8_cost_variance; p.out.rc_me_distortion = out->rc_me_distortion;
     p.out.stationary_block_present_sb = out->stationary_block_present_sb; p.out.rc_me_allow_gm = out->rc_me_allow_gm;
     p.out.sb_best_sad = out->sb_best_sad; p.out.sb_best_mv = out->sb_best_mv; p.out.do_ref = out->do_ref; p.out.hme_sc = out->hme_sc;
+    p.out.tf_exit_sb = out->tf_exit_sb; p.out.tf_blk_counts = out->tf_blk_counts;
+    if (out->tf_blk_counts) out->tf_blk_counts[0] = out->tf_blk_counts[1] = 0;
     p.n_steps = build_program(p.k, p.prog);
     ScalarBackend be;
     be.p = &p;

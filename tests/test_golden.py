@@ -32,6 +32,17 @@ def _cases(g):
         n += 1
 
 
+def _tf_cases(g):
+    n = 0
+    while "tf%d_knobs" % n in g:
+        k = abi.Knobs.from_buffer_copy(g["tf%d_knobs" % n].tobytes())
+        lvl, th, cur, nb = g["tf%d_meta" % n].tolist()
+        want = {name[len("tf%d_" % n):]: g[name] for name in g.files
+                if name.startswith("tf%d_" % n) and not name.endswith(("_knobs", "_meta"))}
+        yield n, k, cur, nb, want, (lvl, th)
+        n += 1
+
+
 def _check(got, want, what):
     for name, arr in want.items():
         assert name in got.arrays, "%s: missing output %s" % (what, name)
@@ -52,6 +63,25 @@ def test_oracle_reproduces_golden_vectors(oracle, gold):
     for n, k, cur, l0, l1, want, _ in _cases(gold):
         got = oracle.me_picture(k, pics[cur], H.refs_dict(pics, l0, l1), n_threads=2, extended=True)
         _check(got, want, "oracle case %d" % n)
+
+
+def test_oracle_reproduces_golden_temporal_filter_vectors(oracle, gold):
+    pics = [refbind.PaddedPicture(f, i) for i, f in enumerate(list(gold["frames"]))]
+    for p in pics:
+        oracle.build_planes(p, 1)
+    n_cases = 0
+    for n, k, cur, nb, want, _ in _tf_cases(gold):
+        got = oracle.me_picture(k, pics[cur], {(0, 0): pics[nb]}, n_threads=2, extended=True)
+        _check(got, want, "oracle tf case %d" % n)
+        n_cases += 1
+    assert n_cases == 4
+
+
+def test_knob_mirror_reproduces_golden_temporal_filter_knobs(gold):
+    for n, k, cur, nb, want, (lvl, th) in _tf_cases(gold):
+        mine = api.derive_tf_knobs(hme_me_level=lvl, qp_opt=1, me_exit_th=th, qp=35, width=192, height=136,
+                                   picture_number=cur, temporal_layer_index=0, is_ref=1)
+        assert bytes(mine) == bytes(k), "tf case %d: derived knobs differ from the reference's" % n
 
 
 def test_knob_mirror_reproduces_golden_knobs(gold):
@@ -76,5 +106,8 @@ def test_cuda_reproduces_golden_vectors(gold, pipeline):
         for n, k, cur, l0, l1, want, _ in _cases(gold):
             got = dev.me_picture(k, pd[cur], H.refs_dict(pd, l0, l1), extended=True)
             _check(got, want, "cuda case %d" % n)
+        for n, k, cur, nb, want, _ in _tf_cases(gold):
+            got = dev.me_picture(k, pd[cur], {(0, 0): pd[nb]}, extended=True)
+            _check(got, want, "cuda tf case %d" % n)
     finally:
         dev.close()
