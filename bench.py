@@ -44,6 +44,10 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=32, help="pictures of the workload timed on the host cores per step")
     ap.add_argument("--cpu-seconds", type=float, default=8.0, help="CPU-baseline budget of the default run (about this much work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mode", default="me", choices=["me", "tf"],
+                    help="me: the headline open-loop ME workload; tf: the temporal-filter (ME_MCTF) searches of the same "
+                         "mini-GOP -- a secondary measurement of SURVEY section 8(f) rank 2, not the headline metric")
+    ap.add_argument("--tf-window", type=int, default=3, help="tf mode: neighbouring pictures searched on each side of a centre")
     return ap.parse_args()
 
 
@@ -70,6 +74,25 @@ class Workload:
             self.pics.append((e["poc"], k, l0, l1))
         self.name = "%dx%d 8-bit 4:2:0 synthetic, preset M%d, mini-GOP %d (hier. levels %d), refs<=%d+%d" % (
             self.w, self.h, args.preset, self.gop, self.hl, k0.max_l0, k0.max_refs - k0.max_l0)
+        self.units, self.unit, self.extended = self.gop, "pictures", False
+        self.metric = "ME pictures/sec at 4K"
+        if args.mode == "tf":
+            # The temporal filter's motion searches in this mini-GOP: the filtered (centre) pictures are the leading
+            # picture and the layer-0 / layer-1 pictures; each searches its +-tf_window neighbours one at a time
+            # (temporal_filtering.c:3129-3174).  TfControls of presets M5-M7 (tf level 5, enc_handle.c:2951-3023):
+            # hme_me_level 2, me_exit_th 0, qp_opt 1.
+            self.pics = []
+            for c in (0, self.gop // 2, self.gop):
+                k = api.derive_tf_knobs(hme_me_level=2, qp_opt=1, me_exit_th=0, qp=35, width=self.w, height=self.h,
+                                        picture_number=c, temporal_layer_index=0 if c != self.gop // 2 else 1, is_ref=1)
+                for d in range(1, args.tf_window + 1):
+                    for nb in (c - d, c + d):
+                        if 0 <= nb < self.n_frames:
+                            self.pics.append((c, k, [nb], []))
+            self.units, self.unit, self.extended = len(self.pics), "picture pairs", True
+            self.metric = "temporal-filter ME picture-pair searches/sec at 4K"
+            self.name = "%dx%d 8-bit synthetic, temporal-filter ME (ME_MCTF, tf hme_me_level 2 = presets M5-M7), centres 0/%d/%d of a mini-GOP of %d, +-%d neighbours = %d pair searches" % (
+                self.w, self.h, self.gop // 2, self.gop, self.gop, args.tf_window, len(self.pics))
 
 
 class ClockSampler(threading.Thread):
@@ -183,7 +206,7 @@ def reference_arm(wl, n_pictures, steps, warmup, seconds=None):
             ref.build_planes(padded[poc], 1)  # decimation of the current picture is part of the path
             refs = {(0, i): padded[p] for i, p in enumerate(l0)}
             refs.update({(1, i): padded[p] for i, p in enumerate(l1)})
-            ref.me_picture(k, padded[poc], refs, n_threads=cores, extended=False)
+            ref.me_picture(k, padded[poc], refs, n_threads=cores, extended=wl.extended)
 
     for _ in range(warmup):
         step()
@@ -195,8 +218,8 @@ def reference_arm(wl, n_pictures, steps, warmup, seconds=None):
     steps = done
     dt = time.perf_counter() - t0
     pps = len(sample) * steps / dt
-    return {"value": pps, "unit": "pictures/s", "cores": cores, "kind": kind,
-            "sample": "%d pictures (decode-order %s) of the workload x %d steps = %.1f s, %s, %d threads" % (
+    return {"value": pps, "unit": wl.unit + "/s", "cores": cores, "kind": kind,
+            "sample": "%d searches (decode-order %s) of the workload x %d steps = %.1f s, %s, %d threads" % (
                 len(sample), "all" if len(sample) == len(wl.pics) else idx, steps, dt, what, cores)}, dt
 
 
@@ -212,11 +235,11 @@ def main():
         wl = Workload(args, seed=100)
         steps, warmup = max(1, min(args.steps, 40)), min(args.warmup, 2)  # a step = the whole mini-GOP, ~0.2 s on 16 cores
         cb, dt = reference_arm(wl, args.cpu_sample, steps, warmup)
-        line = {"impl": "reference", "metric": "ME pictures/sec at 4K", "value": cb["value"], "unit": "pictures/s",
+        line = {"impl": "reference", "metric": wl.metric, "value": cb["value"], "unit": wl.unit + "/s",
                 "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": {"workload": wl.name, "l2": "inputs larger than L2"},
-                "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": "pictures/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+                "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": wl.unit + "/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         print(json.dumps(line))
         return 0
 
@@ -246,7 +269,7 @@ def main():
         keep.append(t)
         return t.numpy()
 
-    outs = [abi.ResultBuffers(n_b64, k, extended=False, pinned_alloc=pinned) for _, k, _, _ in wl.pics]
+    outs = [abi.ResultBuffers(n_b64, k, extended=wl.extended, pinned_alloc=pinned) for _, k, _, _ in wl.pics]
     d2h = sum(o.nbytes() for o in outs)
     h2d = nf * w * h
 
@@ -268,7 +291,7 @@ def main():
         ms = e0.elapsed_time(e1)
         barrier()
         # whole job: SUM of the pictures of all ranks, MAX of their device times (svtme/shard.py)
-        return shard.reduce_job(wl.gop * steps, ms, dist, device="cuda")
+        return shard.reduce_job(wl.units * steps, ms, dist, device="cuda")
 
     # the picture consecutive mini-GOPs share (last of rank r = leading base picture of rank r + 1) moves GPU to GPU
     # every step: NCCL point-to-point over NVLink; the receiver decimates it locally
@@ -342,7 +365,8 @@ def main():
     alg_bytes = (1 + refs_avg) * 1.3125 * w * h + d2h / len(wl.pics)
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["search_dram_bytes_per_picture"]
+        if args.mode == "me":  # the capture is of the headline workload
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["search_dram_bytes_per_picture"]
     except Exception:
         pass
     ach = px_total / (ms_total * 1e-3) / 1e12
@@ -358,13 +382,13 @@ def main():
                 "hbm": {"achieved": alg_bytes / (ms_total / n_launch * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": alg_bytes / (ms_total / n_launch * 1e-3) / 1e9 / hbm_peak, "algorithmic_bytes_per_launch": alg_bytes,
                         "peak_source": hbm_src}}
-    line = {"metric": "ME pictures/sec at 4K", "value": value, "unit": "pictures/s", "n_gpus": world, "steps": args.steps,
+    line = {"metric": wl.metric, "value": value, "unit": wl.unit + "/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": wl.name, "pictures_per_step_per_gpu": wl.gop, "parallelism": "pictures sharded by mini-GOP, %d rank(s)%s" % (
+            "config": {"workload": wl.name, "%s_per_step_per_gpu" % wl.unit.replace(" ", "_"): wl.units, "parallelism": "pictures sharded by mini-GOP, %d rank(s)%s" % (
                            world, "; shared base picture handed rank r -> r+1 by NCCL p2p every step (verified equal)" if world > 1 else ""),
                        "l2": "inputs larger than L2 (%.0f MB of planes per step)" % (nf * w * h * 1.55 / 1e6), "inflight": args.inflight},
-            "e2e": {"value": e2e, "unit": "pictures/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "e2e": {"value": e2e, "unit": wl.unit + "/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_host / args.steps, "h2d_copy_alone_ms_per_step": h2d_only_ms,
                     "h2d_link_gbs": h2d / h2d_only_ms / 1e6},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline}

@@ -121,6 +121,7 @@ SVTME_HD void sb_init(B &be, const MeParams &p, SbState &s, uint32_t b64_index) 
     if (be.leader()) {
         const DevPlane &f  = p.cur.lvl[0];
         const uint16_t  aw = (uint16_t)((f.width + 7) & ~7), ah = (uint16_t)((f.height + 7) & ~7);
+        s.home      = &s;
         s.b64_index = b64_index;
         s.org_x     = (b64_index % p.wb) * 64;
         s.org_y     = (b64_index / p.wb) * 64;
@@ -527,7 +528,7 @@ SVTME_HD void isearch_adjust(const MeParams &p, SbState &s, int li, int ri, uint
         }
         if (k.enable_me_sr_adjustment == 2) {
             if ((accurate && (best_hme_sad < (24 * 24))) || (k.is_ref && s.hme_sad[li][ri] < (24 * 24))) h = (int16_t)(h / 2);
-            if ((li || ri) && s.best_sad[0][0][0] < 5000 && h == s.isa_h0[li][ri] && w == s.isa_w0[li][ri]) {
+            if ((li || ri) && s.home->best_sad[0][0][0] < 5000 && h == s.isa_h0[li][ri] && w == s.isa_w0[li][ri]) {
                 h = (int16_t)(h >> 1); w = (int16_t)(w >> 1);
             }
         }
@@ -550,7 +551,7 @@ SVTME_HD void isearch_final_job(const MeParams &p, SbState &s, int li, int ri) {
     int16_t w = s.isa_w[li][ri], h = s.isa_h[li][ri];
     const int16_t xc = s.isc_x[li][ri], yc = s.isc_y[li][ri];
     if (s.probe[li][ri]) {
-        const uint32_t *bs = s.best_sad[li][ri];
+        const uint32_t *bs = s.home->best_sad[li][ri];
         const uint32_t  mean = bs[0] / 64;
         uint32_t        ssq  = 0;
         for (int i = 0; i < 64; i++) {
@@ -629,7 +630,7 @@ SVTME_HD void me_prune_ref(const MeParams &p, SbState &s) {
     SVTME_FOR_REFS(k, li, ri) {
         if (s.do_ref[li][ri] == 0) { s.hme_sad[li][ri] = (uint64_t)SVTME_MAX_SAD_VALUE * 64; continue; }
         uint64_t sum = 0;
-        for (int i = 0; i < 64; i++) sum += s.best_sad[li][ri][21 + i];
+        for (int i = 0; i < 64; i++) sum += s.home->best_sad[li][ri][21 + i];
         s.hme_sad[li][ri] = sum;
     }
     const uint16_t th = k.prune_ref_if_me_sad_dev_bigger_than_th;

@@ -69,12 +69,32 @@ __global__ void __launch_bounds__(kStThreads) st_init_kernel(const __grid_consta
 
 // control steps [first, first + count) of the program: one WARP per 64x64 block with a single active lane -- the code is
 // a long scalar dependency chain with block-dependent branches, so 32 blocks per warp would serialise their paths;
-// one block per warp keeps every chain independent (2040 warps in flight at 4K).
+// one block per warp keeps every chain independent (2040 warps in flight at 4K).  The chain is latency bound: the warp
+// first copies the CONTROL part of the block's state (kSbHeadBytes, everything but the best-SAD / best-MV tables) into
+// shared memory with all 32 lanes, lane 0 runs the steps on that copy (shared-memory latency instead of an L2 round
+// trip per field), and the warp writes it back.  The few reads of the result tables go through SbState::home.
+constexpr int kSbHeadBytes = (int)offsetof(SbState, best_sad);
+static_assert(kSbHeadBytes % 16 == 0 && sizeof(SbState) % 16 == 0, "the control part is copied as 16-byte words");
 __global__ void __launch_bounds__(kStThreads) st_ctl_kernel(const __grid_constant__ MeParams p, int first, int count) {
-    const uint32_t sb = blockIdx.x * kStWarps + (threadIdx.x >> 5);
-    if (sb >= p.wb * p.hb || (threadIdx.x & 31) != 0) return;
-    SbState &s = p.states[sb];
-    for (int i = first; i < first + count; i++) ctl_step(p, s, p.prog[i].op, p.prog[i].arg);
+    __shared__ __align__(16) unsigned char head[kStWarps][kSbHeadBytes];
+    const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t sb = blockIdx.x * kStWarps + warp;
+    if (sb >= p.wb * p.hb) return;
+    uint4       *g = reinterpret_cast<uint4 *>(&p.states[sb]);
+    uint4       *l = reinterpret_cast<uint4 *>(head[warp]);
+    constexpr int kN = kSbHeadBytes / 16;
+#pragma unroll
+    for (int i = 0; i < (kN + 31) / 32; i++)
+        if (lane + 32 * i < kN) l[lane + 32 * i] = g[lane + 32 * i];
+    __syncwarp();
+    if (lane == 0) {
+        SbState &s = *reinterpret_cast<SbState *>(head[warp]);
+        for (int i = first; i < first + count; i++) ctl_step(p, s, p.prog[i].op, p.prog[i].arg);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < (kN + 31) / 32; i++)
+        if (lane + 32 * i < kN) g[lane + 32 * i] = l[lane + 32 * i];
 }
 
 __global__ void __launch_bounds__(kStThreads) st_finish_kernel(const __grid_constant__ MeParams p) {

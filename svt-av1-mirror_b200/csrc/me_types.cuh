@@ -128,7 +128,7 @@ constexpr int kMaxNxmJobs = 16;
 constexpr int kMaxFpJobs  = 8;
 
 // SB-scoped part of the reference's MeContext (me_context.h:366-509); lives in shared memory on the device.
-struct SbState {
+struct alignas(16) SbState {
     uint64_t lsad[3][kMaxLists][kMaxRefs][2][2];  // hme_level{0,1,2}_sad[l][r][w][h]
     uint64_t hme_sad[kMaxLists][kMaxRefs];
     PreHme   prehme[kMaxLists][kMaxRefs][2];
@@ -136,8 +136,6 @@ struct SbState {
     int16_t  hme_sc_x[kMaxLists][kMaxRefs], hme_sc_y[kMaxLists][kMaxRefs];
     uint32_t divisor[kMaxLists][kMaxRefs];
     uint32_t zz_sad[kMaxLists][kMaxRefs];
-    uint32_t best_sad[kMaxLists][kMaxRefs][kPus], best_mv[kMaxLists][kMaxRefs][kPus];
-    uint32_t me_distortion[kPus];
     uint8_t  do_ref[kMaxLists][kMaxRefs];
     uint8_t  performed_phme[kMaxLists][kMaxRefs][2];
     uint8_t  tf_exit;  // temporal-filter mode: HME SAD under tf_me_exit_th, no integer search (motion_estimation.c:3109)
@@ -159,6 +157,11 @@ struct SbState {
     int32_t  n_sad, n_nxm, n_fp;
     unsigned long long px;  // algorithmic pixel-compares of this SB so far (staged pipeline)
     uint32_t l0_searched;  // references whose HME-L0 quadrants were searched in the current pass (bit li*4+ri)
+    // Everything above is the CONTROL part: the staged pipeline's control kernel works on a shared-memory copy of it
+    // (kSbHeadBytes) and reaches the search results below through `home`, the block's own state in HBM/L2.
+    SbState *home;
+    uint32_t best_sad[kMaxLists][kMaxRefs][kPus], best_mv[kMaxLists][kMaxRefs][kPus];
+    uint32_t me_distortion[kPus];
 };
 
 }  // namespace svtme

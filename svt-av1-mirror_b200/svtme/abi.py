@@ -193,16 +193,18 @@ class ResultBuffers:
         self.pu_count = pu_count_of(knobs)
         mr, mc = max(1, knobs.max_refs), max(1, knobs.max_cand)
         alloc = pinned_alloc or (lambda shape, dt: np.zeros(shape, dt))
-        self.arrays = {
-            "me_mv": alloc((n_b64, self.pu_count, mr), np.uint32),
-            "me_cand": alloc((n_b64, self.pu_count, mc), np.uint8),
-            "total_me_candidate_index": alloc((n_b64, self.pu_count), np.uint8),
-        }
-        for n in self.SCALARS32:
-            self.arrays[n] = alloc((n_b64,), np.uint32)
-        for n in self.SCALARS8:
-            self.arrays[n] = alloc((n_b64,), np.uint8)
-        if extended:
+        self.arrays = {}
+        if knobs.me_type != ME_MCTF:  # the temporal filter reads no candidates or statistics
+            self.arrays = {
+                "me_mv": alloc((n_b64, self.pu_count, mr), np.uint32),
+                "me_cand": alloc((n_b64, self.pu_count, mc), np.uint8),
+                "total_me_candidate_index": alloc((n_b64, self.pu_count), np.uint8),
+            }
+            for n in self.SCALARS32:
+                self.arrays[n] = alloc((n_b64,), np.uint32)
+            for n in self.SCALARS8:
+                self.arrays[n] = alloc((n_b64,), np.uint8)
+        if extended or knobs.me_type == ME_MCTF:
             self.arrays["sb_best_sad"] = alloc((n_b64, 2, 4, 85), np.uint32)
             self.arrays["sb_best_mv"] = alloc((n_b64, 2, 4, 85), np.uint32)
             self.arrays["do_ref"] = alloc((n_b64, 2, 4), np.uint8)
