@@ -1232,6 +1232,12 @@ struct FpSub {
     int32_t off, plane_words, rbase, rounds;
 };
 
+// FULL (all 64 rows, the temporal filter's ME at tf hme_me_level <= 2): SAD_full(y) = [even source rows against window
+// rows y + 2r] + [odd source rows against window rows y + 1 + 2r] -- two sub-sampled sums.  Half-warp `half` keeps the
+// source rows of parity `half`; both halves walk the same candidates (rows 4k + e and 4k + e + 2, e = 0, 1 in turn),
+// each reading the plane of parity (e + half) & 1, and one exchange over lane ^ 16 completes the sums: half h ends up
+// with the four candidates of row 4k + e + 2h.
+template <bool FULL>
 __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_constant__ MeParams p) {
     extern __shared__ __align__(16) uint32_t fp_win[];  // kFpBufWords
     __shared__ uint32_t               sub_key[kFpMaxSub][kPus];  // (sad << 12 | candidate) minima of the batch's sub-windows
@@ -1264,10 +1270,11 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
         const uint8_t  *sp0 = f.org + (int64_t)((blockIdx.x / p.wb) * 64 + 16 * by) * f.stride + (blockIdx.x % p.wb) * 64 + 16 * bx;
 #pragma unroll
         for (int r = 0; r < 8; r++) {
-            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(sp0 + (int64_t)(2 * r) * f.stride));
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(sp0 + (int64_t)(2 * r + (FULL ? half : 0)) * f.stride));
             sreg[r][0] = v.x; sreg[r][1] = v.y; sreg[r][2] = v.z; sreg[r][3] = v.w;
         }
     }
+    constexpr uint32_t kPxPerCand = FULL ? 64u * 64u : 64u * 32u;
     // the running best SADs this thread will compare against at the end: requested now, needed last
     constexpr int kFoldPer = (kMaxFpJobs * kPus + kStThreads - 1) / kStThreads;
     uint32_t      prev_best[kFoldPer];
@@ -1288,7 +1295,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
         plane           = ((plane + 15) & ~31) + 16;  // = 16 mod 32
         u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
         u.a = (int16_t)a; u.ngroups = (int16_t)ngroups; u.P = (int16_t)P;
-        u.plane_words = plane; u.rounds = (nyp >> 2) * ngroups;
+        u.plane_words = plane; u.rounds = (nyp >> 2) * ngroups * (FULL ? 2 : 1);
     };
     if (warp == 0) {
         const bool valid = lane < n && jobs[lane].w > 0 && jobs[lane].h > 0;
@@ -1303,7 +1310,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
                 sub_geometry(jobs[lane], 0, 0, jobs[lane].w, jobs[lane].h, u);
                 u.job = (int16_t)lane;
                 words = 2 * u.plane_words; rounds = u.rounds;
-                px    = (uint32_t)(jobs[lane].w * jobs[lane].h) * (64u * 32u);  // <= 64 * 64 * 2048
+                px    = (uint32_t)(jobs[lane].w * jobs[lane].h) * kPxPerCand;  // <= 64 * 64 * 4096
             }
             int cw = words, cr = rounds;
             for (int o = 1; o < 8; o <<= 1) {  // jobs live in lanes 0..7
@@ -1351,7 +1358,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
                     u.job = (int16_t)cur_job; u.off = used; u.rbase = rb;
                     subs[ns++] = u;
                     used += 2 * u.plane_words; rb += u.rounds;
-                    if (cur_xt == 0 && cur_st == 0) px += (unsigned long long)j.w * j.h * (64 * 32);
+                    if (cur_xt == 0 && cur_st == 0) px += (unsigned long long)j.w * j.h * kPxPerCand;
                     if (++cur_st == nst) { cur_st = 0; if (++cur_xt == nxt) { cur_xt = 0; cur_job++; } }
                 }
                 n_sub = ns;
@@ -1397,10 +1404,14 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
             const int ngroups = u.ngroups, nx = u.nx, ny = u.ny, P = u.P;
             int       k = first / ngroups, g = first - k * ngroups;
             uint32_t  best8[4] = {~0u, ~0u, ~0u, ~0u}, best16 = ~0u, best32 = ~0u, best64 = ~0u;
-            const uint32_t *wbase = fp_win + u.off + half * u.plane_words + 4 * bx + (8 * by) * P + by;
+            const uint32_t *wbase0 = fp_win + u.off + 4 * bx + (8 * by) * P + by;
             for (int local = first; local < u.rounds; local += kStWarps) {
-                const int  yy = 4 * k + half;
-                const bool active = yy < ny;
+                // SUB: k counts groups of 4 candidate rows.  FULL: k counts pairs (rows 4kk + e, 4kk + e + 2)
+                const int       kk = FULL ? (k >> 1) : k, e = FULL ? (k & 1) : 0;
+                const int       yy = 4 * kk + (FULL ? e : half);
+                const int       i0 = 2 * kk + (FULL ? (e & half) : 0);
+                const uint32_t *wbase = wbase0 + (FULL ? (e ^ half) : half) * u.plane_words;
+                const bool      active = yy < ny;
                 uint32_t   acc[2][4][4];
 #pragma unroll
                 for (int y2 = 0; y2 < 2; y2++)
@@ -1410,7 +1421,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
                     const uint32_t *rowp = wbase + g;
 #pragma unroll
                     for (int rr = 0; rr < 9; rr++) {
-                        const int       i  = 2 * k + rr;  // + 8 * by is in wbase, and (i + 8 by) >> 3 = by + (i >> 3)
+                        const int       i  = i0 + rr;  // + 8 * by is in wbase, and (i + 8 by) >> 3 = by + (i >> 3)
                         const uint32_t *rp = rowp + i * P + (i >> 3);
                         uint32_t        w[5];
 #pragma unroll
@@ -1434,57 +1445,100 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
                     }
                 }
                 const int xb = 4 * g - u.a;
-                uint32_t  s16[8];
-#pragma unroll
-                for (int y2 = 0; y2 < 2; y2++)
+                if constexpr (FULL) {
+                    // complete the sums: this half keeps candidate row yy + 2 * half and gets the other parity's share of it
+                    uint32_t s16[4];
+                    const int  y = yy + 2 * half;
 #pragma unroll
                     for (int c = 0; c < 4; c++) {
-                        const int      xx = xb + c, y = yy + 2 * y2;
+                        const int      xx = xb + c;
                         const bool     valid = y < ny && xx >= 0 && xx < nx;
                         const uint32_t ord = (uint32_t)(y * nx + xx);  // < 4096
                         uint32_t       t = 0;
 #pragma unroll
                         for (int q = 0; q < 4; q++) {
-                            if (valid) best8[q] = min(best8[q], acc[y2][c][q] * 4096u + ord);
-                            t += acc[y2][c][q];
+                            const uint32_t send = half ? acc[0][c][q] : acc[1][c][q], keep = half ? acc[1][c][q] : acc[0][c][q];
+                            const uint32_t v = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+                            if (valid) best8[q] = min(best8[q], v * 4096u + ord);
+                            t += v;
                         }
                         if (valid) best16 = min(best16, t * 4096u + ord);
-                        s16[y2 * 4 + c] = t;
+                        s16[c] = t;
                     }
-                // transposing butterfly over the 4 lanes of a 32x32 block, then over the 4 blocks: candidate e = y2 * 4 + c
-                uint32_t t4[4], t2[2], t1;
-                {
-                    const bool up = b & 1;  // keeps y2 = b0
+                    // transposing butterfly over the 4 lanes of a 32x32 block: candidate c = 2 * b0 + b1 stays here
+                    uint32_t t2[2], t1;
+                    {
+                        const bool up = b & 1;
 #pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const uint32_t send = up ? s16[i] : s16[4 + i], keep = up ? s16[4 + i] : s16[i];
-                        t4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+                        for (int i = 0; i < 2; i++) {
+                            const uint32_t send = up ? s16[i] : s16[2 + i], keep = up ? s16[2 + i] : s16[i];
+                            t2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+                        }
                     }
-                }
-                {
-                    const bool up = b & 2;  // keeps c >> 1 = b1
-#pragma unroll
+                    {
+                        const bool     up = b & 2;
+                        const uint32_t send = up ? t2[0] : t2[1], keep = up ? t2[1] : t2[0];
+                        t1 = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+                    }
+                    const int  xx = xb + 2 * (b & 1) + ((b >> 1) & 1);
+                    const bool ok = y < ny && xx >= 0 && xx < nx;
+                    if (ok) best32 = min(best32, t1 * 4096u + (uint32_t)(y * nx + xx));
+                    t1 += __shfl_xor_sync(0xffffffffu, t1, 4);
+                    t1 += __shfl_xor_sync(0xffffffffu, t1, 8);
+                    if (ok) best64 = min(best64, t1 * 4096u + (uint32_t)(y * nx + xx));
+                } else {
+                    uint32_t  s16[8];
+    #pragma unroll
+                    for (int y2 = 0; y2 < 2; y2++)
+    #pragma unroll
+                        for (int c = 0; c < 4; c++) {
+                            const int      xx = xb + c, y = yy + 2 * y2;
+                            const bool     valid = y < ny && xx >= 0 && xx < nx;
+                            const uint32_t ord = (uint32_t)(y * nx + xx);  // < 4096
+                            uint32_t       t = 0;
+    #pragma unroll
+                            for (int q = 0; q < 4; q++) {
+                                if (valid) best8[q] = min(best8[q], acc[y2][c][q] * 4096u + ord);
+                                t += acc[y2][c][q];
+                            }
+                            if (valid) best16 = min(best16, t * 4096u + ord);
+                            s16[y2 * 4 + c] = t;
+                        }
+                    // transposing butterfly over the 4 lanes of a 32x32 block, then over the 4 blocks: candidate e = y2 * 4 + c
+                    uint32_t t4[4], t2[2], t1;
+                    {
+                        const bool up = b & 1;  // keeps y2 = b0
+    #pragma unroll
+                        for (int i = 0; i < 4; i++) {
+                            const uint32_t send = up ? s16[i] : s16[4 + i], keep = up ? s16[4 + i] : s16[i];
+                            t4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+                        }
+                    }
+                    {
+                        const bool up = b & 2;  // keeps c >> 1 = b1
+    #pragma unroll
+                        for (int i = 0; i < 2; i++) {
+                            const uint32_t send = up ? t4[i] : t4[2 + i], keep = up ? t4[2 + i] : t4[i];
+                            t2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+                        }
+                    }
+                    const int  y32 = yy + 2 * (b & 1), x32 = xb + (b & 2);
+                    const bool yok = y32 < ny;
+    #pragma unroll
                     for (int i = 0; i < 2; i++) {
-                        const uint32_t send = up ? t4[i] : t4[2 + i], keep = up ? t4[2 + i] : t4[i];
-                        t2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+                        const int xx = x32 + i;
+                        if (yok && xx >= 0 && xx < nx) best32 = min(best32, t2[i] * 4096u + (uint32_t)(y32 * nx + xx));
                     }
-                }
-                const int  y32 = yy + 2 * (b & 1), x32 = xb + (b & 2);
-                const bool yok = y32 < ny;
-#pragma unroll
-                for (int i = 0; i < 2; i++) {
-                    const int xx = x32 + i;
-                    if (yok && xx >= 0 && xx < nx) best32 = min(best32, t2[i] * 4096u + (uint32_t)(y32 * nx + xx));
-                }
-                {
-                    const bool     up   = b & 4;  // keeps c & 1 = b2
-                    const uint32_t send = up ? t2[0] : t2[1], keep = up ? t2[1] : t2[0];
-                    t1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-                }
-                t1 += __shfl_xor_sync(0xffffffffu, t1, 8);
-                {
-                    const int xx = x32 + ((b >> 2) & 1);
-                    if (yok && xx >= 0 && xx < nx) best64 = min(best64, t1 * 4096u + (uint32_t)(y32 * nx + xx));
+                    {
+                        const bool     up   = b & 4;  // keeps c & 1 = b2
+                        const uint32_t send = up ? t2[0] : t2[1], keep = up ? t2[1] : t2[0];
+                        t1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+                    }
+                    t1 += __shfl_xor_sync(0xffffffffu, t1, 8);
+                    {
+                        const int xx = x32 + ((b >> 2) & 1);
+                        if (yok && xx >= 0 && xx < nx) best64 = min(best64, t1 * 4096u + (uint32_t)(y32 * nx + xx));
+                    }
                 }
                 g += kStWarps;
                 while (g >= ngroups) { g -= ngroups; k++; }
@@ -1500,14 +1554,14 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
         PH(0, 4)  // search (this warp)
         __syncthreads();
         PH(0, 5)  // waiting for the other warps
-        // sub-window keys -> job keys: (doubled SAD, raster index inside the job's window)
+        // sub-window keys -> job keys: (SAD -- doubled in sub-sampled mode --, raster index inside the job's window)
         for (int i = threadIdx.x; i < ns * kPus; i += blockDim.x) {
             const int      si = s_lo + i / kPus, pu = i - (i / kPus) * kPus;
             const uint32_t key = sub_key[si][pu];
             if (key == ~0u) continue;
             const FpSub   &u = subs[si];
             const uint32_t sad = key >> 12, ord = key & 4095u, y = ord / (uint32_t)u.nx, x = ord - y * (uint32_t)u.nx;
-            atomicMin(&fp_key[u.job][pu], ((unsigned long long)(sad << 1) << 32) | (uint32_t)((u.y0 + y) * jobs[u.job].w + u.x0 + x));
+            atomicMin(&fp_key[u.job][pu], ((unsigned long long)(FULL ? sad : sad << 1) << 32) | (uint32_t)((u.y0 + y) * jobs[u.job].w + u.x0 + x));
         }
         __syncthreads();  // the windows are reused by the next batch
         PH(0, 6)  // key fold
@@ -1537,7 +1591,8 @@ cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_
         cudaError_t e = cudaFuncSetAttribute(st_fp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStWarps * kFpWarpWin);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStWarps * kFpWarpWin);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(st_sad16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kS16BufWords * 4);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_sub_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpBufWords * 4);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_sub_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpBufWords * 4);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_sub_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpBufWords * 4);
         return e;
     }();
     if (attr != cudaSuccess) return attr;
@@ -1571,7 +1626,8 @@ cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_
                 else if (lvl == 2 && p.k.hme_search_method == 0 && !sad_old) st_sad16_kernel<<<n_sb, kStThreads, kS16BufWords * 4, st>>>(p);
                 else st_sad_kernel<<<n_sb, kStThreads, 0, st>>>(p, lvl);
             }
-            else if (p.k.me_search_method == 0 && !fp_old) st_fp_sub_kernel<<<n_sb, kStThreads, kFpBufWords * 4, st>>>(p);
+            else if (p.k.me_search_method == 0 && !fp_old) st_fp_sub_kernel<false><<<n_sb, kStThreads, kFpBufWords * 4, st>>>(p);
+            else if (!fp_old) st_fp_sub_kernel<true><<<n_sb, kStThreads, kFpBufWords * 4, st>>>(p);
             else if (p.k.me_search_method == 0) st_fp_kernel<true><<<n_sb, kStThreads, kStWarps * kFpWarpWin, st>>>(p);
             else st_fp_kernel<false><<<n_sb, kStThreads, kStWarps * kFpWarpWin, st>>>(p);
             mark(p.prog[i].kind == STEP_NXM ? "nxm" : p.prog[i].kind == STEP_SAD ? "sad" : "fp");
