@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=32, help="pictures of the workload timed on the host cores per step")
     ap.add_argument("--cpu-seconds", type=float, default=8.0, help="CPU-baseline budget of the default run (about this much work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--mode", default="me", choices=["me", "tf"],
+    ap.add_argument("--mode", default="me", choices=["me", "tf", "dg"],
                     help="me: the headline open-loop ME workload; tf: the temporal-filter (ME_MCTF) searches of the same "
                          "mini-GOP -- a secondary measurement of SURVEY section 8(f) rank 2, not the headline metric")
     ap.add_argument("--tf-window", type=int, default=3, help="tf mode: neighbouring pictures searched on each side of a centre")
@@ -98,9 +98,10 @@ class Workload:
 class ClockSampler(threading.Thread):
     """SM clock + throttle reasons of one GPU sampled through NVML while the timed region runs."""
 
-    def __init__(self, index):
+    def __init__(self, index, period=0.05):
         super().__init__(daemon=True)
         self.index, self.samples, self.reasons, self.max_mhz, self._halt = index, [], set(), None, threading.Event()
+        self.period = period
 
     def run(self):
         try:
@@ -116,7 +117,7 @@ class ClockSampler(threading.Thread):
                 for bit, n in names.items():
                     if bit and (r & bit) and n != "GpuIdle":
                         self.reasons.add(n)
-                time.sleep(0.05)
+                time.sleep(self.period)
         except Exception as ex:  # NVML missing: report that rather than invent clocks
             self.reasons.add("nvml_unavailable:%s" % type(ex).__name__)
 
@@ -223,12 +224,143 @@ def reference_arm(wl, n_pictures, steps, warmup, seconds=None):
                 len(sample), "all" if len(sample) == len(wl.pics) else idx, steps, dt, what, cores)}, dt
 
 
+DG_PAIRS = lambda gop: [(gop, 0), (gop, gop // 2), (gop // 2, 0)]  # noqa: E731  eval_sub_mini_gop (pd_process.c:682-705): (end, start), (end, mid), (mid, start)
+
+
+def dg_cpu_arm(frames, pairs, res, seconds, steps=None):
+    """The reference's own dg_detector_hme_level0 (oracle/_ref, AVX2 kernels) on the host cores: the picture pairs of the
+    workload run concurrently, one thread each, repeated over all cores (the reference splits a pair into 48 segments
+    over its ME threads instead; the work per pair is the same)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import refbind
+    from concurrent.futures import ThreadPoolExecutor
+    if refbind.have_reference():
+        ref, kind = refbind.Reference(), "reference"
+        what = "reference C sources compiled by oracle/Makefile, %s kernels" % ("AVX2" if ref.set_isa(1) == 1 else "C")
+    else:
+        ref, kind, what = refbind.Oracle(), "port", "oracle restatement (oracle/_ref not built)"
+    cores = os.cpu_count() or 1
+    need = sorted(set(p for pr in pairs for p in pr))
+    padded = {p: refbind.PaddedPicture(frames[p], p) for p in need}
+    for p in need:
+        ref.build_planes(padded[p], 1)
+    jobs = [pairs[i % len(pairs)] for i in range(max(cores, len(pairs)))]
+    t0, done = time.perf_counter(), 0
+    with ThreadPoolExecutor(cores) as ex:
+        while (steps is None and time.perf_counter() - t0 < seconds) or (steps is not None and done < steps * len(jobs)):
+            list(ex.map(lambda pr: ref.dg_hme_level0(padded[pr[0]], padded[pr[1]], res), jobs))
+            done += len(jobs)
+    dt = time.perf_counter() - t0
+    return {"value": done / dt, "unit": "picture pairs/s", "cores": cores, "kind": kind,
+            "sample": "%d pair searches in %.1f s, %d at a time, %s" % (done, dt, len(jobs), what)}, dt, done
+
+
+def main_dg(args, rank, local_rank, world):
+    """--mode dg: the dynamic-GOP detector's HME level 0 -- per mini-GOP the three picture
+    pairs eval_sub_mini_gop compares, each a 128 x 128 full-SAD search of every block's sixteenth-plane 16x16."""
+    from svtme import synth
+    w, h, gop = args.width, args.height, 1 << args.hier_levels
+    res = 0 if w * h <= 352 * 240 else 1 if w * h <= 640 * 360 else 2 if w * h <= 854 * 480 else 3 if w * h <= 1280 * 720 else 4 if w * h <= 1920 * 1080 else 5 if w * h <= 3840 * 2160 else 6
+    pairs = DG_PAIRS(gop)
+    need = sorted(set(p for pr in pairs for p in pr))
+    name = "%dx%d 8-bit synthetic, dynamic-GOP detector HME level 0 (16x16 full SAD, 128x128 window per 64x64 block), pairs (end,start) (end,mid) (mid,start) of a mini-GOP of %d" % (w, h, gop)
+    metric, unit = "DG-detector HME-L0 picture-pair searches/sec at 4K", "picture pairs"
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        clip = synth.make_clip(w, h, gop + 1, seed=100, kind="pan")
+        cb, dt, done = dg_cpu_arm(clip, pairs, res, None, steps=max(1, min(args.steps, 4)))
+        print(json.dumps({"impl": "reference", "metric": metric, "value": cb["value"], "unit": unit + "/s", "n_gpus": args.gpus,
+                          "steps": max(1, min(args.steps, 4)), "warmup": 0, "ms_per_step": 1e3 * dt / max(1, min(args.steps, 4)),
+                          "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                          "config": {"workload": name}, "cpu_baseline": cb,
+                          "e2e": {"value": cb["value"], "unit": unit + "/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return 0
+    import torch
+    from svtme import api, shard
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    clip = synth.make_clip(w, h, gop + 1, seed=100, kind="pan", first=rank * gop)
+    dev = api.MeDevice(device=local_rank, max_pictures=8)
+    h_luma = torch.empty((len(need), h, w), dtype=torch.uint8).pin_memory()
+    h_luma.numpy()[:] = np.stack([clip[p] for p in need])
+    d_luma = h_luma.cuda()
+    slot = {p: i for i, p in enumerate(need)}
+    stats = {"px": 0, "ms": 0.0, "n": 0}
+
+    def step(host):
+        pics = {p: (dev.register_ptr(h_luma.data_ptr() + slot[p] * w * h, w, w, h, p) if host else
+                    dev.register_device(d_luma.data_ptr() + slot[p] * w * h, w, w, h, p)) for p in need}
+        for a, b in pairs:
+            _, _, _, ms, px = dev.dg_hme_level0(pics[a], pics[b], res, per_block=False)
+            stats["px"] += px; stats["ms"] += ms; stats["n"] += 1
+        for p in pics.values():
+            p.release()
+
+    def timed(host, steps):
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step(host)
+        torch.cuda.synchronize()
+        e1.record()
+        torch.cuda.synchronize()
+        return shard.reduce_job(len(pairs) * steps, e0.elapsed_time(e1), dist, device="cuda")
+
+    for _ in range(max(3, args.warmup)):
+        step(False)
+    sampler = ClockSampler(local_rank, period=0.002)  # a step is well under a millisecond of device time
+    sampler.start()
+    time.sleep(0.01)
+    l0 = dev.launch_count()
+    stats.update(px=0, ms=0.0, n=0)
+    units, ms_dev = timed(False, args.steps)
+    launches = dev.launch_count() - l0
+    kern = dict(stats)
+    clocks = sampler.stop()
+    step(True)
+    _, ms_host = timed(True, args.steps)
+    if rank != 0:
+        return 0
+    sad_peak = dev.measure_sad_peak() * 4 / 1e3
+    ach = kern["px"] / (kern["ms"] * 1e-3) / 1e12
+    line = {"metric": metric, "value": units / (ms_dev * 1e-3), "unit": unit + "/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": name, "picture_pairs_per_step_per_gpu": len(pairs),
+                       "l2": "3 pictures re-uploaded / re-decimated per step; windows are re-read from L2 by design (8.6 G pixel-compares over 0.5 MB planes)"},
+            "e2e": {"value": units / (ms_host * 1e-3), "unit": unit + "/s", "h2d_bytes_per_step": len(need) * w * h,
+                    "d2h_bytes_per_step": 24 * len(pairs), "ms_per_step": ms_host / args.steps},
+            "gpu_launches": launches, "clocks": clocks,
+            "roofline": {"bound": "int", "kernel": "dg_hme_kernel (me_dg.cu)", "achieved": ach, "peak": sad_peak, "unit": "Tpx-compares/s",
+                         "frac": ach / sad_peak, "traffic": None, "px_compares_per_launch": kern["px"] / kern["n"],
+                         "avg_launch_ms": kern["ms"] / kern["n"], "launch": "one picture pair = one kernel, CUDA events on its stream inside the timed region",
+                         "peak_source": "VABSDIFF4.U8.ACC issue rate measured in this run (svtme_measure_sad_peak) x 4 px"}}
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"], _, _ = dg_cpu_arm(clip, pairs, res, args.cpu_seconds)
+    print(json.dumps(line))
+    dev.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
 
+    if args.mode == "dg":
+        return main_dg(args, rank, local_rank, world)
     if args.impl == "reference":
         if rank != 0:
             return 0

@@ -305,6 +305,24 @@ int32_t svtme_search_elapsed_ms(SvtMeHandle *h, uint64_t ticket, float *ms);
 /* Algorithmic work of a completed search: pixel-compares (block pixels x candidate positions summed over every SAD
  * evaluation the reference's svt_sad_loop_kernel / svt_nxm_sad_kernel / full-pel scan would perform). */
 int32_t svtme_search_px_compares(SvtMeHandle *h, uint64_t ticket, uint64_t *px_compares);
+/*
+ * Dynamic-GOP detector, HME level 0.  Replaces: the TASK_DG_DETECTOR_HME branch of the ME
+ * kernel thread (me_process.c:327-329) = dg_detector_hme_level0 (pd_process.c:493-590) for EVERY segment of the
+ * picture, with early_hme_b64 (:392-491): the 16x16 sixteenth-plane block of each 64x64 block of `src` is searched
+ * with full SAD over a 16 / 64 / 128-square window (input_resolution <= 360p / <= 480p / larger, :497-498) of `ref`'s
+ * sixteenth plane, and the picture-level DGDetectorMetrics (pcs.h:731-737) are accumulated on the device.
+ * Synchronous.  Optional outputs (may be NULL): sb_sad [b64] level-0 SAD, sb_mv [b64][2] = (col, row) in full-resolution
+ * pixels, elapsed_ms = device time of the search, px_compares = its algorithmic work.
+ */
+typedef struct SvtMeDgMetrics {
+    uint64_t tot_dist;        /* sum of the level-0 SADs */
+    uint32_t tot_cplx;        /* blocks with SAD > 16*16*30 */
+    uint32_t tot_active;      /* blocks with a non-zero vector */
+    int32_t  sum_in_vectors;  /* vectors pointing away from (+) / towards (-) the picture centre, per component */
+} SvtMeDgMetrics;
+int32_t svtme_dg_detector_hme_level0(SvtMeHandle *h, SvtMePic *src, SvtMePic *ref, uint32_t input_resolution,
+                                     SvtMeDgMetrics *metrics, uint32_t *sb_sad, int16_t *sb_mv, float *elapsed_ms,
+                                     uint64_t *px_compares);
 /* Diagnostic: measured peak issue rate of the packed-byte SAD instruction (VABSDIFF4.U8.ACC, 4 pixel-compares per
  * lane) on this device, in 1e9 instructions per second; the INT-roofline denominator of DESIGN.md. */
 int32_t svtme_measure_sad_peak(SvtMeHandle *h, double *gsad4_per_s);

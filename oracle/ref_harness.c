@@ -561,3 +561,50 @@ void svtref_build_planes(const SvtRefPic *pic, int hme_level1) {
     pcs.enable_hme_level1_flag = hme_level1 ? 1 : 0;
     svt_aom_downsample_filtering_input_picture(&pcs, &d[0], &d[1], &d[2]);
 }
+
+/* ---- dynamic-GOP detector HME level 0: the reference's own dg_detector_hme_level0 (pd_process.c:493-590), compiled from
+ * pd_process.c, driven as the TASK_DG_DETECTOR_HME branch of the ME kernel thread does (me_process.c:327-329) with one
+ * segment covering the picture.  The mutex / semaphore calls of that function become no-ops here (single thread). ---- */
+#include "reference_object.h"
+#include "object.h"
+EbErrorType svt_block_on_mutex(EbHandle mutex_handle) { (void)mutex_handle; return EB_ErrorNone; }
+EbErrorType svt_release_mutex(EbHandle mutex_handle) { (void)mutex_handle; return EB_ErrorNone; }
+EbErrorType svt_post_semaphore(EbHandle semaphore_handle) { (void)semaphore_handle; return EB_ErrorNone; }
+void        dg_detector_hme_level0(struct PictureParentControlSet *ppcs, uint32_t seg_idx);
+
+int svtref_dg_hme_level0(const SvtRefPic *src, const SvtRefPic *ref, uint32_t input_resolution, SvtMeDgMetrics *m) {
+    PictureParentControlSet *pcs[2];
+    EbPaReferenceObject     *obj[2];
+    EbObjectWrapper         *wr[2];
+    EbPictureBufferDesc      d[2];
+    SequenceControlSet      *scs = (SequenceControlSet *)calloc(1, sizeof(*scs));
+    DGDetectorSeg           *dg  = (DGDetectorSeg *)calloc(1, sizeof(*dg));
+    scs->b64_size = 64;
+    desc_from_plane(&d[0], &src->lvl[2]);
+    desc_from_plane(&d[1], &ref->lvl[2]);
+    for (int i = 0; i < 2; i++) {
+        pcs[i] = (PictureParentControlSet *)calloc(1, sizeof(PictureParentControlSet));
+        obj[i] = (EbPaReferenceObject *)calloc(1, sizeof(EbPaReferenceObject));
+        wr[i]  = (EbObjectWrapper *)calloc(1, sizeof(EbObjectWrapper));
+        obj[i]->sixteenth_downsampled_picture_ptr = &d[i];
+        wr[i]->object_ptr                         = obj[i];
+        pcs[i]->pa_ref_pic_wrapper                = wr[i];
+        pcs[i]->scs                               = scs;
+    }
+    pcs[0]->dg_detector              = dg;
+    dg->ref_pic                      = pcs[1];
+    pcs[0]->input_resolution         = (uint8_t)input_resolution;
+    pcs[0]->aligned_width            = (uint16_t)((src->lvl[0].width + 7) & ~7u);
+    pcs[0]->aligned_height           = (uint16_t)((src->lvl[0].height + 7) & ~7u);
+    pcs[0]->me_segments_column_count = 1;
+    pcs[0]->me_segments_row_count    = 1;
+    dg_detector_hme_level0(pcs[0], 0);
+    m->tot_dist       = dg->metrics.tot_dist;
+    m->tot_cplx       = dg->metrics.tot_cplx;
+    m->tot_active     = dg->metrics.tot_active;
+    m->sum_in_vectors = dg->metrics.sum_in_vectors;
+    const int done    = dg->metrics.seg_completed == 1;
+    for (int i = 0; i < 2; i++) { free(pcs[i]); free(obj[i]); free(wr[i]); }
+    free(scs); free(dg);
+    return done ? 0 : -1;
+}

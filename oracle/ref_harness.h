@@ -25,6 +25,8 @@ void     svtref_generate_padding(uint8_t *pic, uint32_t stride, uint32_t w, uint
 void     svtref_fullpel_search_sblock(const uint8_t *src, uint32_t src_stride, const uint8_t *ref, uint32_t ref_stride,
                                       int16_t x_org, int16_t y_org, uint32_t sa_w, uint32_t sa_h, uint8_t sub_sad,
                                       uint32_t *best_sad, uint32_t *best_mv);
+/* the reference's dg_detector_hme_level0 (pd_process.c:493) over the whole picture */
+int      svtref_dg_hme_level0(const SvtRefPic *src, const SvtRefPic *ref, uint32_t input_resolution, SvtMeDgMetrics *m);
 #ifdef __cplusplus
 }
 #endif

@@ -129,6 +129,26 @@ class _Binding:
         out._keep = (arr, refs, cur)
         return out
 
+    def dg_hme_level0(self, src, ref, input_resolution, per_block=True):
+        """dg_detector_hme_level0 over the whole picture: (metrics dict, sb_sad, sb_mv) -- the per-block arrays only from
+        the oracle restatement (the reference keeps the metrics only)."""
+        m = abi.DgMetrics()
+        n_b64 = ((src.width + 63) // 64) * ((src.height + 63) // 64)
+        if self.prefix == "svtorc_":
+            sad = np.zeros(n_b64, np.uint32)
+            mv = np.zeros((n_b64, 2), np.int16)
+            fn = self._f("dg_hme_level0")
+            fn.argtypes = [C.POINTER(RefPic), C.POINTER(RefPic), C.c_uint32, C.POINTER(abi.DgMetrics), C.c_void_p, C.c_void_p]
+            rc = fn(C.byref(src.struct), C.byref(ref.struct), input_resolution, C.byref(m), sad.ctypes.data, mv.ctypes.data)
+        else:
+            sad = mv = None
+            fn = self._f("dg_hme_level0")
+            fn.argtypes = [C.POINTER(RefPic), C.POINTER(RefPic), C.c_uint32, C.POINTER(abi.DgMetrics)]
+            rc = fn(C.byref(src.struct), C.byref(ref.struct), input_resolution, C.byref(m))
+        if rc != 0:
+            raise RuntimeError("dg_hme_level0 failed: %d" % rc)
+        return m.as_dict(), sad, mv
+
     def sad_loop_kernel(self, src, src_off, src_stride, ref, ref_off, ref_stride, bh, bw, raw_stride, skip, sa_w, sa_h):
         best = C.c_uint64(0)
         x = C.c_int16(-12345)

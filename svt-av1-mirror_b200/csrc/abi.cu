@@ -97,6 +97,12 @@ struct SvtMeHandle {
     size_t                 scratch_bytes = 0;
     uint32_t              *d_small = nullptr;
     float                  last_ms = 0.f;
+    // dynamic-GOP detector (svtme_dg_detector_hme_level0): its own stream, events and result arena
+    std::mutex             dg_mu;
+    cudaStream_t           dg_stream = nullptr;
+    cudaEvent_t            dg_e0 = nullptr, dg_e1 = nullptr;
+    uint8_t               *d_dg = nullptr, *h_dg = nullptr;
+    size_t                 dg_cap = 0;
 };
 
 namespace {
@@ -125,6 +131,8 @@ void plane_geometry(uint32_t w, uint32_t h, PlaneGeom g[3], size_t *total) {
     }
     *total = off;
 }
+
+inline size_t al4k(size_t v) { return (v + 4095) & ~size_t(4095); }
 
 int set_device(SvtMeHandle *h) {
     CK(cudaSetDevice(h->cfg.device));
@@ -415,6 +423,9 @@ void svtme_destroy(SvtMeHandle *h) {
     for (auto &b : h->free_bufs) { cudaFree(b.base); cudaEventDestroy(b.last_use); }
     if (h->d_scratch) cudaFree(h->d_scratch);
     if (h->d_small) cudaFree(h->d_small);
+    if (h->dg_stream) { cudaStreamDestroy(h->dg_stream); cudaEventDestroy(h->dg_e0); cudaEventDestroy(h->dg_e1); }
+    if (h->d_dg) cudaFree(h->d_dg);
+    if (h->h_dg) cudaFreeHost(h->h_dg);
     delete h;
 }
 
@@ -605,6 +616,58 @@ int32_t svtme_measure_sad_peak(SvtMeHandle *h, double *gsad4_per_s) {
     h->launches += 6;
     if (e != cudaSuccess) return fail(h, SVTME_ERR_UNDEFINED, "sad peak probe", e);
     *gsad4_per_s = (double)grid * 256 * iters * 32.0 / (best * 1e-3) / 1e9;
+    return SVTME_OK;
+}
+
+int32_t svtme_dg_detector_hme_level0(SvtMeHandle *h, SvtMePic *src, SvtMePic *ref, uint32_t input_resolution,
+                                     SvtMeDgMetrics *metrics, uint32_t *sb_sad, int16_t *sb_mv, float *elapsed_ms,
+                                     uint64_t *px_compares) {
+    if (!h || !src || !ref || !metrics) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    if (src->width != ref->width || src->height != ref->height) return fail(h, SVTME_ERR_BAD_PARAMETER, "reference size differs");
+    int rc = set_device(h);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(h->dg_mu);
+    const uint32_t aw = (src->width + 7) & ~7u, ah = (src->height + 7) & ~7u, wb = (aw + 63) / 64, hb = (ah + 63) / 64, n = wb * hb;
+    const size_t   off_sad = 256, off_mv = off_sad + al4k((size_t)n * 4), total = off_mv + al4k((size_t)n * 4);
+    if (!h->dg_stream) {
+        CK(cudaStreamCreateWithFlags(&h->dg_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreate(&h->dg_e0));
+        CK(cudaEventCreate(&h->dg_e1));
+    }
+    if (h->dg_cap < total) {
+        if (h->d_dg) cudaFree(h->d_dg);
+        if (h->h_dg) cudaFreeHost(h->h_dg);
+        h->d_dg = h->h_dg = nullptr; h->dg_cap = 0;
+        CK(cudaMalloc(&h->d_dg, total));
+        CK(cudaMallocHost(&h->h_dg, total));
+        h->dg_cap = total;
+    }
+    cudaStream_t st = h->dg_stream;
+    CK(cudaStreamWaitEvent(st, src->ready, 0));
+    CK(cudaStreamWaitEvent(st, ref->ready, 0));
+    CK(cudaMemsetAsync(h->d_dg, 0, sizeof(svtme::DgSums), st));
+    // search area of early_hme (pd_process.c:497-498)
+    const int sa = input_resolution <= SVTME_INPUT_SIZE_360p ? 16 : input_resolution <= SVTME_INPUT_SIZE_480p ? 64 : 128;
+    CK(cudaEventRecord(h->dg_e0, st));
+    CK(svtme::launch_dg_hme(src->dev.lvl[2], ref->dev.lvl[2], sa, wb, hb, reinterpret_cast<uint32_t *>(h->d_dg + off_sad),
+                            reinterpret_cast<int16_t *>(h->d_dg + off_mv), reinterpret_cast<svtme::DgSums *>(h->d_dg), st));
+    CK(cudaEventRecord(h->dg_e1, st));
+    CK(cudaMemcpyAsync(h->h_dg, h->d_dg, (sb_sad || sb_mv) ? total : 256, cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(src->buf.last_use, st));
+    CK(cudaEventRecord(ref->buf.last_use, st));
+    src->buf.used_once = ref->buf.used_once = true;
+    CK(cudaStreamSynchronize(st));
+    const svtme::DgSums *r = reinterpret_cast<const svtme::DgSums *>(h->h_dg);
+    metrics->tot_dist = r->tot_dist; metrics->tot_cplx = r->tot_cplx; metrics->tot_active = r->tot_active;
+    metrics->sum_in_vectors = r->sum_in_vectors;
+    if (sb_sad) memcpy(sb_sad, h->h_dg + off_sad, (size_t)n * 4);
+    if (sb_mv) memcpy(sb_mv, h->h_dg + off_mv, (size_t)n * 4);
+    if (px_compares) *px_compares = r->px_compares;
+    if (elapsed_ms) cudaEventElapsedTime(elapsed_ms, h->dg_e0, h->dg_e1);
+    {
+        std::lock_guard<std::mutex> lk2(h->mu);
+        h->launches += 1;
+    }
     return SVTME_OK;
 }
 

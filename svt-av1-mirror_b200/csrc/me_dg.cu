@@ -1,0 +1,137 @@
+// me_dg.cu -- dynamic-GOP detector, HME level 0.
+//
+// Reference: dg_detector_hme_level0 (pd_process.c:493-590) with early_hme_b64 (:392-491), run by the ME kernel
+// thread for TASK_DG_DETECTOR_HME messages (me_process.c:327-329): for every 64x64 block of the source picture, its
+// 16x16 block of the sixteenth plane is searched with FULL SAD over a 16 / 64 / 128-square window of the reference
+// picture's sixteenth plane (svt_sad_loop_kernel, compute_sad_c.c:58-101: first candidate in raster order wins on
+// strict '<'), and four picture-level sums (DGDetectorMetrics, pcs.h:731-737) are accumulated under a mutex.
+//
+// Here: one kernel over the picture, one CTA per 64x64 block.  Unlike the per-SB ME searches this one is large and
+// regular (128 x 128 candidates x 256 pixels = 4.2 M pixel-compares per block), so the kernel is built around the
+// VABSDIFF4 issue rate alone:
+//   * the window (<= 143 x 143 bytes) is staged once, byte-aligned on the way in (candidate 0 at byte 0 of a word);
+//   * an item = 4 x-adjacent candidates x R candidate rows.  The R rows share R + 15 window rows: each window row is
+//     loaded once (5 LDS), shifted once (12 SHF) and used by up to R block rows -> 64 R SADs per 5 (R + 15) LDS and
+//     12 (R + 15) SHF; R = 8: 2048 SADs, 115 LDS, 276 SHF (SAD = 84 % of the ALU-pipe instructions);
+//   * the 16x16 source block lives in 64 registers, the R x 4 accumulators in 32;
+//   * minima are kept as (sad << 14 | raster index): the reference's tie-break independent of the item order.
+#include <cuda_runtime.h>
+#include <cstdint>
+#include "me_engines.cuh"
+#include "me_launch.h"
+
+namespace svtme {
+
+constexpr int kDgThreads = 128;
+constexpr int kDgPitch   = 36;            // words per staged row: 32 groups of 4 candidates + the 4 words of the block width
+constexpr int kDgStrip   = 8;             // candidate rows per item
+constexpr int kDgRows    = 128 + 15 + kDgStrip;
+
+__global__ void __launch_bounds__(kDgThreads, 4)
+dg_hme_kernel(const DevPlane sp, const DevPlane rp, int sa0, uint32_t wb, uint32_t hb, uint32_t *sb_sad, int16_t *sb_mv, DgSums *out) {
+    extern __shared__ __align__(16) uint32_t dg_win[];  // kDgRows x kDgPitch
+    __shared__ uint32_t wbest[kDgThreads / 32];
+    const uint32_t xb = blockIdx.x % wb, yb = blockIdx.x / wb;
+    // early_hme_b64 (pd_process.c:406-452): the window is centred on the block; left / top clipping moves it without
+    // shrinking it (:415-418, 437-440), right / bottom clipping shrinks it, the width is then rounded down to 8
+    const int org_x = (int)(xb * 16), org_y = (int)(yb * 16);
+    int       sa_w = (sa0 + 7) & ~7, sa_h = sa0;
+    const int pad_w = rp.ref_org - 1, pad_h = rp.ref_org - 1;
+    int       ox = -(sa_w >> 1), oy = -(sa_h >> 1);
+    if (org_x + ox < -pad_w) ox = -pad_w - org_x;
+    if (org_x + ox > rp.width - 1) ox -= (org_x + ox) - (rp.width - 1);
+    if (org_x + ox + sa_w > rp.width) sa_w = max(1, sa_w - ((org_x + ox + sa_w) - rp.width));
+    sa_w = sa_w < 8 ? sa_w : sa_w & ~7;
+    if (org_y + oy < -pad_h) oy = -pad_h - org_y;
+    if (org_y + oy > rp.height - 1) oy -= (org_y + oy) - (rp.height - 1);
+    if (org_y + oy + sa_h > rp.height) sa_h = max(1, sa_h - ((org_y + oy + sa_h) - rp.height));
+
+    // the 16x16 source block (always 16x16: blocks cut by the picture edge read the padding, :524-536)
+    uint32_t       sreg[16][4];
+    const uint8_t *b0 = sp.org + (int64_t)org_y * sp.stride + org_x;
+#pragma unroll
+    for (int r = 0; r < 16; r++) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(b0 + (int64_t)r * sp.stride));
+        sreg[r][0] = v.x; sreg[r][1] = v.y; sreg[r][2] = v.z; sreg[r][3] = v.w;
+    }
+    // stage the window, byte-aligned: word (r, c) = window bytes 4c .. 4c + 3 of row r
+    const int ng = (sa_w + 3) >> 2, nwords = ng + 4, nrows = sa_h + 15;
+    {
+        const uint8_t *g  = rp.org + (int64_t)(org_y + oy) * rp.stride + (org_x + ox);
+        const int      a  = (int)((uintptr_t)g & 3);
+        const uint8_t *ga = g - a;
+        for (int idx = threadIdx.x; idx < nrows * nwords; idx += kDgThreads) {
+            const int       r = idx / nwords, c = idx - r * nwords;
+            const uint32_t *q = reinterpret_cast<const uint32_t *>(ga + (int64_t)r * rp.stride) + c;
+            dg_win[r * kDgPitch + c] = __funnelshift_r(__ldg(q), __ldg(q + 1), 8 * a);
+        }
+    }
+    __syncthreads();
+    const int nstrips = (sa_h + kDgStrip - 1) / kDgStrip, items = ng * nstrips;
+    uint32_t  best = ~0u;
+    for (int it = threadIdx.x; it < items; it += kDgThreads) {
+        const int       s = it / ng, g = it - s * ng;
+        const uint32_t *rowp = dg_win + (s * kDgStrip) * kDgPitch + g;
+        uint32_t        acc[kDgStrip][4];
+#pragma unroll
+        for (int y2 = 0; y2 < kDgStrip; y2++) acc[y2][0] = acc[y2][1] = acc[y2][2] = acc[y2][3] = 0;
+#pragma unroll
+        for (int rr = 0; rr < kDgStrip + 15; rr++) {
+            uint32_t w[5];
+#pragma unroll
+            for (int c = 0; c < 5; c++) w[c] = rowp[rr * kDgPitch + c];
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const uint32_t s0 = w[c], s1 = fsr(w[c], w[c + 1], 1), s2 = fsr(w[c], w[c + 1], 2), s3 = fsr(w[c], w[c + 1], 3);
+#pragma unroll
+                for (int y2 = 0; y2 < kDgStrip; y2++) {
+                    const int i = rr - y2;  // block row that meets window row rr for candidate row y2 of the strip
+                    if (i >= 0 && i < 16) {
+                        const uint32_t sw = sreg[i][c];
+                        acc[y2][0] = sad4(s0, sw, acc[y2][0]); acc[y2][1] = sad4(s1, sw, acc[y2][1]);
+                        acc[y2][2] = sad4(s2, sw, acc[y2][2]); acc[y2][3] = sad4(s3, sw, acc[y2][3]);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int y2 = 0; y2 < kDgStrip; y2++) {
+            const int y = s * kDgStrip + y2;
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (y < sa_h && 4 * g + k < sa_w) best = min(best, (acc[y2][k] << 14) | (uint32_t)(y * sa_w + 4 * g + k));
+        }
+    }
+    best = __reduce_min_sync(0xffffffffu, best);
+    if ((threadIdx.x & 31) == 0) wbest[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t b = wbest[0];
+#pragma unroll
+        for (int i = 1; i < kDgThreads / 32; i++) b = min(b, wbest[i]);
+        const uint32_t sad = b >> 14, idx = b & 0x3fffu;
+        const int      y = (int)idx / sa_w, x = (int)idx - y * sa_w;
+        const int16_t  col = (int16_t)((x + ox) * 4), row = (int16_t)((y + oy) * 4);  // :484-487
+        if (sb_sad) sb_sad[blockIdx.x] = sad;
+        if (sb_mv) { sb_mv[2 * blockIdx.x] = col; sb_mv[2 * blockIdx.x + 1] = row; }
+        // the picture-level metrics (:541-581)
+        int in = 0;
+        if (yb < hb / 2) in += row > 0 ? -1 : row < 0 ? 1 : 0;
+        else if (yb > hb / 2) in += row > 0 ? 1 : row < 0 ? -1 : 0;
+        if (xb < wb / 2) in += col > 0 ? -1 : col < 0 ? 1 : 0;
+        else if (xb > wb / 2) in += col > 0 ? 1 : col < 0 ? -1 : 0;
+        atomicAdd(&out->tot_dist, (unsigned long long)sad);
+        if (sad > 16 * 16 * 30) atomicAdd(&out->tot_cplx, 1u);
+        if (col != 0 || row != 0) atomicAdd(&out->tot_active, 1u);
+        if (in) atomicAdd(&out->sum_in_vectors, in);
+        atomicAdd(&out->px_compares, (unsigned long long)sa_w * (unsigned long long)sa_h * 256ull);
+    }
+}
+
+cudaError_t launch_dg_hme(const DevPlane &src16, const DevPlane &ref16, int sa, uint32_t wb, uint32_t hb, uint32_t *d_sb_sad,
+                          int16_t *d_sb_mv, DgSums *d_out, cudaStream_t st) {
+    dg_hme_kernel<<<wb * hb, kDgThreads, kDgRows * kDgPitch * 4, st>>>(src16, ref16, sa, wb, hb, d_sb_sad, d_sb_mv, d_out);
+    return cudaGetLastError();
+}
+
+}  // namespace svtme

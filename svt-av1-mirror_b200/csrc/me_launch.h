@@ -22,4 +22,14 @@ namespace svtme {
 // staged (picture-wide kernels) execution of the step program; p.states must hold staged_state_bytes(n_sb) bytes
 cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_launches);
 size_t      staged_state_bytes(uint32_t n_sb);
+// dynamic-GOP detector HME level 0 (me_dg.cu): picture-level sums accumulated by the kernel (zero them first)
+struct DgSums {
+    unsigned long long tot_dist;
+    uint32_t           tot_cplx, tot_active;
+    int32_t            sum_in_vectors;
+    uint32_t           pad_;
+    unsigned long long px_compares;
+};
+cudaError_t launch_dg_hme(const DevPlane &src16, const DevPlane &ref16, int sa, uint32_t wb, uint32_t hb, uint32_t *d_sb_sad,
+                          int16_t *d_sb_mv, DgSums *d_out, cudaStream_t st);
 }  // namespace svtme

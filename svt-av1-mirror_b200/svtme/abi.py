@@ -159,6 +159,14 @@ class PictureResults(C.Structure):
     ]
 
 
+class DgMetrics(C.Structure):
+    """SvtMeDgMetrics = DGDetectorMetrics of the reference (pcs.h:731-737) without the segment counter."""
+    _fields_ = [("tot_dist", C.c_uint64), ("tot_cplx", C.c_uint32), ("tot_active", C.c_uint32), ("sum_in_vectors", C.c_int32)]
+
+    def as_dict(self):
+        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+
+
 class DeviceCfg(C.Structure):
     _fields_ = [
         ("device", C.c_int32),

@@ -22,7 +22,7 @@ EXPORTS = [
     "svtme_picture_register_device", "svtme_picture_wait", "svtme_picture_read_plane", "svtme_picture_release",
     "svtme_picture_search", "svtme_search_wait", "svtme_picture_search_device", "svtme_search_elapsed_ms",
     "svtme_search_px_compares", "svtme_measure_sad_peak", "svtme_launch_count", "svtme_last_error", "svtme_cuda_sad_loop_kernel", "svtme_cuda_downsample_2d",
-    "svtme_cuda_nxm_sad_kernel", "svtme_cuda_fullpel_search_sblock",
+    "svtme_cuda_nxm_sad_kernel", "svtme_cuda_fullpel_search_sblock", "svtme_dg_detector_hme_level0",
 ]
 
 
@@ -83,6 +83,8 @@ def load_library():
     lib.svtme_cuda_fullpel_search_sblock.argtypes = [vp, u8p, u32, u8p, u32, C.c_int16, C.c_int16, u32, u32, C.c_uint8,
                                                      vp, vp]
     lib.svtme_cuda_fullpel_search_sblock.restype = None
+    lib.svtme_dg_detector_hme_level0.argtypes = [vp, vp, vp, u32, C.POINTER(abi.DgMetrics), vp, vp, C.POINTER(C.c_float),
+                                                 C.POINTER(u64)]
     _lib = lib
     return lib
 
@@ -241,6 +243,19 @@ class MeDevice:
         out.px_compares = self.px_compares(t)
         out.kernel_ms = self.elapsed_ms(t)
         return out
+
+    def dg_hme_level0(self, src, ref, input_resolution, per_block=True):
+        """Dynamic-GOP detector HME level 0 of picture `src` against `ref` (dg_detector_hme_level0, pd_process.c:493):
+        (metrics dict, sb_sad, sb_mv, device ms, pixel-compares)."""
+        n_b64 = ((src.width + 63) // 64) * ((src.height + 63) // 64)
+        m, ms, px = abi.DgMetrics(), C.c_float(), C.c_uint64()
+        sad = np.zeros(n_b64, np.uint32) if per_block else None
+        mv = np.zeros((n_b64, 2), np.int16) if per_block else None
+        self._check(self.lib.svtme_dg_detector_hme_level0(self.h, src.ptr, ref.ptr, input_resolution, C.byref(m),
+                                                          sad.ctypes.data if per_block else None,
+                                                          mv.ctypes.data if per_block else None, C.byref(ms), C.byref(px)),
+                    "svtme_dg_detector_hme_level0")
+        return m.as_dict(), sad, mv, ms.value, px.value
 
     def measure_sad_peak(self):
         """Peak VABSDIFF4 rate of this GPU in 1e9 instructions/s (x4 = pixel-compares)."""
