@@ -60,10 +60,13 @@ dg_hme_kernel(const DevPlane sp, const DevPlane rp, int sa0, uint32_t wb, uint32
         const uint8_t *g  = rp.org + (int64_t)(org_y + oy) * rp.stride + (org_x + ox);
         const int      a  = (int)((uintptr_t)g & 3);
         const uint8_t *ga = g - a;
-        for (int idx = threadIdx.x; idx < nrows * nwords; idx += kDgThreads) {
-            const int       r = idx / nwords, c = idx - r * nwords;
-            const uint32_t *q = reinterpret_cast<const uint32_t *>(ga + (int64_t)r * rp.stride) + c;
-            dg_win[r * kDgPitch + c] = __funnelshift_r(__ldg(q), __ldg(q + 1), 8 * a);
+        // flat over (row, word) with the constant pitch as the divisor (a full window has nwords == kDgPitch)
+        for (int idx = threadIdx.x; idx < nrows * kDgPitch; idx += kDgThreads) {
+            const int r = idx / kDgPitch, c = idx - r * kDgPitch;
+            if (c < nwords) {
+                const uint32_t *q = reinterpret_cast<const uint32_t *>(ga + (int64_t)r * rp.stride) + c;
+                dg_win[idx] = __funnelshift_r(__ldg(q), __ldg(q + 1), 8 * a);
+            }
         }
     }
     __syncthreads();
@@ -94,12 +97,25 @@ dg_hme_kernel(const DevPlane sp, const DevPlane rp, int sa0, uint32_t wb, uint32
                 }
             }
         }
+        // keys (sad << 14 | raster index); items that lie wholly inside the window (all of them for an interior block)
+        // skip the per-candidate bounds tests
+        const int ybase = s * kDgStrip, xbase = 4 * g;
+        if (ybase + kDgStrip <= sa_h && xbase + 4 <= sa_w) {
 #pragma unroll
-        for (int y2 = 0; y2 < kDgStrip; y2++) {
-            const int y = s * kDgStrip + y2;
+            for (int y2 = 0; y2 < kDgStrip; y2++) {
+                const uint32_t o = (uint32_t)((ybase + y2) * sa_w + xbase);
+                const uint32_t k0 = acc[y2][0] * 16384u + o, k1 = acc[y2][1] * 16384u + (o + 1), k2 = acc[y2][2] * 16384u + (o + 2),
+                               k3 = acc[y2][3] * 16384u + (o + 3);
+                best = min(min(best, k0), min(min(k1, k2), k3));
+            }
+        } else {
 #pragma unroll
-            for (int k = 0; k < 4; k++)
-                if (y < sa_h && 4 * g + k < sa_w) best = min(best, (acc[y2][k] << 14) | (uint32_t)(y * sa_w + 4 * g + k));
+            for (int y2 = 0; y2 < kDgStrip; y2++) {
+                const int y = ybase + y2;
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    if (y < sa_h && xbase + k < sa_w) best = min(best, (acc[y2][k] << 14) | (uint32_t)(y * sa_w + xbase + k));
+            }
         }
     }
     best = __reduce_min_sync(0xffffffffu, best);
