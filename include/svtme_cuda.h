@@ -209,6 +209,13 @@ typedef struct SvtMePictureResults {
     uint8_t  *tf_exit_sb;                  /* [b64] 1: search_results[0][0].hme_sad < tf_me_exit_th, the integer search
                                             * was skipped and tf_use_pred_64x64_only_th = 0xFF (motion_estimation.c:3109) */
     uint32_t *tf_blk_counts;               /* [2] tf_tot_horz_blks, tf_tot_vert_blks of this picture pair (:2469-2474) */
+    /* Optional (may be NULL; not in temporal-filter mode): the picture-level sums the ME kernel thread's consumers
+     * loop over the per-block arrays for, accumulated on the device:
+     *   [0] sum of me_8x8_distortion        -> Initial RC: norm_me_dist = [0] / b64_total_count (initial_rc_process.c:683-691)
+     *   [1] sum of rc_me_distortion         -> global_me.c:162-168: total_me_sad = (uint32_t)[1] (the reference sums in 32 bits)
+     *   [2] sum of stationary_block_present_sb -> total_stationary_sb
+     *   [3] sum of rc_me_allow_gm           -> total_gm_sbs */
+    uint64_t *picture_sums;                /* [4] */
 } SvtMePictureResults;
 
 typedef struct SvtMeDeviceCfg {

@@ -475,6 +475,20 @@ static void *ref_worker(void *arg) {
     return NULL;
 }
 
+/* Picture-level sums (SvtMePictureResults.picture_sums): the loops of Initial RC (initial_rc_process.c:683-691) and of
+ * svt_aom_global_motion_estimation (global_me.c:162-168) over the per-block arrays of a completed picture. */
+static void picture_sums(const SvtMeKnobs *k, SvtMePictureResults *out, uint32_t n_b64) {
+    if (!out->picture_sums || k->me_type == SVTME_ME_MCTF) return;
+    uint64_t dist = 0, me_sad = 0, stat = 0, gm = 0;
+    for (uint32_t b = 0; b < n_b64; b++) {
+        dist += out->me_8x8_distortion[b];
+        me_sad += out->rc_me_distortion[b];
+        stat += out->stationary_block_present_sb[b];
+        gm += out->rc_me_allow_gm[b];
+    }
+    out->picture_sums[0] = dist; out->picture_sums[1] = me_sad; out->picture_sums[2] = stat; out->picture_sums[3] = gm;
+}
+
 int svtref_me_picture(const SvtMeKnobs *k, const SvtRefPic *cur, const SvtRefPic *refs, SvtMePictureResults *out,
                       int n_threads) {
     const uint32_t W = cur->lvl[0].width, H = cur->lvl[0].height;
@@ -538,6 +552,7 @@ int svtref_me_picture(const SvtMeKnobs *k, const SvtRefPic *cur, const SvtRefPic
     for (int t = 1; t < n_threads; t++) pthread_create(&th[t], NULL, ref_worker, &job);
     ref_worker(&job);
     for (int t = 1; t < n_threads; t++) pthread_join(th[t], NULL);
+    picture_sums(k, out, wb * hb);
     free(pcs->b64_geom);
     free(sbr);
     free(med->me_results);

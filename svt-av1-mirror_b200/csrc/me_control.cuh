@@ -758,7 +758,7 @@ SVTME_HD void cand_one_pu(const MeParams &p, SbState &s, const SbOut &o, unsigne
 }
 
 // ---- compute_distortion (:2964-3007); leader only ----
-SVTME_HD void compute_distortion(const MeParams &p, const SbState &s) {
+SVTME_HD void compute_distortion(const MeParams &p, const SbState &s, uint32_t sums[4]) {
     const uint32_t i = s.b64_index;
     uint32_t d64 = s.me_distortion[0], d32 = 0, d16 = 0, d8 = 0;
     for (int j = 0; j < 4; j++) d32 += s.me_distortion[1 + j];
@@ -777,11 +777,13 @@ SVTME_HD void compute_distortion(const MeParams &p, const SbState &s) {
     p.out.me_32x32_distortion[i]  = (d32 * 4096u) / pix;
     p.out.me_16x16_distortion[i]  = (d16 * 4096u) / pix;
     p.out.me_8x8_distortion[i]    = (d8 * 4096u) / pix;
+    sums[0] = (d8 * 4096u) / pix;
+    sums[1] = (p.k.input_resolution <= SVTME_INPUT_SIZE_480p) ? d8 : d16;
 }
 
 // ---- perform_gm_detection (:2838-2961); leader only.  n indexes BOTH the raster-ordered candidate array and the
 // tier-zero-ordered p_sb_best_mv, exactly as the reference does. ----
-SVTME_HD void gm_detection(const MeParams &p, const SbState &s, const SbOut &o) {
+SVTME_HD void gm_detection(const MeParams &p, const SbState &s, const SbOut &o, uint32_t sums[4]) {
     const SvtMeKnobs &k = p.k;
     uint32_t stationary = 0, tot = 0;
     uint8_t  cnt[kMaxLists][kMaxRefs][2][2];
@@ -824,12 +826,12 @@ SVTME_HD void gm_detection(const MeParams &p, const SbState &s, const SbOut &o) 
         if (SVTME_ABS(mx) <= st && SVTME_ABS(my) <= st) stationary++;
         tot++;
     }
-    if (stationary > ((tot * 5) / 100)) p.out.stationary_block_present_sb[s.b64_index] = 1;
+    if (stationary > ((tot * 5) / 100)) { p.out.stationary_block_present_sb[s.b64_index] = 1; sums[2] = 1; }
     for (int l = 0; l < kMaxLists; l++)
         for (int r = 0; r < kMaxRefs; r++)
             for (int c = 0; c < 2; c++)
                 for (int q = 0; q < 2; q++)
-                    if (cnt[l][r][c][q] > (tot / 2)) p.out.rc_me_allow_gm[s.b64_index] = 1;
+                    if (cnt[l][r][c][q] > (tot / 2)) { p.out.rc_me_allow_gm[s.b64_index] = 1; sums[3] = 1; }
 }
 
 // ---- the step program: svt_aom_motion_estimation_b64 (:3076-3153) for ME_OPEN_LOOP with hme_b64 (:2441-2475) and
@@ -910,10 +912,25 @@ SVTME_HD void sb_results(B &be, const MeParams &p, SbState &s, uint32_t b64_inde
     for (unsigned n = be.tid(); n < k.max_number_of_pus_per_sb; n += be.nthreads()) cand_one_pu(p, s, o, n);
     be.sync();
     if (be.leader()) {
-        compute_distortion(p, s);
+        uint32_t sums[4] = {0, 0, 0, 0};
+        compute_distortion(p, s, sums);
         p.out.stationary_block_present_sb[b64_index] = 0;
         p.out.rc_me_allow_gm[b64_index]              = 0;
-        if (k.gm_enabled) gm_detection(p, s, o);
+        if (k.gm_enabled) gm_detection(p, s, o, sums);
+        if (p.out.picture_sums) {
+            // what Initial RC (initial_rc_process.c:683-691) and svt_aom_global_motion_estimation (global_me.c:162-168)
+            // sum over the per-block arrays once the picture is complete
+            unsigned long long *ps = p.out.picture_sums;
+#ifdef __CUDA_ARCH__
+            ps += (b64_index % kSumSlots) * kSumSlotWords;
+            if (sums[0]) atomicAdd(ps + 0, (unsigned long long)sums[0]);
+            if (sums[1]) atomicAdd(ps + 1, (unsigned long long)sums[1]);
+            if (sums[2]) atomicAdd(ps + 2, 1ull);
+            if (sums[3]) atomicAdd(ps + 3, 1ull);
+#else
+            for (int i = 0; i < 4; i++) ps[i] += sums[i];
+#endif
+        }
     }
 }
 

@@ -54,7 +54,12 @@ struct DevResults {
     int16_t  *hme_sc;                    // optional
     uint8_t  *tf_exit_sb;                // temporal-filter mode only
     uint32_t *tf_blk_counts;             // temporal-filter mode only: [horz, vert]
+    // optional: sums of me_8x8_distortion, rc_me_distortion, stationary blocks, GM votes.  On the device kSumSlots partial
+    // sums, 64 bytes apart (block b adds into slot b % kSumSlots): 2040 blocks adding into ONE address serialise in L2 for
+    // ~16 us; the host adds the slots up.  The host emulation uses slot 0 only.
+    unsigned long long *picture_sums;
 };
+constexpr int kSumSlots = 64, kSumSlotWords = 8;
 
 // One step of the per-SB program (me_control.cuh: build_program)
 struct Step {

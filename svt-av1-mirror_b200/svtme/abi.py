@@ -156,6 +156,7 @@ class PictureResults(C.Structure):
         ("hme_sc", C.POINTER(C.c_int16)),
         ("tf_exit_sb", C.POINTER(C.c_uint8)),
         ("tf_blk_counts", C.POINTER(C.c_uint32)),
+        ("picture_sums", C.POINTER(C.c_uint64)),
     ]
 
 
@@ -212,6 +213,7 @@ class ResultBuffers:
                 self.arrays[n] = alloc((n_b64,), np.uint32)
             for n in self.SCALARS8:
                 self.arrays[n] = alloc((n_b64,), np.uint8)
+            self.arrays["picture_sums"] = alloc((4,), np.uint64)
         if extended or knobs.me_type == ME_MCTF:
             self.arrays["sb_best_sad"] = alloc((n_b64, 2, 4, 85), np.uint32)
             self.arrays["sb_best_mv"] = alloc((n_b64, 2, 4, 85), np.uint32)

@@ -106,3 +106,43 @@ def test_gpu_per_block_outputs_are_optional(dev, oracle):
     a, b = dev.register(frames[1], 1), dev.register(frames[0], 0)
     m, sad, mv, _, _ = dev.dg_hme_level0(a, b, 3, per_block=False)
     assert m == want and sad is None and mv is None
+
+
+# ---- picture-level sums of the ME results ----
+def _sums_of(res):
+    return [int(res["me_8x8_distortion"].astype(np.uint64).sum()), int(res["rc_me_distortion"].astype(np.uint64).sum()),
+            int(res["stationary_block_present_sb"].sum()), int(res["rc_me_allow_gm"].sum())]
+
+
+@pytest.mark.parametrize("enc_mode", [4, 10])
+def test_picture_sums_reference_and_oracle(reference, oracle, enc_mode):
+    """picture_sums = what Initial RC (norm_me_dist, initial_rc_process.c:683-691) and svt_aom_global_motion_estimation
+    (total_me_sad / total_stationary_sb / total_gm_sbs, global_me.c:162-168) sum over the per-block arrays."""
+    w, h, n = 448, 264, 5
+    _, pr = H.make_pictures(reference, w, h, n, seed=21, kind="pan")
+    _, po = H.make_pictures(oracle, w, h, n, seed=21, kind="pan")
+    k = H.preset_knobs(reference, enc_mode, w, h, 2, 1)
+    l0, l1 = H.ref_lists(2, n, k.num_of_ref_pic_to_search[0], k.num_of_ref_pic_to_search[1])
+    a = reference.me_picture(k, pr[2], H.refs_dict(pr, l0, l1), n_threads=2)
+    b = oracle.me_picture(k, po[2], H.refs_dict(po, l0, l1), n_threads=2)
+    assert a["picture_sums"].tolist() == _sums_of(a) == b["picture_sums"].tolist()
+    assert a["picture_sums"][0] > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pipeline", [0, 1], ids=["staged", "persistent"])
+def test_gpu_picture_sums(oracle, pipeline):
+    w, h, n = 832, 488, 5
+    frames, po = H.make_pictures(oracle, w, h, n, seed=22, kind="pan")
+    k = api.derive_knobs(enc_mode=6, qp=35, frame_rate_q16=30 << 16, width=w, height=h, hierarchical_levels=3,
+                         picture_number=2, temporal_layer_index=1, is_ref=1, slice_type_b=1)
+    l0, l1 = H.ref_lists(2, n, k.num_of_ref_pic_to_search[0], k.num_of_ref_pic_to_search[1])
+    want = oracle.me_picture(k, po[2], H.refs_dict(po, l0, l1), n_threads=8)
+    d = api.MeDevice(device=0, pipeline=pipeline)
+    try:
+        pd = [d.register(f, i) for i, f in enumerate(frames)]
+        for rep in range(2):  # the sums are re-zeroed per search
+            got = d.me_picture(k, pd[2], H.refs_dict(pd, l0, l1), extended=False)
+            assert got["picture_sums"].tolist() == want["picture_sums"].tolist() == _sums_of(got)
+    finally:
+        d.close()
