@@ -219,6 +219,27 @@ def test_picture_other_sizes(oracle, dev, size, enc_mode):
         p.release()
 
 
+@pytest.mark.parametrize("size,enc_mode,hl,bits", [((3840, 2160), 6, 5, 8), ((3840, 2160), 6, 5, 10), ((7680, 4320), 8, 4, 8)],
+                         ids=["4K-M6", "4K-M6-10bit", "8K-M8"])
+def test_picture_full_size(oracle, size, enc_mode, hl, bits):
+    """BASELINE configs 3, 4 and 5 at their full picture sizes (2040 / 8160 blocks, partial last block row): every output
+    byte and the work counter against the oracle.  10-bit input: the search runs on the 8-bit MSB plane."""
+    w, h = size
+    n = 4
+    frames, po = H.make_pictures(oracle, w, h, n, seed=33, kind="pan")
+    d = api.MeDevice(device=0, max_pictures=8)
+    try:
+        if bits == 10:
+            rng = np.random.default_rng(1)
+            up = [(f.astype(np.uint16) << 2) | rng.integers(0, 4, f.shape, dtype=np.uint16) for f in frames]
+        else:
+            up = frames
+        pd = [d.register(f, i) for i, f in enumerate(up)]
+        _run_case(oracle, d, po, pd, dict(enc_mode=enc_mode, tl=2, hl=hl), 2, w, h, n)
+    finally:
+        d.close()
+
+
 def test_async_pipeline_and_buffer_reuse(oracle, dev, clips):
     """Several searches in flight + picture buffers recycled through the pool give the same results."""
     po, pd = clips["pan"]
