@@ -330,6 +330,23 @@ typedef struct SvtMeDgMetrics {
 int32_t svtme_dg_detector_hme_level0(SvtMeHandle *h, SvtMePic *src, SvtMePic *ref, uint32_t input_resolution,
                                      SvtMeDgMetrics *metrics, uint32_t *sb_sad, int16_t *sb_mv, float *elapsed_ms,
                                      uint64_t *px_compares);
+/*
+ * Picture-analysis statistics on the sixteenth plane (second half).  Replaces: the
+ * histogram part of svt_aom_gathering_picture_statistics (pic_analysis_process.c:1559-1577) =
+ * sub_sample_luma_generate_pixel_intensity_histogram_bins (:1461-1524) with calculate_histogram (:166-184): per region
+ * of the regions_per_width x regions_per_height grid (4 x 4 for pictures of at least 64 x 64, enc_handle.c:4221-4224;
+ * the last row / column of regions takes the remainder) a 256-bin histogram of every decim_step-th pixel of every
+ * decim_step-th row of the sixteenth plane (decim_step 1 with scene-change detection, else 4), bins starting at 1 and
+ * scaled by 16 * decim_step^2, the rounded average intensity of the region, and the picture's avg_luma.  The plane is the
+ * one svtme_picture_register built, so nothing is uploaded.  Synchronous.
+ */
+typedef struct SvtMePicStats {
+    uint32_t picture_histogram[4][4][256];          /* [region_in_picture_width_index][region_in_picture_height_index][bin] */
+    uint64_t average_intensity_per_region[4][4];
+    uint64_t avg_luma;
+} SvtMePicStats;
+int32_t svtme_picture_statistics(SvtMeHandle *h, SvtMePic *pic, uint32_t regions_per_width, uint32_t regions_per_height,
+                                 uint32_t decim_step, SvtMePicStats *out);
 /* Diagnostic: measured peak issue rate of the packed-byte SAD instruction (VABSDIFF4.U8.ACC, 4 pixel-compares per
  * lane) on this device, in 1e9 instructions per second; the INT-roofline denominator of DESIGN.md. */
 int32_t svtme_measure_sad_peak(SvtMeHandle *h, double *gsad4_per_s);

@@ -623,3 +623,35 @@ int svtref_dg_hme_level0(const SvtRefPic *src, const SvtRefPic *ref, uint32_t in
     free(scs); free(dg);
     return done ? 0 : -1;
 }
+
+/* ---- picture-analysis statistics: the reference's svt_aom_gathering_picture_statistics (pic_analysis_process.c:1559)
+ * with calc_hist set and the variance pass off; decim_step 1 <=> scene_change_detection (:1492) ---- */
+void svt_aom_gathering_picture_statistics(SequenceControlSet *scs, PictureParentControlSet *pcs,
+                                          EbPictureBufferDesc *input_padded_pic,
+                                          EbPictureBufferDesc *sixteenth_decimated_picture_ptr);
+int svtref_picture_statistics(const SvtRefPic *pic, uint32_t rw_n, uint32_t rh_n, uint32_t step, SvtMePicStats *out) {
+    if (rw_n < 1 || rw_n > 4 || rh_n < 1 || rh_n > 4 || (step != 1 && step != 4)) return -1;
+    SequenceControlSet      *scs = (SequenceControlSet *)calloc(1, sizeof(*scs));
+    PictureParentControlSet *pcs = (PictureParentControlSet *)calloc(1, sizeof(*pcs));
+    EbPictureBufferDesc      d[2];
+    uint32_t                *rows[4][4], **cols[4];
+    desc_from_plane(&d[0], &pic->lvl[0]);
+    desc_from_plane(&d[1], &pic->lvl[2]);
+    scs->calc_hist                                     = 1;
+    scs->calculate_variance                            = 0;
+    scs->static_config.scene_change_detection          = step == 1;
+    scs->picture_analysis_number_of_regions_per_width  = rw_n;
+    scs->picture_analysis_number_of_regions_per_height = rh_n;
+    for (int a = 0; a < 4; a++) {
+        for (int b = 0; b < 4; b++) rows[a][b] = out->picture_histogram[a][b];
+        cols[a] = rows[a];
+    }
+    memset(out, 0, sizeof(*out));
+    pcs->picture_histogram = cols;
+    svt_aom_gathering_picture_statistics(scs, pcs, &d[0], &d[1]);
+    for (uint32_t a = 0; a < rw_n; a++)
+        for (uint32_t b = 0; b < rh_n; b++) out->average_intensity_per_region[a][b] = pcs->average_intensity_per_region[a][b];
+    out->avg_luma = pcs->avg_luma;
+    free(pcs); free(scs);
+    return 0;
+}

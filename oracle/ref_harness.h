@@ -27,6 +27,8 @@ void     svtref_fullpel_search_sblock(const uint8_t *src, uint32_t src_stride, c
                                       uint32_t *best_sad, uint32_t *best_mv);
 /* the reference's dg_detector_hme_level0 (pd_process.c:493) over the whole picture */
 int      svtref_dg_hme_level0(const SvtRefPic *src, const SvtRefPic *ref, uint32_t input_resolution, SvtMeDgMetrics *m);
+/* the reference's svt_aom_gathering_picture_statistics (pic_analysis_process.c:1559), histogram part */
+int      svtref_picture_statistics(const SvtRefPic *pic, uint32_t regions_w, uint32_t regions_h, uint32_t decim_step, SvtMePicStats *out);
 #ifdef __cplusplus
 }
 #endif

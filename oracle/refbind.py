@@ -149,6 +149,16 @@ class _Binding:
             raise RuntimeError("dg_hme_level0 failed: %d" % rc)
         return m.as_dict(), sad, mv
 
+    def picture_statistics(self, pic, regions_w=4, regions_h=4, decim_step=4):
+        """(histogram [4][4][256], average_intensity_per_region [4][4], avg_luma) of the sixteenth plane."""
+        st = abi.PicStats()
+        fn = self._f("picture_statistics")
+        fn.argtypes = [C.POINTER(RefPic), C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(abi.PicStats)]
+        rc = fn(C.byref(pic.struct), regions_w, regions_h, decim_step, C.byref(st))
+        if rc != 0:
+            raise RuntimeError("picture_statistics failed: %d" % rc)
+        return st.as_arrays()
+
     def sad_loop_kernel(self, src, src_off, src_stride, ref, ref_off, ref_stride, bh, bw, raw_stride, skip, sa_w, sa_h):
         best = C.c_uint64(0)
         x = C.c_int16(-12345)

@@ -683,6 +683,61 @@ int32_t svtme_dg_detector_hme_level0(SvtMeHandle *h, SvtMePic *src, SvtMePic *re
     return SVTME_OK;
 }
 
+int32_t svtme_picture_statistics(SvtMeHandle *h, SvtMePic *pic, uint32_t regions_per_width, uint32_t regions_per_height,
+                                 uint32_t decim_step, SvtMePicStats *out) {
+    if (!h || !pic || !out) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    if (regions_per_width < 1 || regions_per_width > 4 || regions_per_height < 1 || regions_per_height > 4 || decim_step < 1 ||
+        (pic->width >> 2) < regions_per_width || (pic->height >> 2) < regions_per_height)
+        return fail(h, SVTME_ERR_BAD_PARAMETER, "regions / decim_step");
+    int rc = set_device(h);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(h->dg_mu);
+    const size_t total = al4k(sizeof(svtme::StatAcc));
+    if (!h->dg_stream) {
+        CK(cudaStreamCreateWithFlags(&h->dg_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreate(&h->dg_e0));
+        CK(cudaEventCreate(&h->dg_e1));
+    }
+    if (h->dg_cap < total) {
+        if (h->d_dg) cudaFree(h->d_dg);
+        if (h->h_dg) cudaFreeHost(h->h_dg);
+        h->d_dg = h->h_dg = nullptr; h->dg_cap = 0;
+        CK(cudaMalloc(&h->d_dg, total));
+        CK(cudaMallocHost(&h->h_dg, total));
+        h->dg_cap = total;
+    }
+    cudaStream_t st = h->dg_stream;
+    CK(cudaStreamWaitEvent(st, pic->ready, 0));
+    CK(cudaMemsetAsync(h->d_dg, 0, sizeof(svtme::StatAcc), st));
+    CK(svtme::launch_hist16(pic->dev.lvl[2], (int)regions_per_width, (int)regions_per_height, (int)decim_step,
+                            reinterpret_cast<svtme::StatAcc *>(h->d_dg), st));
+    CK(cudaMemcpyAsync(h->h_dg, h->d_dg, sizeof(svtme::StatAcc), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(pic->buf.last_use, st));
+    pic->buf.used_once = true;
+    CK(cudaStreamSynchronize(st));
+    // the reference's scaling and rounding (pic_analysis_process.c:1480, 1504-1521)
+    const svtme::StatAcc *a = reinterpret_cast<const svtme::StatAcc *>(h->h_dg);
+    const uint32_t pw = pic->width >> 2, ph = pic->height >> 2, region_w = pw / regions_per_width, region_h = ph / regions_per_height;
+    const uint32_t scale = 4 * 4 * decim_step * decim_step;
+    memset(out, 0, sizeof(*out));
+    uint64_t total_sum = 0;
+    for (uint32_t wi = 0; wi < regions_per_width; wi++)
+        for (uint32_t hi = 0; hi < regions_per_height; hi++) {
+            const uint32_t w = region_w + (wi == regions_per_width - 1 ? pw - regions_per_width * region_w : 0);
+            const uint32_t hh = region_h + (hi == regions_per_height - 1 ? ph - regions_per_height * region_h : 0);
+            for (int b = 0; b < 256; b++) out->picture_histogram[wi][hi][b] = (1u + a->hist[wi * 4 + hi][b]) * scale;
+            const uint64_t sum = a->sum[wi * 4 + hi] * (uint64_t)decim_step * decim_step;
+            out->average_intensity_per_region[wi][hi] = (uint8_t)((sum + ((w * hh) >> 1)) / (w * hh));
+            total_sum += sum;
+        }
+    out->avg_luma = total_sum / ((uint64_t)pw * ph);
+    {
+        std::lock_guard<std::mutex> lk2(h->mu);
+        h->launches += 1;
+    }
+    return SVTME_OK;
+}
+
 const char *svtme_last_error(SvtMeHandle *h) { return h ? h->err.c_str() : "null handle"; }
 
 // ---- RTCD-level entry points: host pointers, synchronous.  Inputs are copied into an aligned device scratch. ----

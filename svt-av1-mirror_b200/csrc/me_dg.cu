@@ -151,3 +151,49 @@ cudaError_t launch_dg_hme(const DevPlane &src16, const DevPlane &ref16, int sa, 
 }
 
 }  // namespace svtme
+
+// ---- picture-analysis statistics on the sixteenth plane (second half) ----
+// sub_sample_luma_generate_pixel_intensity_histogram_bins (pic_analysis_process.c:1461-1524) with calculate_histogram
+// (:166-184): per region a 256-bin count of every step-th pixel of every step-th row, and their sum.  One CTA per
+// (region, row slice): counts in shared memory, one global atomic per non-empty bin at the end.  The host applies the
+// reference's "+1, x 16 step^2" scaling and the rounded averages (svtme_picture_statistics, abi.cu).  HBM-bound and tiny
+// (0.5 MB at 4K).
+namespace svtme {
+
+__global__ void __launch_bounds__(256) hist16_kernel(const DevPlane p, int rw_n, int rh_n, int step, StatAcc *acc) {
+    __shared__ uint32_t           h[256];
+    __shared__ unsigned long long ssum;
+    const int wi = blockIdx.x / rh_n, hi = blockIdx.x - wi * rh_n;
+    const int region_w = p.width / rw_n, region_h = p.height / rh_n;
+    const int w = region_w + (wi == rw_n - 1 ? p.width - rw_n * region_w : 0);
+    const int hh = region_h + (hi == rh_n - 1 ? p.height - rh_n * region_h : 0);
+    h[threadIdx.x] = 0;
+    if (threadIdx.x == 0) ssum = 0;
+    __syncthreads();
+    const uint8_t *s = p.org + (int64_t)(hi * region_h) * p.stride + wi * region_w;
+    const int      nsx = (w + step - 1) / step, nsy = (hh + step - 1) / step;
+    uint32_t       sum = 0;  // <= 255 x samples of this thread
+    for (int sy = blockIdx.y; sy < nsy; sy += gridDim.y) {
+        const uint8_t *row = s + (int64_t)(sy * step) * p.stride;
+        for (int sx = threadIdx.x; sx < nsx; sx += blockDim.x) {
+            const uint32_t v = row[sx * step];
+            atomicAdd(&h[v], 1u);
+            sum += v;
+        }
+    }
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if ((threadIdx.x & 31) == 0 && sum) atomicAdd(&ssum, (unsigned long long)sum);
+    __syncthreads();
+    const int r = wi * 4 + hi;
+    if (h[threadIdx.x]) atomicAdd(&acc->hist[r][threadIdx.x], h[threadIdx.x]);
+    if (threadIdx.x == 0 && ssum) atomicAdd(&acc->sum[r], ssum);
+}
+
+cudaError_t launch_hist16(const DevPlane &p16, int rw_n, int rh_n, int step, StatAcc *d_acc, cudaStream_t st) {
+    const int nsy = (p16.height / rh_n + step - 1) / step;
+    dim3      grid((unsigned)(rw_n * rh_n), (unsigned)max(1, min(32, nsy / 4)));
+    hist16_kernel<<<grid, 256, 0, st>>>(p16, rw_n, rh_n, step, d_acc);
+    return cudaGetLastError();
+}
+
+}  // namespace svtme

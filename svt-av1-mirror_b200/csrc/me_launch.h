@@ -30,6 +30,12 @@ struct DgSums {
     uint32_t           pad_;
     unsigned long long px_compares;
 };
+// picture-analysis histograms of the sixteenth plane (me_dg.cu): raw counts / sums per region [wi * 4 + hi] (zero them first)
+struct StatAcc {
+    uint32_t           hist[16][256];
+    unsigned long long sum[16];
+};
+cudaError_t launch_hist16(const DevPlane &p16, int rw_n, int rh_n, int step, StatAcc *d_acc, cudaStream_t st);
 cudaError_t launch_dg_hme(const DevPlane &src16, const DevPlane &ref16, int sa, uint32_t wb, uint32_t hb, uint32_t *d_sb_sad,
                           int16_t *d_sb_mv, DgSums *d_out, cudaStream_t st);
 }  // namespace svtme

@@ -168,6 +168,16 @@ class DgMetrics(C.Structure):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
 
 
+class PicStats(C.Structure):
+    """SvtMePicStats: per-region histograms / average intensities of the sixteenth plane and the picture's avg_luma."""
+    _fields_ = [("picture_histogram", ((C.c_uint32 * 256) * 4) * 4), ("average_intensity_per_region", (C.c_uint64 * 4) * 4),
+                ("avg_luma", C.c_uint64)]
+
+    def as_arrays(self):
+        return (np.ctypeslib.as_array(self.picture_histogram).copy(), np.ctypeslib.as_array(self.average_intensity_per_region).copy(),
+                int(self.avg_luma))
+
+
 class DeviceCfg(C.Structure):
     _fields_ = [
         ("device", C.c_int32),

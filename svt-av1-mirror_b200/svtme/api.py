@@ -23,6 +23,7 @@ EXPORTS = [
     "svtme_picture_search", "svtme_search_wait", "svtme_picture_search_device", "svtme_search_elapsed_ms",
     "svtme_search_px_compares", "svtme_measure_sad_peak", "svtme_launch_count", "svtme_last_error", "svtme_cuda_sad_loop_kernel", "svtme_cuda_downsample_2d",
     "svtme_cuda_nxm_sad_kernel", "svtme_cuda_fullpel_search_sblock", "svtme_dg_detector_hme_level0",
+    "svtme_picture_statistics",
 ]
 
 
@@ -85,6 +86,7 @@ def load_library():
     lib.svtme_cuda_fullpel_search_sblock.restype = None
     lib.svtme_dg_detector_hme_level0.argtypes = [vp, vp, vp, u32, C.POINTER(abi.DgMetrics), vp, vp, C.POINTER(C.c_float),
                                                  C.POINTER(u64)]
+    lib.svtme_picture_statistics.argtypes = [vp, vp, u32, u32, u32, C.POINTER(abi.PicStats)]
     _lib = lib
     return lib
 
@@ -256,6 +258,14 @@ class MeDevice:
                                                           mv.ctypes.data if per_block else None, C.byref(ms), C.byref(px)),
                     "svtme_dg_detector_hme_level0")
         return m.as_dict(), sad, mv, ms.value, px.value
+
+    def picture_statistics(self, pic, regions_w=4, regions_h=4, decim_step=4):
+        """Histograms / average intensities of the picture's sixteenth plane (svt_aom_gathering_picture_statistics,
+        pic_analysis_process.c:1559): (histogram [4][4][256], average_intensity_per_region [4][4], avg_luma)."""
+        st = abi.PicStats()
+        self._check(self.lib.svtme_picture_statistics(self.h, pic.ptr, regions_w, regions_h, decim_step, C.byref(st)),
+                    "svtme_picture_statistics")
+        return st.as_arrays()
 
     def measure_sad_peak(self):
         """Peak VABSDIFF4 rate of this GPU in 1e9 instructions/s (x4 = pixel-compares)."""

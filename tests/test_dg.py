@@ -146,3 +146,46 @@ def test_gpu_picture_sums(oracle, pipeline):
             assert got["picture_sums"].tolist() == want["picture_sums"].tolist() == _sums_of(got)
     finally:
         d.close()
+
+
+# ---- picture-analysis statistics on the sixteenth plane (second half) ----
+STAT_CASES = [(448, 264, "pan"), (1280, 720, "pan"), (320, 184, "zero"), (1920, 1080, "noise"), (72, 136, "pan")]
+
+
+@pytest.mark.parametrize("case", STAT_CASES, ids=lambda c: "%dx%d-%s" % c)
+def test_picture_statistics_oracle_matches_reference(reference, oracle, case):
+    """svt_aom_gathering_picture_statistics (pic_analysis_process.c:1559) of the compiled reference vs the restatement."""
+    w, h, kind = case
+    _, pr = H.make_pictures(reference, w, h, 1, seed=w, kind=kind)
+    _, po = H.make_pictures(oracle, w, h, 1, seed=w, kind=kind)
+    for step in (1, 4):
+        for rw, rh in ((4, 4), (1, 1), (2, 3)):
+            a, b = reference.picture_statistics(pr[0], rw, rh, step), oracle.picture_statistics(po[0], rw, rh, step)
+            assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and a[2] == b[2], (case, step, rw, rh)
+
+
+def test_picture_statistics_properties(oracle):
+    """Bins start at 1 and are scaled by 16 step^2: with step 1 the bins of a region sum to 16 (256 + its pixels)."""
+    w, h = 448, 264
+    _, po = H.make_pictures(oracle, w, h, 1, seed=3, kind="pan")
+    hist, avg, luma = oracle.picture_statistics(po[0], 4, 4, 1)
+    rw, rh = (w // 4) // 4, (h // 4) // 4
+    assert int(hist[0][0].sum()) == 16 * (256 + rw * rh)
+    assert int(hist.sum()) == 16 * (16 * 256 + (w // 4) * (h // 4))
+    assert abs(luma - float(po[0].interior(2).mean())) <= 1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", STAT_CASES + [(3840, 2160, "pan"), (64, 64, "noise")], ids=lambda c: "%dx%d-%s" % c)
+def test_gpu_picture_statistics(dev, oracle, case):
+    w, h, kind = case
+    frames, po = H.make_pictures(oracle, w, h, 1, seed=w, kind=kind)
+    pic = dev.register(frames[0], 0)
+    try:
+        for step in (1, 4):
+            for rw, rh in ((4, 4), (1, 1), (2, 3)):
+                a, b = oracle.picture_statistics(po[0], rw, rh, step), dev.picture_statistics(pic, rw, rh, step)
+                assert np.array_equal(a[0], b[0]), (case, step, rw, rh, np.argwhere(a[0] != b[0])[:4].tolist())
+                assert np.array_equal(a[1], b[1]) and a[2] == b[2], (case, step, rw, rh)
+    finally:
+        pic.release()
