@@ -17,6 +17,7 @@
 //   * minima are kept as (sad << 14 | raster index): the reference's tie-break independent of the item order.
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <cstdio>
 #include "me_engines.cuh"
 #include "me_launch.h"
 
@@ -65,6 +66,16 @@ dg_hme_kernel(const DevPlane sp, const DevPlane rp, int sa0, uint32_t wb, uint32
             const int r = idx / kDgPitch, c = idx - r * kDgPitch;
             if (c < nwords) {
                 const uint32_t *q = reinterpret_cast<const uint32_t *>(ga + (int64_t)r * rp.stride) + c;
+#ifdef SVTME_BOUNDS  // diagnostics build: both words must lie inside the plane's physical padding (32 pixels at this level)
+                {
+                    const int64_t off = reinterpret_cast<const uint8_t *>(q) - (rp.org - 32 * (int64_t)rp.stride - 32);  // from the padded origin
+                    const int64_t y = off / rp.stride - 32, x = off % rp.stride - 32;
+                    if (off < 0 || y >= rp.height + 32 || x + 8 > rp.width + 32) {
+                        printf("svtme bounds: dg window word at (%lld, %lld) outside the padded %d x %d plane\n", (long long)x, (long long)y, rp.width, rp.height);
+                        __trap();
+                    }
+                }
+#endif
                 dg_win[idx] = __funnelshift_r(__ldg(q), __ldg(q + 1), 8 * a);
             }
         }
