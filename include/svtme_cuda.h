@@ -216,6 +216,11 @@ typedef struct SvtMePictureResults {
      *   [2] sum of stationary_block_present_sb -> total_stationary_sb
      *   [3] sum of rc_me_allow_gm           -> total_gm_sbs */
     uint64_t *picture_sums;                /* [4] */
+    /* Optional, temporal-filter mode only: the [0][0] rows of sb_best_sad / sb_best_mv alone -- all the filter reads (one
+     * reference per search).  A caller that passes these and leaves sb_best_sad / sb_best_mv NULL gets 0.7 KB per block
+     * copied back instead of 5.4 KB. */
+    uint32_t *tf_best_sad;                 /* [b64][85] p_sb_best_sad[0][0] */
+    uint32_t *tf_best_mv;                  /* [b64][85] p_sb_best_mv[0][0] */
 } SvtMePictureResults;
 
 typedef struct SvtMeDeviceCfg {

@@ -457,6 +457,8 @@ static void *ref_worker(void *arg) {
         if (out->tf_exit_sb) out->tf_exit_sb[sb] = ctx->tf_use_pred_64x64_only_th == (uint8_t)~0;
         if (out->sb_best_sad) memcpy(out->sb_best_sad + (size_t)sb * 2 * 4 * 85, ctx->p_sb_best_sad, sizeof(uint32_t) * 2 * 4 * 85);
         if (out->sb_best_mv) memcpy(out->sb_best_mv + (size_t)sb * 2 * 4 * 85, ctx->p_sb_best_mv, sizeof(uint32_t) * 2 * 4 * 85);
+        if (out->tf_best_sad) memcpy(out->tf_best_sad + (size_t)sb * 85, ctx->p_sb_best_sad[0][0], sizeof(uint32_t) * 85);
+        if (out->tf_best_mv) memcpy(out->tf_best_mv + (size_t)sb * 85, ctx->p_sb_best_mv[0][0], sizeof(uint32_t) * 85);
         for (int li = 0; li < 2; li++)
             for (int ri = 0; ri < 4; ri++) {
                 int used = li < k->num_of_list_to_search && ri < k->num_of_ref_pic_to_search[li];

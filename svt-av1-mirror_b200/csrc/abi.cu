@@ -55,11 +55,11 @@ struct SvtMePic {
 namespace {
 
 struct ResultLayout {
-    size_t   off[18];
-    size_t   bytes[18];
+    size_t   off[20];
+    size_t   bytes[20];
     size_t   total;
 };
-enum { R_MV, R_CAND, R_COUNT, R_D64, R_D32, R_D16, R_D8, R_VAR, R_RC, R_STAT, R_GM, R_SAD, R_BMV, R_DOREF, R_HMESC, R_TFEXIT, R_TFCNT, R_PSUM, R_N };
+enum { R_MV, R_CAND, R_COUNT, R_D64, R_D32, R_D16, R_D8, R_VAR, R_RC, R_STAT, R_GM, R_SAD, R_BMV, R_DOREF, R_HMESC, R_TFEXIT, R_TFCNT, R_PSUM, R_TFSAD, R_TFMV, R_N };
 
 struct Inflight {
     cudaStream_t        stream = nullptr;
@@ -204,11 +204,11 @@ void result_layout(uint32_t n_b64, uint32_t pu_count, const SvtMeKnobs &k, bool 
     const size_t n = n_b64;
     size_t sz[R_N] = {n * pu_count * k.max_refs * 4, n * pu_count * k.max_cand, n * pu_count, n * 4, n * 4, n * 4, n * 4,
                       n * 4, n * 4, n, n, extended ? n * 680 * 4 : 0, extended ? n * 680 * 4 : 0, extended ? n * 8 : 0,
-                      extended ? n * 16 * 2 : 0, 0, 0, (size_t)svtme::kSumSlots * svtme::kSumSlotWords * 8};
+                      extended ? n * 16 * 2 : 0, 0, 0, (size_t)svtme::kSumSlots * svtme::kSumSlotWords * 8, 0, 0};
     if (k.me_type == SVTME_ME_MCTF) {
         // the temporal filter reads no candidates or statistics (motion_estimation.c:3126): only MVs / SADs / centres
         for (int i = R_MV; i <= R_GM; i++) sz[i] = 0;
-        sz[R_TFEXIT] = n; sz[R_TFCNT] = 8; sz[R_PSUM] = 0;
+        sz[R_TFEXIT] = n; sz[R_TFCNT] = 8; sz[R_PSUM] = 0; sz[R_TFSAD] = sz[R_TFMV] = n * 85 * 4;
     }
     size_t off = 0;
     for (int i = 0; i < R_N; i++) {
@@ -308,6 +308,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     }
     if (knobs->me_type == SVTME_ME_MCTF) {
         p.out.tf_exit_sb = d + L.off[R_TFEXIT]; p.out.tf_blk_counts = (uint32_t *)(d + L.off[R_TFCNT]);
+        p.out.tf_best_sad = (uint32_t *)(d + L.off[R_TFSAD]); p.out.tf_best_mv = (uint32_t *)(d + L.off[R_TFMV]);
     } else {
         p.out.picture_sums = (unsigned long long *)(d + L.off[R_PSUM]);
     }
@@ -332,7 +333,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
         void *dst[R_N] = {out->me_mv, out->me_cand, out->total_me_candidate_index, out->me_64x64_distortion, out->me_32x32_distortion,
                           out->me_16x16_distortion, out->me_8x8_distortion, out->me_8x8_cost_variance, out->rc_me_distortion,
                           out->stationary_block_present_sb, out->rc_me_allow_gm, out->sb_best_sad, out->sb_best_mv, out->do_ref, out->hme_sc,
-                          out->tf_exit_sb, out->tf_blk_counts, out->picture_sums};
+                          out->tf_exit_sb, out->tf_blk_counts, out->picture_sums, out->tf_best_sad, out->tf_best_mv};
         size_t lo = L.total, hi = 0;
         for (int i = 0; i < R_N && e == cudaSuccess; i++) {
             sl->direct[i] = false;
@@ -518,8 +519,9 @@ int32_t svtme_picture_release(SvtMeHandle *h, SvtMePic *pic) {
 int32_t svtme_picture_search(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
                              const SvtMeKnobs *knobs, SvtMePictureResults *out, uint64_t *ticket) {
     if (out && knobs && knobs->me_type == SVTME_ME_MCTF) {
-        if (!out->sb_best_mv || !out->sb_best_sad || !out->hme_sc || !out->tf_exit_sb || !out->tf_blk_counts)
-            return fail(h, SVTME_ERR_BAD_PARAMETER, "temporal-filter mode needs sb_best_mv, sb_best_sad, hme_sc, tf_exit_sb and tf_blk_counts");
+        const bool full = out->sb_best_mv && out->sb_best_sad, compact = out->tf_best_mv && out->tf_best_sad;
+        if (!(full || compact) || !out->hme_sc || !out->tf_exit_sb || !out->tf_blk_counts)
+            return fail(h, SVTME_ERR_BAD_PARAMETER, "temporal-filter mode needs sb_best_mv + sb_best_sad (or tf_best_mv + tf_best_sad), hme_sc, tf_exit_sb and tf_blk_counts");
         return search_impl(h, cur, refs, knobs, out, 0, true, ticket);
     }
     if (!out || !out->me_mv || !out->me_cand || !out->total_me_candidate_index || !out->me_64x64_distortion ||
@@ -561,7 +563,7 @@ int32_t svtme_search_wait(SvtMeHandle *h, uint64_t ticket) {
         void *dst[R_N] = {u.me_mv, u.me_cand, u.total_me_candidate_index, u.me_64x64_distortion, u.me_32x32_distortion,
                           u.me_16x16_distortion, u.me_8x8_distortion, u.me_8x8_cost_variance, u.rc_me_distortion,
                           u.stationary_block_present_sb, u.rc_me_allow_gm, u.sb_best_sad, u.sb_best_mv, u.do_ref, u.hme_sc,
-                          u.tf_exit_sb, u.tf_blk_counts, u.picture_sums};
+                          u.tf_exit_sb, u.tf_blk_counts, u.picture_sums, u.tf_best_sad, u.tf_best_mv};
         for (int i = 0; i < R_N; i++)
             if (dst[i] && L.bytes[i] && !sl->direct[i]) {
                 if (i == R_PSUM) {  // the device keeps kSumSlots partial sums (me_types.cuh)

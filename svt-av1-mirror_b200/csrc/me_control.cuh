@@ -958,6 +958,10 @@ SVTME_HD void sb_finish(B &be, const MeParams &p, SbState &s, uint32_t b64_index
         for (uint32_t i = be.tid(); i < kMaxLists * kMaxRefs * kPus; i += be.nthreads()) p.out.sb_best_sad[(size_t)b64_index * 680 + i] = (&s.best_sad[0][0][0])[i];
     if (p.out.sb_best_mv)
         for (uint32_t i = be.tid(); i < kMaxLists * kMaxRefs * kPus; i += be.nthreads()) p.out.sb_best_mv[(size_t)b64_index * 680 + i] = (&s.best_mv[0][0][0])[i];
+    if (p.out.tf_best_sad)
+        for (uint32_t i = be.tid(); i < kPus; i += be.nthreads()) p.out.tf_best_sad[(size_t)b64_index * kPus + i] = s.best_sad[0][0][i];
+    if (p.out.tf_best_mv)
+        for (uint32_t i = be.tid(); i < kPus; i += be.nthreads()) p.out.tf_best_mv[(size_t)b64_index * kPus + i] = s.best_mv[0][0][i];
     if (be.leader()) {
         for (int li = 0; li < kMaxLists; li++)
             for (int ri = 0; ri < kMaxRefs; ri++) {

@@ -58,6 +58,7 @@ struct DevResults {
     // sums, 64 bytes apart (block b adds into slot b % kSumSlots): 2040 blocks adding into ONE address serialise in L2 for
     // ~16 us; the host adds the slots up.  The host emulation uses slot 0 only.
     unsigned long long *picture_sums;
+    uint32_t *tf_best_sad, *tf_best_mv;  // optional, temporal-filter mode: [b64][85] = the [0][0] rows of sb_best_sad / sb_best_mv
 };
 constexpr int kSumSlots = 64, kSumSlotWords = 8;
 

@@ -157,6 +157,8 @@ class PictureResults(C.Structure):
         ("tf_exit_sb", C.POINTER(C.c_uint8)),
         ("tf_blk_counts", C.POINTER(C.c_uint32)),
         ("picture_sums", C.POINTER(C.c_uint64)),
+        ("tf_best_sad", C.POINTER(C.c_uint32)),
+        ("tf_best_mv", C.POINTER(C.c_uint32)),
     ]
 
 
@@ -207,7 +209,7 @@ class ResultBuffers:
                  "me_8x8_cost_variance", "rc_me_distortion")
     SCALARS8 = ("stationary_block_present_sb", "rc_me_allow_gm")
 
-    def __init__(self, n_b64, knobs, extended=True, pinned_alloc=None):
+    def __init__(self, n_b64, knobs, extended=True, pinned_alloc=None, tf_compact=False):
         self.n_b64 = n_b64
         self.pu_count = pu_count_of(knobs)
         mr, mc = max(1, knobs.max_refs), max(1, knobs.max_cand)
@@ -224,9 +226,13 @@ class ResultBuffers:
             for n in self.SCALARS8:
                 self.arrays[n] = alloc((n_b64,), np.uint8)
             self.arrays["picture_sums"] = alloc((4,), np.uint64)
+        if knobs.me_type == ME_MCTF and tf_compact:  # only what the temporal filter reads
+            self.arrays["tf_best_sad"] = alloc((n_b64, 85), np.uint32)
+            self.arrays["tf_best_mv"] = alloc((n_b64, 85), np.uint32)
         if extended or knobs.me_type == ME_MCTF:
-            self.arrays["sb_best_sad"] = alloc((n_b64, 2, 4, 85), np.uint32)
-            self.arrays["sb_best_mv"] = alloc((n_b64, 2, 4, 85), np.uint32)
+            if not (knobs.me_type == ME_MCTF and tf_compact):
+                self.arrays["sb_best_sad"] = alloc((n_b64, 2, 4, 85), np.uint32)
+                self.arrays["sb_best_mv"] = alloc((n_b64, 2, 4, 85), np.uint32)
             self.arrays["do_ref"] = alloc((n_b64, 2, 4), np.uint8)
             self.arrays["hme_sc"] = alloc((n_b64, 2, 4, 2), np.int16)
             if knobs.me_type == ME_MCTF:

@@ -203,11 +203,11 @@ class MeDevice:
             arr[li * 4 + ri] = p.ptr
         return arr
 
-    def search_async(self, knobs, cur, refs, out=None, extended=False, alloc=None):
+    def search_async(self, knobs, cur, refs, out=None, extended=False, alloc=None, tf_compact=False):
         """refs: {(list, idx): Picture}.  Returns (ticket, ResultBuffers)."""
         n_b64 = ((cur.width + 63) // 64) * ((cur.height + 63) // 64)
         if out is None:
-            out = abi.ResultBuffers(n_b64, knobs, extended=extended, pinned_alloc=alloc)
+            out = abi.ResultBuffers(n_b64, knobs, extended=extended, pinned_alloc=alloc, tf_compact=tf_compact)
         arr = self._refs_array(refs)
         ticket = C.c_uint64()
         self._check(self.lib.svtme_picture_search(self.h, cur.ptr, C.byref(arr), C.byref(knobs), C.byref(out.struct),

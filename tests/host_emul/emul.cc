@@ -117,6 +117,7 @@ extern "C" int svtemu_me_picture(const SvtMeKnobs *k, const SvtRefPic *cur, cons
     p.out.stationary_block_present_sb = out->stationary_block_present_sb; p.out.rc_me_allow_gm = out->rc_me_allow_gm;
     p.out.sb_best_sad = out->sb_best_sad; p.out.sb_best_mv = out->sb_best_mv; p.out.do_ref = out->do_ref; p.out.hme_sc = out->hme_sc;
     p.out.tf_exit_sb = out->tf_exit_sb; p.out.tf_blk_counts = out->tf_blk_counts;
+    p.out.tf_best_sad = out->tf_best_sad; p.out.tf_best_mv = out->tf_best_mv;
     if (out->tf_blk_counts) out->tf_blk_counts[0] = out->tf_blk_counts[1] = 0;
     p.out.picture_sums = k->me_type == SVTME_ME_MCTF ? nullptr : (unsigned long long *)out->picture_sums;
     if (p.out.picture_sums) memset(p.out.picture_sums, 0, 32);

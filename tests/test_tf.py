@@ -130,3 +130,38 @@ def test_gpu_matches_oracle(oracle, gpu_clip, pipeline, level, exit_th, dist):
     for n in TF_ARRAYS:
         assert np.array_equal(want[n], got[n]), (n, np.argwhere(want[n] != got[n])[:5].tolist())
     assert int(got["tf_blk_counts"].sum()) == got.n_b64
+
+
+def test_compact_outputs_oracle_and_reference(reference, oracle, clips):
+    """tf_best_sad / tf_best_mv = the [0][0] rows of sb_best_sad / sb_best_mv."""
+    pr, po = clips["pan"]
+    k = tf_knobs(reference, 2, 256)
+    for b, pics in ((reference, pr), (oracle, po)):
+        full = b.me_picture(k, pics[3], {(0, 0): pics[2]}, n_threads=2)
+        out = abi.ResultBuffers(full.n_b64, k, tf_compact=True)
+        arr = (refbind.RefPic * 8)()
+        arr[0] = pics[2].struct
+        assert b._f("me_picture")(C.byref(k), C.byref(pics[3].struct), arr, C.byref(out.struct), 2) == 0
+        assert "sb_best_sad" not in out.arrays
+        assert np.array_equal(out["tf_best_sad"], full["sb_best_sad"][:, 0, 0]) and np.array_equal(out["tf_best_mv"], full["sb_best_mv"][:, 0, 0])
+        assert np.array_equal(out["tf_exit_sb"], full["tf_exit_sb"]) and np.array_equal(out["hme_sc"], full["hme_sc"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pipeline", [0, 1], ids=["staged", "persistent"])
+def test_gpu_compact_outputs(oracle, gpu_clip, pipeline):
+    frames, po = gpu_clip
+    k = api.derive_tf_knobs(hme_me_level=2, qp_opt=1, me_exit_th=256, qp=35, width=GW, height=GH, picture_number=3,
+                            temporal_layer_index=0, is_ref=1)
+    want = oracle.me_picture(k, po[3], {(0, 0): po[1]}, n_threads=8)
+    dev = api.MeDevice(device=0, pipeline=pipeline)
+    try:
+        cur, ref = dev.register(frames[3], 3), dev.register(frames[1], 1)
+        t, got = dev.search_async(k, cur, {(0, 0): ref}, tf_compact=True)
+        dev.wait(t)
+    finally:
+        dev.close()
+    assert "sb_best_sad" not in got.arrays
+    assert np.array_equal(got["tf_best_sad"], want["sb_best_sad"][:, 0, 0]) and np.array_equal(got["tf_best_mv"], want["sb_best_mv"][:, 0, 0])
+    for n in ("hme_sc", "tf_exit_sb", "tf_blk_counts"):
+        assert np.array_equal(got[n], want[n]), n
