@@ -267,3 +267,49 @@ def test_errors_are_loud(dev, clips):
         dev.me_picture(k, pd[4], {})  # missing references
     with pytest.raises(api.SvtMeError):
         dev.register(np.zeros((30, 64), np.uint8), 0)  # height not a multiple of 8
+
+
+def test_concurrent_callers(oracle, clips):
+    """The ME kernel threads of the encoder enter the library concurrently (me_process.c: 20-25 threads, one picture or
+    segment each): four host threads submit searches of different pictures, wait for them, and run the dynamic-GOP
+    detector and the picture statistics at the same time.  Every result must equal the single-threaded oracle's."""
+    import threading
+    po, _ = clips["pan"]
+    frames = [p.interior(0).copy() for p in po]
+    d = api.MeDevice(device=0, max_inflight=8, max_pictures=32)
+    errors = []
+    try:
+        pd = [d.register(f, i) for i, f in enumerate(frames)]
+        jobs = []
+        for cur, em, tl in ((4, 6, 1), (3, 10, 2), (5, 4, 3), (2, 8, 0)):
+            k = api.derive_knobs(enc_mode=em, qp=35, frame_rate_q16=30 << 16, width=W, height=HH, hierarchical_levels=3,
+                                 picture_number=cur, temporal_layer_index=tl, is_ref=1 if tl < 3 else 0, slice_type_b=1)
+            l0, l1 = H.ref_lists(cur, 9, k.num_of_ref_pic_to_search[0], k.num_of_ref_pic_to_search[1])
+            jobs.append((k, cur, l0, l1, oracle.me_picture(k, po[cur], H.refs_dict(po, l0, l1), n_threads=4, extended=False)))
+        dg_want = oracle.dg_hme_level0(po[8], po[0], 3)
+        st_want = oracle.picture_statistics(po[1])
+
+        def worker(i):
+            try:
+                k, cur, l0, l1, want = jobs[i]
+                for rep in range(6):
+                    t, out = d.search_async(k, pd[cur], H.refs_dict(pd, l0, l1))
+                    if i == 0:
+                        m, sad, mv, _, _ = d.dg_hme_level0(pd[8], pd[0], 3)
+                        assert m == dg_want[0] and np.array_equal(sad, dg_want[1]) and np.array_equal(mv, dg_want[2])
+                    if i == 1:
+                        st = d.picture_statistics(pd[1])
+                        assert np.array_equal(st[0], st_want[0]) and st[2] == st_want[2]
+                    d.wait(t)
+                    H.assert_same(want, out, "thread %d rep %d" % (i, rep))
+            except Exception as ex:  # surfaced in the main thread
+                errors.append("thread %d: %r" % (i, ex))
+
+        th = [threading.Thread(target=worker, args=(i,)) for i in range(4)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+    finally:
+        d.close()
+    assert not errors, errors
