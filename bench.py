@@ -51,6 +51,9 @@ def parse():
     return ap.parse_args()
 
 
+SUBMIT_THREADS = int(os.environ.get("SVTME_BENCH_THREADS", "1"))  # host threads submitting searches in the device-resident step
+
+
 class Workload:
     """A synthetic 8-bit clip of one mini-GOP (+ its leading base picture) and its prediction structure."""
 
@@ -137,15 +140,26 @@ def run_step_device(dev, wl, d_luma, inflight, handoff=None):
     first = handoff() if handoff else None
     pics = {i: dev.register_device((first if (i == 0 and first) else d_luma.data_ptr() + i * w * h), w, w, h, i)
             for i in range(wl.n_frames)}
-    pending = []
-    for poc, k, l0, l1 in wl.pics:
-        refs = {(0, i): pics[p] for i, p in enumerate(l0)}
-        refs.update({(1, i): pics[p] for i, p in enumerate(l1)})
-        if len(pending) >= inflight:
-            dev.wait(pending.pop(0))
-        pending.append(dev.search_device_async(k, pics[poc], refs))
-    for t in pending:
-        dev.wait(t)
+    def submit(items, window):
+        pending = []
+        for poc, k, l0, l1 in items:
+            refs = {(0, i): pics[p] for i, p in enumerate(l0)}
+            refs.update({(1, i): pics[p] for i, p in enumerate(l1)})
+            if len(pending) >= window:
+                dev.wait(pending.pop(0))
+            pending.append(dev.search_device_async(k, pics[poc], refs))
+        for t in pending:
+            dev.wait(t)
+
+    nt = SUBMIT_THREADS
+    if nt <= 1:
+        submit(wl.pics, inflight)
+    else:  # the encoder's ME kernel threads submit concurrently (me_process.c); the library is thread-safe
+        th = [threading.Thread(target=submit, args=(wl.pics[i::nt], max(1, inflight // nt))) for i in range(nt)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
     for p in pics.values():
         p.release()
 
