@@ -3,6 +3,6 @@ for r in $(seq ${REPS:-1}); do for f in variants/*.so; do echo "== $f"; SVTME_LI
 import sys,json
 for l in sys.stdin:
     if l.startswith('{'):
-        d=json.loads(l); print('value %.0f e2e %.0f frac %.3f launch_ms %.3f'%(d['value'],d['e2e']['value'],d['roofline']['frac'],d['roofline']['avg_launch_ms']))
+        d=json.loads(l); print('value %.0f e2e %.0f frac %.3f launch_ms %.3f'%(d['value'],d['e2e']['value'],d['roofline']['serialised']['frac'],d['roofline']['serialised']['avg_launch_ms']))
     else: print(l.rstrip()[-300:])
 "; done; done
