@@ -54,6 +54,12 @@ constexpr int kStWarps    = kStThreads / 32;
 constexpr int kSadWarpWin = 8 * 1024;        // HME window bytes per warp
 constexpr int kFpWarpWin  = 16 * 1024;       // full-pel window bytes per warp (64 block rows + candidates)
 
+// Programmatic dependent launch (default; SVTME_PDL=0 turns it off): every kernel of a picture's chain may be launched before its predecessor in
+// the stream has finished; it then waits here, first thing, until the predecessor's grid is complete and its memory
+// visible, having already let ITS successor be scheduled.  This hides the launch latency between the ~21 dependent
+// kernels of a search; without the launch attribute both instructions are no-ops.
+#define PDL_ENTRY() asm volatile("griddepcontrol.launch_dependents;\ngriddepcontrol.wait;" ::: "memory")
+
 // cooperative helpers of a block CTA working on global state
 struct StBackend {
     __device__ __forceinline__ bool     leader() const { return threadIdx.x == 0; }
@@ -63,6 +69,7 @@ struct StBackend {
 };
 
 __global__ void __launch_bounds__(kStThreads) st_init_kernel(const __grid_constant__ MeParams p) {
+    PDL_ENTRY();
     StBackend be;
     sb_init(be, p, p.states[blockIdx.x], blockIdx.x);
 }
@@ -76,6 +83,7 @@ __global__ void __launch_bounds__(kStThreads) st_init_kernel(const __grid_consta
 constexpr int kSbHeadBytes = (int)offsetof(SbState, best_sad);
 static_assert(kSbHeadBytes % 16 == 0 && sizeof(SbState) % 16 == 0, "the control part is copied as 16-byte words");
 __global__ void __launch_bounds__(kStThreads) st_ctl_kernel(const __grid_constant__ MeParams p, int first, int count) {
+    PDL_ENTRY();
     __shared__ __align__(16) unsigned char head[kStWarps][kSbHeadBytes];
     const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t sb = blockIdx.x * kStWarps + warp;
@@ -98,6 +106,7 @@ __global__ void __launch_bounds__(kStThreads) st_ctl_kernel(const __grid_constan
 }
 
 __global__ void __launch_bounds__(kStThreads) st_finish_kernel(const __grid_constant__ MeParams p) {
+    PDL_ENTRY();
     StBackend be;
     sb_finish(be, p, p.states[blockIdx.x], blockIdx.x);
     if (threadIdx.x == 0 && p.px_counter) atomicAdd(p.px_counter, p.states[blockIdx.x].px);
@@ -105,6 +114,7 @@ __global__ void __launch_bounds__(kStThreads) st_finish_kernel(const __grid_cons
 
 // ---- svt_nxm_sad_kernel jobs: one warp per job, straight from global memory (2 KB per operand) ----
 __global__ void __launch_bounds__(kStThreads) st_nxm_kernel(const __grid_constant__ MeParams p) {
+    PDL_ENTRY();
     SbState  &s    = p.states[blockIdx.x];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n    = s.n_nxm;
@@ -575,6 +585,7 @@ __device__ __forceinline__ void rows_job(const MeParams &p, int lvl, const SadJo
 // `lvl` 1: quarter plane, <8, 16>; `lvl` 0: full plane, <16, 32>.  Launched only when hme_search_method is sub-sampled.
 template <int NW, int ROWS>
 __global__ void __launch_bounds__(kStThreads, 6) st_sad_rows_kernel(const __grid_constant__ MeParams p, int lvl) {
+    PDL_ENTRY();
     using C = RowsCfg<NW, ROWS>;
     constexpr int kBlkPitch = 17;  // odd: lane = row reads are conflict free
     __shared__ uint32_t                    blk[ROWS * kBlkPitch];
@@ -625,6 +636,7 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad_rows_kernel(const __grid
 // `lvl`: plane of this phase (2 sixteenth: pre-HME / level 0, 1 quarter: level 1, 0 full: level 2).  The source block is
 // derived from the block index alone, so its staging overlaps the fetch of the job descriptors.
 __global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constant__ MeParams p, int lvl) {
+    PDL_ENTRY();
     __shared__ __align__(16) uint32_t blk[64 * 16];
     __shared__ __align__(16) uint8_t  win[kStWarps][kSadWarpWin];
     __shared__ __align__(16) SadJob   jobs[kMaxSadJobs];
@@ -701,6 +713,7 @@ struct S16Sub {
 };
 
 __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_constant__ MeParams p) {
+    PDL_ENTRY();
     extern __shared__ __align__(16) uint32_t s16_win[];  // kS16BufWords
     __shared__ __align__(16) SadJob        jobs[kMaxSadJobs];
     __shared__ unsigned long long          job_key[kMaxSadJobs];
@@ -1005,6 +1018,7 @@ constexpr int kFpTileNx = 64;
 
 template <bool SUB>
 __global__ void __launch_bounds__(kStThreads) st_fp_kernel(const __grid_constant__ MeParams p) {
+    PDL_ENTRY();
     __shared__ __align__(16) uint32_t src64[64 * 16];
     extern __shared__ __align__(16) uint8_t win_dyn[];  // kStWarps x kFpWarpWin
     __shared__ unsigned long long     fp_key[kMaxFpJobs][kPus];
@@ -1239,6 +1253,7 @@ struct FpSub {
 // with the four candidates of row 4k + e + 2h.
 template <bool FULL>
 __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_constant__ MeParams p) {
+    PDL_ENTRY();
     extern __shared__ __align__(16) uint32_t fp_win[];  // kFpBufWords
     __shared__ uint32_t               sub_key[kFpMaxSub][kPus];  // (sad << 12 | candidate) minima of the batch's sub-windows
     __shared__ unsigned long long     fp_key[kMaxFpJobs][kPus];
@@ -1610,32 +1625,44 @@ cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_
         cudaEventCreate(&ev[ne]); cudaEventRecord(ev[ne], st); nm[ne] = name; ne++;
     };
     mark("start");
-    st_init_kernel<<<n_sb, kStThreads, 0, st>>>(p); nl++; mark("init");
+    // on by default; SVTME_PDL=0 launches every kernel fully stream-ordered (A/B: 0.438 -> 0.418 ms per picture alone,
+    // +5 % end to end)
+    static const bool pdl = !(getenv("SVTME_PDL") != nullptr && atoi(getenv("SVTME_PDL")) == 0) && !trace;
+    auto launch = [&](auto kern, int grid, size_t smem, auto... args) {
+        cudaLaunchConfig_t   cfg = {};
+        cudaLaunchAttribute  at[1];
+        cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(kStThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        cudaLaunchKernelEx(&cfg, kern, args...);
+    };
+    launch(st_init_kernel, n_sb, 0, p); nl++; mark("init");
     for (int i = 0; i < p.n_steps;) {
         if (p.prog[i].kind == STEP_CTL) {
             int c = 1;
             while (i + c < p.n_steps && p.prog[i + c].kind == STEP_CTL) c++;
-            st_ctl_kernel<<<(n_sb + kStWarps - 1) / kStWarps, kStThreads, 0, st>>>(p, i, c);
+            launch(st_ctl_kernel, (n_sb + kStWarps - 1) / kStWarps, 0, p, i, c);
             i += c; mark("ctl");
         } else {
-            if (p.prog[i].kind == STEP_NXM) st_nxm_kernel<<<n_sb, kStThreads, 0, st>>>(p);
+            if (p.prog[i].kind == STEP_NXM) launch(st_nxm_kernel, n_sb, 0, p);
             else if (p.prog[i].kind == STEP_SAD) {
                 const int lvl = (int)p.prog[i].arg;
-                if (lvl == 1 && p.k.hme_search_method == 0) st_sad_rows_kernel<8, 16><<<n_sb, kStThreads, 0, st>>>(p, lvl);
-                else if (lvl == 0 && p.k.hme_search_method == 0) st_sad_rows_kernel<16, 32><<<n_sb, kStThreads, 0, st>>>(p, lvl);
-                else if (lvl == 2 && p.k.hme_search_method == 0 && !sad_old) st_sad16_kernel<<<n_sb, kStThreads, kS16BufWords * 4, st>>>(p);
-                else st_sad_kernel<<<n_sb, kStThreads, 0, st>>>(p, lvl);
+                if (lvl == 1 && p.k.hme_search_method == 0) launch(st_sad_rows_kernel<8, 16>, n_sb, 0, p, lvl);
+                else if (lvl == 0 && p.k.hme_search_method == 0) launch(st_sad_rows_kernel<16, 32>, n_sb, 0, p, lvl);
+                else if (lvl == 2 && p.k.hme_search_method == 0 && !sad_old) launch(st_sad16_kernel, n_sb, (size_t)kS16BufWords * 4, p);
+                else launch(st_sad_kernel, n_sb, 0, p, lvl);
             }
-            else if (p.k.me_search_method == 0 && !fp_old) st_fp_sub_kernel<false><<<n_sb, kStThreads, kFpBufWords * 4, st>>>(p);
-            else if (!fp_old) st_fp_sub_kernel<true><<<n_sb, kStThreads, kFpBufWords * 4, st>>>(p);
-            else if (p.k.me_search_method == 0) st_fp_kernel<true><<<n_sb, kStThreads, kStWarps * kFpWarpWin, st>>>(p);
-            else st_fp_kernel<false><<<n_sb, kStThreads, kStWarps * kFpWarpWin, st>>>(p);
+            else if (p.k.me_search_method == 0 && !fp_old) launch(st_fp_sub_kernel<false>, n_sb, (size_t)kFpBufWords * 4, p);
+            else if (!fp_old) launch(st_fp_sub_kernel<true>, n_sb, (size_t)kFpBufWords * 4, p);
+            else if (p.k.me_search_method == 0) launch(st_fp_kernel<true>, n_sb, (size_t)kStWarps * kFpWarpWin, p);
+            else launch(st_fp_kernel<false>, n_sb, (size_t)kStWarps * kFpWarpWin, p);
             mark(p.prog[i].kind == STEP_NXM ? "nxm" : p.prog[i].kind == STEP_SAD ? "sad" : "fp");
             i++;
         }
         nl++;
     }
-    st_finish_kernel<<<n_sb, kStThreads, 0, st>>>(p); nl++; mark("finish");
+    launch(st_finish_kernel, n_sb, 0, p); nl++; mark("finish");
     if (trace) {
         cudaStreamSynchronize(st);
         float tot = 0.f;
