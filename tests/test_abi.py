@@ -31,7 +31,7 @@ def test_every_declared_symbol_is_exported(lib):
 def test_struct_layouts_match_the_header(tmp_path):
     """sizeof/offsetof of the POD structs as gcc sees the header == the ctypes mirror."""
     fields = {"SvtMeKnobs": abi.Knobs, "SvtMePresetCfg": abi.PresetCfg, "SvtMePictureResults": abi.PictureResults,
-              "SvtMeDeviceCfg": abi.DeviceCfg}
+              "SvtMeDeviceCfg": abi.DeviceCfg, "SvtMeTfCfg": abi.TfCfg, "SvtMeDgMetrics": abi.DgMetrics, "SvtMePicStats": abi.PicStats}
     src = ['#include <stdio.h>', '#include <stddef.h>', '#include "svtme_cuda.h"', "int main(void) {"]
     for cname, cls in fields.items():
         src.append('printf("%s %%zu\\n", sizeof(%s));' % (cname, cname))
