@@ -4,6 +4,7 @@
 // per-search result arenas (device + pinned host mirror), a stream per in-flight picture, and the RTCD-level
 // single-call entry points.  There is NO CPU implementation behind any entry point: every call either runs
 // the CUDA kernels or returns an error code.
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <algorithm>
 #include <cstdio>
@@ -23,7 +24,7 @@ namespace {
 // Device plane geometry: padding >= the reference's (72 / 32 / 16: enc_handle.c:4057-4070, reference_object.c:267-295)
 // rounded so that pixel (0,0) and every row start are 16-byte aligned and aligned vector loads of a search window
 // never leave the allocation.
-constexpr int kPad[3]    = {96, 48, 32};
+constexpr const int *kPad = svtme::kDevPad;
 constexpr int kRefOrg[3] = {72, 32, 16};
 
 struct PlaneGeom {
@@ -37,6 +38,7 @@ struct PicBuffer {
     uint32_t    w = 0, h = 0;
     cudaEvent_t last_use = nullptr;  // last search that read this buffer
     bool        used_once = false;
+    uint32_t    map_w = 0, map_h = 0;  // picture size the TMA descriptors at the end of the buffer were encoded for
 };
 
 }  // namespace
@@ -50,6 +52,7 @@ struct SvtMePic {
     cudaEvent_t ready;
     cudaStream_t stream;
     uint16_t   *staging16;
+    const void *d_tmap16;  // kS16Classes x kS16HClasses CUtensorMaps of the sixteenth plane (device memory, behind the planes)
 };
 
 namespace {
@@ -97,6 +100,7 @@ struct SvtMeHandle {
     size_t                 scratch_bytes = 0;
     uint32_t              *d_small = nullptr;
     float                  last_ms = 0.f;
+    void                  *encode_tiled = nullptr;  // cuTensorMapEncodeTiled (driver entry point)
     // dynamic-GOP detector (svtme_dg_detector_hme_level0): its own stream, events and result arena
     std::mutex             dg_mu;
     cudaStream_t           dg_stream = nullptr;
@@ -166,6 +170,8 @@ int make_pic(SvtMeHandle *h, uint64_t picture_number, uint32_t width, uint32_t h
     p->picture_number = picture_number; p->width = width; p->height = height; p->staging16 = nullptr;
     size_t total;
     plane_geometry(width, height, p->geom, &total);
+    const size_t tmap_off = total;  // a multiple of 256
+    total += (size_t)kS16Classes * kS16HClasses * kTmapBytes;
     {
         std::lock_guard<std::mutex> lk(h->mu);
         rc = acquire_buffer(h, width, height, total, &p->buf);
@@ -185,6 +191,27 @@ int make_pic(SvtMeHandle *h, uint64_t picture_number, uint32_t width, uint32_t h
     if (e != cudaSuccess) { delete p; return fail(h, SVTME_ERR_UNDEFINED, "cudaEventCreate", e); }
     // a recycled buffer may still be read by a search in flight
     if (p->buf.used_once) cudaStreamWaitEvent(p->stream, p->buf.last_use, 0);
+    // TMA descriptors of the padded sixteenth plane (st_sad16_kernel): encoded once per buffer and picture size
+    p->d_tmap16 = p->buf.base + tmap_off;
+    if (p->buf.map_w != width || p->buf.map_h != height) {
+        typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                     const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+        const PlaneGeom &g = p->geom[2];
+        alignas(64) CUtensorMap maps[kS16Classes * kS16HClasses];
+        static_assert(sizeof(CUtensorMap) == kTmapBytes, "CUtensorMap is 128 bytes");
+        for (int c = 0; c < kS16Classes * kS16HClasses; c++) {
+            const cuuint64_t gdim[2] = {(cuuint64_t)g.stride, (cuuint64_t)(g.h + 2 * g.pad)}, gstr[1] = {(cuuint64_t)g.stride};
+            const cuuint32_t box[2] = {(cuuint32_t)kS16BoxBytes[c / kS16HClasses], (cuuint32_t)kS16BoxRows[c % kS16HClasses]}, estr[2] = {1, 1};
+            const CUresult   r = reinterpret_cast<EncodeFn>(h->encode_tiled)(
+                &maps[c], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, p->buf.base + g.offset, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) { cudaEventDestroy(p->ready); delete p; return fail(h, SVTME_ERR_UNDEFINED, "cuTensorMapEncodeTiled"); }
+        }
+        e = cudaMemcpyAsync(p->buf.base + tmap_off, maps, sizeof(maps), cudaMemcpyHostToDevice, p->stream);  // pageable source: staged before the call returns
+        if (e != cudaSuccess) { cudaEventDestroy(p->ready); delete p; return fail(h, SVTME_ERR_UNDEFINED, "cudaMemcpyAsync(tensor maps)", e); }
+        p->buf.map_w = width; p->buf.map_h = height;
+    }
     *out = p;
     return SVTME_OK;
 }
@@ -290,7 +317,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     p.k   = *knobs;
     p.cur = cur->dev;
     for (int l = 0; l < knobs->num_of_list_to_search; l++)
-        for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) p.refs[l][r] = refs[l][r]->dev;
+        for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) { p.refs[l][r] = refs[l][r]->dev; p.tmap16[l][r] = refs[l][r]->d_tmap16; }
     p.n_steps = build_program(p.k, p.prog);
     p.wb = wb; p.hb = hb; p.pu_count = pu_count; p.work_counter = sl->d_counter;
     p.px_counter = reinterpret_cast<unsigned long long *>(sl->d_counter + 2);
@@ -402,6 +429,11 @@ int32_t svtme_init(const SvtMeDeviceCfg *cfg, SvtMeHandle **out) {
     for (auto &s : h->up_streams)
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMalloc(&h->d_small, 4096);
+    if (e == cudaSuccess) {
+        cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+        e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &h->encode_tiled, cudaEnableDefault, &q);
+        if (e == cudaSuccess && (q != cudaDriverEntryPointSuccess || !h->encode_tiled)) e = cudaErrorNotSupported;
+    }
     if (e != cudaSuccess) { fprintf(stderr, "svtme_init: %s\n", cudaGetErrorString(e)); svtme_destroy(h); return SVTME_ERR_UNDEFINED; }
     *out = h;
     return SVTME_OK;

@@ -695,31 +695,61 @@ __global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constan
 }
 
 // ---- pre-HME / HME level 0 on the sixteenth plane (16x16 blocks, 8 sub-sampled rows): CTA-wide windows, lane = item ----
-// The windows of a batch of (job, column tile, row strip) sub-windows are staged together with asynchronous copies,
-// and ALL their items form one flat list dealt to the 128 lanes -- HME level 0 has ~20 tiny windows per block (8x8
-// candidates when the reference is close), which per-warp or per-window scheduling leaves mostly idle.
+// The windows of a batch of (job, column tile, row strip) sub-windows are staged together by TMA (2-D tiled copies of
+// the reference's padded sixteenth plane: boxes of 8 rows x 48 .. 176 bytes, one instruction per box, completion on
+// one mbarrier -- nothing of the copy is executed by the SM's own pipes), and ALL their items form one flat list dealt
+// to the 128 lanes -- HME level 0 has ~20 tiny windows per block (8x8 candidates when the reference is close), which
+// per-warp or per-window scheduling leaves mostly idle.  A box must start on a 16-byte boundary of the plane (the
+// TMA unit raises an illegal-instruction error otherwise: tools/microbench/tma_u8.cu), so candidate 0 sits at byte
+// 4 * wo + a of a staged row: groups start at word wo, candidates are shifted by a bytes.
 // An item = 4 x-adjacent candidates on the two candidate rows y and y + 2, which share 7 of their 8 reference rows:
 // 9 window rows (45 LDS, 108 SHF) per 256 SADs.  With prehme_skip_search_line only odd candidate rows exist
-// (y = 4k + 1 and 4k + 3).  Even / odd window rows are kept in two planes with an odd pitch.  A lane keeps the
-// minimum of its current sub-window as (sad << 16 | candidate index) and folds it into the job's 64-bit key
+// (y = 4k + 1 and 4k + 3).  The row pitch is 4 x odd words (8 consecutive rows fall on 8 different bank quads).  A lane
+// keeps the minimum of its current sub-window as (sad << 16 | candidate index) and folds it into the job's 64-bit key
 // (sad, y, x) when it moves on.  Blocks cut by the picture edge take the generic per-warp path.
 constexpr int kS16BufWords = 7 * 1024;
 constexpr int kS16MaxSub   = 64;
 struct S16Sub {
-    int16_t job, x0, y0, nx, ny, a, ngroups, P;
-    int32_t plane_words, items, off, ibase;  // off / ibase: words / items before this sub-window inside its batch
+    int16_t job, x0, y0, nx, ny, ngroups, P, nbox;  // P: row pitch in words = box bytes / 4; nbox: boxes of `brows` rows
+    int16_t a, wo;                                  // candidate 0 at byte 4 * wo + a of a staged row
+    int32_t items, off, ibase;                      // off / ibase: words / items before this sub-window inside its batch
+    int32_t tx, ty;                                 // the sub-window's first byte in the padded plane (TMA coordinates)
     float   inv_ng, inv_nx;
-    int16_t hsel, q, wo, chunks;             // hsel 1: odd rows only; q: log2 lanes per staged row; wo: first word of group 0
+    int16_t hsel, cls, brows, pad_;                 // hsel 1: odd rows only; cls: descriptor index; brows: rows per box
 };
+
+constexpr int kPad16 = kDevPad[2];
+
+// mbarrier / TMA primitives (PTX ISA: mbarrier, cp.async.bulk.tensor)
+SVTME_D void mbar_init(uint32_t mbar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\nfence.mbarrier_init.release.cluster;" ::"r"(mbar), "r"(count) : "memory");
+}
+SVTME_D void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+SVTME_D void mbar_wait(uint32_t mbar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(mbar), "r"(parity) : "memory");
+    } while (!done);
+}
+// one box of a 2-D tiled tensor map -> shared memory (dst 128-byte aligned), completion counted on `mbar`
+SVTME_D void tma_load_2d(uint32_t dst, const void *tmap, int x, int y, uint32_t mbar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(tmap), "r"(x), "r"(y), "r"(mbar) : "memory");
+}
 
 __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_constant__ MeParams p) {
     PDL_ENTRY();
-    extern __shared__ __align__(16) uint32_t s16_win[];  // kS16BufWords
+    extern __shared__ __align__(128) uint32_t s16_win[];  // kS16BufWords
     __shared__ __align__(16) SadJob        jobs[kMaxSadJobs];
     __shared__ unsigned long long          job_key[kMaxSadJobs];
     __shared__ S16Sub                      subs[kS16MaxSub];
     __shared__ uint32_t                    sub_key[kS16MaxSub];
-    __shared__ int                         n_sub_all, n_batch, b_start[kS16MaxSub + 1], b_items[kS16MaxSub];
+    __shared__ int                         n_sub_all, n_batch, b_start[kS16MaxSub + 1], b_items[kS16MaxSub], b_words[kS16MaxSub];
+    __shared__ __align__(8) unsigned long long mbar_store;
+    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&mbar_store);
     PH_DECL
     SbState  &s = p.states[blockIdx.x];
     {
@@ -735,6 +765,7 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
         if (i1 < kWords) dst[i1] = v1;
         if (threadIdx.x < kMaxSadJobs) job_key[threadIdx.x] = ~0ull;
         if (threadIdx.x < kS16MaxSub) sub_key[threadIdx.x] = ~0u;
+        if (threadIdx.x == 0) mbar_init(mbar, 1);
     }
     const int n = s.n_sad;
     // block geometry as in make_sad_job (me_control.cuh)
@@ -763,8 +794,11 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
         uint32_t   px = 0;
         if (valid) {
             const int W = jobs[ji].sa_w, H = jobs[ji].sa_h;
-            const int pmax = (((15 + min(128, W) + 3) >> 2) + 4 + 3) & ~3;  // widest row pitch of a tile, in words (8 .. 40)
-            ny_cap = max(16, min(512, (int)(3584.0f / (float)pmax) - 16)) & ~3;  // a sub-window: <= ~5.5 K words, < 64 K candidates
+            const int a16  = (int)((uintptr_t)jobs[ji].ref & 15);                          // the same for every tile (x0 = 128 t)
+            const int need = 4 * ((a16 >> 2) + (((a16 & 3) + min(128, W) + 3) >> 2)) + 16;  // bytes of the widest tile's rows
+            const int pmax = need <= 48 ? 12 : need <= 80 ? 20 : need <= 112 ? 28 : need <= 144 ? 36 : 44;  // its row pitch in words
+            // a sub-window (rows rounded up to boxes of 128) fits the buffer and has < 64 K candidates
+            ny_cap = min(448, (kS16BufWords / (128 * pmax)) * 128 - 14) & ~3;
             nst    = H <= ny_cap ? 1 : (H + ny_cap - 1) / ny_cap;
             cnt    = ((W + 127) >> 7) * nst;
             px     = (uint32_t)W * (uint32_t)(jobs[ji].skip_line ? (H >> 1) : H) * (8 * 16);
@@ -774,19 +808,23 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
         // one sub-window per job in the common case: everything below is then lane-parallel
         auto fill = [&](S16Sub &u, int x0, int y0, int nx, int ny, int &words) {
             const SadJob &j = jobs[ji];
-            const int     a16 = (int)((uintptr_t)(j.ref + x0) & 15), a = a16 & 3, wo = a16 >> 2;
-            const int     ngroups = (a + nx + 3) >> 2;
-            int           chunks = (wo + ngroups + 4 + 3) >> 2;  // 16-byte copies per row: groups + 4 block words + shifted-in word
-            chunks |= 1;                                          // pitch = 4 * odd words: candidate rows k, k+1 .. fall 8 banks apart
-            const int P = 4 * chunks, nyp = (ny + 3) & ~3, PR = ((nyp + 14 + 1) >> 1) + 1;
+            const int     a16 = (int)((uintptr_t)(j.ref + x0) & 15), a = a16 & 3, wo = a16 >> 2;  // planes and rows are 16-byte aligned
+            const int     ngroups = (a + nx + 3) >> 2, need = 4 * (wo + ngroups) + 16;  // a group reads 5 words: 4 candidates + 15 more bytes
+            const int     cls = need <= 48 ? 0 : need <= 80 ? 1 : need <= 112 ? 2 : need <= 144 ? 3 : 4, P = 12 + 8 * cls;  // kS16BoxBytes[cls] / 4
+            const int     nyp = (ny + 3) & ~3, nrows = nyp + 14, hc = nrows <= 24 ? 0 : nrows <= 96 ? 1 : 2;
+            const int     brows = 8 << (2 * hc), nbox = (nrows + brows - 1) / brows;  // kS16BoxRows[hc]
+            // the sub-window's first byte inside the reference's padded sixteenth plane
+            const DevPlane &rpl = p.refs[j.li][j.ri].lvl[2];
+            const int       offb = (int)((j.ref + (int64_t)y0 * j.raw_stride + x0) - (rpl.org - (int64_t)kPad16 * rpl.stride - kPad16));
+            const int       ty = offb / rpl.stride;
             u.job = (int16_t)ji; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
-            u.a = (int16_t)a; u.wo = (int16_t)wo; u.chunks = (int16_t)chunks; u.ngroups = (int16_t)ngroups; u.P = (int16_t)P;
-            u.plane_words = ((PR * P + 27) & ~31) + 4;   // = 4 mod 32: rows k (8 banks apart) of the two planes interleave
+            u.ngroups = (int16_t)ngroups; u.P = (int16_t)P; u.nbox = (int16_t)nbox; u.cls = (int16_t)(cls * kS16HClasses + hc); u.brows = (int16_t)brows;
+            u.a = (int16_t)a; u.wo = (int16_t)wo;
+            u.tx = offb - ty * rpl.stride - a16; u.ty = ty;
             u.hsel  = j.skip_line ? 1 : 0;
             u.items = (nyp >> 2) * (j.skip_line ? 1 : 2) * ngroups;
             u.inv_ng = __fdividef(1.0f, (float)ngroups) * 1.0000001f; u.inv_nx = __fdividef(1.0f, (float)nx) * 1.0000001f;
-            u.q = (int16_t)(chunks <= 2 ? 1 : chunks <= 4 ? 2 : chunks <= 8 ? 3 : 4);
-            words = 2 * u.plane_words;
+            words = nbox * brows * P;
         };
         const unsigned vmask = __ballot_sync(0xffffffffu, valid);
         if (__all_sync(0xffffffffu, cnt <= 1)) {
@@ -808,14 +846,15 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
                 const int fw = __shfl_sync(0xffffffffu, cw - words, first), fi = __shfl_sync(0xffffffffu, ci - items, first);
                 const int fidx = __shfl_sync(0xffffffffu, idx, first);
                 // items of the batch that ends here = fi - (items before the batch); every lane >= first moves its base
-                const int prev_base_i = __shfl_sync(0xffffffffu, base_i, first);
-                if (lane == 0) { b_items[nb] = fi - prev_base_i; b_start[nb + 1] = fidx; }
+                const int prev_base_i = __shfl_sync(0xffffffffu, base_i, first), prev_base_w = __shfl_sync(0xffffffffu, base_w, first);
+                if (lane == 0) { b_items[nb] = fi - prev_base_i; b_words[nb] = fw - prev_base_w; b_start[nb + 1] = fidx; }
                 nb++;
                 if (lane >= first) { base_w = fw; base_i = fi; }
             }
             if (valid) { subs[idx].off = cw - words - base_w; subs[idx].ibase = ci - items - base_i; }
             const int tot_i = __shfl_sync(0xffffffffu, ci, 31), last_base_i = __shfl_sync(0xffffffffu, base_i, 31);
-            if (lane == 0) { b_items[nb] = tot_i - last_base_i; b_start[nb + 1] = S; n_batch = S ? nb + 1 : 0; n_sub_all = S; }
+            const int tot_w = __shfl_sync(0xffffffffu, cw, 31), last_base_w = __shfl_sync(0xffffffffu, base_w, 31);
+            if (lane == 0) { b_items[nb] = tot_i - last_base_i; b_words[nb] = tot_w - last_base_w; b_start[nb + 1] = S; n_batch = S ? nb + 1 : 0; n_sub_all = S; }
         } else {
             int incl = cnt;
             for (int o = 1; o < 32; o <<= 1) {
@@ -840,15 +879,19 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
                 b_start[0] = 0;
                 for (int i = 0; i < S; i++) {
                     S16Sub   &u = subs[i];
-                    const int w2 = 2 * u.plane_words;
-                    if (used + w2 > kS16BufWords) { b_items[nb] = items; b_start[++nb] = i; used = 0; items = 0; }
+                    const int w2 = u.nbox * u.brows * u.P;
+                    if (used + w2 > kS16BufWords) { b_items[nb] = items; b_words[nb] = used; b_start[++nb] = i; used = 0; items = 0; }
                     u.off = used; u.ibase = items;
                     used += w2; items += u.items;
                 }
-                b_items[nb] = items; b_start[++nb] = S;
+                b_items[nb] = items; b_words[nb] = used; b_start[++nb] = S;
                 n_batch = nb;
             }
         }
+        __syncwarp();
+        // the first batch's bytes are announced before anybody can issue its copies (barrier below)
+        if (lane == 0 && bw == 16 && rows == 8 && n_sub_all > 0 && n_sub_all <= kS16MaxSub && n_batch > 0)
+            mbar_expect_tx(mbar, 4u * (uint32_t)b_words[0]);
     }
     __syncthreads();
     const int S = n_sub_all;
@@ -893,37 +936,17 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
     const int nb = n_batch;
     for (int bi = 0; bi < nb; bi++) {
         const int s_lo = b_start[bi], s_hi = b_start[bi + 1];
-        // stage: one warp per sub-window, 16-byte copies, 2^q lanes per window row.  The rounded-up rows may read a few
-        // bytes past the window: inside the plane's padding / the allocation's slack, never used.
+        // stage: one warp per sub-window, one lane per box.  Boxes may reach past the window (rounded-up
+        // rows, the box class's width) or past the plane (zero fill): never used.
         for (int si = s_lo + warp; si < s_hi; si += kStWarps) {
             const S16Sub  &u = subs[si];
             const SadJob  &j = jobs[u.job];
-            const int      nrows = ((u.ny + 3) & ~3) + 14, chunks = u.chunks, q = u.q;
-            const uint32_t raw = (uint32_t)j.raw_stride;
-            const int      rpi = 32 >> q, lr = lane >> q, lc = lane & ((1 << q) - 1);
-            if (lc < chunks) {
-                const uint8_t *g0 = j.ref + (int64_t)u.y0 * (int64_t)raw + u.x0 - (u.a + 4 * u.wo) + 16 * lc;
-                const uint32_t P4 = 4u * (uint32_t)u.P;
-                const uint32_t w0 = sbase + 4u * (uint32_t)u.off + 16u * (uint32_t)lc, pw = 4u * (uint32_t)u.plane_words;
-                if (rpi >= 2) {  // the parity of the lane's rows is fixed
-                    const uint32_t sa0 = w0 + (uint32_t)(lr & 1) * pw;
-#pragma unroll 4
-                    for (int R = lr; R < nrows; R += rpi) {
-                        CHECK_SRC(p, 2, j.li, j.ri, g0 + (uint64_t)(uint32_t)R * (uint64_t)raw, 16, 2);
-                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa0 + (uint32_t)(R >> 1) * P4),
-                                     "l"(g0 + (uint64_t)(uint32_t)R * (uint64_t)raw));
-                    }
-                } else {
-#pragma unroll 4
-                    for (int R = 0; R < nrows; R++)
-                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(w0 + (uint32_t)(R & 1) * pw + (uint32_t)(R >> 1) * P4),
-                                     "l"(g0 + (uint64_t)(uint32_t)R * (uint64_t)raw));
-                }
-            }
+            const uint8_t *tm = static_cast<const uint8_t *>(p.tmap16[j.li][j.ri]) + u.cls * kTmapBytes;
+            const uint32_t box_bytes = 4u * (uint32_t)u.brows * (uint32_t)u.P, dst0 = sbase + 4u * (uint32_t)u.off;
+            if (lane < u.nbox) tma_load_2d(dst0 + (uint32_t)lane * box_bytes, tm, u.tx, u.ty + u.brows * lane, mbar);  // <= 4 boxes
         }
         PH(1, 2)  // copy issue
-        asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
-        __syncthreads();
+        mbar_wait(mbar, (uint32_t)(bi & 1));
         PH(1, 3)  // copy wait
         // compute: flat item list of the batch, lane f takes items f, f + 128, ...
         {
@@ -933,7 +956,6 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
             int       u_ng = 1, u_nx = 1, u_ny = 0, u_P = 1, u_a = 0, u_hsel = 0, u_ibase = 0;
             float     u_inv_ng = 1.f;
             const uint32_t *u_win = s16_win;
-            uint32_t        u_pw = 0;
             auto flush = [&]() {
                 if (best != ~0u) { atomicMin(&sub_key[si], best); best = ~0u; }
             };
@@ -943,7 +965,7 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
                     do { si++; next_base = subs[si].ibase + subs[si].items; } while (f >= next_base);
                     const S16Sub &u = subs[si];
                     u_ng = u.ngroups; u_nx = u.nx; u_ny = u.ny; u_P = u.P; u_a = u.a; u_hsel = u.hsel; u_ibase = u.ibase;
-                    u_inv_ng = u.inv_ng; u_win = s16_win + u.off + u.wo; u_pw = (uint32_t)u.plane_words;
+                    u_inv_ng = u.inv_ng; u_win = s16_win + u.off + u.wo;
                 }
                 const int item = f - u_ibase;
                 const int kh = (int)(((float)item + 0.5f) * u_inv_ng), g = item - kh * u_ng;
@@ -952,10 +974,10 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
                 uint32_t  acc[2][4];
 #pragma unroll
                 for (int c = 0; c < 4; c++) acc[0][c] = acc[1][c] = 0;
-                const uint32_t *rowp = u_win + h * u_pw + (2 * k) * u_P + g;
+                const uint32_t *rowp = u_win + yy * u_P + g;  // window rows yy, yy + 2, .. yy + 16
 #pragma unroll
                 for (int rr = 0; rr < 9; rr++) {
-                    const uint32_t *rp = rowp + rr * u_P;
+                    const uint32_t *rp = rowp + rr * (2 * u_P);
                     uint32_t        w[5];
 #pragma unroll
                     for (int c = 0; c < 5; c++) w[c] = rp[c];
@@ -988,6 +1010,7 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
             flush();
         }
         PH(1, 4)  // search (this thread)
+        if (threadIdx.x == 0 && bi + 1 < nb) mbar_expect_tx(mbar, 4u * (uint32_t)b_words[bi + 1]);
         __syncthreads();  // the windows are reused by the next batch
         PH(1, 5)  // waiting for the other warps
     }

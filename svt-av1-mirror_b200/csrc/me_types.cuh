@@ -62,6 +62,16 @@ struct DevResults {
 };
 constexpr int kSumSlots = 64, kSumSlotWords = 8;
 
+// device padding of the three planes (>= the reference's 72 / 32 / 16, rounded so that rows stay 16-byte aligned)
+constexpr int kDevPad[3] = {96, 48, 32};
+// TMA boxes of the sixteenth plane: kS16Classes widths in bytes (pitch = 4 x odd words: rows 8 banks apart) x
+// kS16HClasses heights (8 / 32 / 128 rows: the TMA unit's cost is per box, so tall windows take tall boxes);
+// descriptor index = width class * kS16HClasses + height class
+constexpr int kS16Classes = 5, kS16HClasses = 3;
+constexpr int kS16BoxBytes[kS16Classes] = {48, 80, 112, 144, 176};
+constexpr int kS16BoxRows[kS16HClasses] = {8, 32, 128};
+constexpr int kTmapBytes = 128;
+
 // One step of the per-SB program (me_control.cuh: build_program)
 struct Step {
     uint8_t kind, op, arg;
@@ -80,6 +90,9 @@ struct MeParams {
     uint32_t  *work_counter;  // persistent-CTA SB queue
     unsigned long long *px_counter;  // optional: algorithmic pixel-compares of the picture (roofline numerator)
     SbState   *states;        // staged pipeline: one SbState per 64x64 block in HBM/L2
+    // TMA descriptors of every reference picture's padded sixteenth plane: kS16Classes x kS16HClasses CUtensorMaps (128 bytes each)
+    // in device memory, box = kS16BoxBytes[class] x kS16BoxRows[height class] (st_sad16_kernel stages its search windows with them)
+    const void *tmap16[kMaxLists][kMaxRefs];
     int32_t    n_steps;
     Step       prog[kMaxSteps];
 };
