@@ -259,6 +259,22 @@ def test_async_pipeline_and_buffer_reuse(oracle, dev, clips):
             p.release()
 
 
+def test_recycled_buffers_across_picture_sizes(oracle):
+    """A freed picture buffer is reused for a slightly smaller picture (pool rule: up to 25 % larger than needed): the plane
+    geometry and the TMA descriptors stored behind the planes must follow the new size, and again when the size flips back."""
+    d = api.MeDevice(device=0, max_pictures=16)
+    try:
+        for it, (w, h) in enumerate([(376, 200), (328, 192), (376, 200), (328, 184)]):  # same row pitches: the buffers ARE reused
+            n = 6
+            frames, po = H.make_pictures(oracle, w, h, n, seed=50 + it, kind="pan")
+            pd = [d.register(f, i) for i, f in enumerate(frames)]
+            _run_case(oracle, d, po, pd, dict(enc_mode=6, tl=1, hl=4), 3, w, h, n)
+            for p in pd:
+                p.release()
+    finally:
+        d.close()
+
+
 def test_errors_are_loud(dev, clips):
     _, pd = clips["pan"]
     k = api.derive_knobs(enc_mode=8, qp=35, frame_rate_q16=30 << 16, width=W, height=HH, hierarchical_levels=3,
