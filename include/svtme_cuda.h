@@ -378,6 +378,15 @@ void svtme_cuda_downsample_2d(SvtMeHandle *h, const uint8_t *input_samples, uint
 /* aom_dsp_rtcd.h:856 svt_nxm_sad_kernel */
 uint32_t svtme_cuda_nxm_sad_kernel(SvtMeHandle *h, const uint8_t *src, uint32_t src_stride, const uint8_t *ref,
                                    uint32_t ref_stride, uint32_t height, uint32_t width);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * svtme_cuda_nxm_sad_kernel, but the operand staging and the result word live in a file-scope device array of the
+ * library (33 024 bytes per GPU, held until exit) instead of the handle's cudaMalloc'ed scratch: the call allocates
+ * nothing.  Limit: width <= 64, height <= 128; larger blocks return SVTME_ERR_BAD_PARAMETER (text in
+ * svtme_last_error).  All calls share the array: host callers are serialised by a mutex and the call returns after
+ * its work has left the GPU; calls made to overlap on the GPU by other means would race. */
+int32_t svtme_cuda_nxm_sad_kernel_noalloc(SvtMeHandle *h, const uint8_t *src, uint32_t src_stride, const uint8_t *ref,
+                                          uint32_t ref_stride, uint32_t height, uint32_t width, uint32_t *sad);
 /* open_loop_me_fullpel_search_sblock (motion_estimation.c:781-817) = the fused
  * svt_initialize_buffer_32bits + svt_ext_all_sad_calculation_8x8_16x16 +
  * svt_ext_eight_sad_calculation_32x32_64x64 + svt_ext_sad_calculation_* loop

@@ -893,3 +893,67 @@ void svtme_cuda_fullpel_search_sblock(SvtMeHandle *h, const uint8_t *src, uint32
 }
 
 }  // extern "C"
+
+// ---- allocation-free entry point (no counterpart in the reference) ----
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it):
+// svt_nxm_sad_kernel with its operand staging and its result word in a file-scope device array instead of the handle's
+// cudaMalloc'ed scratch.  Every GPU that loads the library holds the array (kNoAllocBytes) until exit.  All calls share
+// it and it keeps the last call's contents: the result word is cleared on the stream before every launch; calls that
+// overlap on the GPU race (the entry serialises host callers with a mutex and synchronises before it returns).
+namespace {
+
+constexpr uint32_t kNoAllocMaxWidth = 64, kNoAllocMaxHeight = 128, kNoAllocPitch = 128;
+constexpr size_t   kNoAllocResult = 256;  // bytes reserved in front of the operands (result word at offset 0)
+constexpr size_t   kNoAllocPlane  = (size_t)kNoAllocPitch * kNoAllocMaxHeight;
+constexpr size_t   kNoAllocBytes  = kNoAllocResult + 2 * kNoAllocPlane;  // 33 024 bytes
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+// one warp per group of rows; the partial sums meet in the (cleared) result word
+__global__ void __launch_bounds__(128) noalloc_nxm_kernel(unsigned char *scratch, uint32_t rows, uint32_t width) {
+    const unsigned char *src = scratch + kNoAllocResult, *ref = src + kNoAllocPlane;
+    uint32_t            *out = reinterpret_cast<uint32_t *>(scratch);
+    const uint32_t       nw = (width + 3) >> 2, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t             acc = 0;
+    for (uint32_t i = warp * 32 + lane; i < rows * nw; i += 128) {
+        const uint32_t r = i / nw, c = i - r * nw, nb = min(4u, width - 4 * c);
+        uint32_t       a = *reinterpret_cast<const uint32_t *>(src + r * kNoAllocPitch + 4 * c);
+        uint32_t       b = *reinterpret_cast<const uint32_t *>(ref + r * kNoAllocPitch + 4 * c);
+        if (nb < 4) { const uint32_t m = (1u << (8 * nb)) - 1u; a &= m; b &= m; }  // bytes past the row hold an earlier call's data
+        acc = __vsadu4(a, b) + acc;
+    }
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0 && acc) atomicAdd(out, acc);
+}
+
+std::mutex     g_noalloc_mu;
+unsigned char *g_noalloc_ptr[64] = {};  // device address of g_noalloc_scratch, per device ordinal
+
+}  // namespace
+
+extern "C" int32_t svtme_cuda_nxm_sad_kernel_noalloc(SvtMeHandle *h, const uint8_t *src, uint32_t src_stride, const uint8_t *ref,
+                                                     uint32_t ref_stride, uint32_t height, uint32_t width, uint32_t *sad) {
+    if (!h || !src || !ref || !sad) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    if (width == 0 || height == 0 || width > kNoAllocMaxWidth || height > kNoAllocMaxHeight)
+        return fail(h, SVTME_ERR_BAD_PARAMETER, "svtme_cuda_nxm_sad_kernel_noalloc: block larger than the static scratch (at most 64 wide x 128 rows)");
+    if (src_stride < width || ref_stride < width) return fail(h, SVTME_ERR_BAD_PARAMETER, "stride smaller than the block width");
+    if (h->cfg.device < 0 || h->cfg.device >= 64) return fail(h, SVTME_ERR_BAD_PARAMETER, "device ordinal beyond the per-device table");
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    CK(cudaSetDevice(h->cfg.device));
+    unsigned char *&d = g_noalloc_ptr[h->cfg.device];
+    if (!d) {  // once per device, with that device current: the array's name is only a host-side stand-in
+        void *p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        d = static_cast<unsigned char *>(p);
+    }
+    CK(cudaMemsetAsync(d, 0, kNoAllocResult, 0));  // the result word must start at zero
+    CK(cudaMemcpy2DAsync(d + kNoAllocResult, kNoAllocPitch, src, src_stride, width, height, cudaMemcpyHostToDevice, 0));
+    CK(cudaMemcpy2DAsync(d + kNoAllocResult + kNoAllocPlane, kNoAllocPitch, ref, ref_stride, width, height, cudaMemcpyHostToDevice, 0));
+    noalloc_nxm_kernel<<<1, 128, 0, 0>>>(d, height, width);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(sad, d, sizeof(uint32_t), cudaMemcpyDeviceToHost));  // synchronous: the call has left the GPU when it returns
+    {
+        std::lock_guard<std::mutex> lk2(h->mu);
+        h->launches += 1;
+    }
+    return SVTME_OK;
+}

@@ -23,7 +23,7 @@ EXPORTS = [
     "svtme_picture_search", "svtme_search_wait", "svtme_picture_search_device", "svtme_search_elapsed_ms",
     "svtme_search_px_compares", "svtme_measure_sad_peak", "svtme_launch_count", "svtme_last_error", "svtme_cuda_sad_loop_kernel", "svtme_cuda_downsample_2d",
     "svtme_cuda_nxm_sad_kernel", "svtme_cuda_fullpel_search_sblock", "svtme_dg_detector_hme_level0",
-    "svtme_picture_statistics",
+    "svtme_picture_statistics", "svtme_cuda_nxm_sad_kernel_noalloc",
 ]
 
 
@@ -81,6 +81,7 @@ def load_library():
     lib.svtme_cuda_downsample_2d.restype = None
     lib.svtme_cuda_nxm_sad_kernel.argtypes = [vp, u8p, u32, u8p, u32, u32, u32]
     lib.svtme_cuda_nxm_sad_kernel.restype = u32
+    lib.svtme_cuda_nxm_sad_kernel_noalloc.argtypes = [vp, u8p, u32, u8p, u32, u32, u32, C.POINTER(u32)]
     lib.svtme_cuda_fullpel_search_sblock.argtypes = [vp, u8p, u32, u8p, u32, C.c_int16, C.c_int16, u32, u32, C.c_uint8,
                                                      vp, vp]
     lib.svtme_cuda_fullpel_search_sblock.restype = None
@@ -289,6 +290,13 @@ class MeDevice:
     def nxm_sad_kernel(self, src, src_off, src_stride, ref, ref_off, ref_stride, h, w):
         return self.lib.svtme_cuda_nxm_sad_kernel(self.h, src.ctypes.data + src_off, src_stride, ref.ctypes.data + ref_off,
                                                   ref_stride, h, w)
+
+    def nxm_sad_kernel_noalloc(self, src, src_off, src_stride, ref, ref_off, ref_stride, h, w):
+        """The allocation-free variant (static device scratch); raises on sizes beyond 64 x 128."""
+        out = C.c_uint32(0xdeadbeef)
+        self._check(self.lib.svtme_cuda_nxm_sad_kernel_noalloc(self.h, src.ctypes.data + src_off, src_stride, ref.ctypes.data + ref_off,
+                                                               ref_stride, h, w, C.byref(out)), "svtme_cuda_nxm_sad_kernel_noalloc")
+        return out.value
 
     def downsample_2d(self, inp, w, h, step):
         ow, oh = (w - (step >> 1) + step - 1) // step, (h - (step >> 1) + step - 1) // step
