@@ -231,8 +231,8 @@ typedef struct SvtMeDeviceCfg {
     uint32_t max_inflight;      /* concurrent picture searches (streams); 0 => 4 */
     uint32_t sixteenth_from_full; /* 1: HME level 1 is off, the sixteenth plane is decimated from the full plane with
                                    * step 4 (pic_analysis_process.c:1981-1992); 0: from the quarter plane with step 2 */
-    uint32_t pipeline;          /* 0: staged -- every step of the per-SB program is one kernel over the whole picture
-                                 * (default); 1: one persistent kernel, a CTA runs the whole program of a 64x64 block */
+    uint32_t pipeline;          /* must be 0: staged -- every search engine of the per-SB program is one kernel over the
+                                 * whole picture (the round-1 persistent kernel, value 1, is no longer built) */
 } SvtMeDeviceCfg;
 
 typedef struct SvtMeHandle SvtMeHandle;   /* opaque */

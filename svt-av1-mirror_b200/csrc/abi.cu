@@ -7,10 +7,12 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <algorithm>
+#include <condition_variable>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/svtme_cuda.h"
@@ -32,13 +34,16 @@ struct PlaneGeom {
     size_t offset, bytes;
 };
 
+// One pooled allocation: three padded planes.  A buffer is only ever reused for a picture of the SAME size, so the TMA
+// descriptors of its sixteenth plane are encoded once, on the host, when it is allocated; a search hands them to
+// st_sad16_kernel by value (S16Maps, me_types.cuh).
 struct PicBuffer {
     uint8_t    *base = nullptr;
     size_t      bytes = 0;
     uint32_t    w = 0, h = 0;
-    cudaEvent_t last_use = nullptr;  // last search that read this buffer
-    bool        used_once = false;
-    uint32_t    map_w = 0, map_h = 0;  // picture size the TMA descriptors at the end of the buffer were encoded for
+    cudaEvent_t free_ev = nullptr;  // recorded at release, after every reader of the previous owner: the next owner waits on it
+    bool        recycled = false;
+    unsigned char (*maps)[kTmapBytes] = nullptr;  // host: the kS16Classes x kS16HClasses CUtensorMaps of the sixteenth plane (64-byte aligned)
 };
 
 }  // namespace
@@ -52,7 +57,8 @@ struct SvtMePic {
     cudaEvent_t ready;
     cudaStream_t stream;
     uint16_t   *staging16;
-    const void *d_tmap16;  // kS16Classes x kS16HClasses CUtensorMaps of the sixteenth plane (device memory, behind the planes)
+    uint64_t    reader_slots;  // search slots whose streams have read this picture (bit = slot index; guarded by the handle's mutex)
+    bool        dg_reader;     // the dynamic-GOP detector / statistics stream has read it
 };
 
 namespace {
@@ -75,7 +81,9 @@ struct Inflight {
     ResultLayout        lay{};
     SvtMePictureResults user{};
     bool                to_host = false, busy = false;
+    std::thread::id     owner;  // the thread that submitted the search in flight
     bool                direct[32] = {};  // result array i went straight into the caller's (page-locked) buffer
+    S16Maps             maps;             // launch parameter of st_sad16_kernel: the references' TMA descriptors
     uint64_t            ticket = 0;
     float               ms = 0.f;
     unsigned long long *h_px = nullptr;  // pinned
@@ -87,14 +95,14 @@ struct Inflight {
 struct SvtMeHandle {
     SvtMeDeviceCfg         cfg;
     std::mutex             mu;
+    std::condition_variable slot_cv;  // a search slot was freed
     std::vector<PicBuffer> free_bufs;
     std::vector<Inflight>  slots;
     std::vector<cudaStream_t> up_streams;
     size_t                 next_up = 0;
     uint64_t               next_ticket = 1;
     uint64_t               launches = 0;
-    int                    sm_count = 0, ctas_per_sm = 0;
-    std::string            err;
+    int                    sm_count = 0;
     // RTCD-level scratch
     uint8_t               *d_scratch = nullptr;
     size_t                 scratch_bytes = 0;
@@ -104,18 +112,19 @@ struct SvtMeHandle {
     // dynamic-GOP detector (svtme_dg_detector_hme_level0): its own stream, events and result arena
     std::mutex             dg_mu;
     cudaStream_t           dg_stream = nullptr;
-    cudaEvent_t            dg_e0 = nullptr, dg_e1 = nullptr;
+    cudaEvent_t            dg_e0 = nullptr, dg_e1 = nullptr, dg_done = nullptr;
     uint8_t               *d_dg = nullptr, *h_dg = nullptr;
     size_t                 dg_cap = 0;
 };
 
 namespace {
 
-int fail(SvtMeHandle *h, int code, const char *what, cudaError_t e = cudaSuccess) {
-    if (h) {
-        h->err = what;
-        if (e != cudaSuccess) { h->err += ": "; h->err += cudaGetErrorString(e); }
-    }
+// Error text of the calling thread's last failed call (svtme_last_error): thread-local, so concurrent callers of one
+// handle never write the same string.
+thread_local std::string t_err;
+int fail(SvtMeHandle *, int code, const char *what, cudaError_t e = cudaSuccess) {
+    t_err = what;
+    if (e != cudaSuccess) { t_err += ": "; t_err += cudaGetErrorString(e); }
     return code;
 }
 #define CK(call)                                                                  \
@@ -145,17 +154,16 @@ int set_device(SvtMeHandle *h) {
 
 int acquire_buffer(SvtMeHandle *h, uint32_t w, uint32_t hgt, size_t bytes, PicBuffer *out) {
     for (size_t i = 0; i < h->free_bufs.size(); i++)
-        if (h->free_bufs[i].bytes >= bytes && h->free_bufs[i].bytes <= bytes + bytes / 4) {
+        if (h->free_bufs[i].w == w && h->free_bufs[i].h == hgt && h->free_bufs[i].bytes == bytes) {
             *out = h->free_bufs[i];
             h->free_bufs.erase(h->free_bufs.begin() + i);
-            out->w = w; out->h = hgt;
             return SVTME_OK;
         }
     PicBuffer b;
     cudaError_t e = cudaMalloc(&b.base, bytes);
     if (e != cudaSuccess) return fail(h, SVTME_ERR_INSUFFICIENT, "cudaMalloc(picture planes)", e);
     b.bytes = bytes; b.w = w; b.h = hgt;
-    e = cudaEventCreateWithFlags(&b.last_use, cudaEventDisableTiming);
+    e = cudaEventCreateWithFlags(&b.free_ev, cudaEventDisableTiming);
     if (e != cudaSuccess) { cudaFree(b.base); return fail(h, SVTME_ERR_UNDEFINED, "cudaEventCreate", e); }
     *out = b;
     return SVTME_OK;
@@ -168,10 +176,9 @@ int make_pic(SvtMeHandle *h, uint64_t picture_number, uint32_t width, uint32_t h
     if (rc) return rc;
     SvtMePic *p = new SvtMePic();
     p->picture_number = picture_number; p->width = width; p->height = height; p->staging16 = nullptr;
+    p->reader_slots = 0; p->dg_reader = false;
     size_t total;
     plane_geometry(width, height, p->geom, &total);
-    const size_t tmap_off = total;  // a multiple of 256
-    total += (size_t)kS16Classes * kS16HClasses * kTmapBytes;
     {
         std::lock_guard<std::mutex> lk(h->mu);
         rc = acquire_buffer(h, width, height, total, &p->buf);
@@ -187,30 +194,35 @@ int make_pic(SvtMeHandle *h, uint64_t picture_number, uint32_t width, uint32_t h
         p->dev.lvl[l].ref_org = kRefOrg[l];
     }
     p->dev.picture_number = picture_number;
+    auto give_back = [&](int code) {  // error paths: the buffer returns to the pool
+        std::lock_guard<std::mutex> lk(h->mu);
+        h->free_bufs.push_back(p->buf);
+        delete p;
+        return code;
+    };
     cudaError_t e = cudaEventCreateWithFlags(&p->ready, cudaEventDisableTiming);
-    if (e != cudaSuccess) { delete p; return fail(h, SVTME_ERR_UNDEFINED, "cudaEventCreate", e); }
-    // a recycled buffer may still be read by a search in flight
-    if (p->buf.used_once) cudaStreamWaitEvent(p->stream, p->buf.last_use, 0);
-    // TMA descriptors of the padded sixteenth plane (st_sad16_kernel): encoded once per buffer and picture size
-    p->d_tmap16 = p->buf.base + tmap_off;
-    if (p->buf.map_w != width || p->buf.map_h != height) {
+    if (e != cudaSuccess) return give_back(fail(h, SVTME_ERR_UNDEFINED, "cudaEventCreate", e));
+    // a recycled buffer: everything its previous owner's readers (searches, detector, its own upload) had in flight at
+    // release time precedes `free_ev`
+    if (p->buf.recycled) cudaStreamWaitEvent(p->stream, p->buf.free_ev, 0);
+    // TMA descriptors of the padded sixteenth plane (st_sad16_kernel): encoded once per buffer, kept on the host
+    if (!p->buf.maps) {
         typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                      const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                      CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
         const PlaneGeom &g = p->geom[2];
-        alignas(64) CUtensorMap maps[kS16Classes * kS16HClasses];
         static_assert(sizeof(CUtensorMap) == kTmapBytes, "CUtensorMap is 128 bytes");
+        void *mem = nullptr;
+        if (posix_memalign(&mem, 64, (size_t)kS16Classes * kS16HClasses * kTmapBytes) != 0) { cudaEventDestroy(p->ready); return give_back(fail(h, SVTME_ERR_INSUFFICIENT, "tensor maps")); }
+        p->buf.maps = reinterpret_cast<unsigned char (*)[kTmapBytes]>(mem);
         for (int c = 0; c < kS16Classes * kS16HClasses; c++) {
             const cuuint64_t gdim[2] = {(cuuint64_t)g.stride, (cuuint64_t)(g.h + 2 * g.pad)}, gstr[1] = {(cuuint64_t)g.stride};
             const cuuint32_t box[2] = {(cuuint32_t)kS16BoxBytes[c / kS16HClasses], (cuuint32_t)kS16BoxRows[c % kS16HClasses]}, estr[2] = {1, 1};
             const CUresult   r = reinterpret_cast<EncodeFn>(h->encode_tiled)(
-                &maps[c], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, p->buf.base + g.offset, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-            if (r != CUDA_SUCCESS) { cudaEventDestroy(p->ready); delete p; return fail(h, SVTME_ERR_UNDEFINED, "cuTensorMapEncodeTiled"); }
+                reinterpret_cast<CUtensorMap *>(p->buf.maps[c]), CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, p->buf.base + g.offset, gdim, gstr, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) { cudaEventDestroy(p->ready); return give_back(fail(h, SVTME_ERR_UNDEFINED, "cuTensorMapEncodeTiled")); }
         }
-        e = cudaMemcpyAsync(p->buf.base + tmap_off, maps, sizeof(maps), cudaMemcpyHostToDevice, p->stream);  // pageable source: staged before the call returns
-        if (e != cudaSuccess) { cudaEventDestroy(p->ready); delete p; return fail(h, SVTME_ERR_UNDEFINED, "cudaMemcpyAsync(tensor maps)", e); }
-        p->buf.map_w = width; p->buf.map_h = height;
     }
     *out = p;
     return SVTME_OK;
@@ -284,17 +296,31 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     rc = set_device(h);
     if (rc) return rc;
 
-    // pick a slot (wait for the oldest if all are busy)
+    // pick a slot; when all are in flight, block until another thread's svtme_search_wait frees one (the ME kernel
+    // threads of an encoder each submit and wait for one picture).  If every slot is held by THIS thread nobody else can
+    // free one: that is a caller error, reported instead of deadlocking.
     Inflight *sl = nullptr;
     {
-        std::lock_guard<std::mutex> lk(h->mu);
-        for (auto &s : h->slots)
-            if (!s.busy) { sl = &s; break; }
-        if (!sl) return fail(h, SVTME_ERR_INSUFFICIENT, "all search slots in flight: call svtme_search_wait first");
+        std::unique_lock<std::mutex> lk(h->mu);
+        for (;;) {
+            bool all_mine = true;
+            for (auto &s : h->slots) {
+                if (!s.busy) { sl = &s; break; }
+                if (s.owner != std::this_thread::get_id()) all_mine = false;
+            }
+            if (sl) break;
+            if (all_mine) return fail(h, SVTME_ERR_INSUFFICIENT, "all search slots are held by this thread: call svtme_search_wait first");
+            h->slot_cv.wait(lk);
+        }
         sl->busy = true;
+        sl->owner = std::this_thread::get_id();
         sl->ticket = h->next_ticket++;
     }
-    auto release_slot = [&](int code) { std::lock_guard<std::mutex> lk(h->mu); sl->busy = false; return code; };
+    auto release_slot = [&](int code) {
+        { std::lock_guard<std::mutex> lk(h->mu); sl->busy = false; }
+        h->slot_cv.notify_one();
+        return code;
+    };
     result_layout(n_b64, pu_count, *knobs, extended, &sl->lay);
     if (sl->cap < sl->lay.total) {
         if (sl->d_res) cudaFree(sl->d_res);
@@ -305,7 +331,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
         if (e != cudaSuccess) return release_slot(fail(h, SVTME_ERR_INSUFFICIENT, "result arena", e));
         sl->cap = sl->lay.total;
     }
-    if (h->cfg.pipeline == 0 && sl->states_cap < staged_state_bytes(n_b64)) {
+    if (sl->states_cap < staged_state_bytes(n_b64)) {
         if (sl->d_states) cudaFree(sl->d_states);
         sl->d_states = nullptr; sl->states_cap = 0;
         cudaError_t e = cudaMalloc(&sl->d_states, staged_state_bytes(n_b64));
@@ -314,10 +340,14 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     }
     MeParams p;
     memset(&p, 0, sizeof(p));
+    S16Maps *maps = &sl->maps;  // unused entries keep whatever they held: the kernel only reads the maps of the picture's references
     p.k   = *knobs;
     p.cur = cur->dev;
     for (int l = 0; l < knobs->num_of_list_to_search; l++)
-        for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) { p.refs[l][r] = refs[l][r]->dev; p.tmap16[l][r] = refs[l][r]->d_tmap16; }
+        for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) {
+            p.refs[l][r] = refs[l][r]->dev;
+            memcpy(maps->m[l * kMaxRefs + r], refs[l][r]->buf.maps, sizeof(maps->m[0]));
+        }
     p.n_steps = build_program(p.k, p.prog);
     p.wb = wb; p.hb = hb; p.pu_count = pu_count; p.work_counter = sl->d_counter;
     p.px_counter = reinterpret_cast<unsigned long long *>(sl->d_counter + 2);
@@ -347,9 +377,8 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     if (e == cudaSuccess && p.out.tf_blk_counts) e = cudaMemsetAsync(p.out.tf_blk_counts, 0, 8, st);
     if (e == cudaSuccess && p.out.picture_sums) e = cudaMemsetAsync(p.out.picture_sums, 0, L.bytes[R_PSUM], st);
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_start, st);
-    const int grid = (int)std::min<uint32_t>(n_b64, (uint32_t)(h->sm_count * h->ctas_per_sm));
-    int n_launch = 1;
-    if (e == cudaSuccess) e = h->cfg.pipeline == 0 ? launch_me_picture_staged(p, st, &n_launch) : launch_me_picture(p, grid, st);
+    int n_launch = 0;
+    if (e == cudaSuccess) e = launch_me_picture_staged(p, *maps, st, &n_launch);
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_kernel, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(sl->h_px, sl->d_counter + 2, 8, cudaMemcpyDeviceToHost, st);
     sl->to_host = out != nullptr;
@@ -376,19 +405,17 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
         if (e == cudaSuccess && hi > lo) e = cudaMemcpyAsync(sl->h_res + lo, sl->d_res + lo, hi - lo, cudaMemcpyDeviceToHost, st);
     }
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_done, st);
-    // the planes must outlive this search
-    if (e == cudaSuccess) e = cudaEventRecord(cur->buf.last_use, st);
-    cur->buf.used_once = true;
-    for (int l = 0; l < knobs->num_of_list_to_search && e == cudaSuccess; l++)
-        for (int r = 0; r < knobs->num_of_ref_pic_to_search[l] && e == cudaSuccess; r++) {
-            e = cudaEventRecord(refs[l][r]->buf.last_use, st);
-            refs[l][r]->buf.used_once = true;
-        }
-    if (e != cudaSuccess) return release_slot(fail(h, SVTME_ERR_UNDEFINED, "search launch", e));
     {
+        // the planes must outlive this search: every picture remembers the slots whose streams read it, and its release
+        // waits for the last thing recorded on each of them (`ev_done`, in stream order behind this search)
         std::lock_guard<std::mutex> lk(h->mu);
+        const uint64_t bit = 1ull << (sl - h->slots.data());
+        cur->reader_slots |= bit;
+        for (int l = 0; l < knobs->num_of_list_to_search; l++)
+            for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) refs[l][r]->reader_slots |= bit;
         h->launches += (uint64_t)n_launch;
     }
+    if (e != cudaSuccess) return release_slot(fail(h, SVTME_ERR_UNDEFINED, "search launch", e));
     *ticket = sl->ticket;
     return SVTME_OK;
 }
@@ -406,16 +433,17 @@ int32_t svtme_init(const SvtMeDeviceCfg *cfg, SvtMeHandle **out) {
     h->cfg = *cfg;
     if (h->cfg.max_pictures == 0) h->cfg.max_pictures = 64;
     if (h->cfg.max_inflight == 0) h->cfg.max_inflight = 4;
+    if (h->cfg.max_inflight > 64) h->cfg.max_inflight = 64;  // one bit per slot in SvtMePic::reader_slots
+    if (h->cfg.pipeline != 0) { delete h; return SVTME_ERR_BAD_PARAMETER; }  // only the staged pipeline ships
     const uint32_t inflight = h->cfg.max_inflight;
     cudaError_t e = cudaSetDevice(cfg->device);
     cudaDeviceProp prop;
     if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, cfg->device);
     if (e == cudaSuccess && prop.major < 10) { delete h; return SVTME_ERR_UNDEFINED; }  // built for sm_100a only
-    if (e == cudaSuccess) {
-        h->sm_count    = prop.multiProcessorCount;
-        h->ctas_per_sm = me_max_ctas_per_sm();
-        if (h->ctas_per_sm < 1) e = cudaErrorInvalidConfiguration;
-    }
+    if (e == cudaSuccess) h->sm_count = prop.multiProcessorCount;
+    // opt-ins to more than 48 KB of dynamic shared memory are per device: set them for THIS handle's device
+    if (e == cudaSuccess) e = staged_set_attributes();
+    if (e == cudaSuccess) e = rtcd_set_attributes();
     h->slots.resize(inflight);
     for (auto &s : h->slots) {
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
@@ -456,10 +484,10 @@ void svtme_destroy(SvtMeHandle *h) {
     }
     for (auto &s : h->up_streams)
         if (s) cudaStreamDestroy(s);
-    for (auto &b : h->free_bufs) { cudaFree(b.base); cudaEventDestroy(b.last_use); }
+    for (auto &b : h->free_bufs) { cudaFree(b.base); cudaEventDestroy(b.free_ev); free(b.maps); }
     if (h->d_scratch) cudaFree(h->d_scratch);
     if (h->d_small) cudaFree(h->d_small);
-    if (h->dg_stream) { cudaStreamDestroy(h->dg_stream); cudaEventDestroy(h->dg_e0); cudaEventDestroy(h->dg_e1); }
+    if (h->dg_stream) { cudaStreamDestroy(h->dg_stream); cudaEventDestroy(h->dg_e0); cudaEventDestroy(h->dg_e1); cudaEventDestroy(h->dg_done); }
     if (h->d_dg) cudaFree(h->d_dg);
     if (h->h_dg) cudaFreeHost(h->h_dg);
     delete h;
@@ -536,14 +564,21 @@ int32_t svtme_picture_release(SvtMeHandle *h, SvtMePic *pic) {
     if (!h || !pic) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
     cudaSetDevice(h->cfg.device);
     if (pic->staging16) { cudaEventSynchronize(pic->ready); cudaFree(pic->staging16); }
-    // the buffer goes back to the pool; its next user waits on `last_use` (searches still reading it) on its own stream
-    cudaStreamWaitEvent(pic->stream, pic->ready, 0);
-    cudaEventDestroy(pic->ready);
+    // The buffer goes back to the pool while work that reads it may still be in flight.  The picture's own stream (its
+    // upload and decimation are already in it) waits for the last thing recorded on the stream of every search slot that
+    // read the picture and on the detector stream, then `free_ev` is recorded behind all of that; the buffer's next owner
+    // waits on `free_ev` before it writes.
     {
         std::lock_guard<std::mutex> lk(h->mu);
+        for (size_t i = 0; i < h->slots.size(); i++)
+            if (pic->reader_slots & (1ull << i)) cudaStreamWaitEvent(pic->stream, h->slots[i].ev_done, 0);
+        if (pic->dg_reader && h->dg_done) cudaStreamWaitEvent(pic->stream, h->dg_done, 0);
+        cudaEventRecord(pic->buf.free_ev, pic->stream);
+        pic->buf.recycled = true;
         if (h->free_bufs.size() < h->cfg.max_pictures) h->free_bufs.push_back(pic->buf);
-        else { cudaEventSynchronize(pic->buf.last_use); cudaFree(pic->buf.base); cudaEventDestroy(pic->buf.last_use); }
+        else { cudaEventSynchronize(pic->buf.free_ev); cudaFree(pic->buf.base); cudaEventDestroy(pic->buf.free_ev); free(pic->buf.maps); }
     }
+    cudaEventDestroy(pic->ready);
     delete pic;
     return SVTME_OK;
 }
@@ -585,8 +620,13 @@ int32_t svtme_search_wait(SvtMeHandle *h, uint64_t ticket) {
         sl = find_slot(h, ticket);
         if (!sl || !sl->busy) return fail(h, SVTME_ERR_BAD_PARAMETER, "unknown ticket");
     }
-    CK(cudaSetDevice(h->cfg.device));
-    CK(cudaEventSynchronize(sl->ev_done));
+    cudaError_t we = cudaSetDevice(h->cfg.device);
+    if (we == cudaSuccess) we = cudaEventSynchronize(sl->ev_done);
+    if (we != cudaSuccess) {  // the slot is not left busy forever
+        { std::lock_guard<std::mutex> lk(h->mu); sl->busy = false; }
+        h->slot_cv.notify_one();
+        return fail(h, SVTME_ERR_UNDEFINED, "svtme_search_wait", we);
+    }
     cudaEventElapsedTime(&sl->ms, sl->ev_start, sl->ev_kernel);
     sl->px = *sl->h_px;
     if (sl->to_host) {
@@ -608,9 +648,12 @@ int32_t svtme_search_wait(SvtMeHandle *h, uint64_t ticket) {
                 } else memcpy(dst[i], sl->h_res + L.off[i], L.bytes[i]);
             }
     }
-    std::lock_guard<std::mutex> lk(h->mu);
-    h->last_ms = sl->ms;
-    sl->busy = false;
+    {
+        std::lock_guard<std::mutex> lk(h->mu);
+        h->last_ms = sl->ms;
+        sl->busy = false;
+    }
+    h->slot_cv.notify_one();
     return SVTME_OK;
 }
 
@@ -679,6 +722,7 @@ int32_t svtme_dg_detector_hme_level0(SvtMeHandle *h, SvtMePic *src, SvtMePic *re
         CK(cudaStreamCreateWithFlags(&h->dg_stream, cudaStreamNonBlocking));
         CK(cudaEventCreate(&h->dg_e0));
         CK(cudaEventCreate(&h->dg_e1));
+        CK(cudaEventCreateWithFlags(&h->dg_done, cudaEventDisableTiming));
     }
     if (h->dg_cap < total) {
         if (h->d_dg) cudaFree(h->d_dg);
@@ -699,9 +743,8 @@ int32_t svtme_dg_detector_hme_level0(SvtMeHandle *h, SvtMePic *src, SvtMePic *re
                             reinterpret_cast<int16_t *>(h->d_dg + off_mv), reinterpret_cast<svtme::DgSums *>(h->d_dg), st));
     CK(cudaEventRecord(h->dg_e1, st));
     CK(cudaMemcpyAsync(h->h_dg, h->d_dg, (sb_sad || sb_mv) ? total : 256, cudaMemcpyDeviceToHost, st));
-    CK(cudaEventRecord(src->buf.last_use, st));
-    CK(cudaEventRecord(ref->buf.last_use, st));
-    src->buf.used_once = ref->buf.used_once = true;
+    CK(cudaEventRecord(h->dg_done, st));
+    { std::lock_guard<std::mutex> lk2(h->mu); src->dg_reader = ref->dg_reader = true; }
     CK(cudaStreamSynchronize(st));
     const svtme::DgSums *r = reinterpret_cast<const svtme::DgSums *>(h->h_dg);
     metrics->tot_dist = r->tot_dist; metrics->tot_cplx = r->tot_cplx; metrics->tot_active = r->tot_active;
@@ -731,6 +774,7 @@ int32_t svtme_picture_statistics(SvtMeHandle *h, SvtMePic *pic, uint32_t regions
         CK(cudaStreamCreateWithFlags(&h->dg_stream, cudaStreamNonBlocking));
         CK(cudaEventCreate(&h->dg_e0));
         CK(cudaEventCreate(&h->dg_e1));
+        CK(cudaEventCreateWithFlags(&h->dg_done, cudaEventDisableTiming));
     }
     if (h->dg_cap < total) {
         if (h->d_dg) cudaFree(h->d_dg);
@@ -746,8 +790,8 @@ int32_t svtme_picture_statistics(SvtMeHandle *h, SvtMePic *pic, uint32_t regions
     CK(svtme::launch_hist16(pic->dev.lvl[2], (int)regions_per_width, (int)regions_per_height, (int)decim_step,
                             reinterpret_cast<svtme::StatAcc *>(h->d_dg), st));
     CK(cudaMemcpyAsync(h->h_dg, h->d_dg, sizeof(svtme::StatAcc), cudaMemcpyDeviceToHost, st));
-    CK(cudaEventRecord(pic->buf.last_use, st));
-    pic->buf.used_once = true;
+    CK(cudaEventRecord(h->dg_done, st));
+    { std::lock_guard<std::mutex> lk2(h->mu); pic->dg_reader = true; }
     CK(cudaStreamSynchronize(st));
     // the reference's scaling and rounding (pic_analysis_process.c:1480, 1504-1521)
     const svtme::StatAcc *a = reinterpret_cast<const svtme::StatAcc *>(h->h_dg);
@@ -772,7 +816,7 @@ int32_t svtme_picture_statistics(SvtMeHandle *h, SvtMePic *pic, uint32_t regions
     return SVTME_OK;
 }
 
-const char *svtme_last_error(SvtMeHandle *h) { return h ? h->err.c_str() : "null handle"; }
+const char *svtme_last_error(SvtMeHandle *h) { return h ? t_err.c_str() : "null handle"; }
 
 // ---- RTCD-level entry points: host pointers, synchronous.  Inputs are copied into an aligned device scratch. ----
 static uint8_t *scratch(SvtMeHandle *h, size_t bytes) {
@@ -792,7 +836,7 @@ void svtme_cuda_sad_loop_kernel(SvtMeHandle *h, const uint8_t *src, uint32_t src
                                 int16_t search_area_height) {
     *best_sad = 0xffffff;  // compute_sad_c.c:71
     if (!h || block_width == 0 || block_height == 0 || block_width > 64 || block_height > 64 || search_area_width <= 0 || search_area_height <= 0) return;
-    if (src_stride_raw == 0 || ref_stride % src_stride_raw) { h->err = "ref_stride must be a multiple of src_stride_raw"; return; }
+    if (src_stride_raw == 0 || ref_stride % src_stride_raw) { t_err = "ref_stride must be a multiple of src_stride_raw"; return; }
     std::lock_guard<std::mutex> lk(h->mu);
     cudaSetDevice(h->cfg.device);
     // reference rows touched: (sa_h - 1) * raw + (bh - 1) * ref_stride + sa_w + bw - 1 bytes from `ref`
@@ -801,7 +845,7 @@ void svtme_cuda_sad_loop_kernel(SvtMeHandle *h, const uint8_t *src, uint32_t src
     const size_t d_rstride = al(ref_w + 64, 128), d_sstride = 128;
     const size_t need      = d_rstride * (ref_rows + 1) + d_sstride * block_height + 512;
     uint8_t     *d         = scratch(h, need);
-    if (!d) { h->err = "scratch alloc"; return; }
+    if (!d) { t_err = "scratch alloc"; return; }
     uint8_t *d_ref = d, *d_src = d + al(d_rstride * (ref_rows + 1), 256);
     cudaMemsetAsync(d, 0, need, 0);
     cudaMemcpy2DAsync(d_ref, d_rstride, ref, src_stride_raw, ref_w, ref_rows, cudaMemcpyHostToDevice, 0);
@@ -817,7 +861,7 @@ void svtme_cuda_sad_loop_kernel(SvtMeHandle *h, const uint8_t *src, uint32_t src
     cudaError_t e = launch_rtcd_sad_loop(j, h->d_small, 0);
     if (e == cudaSuccess) e = cudaMemcpy(res, h->d_small, sizeof(res), cudaMemcpyDeviceToHost);
     h->launches++;
-    if (e != cudaSuccess) { h->err = cudaGetErrorString(e); return; }
+    if (e != cudaSuccess) { t_err = cudaGetErrorString(e); return; }
     if (res[0]) { *best_sad = res[1]; *x_search_center = (int16_t)(int32_t)res[2]; *y_search_center = (int16_t)(int32_t)res[3]; }
 }
 
@@ -831,14 +875,14 @@ void svtme_cuda_downsample_2d(SvtMeHandle *h, const uint8_t *input_samples, uint
     const uint32_t oh = (input_area_height - (decim_step >> 1) + decim_step - 1) / decim_step;
     const size_t out_stride = al(ow, 128);
     uint8_t *d = scratch(h, in_stride * input_area_height + out_stride * oh + 512);
-    if (!d) { h->err = "scratch alloc"; return; }
+    if (!d) { t_err = "scratch alloc"; return; }
     uint8_t *d_in = d, *d_out = d + al(in_stride * input_area_height, 256);
     cudaMemcpy2DAsync(d_in, in_stride, input_samples, input_stride, input_area_width, input_area_height, cudaMemcpyHostToDevice, 0);
     cudaError_t e = launch_downsample_generic(d_in, (int)in_stride, (int)input_area_width, (int)input_area_height, d_out, (int)out_stride,
                                               (int)decim_step, 0);
     if (e == cudaSuccess) e = cudaMemcpy2D(decim_samples, decim_stride, d_out, out_stride, ow, oh, cudaMemcpyDeviceToHost);
     h->launches++;
-    if (e != cudaSuccess) h->err = cudaGetErrorString(e);
+    if (e != cudaSuccess) t_err = cudaGetErrorString(e);
 }
 
 uint32_t svtme_cuda_nxm_sad_kernel(SvtMeHandle *h, const uint8_t *src, uint32_t src_stride, const uint8_t *ref, uint32_t ref_stride,
@@ -848,7 +892,7 @@ uint32_t svtme_cuda_nxm_sad_kernel(SvtMeHandle *h, const uint8_t *src, uint32_t 
     cudaSetDevice(h->cfg.device);
     const size_t st = al(width, 128);
     uint8_t *d = scratch(h, 2 * st * height + 512);
-    if (!d) { h->err = "scratch alloc"; return 0; }
+    if (!d) { t_err = "scratch alloc"; return 0; }
     uint8_t *d_src = d, *d_ref = d + al(st * height, 256);
     cudaMemcpy2DAsync(d_src, st, src, src_stride, width, height, cudaMemcpyHostToDevice, 0);
     cudaMemcpy2DAsync(d_ref, st, ref, ref_stride, width, height, cudaMemcpyHostToDevice, 0);
@@ -859,7 +903,7 @@ uint32_t svtme_cuda_nxm_sad_kernel(SvtMeHandle *h, const uint8_t *src, uint32_t 
     cudaError_t e = launch_rtcd_nxm(j, h->d_small, 0);
     if (e == cudaSuccess) e = cudaMemcpy(&res, h->d_small, 4, cudaMemcpyDeviceToHost);
     h->launches++;
-    if (e != cudaSuccess) h->err = cudaGetErrorString(e);
+    if (e != cudaSuccess) t_err = cudaGetErrorString(e);
     return res;
 }
 
@@ -873,7 +917,7 @@ void svtme_cuda_fullpel_search_sblock(SvtMeHandle *h, const uint8_t *src, uint32
     const size_t d_rstride = al(ref_w + 64, 128);
     const size_t need = d_rstride * (ref_rows + 1) + 128 * 64 + 2 * 85 * 4 + 1024;
     uint8_t *d = scratch(h, need);
-    if (!d) { h->err = "scratch alloc"; return; }
+    if (!d) { t_err = "scratch alloc"; return; }
     uint8_t  *d_ref = d, *d_src = d + al(d_rstride * (ref_rows + 1), 256);
     uint32_t *d_bs = (uint32_t *)(d_src + 128 * 64), *d_bm = d_bs + 88;
     cudaMemsetAsync(d, 0, need, 0);
@@ -889,7 +933,7 @@ void svtme_cuda_fullpel_search_sblock(SvtMeHandle *h, const uint8_t *src, uint32
     if (e == cudaSuccess) e = cudaMemcpy(best_sad, d_bs, 85 * 4, cudaMemcpyDeviceToHost);
     if (e == cudaSuccess) e = cudaMemcpy(best_mv, d_bm, 85 * 4, cudaMemcpyDeviceToHost);
     h->launches++;
-    if (e != cudaSuccess) h->err = cudaGetErrorString(e);
+    if (e != cudaSuccess) t_err = cudaGetErrorString(e);
 }
 
 }  // extern "C"

@@ -26,6 +26,40 @@ namespace svtme {
 #define SVTME_MIN(a, b) ((a) < (b) ? (a) : (b))
 #define SVTME_MAX(a, b) ((a) > (b) ? (a) : (b))
 
+// ---- lanes ----
+// A control step is executed by ONE WARP: lane l = (list << 4) | (reference << 2) | quadrant owns reference (li, ri)
+// and one of its (up to) four search jobs -- quadrant (qw, qh) of an HME level, or pre-HME region sr = q < 2.  Lanes
+// exchange data only through the block state (shared memory on the device) between SVTME_WSYNC() points, so the same
+// code runs on the host as 32 sequential iterations (tests/host_emul).  Search jobs live in FIXED slots: SadJob slot =
+// lane, NxmJob slot = 2 * (li * 4 + ri) + {0, 1}, FpJob slot = li * 4 + ri; an unused slot has an empty window.
+#if defined(__CUDA_ARCH__)
+#define SVTME_LANES(l) for (int l = (int)(threadIdx.x & 31u), l##_it = 0; l##_it < 1; ++l##_it)
+#define SVTME_WSYNC() __syncwarp()
+#elif defined(SVTME_LANES_REVERSE)  // host test build: the lanes of a region must not depend on each other's order
+#define SVTME_LANES(l) for (int l = 31; l >= 0; --l)
+#define SVTME_WSYNC() ((void)0)
+#else
+#define SVTME_LANES(l) for (int l = 0; l < 32; ++l)
+#define SVTME_WSYNC() ((void)0)
+#endif
+
+struct LaneRef {
+    int  li, ri, q, qw, qh;
+    bool used;  // (li, ri) is a reference of this picture
+};
+SVTME_HD LaneRef lane_ref(const SvtMeKnobs &k, int l) {
+    LaneRef r;
+    r.li = l >> 4; r.ri = (l >> 2) & 3; r.q = l & 3; r.qw = r.q & 1; r.qh = r.q >> 1;
+    r.used = r.li < k.num_of_list_to_search && r.ri < k.num_of_ref_pic_to_search[r.li];
+    return r;
+}
+constexpr uint8_t kNoJob = 0xff;  // SadJob::level of an unused slot
+SVTME_HD void clear_sad_slot(SbState &s, int slot) {
+    SadJob &j = s.sad_jobs[slot];
+    j.level = kNoJob; j.sa_w = 0; j.sa_h = 0; j.found = 0;
+}
+SVTME_HD int nxm_slot(int li, int ri, int second) { return 2 * (li * 4 + ri) + second; }
+
 SVTME_HD bool hme_active(const SvtMeKnobs &k, int li) { return k.temporal_layer_index > 0 || li == 0; }
 
 // get_me_reference's distance (:1232-1234) and svt_aom_get_scaled_picture_distance (:1239-1243)
@@ -56,14 +90,14 @@ SVTME_HD const uint8_t *cur_block(const MeParams &p, const SbState &s, int lvl) 
     return pl.org + (int64_t)(s.org_y >> lvl) * pl.stride + (s.org_x >> lvl);
 }
 
-// Fill one SadJob for an HME search at `lvl` (0 full, 1 quarter, 2 sixteenth) of reference (li,ri):
+// Fill SadJob `slot` for an HME search at `lvl` (0 full, 1 quarter, 2 sixteenth) of reference (li,ri):
 // the tail of hme_level_0/1/2 / prehme_core (:882-909, 984-1011, 1080-1104, 1631-1655).
-SVTME_HD void make_sad_job(const MeParams &p, SbState &s, int lvl, int li, int ri, int16_t ox, int16_t oy, int16_t w,
+SVTME_HD void make_sad_job(const MeParams &p, SbState &s, int slot, int lvl, int li, int ri, int16_t ox, int16_t oy, int16_t w,
                            int16_t h, uint8_t skip, uint8_t dst_level, uint8_t qw, uint8_t qh) {
     const DevPlane &rp   = p.refs[li][ri].lvl[lvl];
     const DevPlane &cp   = p.cur.lvl[lvl];
     const bool      full = p.k.hme_search_method == 1;  // FULL_SAD_SEARCH
-    SadJob         &j    = s.sad_jobs[s.n_sad++];
+    SadJob         &j    = s.sad_jobs[slot];
     const int16_t org_x = (int16_t)(((int16_t)s.org_x) >> lvl), org_y = (int16_t)(((int16_t)s.org_y) >> lvl);
     j.blk        = cur_block(p, s, lvl);
     j.blk_stride = full ? cp.stride : cp.stride * 2;
@@ -104,37 +138,42 @@ SVTME_HD void fold_sad_job(const MeParams &p, SbState &s, const SadJob &j) {
     }
 }
 
-SVTME_HD void set_quadrants(const SvtMeKnobs &k, SbState &s, int lvl, int li, int ri, int16_t x, int16_t y, uint64_t sad) {
-    for (int h = 0; h < k.num_hme_sa_h; h++)
-        for (int w = 0; w < k.num_hme_sa_w; w++) {
-            s.lx[lvl][li][ri][w][h] = x; s.ly[lvl][li][ri][w][h] = y; s.lsad[lvl][li][ri][w][h] = sad;
-        }
+// set_quadrants of the reference code paths, one quadrant per lane
+SVTME_HD void set_quadrant(const SvtMeKnobs &k, SbState &s, int lvl, const LaneRef &r, int16_t x, int16_t y, uint64_t sad) {
+    if (r.qh < k.num_hme_sa_h && r.qw < k.num_hme_sa_w) {
+        s.lx[lvl][r.li][r.ri][r.qw][r.qh] = x; s.ly[lvl][r.li][r.ri][r.qw][r.qh] = y; s.lsad[lvl][r.li][r.ri][r.qw][r.qh] = sad;
+    }
 }
 
-// init_me_hme_data (:3010-3070) + the block-size derivation of svt_aom_motion_estimation_b64 (:3093-3100)
+// init_me_hme_data (:3010-3070) + the block-size derivation of svt_aom_motion_estimation_b64 (:3093-3100): the CONTROL
+// part of the state (`s`, zeroed by the caller) -- the result tables are initialised by sb_init_tables
+SVTME_HD void sb_init_head(const MeParams &p, SbState &s, SbState *home, uint32_t b64_index) {
+    const DevPlane &f  = p.cur.lvl[0];
+    const uint16_t  aw = (uint16_t)((f.width + 7) & ~7), ah = (uint16_t)((f.height + 7) & ~7);
+    s.home      = home;
+    s.b64_index = b64_index;
+    s.org_x     = (b64_index % p.wb) * 64;
+    s.org_y     = (b64_index / p.wb) * 64;
+    s.b64_w     = (aw - s.org_x) < 64 ? aw - s.org_x : 64;
+    s.b64_h     = (ah - s.org_y) < 64 ? ah - s.org_y : 64;
+    s.src        = f.org + (int64_t)s.org_y * f.stride + s.org_x;
+    s.src_stride = f.stride;
+    s.hme_l0_sa  = p.k.hme_l0_sa;
+    for (int li = 0; li < kMaxLists; li++)
+        for (int ri = 0; ri < kMaxRefs; ri++) {
+            s.do_ref[li][ri] = 1; s.hme_sad[li][ri] = kMaxU32; s.divisor[li][ri] = 1; s.zz_sad[li][ri] = kMaxU32;
+        }
+    for (int i = 0; i < kMaxSadJobs; i++) clear_sad_slot(s, i);
+    s.n_sad = kMaxSadJobs; s.n_nxm = kMaxNxmJobs; s.n_fp = kMaxFpJobs;  // fixed slots; rows / w == 0 marks the unused ones
+}
+
+// host emulation: zero the whole SB state, then the control part and the tables
 template <class B>
 SVTME_HD void sb_init(B &be, const MeParams &p, SbState &s, uint32_t b64_index) {
-    // zero the whole SB state cooperatively (HME centres, best MVs, pre-HME valid flags, performed_phme ...)
     uint32_t *w = reinterpret_cast<uint32_t *>(&s);
     for (uint32_t i = be.tid(); i < sizeof(SbState) / 4; i += be.nthreads()) w[i] = 0;
     be.sync();
-    if (be.leader()) {
-        const DevPlane &f  = p.cur.lvl[0];
-        const uint16_t  aw = (uint16_t)((f.width + 7) & ~7), ah = (uint16_t)((f.height + 7) & ~7);
-        s.home      = &s;
-        s.b64_index = b64_index;
-        s.org_x     = (b64_index % p.wb) * 64;
-        s.org_y     = (b64_index / p.wb) * 64;
-        s.b64_w     = (aw - s.org_x) < 64 ? aw - s.org_x : 64;
-        s.b64_h     = (ah - s.org_y) < 64 ? ah - s.org_y : 64;
-        s.src        = f.org + (int64_t)s.org_y * f.stride + s.org_x;
-        s.src_stride = f.stride;
-        s.hme_l0_sa  = p.k.hme_l0_sa;
-        for (int li = 0; li < kMaxLists; li++)
-            for (int ri = 0; ri < kMaxRefs; ri++) {
-                s.do_ref[li][ri] = 1; s.hme_sad[li][ri] = kMaxU32; s.divisor[li][ri] = 1; s.zz_sad[li][ri] = kMaxU32;
-            }
-    }
+    if (be.leader()) sb_init_head(p, s, &s, b64_index);
     // unsearched references report MAX_SAD_VALUE (convention of include/svtme_cuda.h)
     uint32_t *bs = &s.best_sad[0][0][0];
     be.sync();
@@ -148,9 +187,9 @@ SVTME_HD void sb_init(B &be, const MeParams &p, SbState &s, uint32_t b64_index) 
 
 // Zero-MV (or any fixed-MV) 64x32-subsampled SAD job against the full-resolution plane (get_zz_sad :1667-1689,
 // check_00_center :1153-1163, 1189-1197).
-SVTME_HD void make_nxm_job(const MeParams &p, SbState &s, int li, int ri, int16_t mvx, int16_t mvy, uint8_t kind) {
+SVTME_HD void make_nxm_job(const MeParams &p, SbState &s, int slot, int li, int ri, int16_t mvx, int16_t mvy, uint8_t kind) {
     const DevPlane &rp = p.refs[li][ri].lvl[0];
-    NxmJob         &j  = s.nxm_jobs[s.n_nxm++];
+    NxmJob         &j  = s.nxm_jobs[slot];
     j.src        = s.src;
     j.src_stride = s.src_stride << 1;
     j.ref        = rp.org + (int64_t)((int16_t)s.org_y + mvy) * rp.stride + ((int16_t)s.org_x + mvx);
@@ -159,35 +198,54 @@ SVTME_HD void make_nxm_job(const MeParams &p, SbState &s, int li, int ri, int16_
     j.width      = (int16_t)s.b64_w;
     j.li = (uint8_t)li; j.ri = (uint8_t)ri; j.kind = kind; j.sad = 0;
 }
+SVTME_HD void clear_nxm_slots(SbState &s) {
+    SVTME_LANES(l) if (l < kMaxNxmJobs) { s.nxm_jobs[l].rows = 0; s.nxm_jobs[l].sad = 0; }
+    SVTME_WSYNC();
+}
+SVTME_HD void clear_fp_slots(SbState &s) {
+    SVTME_LANES(l) if (l < kMaxFpJobs) { s.fp_jobs[l].w = 0; s.fp_jobs[l].h = 0; }
+    SVTME_WSYNC();
+}
 
 // ---- init_zz_sad (:2382-2437): make the zero-MV SAD jobs / fold them and prune ----
 SVTME_HD void zz_make(const MeParams &p, SbState &s) {
     const SvtMeKnobs &k = p.k;
-    s.n_nxm = 0;
-    SVTME_FOR_REFS(k, li, ri) if (hme_active(k, li)) make_nxm_job(p, s, li, ri, 0, 0, 0);
+    clear_nxm_slots(s);
+    SVTME_LANES(l) {
+        const LaneRef r = lane_ref(k, l);
+        if (r.used && r.q == 0 && hme_active(k, r.li)) make_nxm_job(p, s, nxm_slot(r.li, r.ri, 0), r.li, r.ri, 0, 0, 0);
+    }
+    SVTME_WSYNC();
 }
 SVTME_HD void zz_fold(const MeParams &p, SbState &s) {
     const SvtMeKnobs &k = p.k;
-    uint32_t best = kMaxU32;
-    for (int i = 0; i < s.n_nxm; i++) {
-        const NxmJob &j = s.nxm_jobs[i];
+    SVTME_LANES(l) {
+        const LaneRef r = lane_ref(k, l);
+        if (r.q != 0) continue;
+        const NxmJob &j = s.nxm_jobs[nxm_slot(r.li, r.ri, 0)];
+        if (j.rows <= 0) continue;
         uint32_t zz = j.sad << 1;
         zz = (zz * 64 * 64) / (s.b64_w * s.b64_h);  // normalise incomplete b64 (:2395)
-        s.zz_sad[j.li][j.ri] = zz;
-        best = SVTME_MIN(best, zz);
+        s.zz_sad[r.li][r.ri] = zz;
     }
-    if (k.temporal_layer_index > 0 && best < k.zz_sad_th) {
-        SVTME_FOR_REFS(k, li, ri) {
-            if (ri == 0) continue;
-            if ((s.zz_sad[li][ri] - best) * 100 > ((uint32_t)k.zz_sad_pct * best)) s.do_ref[li][ri] = 0;  // u32 wrap (:2409)
+    SVTME_WSYNC();
+    SVTME_LANES(l) {
+        const LaneRef r = lane_ref(k, l);
+        if (!r.used || r.q != 0) continue;
+        uint32_t best = kMaxU32;  // over the references whose zero-MV SAD was computed
+        for (int i = 0; i < kMaxLists * kMaxRefs; i++)
+            if (s.nxm_jobs[2 * i].rows > 0) best = SVTME_MIN(best, s.zz_sad[i >> 2][i & 3]);
+        if (k.temporal_layer_index > 0 && best < k.zz_sad_th && r.ri != 0) {
+            if ((s.zz_sad[r.li][r.ri] - best) * 100 > ((uint32_t)k.zz_sad_pct * best)) s.do_ref[r.li][r.ri] = 0;  // u32 wrap (:2409)
+        }
+        if (k.me_safe_limit_zz_th) {
+            const bool safe = k.hierarchical_levels > 0 && k.num_of_list_to_search == 2 &&
+                k.temporal_layer_index >= k.hierarchical_levels && k.similar_brightness_refs &&
+                s.zz_sad[0][0] < k.me_safe_limit_zz_th && s.zz_sad[1][0] < k.me_safe_limit_zz_th;
+            if (safe && r.ri > 0) s.do_ref[r.li][r.ri] = 0;
         }
     }
-    if (k.me_safe_limit_zz_th) {
-        const bool safe = k.hierarchical_levels > 0 && k.num_of_list_to_search == 2 &&
-            k.temporal_layer_index >= k.hierarchical_levels && k.similar_brightness_refs &&
-            s.zz_sad[0][0] < k.me_safe_limit_zz_th && s.zz_sad[1][0] < k.me_safe_limit_zz_th;
-        SVTME_FOR_REFS(k, li, ri) if (safe && ri > 0) s.do_ref[li][ri] = 0;
-    }
+    SVTME_WSYNC();
 }
 
 // ---- prehme_b64 (:1722-1796) with check_prehme_early_exit (:1693-1719) and prehme_core (:1568-1666) ----
@@ -208,61 +266,62 @@ SVTME_HD bool prehme_early_exit(const SvtMeKnobs &k, SbState &s, int li, int ri,
     return false;
 }
 
-SVTME_HD void prehme_make_jobs(const MeParams &p, SbState &s, int li) {
-    const SvtMeKnobs &k = p.k;
-    for (int ri = 0; ri < k.num_of_ref_pic_to_search[li]; ++ri) {
-        const uint32_t f = scaled_dist(ref_dist(p, li, ri));
-        for (int sr = 0; sr < 2; sr++) {
-            if (prehme_early_exit(k, s, li, ri, sr)) continue;
-            PreHme &q = s.prehme[li][ri][sr];
-            if (!s.do_ref[li][ri]) { q.mv_x = 0; q.mv_y = 0; q.sad = kMaxU32; continue; }
-            q.sa_w = (uint16_t)SVTME_MIN((k.prehme_sa_cfg[sr].sa_min.width * f), (uint32_t)k.prehme_sa_cfg[sr].sa_max.width);
-            q.sa_h = (uint16_t)SVTME_MIN((k.prehme_sa_cfg[sr].sa_min.height * f), (uint32_t)k.prehme_sa_cfg[sr].sa_max.height);
-            const DevPlane &rp = p.refs[li][ri].lvl[2];
-            int16_t w = (int16_t)q.sa_w, h = (int16_t)q.sa_h;
-            int16_t ox = (int16_t)(-(int16_t)(w >> 1)), oy = (int16_t)(-(int16_t)(h >> 1));
-            clip_window((int16_t)(((int16_t)s.org_x) >> 2), (int16_t)(((int16_t)s.org_y) >> 2), (int16_t)(rp.ref_org - 1),
-                        (int16_t)(rp.ref_org - 1), (int16_t)rp.width, (int16_t)rp.height, ox, oy, w, h, false);
-            make_sad_job(p, s, 2, li, ri, ox, oy, w, h, k.prehme_skip_search_line, 3, (uint8_t)sr, 0);
-            s.performed_phme[li][ri][sr] = 1;
-        }
-    }
-}
-
 // `arg`: 0 = list 0 only, 1 = list 1 only (its early exit reads the list-0 results, :1706-1717), 2 = both lists.
-// List 1 of a base-layer picture mirrors list 0 (:1769-1777) and has no searches of its own.
+// List 1 of a base-layer picture mirrors list 0 (:1769-1777) and has no searches of its own.  Lane = (li, ri, region).
 SVTME_HD void prehme_make(const MeParams &p, SbState &s, int arg) {
     const SvtMeKnobs &k = p.k;
     const bool l1_active = k.num_of_list_to_search > 1 && hme_active(k, 1);
-    s.n_sad = 0;
-    if (arg == 0 || arg == 2) prehme_make_jobs(p, s, 0);
-    if (l1_active && (arg == 1 || arg == 2)) prehme_make_jobs(p, s, 1);
+    SVTME_LANES(l) {
+        clear_sad_slot(s, l);
+        const LaneRef r = lane_ref(k, l);
+        if (!r.used || r.q >= 2) continue;
+        if (r.li == 0 ? !(arg == 0 || arg == 2) : !(l1_active && (arg == 1 || arg == 2))) continue;
+        const int li = r.li, ri = r.ri, sr = r.q;
+        const uint32_t f = scaled_dist(ref_dist(p, li, ri));
+        if (prehme_early_exit(k, s, li, ri, sr)) continue;
+        PreHme &q = s.prehme[li][ri][sr];
+        if (!s.do_ref[li][ri]) { q.mv_x = 0; q.mv_y = 0; q.sad = kMaxU32; continue; }
+        q.sa_w = (uint16_t)SVTME_MIN((k.prehme_sa_cfg[sr].sa_min.width * f), (uint32_t)k.prehme_sa_cfg[sr].sa_max.width);
+        q.sa_h = (uint16_t)SVTME_MIN((k.prehme_sa_cfg[sr].sa_min.height * f), (uint32_t)k.prehme_sa_cfg[sr].sa_max.height);
+        const DevPlane &rp = p.refs[li][ri].lvl[2];
+        int16_t w = (int16_t)q.sa_w, h = (int16_t)q.sa_h;
+        int16_t ox = (int16_t)(-(int16_t)(w >> 1)), oy = (int16_t)(-(int16_t)(h >> 1));
+        clip_window((int16_t)(((int16_t)s.org_x) >> 2), (int16_t)(((int16_t)s.org_y) >> 2), (int16_t)(rp.ref_org - 1),
+                    (int16_t)(rp.ref_org - 1), (int16_t)rp.width, (int16_t)rp.height, ox, oy, w, h, false);
+        make_sad_job(p, s, l, 2, li, ri, ox, oy, w, h, k.prehme_skip_search_line, 3, (uint8_t)sr, 0);
+        s.performed_phme[li][ri][sr] = 1;
+    }
+    SVTME_WSYNC();
 }
 SVTME_HD void sad_fold(const MeParams &p, SbState &s) {
-    for (int i = 0; i < s.n_sad; i++) fold_sad_job(p, s, s.sad_jobs[i]);
+    SVTME_LANES(l) if (s.sad_jobs[l].level != kNoJob) fold_sad_job(p, s, s.sad_jobs[l]);
+    SVTME_WSYNC();
 }
 SVTME_HD void prehme_final(const MeParams &p, SbState &s) {
     const SvtMeKnobs &k = p.k;
-    uint32_t best_sad = kMaxU32;
-    SVTME_FOR_REFS(k, li, ri) {
-        if (hme_active(k, li)) {
+    SVTME_LANES(l) {  // a list without HME of its own mirrors list 0 (:1769-1777)
+        const LaneRef r = lane_ref(k, l);
+        if (r.used && r.q < 2 && !hme_active(k, r.li)) {
+            s.prehme[1][r.ri][r.q].mv_x = (int16_t)-s.prehme[0][r.ri][r.q].mv_x;
+            s.prehme[1][r.ri][r.q].mv_y = (int16_t)-s.prehme[0][r.ri][r.q].mv_y;
+            s.prehme[1][r.ri][r.q].sad  = s.prehme[0][r.ri][r.q].sad;
+        }
+    }
+    SVTME_WSYNC();
+    SVTME_LANES(l) {
+        const LaneRef r = lane_ref(k, l);
+        if (!r.used || r.q != 0 || r.ri == 0 || !s.do_ref[r.li][r.ri]) continue;
+        uint32_t best_sad = kMaxU32;
+        SVTME_FOR_REFS(k, li, ri) if (hme_active(k, li)) {
             const uint32_t m = (uint32_t)SVTME_MIN(s.prehme[li][ri][0].sad, s.prehme[li][ri][1].sad);
             best_sad         = SVTME_MIN(best_sad, m);
-        } else {
-            for (int sr = 0; sr < 2; sr++) {
-                s.prehme[1][ri][sr].mv_x = (int16_t)-s.prehme[0][ri][sr].mv_x;
-                s.prehme[1][ri][sr].mv_y = (int16_t)-s.prehme[0][ri][sr].mv_y;
-                s.prehme[1][ri][sr].sad  = s.prehme[0][ri][sr].sad;
-            }
+        }
+        if (k.temporal_layer_index > 0 && best_sad < k.phme_sad_th) {
+            const uint32_t m = (uint32_t)SVTME_MIN(s.prehme[r.li][r.ri][0].sad, s.prehme[r.li][r.ri][1].sad);
+            if ((m - best_sad) * 100 > ((uint32_t)k.phme_sad_pct * best_sad)) s.do_ref[r.li][r.ri] = 0;  // u32 wrap (:1790)
         }
     }
-    if (k.temporal_layer_index > 0 && best_sad < k.phme_sad_th) {
-        SVTME_FOR_REFS(k, li, ri) {
-            if (!s.do_ref[li][ri] || ri == 0) continue;
-            const uint32_t m = (uint32_t)SVTME_MIN(s.prehme[li][ri][0].sad, s.prehme[li][ri][1].sad);
-            if ((m - best_sad) * 100 > ((uint32_t)k.phme_sad_pct * best_sad)) s.do_ref[li][ri] = 0;  // u32 wrap (:1790)
-        }
-    }
+    SVTME_WSYNC();
 }
 
 // ---- get_hme_l0_search_area (:1800-1867); works on a private copy of hme_l0_sa, which is what the reference's
@@ -295,32 +354,35 @@ SVTME_HD void hme_l0_area(const MeParams &p, const SbState &s, int li, int ri, i
     sa_w = w; sa_h = h;
 }
 
-// One reference's share of hme_level0_b64 (:1921-2033) up to the job creation.  Returns true if jobs were made.
-SVTME_HD bool hme_l0_make_jobs(const MeParams &p, SbState &s, int li, int ri) {
+// One quadrant of one reference's share of hme_level0_b64 (:1921-2033) up to the job creation.  Returns true if the
+// reference's quadrants are searched.
+SVTME_HD bool hme_l0_make_job(const MeParams &p, SbState &s, int slot, const LaneRef &r) {
     const SvtMeKnobs &k = p.k;
-    if (k.me_early_exit_th && s.zz_sad[li][ri] < (k.me_early_exit_th >> 2)) { set_quadrants(k, s, 0, li, ri, 0, 0, 0); return false; }
+    const int li = r.li, ri = r.ri;
+    if (k.me_early_exit_th && s.zz_sad[li][ri] < (k.me_early_exit_th >> 2)) { set_quadrant(k, s, 0, r, 0, 0, 0); return false; }
     if (k.prev_me_stage_based_exit_th) {
         const int sr = s.prehme[li][ri][0].sad <= s.prehme[li][ri][1].sad ? 0 : 1;
         if (s.performed_phme[li][ri][sr] && s.prehme[li][ri][sr].sad < (k.prev_me_stage_based_exit_th >> 4)) {
-            set_quadrants(k, s, 0, li, ri, s.prehme[li][ri][sr].mv_x, s.prehme[li][ri][sr].mv_y, s.prehme[li][ri][sr].sad);
+            set_quadrant(k, s, 0, r, s.prehme[li][ri][sr].mv_x, s.prehme[li][ri][sr].mv_y, s.prehme[li][ri][sr].sad);
             return false;
         }
     }
-    if (!s.do_ref[li][ri]) { set_quadrants(k, s, 0, li, ri, 0, 0, kMaxU32); return false; }
+    if (!s.do_ref[li][ri]) { set_quadrant(k, s, 0, r, 0, 0, kMaxU32); return false; }
     if (!hme_active(k, li)) return false;
+    if (r.qh >= k.num_hme_sa_h || r.qw >= k.num_hme_sa_w) return true;
     int16_t sa_w = 0, sa_h = 0;
     hme_l0_area(p, s, li, ri, sa_w, sa_h);
     const DevPlane &rp = p.refs[li][ri].lvl[2];
-    for (int qh = 0; qh < k.num_hme_sa_h; qh++)
-        for (int qw = 0; qw < k.num_hme_sa_w; qw++) {  // hme_level_0 (:820-920)
-            int16_t w = (int16_t)((sa_w + 7) & ~0x07), h = sa_h;
-            const int16_t xd = (int16_t)(w * qw), yd = (int16_t)(h * qh);
-            int16_t ox = (int16_t)(-(int16_t)((w * k.num_hme_sa_w) >> 1) + xd);
-            int16_t oy = (int16_t)(-(int16_t)((h * k.num_hme_sa_h) >> 1) + yd);
-            clip_window((int16_t)(((int16_t)s.org_x) >> 2), (int16_t)(((int16_t)s.org_y) >> 2), (int16_t)(rp.ref_org - 1),
-                        (int16_t)(rp.ref_org - 1), (int16_t)rp.width, (int16_t)rp.height, ox, oy, w, h, true);
-            make_sad_job(p, s, 2, li, ri, ox, oy, w, h, 0, 0, (uint8_t)qw, (uint8_t)qh);
-        }
+    {   // hme_level_0 (:820-920)
+        const int qw = r.qw, qh = r.qh;
+        int16_t w = (int16_t)((sa_w + 7) & ~0x07), h = sa_h;
+        const int16_t xd = (int16_t)(w * qw), yd = (int16_t)(h * qh);
+        int16_t ox = (int16_t)(-(int16_t)((w * k.num_hme_sa_w) >> 1) + xd);
+        int16_t oy = (int16_t)(-(int16_t)((h * k.num_hme_sa_h) >> 1) + yd);
+        clip_window((int16_t)(((int16_t)s.org_x) >> 2), (int16_t)(((int16_t)s.org_y) >> 2), (int16_t)(rp.ref_org - 1),
+                    (int16_t)(rp.ref_org - 1), (int16_t)rp.width, (int16_t)rp.height, ox, oy, w, h, true);
+        make_sad_job(p, s, slot, 2, li, ri, ox, oy, w, h, 0, 0, (uint8_t)qw, (uint8_t)qh);
+    }
     return true;
 }
 
@@ -347,130 +409,144 @@ SVTME_HD void hme_l0_replace_worst(const SvtMeKnobs &k, SbState &s, int li, int 
 // `arg`: 0 = reference (0,0) only, 1 = all others (they read the (0,0) level-0 centre, :1804-1825), 2 = all.
 SVTME_HD void l0_make(const MeParams &p, SbState &s, int arg) {
     const SvtMeKnobs &k = p.k;
-    s.n_sad = 0;
-    uint32_t searched = 0;  // bit li*4+ri
-    SVTME_FOR_REFS(k, li, ri) {
-        const bool first = (li == 0 && ri == 0);
-        if (arg != 2 && (first != (arg == 0))) continue;
-        if (hme_l0_make_jobs(p, s, li, ri)) searched |= 1u << (li * 4 + ri);
+    SVTME_LANES(l) {
+        clear_sad_slot(s, l);
+        const LaneRef r = lane_ref(k, l);
+        bool searched = false;
+        const bool first = (r.li == 0 && r.ri == 0);
+        if (r.used && (arg == 2 || (first == (arg == 0)))) searched = hme_l0_make_job(p, s, l, r);
+        if (r.q == 0) s.l0_done[r.li][r.ri] = searched ? 1 : 0;  // references whose quadrants are searched in THIS pass
     }
-    s.l0_searched = searched;
+    SVTME_WSYNC();
 }
 SVTME_HD void l0_fold(const MeParams &p, SbState &s) {
     const SvtMeKnobs &k = p.k;
-    for (int i = 0; i < s.n_sad; i++) fold_sad_job(p, s, s.sad_jobs[i]);
-    const uint32_t searched = s.l0_searched;
-    SVTME_FOR_REFS(k, li, ri) if (searched & (1u << (li * 4 + ri))) hme_l0_replace_worst(k, s, li, ri);
+    sad_fold(p, s);
+    SVTME_LANES(l) {
+        const LaneRef r = lane_ref(k, l);
+        if (r.used && r.q == 0 && s.l0_done[r.li][r.ri]) hme_l0_replace_worst(k, s, r.li, r.ri);
+    }
+    SVTME_WSYNC();
 }
 
 // ---- hme_level1_b64 (:2041-2122) + hme_level_1 (:923-1022) ----
 SVTME_HD void l1_make(const MeParams &p, SbState &s) {
     const SvtMeKnobs &k = p.k;
-    s.n_sad = 0;
-    SVTME_FOR_REFS(k, li, ri) {
-        if (!hme_active(k, li)) continue;
-        if (k.me_early_exit_th && s.zz_sad[li][ri] < (k.me_early_exit_th >> 2)) { set_quadrants(k, s, 1, li, ri, 0, 0, 0); continue; }
-        if (!s.do_ref[li][ri]) { set_quadrants(k, s, 1, li, ri, 0, 0, kMaxU32); continue; }
+    SVTME_LANES(l) {
+        clear_sad_slot(s, l);
+        const LaneRef r = lane_ref(k, l);
+        const int li = r.li, ri = r.ri, qw = r.qw, qh = r.qh;
+        if (!r.used || !hme_active(k, li)) continue;
+        if (k.me_early_exit_th && s.zz_sad[li][ri] < (k.me_early_exit_th >> 2)) { set_quadrant(k, s, 1, r, 0, 0, 0); continue; }
+        if (!s.do_ref[li][ri]) { set_quadrant(k, s, 1, r, 0, 0, kMaxU32); continue; }
+        if (qh >= k.num_hme_sa_h || qw >= k.num_hme_sa_w) continue;
         const DevPlane &rp = p.refs[li][ri].lvl[1];
-        for (int qh = 0; qh < k.num_hme_sa_h; qh++)
-            for (int qw = 0; qw < k.num_hme_sa_w; qw++) {
-                if (k.prev_me_stage_based_exit_th && s.lsad[0][li][ri][qw][qh] < (k.prev_me_stage_based_exit_th >> 5)) {
-                    s.lx[1][li][ri][qw][qh] = s.lx[0][li][ri][qw][qh]; s.ly[1][li][ri][qw][qh] = s.ly[0][li][ri][qw][qh];
-                    s.lsad[1][li][ri][qw][qh] = s.lsad[0][li][ri][qw][qh];
-                    continue;
-                }
-                int16_t w = (int16_t)(((int16_t)k.hme_l1_sa.width + 7) & ~0x07), h = (int16_t)k.hme_l1_sa.height;
-                const int16_t cx = (int16_t)(s.lx[0][li][ri][qw][qh] >> 1), cy = (int16_t)(s.ly[0][li][ri][qw][qh] >> 1);
-                int16_t ox = (int16_t)(-(w >> 1) + cx), oy = (int16_t)(-(h >> 1) + cy);
-                clip_window((int16_t)(((int16_t)s.org_x) >> 1), (int16_t)(((int16_t)s.org_y) >> 1), (int16_t)(rp.ref_org - 1),
-                            (int16_t)(rp.ref_org - 1), (int16_t)rp.width, (int16_t)rp.height, ox, oy, w, h, true);
-                make_sad_job(p, s, 1, li, ri, ox, oy, w, h, 0, 1, (uint8_t)qw, (uint8_t)qh);
-            }
+        if (k.prev_me_stage_based_exit_th && s.lsad[0][li][ri][qw][qh] < (k.prev_me_stage_based_exit_th >> 5)) {
+            s.lx[1][li][ri][qw][qh] = s.lx[0][li][ri][qw][qh]; s.ly[1][li][ri][qw][qh] = s.ly[0][li][ri][qw][qh];
+            s.lsad[1][li][ri][qw][qh] = s.lsad[0][li][ri][qw][qh];
+            continue;
+        }
+        int16_t w = (int16_t)(((int16_t)k.hme_l1_sa.width + 7) & ~0x07), h = (int16_t)k.hme_l1_sa.height;
+        const int16_t cx = (int16_t)(s.lx[0][li][ri][qw][qh] >> 1), cy = (int16_t)(s.ly[0][li][ri][qw][qh] >> 1);
+        int16_t ox = (int16_t)(-(w >> 1) + cx), oy = (int16_t)(-(h >> 1) + cy);
+        clip_window((int16_t)(((int16_t)s.org_x) >> 1), (int16_t)(((int16_t)s.org_y) >> 1), (int16_t)(rp.ref_org - 1),
+                    (int16_t)(rp.ref_org - 1), (int16_t)rp.width, (int16_t)rp.height, ox, oy, w, h, true);
+        make_sad_job(p, s, l, 1, li, ri, ox, oy, w, h, 0, 1, (uint8_t)qw, (uint8_t)qh);
     }
+    SVTME_WSYNC();
 }
 
 // ---- hme_level2_b64 (:2127-2177) + hme_level_2 (:1025-1113; pad is BLOCK_SIZE_64-1 regardless of the buffer) ----
 SVTME_HD void l2_make(const MeParams &p, SbState &s) {
     const SvtMeKnobs &k = p.k;
-    s.n_sad = 0;
-    SVTME_FOR_REFS(k, li, ri) {
-        if (!hme_active(k, li)) continue;
+    SVTME_LANES(l) {
+        clear_sad_slot(s, l);
+        const LaneRef r = lane_ref(k, l);
+        const int li = r.li, ri = r.ri, qw = r.qw, qh = r.qh;
+        if (!r.used || !hme_active(k, li) || qh >= k.num_hme_sa_h || qw >= k.num_hme_sa_w) continue;
         const DevPlane &rp = p.refs[li][ri].lvl[0];
-        for (int qh = 0; qh < k.num_hme_sa_h; qh++)
-            for (int qw = 0; qw < k.num_hme_sa_w; qw++) {
-                if (k.prev_me_stage_based_exit_th && s.lsad[1][li][ri][qw][qh] < (k.prev_me_stage_based_exit_th >> 2)) {
-                    s.lx[2][li][ri][qw][qh] = s.lx[1][li][ri][qw][qh]; s.ly[2][li][ri][qw][qh] = s.ly[1][li][ri][qw][qh];
-                    s.lsad[2][li][ri][qw][qh] = s.lsad[1][li][ri][qw][qh];
-                    continue;
-                }
-                int16_t w = (int16_t)(((int16_t)k.hme_l2_sa.width + 7) & ~0x07), h = (int16_t)k.hme_l2_sa.height;
-                int16_t ox = (int16_t)(-(w >> 1) + s.lx[1][li][ri][qw][qh]), oy = (int16_t)(-(h >> 1) + s.ly[1][li][ri][qw][qh]);
-                clip_window((int16_t)s.org_x, (int16_t)s.org_y, 63, 63, (int16_t)rp.width, (int16_t)rp.height, ox, oy, w, h, true);
-                make_sad_job(p, s, 0, li, ri, ox, oy, w, h, 0, 2, (uint8_t)qw, (uint8_t)qh);
-            }
+        if (k.prev_me_stage_based_exit_th && s.lsad[1][li][ri][qw][qh] < (k.prev_me_stage_based_exit_th >> 2)) {
+            s.lx[2][li][ri][qw][qh] = s.lx[1][li][ri][qw][qh]; s.ly[2][li][ri][qw][qh] = s.ly[1][li][ri][qw][qh];
+            s.lsad[2][li][ri][qw][qh] = s.lsad[1][li][ri][qw][qh];
+            continue;
+        }
+        int16_t w = (int16_t)(((int16_t)k.hme_l2_sa.width + 7) & ~0x07), h = (int16_t)k.hme_l2_sa.height;
+        int16_t ox = (int16_t)(-(w >> 1) + s.lx[1][li][ri][qw][qh]), oy = (int16_t)(-(h >> 1) + s.ly[1][li][ri][qw][qh]);
+        clip_window((int16_t)s.org_x, (int16_t)s.org_y, 63, 63, (int16_t)rp.width, (int16_t)rp.height, ox, oy, w, h, true);
+        make_sad_job(p, s, l, 0, li, ri, ox, oy, w, h, 0, 2, (uint8_t)qw, (uint8_t)qh);
     }
+    SVTME_WSYNC();
 }
 
-// ---- set_final_seach_centre_sb (:2182-2380) followed by hme_prune_ref_and_adjust_sr (:2477-2518); leader only ----
+// ---- set_final_seach_centre_sb (:2182-2380) followed by hme_prune_ref_and_adjust_sr (:2477-2518) ----
 SVTME_HD void final_centre_and_prune(const MeParams &p, SbState &s) {
     const SvtMeKnobs &k = p.k;
-    int16_t  xc = 0, yc = 0, sx = 0, sy = 0;
-    uint64_t hme_mv_sad = 0;  // carries over between references exactly like the reference's local (:2193, 2370)
-    SVTME_FOR_REFS(k, li, ri) {
-        if (hme_active(k, li)) {
-            if (k.enable_hme_flag) {
-                int L = -1;  // the three per-level blocks of the reference are mutually exclusive
-                if (k.enable_hme_level0_flag && !k.enable_hme_level1_flag && !k.enable_hme_level2_flag) L = 0;
-                if (k.enable_hme_level1_flag && !k.enable_hme_level2_flag) L = 1;
-                if (k.enable_hme_level2_flag) L = 2;
-                if (L >= 0) {
-                    xc = s.lx[L][li][ri][0][0]; yc = s.ly[L][li][ri][0][0]; hme_mv_sad = s.lsad[L][li][ri][0][0];
-                    uint32_t w = 1, h = 0;  // scan starts at [1][0]: ties keep the earlier quadrant (:2226-2261)
-                    while (h < k.num_hme_sa_h) {
-                        while (w < k.num_hme_sa_w) {
-                            if (s.lsad[L][li][ri][w][h] < hme_mv_sad) {
-                                xc = s.lx[L][li][ri][w][h]; yc = s.ly[L][li][ri][w][h]; hme_mv_sad = s.lsad[L][li][ri][w][h];
-                            }
-                            w++;
-                        }
-                        w = 0; h++;
-                    }
-                }
-                sx = xc; sy = yc;
+    int L = -1;  // the three per-level blocks of the reference are mutually exclusive
+    if (k.enable_hme_level0_flag && !k.enable_hme_level1_flag && !k.enable_hme_level2_flag) L = 0;
+    if (k.enable_hme_level1_flag && !k.enable_hme_level2_flag) L = 1;
+    if (k.enable_hme_level2_flag) L = 2;
+    // a reference with HME results of its own: the minimum over its quadrants, lane = reference
+    SVTME_LANES(l) {
+        const LaneRef r = lane_ref(k, l);
+        if (!r.used || r.q != 0 || !hme_active(k, r.li) || !k.enable_hme_flag || L < 0) continue;
+        const int li = r.li, ri = r.ri;
+        int16_t  xc = s.lx[L][li][ri][0][0], yc = s.ly[L][li][ri][0][0];
+        uint64_t sad = s.lsad[L][li][ri][0][0];
+        uint32_t w = 1, h = 0;  // scan starts at [1][0]: ties keep the earlier quadrant (:2226-2261)
+        while (h < k.num_hme_sa_h) {
+            while (w < k.num_hme_sa_w) {
+                if (s.lsad[L][li][ri][w][h] < sad) { xc = s.lx[L][li][ri][w][h]; yc = s.ly[L][li][ri][w][h]; sad = s.lsad[L][li][ri][w][h]; }
+                w++;
             }
-        } else {
-            sx = 0; sy = 0;
+            w = 0; h++;
         }
-        s.hme_sc_x[li][ri] = sx; s.hme_sc_y[li][ri] = sy; s.hme_sad[li][ri] = hme_mv_sad;
+        s.hme_sc_x[li][ri] = xc; s.hme_sc_y[li][ri] = yc; s.hme_sad[li][ri] = sad;
     }
-    if (k.me_type == SVTME_ME_MCTF) {
+    SVTME_WSYNC();
+    // the reference's locals carry over from one reference to the next (:2193, 2370): one lane walks the lists
+    SVTME_LANES(l) {
+        if (l != 0) continue;
+        int16_t  xc = 0, yc = 0, sx = 0, sy = 0;
+        uint64_t hme_mv_sad = 0;
+        SVTME_FOR_REFS(k, li, ri) {
+            if (hme_active(k, li)) {
+                if (k.enable_hme_flag) {
+                    if (L >= 0) { xc = s.hme_sc_x[li][ri]; yc = s.hme_sc_y[li][ri]; hme_mv_sad = s.hme_sad[li][ri]; }
+                    sx = xc; sy = yc;
+                }
+            } else {
+                sx = 0; sy = 0;
+            }
+            s.hme_sc_x[li][ri] = sx; s.hme_sc_y[li][ri] = sy; s.hme_sad[li][ri] = hme_mv_sad;
+        }
         // temporal-filter mode: no reference pruning or SR adjustment (:3103); a block whose HME SAD is already under
         // the threshold skips the integer search altogether (:3109-3113)
-        s.tf_exit = s.hme_sad[0][0] < k.tf_me_exit_th;
-        return;
+        if (k.me_type == SVTME_ME_MCTF) s.tf_exit = s.hme_sad[0][0] < k.tf_me_exit_th;
     }
+    SVTME_WSYNC();
+    if (k.me_type == SVTME_ME_MCTF) return;
     if (!k.enable_hme_flag) return;  // prune_ref = enable_hme_flag && me_type != ME_MCTF (:3103, 3115)
     const uint16_t th = k.prune_ref_if_hme_sad_dev_bigger_than_th;
-    if (k.enable_me_hme_ref_pruning && th != (uint16_t)~0) {
-        uint64_t best = ~0ull;  // over ALL [2][4] slots; unused ones hold the init value MAX_U32
-        for (int i = 0; i < kMaxLists; i++)
-            for (int j = 0; j < kMaxRefs; j++)
-                if (s.hme_sad[i][j] < best) best = s.hme_sad[i][j];
-        for (int li = 0; li < kMaxLists; li++)
-            for (int ri = 1; ri < kMaxRefs; ri++)
-                if ((s.hme_sad[li][ri] - best) * 100 > ((uint64_t)th * best)) s.do_ref[li][ri] = 0;  // u64 wrap (:2492)
+    SVTME_LANES(l) {  // every [2][4] slot, used or not
+        const int li = l >> 4, ri = (l >> 2) & 3;
+        if ((l & 3) != 0) continue;
+        if (k.enable_me_hme_ref_pruning && th != (uint16_t)~0 && ri >= 1) {
+            uint64_t best = ~0ull;  // over ALL [2][4] slots; unused ones hold the init value MAX_U32
+            for (int i = 0; i < kMaxLists; i++)
+                for (int j = 0; j < kMaxRefs; j++)
+                    if (s.hme_sad[i][j] < best) best = s.hme_sad[i][j];
+            if ((s.hme_sad[li][ri] - best) * 100 > ((uint64_t)th * best)) s.do_ref[li][ri] = 0;  // u64 wrap (:2492)
+        }
+        if (k.enable_me_sr_adjustment) {
+            if (SVTME_ABS(s.hme_sc_x[li][ri]) <= k.reduce_me_sr_based_on_mv_length_th &&
+                SVTME_ABS(s.hme_sc_y[li][ri]) <= k.reduce_me_sr_based_on_mv_length_th &&
+                s.hme_sad[li][ri] < k.stationary_hme_sad_abs_th)
+                s.divisor[li][ri] = k.stationary_me_sr_divisor;
+            else if (s.hme_sad[li][ri] < k.reduce_me_sr_based_on_hme_sad_abs_th)
+                s.divisor[li][ri] = k.me_sr_divisor_for_low_hme_sad;
+        }
     }
-    if (k.enable_me_sr_adjustment) {
-        for (int li = 0; li < kMaxLists; li++)
-            for (int ri = 0; ri < kMaxRefs; ri++) {
-                if (SVTME_ABS(s.hme_sc_x[li][ri]) <= k.reduce_me_sr_based_on_mv_length_th &&
-                    SVTME_ABS(s.hme_sc_y[li][ri]) <= k.reduce_me_sr_based_on_mv_length_th &&
-                    s.hme_sad[li][ri] < k.stationary_hme_sad_abs_th)
-                    s.divisor[li][ri] = k.stationary_me_sr_divisor;
-                else if (s.hme_sad[li][ri] < k.reduce_me_sr_based_on_hme_sad_abs_th)
-                    s.divisor[li][ri] = k.me_sr_divisor_for_low_hme_sad;
-            }
-    }
+    SVTME_WSYNC();
 }
 
 // ---- integer_search_b64 (:1249-1516), split into its data-dependent steps ----
@@ -506,8 +582,8 @@ SVTME_HD void isearch_c00_jobs(const MeParams &p, SbState &s, int li, int ri) {
     yc = ((org_y + yc) > (int16_t)rp.height - 1) ? (int16_t)(yc - ((org_y + yc) - ((int16_t)rp.height - 1))) : yc;
     s.isc_x[li][ri] = xc; s.isc_y[li][ri] = yc;
     s.c00_done[li][ri] = 1;
-    if (!k.me_early_exit_th) make_nxm_job(p, s, li, ri, 0, 0, 1);  // zero-MV SAD (else zz_sad is reused, :1155-1156)
-    make_nxm_job(p, s, li, ri, xc, yc, 2);                         // HME-centre SAD
+    if (!k.me_early_exit_th) make_nxm_job(p, s, nxm_slot(li, ri, 0), li, ri, 0, 0, 1);  // zero-MV SAD (else zz_sad is reused, :1155-1156)
+    make_nxm_job(p, s, nxm_slot(li, ri, 1), li, ri, xc, yc, 2);                         // HME-centre SAD
 }
 
 // Step B (:1321-1365 + 1391-1412): early exit / SR adjustment, then decide whether the 8x8-variance probe runs.
@@ -539,25 +615,19 @@ SVTME_HD void isearch_adjust(const MeParams &p, SbState &s, int li, int ri, uint
 
 SVTME_HD void make_fp_job(const MeParams &p, SbState &s, int li, int ri, int16_t xo, int16_t yo, int16_t w, int16_t h) {
     const DevPlane &rp = p.refs[li][ri].lvl[0];
-    FpJob          &j  = s.fp_jobs[s.n_fp++];
+    FpJob          &j  = s.fp_jobs[li * kMaxRefs + ri];
     j.ref        = rp.org + (int64_t)((int32_t)s.org_y + yo) * rp.stride + ((int32_t)s.org_x + xo);
     j.ref_stride = rp.stride;
     j.xo = xo; j.yo = yo; j.w = w; j.h = h; j.li = (uint8_t)li; j.ri = (uint8_t)ri;
 }
 
-// Step C (:1414-1491): 8x8-variance scaling of the area, then clip to the picture (+63 px) and queue the main scan.
-SVTME_HD void isearch_final_job(const MeParams &p, SbState &s, int li, int ri) {
+// Step C (:1414-1491): 8x8-variance scaling of the area (`ssq` = sum of squared deviations of the 64 8x8 SADs of the
+// probe, wrapped to 32 bits as in the reference), then clip to the picture (+63 px) and queue the main scan.
+SVTME_HD void isearch_final_job(const MeParams &p, SbState &s, int li, int ri, uint32_t ssq) {
     const SvtMeKnobs &k = p.k;
     int16_t w = s.isa_w[li][ri], h = s.isa_h[li][ri];
     const int16_t xc = s.isc_x[li][ri], yc = s.isc_y[li][ri];
     if (s.probe[li][ri]) {
-        const uint32_t *bs = s.home->best_sad[li][ri];
-        const uint32_t  mean = bs[0] / 64;
-        uint32_t        ssq  = 0;
-        for (int i = 0; i < 64; i++) {
-            const int32_t d = (int32_t)bs[21 + i] - (int32_t)mean;
-            ssq += (uint32_t)(d * d);
-        }
         const uint32_t var = ssq / 64;
         if (var > k.me_sr_mult2_th) { w = (int16_t)((SVTME_MAX(1, w * 3 / 2) + 7) & ~0x7); h = (int16_t)SVTME_MAX(1, h * 3 / 2); }
         if (var < k.me_sr_div4_th) {
@@ -592,56 +662,89 @@ SVTME_HD bool is_in_pass(const SbState &s, int li, int ri, int arg) {
 // A: area from distance / MV / divisor, and the zero-MV / HME-centre SAD jobs of check_00_center
 SVTME_HD void is_a(const MeParams &p, SbState &s, int arg) {
     const SvtMeKnobs &k = p.k;
-    s.n_nxm = 0;
-    SVTME_FOR_REFS(k, li, ri) {
-        if (!is_in_pass(s, li, ri, arg)) continue;
-        isearch_area(p, s, li, ri);
-        if (!k.me_early_exit_th && (s.isc_x[li][ri] != 0 || s.isc_y[li][ri] != 0) && k.is_ref) isearch_c00_jobs(p, s, li, ri);
+    clear_nxm_slots(s);
+    SVTME_LANES(l) {
+        const LaneRef r = lane_ref(k, l);
+        if (!r.used || r.q != 0 || !is_in_pass(s, r.li, r.ri, arg)) continue;
+        isearch_area(p, s, r.li, r.ri);
+        if (!k.me_early_exit_th && (s.isc_x[r.li][r.ri] != 0 || s.isc_y[r.li][r.ri] != 0) && k.is_ref) isearch_c00_jobs(p, s, r.li, r.ri);
     }
+    SVTME_WSYNC();
 }
 // B: early exit / SR adjustment; queue the 1x1 probe at the search centre, which runs BEFORE the main scan on the
 // same best arrays (:1391-1412)
 SVTME_HD void is_b(const MeParams &p, SbState &s, int arg) {
     const SvtMeKnobs &k = p.k;
-    s.n_fp = 0;
-    SVTME_FOR_REFS(k, li, ri) {
-        if (!is_in_pass(s, li, ri, arg)) continue;
-        uint32_t zero_raw = s.zz_sad[li][ri], hme_raw = 0;  // zz_sad stands in for the zero-MV SAD when early exit is on
-        for (int i = 0; i < s.n_nxm; i++) {
-            const NxmJob &j = s.nxm_jobs[i];
-            if (j.li != li || j.ri != ri) continue;
-            if (j.kind == 1) zero_raw = j.sad;
-            if (j.kind == 2) hme_raw = j.sad;
-        }
+    clear_fp_slots(s);
+    SVTME_LANES(l) {
+        const LaneRef r = lane_ref(k, l);
+        if (!r.used || r.q != 0 || !is_in_pass(s, r.li, r.ri, arg)) continue;
+        const int li = r.li, ri = r.ri;
+        const NxmJob &jz = s.nxm_jobs[nxm_slot(li, ri, 0)], &jh = s.nxm_jobs[nxm_slot(li, ri, 1)];
+        // zz_sad stands in for the zero-MV SAD when early exit is on
+        const uint32_t zero_raw = (jz.rows > 0 && jz.kind == 1) ? jz.sad : s.zz_sad[li][ri];
+        const uint32_t hme_raw  = (jh.rows > 0 && jh.kind == 2) ? jh.sad : 0;
         isearch_adjust(p, s, li, ri, zero_raw, hme_raw);
         if (s.probe[li][ri]) make_fp_job(p, s, li, ri, s.isc_x[li][ri], s.isc_y[li][ri], 1, 1);
     }
+    SVTME_WSYNC();
 }
-// C: 8x8-variance scaling, clipping, the main scan
+// C: 8x8-variance scaling, clipping, the main scan.  The four lanes of a reference share the 64 8x8 SADs of its probe.
 SVTME_HD void is_c(const MeParams &p, SbState &s, int arg) {
     const SvtMeKnobs &k = p.k;
-    s.n_fp = 0;
-    SVTME_FOR_REFS(k, li, ri) if (is_in_pass(s, li, ri, arg)) isearch_final_job(p, s, li, ri);
+    clear_fp_slots(s);
+    SVTME_LANES(l) {
+        const LaneRef r = lane_ref(k, l);
+        uint32_t      part = 0;
+        if (r.used && is_in_pass(s, r.li, r.ri, arg) && s.probe[r.li][r.ri]) {
+            const uint32_t *bs = s.home->best_sad[r.li][r.ri];
+            const uint32_t  mean = bs[0] / 64;
+            for (int i = 16 * r.q; i < 16 * r.q + 16; i++) {
+                const int32_t d = (int32_t)bs[21 + i] - (int32_t)mean;
+                part += (uint32_t)(d * d);
+            }
+        }
+        s.scratch[l] = part;
+    }
+    SVTME_WSYNC();
+    SVTME_LANES(l) {
+        const LaneRef r = lane_ref(k, l);
+        if (!r.used || r.q != 0 || !is_in_pass(s, r.li, r.ri, arg)) continue;
+        isearch_final_job(p, s, r.li, r.ri, s.scratch[l] + s.scratch[l + 1] + s.scratch[l + 2] + s.scratch[l + 3]);
+    }
+    SVTME_WSYNC();
 }
 
-// ---- me_prune_ref (:1522-1565); leader only ----
+// ---- me_prune_ref (:1522-1565) ----
 SVTME_HD void me_prune_ref(const MeParams &p, SbState &s) {
     const SvtMeKnobs &k = p.k;
-    SVTME_FOR_REFS(k, li, ri) {
-        if (s.do_ref[li][ri] == 0) { s.hme_sad[li][ri] = (uint64_t)SVTME_MAX_SAD_VALUE * 64; continue; }
-        uint64_t sum = 0;
-        for (int i = 0; i < 64; i++) sum += s.home->best_sad[li][ri][21 + i];
-        s.hme_sad[li][ri] = sum;
+    SVTME_LANES(l) {
+        const LaneRef r = lane_ref(k, l);
+        uint64_t      part = 0;
+        if (r.used && s.do_ref[r.li][r.ri])
+            for (int i = 16 * r.q; i < 16 * r.q + 16; i++) part += s.home->best_sad[r.li][r.ri][21 + i];
+        s.scratch64[l] = part;
     }
+    SVTME_WSYNC();
+    SVTME_LANES(l) {
+        const LaneRef r = lane_ref(k, l);
+        if (!r.used || r.q != 0) continue;
+        s.hme_sad[r.li][r.ri] = s.do_ref[r.li][r.ri] == 0 ? (uint64_t)SVTME_MAX_SAD_VALUE * 64
+                                                           : s.scratch64[l] + s.scratch64[l + 1] + s.scratch64[l + 2] + s.scratch64[l + 3];
+    }
+    SVTME_WSYNC();
     const uint16_t th = k.prune_ref_if_me_sad_dev_bigger_than_th;
     if (k.enable_me_hme_ref_pruning && th != (uint16_t)~0) {
-        uint64_t best = ~0ull;
-        for (int i = 0; i < kMaxLists; i++)
-            for (int j = 0; j < kMaxRefs; j++)
-                if (s.hme_sad[i][j] < best) best = s.hme_sad[i][j];
-        for (int li = 0; li < kMaxLists; li++)
-            for (int ri = 1; ri < kMaxRefs; ri++)
-                if ((s.hme_sad[li][ri] - best) * 100 > ((uint64_t)th * best)) s.do_ref[li][ri] = 0;
+        SVTME_LANES(l) {
+            const int li = l >> 4, ri = (l >> 2) & 3;
+            if ((l & 3) != 0 || ri < 1) continue;
+            uint64_t best = ~0ull;
+            for (int i = 0; i < kMaxLists; i++)
+                for (int j = 0; j < kMaxRefs; j++)
+                    if (s.hme_sad[i][j] < best) best = s.hme_sad[i][j];
+            if ((s.hme_sad[li][ri] - best) * 100 > ((uint64_t)th * best)) s.do_ref[li][ri] = 0;
+        }
+        SVTME_WSYNC();
     }
 }
 
@@ -671,13 +774,14 @@ SVTME_HD unsigned number_of_pus(const SvtMeKnobs &k) { return k.enable_me_16x16 
 
 SVTME_HD void cand_one_pu(const MeParams &p, SbState &s, const SbOut &o, unsigned n) {
     const SvtMeKnobs &k   = p.k;
+    SbState          &t   = *s.home;  // the result tables live in the block's own state (HBM/L2)
     const uint8_t    *nr  = k.num_of_ref_pic_to_search;
     const bool        use = use_me_pu(k, n);
     if (nr[0] == 1 && nr[1] == 0) {  // construct_me_candidate_array_single_ref (:2646-2697)
         const unsigned pu = z_to_raster(n);
-        s.me_distortion[pu] = s.best_sad[0][0][n];
+        t.me_distortion[pu] = t.best_sad[0][0][n];
         if (s.do_ref[0][0] == 0) return;
-        if (use) { o.cand[pu * k.max_cand] = pack_cand(0, 0, 0, 0, 0); o.mv[pu * k.max_refs] = s.best_mv[0][0][n]; }
+        if (use) { o.cand[pu * k.max_cand] = pack_cand(0, 0, 0, 0, 0); o.mv[pu * k.max_refs] = t.best_mv[0][0][n]; }
         return;
     }
     if (nr[0] == 1 && nr[1] == 1) {  // construct_me_candidate_array_mrp_off (:2532-2645)
@@ -688,24 +792,24 @@ SVTME_HD void cand_one_pu(const MeParams &p, SbState &s, const SbOut &o, unsigne
         const uint32_t prune_th = (org0 && org1) ? (uint32_t)k.prune_me_candidates_th : 0;
         uint8_t blk[2] = {org0, org1};
         uint8_t off = 0;
-        const uint32_t s0 = s.best_sad[0][0][n], s1 = s.best_sad[1][0][n];
+        const uint32_t s0 = t.best_sad[0][0][n], s1 = t.best_sad[1][0][n];
         const uint32_t best = (org0 && org1) ? SVTME_MIN(s0, s1) : org0 ? s0 : s1;
-        s.me_distortion[pu] = best;
+        t.me_distortion[pu] = best;
         int min_list = -1;
         if (k.use_best_unipred_cand_only && blk[0] && blk[1]) min_list = s0 < s1 ? 0 : 1;
         for (int li = 0; (uint32_t)li < num_lists && (use || off == 0); ++li) {
             if (blk[li] == 0) continue;
             if (prune_th > 0) {
-                const uint32_t d = (s.best_sad[li][0][n] - best) * 100;  // u32 (:2597-2600)
+                const uint32_t d = (t.best_sad[li][0][n] - best) * 100;  // u32 (:2597-2600)
                 if (d > (best * prune_th)) { blk[li] = 0; continue; }
             }
             if (min_list != -1 && min_list != li) {
-                if (use) o.mv[pu * k.max_refs + (li ? k.max_l0 : 0)] = s.best_mv[li][0][n];
+                if (use) o.mv[pu * k.max_refs + (li ? k.max_l0 : 0)] = t.best_mv[li][0][n];
                 continue;
             }
             if (use) {
                 o.cand[pu * k.max_cand + off]                 = pack_cand((unsigned)li, 0, 0, li == 0 ? 0 : 24, li == 1 ? 1 : 24);
-                o.mv[pu * k.max_refs + (li ? k.max_l0 : 0)] = s.best_mv[li][0][n];
+                o.mv[pu * k.max_refs + (li ? k.max_l0 : 0)] = t.best_mv[li][0][n];
             }
             off++;
         }
@@ -726,19 +830,19 @@ SVTME_HD void cand_one_pu(const MeParams &p, SbState &s, const SbOut &o, unsigne
         for (uint32_t ri = 0; ri < nr[li]; ri++) {
             blk[li][ri] = s.do_ref[li][ri];
             if (!blk[li][ri]) continue;
-            if (s.best_sad[li][ri][n] < best) best = s.best_sad[li][ri][n];
+            if (t.best_sad[li][ri][n] < best) best = t.best_sad[li][ri][n];
         }
-    s.me_distortion[pu] = best;
+    t.me_distortion[pu] = best;
     for (uint32_t li = 0; li < num_lists && (use || off == 0); ++li)
         for (uint32_t ri = 0; ri < nr[li] && (use || off == 0); ++ri) {
             if (!blk[li][ri]) continue;
             if (prune_th > 0) {
-                const uint32_t d = (s.best_sad[li][ri][n] - best) * 100;  // u32 (:2744-2748)
+                const uint32_t d = (t.best_sad[li][ri][n] - best) * 100;  // u32 (:2744-2748)
                 if (d > (best * prune_th)) { blk[li][ri] = 0; continue; }
             }
             if (use) {
                 o.cand[pu * k.max_cand + off] = pack_cand(li, ri, ri, li == 0 ? 0 : 24, li == 1 ? 1 : 24);
-                o.mv[pu * k.max_refs + (li ? k.max_l0 : 0) + ri] = s.best_mv[li][ri][n];
+                o.mv[pu * k.max_refs + (li ? k.max_l0 : 0) + ri] = t.best_mv[li][ri][n];
             }
             off++;
         }
@@ -759,15 +863,16 @@ SVTME_HD void cand_one_pu(const MeParams &p, SbState &s, const SbOut &o, unsigne
 
 // ---- compute_distortion (:2964-3007); leader only ----
 SVTME_HD void compute_distortion(const MeParams &p, const SbState &s, uint32_t sums[4]) {
+    const SbState &t = *s.home;
     const uint32_t i = s.b64_index;
-    uint32_t d64 = s.me_distortion[0], d32 = 0, d16 = 0, d8 = 0;
-    for (int j = 0; j < 4; j++) d32 += s.me_distortion[1 + j];
-    for (int j = 0; j < 16; j++) d16 += s.me_distortion[5 + j];
-    for (int j = 0; j < 64; j++) d8 += s.me_distortion[21 + j];
+    uint32_t d64 = t.me_distortion[0], d32 = 0, d16 = 0, d8 = 0;
+    for (int j = 0; j < 4; j++) d32 += t.me_distortion[1 + j];
+    for (int j = 0; j < 16; j++) d16 += t.me_distortion[5 + j];
+    for (int j = 0; j < 64; j++) d8 += t.me_distortion[21 + j];
     const uint64_t mean = d8 / 64;
     uint64_t       ssq  = 0;
     for (int j = 0; j < 64; j++) {
-        const int64_t diff = (int64_t)s.me_distortion[21 + j] - (int64_t)mean;
+        const int64_t diff = (int64_t)t.me_distortion[21 + j] - (int64_t)mean;
         ssq += (uint64_t)(diff * diff);
     }
     p.out.me_8x8_cost_variance[i] = (uint32_t)(ssq / 64);
@@ -785,6 +890,7 @@ SVTME_HD void compute_distortion(const MeParams &p, const SbState &s, uint32_t s
 // tier-zero-ordered p_sb_best_mv, exactly as the reference does. ----
 SVTME_HD void gm_detection(const MeParams &p, const SbState &s, const SbOut &o, uint32_t sums[4]) {
     const SvtMeKnobs &k = p.k;
+    const SbState    &t = *s.home;
     uint32_t stationary = 0, tot = 0;
     uint8_t  cnt[kMaxLists][kMaxRefs][2][2];
     for (int l = 0; l < kMaxLists; l++)
@@ -818,7 +924,7 @@ SVTME_HD void gm_detection(const MeParams &p, const SbState &s, const SbOut &o, 
             const uint16_t dist = (uint16_t)SVTME_ABS(d16);
             active_th           = k.gm_use_distance_based_active_th ? SVTME_MAX(dist * 16, 32) : 32;
         }
-        const uint32_t mv = s.best_mv[li][ri][n];
+        const uint32_t mv = t.best_mv[li][ri][n];
         const int mx = (int)(int16_t)(mv & 0xFFFF) * 4, my = (int)(int16_t)(mv >> 16) * 4;
         if (mx < -active_th) cnt[li][ri][0][0]++; else if (mx > active_th) cnt[li][ri][0][1]++;
         if (my < -active_th) cnt[li][ri][1][0]++; else if (my > active_th) cnt[li][ri][1][1]++;
@@ -867,7 +973,11 @@ SVTME_HDX int build_program(const SvtMeKnobs &k, Step *st) {
         const bool dep = (k.enable_me_sr_adjustment == 2) && !k.me_early_exit_th;
         for (int pass = 0; pass < (dep ? 2 : 1); pass++) {
             const uint8_t a = (uint8_t)(dep ? pass : 2);
-            ctl(C_IS_A, a); eng(STEP_NXM); ctl(C_IS_B, a); eng(STEP_FP); ctl(C_IS_C, a); eng(STEP_FP);
+            ctl(C_IS_A, a);
+            if (!k.me_early_exit_th && k.is_ref) eng(STEP_NXM);  // check_00_center's SADs: is_a queues them only then
+            ctl(C_IS_B, a);
+            if (k.me_8x8_var_enabled) eng(STEP_FP);  // the 1x1 probe of the 8x8-variance test
+            ctl(C_IS_C, a); eng(STEP_FP);
         }
     }
     if (k.enable_hme_flag && k.enable_me_hme_ref_pruning && k.me_type != SVTME_ME_MCTF) ctl(C_PRUNE, 0);
@@ -938,6 +1048,7 @@ SVTME_HD void sb_results(B &be, const MeParams &p, SbState &s, uint32_t b64_inde
 template <class B>
 SVTME_HD void sb_finish(B &be, const MeParams &p, SbState &s, uint32_t b64_index) {
     const SvtMeKnobs &k = p.k;
+    const SbState    &t = *s.home;
     const uint8_t *nr     = k.num_of_ref_pic_to_search;
     if (k.me_type == SVTME_ME_MCTF) {
         // no candidates, distortions or GM for the temporal filter (:3126); it reads the best MVs / SADs below
@@ -955,13 +1066,13 @@ SVTME_HD void sb_finish(B &be, const MeParams &p, SbState &s, uint32_t b64_index
     }
     // optional MeContext state for parity checks
     if (p.out.sb_best_sad)
-        for (uint32_t i = be.tid(); i < kMaxLists * kMaxRefs * kPus; i += be.nthreads()) p.out.sb_best_sad[(size_t)b64_index * 680 + i] = (&s.best_sad[0][0][0])[i];
+        for (uint32_t i = be.tid(); i < kMaxLists * kMaxRefs * kPus; i += be.nthreads()) p.out.sb_best_sad[(size_t)b64_index * 680 + i] = (&t.best_sad[0][0][0])[i];
     if (p.out.sb_best_mv)
-        for (uint32_t i = be.tid(); i < kMaxLists * kMaxRefs * kPus; i += be.nthreads()) p.out.sb_best_mv[(size_t)b64_index * 680 + i] = (&s.best_mv[0][0][0])[i];
+        for (uint32_t i = be.tid(); i < kMaxLists * kMaxRefs * kPus; i += be.nthreads()) p.out.sb_best_mv[(size_t)b64_index * 680 + i] = (&t.best_mv[0][0][0])[i];
     if (p.out.tf_best_sad)
-        for (uint32_t i = be.tid(); i < kPus; i += be.nthreads()) p.out.tf_best_sad[(size_t)b64_index * kPus + i] = s.best_sad[0][0][i];
+        for (uint32_t i = be.tid(); i < kPus; i += be.nthreads()) p.out.tf_best_sad[(size_t)b64_index * kPus + i] = t.best_sad[0][0][i];
     if (p.out.tf_best_mv)
-        for (uint32_t i = be.tid(); i < kPus; i += be.nthreads()) p.out.tf_best_mv[(size_t)b64_index * kPus + i] = s.best_mv[0][0][i];
+        for (uint32_t i = be.tid(); i < kPus; i += be.nthreads()) p.out.tf_best_mv[(size_t)b64_index * kPus + i] = t.best_mv[0][0][i];
     if (be.leader()) {
         for (int li = 0; li < kMaxLists; li++)
             for (int ri = 0; ri < kMaxRefs; ri++) {
@@ -982,9 +1093,7 @@ SVTME_HD void me_sb(B &be, const MeParams &p, SbState &s, uint32_t b64_index) {
     for (int i = 0; i < p.n_steps; i++) {
         const Step st = p.prog[i];
         switch (st.kind) {
-        case STEP_CTL:
-            if (be.leader()) ctl_step(p, s, st.op, st.arg);
-            break;
+        case STEP_CTL: ctl_step(p, s, st.op, st.arg); break;  // a warp on the device, 32 sequential lanes on the host
         case STEP_NXM: be.run_nxm(s); break;
         case STEP_SAD: be.run_sad(s); break;
         default: be.run_fullpel(s); break;

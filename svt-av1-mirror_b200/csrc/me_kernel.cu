@@ -1,7 +1,5 @@
 // me_kernel.cu -- device kernels of libsvtme_cuda.so (sm_100a) and their launch wrappers.
 //
-//   me_picture_kernel      persistent CTAs, one 64x64 block at a time from a work queue: the whole of
-//                          svt_aom_motion_estimation_b64 (motion_estimation.c:3076-3153) for a picture
 //   pad_plane_kernel       svt_aom_generate_padding (pic_operators.c:338) on the full-resolution plane
 //   decimate_kernel        svt_aom_downsample_filtering_input_picture (pic_analysis_process.c:1945-2002):
 //                          quarter + sixteenth planes and their padding in one pass over the full plane
@@ -26,22 +24,6 @@ __device__ __forceinline__ CudaBackend make_backend(const MeParams *p, unsigned 
     be.sh  = &cs->eng;
     be.win = smem + ((sizeof(CtaShared) + 15) & ~size_t(15));
     return be;
-}
-
-__global__ void __launch_bounds__(kThreads, SVTME_MIN_CTAS) me_picture_kernel(const __grid_constant__ MeParams p) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    CtaShared  *cs = reinterpret_cast<CtaShared *>(smem);
-    CudaBackend be = make_backend(&p, smem);
-    const uint32_t n_sb = p.wb * p.hb;
-    for (;;) {
-        if (threadIdx.x == 0) cs->eng.next_sb = atomicAdd(p.work_counter, 1u);
-        __syncthreads();
-        const uint32_t sb = cs->eng.next_sb;
-        if (sb >= n_sb) break;
-        if (threadIdx.x == 0) cs->eng.px = 0;
-        me_sb(be, p, cs->sb, sb);
-        if (threadIdx.x == 0 && p.px_counter) atomicAdd(p.px_counter, cs->eng.px);
-    }
 }
 
 // ---- planes ----
@@ -209,31 +191,12 @@ cudaError_t launch_sad_peak(uint32_t *d_out, int grid, int iters, cudaStream_t s
 }
 
 // ---- launch wrappers (host) ----
-static cudaError_t ensure_attrs() {
-    static cudaError_t st = [] {
-        cudaError_t e = cudaFuncSetAttribute(me_picture_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(rtcd_sad_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(rtcd_nxm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(rtcd_fullpel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
-        return e;
-    }();
-    return st;
-}
-
-size_t me_smem_bytes() { return kSmemBytes; }
-
-int me_max_ctas_per_sm() {
-    if (ensure_attrs() != cudaSuccess) return 0;
-    int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, me_picture_kernel, kThreads, kSmemBytes) != cudaSuccess) return 0;
-    return n;
-}
-
-cudaError_t launch_me_picture(const MeParams &p, int grid, cudaStream_t st) {
-    cudaError_t e = ensure_attrs();
-    if (e != cudaSuccess) return e;
-    me_picture_kernel<<<grid, kThreads, kSmemBytes, st>>>(p);
-    return cudaGetLastError();
+// the opt-in to more than 48 KB of dynamic shared memory is per device: svtme_init calls this with its device current
+cudaError_t rtcd_set_attributes() {
+    cudaError_t e = cudaFuncSetAttribute(rtcd_sad_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rtcd_nxm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rtcd_fullpel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+    return e;
 }
 
 cudaError_t launch_pad_plane(uint8_t *org, int stride, int w, int h, int pad, cudaStream_t st) {
@@ -263,21 +226,15 @@ cudaError_t launch_downsample_generic(const uint8_t *in, int in_stride, int w, i
 }
 
 cudaError_t launch_rtcd_sad_loop(const SadJob &job, uint32_t *d_out, cudaStream_t st) {
-    cudaError_t e = ensure_attrs();
-    if (e != cudaSuccess) return e;
     rtcd_sad_loop_kernel<<<1, kThreads, kSmemBytes, st>>>(job, d_out);
     return cudaGetLastError();
 }
 cudaError_t launch_rtcd_nxm(const NxmJob &job, uint32_t *d_out, cudaStream_t st) {
-    cudaError_t e = ensure_attrs();
-    if (e != cudaSuccess) return e;
     rtcd_nxm_kernel<<<1, kThreads, kSmemBytes, st>>>(job, d_out);
     return cudaGetLastError();
 }
 cudaError_t launch_rtcd_fullpel(const uint8_t *src, int src_stride, const FpJob &job, int sub_sad, uint32_t *d_best_sad,
                                 uint32_t *d_best_mv, cudaStream_t st) {
-    cudaError_t e = ensure_attrs();
-    if (e != cudaSuccess) return e;
     rtcd_fullpel_kernel<<<1, kThreads, kSmemBytes, st>>>(src, src_stride, job, sub_sad, d_best_sad, d_best_mv);
     return cudaGetLastError();
 }

@@ -4,9 +4,7 @@
 #include "me_types.cuh"
 
 namespace svtme {
-size_t      me_smem_bytes();
-int         me_max_ctas_per_sm();
-cudaError_t launch_me_picture(const MeParams &p, int grid, cudaStream_t st);
+cudaError_t rtcd_set_attributes();  // per device, with the device current
 cudaError_t launch_pad_plane(uint8_t *org, int stride, int w, int h, int pad, cudaStream_t st);
 cudaError_t launch_decimate(const DevPic &pic, int pad_q, int pad_s, int sixteenth_from_full, cudaStream_t st);
 cudaError_t launch_unpack16(const uint16_t *in, int in_stride, uint8_t *out, int out_stride, int w, int h, cudaStream_t st);
@@ -20,7 +18,8 @@ cudaError_t launch_sad_peak(uint32_t *d_out, int grid, int iters, cudaStream_t s
 }  // namespace svtme
 namespace svtme {
 // staged (picture-wide kernels) execution of the step program; p.states must hold staged_state_bytes(n_sb) bytes
-cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_launches);
+cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, cudaStream_t st, int *n_launches);
+cudaError_t staged_set_attributes();  // per device, with the device current
 size_t      staged_state_bytes(uint32_t n_sb);
 // dynamic-GOP detector HME level 0 (me_dg.cu): picture-level sums accumulated by the kernel (zero them first)
 struct DgSums {

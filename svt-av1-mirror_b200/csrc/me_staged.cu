@@ -1,15 +1,17 @@
 // me_staged.cu -- the picture-wide ("staged") execution of the per-SB step program.
 //
-// The v1 kernel (me_kernel.cu: one persistent CTA runs the whole program of a 64x64 block) is latency bound: a single
-// leader thread executes the scalar control steps while the rest of the CTA waits at barriers (ncu: 56 % of warp
-// time in barrier stalls, 7.5x more instructions than SADs).  Here every step of the program becomes ONE KERNEL OVER
-// THE WHOLE PICTURE:
-//     control steps : one thread per 64x64 block (all 2040 blocks of a 4K picture advance together)
-//     engine steps  : one CTA per block, one WARP per search job -- no block barriers inside a job, windows staged in
-//                     warp-private shared memory, minima reduced with warp shuffles
-// Block state (SbState, the SB-scoped part of the reference's MeContext) lives in HBM/L2 between kernels.  Kernel
-// launches of one picture are stream ordered; several pictures are in flight on different streams, so the small
-// control kernels of one picture overlap the engine kernels of another.
+// Every ENGINE step of the program (me_control.cuh: build_program) is ONE KERNEL OVER THE WHOLE PICTURE, one CTA of 128
+// threads per 64x64 block:
+//     pre-HME / HME level 0 (sixteenth plane)   st_sad16_kernel      CTA-wide TMA-staged windows, flat item list
+//     HME level 1 / 2 (quarter / full plane)     st_sad_rows_kernel   warp per 8x3 refinement window, lane = block row
+//     1x1 probe + full-pel scan                  st_fp_sub_kernel     CTA-wide windows, rounds dealt to the warps
+//     anything unusual (full SAD, picture edge)  st_sad_kernel        generic warp-per-job path
+// The control steps between two engines (fold the search results, prune references, derive the next search windows:
+// the scalar code of motion_estimation.c around its SAD loops) and the light svt_nxm_sad_kernel probes run in the TAIL
+// of the kernel in front of them, on the shared-memory copy of the block's control state that the kernel already holds;
+// the last kernel's tail also builds the results.  Block state (SbState) lives in HBM/L2 between kernels.  Kernel
+// launches of one picture are stream ordered (programmatic dependent launch); several pictures are in flight on
+// different streams.
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstdlib>
@@ -52,7 +54,6 @@ __device__ __forceinline__ void check_src(const MeParams &p, int lvl, int li, in
 constexpr int kStThreads  = 128;             // 4 warps per block CTA
 constexpr int kStWarps    = kStThreads / 32;
 constexpr int kSadWarpWin = 8 * 1024;        // HME window bytes per warp
-constexpr int kFpWarpWin  = 16 * 1024;       // full-pel window bytes per warp (64 block rows + candidates)
 
 // Programmatic dependent launch (default; SVTME_PDL=0 turns it off): every kernel of a picture's chain carries the
 // programmatic-stream-serialization attribute and waits here, first thing, until its predecessor's grid is complete and
@@ -64,7 +65,7 @@ constexpr int kFpWarpWin  = 16 * 1024;       // full-pel window bytes per warp (
 // Without the launch attribute the instruction is a no-op.
 #define PDL_ENTRY() asm volatile("griddepcontrol.wait;" ::: "memory")
 
-// cooperative helpers of a block CTA working on global state
+// cooperative helpers of a block CTA
 struct StBackend {
     __device__ __forceinline__ bool     leader() const { return threadIdx.x == 0; }
     __device__ __forceinline__ void     sync() const { __syncthreads(); }
@@ -72,63 +73,68 @@ struct StBackend {
     __device__ __forceinline__ uint32_t nthreads() const { return blockDim.x; }
 };
 
-__global__ void __launch_bounds__(kStThreads) st_init_kernel(const __grid_constant__ MeParams p) {
-    PDL_ENTRY();
-    StBackend be;
-    sb_init(be, p, p.states[blockIdx.x], blockIdx.x);
-}
-
-// control steps [first, first + count) of the program: one WARP per 64x64 block with a single active lane -- the code is
-// a long scalar dependency chain with block-dependent branches, so 32 blocks per warp would serialise their paths;
-// one block per warp keeps every chain independent (2040 warps in flight at 4K).  The chain is latency bound: the warp
-// first copies the CONTROL part of the block's state (kSbHeadBytes, everything but the best-SAD / best-MV tables) into
-// shared memory with all 32 lanes, lane 0 runs the steps on that copy (shared-memory latency instead of an L2 round
-// trip per field), and the warp writes it back.  The few reads of the result tables go through SbState::home.
+// ---- the block's control state on chip ----
+// Every kernel of a picture's chain works on a shared-memory copy of the CONTROL part of its block's state (kSbHeadBytes:
+// HME centres / SADs, pruning flags, the three job tables; everything but the best-SAD / best-MV tables, which stay in
+// HBM/L2 behind SbState::home).  The copy is requested first thing with 16-byte cp.async (it lands while the kernel fetches
+// its source block), the engine reads its jobs from it and leaves their results in it, and the control steps that follow
+// the engine in the program (fold the results, prune, make the next kernel's jobs) run on it in the kernel's TAIL --
+// one warp, lane = reference x quadrant (me_control.cuh) -- before it is written back.  There are no separate control
+// launches and no round trip of the state between an engine and its control code.
 constexpr int kSbHeadBytes = (int)offsetof(SbState, best_sad);
 static_assert(kSbHeadBytes % 16 == 0 && sizeof(SbState) % 16 == 0, "the control part is copied as 16-byte words");
-__global__ void __launch_bounds__(kStThreads) st_ctl_kernel(const __grid_constant__ MeParams p, int first, int count) {
-    PDL_ENTRY();
-    __shared__ __align__(16) unsigned char head[kStWarps][kSbHeadBytes];
-    const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t sb = blockIdx.x * kStWarps + warp;
-    if (sb >= p.wb * p.hb) return;
-    uint4       *g = reinterpret_cast<uint4 *>(&p.states[sb]);
-    uint4       *l = reinterpret_cast<uint4 *>(head[warp]);
-    constexpr int kN = kSbHeadBytes / 16;
-#pragma unroll
-    for (int i = 0; i < (kN + 31) / 32; i++)
-        if (lane + 32 * i < kN) l[lane + 32 * i] = g[lane + 32 * i];
-    __syncwarp();
-    if (lane == 0) {
-        SbState &s = *reinterpret_cast<SbState *>(head[warp]);
-        for (int i = first; i < first + count; i++) ctl_step(p, s, p.prog[i].op, p.prog[i].arg);
-    }
-    __syncwarp();
-#pragma unroll
-    for (int i = 0; i < (kN + 31) / 32; i++)
-        if (lane + 32 * i < kN) g[lane + 32 * i] = l[lane + 32 * i];
+constexpr int kHeadVecs = kSbHeadBytes / 16;
+
+__device__ __forceinline__ void head_load_async(unsigned char *head, const SbState *g) {
+    const uint32_t sb = (uint32_t)__cvta_generic_to_shared(head);
+    const uint4   *gp = reinterpret_cast<const uint4 *>(g);
+    for (int i = threadIdx.x; i < kHeadVecs; i += blockDim.x)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sb + 16u * (uint32_t)i), "l"(gp + i));
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void head_wait() {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+}
+// the job table has landed; true when any of its slots holds work (a block whose references all took an early exit has none)
+template <class F>
+__device__ __forceinline__ bool jobs_wait_any(int n, F used) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    return __syncthreads_or((int)threadIdx.x < n && used((int)threadIdx.x)) != 0;
+}
+__device__ __forceinline__ void head_store(const unsigned char *head, SbState *g) {
+    const uint4 *l = reinterpret_cast<const uint4 *>(head);
+    uint4       *gp = reinterpret_cast<uint4 *>(g);
+    for (int i = threadIdx.x; i < kHeadVecs; i += blockDim.x) gp[i] = l[i];
 }
 
-__global__ void __launch_bounds__(kStThreads) st_finish_kernel(const __grid_constant__ MeParams p) {
-    PDL_ENTRY();
-    StBackend be;
-    sb_finish(be, p, p.states[blockIdx.x], blockIdx.x);
-    if (threadIdx.x == 0 && p.px_counter) atomicAdd(p.px_counter, p.states[blockIdx.x].px);
+// The search engines only need their job table: it is fetched into shared memory with 16-byte cp.async while the kernel
+// loads its source block; results go back into the block's state in HBM/L2.
+template <class J, int N>
+__device__ __forceinline__ void jobs_load_async(J *dst, const J *src) {
+    static_assert(sizeof(J) * N % 16 == 0, "job tables are copied as 16-byte words");
+    const uint32_t sb = (uint32_t)__cvta_generic_to_shared(dst);
+    const uint4   *gp = reinterpret_cast<const uint4 *>(src);
+    for (int i = threadIdx.x; i < (int)(sizeof(J) * N / 16); i += kStThreads)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sb + 16u * (uint32_t)i), "l"(gp + i));
+    asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
 // ---- svt_nxm_sad_kernel jobs: one warp per job, straight from global memory (2 KB per operand) ----
-__global__ void __launch_bounds__(kStThreads) st_nxm_kernel(const __grid_constant__ MeParams p) {
-    PDL_ENTRY();
-    SbState  &s    = p.states[blockIdx.x];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n    = s.n_nxm;
+__device__ void nxm_engine(SbState &s) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    // the used slots of the table, dealt round-robin to the warps
+    const unsigned used = __ballot_sync(0xffffffffu, lane < kMaxNxmJobs && s.nxm_jobs[lane & (kMaxNxmJobs - 1)].rows > 0);
     if (threadIdx.x == 0) {
         unsigned long long px = 0;
-        for (int ji = 0; ji < n; ji++) px += (unsigned long long)s.nxm_jobs[ji].rows * s.nxm_jobs[ji].width;
-        if (px) atomicAdd(&s.px, px);
+        for (unsigned m = used; m; m &= m - 1) { const NxmJob &j = s.nxm_jobs[__ffs(m) - 1]; px += (unsigned long long)j.rows * j.width; }
+        if (px) s.px += px;  // the only writer at this point (barriers on both sides of the step)
     }
-    for (int ji = warp; ji < n; ji += kStWarps) {
-        NxmJob        &j   = s.nxm_jobs[ji];
+    int idx = 0;
+    for (unsigned m = used; m; m &= m - 1, idx++) {
+        if (idx % nwarps != warp) continue;
+        NxmJob        &j   = s.nxm_jobs[__ffs(m) - 1];
         const int      nw  = (j.width + 3) >> 2, rows = j.rows, width = j.width;
         const uint8_t *src = j.src, *ref = j.ref;
         const int      sst = j.src_stride, rst = j.ref_stride;
@@ -155,8 +161,8 @@ __global__ void __launch_bounds__(kStThreads) st_nxm_kernel(const __grid_constan
                 const uint32_t *ra = reinterpret_cast<const uint32_t *>(rp - ((uintptr_t)rp & 3));
                 const uint32_t  lo = ra[0], hi = (((uintptr_t)rp & 3) ? ra[1] : 0u);
                 uint32_t        b  = __funnelshift_r(lo, hi, 8 * (int)((uintptr_t)rp & 3));
-                const uint32_t m = (c == nw - 1) ? tail : 0xffffffffu;
-                acc = sad4(a & m, b & m, acc);
+                const uint32_t m2 = (c == nw - 1) ? tail : 0xffffffffu;
+                acc = sad4(a & m2, b & m2, acc);
             }
         } else {
             for (int i = lane; i < rows * nw; i += 32) {
@@ -171,6 +177,58 @@ __global__ void __launch_bounds__(kStThreads) st_nxm_kernel(const __grid_constan
         for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
         if (lane == 0) j.sad = acc;
     }
+}
+
+// The tail of a kernel: steps [first, first + count) of the program -- control steps (warp 0) and the light
+// svt_nxm_sad_kernel probes (all warps) -- then, in the picture's last kernel, the results (sb_finish), and the state goes
+// back to HBM/L2.  Called by every thread of the CTA after a barrier; one copy of this code serves all kernels.
+__device__ __forceinline__ void run_tail(const MeParams &p, unsigned char *head, int first, int count, int finish) {
+    SbState &s = *reinterpret_cast<SbState *>(head);
+    for (int i = first; i < first + count; i++) {
+        const Step st = p.prog[i];
+        if (st.kind == STEP_CTL) {
+            if (threadIdx.x < 32) ctl_step(p, s, st.op, st.arg);
+        } else {
+            nxm_engine(s);
+        }
+        __syncthreads();
+    }
+    if (finish) {
+        StBackend be;
+        sb_finish(be, p, s, blockIdx.x);
+        if (threadIdx.x == 0 && p.px_counter) atomicAdd(p.px_counter, s.px);
+    }
+    head_store(head, s.home);
+}
+
+// The steps between two search engines (and the results behind the last one): a light kernel, ONE WARP per block --
+// 32 threads, ~2 K registers and 4.7 KB of shared memory per CTA, so that it slips in beside the six resident CTAs of
+// another picture's search engine instead of displacing one (a 128-thread version cost 5 % of the picture rate)
+constexpr int kLightThreads = 32;
+__global__ void __launch_bounds__(kLightThreads) st_light_kernel(const __grid_constant__ MeParams p, int first, int count, int finish) {
+    PDL_ENTRY();
+    __shared__ __align__(16) unsigned char head[kSbHeadBytes];
+    head_load_async(head, &p.states[blockIdx.x]);
+    head_wait();
+    run_tail(p, head, first, count, finish);
+}
+
+// First kernel of a picture: init_me_hme_data for every block, then the steps in front of the first search engine
+__global__ void __launch_bounds__(kStThreads) st_init_kernel(const __grid_constant__ MeParams p, int count, int finish) {
+    PDL_ENTRY();
+    __shared__ __align__(16) unsigned char head[kSbHeadBytes];
+    SbState *home = &p.states[blockIdx.x];
+    for (int i = threadIdx.x; i < kHeadVecs; i += blockDim.x) reinterpret_cast<uint4 *>(head)[i] = make_uint4(0u, 0u, 0u, 0u);
+    // the result tables: unsearched references report MAX_SAD_VALUE (convention of include/svtme_cuda.h), p_sb_best_mv = 0
+    for (int i = threadIdx.x; i < kMaxLists * kMaxRefs * kPus; i += blockDim.x) {
+        (&home->best_sad[0][0][0])[i] = SVTME_MAX_SAD_VALUE;
+        (&home->best_mv[0][0][0])[i]  = 0u;
+    }
+    for (int i = threadIdx.x; i < kPus; i += blockDim.x) home->me_distortion[i] = 0u;
+    __syncthreads();
+    if (threadIdx.x == 0) sb_init_head(p, *reinterpret_cast<SbState *>(head), home, blockIdx.x);
+    __syncthreads();
+    run_tail(p, head, 0, count, finish);
 }
 
 // ---- svt_sad_loop_kernel jobs (pre-HME, HME level 0/1/2): one warp per job ----
@@ -596,19 +654,8 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad_rows_kernel(const __grid
     __shared__ __align__(16) uint32_t      win[kStWarps][C::kWinW];
     __shared__ __align__(16) SadJob        jobs[kMaxSadJobs];
     SbState  &s = p.states[blockIdx.x];
-    {
-        // the whole job table is fetched together with the job count (one memory round trip instead of two)
-        constexpr int kWords = kMaxSadJobs * (int)sizeof(SadJob) / 8;
-        static_assert(kWords <= 2 * kStThreads, "two 64-bit words per thread");
-        const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.sad_jobs[0]);
-        unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
-        const int                 i0 = threadIdx.x, i1 = threadIdx.x + kStThreads;
-        const unsigned long long  v0 = src[i0], v1 = i1 < kWords ? src[i1] : 0ull;
-        if (s.n_sad == 0) return;
-        dst[i0] = v0;
-        if (i1 < kWords) dst[i1] = v1;
-    }
-    const int n = s.n_sad;
+    jobs_load_async<SadJob, kMaxSadJobs>(jobs, s.sad_jobs);
+    constexpr int n = kMaxSadJobs;  // fixed slots, unused ones have empty windows
     // block geometry as in make_sad_job (me_control.cuh)
     const DevPlane &cp = p.cur.lvl[lvl];
     const uint32_t  aw = (uint32_t)((p.cur.lvl[0].width + 7) & ~7), ah = (uint32_t)((p.cur.lvl[0].height + 7) & ~7);
@@ -622,7 +669,7 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad_rows_kernel(const __grid
             blk[r * kBlkPitch + c] = (r < rows && c < nw_eff) ? __ldg(reinterpret_cast<const uint32_t *>(b0 + (int64_t)(2 * r) * cp.stride) + c) : 0u;
         }
     }
-    __syncthreads();
+    if (!jobs_wait_any(n, [&](int i) { return jobs[i].sa_w > 0 && jobs[i].sa_h > 0; })) return;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint32_t  sreg[NW];
 #pragma unroll
@@ -644,14 +691,9 @@ __global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constan
     __shared__ __align__(16) uint32_t blk[64 * 16];
     __shared__ __align__(16) uint8_t  win[kStWarps][kSadWarpWin];
     __shared__ __align__(16) SadJob   jobs[kMaxSadJobs];
-    static_assert(sizeof(SadJob) % 8 == 0, "SadJob is copied as 64-bit words");
     SbState  &s = p.states[blockIdx.x];
-    const int n = s.n_sad;
-    {
-        const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.sad_jobs[0]);
-        unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
-        for (int i = threadIdx.x; i < (int)(kMaxSadJobs * sizeof(SadJob) / 8); i += blockDim.x) dst[i] = src[i];
-    }
+    jobs_load_async<SadJob, kMaxSadJobs>(jobs, s.sad_jobs);
+    constexpr int n = kMaxSadJobs;  // fixed slots, unused ones have empty windows
     // block geometry as in make_sad_job (me_control.cuh)
     const DevPlane &cp   = p.cur.lvl[lvl];
     const bool      full = p.k.hme_search_method == 1;
@@ -675,8 +717,7 @@ __global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constan
             blk[r * 16 + c] = a;
         }
     }
-    if (n == 0) return;
-    __syncthreads();
+    if (!jobs_wait_any(n, [&](int i) { return jobs[i].sa_w > 0 && jobs[i].sa_h > 0; })) return;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     unsigned long long px = 0;
     for (int ji = warp; ji < n; ji += kStWarps) {
@@ -744,7 +785,7 @@ SVTME_D void tma_load_2d(uint32_t dst, const void *tmap, int x, int y, uint32_t 
                  ::"r"(dst), "l"(tmap), "r"(x), "r"(y), "r"(mbar) : "memory");
 }
 
-__global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_constant__ MeParams p) {
+__global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_constant__ MeParams p, const __grid_constant__ S16Maps maps) {
     PDL_ENTRY();
     extern __shared__ __align__(128) uint32_t s16_win[];  // kS16BufWords
     __shared__ __align__(16) SadJob        jobs[kMaxSadJobs];
@@ -756,22 +797,14 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
     const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&mbar_store);
     PH_DECL
     SbState  &s = p.states[blockIdx.x];
+    jobs_load_async<SadJob, kMaxSadJobs>(jobs, s.sad_jobs);
     {
-        // the whole job table is fetched together with the job count (one memory round trip instead of two)
-        constexpr int kWords = kMaxSadJobs * (int)sizeof(SadJob) / 8;
-        static_assert(kWords <= 2 * kStThreads, "two 64-bit words per thread");
-        const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.sad_jobs[0]);
-        unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
-        const int                 i0 = threadIdx.x, i1 = threadIdx.x + kStThreads;
-        const unsigned long long  v0 = src[i0], v1 = i1 < kWords ? src[i1] : 0ull;
-        if (s.n_sad == 0) return;
-        dst[i0] = v0;
-        if (i1 < kWords) dst[i1] = v1;
         if (threadIdx.x < kMaxSadJobs) job_key[threadIdx.x] = ~0ull;
         if (threadIdx.x < kS16MaxSub) sub_key[threadIdx.x] = ~0u;
         if (threadIdx.x == 0) mbar_init(mbar, 1);
     }
-    const int n = s.n_sad;
+    constexpr int n = kMaxSadJobs;  // fixed slots, unused ones have empty windows
+    static_assert(kMaxSadJobs == 32, "the decomposition below is lane = job");
     // block geometry as in make_sad_job (me_control.cuh)
     const DevPlane &cp = p.cur.lvl[2];
     const uint32_t  aw = (uint32_t)((p.cur.lvl[0].width + 7) & ~7), ah = (uint32_t)((p.cur.lvl[0].height + 7) & ~7);
@@ -788,7 +821,7 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
             sreg[r][0] = v.x; sreg[r][1] = v.y; sreg[r][2] = v.z; sreg[r][3] = v.w;
         }
     }
-    __syncthreads();
+    if (!jobs_wait_any(n, [&](int i) { return jobs[i].sa_w > 0 && jobs[i].sa_h > 0; })) return;
     PH(1, 0)  // job fetch
     // ---- decomposition by warp 0: lane = job.  Sub-windows = (column tile of <= 128 candidates) x (row strip) ----
     if (warp == 0) {
@@ -945,7 +978,7 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
         for (int si = s_lo + warp; si < s_hi; si += kStWarps) {
             const S16Sub  &u = subs[si];
             const SadJob  &j = jobs[u.job];
-            const uint8_t *tm = static_cast<const uint8_t *>(p.tmap16[j.li][j.ri]) + u.cls * kTmapBytes;
+            const unsigned char *tm = maps.m[j.li * kMaxRefs + j.ri][u.cls];
             const uint32_t box_bytes = 4u * (uint32_t)u.brows * (uint32_t)u.P, dst0 = sbase + 4u * (uint32_t)u.off;
             if (lane < u.nbox) tma_load_2d(dst0 + (uint32_t)lane * box_bytes, tm, u.tx, u.ty + u.brows * lane, mbar);  // <= 4 boxes
         }
@@ -1037,224 +1070,6 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
     PH(1, 6)  // results to the block state
 }
 
-// ---- open_loop_me_fullpel_search_sblock jobs: one warp per unit (a strip of candidate rows of one job) ----
-struct FpUnit {
-    int16_t job, x0, y0, nx, ny;
-};
-constexpr int kFpTileNx = 64;
-
-template <bool SUB>
-__global__ void __launch_bounds__(kStThreads) st_fp_kernel(const __grid_constant__ MeParams p) {
-    PDL_ENTRY();
-    __shared__ __align__(16) uint32_t src64[64 * 16];
-    extern __shared__ __align__(16) uint8_t win_dyn[];  // kStWarps x kFpWarpWin
-    __shared__ unsigned long long     fp_key[kMaxFpJobs][kPus];
-    __shared__ __align__(16) FpJob    jobs[kMaxFpJobs];
-    __shared__ int                    u_base[kMaxFpJobs + 1], u_strips[kMaxFpJobs], u_ny[kMaxFpJobs];
-    static_assert(sizeof(FpJob) % 8 == 0, "FpJob is copied as 64-bit words");
-    constexpr int RSTEP = SUB ? 2 : 1;
-    SbState  &s = p.states[blockIdx.x];
-    const int n = s.n_fp;
-    if (n == 0) return;
-    {
-        const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.fp_jobs[0]);
-        unsigned long long       *dst = reinterpret_cast<unsigned long long *>(&jobs[0]);
-        for (int i = threadIdx.x; i < (int)(kMaxFpJobs * sizeof(FpJob) / 8); i += blockDim.x) dst[i] = src[i];
-        // the 64x64 source block: its address follows from the block index (sb_init)
-        const DevPlane &f   = p.cur.lvl[0];
-        const uint8_t  *sp0 = f.org + (int64_t)((blockIdx.x / p.wb) * 64) * f.stride + (blockIdx.x % p.wb) * 64;
-        for (int i = threadIdx.x; i < 64 * 4; i += blockDim.x) {
-            const int r = i >> 2, v = i & 3;
-            *reinterpret_cast<uint4 *>(&src64[r * 16 + 4 * v]) = __ldg(reinterpret_cast<const uint4 *>(sp0 + (int64_t)r * f.stride) + v);
-        }
-    }
-    for (int i = threadIdx.x; i < n * kPus; i += blockDim.x) (&fp_key[0][0])[i] = ~0ull;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        // units = (job, 64-candidate-wide column, strip of candidate rows): a strip's window (ny + 63 rows) fits the
-        // warp buffer and holds <= 512 candidates, so that the warps of the CTA share a big job
-        int                nu = 0;
-        unsigned long long px = 0;
-        for (int ji = 0; ji < n; ji++) {
-            const FpJob &j = jobs[ji];
-            u_base[ji] = nu; u_strips[ji] = 0; u_ny[ji] = 1;
-            if (j.w <= 0 || j.h <= 0) continue;
-            px += (unsigned long long)j.w * j.h * (SUB ? 64 * 32 : 64 * 64);
-            const int      nx    = min((int)j.w, kFpTileNx);
-            const uint32_t pitch = ((15 + nx + 63 + 8 + 15) & ~15u) + 16;  // upper bound of the pitch used below
-            const int      fit   = max(1, kFpWarpWin / (int)pitch - 63);
-            u_ny[ji]     = max(1, min(fit, 512 / nx));
-            u_strips[ji] = (j.h + u_ny[ji] - 1) / u_ny[ji];
-            nu += u_strips[ji] * ((j.w + kFpTileNx - 1) / kFpTileNx);
-        }
-        u_base[n] = nu;
-        if (px) atomicAdd(&s.px, px);
-    }
-    __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int b = lane & 15, half = lane >> 4;
-    const int bx = ((b >> 2) & 1) * 2 + (b & 1), by = (b >> 3) * 2 + ((b >> 1) & 1);
-    uint8_t  *w8 = win_dyn + warp * kFpWarpWin;
-    const int n_units = u_base[n];
-
-    for (int pass = 0; pass < (SUB ? 1 : 2); pass++) {
-        uint32_t sreg[8][4];
-#pragma unroll
-        for (int r = 0; r < 8; r++)
-#pragma unroll
-            for (int c = 0; c < 4; c++) sreg[r][c] = src64[(16 * by + (SUB ? 2 * r : 8 * pass + r)) * 16 + 4 * bx + c];
-        for (int u = warp; u < n_units; u += kStWarps) {
-            int uj = 0;
-            while (uj + 1 < n && u >= u_base[uj + 1]) uj++;
-            const FpJob &j = jobs[uj];
-            FpUnit       un;
-            {
-                const int local = u - u_base[uj], xt = local / u_strips[uj], st = local - xt * u_strips[uj];
-                un.job = (int16_t)uj; un.x0 = (int16_t)(xt * kFpTileNx); un.y0 = (int16_t)(st * u_ny[uj]);
-                un.nx = (int16_t)min(j.w - un.x0, kFpTileNx); un.ny = (int16_t)min(j.h - un.y0, u_ny[uj]);
-            }
-            const uint8_t *ref = j.ref + (int64_t)un.y0 * j.ref_stride + un.x0;
-            const uint32_t mis = (uint32_t)((uintptr_t)ref & 15);
-            uint32_t       pitch = (mis + un.nx + 63 + 8 + 15) & ~15u;
-            if (((pitch >> 4) & 1) == 0) pitch += 16;
-            const uint32_t pitchw = pitch >> 2, nvec = pitch >> 4, total = nvec * (uint32_t)(un.ny + 63);
-            const uint8_t *row0 = ref - mis;
-            __syncwarp();
-            for (uint32_t i = lane; i < total; i += 32) {
-                const uint32_t r = i / nvec, v = i - r * nvec;
-                *reinterpret_cast<uint4 *>(w8 + r * pitch + (v << 4)) = __ldg(reinterpret_cast<const uint4 *>(row0 + (int64_t)r * j.ref_stride) + v);
-            }
-            __syncwarp();
-            const int ngroups = (int)(((mis & 3) + un.nx + 3) >> 2);
-            const int items = un.ny * ngroups, rounds = (items + 1) >> 1;
-            uint32_t           best8[4] = {~0u, ~0u, ~0u, ~0u}, best16 = ~0u;
-            unsigned long long best32 = ~0ull, best64 = ~0ull;
-            for (int it = 0; it < rounds; it++) {
-                const int  item   = 2 * it + half;
-                const bool active = item < items;
-                const int  yy = active ? item / ngroups : 0, g = active ? item - yy * ngroups : 0;
-                uint32_t   acc[4][4];
-#pragma unroll
-                for (int c = 0; c < 4; c++) acc[c][0] = acc[c][1] = acc[c][2] = acc[c][3] = 0;
-                if (active) {
-                    const uint32_t *rowp = reinterpret_cast<const uint32_t *>(w8) + (uint32_t)(yy + 16 * by + (SUB ? 0 : 8 * pass)) * pitchw +
-                        (mis >> 2) + g + 4 * bx;
-#pragma unroll
-                    for (int r = 0; r < 8; r++) {
-                        const uint32_t *rp = rowp + (uint32_t)(r * RSTEP) * pitchw;
-                        uint32_t        w[5];
-#pragma unroll
-                        for (int c = 0; c < 5; c++) w[c] = rp[c];
-#pragma unroll
-                        for (int c = 0; c < 4; c++) {
-                            const int      q  = SUB ? ((r >> 2) * 2 + (c >> 1)) : (c >> 1);
-                            const uint32_t sw = sreg[r][c];
-                            acc[0][q] = sad4(w[c], sw, acc[0][q]);
-                            acc[1][q] = sad4(fsr(w[c], w[c + 1], 1), sw, acc[1][q]);
-                            acc[2][q] = sad4(fsr(w[c], w[c + 1], 2), sw, acc[2][q]);
-                            acc[3][q] = sad4(fsr(w[c], w[c + 1], 3), sw, acc[3][q]);
-                        }
-                    }
-                }
-                const int xb = 4 * g - (int)(mis & 3);
-#pragma unroll
-                for (int c = 0; c < 4; c++) {
-                    const int      xx    = xb + c;
-                    const bool     valid = active && xx >= 0 && xx < un.nx;
-                    const uint32_t ord   = (uint32_t)yy * (uint32_t)un.nx + (uint32_t)xx;  // < 65536
-                    if (SUB) {
-                        uint32_t s16 = 0;
-#pragma unroll
-                        for (int q = 0; q < 4; q++) {
-                            if (valid) best8[q] = min(best8[q], (acc[c][q] << 16) | ord);
-                            s16 += acc[c][q];
-                        }
-                        if (valid) best16 = min(best16, (s16 << 16) | ord);
-                        uint32_t s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 1);
-                        s32 += __shfl_xor_sync(0xffffffffu, s32, 2);
-                        uint32_t s64 = s32 + __shfl_xor_sync(0xffffffffu, s32, 4);
-                        s64 += __shfl_xor_sync(0xffffffffu, s64, 8);
-                        if (valid) {
-                            best32 = min(best32, ((unsigned long long)s32 << 32) | ord);
-                            best64 = min(best64, ((unsigned long long)s64 << 32) | ord);
-                        }
-                    } else if (valid) {
-                        best8[0] = min(best8[0], (acc[c][0] << 16) | ord);
-                        best8[1] = min(best8[1], (acc[c][1] << 16) | ord);
-                    }
-                }
-            }
-            // fold this lane's minima of the unit into the job's keys: (SAD, raster index inside the job's window)
-            auto gk = [&](uint32_t sad, uint32_t ord) {
-                const uint32_t yy = ord / (uint32_t)un.nx, xx = ord - yy * (uint32_t)un.nx;
-                return ((unsigned long long)(SUB ? sad << 1 : sad) << 32) | (uint32_t)((un.y0 + yy) * j.w + un.x0 + xx);
-            };
-            if (SUB) {
-#pragma unroll
-                for (int q = 0; q < 4; q++)
-                    if (best8[q] != ~0u) atomicMin(&fp_key[un.job][21 + 4 * b + q], gk(best8[q] >> 16, best8[q] & 0xffff));
-                if (best16 != ~0u) atomicMin(&fp_key[un.job][5 + b], gk(best16 >> 16, best16 & 0xffff));
-                if ((b & 3) == 0 && best32 != ~0ull) atomicMin(&fp_key[un.job][1 + (b >> 2)], gk((uint32_t)(best32 >> 32), (uint32_t)best32));
-                if (b == 0 && best64 != ~0ull) atomicMin(&fp_key[un.job][0], gk((uint32_t)(best64 >> 32), (uint32_t)best64));
-            } else {
-#pragma unroll
-                for (int q = 0; q < 2; q++)
-                    if (best8[q] != ~0u) atomicMin(&fp_key[un.job][21 + 4 * b + 2 * pass + q], gk(best8[q] >> 16, best8[q] & 0xffff));
-            }
-        }
-    }
-    if (!SUB) {
-        // FULL SAD (off the open-loop hot path): 16x16 and larger PUs straight from global memory, lane = 16x16 block
-        for (int ji = 0; ji < n; ji++) {
-            const FpJob   &j     = jobs[ji];
-            const uint32_t ncand = (uint32_t)max(0, (int)j.w) * (uint32_t)max(0, (int)j.h);
-            const uint32_t nsub = 2 * kStWarps, subi = warp * 2 + half, rounds = (ncand + nsub - 1) / nsub;
-            unsigned long long b16 = ~0ull, b32 = ~0ull, b64 = ~0ull;
-            for (uint32_t it = 0; it < rounds; it++) {
-                const uint32_t i = it * nsub + subi;
-                const bool     active = i < ncand;
-                uint32_t       s16 = 0;
-                if (active) {
-                    const uint32_t y = i / (uint32_t)j.w, x = i - y * (uint32_t)j.w;
-                    const uint8_t *rp = j.ref + (int64_t)(y + 16 * by) * j.ref_stride + x + 16 * bx;
-                    for (int r = 0; r < 16; r++)
-                        for (int c = 0; c < 4; c++) {
-                            uint32_t v = 0;
-                            for (int q = 0; q < 4; q++) v |= (uint32_t)rp[(int64_t)r * j.ref_stride + 4 * c + q] << (8 * q);
-                            s16 = sad4(v, src64[(16 * by + r) * 16 + 4 * bx + c], s16);
-                        }
-                }
-                uint32_t s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 1);
-                s32 += __shfl_xor_sync(0xffffffffu, s32, 2);
-                uint32_t s64 = s32 + __shfl_xor_sync(0xffffffffu, s32, 4);
-                s64 += __shfl_xor_sync(0xffffffffu, s64, 8);
-                if (active) {
-                    b16 = min(b16, ((unsigned long long)s16 << 32) | i);
-                    b32 = min(b32, ((unsigned long long)s32 << 32) | i);
-                    b64 = min(b64, ((unsigned long long)s64 << 32) | i);
-                }
-            }
-            if (b16 != ~0ull) atomicMin(&fp_key[ji][5 + b], b16);
-            if ((b & 3) == 0 && b32 != ~0ull) atomicMin(&fp_key[ji][1 + (b >> 2)], b32);
-            if (b == 0 && b64 != ~0ull) atomicMin(&fp_key[ji][0], b64);
-        }
-    }
-    __syncthreads();
-    // fold the window minima into the running best of the reference (strict '<': earlier results win ties)
-    for (int i = threadIdx.x; i < n * kPus; i += blockDim.x) {
-        const int                ji = i / kPus, pu = i - ji * kPus;
-        const FpJob             &j  = jobs[ji];
-        const unsigned long long key = fp_key[ji][pu];
-        if (key == ~0ull) continue;
-        const uint32_t sad = (uint32_t)(key >> 32), ord = (uint32_t)key;
-        if (sad < s.best_sad[j.li][j.ri][pu]) {
-            const int32_t y = (int32_t)(ord / (uint32_t)j.w), x = (int32_t)(ord - (uint32_t)y * (uint32_t)j.w);
-            s.best_sad[j.li][j.ri][pu] = sad;
-            s.best_mv[j.li][j.ri][pu]  = ((uint32_t)(y + j.yo) << 16) | (uint16_t)(x + j.xo);
-        }
-    }
-}
-
 // ---- sub-sampled full-pel search (the open-loop hot path): CTA-wide windows, balanced rounds ----
 // All windows of the block's jobs are staged TOGETHER into shared memory with asynchronous 4-byte copies (one exposed
 // memory latency per CTA); the candidates of all windows then form one flat list of ROUNDS dealt to the 4 warps.
@@ -1289,20 +1104,13 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
     __shared__ int                    n_sub, cur_job, cur_xt, cur_st;
     PH_DECL
     __shared__ int                    b_lo[kFpMaxSub + 1], fast_nb;
-    SbState  &s = p.states[blockIdx.x];
+    SbState  &s = p.states[blockIdx.x], &tab = s;  // the block's state (HBM/L2): job table in, best-SAD / best-MV tables out
+    jobs_load_async<FpJob, kMaxFpJobs>(jobs, s.fp_jobs);
     {
-        // the job table is fetched together with the job count (one memory round trip instead of two)
-        constexpr int kWords = kMaxFpJobs * (int)sizeof(FpJob) / 8;
-        static_assert(kWords <= kStThreads, "one 64-bit word per thread");
-        const unsigned long long *src = reinterpret_cast<const unsigned long long *>(&s.fp_jobs[0]);
-        const unsigned long long  v = (int)threadIdx.x < kWords ? src[threadIdx.x] : 0ull;
-        if (s.n_fp == 0) return;
-        if ((int)threadIdx.x < kWords) reinterpret_cast<unsigned long long *>(&jobs[0])[threadIdx.x] = v;
         for (int i = threadIdx.x; i < kMaxFpJobs * kPus; i += blockDim.x) (&fp_key[0][0])[i] = ~0ull;
         if (threadIdx.x == 0) { cur_job = 0; cur_xt = 0; cur_st = 0; }
     }
-    const int n = s.n_fp;
-    __syncthreads();
+    constexpr int n = kMaxFpJobs;  // fixed slots, unused ones have empty windows
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int b = lane & 15, half = lane >> 4;
     const int bx = ((b >> 2) & 1) * 2 + (b & 1), by = (b >> 3) * 2 + ((b >> 1) & 1);
@@ -1317,13 +1125,14 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
         }
     }
     constexpr uint32_t kPxPerCand = FULL ? 64u * 64u : 64u * 32u;
+    if (!jobs_wait_any(n, [&](int i) { return jobs[i].w > 0 && jobs[i].h > 0; })) return;
     // the running best SADs this thread will compare against at the end: requested now, needed last
     constexpr int kFoldPer = (kMaxFpJobs * kPus + kStThreads - 1) / kStThreads;
     uint32_t      prev_best[kFoldPer];
 #pragma unroll
     for (int t = 0; t < kFoldPer; t++) {
         const int i = threadIdx.x + t * kStThreads, ji = i / kPus, pu = i - ji * kPus;
-        prev_best[t] = i < n * kPus ? s.best_sad[jobs[ji].li][jobs[ji].ri][pu] : 0u;
+        prev_best[t] = (i < n * kPus && jobs[ji].w > 0 && jobs[ji].h > 0) ? tab.best_sad[jobs[ji].li][jobs[ji].ri][pu] : 0u;
     }
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(fp_win);
     PH(0, 0)  // job fetch + source rows
@@ -1620,30 +1429,36 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
         const uint32_t sad = (uint32_t)(key >> 32), ord = (uint32_t)key;
         if (sad < prev_best[t]) {
             const int32_t y = (int32_t)(ord / (uint32_t)j.w), x = (int32_t)(ord - (uint32_t)y * (uint32_t)j.w);
-            s.best_sad[j.li][j.ri][pu] = sad;
-            s.best_mv[j.li][j.ri][pu]  = ((uint32_t)(y + j.yo) << 16) | (uint16_t)(x + j.xo);
+            tab.best_sad[j.li][j.ri][pu] = sad;
+            tab.best_mv[j.li][j.ri][pu]  = ((uint32_t)(y + j.yo) << 16) | (uint16_t)(x + j.xo);
         }
     }
     PH(0, 7)  // results to the block state
 }
 
 // ---- host: run the program of one picture as a stream-ordered sequence of picture-wide kernels ----
-cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_launches) {
-    static cudaError_t attr = [] {
-        cudaError_t e = cudaFuncSetAttribute(st_fp_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStWarps * kFpWarpWin);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStWarps * kFpWarpWin);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(st_sad16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kS16BufWords * 4);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_sub_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpBufWords * 4);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_sub_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpBufWords * 4);
-        return e;
-    }();
-    if (attr != cudaSuccess) return attr;
+// One kernel per ENGINE step (pre-HME / HME level 0 / 1 / 2 searches, the 1x1 probe, the full-pel scan) plus the first
+// one; the control and svt_nxm_sad_kernel steps between two engines run in the tail of the kernel in front of them, the
+// results (candidates, statistics) in the tail of the last kernel: 7 launches per picture at preset M6 where the first
+// version of this pipeline needed 21.
+cudaError_t staged_set_attributes() {  // per device: call with the device current (svtme_init)
+    cudaError_t e = cudaFuncSetAttribute(st_sad16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kS16BufWords * 4);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_sub_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpBufWords * 4);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_sub_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpBufWords * 4);
+    return e;
+}
+
+cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, cudaStream_t st, int *n_launches) {
     const int n_sb = (int)(p.wb * p.hb);
     int       nl   = 0;
-    // SVTME_TRACE=1: per-step device times of every picture on stderr (serialises the stream; diagnostics only)
+#ifdef SVTME_DIAG
+    // diagnostics build only: SVTME_TRACE=1 prints per-kernel device times of every picture on stderr (serialises the
+    // stream); SVTME_PDL=0 launches every kernel fully stream-ordered
     static const bool trace = getenv("SVTME_TRACE") != nullptr;
-    static const bool sad_old = getenv("SVTME_SAD_OLD") != nullptr;
-    static const bool fp_old = getenv("SVTME_FP_OLD") != nullptr;  // A/B switch of the full-pel kernel (diagnostics only)
+    static const bool pdl = !(getenv("SVTME_PDL") != nullptr && atoi(getenv("SVTME_PDL")) == 0) && !trace;
+#else
+    constexpr bool trace = false, pdl = true;
+#endif
     cudaEvent_t ev[kMaxSteps + 4];
     const char *nm[kMaxSteps + 4];
     int         ne = 0;
@@ -1652,53 +1467,50 @@ cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_
         cudaEventCreate(&ev[ne]); cudaEventRecord(ev[ne], st); nm[ne] = name; ne++;
     };
     mark("start");
-    // on by default; SVTME_PDL=0 launches every kernel fully stream-ordered (A/B: 0.438 -> 0.418 ms per picture alone,
-    // +5 % end to end)
-    static const bool pdl = !(getenv("SVTME_PDL") != nullptr && atoi(getenv("SVTME_PDL")) == 0) && !trace;
-    auto launch = [&](auto kern, int grid, size_t smem, auto... args) {
+    cudaError_t err = cudaSuccess;
+    int threads = kStThreads;
+    auto launch = [&](auto kern, size_t smem, auto... args) {
+        if (err != cudaSuccess) return;  // the chain stops at the first failed launch
         cudaLaunchConfig_t   cfg = {};
         cudaLaunchAttribute  at[1];
-        cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(kStThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+        cfg.gridDim = dim3((unsigned)n_sb); cfg.blockDim = dim3((unsigned)threads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
         cfg.attrs = at; cfg.numAttrs = 1;
-        cudaLaunchKernelEx(&cfg, kern, args...);
-    };
-    launch(st_init_kernel, n_sb, 0, p); nl++; mark("init");
-    for (int i = 0; i < p.n_steps;) {
-        if (p.prog[i].kind == STEP_CTL) {
-            int c = 1;
-            while (i + c < p.n_steps && p.prog[i + c].kind == STEP_CTL) c++;
-            launch(st_ctl_kernel, (n_sb + kStWarps - 1) / kStWarps, 0, p, i, c);
-            i += c; mark("ctl");
-        } else {
-            if (p.prog[i].kind == STEP_NXM) launch(st_nxm_kernel, n_sb, 0, p);
-            else if (p.prog[i].kind == STEP_SAD) {
-                const int lvl = (int)p.prog[i].arg;
-                if (lvl == 1 && p.k.hme_search_method == 0) launch(st_sad_rows_kernel<8, 16>, n_sb, 0, p, lvl);
-                else if (lvl == 0 && p.k.hme_search_method == 0) launch(st_sad_rows_kernel<16, 32>, n_sb, 0, p, lvl);
-                else if (lvl == 2 && p.k.hme_search_method == 0 && !sad_old) launch(st_sad16_kernel, n_sb, (size_t)kS16BufWords * 4, p);
-                else launch(st_sad_kernel, n_sb, 0, p, lvl);
-            }
-            else if (p.k.me_search_method == 0 && !fp_old) launch(st_fp_sub_kernel<false>, n_sb, (size_t)kFpBufWords * 4, p);
-            else if (!fp_old) launch(st_fp_sub_kernel<true>, n_sb, (size_t)kFpBufWords * 4, p);
-            else if (p.k.me_search_method == 0) launch(st_fp_kernel<true>, n_sb, (size_t)kStWarps * kFpWarpWin, p);
-            else launch(st_fp_kernel<false>, n_sb, (size_t)kStWarps * kFpWarpWin, p);
-            mark(p.prog[i].kind == STEP_NXM ? "nxm" : p.prog[i].kind == STEP_SAD ? "sad" : "fp");
-            i++;
-        }
+        err = cudaLaunchKernelEx(&cfg, kern, args...);
         nl++;
+    };
+    auto is_engine = [&](int i) { return p.prog[i].kind == STEP_SAD || p.prog[i].kind == STEP_FP; };
+    int i = 0;
+    while (i < p.n_steps && !is_engine(i)) i++;
+    launch(st_init_kernel, 0, p, i, i == p.n_steps ? 1 : 0); mark("init");
+    while (i < p.n_steps) {
+        int j = i + 1;
+        while (j < p.n_steps && !is_engine(j)) j++;
+        const int tf = i + 1, tc = j - i - 1, fin = j == p.n_steps ? 1 : 0;
+        if (p.prog[i].kind == STEP_SAD) {
+            const int lvl = (int)p.prog[i].arg;
+            if (lvl == 1 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<8, 16>, 0, p, lvl); mark("rows8"); }
+            else if (lvl == 0 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<16, 32>, 0, p, lvl); mark("rows16"); }
+            else if (lvl == 2 && p.k.hme_search_method == 0) { launch(st_sad16_kernel, (size_t)kS16BufWords * 4, p, maps); mark("sad16"); }
+            else { launch(st_sad_kernel, 0, p, lvl); mark("sadg"); }
+        } else {
+            if (p.k.me_search_method == 0) launch(st_fp_sub_kernel<false>, (size_t)kFpBufWords * 4, p);
+            else launch(st_fp_sub_kernel<true>, (size_t)kFpBufWords * 4, p);
+            mark("fp");
+        }
+        if (tc > 0 || fin) { threads = kLightThreads; launch(st_light_kernel, 0, p, tf, tc, fin); threads = kStThreads; mark("light"); }
+        i = j;
     }
-    launch(st_finish_kernel, n_sb, 0, p); nl++; mark("finish");
-    if (trace) {
+    if (trace && err == cudaSuccess) {
         cudaStreamSynchronize(st);
         float tot = 0.f;
         fprintf(stderr, "[svtme trace] tl=%d refs=%d+%d:", p.k.temporal_layer_index, p.k.num_of_ref_pic_to_search[0], p.k.num_of_ref_pic_to_search[1]);
-        for (int i = 1; i < ne; i++) {
+        for (int q = 1; q < ne; q++) {
             float ms = 0.f;
-            cudaEventElapsedTime(&ms, ev[i - 1], ev[i]);
+            cudaEventElapsedTime(&ms, ev[q - 1], ev[q]);
             tot += ms;
-            fprintf(stderr, " %s %.1f", nm[i], ms * 1e3f);
+            fprintf(stderr, " %s %.1f", nm[q], ms * 1e3f);
         }
         fprintf(stderr, " | total %.1f us\n", tot * 1e3f);
 #ifdef SVTME_PHASES
@@ -1707,19 +1519,19 @@ cudaError_t launch_me_picture_staged(const MeParams &p, cudaStream_t st, int *n_
             cudaMemcpyFromSymbol(ph, g_phase, sizeof(ph));
             for (int k = 0; k < 2; k++) {
                 unsigned long long sum = 0;
-                for (int i = 0; i < 12; i++) sum += ph[k][i];
+                for (int q = 0; q < 12; q++) sum += ph[k][q];
                 fprintf(stderr, "[svtme phases] %s:", k == 0 ? "fp_sub" : "sad16");
-                for (int i = 0; i < 12; i++) if (ph[k][i]) fprintf(stderr, " p%d %.1f%%", i, 100.0 * (double)ph[k][i] / (double)sum);
+                for (int q = 0; q < 12; q++) if (ph[k][q]) fprintf(stderr, " p%d %.1f%%", q, 100.0 * (double)ph[k][q] / (double)sum);
                 fprintf(stderr, " | %.1f kclk per CTA\n", (double)sum / 1e3 / (double)(n_sb * (k == 0 ? 2 : 2)));
             }
             memset(ph, 0, sizeof(ph));
             cudaMemcpyToSymbol(g_phase, ph, sizeof(ph));
         }
 #endif
-        for (int i = 0; i < ne; i++) cudaEventDestroy(ev[i]);
     }
+    for (int q = 0; q < ne; q++) cudaEventDestroy(ev[q]);
     if (n_launches) *n_launches = nl;
-    return cudaGetLastError();
+    return err != cudaSuccess ? err : cudaGetLastError();
 }
 
 size_t staged_state_bytes(uint32_t n_sb) { return (size_t)n_sb * sizeof(SbState); }

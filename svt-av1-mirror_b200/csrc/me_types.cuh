@@ -90,11 +90,17 @@ struct MeParams {
     uint32_t  *work_counter;  // persistent-CTA SB queue
     unsigned long long *px_counter;  // optional: algorithmic pixel-compares of the picture (roofline numerator)
     SbState   *states;        // staged pipeline: one SbState per 64x64 block in HBM/L2
-    // TMA descriptors of every reference picture's padded sixteenth plane: kS16Classes x kS16HClasses CUtensorMaps (128 bytes each)
-    // in device memory, box = kS16BoxBytes[class] x kS16BoxRows[height class] (st_sad16_kernel stages its search windows with them)
-    const void *tmap16[kMaxLists][kMaxRefs];
     int32_t    n_steps;
     Step       prog[kMaxSteps];
+};
+
+// TMA descriptors of every reference picture's padded sixteenth plane: kS16Classes x kS16HClasses CUtensorMaps (128 bytes
+// each), box = kS16BoxBytes[class] x kS16BoxRows[height class]; st_sad16_kernel stages its search windows with them.
+// Passed to that kernel BY VALUE as a __grid_constant__ parameter (15 KB of the 32 KB a launch may carry): descriptors
+// in parameter space need no proxy fence before the TMA unit fetches them, unlike descriptors read from global memory
+// (a fence.proxy.tensormap per CTA was measured at -8 % of the picture rate).
+struct alignas(64) S16Maps {
+    unsigned char m[kMaxLists * kMaxRefs][kS16Classes * kS16HClasses][kTmapBytes];
 };
 
 // ---- work descriptors produced by the per-SB control code and consumed by the search engines ----
@@ -146,7 +152,9 @@ constexpr int kMaxSadJobs = 32;
 constexpr int kMaxNxmJobs = 16;
 constexpr int kMaxFpJobs  = 8;
 
-// SB-scoped part of the reference's MeContext (me_context.h:366-509); lives in shared memory on the device.
+// SB-scoped part of the reference's MeContext (me_context.h:366-509).  The control part (everything up to `home`) is
+// worked on in shared memory by every kernel of the staged pipeline and kept in HBM/L2 between them; the result tables
+// behind it are reached through `home`.
 struct alignas(16) SbState {
     uint64_t lsad[3][kMaxLists][kMaxRefs][2][2];  // hme_level{0,1,2}_sad[l][r][w][h]
     uint64_t hme_sad[kMaxLists][kMaxRefs];
@@ -170,16 +178,19 @@ struct alignas(16) SbState {
     uint8_t  c00_done[kMaxLists][kMaxRefs];
     uint8_t  probe[kMaxLists][kMaxRefs];
     // job lists
-    SadJob   sad_jobs[kMaxSadJobs];
-    NxmJob   nxm_jobs[kMaxNxmJobs];
-    FpJob    fp_jobs[kMaxFpJobs];
+    alignas(16) SadJob sad_jobs[kMaxSadJobs];  // fetched by the engines with 16-byte copies
+    alignas(16) NxmJob nxm_jobs[kMaxNxmJobs];
+    alignas(16) FpJob  fp_jobs[kMaxFpJobs];
     int32_t  n_sad, n_nxm, n_fp;
     unsigned long long px;  // algorithmic pixel-compares of this SB so far (staged pipeline)
-    uint32_t l0_searched;  // references whose HME-L0 quadrants were searched in the current pass (bit li*4+ri)
+    uint8_t  l0_done[kMaxLists][kMaxRefs];  // references whose HME-L0 quadrants were searched in the current pass
+    uint32_t scratch[32];                    // lane-to-lane exchange of the control steps (me_control.cuh)
+    uint64_t scratch64[32];
     // Everything above is the CONTROL part: the staged pipeline's control kernel works on a shared-memory copy of it
     // (kSbHeadBytes) and reaches the search results below through `home`, the block's own state in HBM/L2.
     SbState *home;
-    uint32_t best_sad[kMaxLists][kMaxRefs][kPus], best_mv[kMaxLists][kMaxRefs][kPus];
+    alignas(16) uint32_t best_sad[kMaxLists][kMaxRefs][kPus];
+    uint32_t best_mv[kMaxLists][kMaxRefs][kPus];
     uint32_t me_distortion[kPus];
 };
 

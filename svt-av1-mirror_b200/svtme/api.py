@@ -136,7 +136,7 @@ class MeDevice:
                  pipeline=None):
         self.lib = load_library()
         if pipeline is None:
-            pipeline = int(os.environ.get("SVTME_PIPELINE", "0"))
+            pipeline = 0  # the staged pipeline is the only one that ships
         cfg = abi.DeviceCfg(device, max_width, max_height, max_pictures, max_inflight, sixteenth_from_full, pipeline)
         h = C.c_void_p()
         rc = self.lib.svtme_init(C.byref(cfg), C.byref(h))

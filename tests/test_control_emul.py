@@ -23,11 +23,16 @@ class Emul(refbind._Binding):
                                           C.POINTER(abi.PictureResults), C.c_int]
 
 
-@pytest.fixture(scope="module")
-def emul():
+@pytest.fixture(scope="module", params=["lanes-forward", "lanes-reverse"])
+def emul(request):
+    """The control steps are written for a warp (lane = reference x quadrant); on the host the 32 lanes of a region run
+    one after another.  Running them in both orders catches a lane that reads what another lane of the same region
+    writes -- which the device, where they run together, would not reproduce."""
     d = os.path.join(ROOT, "tests", "host_emul")
-    so = os.path.join(d, "libsvtme_emul.so")
-    subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", so, os.path.join(d, "emul.cc")])
+    rev = request.param == "lanes-reverse"
+    so = os.path.join(d, "libsvtme_emul_rev.so" if rev else "libsvtme_emul.so")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared"] + (["-DSVTME_LANES_REVERSE"] if rev else []) +
+                          ["-o", so, os.path.join(d, "emul.cc")])
     return Emul(C.CDLL(so))
 
 

@@ -130,7 +130,7 @@ def test_picture_sums_reference_and_oracle(reference, oracle, enc_mode):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("pipeline", [0, 1], ids=["staged", "persistent"])
+@pytest.mark.parametrize("pipeline", [0], ids=["staged"])
 def test_gpu_picture_sums(oracle, pipeline):
     w, h, n = 832, 488, 5
     frames, po = H.make_pictures(oracle, w, h, n, seed=22, kind="pan")

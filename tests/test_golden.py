@@ -94,7 +94,7 @@ def test_knob_mirror_reproduces_golden_knobs(gold):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("pipeline", [0, 1], ids=["staged", "persistent"])
+@pytest.mark.parametrize("pipeline", [0], ids=["staged"])
 def test_cuda_reproduces_golden_vectors(gold, pipeline):
     dev = api.MeDevice(max_width=256, max_height=256, max_pictures=16, pipeline=pipeline)
     try:

@@ -15,9 +15,9 @@ pytestmark = pytest.mark.gpu
 W, HH = 448, 264  # 7 x 5 SB64, last SB row 8 pixels high
 
 
-@pytest.fixture(scope="module", params=[0, 1], ids=["staged", "persistent"])
+@pytest.fixture(scope="module", params=[0], ids=["staged"])
 def dev(request):
-    """Both execution pipelines of the library: picture-wide staged kernels (default) and the single persistent kernel."""
+    """The library's execution pipeline: picture-wide staged kernels (the round-1 persistent kernel no longer ships)."""
     d = api.MeDevice(device=0, max_inflight=4, pipeline=request.param)
     yield d
     d.close()

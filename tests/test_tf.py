@@ -111,7 +111,7 @@ def gpu_clip(oracle):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("pipeline", [0, 1], ids=["staged", "persistent"])
+@pytest.mark.parametrize("pipeline", [0], ids=["staged"])
 @pytest.mark.parametrize("level,exit_th,dist", [(0, 0, 1), (0, 256, 2), (1, 0, 3), (1, 4000, 1), (2, 256, 1), (2, 0, 2),
                                                 (3, 0, 1), (3, 4000, 3), (4, 0, 1), (4, 4000, 2)])
 def test_gpu_matches_oracle(oracle, gpu_clip, pipeline, level, exit_th, dist):
@@ -148,7 +148,7 @@ def test_compact_outputs_oracle_and_reference(reference, oracle, clips):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("pipeline", [0, 1], ids=["staged", "persistent"])
+@pytest.mark.parametrize("pipeline", [0], ids=["staged"])
 def test_gpu_compact_outputs(oracle, gpu_clip, pipeline):
     frames, po = gpu_clip
     k = api.derive_tf_knobs(hme_me_level=2, qp_opt=1, me_exit_th=256, qp=35, width=GW, height=GH, picture_number=3,

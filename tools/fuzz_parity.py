@@ -26,7 +26,7 @@ def main():
         n = int(rng.integers(8, 10))  # enough pictures for 4 + 3 references
         seed = int(rng.integers(0, 1 << 30))
         frames, po = H.make_pictures(oracle, w, h, n, seed=seed, kind=kind)
-        dev = api.MeDevice(device=0, pipeline=int(rng.integers(0, 2)))
+        dev = api.MeDevice(device=0, pipeline=0 * int(rng.integers(0, 2)))
         try:
             pd = [dev.register(f, i) for i, f in enumerate(frames)]
             cur = int(rng.integers(0, n))
