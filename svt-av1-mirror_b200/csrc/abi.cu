@@ -352,6 +352,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     p.wb = wb; p.hb = hb; p.pu_count = pu_count; p.work_counter = sl->d_counter;
     p.px_counter = reinterpret_cast<unsigned long long *>(sl->d_counter + 2);
     p.states = reinterpret_cast<SbState *>(sl->d_states);
+    p.plans16 = sl->d_states + staged_plan_offset(n_b64);
     uint8_t *d = sl->d_res;
     const ResultLayout &L = sl->lay;
     p.out.me_mv = (uint32_t *)(d + L.off[R_MV]); p.out.me_cand = d + L.off[R_CAND]; p.out.total_me_candidate_index = d + L.off[R_COUNT];
@@ -378,7 +379,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     if (e == cudaSuccess && p.out.picture_sums) e = cudaMemsetAsync(p.out.picture_sums, 0, L.bytes[R_PSUM], st);
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_start, st);
     int n_launch = 0;
-    if (e == cudaSuccess) e = launch_me_picture_staged(p, *maps, st, &n_launch);
+    if (e == cudaSuccess) e = launch_me_picture_staged(p, *maps, h->sm_count, st, &n_launch);
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_kernel, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(sl->h_px, sl->d_counter + 2, 8, cudaMemcpyDeviceToHost, st);
     sl->to_host = out != nullptr;
@@ -471,6 +472,7 @@ void svtme_destroy(SvtMeHandle *h) {
     if (!h) return;
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
+    staged_print_phases();
     for (auto &s : h->slots) {
         if (s.stream) cudaStreamDestroy(s.stream);
         if (s.ev_start) cudaEventDestroy(s.ev_start);

@@ -942,7 +942,11 @@ SVTME_HD void gm_detection(const MeParams &p, const SbState &s, const SbOut &o, 
 
 // ---- the step program: svt_aom_motion_estimation_b64 (:3076-3153) for ME_OPEN_LOOP with hme_b64 (:2441-2475) and
 // integer_search_b64 (:1249-1516) unrolled into control steps (scalar, per SB) and engine steps (data parallel) ----
-enum StepKind : uint8_t { STEP_CTL = 0, STEP_NXM = 1, STEP_SAD = 2, STEP_FP = 3 };
+// STEP_PROBE: the 1x1 full-pel "search" at the search centre that feeds the 8x8-variance test -- an FpJob list like
+// STEP_FP, but light enough to run beside the control steps instead of in a search-engine kernel
+// STEP_PLAN16: cut the sixteenth-plane jobs just made into sub-windows and batches for st_sad16_kernel (device only: the
+// host emulation's searches need no plan)
+enum StepKind : uint8_t { STEP_CTL = 0, STEP_NXM = 1, STEP_SAD = 2, STEP_FP = 3, STEP_PROBE = 4, STEP_PLAN16 = 5 };
 enum CtlOp : uint8_t {
     C_ZZ_MAKE, C_ZZ_FOLD, C_PREHME_MAKE, C_SAD_FOLD, C_PREHME_FINAL, C_L0_MAKE, C_L0_FOLD, C_L1_MAKE, C_L2_MAKE,
     C_FINAL_CENTRE, C_IS_A, C_IS_B, C_IS_C, C_PRUNE
@@ -956,14 +960,22 @@ SVTME_HDX int build_program(const SvtMeKnobs &k, Step *st) {
     if (k.me_early_exit_th || k.me_safe_limit_zz_th) { ctl(C_ZZ_MAKE, 0); eng(STEP_NXM); ctl(C_ZZ_FOLD, 0); }
     if (k.prehme_enable) {
         const bool split = k.num_of_list_to_search > 1 && l1_hme && k.prehme_l1_early_exit;
-        for (int pass = 0; pass < (split ? 2 : 1); pass++) { ctl(C_PREHME_MAKE, (uint8_t)(split ? pass : 2)); eng(STEP_SAD, 2); ctl(C_SAD_FOLD, 0); }
+        for (int pass = 0; pass < (split ? 2 : 1); pass++) {
+            ctl(C_PREHME_MAKE, (uint8_t)(split ? pass : 2));
+            if (k.hme_search_method == 0) eng(STEP_PLAN16);
+            eng(STEP_SAD, 2); ctl(C_SAD_FOLD, 0);
+        }
         ctl(C_PREHME_FINAL, 0);
     }
     if (k.enable_hme_flag) {
         if (k.enable_hme_level0_flag) {
             const bool dep = k.enable_me_sr_adjustment && k.distance_based_hme_resizing && k.reduce_hme_l0_sr_th_min &&
                 k.reduce_hme_l0_sr_th_max;
-            for (int pass = 0; pass < (dep ? 2 : 1); pass++) { ctl(C_L0_MAKE, (uint8_t)(dep ? pass : 2)); eng(STEP_SAD, 2); ctl(C_L0_FOLD, 0); }
+            for (int pass = 0; pass < (dep ? 2 : 1); pass++) {
+                ctl(C_L0_MAKE, (uint8_t)(dep ? pass : 2));
+                if (k.hme_search_method == 0) eng(STEP_PLAN16);
+                eng(STEP_SAD, 2); ctl(C_L0_FOLD, 0);
+            }
         }
         if (k.enable_hme_level1_flag) { ctl(C_L1_MAKE, 0); eng(STEP_SAD, 1); ctl(C_SAD_FOLD, 0); }
         if (k.enable_hme_level2_flag) { ctl(C_L2_MAKE, 0); eng(STEP_SAD, 0); ctl(C_SAD_FOLD, 0); }
@@ -976,7 +988,7 @@ SVTME_HDX int build_program(const SvtMeKnobs &k, Step *st) {
             ctl(C_IS_A, a);
             if (!k.me_early_exit_th && k.is_ref) eng(STEP_NXM);  // check_00_center's SADs: is_a queues them only then
             ctl(C_IS_B, a);
-            if (k.me_8x8_var_enabled) eng(STEP_FP);  // the 1x1 probe of the 8x8-variance test
+            if (k.me_8x8_var_enabled) eng(STEP_PROBE);  // the 1x1 probe of the 8x8-variance test
             ctl(C_IS_C, a); eng(STEP_FP);
         }
     }
@@ -1096,6 +1108,7 @@ SVTME_HD void me_sb(B &be, const MeParams &p, SbState &s, uint32_t b64_index) {
         case STEP_CTL: ctl_step(p, s, st.op, st.arg); break;  // a warp on the device, 32 sequential lanes on the host
         case STEP_NXM: be.run_nxm(s); break;
         case STEP_SAD: be.run_sad(s); break;
+        case STEP_PLAN16: break;
         default: be.run_fullpel(s); break;
         }
         be.sync();

@@ -24,7 +24,7 @@ namespace svtme {
 // -DSVTME_PHASES: thread 0 of every CTA accumulates the clocks it spends in each phase of the engine kernels
 // (diagnostics; printed per search by SVTME_TRACE=1)
 #ifdef SVTME_PHASES
-__device__ unsigned long long g_phase[2][12];
+__device__ unsigned long long g_phase[4][12];  // 0 full-pel scan, 1 pre-HME, 2 HME level 0, 3 HME level 1 / 2 rows kernels
 #define PH_DECL unsigned long long ph_t = clock64();
 #define PH(k, i) if (threadIdx.x == 0) { const unsigned long long ph_n = clock64(); atomicAdd(&g_phase[k][i], ph_n - ph_t); ph_t = ph_n; }
 #else
@@ -51,6 +51,9 @@ __device__ __forceinline__ void check_src(const MeParams &p, int lvl, int li, in
 #define CHECK_SRC(p, lvl, li, ri, g, bytes, site)
 #endif
 
+#ifndef SVTME_ENGINE_CTAS
+#define SVTME_ENGINE_CTAS 0  // 0: one CTA per block
+#endif
 constexpr int kStThreads  = 128;             // 4 warps per block CTA
 constexpr int kStWarps    = kStThreads / 32;
 constexpr int kSadWarpWin = 8 * 1024;        // HME window bytes per warp
@@ -179,57 +182,58 @@ __device__ void nxm_engine(SbState &s) {
     }
 }
 
-// The tail of a kernel: steps [first, first + count) of the program -- control steps (warp 0) and the light
-// svt_nxm_sad_kernel probes (all warps) -- then, in the picture's last kernel, the results (sb_finish), and the state goes
-// back to HBM/L2.  Called by every thread of the CTA after a barrier; one copy of this code serves all kernels.
-__device__ __forceinline__ void run_tail(const MeParams &p, unsigned char *head, int first, int count, int finish) {
-    SbState &s = *reinterpret_cast<SbState *>(head);
-    for (int i = first; i < first + count; i++) {
-        const Step st = p.prog[i];
-        if (st.kind == STEP_CTL) {
-            if (threadIdx.x < 32) ctl_step(p, s, st.op, st.arg);
-        } else {
-            nxm_engine(s);
+// ---- the 1x1 probes of the 8x8-variance test (motion_estimation.c:1391-1412): one open_loop_me_fullpel_search_sblock call
+// with a single candidate per reference, sub-sampled SAD.  One warp: lane = (16x16 block b in z-order, upper / lower pair
+// of its 8x8 blocks); the operands come straight from global memory. ----
+__device__ void probe_engine(const MeParams &p, SbState &s) {
+    const int lane = threadIdx.x & 31;
+    if (threadIdx.x >= 32) return;
+    const int b = lane & 15, h = lane >> 4;
+    const int bx = ((b >> 2) & 1) * 2 + (b & 1), by = (b >> 3) * 2 + ((b >> 1) & 1);
+    SbState  &tab = *s.home;
+    unsigned long long px = 0;
+    for (int ji = 0; ji < kMaxFpJobs; ji++) {
+        const FpJob &j = s.fp_jobs[ji];
+        if (j.w <= 0 || j.h <= 0) continue;
+        if (j.w != 1 || j.h != 1) continue;  // (not produced by is_b)
+        px += 64ull * 32ull;
+        // rows 8h, 8h + 2, 8h + 4, 8h + 6 of the lane's 16x16 block: 16 source bytes (aligned) against 16 reference bytes
+        const uint8_t *sp = s.src + (int64_t)(16 * by + 8 * h) * s.src_stride + 16 * bx;
+        const uint8_t *rp = j.ref + (int64_t)(16 * by + 8 * h) * j.ref_stride + 16 * bx;
+        const int      a  = (int)((uintptr_t)rp & 3), sh = 8 * a;
+        const uint32_t *ra = reinterpret_cast<const uint32_t *>(rp - a);
+        uint32_t sad8[2] = {0u, 0u};
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const uint4     sv = *reinterpret_cast<const uint4 *>(sp + (int64_t)(2 * r) * s.src_stride);
+            const uint32_t *rr = ra + (int64_t)(2 * r) * (j.ref_stride >> 2);
+            const uint32_t  w0 = rr[0], w1 = rr[1], w2 = rr[2], w3 = rr[3], w4 = rr[4];  // the fifth word lies inside the padded plane
+            sad8[0] = sad4(sv.x, __funnelshift_r(w0, w1, sh), sad8[0]);
+            sad8[0] = sad4(sv.y, __funnelshift_r(w1, w2, sh), sad8[0]);
+            sad8[1] = sad4(sv.z, __funnelshift_r(w2, w3, sh), sad8[1]);
+            sad8[1] = sad4(sv.w, __funnelshift_r(w3, w4, sh), sad8[1]);
         }
-        __syncthreads();
+        sad8[0] <<= 1; sad8[1] <<= 1;  // sub-sampled SAD: every second row, doubled
+        uint32_t s16 = sad8[0] + sad8[1];
+        s16 += __shfl_xor_sync(0xffffffffu, s16, 16);
+        uint32_t s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 1);
+        s32 += __shfl_xor_sync(0xffffffffu, s32, 2);
+        uint32_t s64 = s32 + __shfl_xor_sync(0xffffffffu, s32, 4);
+        s64 += __shfl_xor_sync(0xffffffffu, s64, 8);
+        // running bests of the reference (strict '<': earlier results win ties)
+        uint32_t      *bs = tab.best_sad[j.li][j.ri], *bm = tab.best_mv[j.li][j.ri];
+        const uint32_t mv = ((uint32_t)(int32_t)j.yo << 16) | (uint16_t)j.xo;
+        auto upd = [&](int pu, uint32_t sad) { if (sad < bs[pu]) { bs[pu] = sad; bm[pu] = mv; } };
+        upd(21 + 4 * b + 2 * h, sad8[0]);
+        upd(21 + 4 * b + 2 * h + 1, sad8[1]);
+        if (h == 0) upd(5 + b, s16);
+        if (lane < 16 && (b & 3) == 0) upd(1 + (b >> 2), s32);
+        if (lane == 0) upd(0, s64);
     }
-    if (finish) {
-        StBackend be;
-        sb_finish(be, p, s, blockIdx.x);
-        if (threadIdx.x == 0 && p.px_counter) atomicAdd(p.px_counter, s.px);
-    }
-    head_store(head, s.home);
+    if (lane == 0 && px) s.px += px;
+    __threadfence_block();
 }
 
-// The steps between two search engines (and the results behind the last one): a light kernel, ONE WARP per block --
-// 32 threads, ~2 K registers and 4.7 KB of shared memory per CTA, so that it slips in beside the six resident CTAs of
-// another picture's search engine instead of displacing one (a 128-thread version cost 5 % of the picture rate)
-constexpr int kLightThreads = 32;
-__global__ void __launch_bounds__(kLightThreads) st_light_kernel(const __grid_constant__ MeParams p, int first, int count, int finish) {
-    PDL_ENTRY();
-    __shared__ __align__(16) unsigned char head[kSbHeadBytes];
-    head_load_async(head, &p.states[blockIdx.x]);
-    head_wait();
-    run_tail(p, head, first, count, finish);
-}
-
-// First kernel of a picture: init_me_hme_data for every block, then the steps in front of the first search engine
-__global__ void __launch_bounds__(kStThreads) st_init_kernel(const __grid_constant__ MeParams p, int count, int finish) {
-    PDL_ENTRY();
-    __shared__ __align__(16) unsigned char head[kSbHeadBytes];
-    SbState *home = &p.states[blockIdx.x];
-    for (int i = threadIdx.x; i < kHeadVecs; i += blockDim.x) reinterpret_cast<uint4 *>(head)[i] = make_uint4(0u, 0u, 0u, 0u);
-    // the result tables: unsearched references report MAX_SAD_VALUE (convention of include/svtme_cuda.h), p_sb_best_mv = 0
-    for (int i = threadIdx.x; i < kMaxLists * kMaxRefs * kPus; i += blockDim.x) {
-        (&home->best_sad[0][0][0])[i] = SVTME_MAX_SAD_VALUE;
-        (&home->best_mv[0][0][0])[i]  = 0u;
-    }
-    for (int i = threadIdx.x; i < kPus; i += blockDim.x) home->me_distortion[i] = 0u;
-    __syncthreads();
-    if (threadIdx.x == 0) sb_init_head(p, *reinterpret_cast<SbState *>(head), home, blockIdx.x);
-    __syncthreads();
-    run_tail(p, head, 0, count, finish);
-}
 
 // ---- svt_sad_loop_kernel jobs (pre-HME, HME level 0/1/2): one warp per job ----
 // A lane evaluates 4 x-adjacent candidates (they share shared-memory words; alignments 1..3 by funnel shift).  When a
@@ -645,21 +649,24 @@ __device__ __forceinline__ void rows_job(const MeParams &p, int lvl, const SadJo
 }
 
 // `lvl` 1: quarter plane, <8, 16>; `lvl` 0: full plane, <16, 32>.  Launched only when hme_search_method is sub-sampled.
+#ifndef SVTME_ROWS8_CTAS
+#define SVTME_ROWS8_CTAS 6
+#endif
 template <int NW, int ROWS>
-__global__ void __launch_bounds__(kStThreads, 6) st_sad_rows_kernel(const __grid_constant__ MeParams p, int lvl) {
-    PDL_ENTRY();
+__device__ __forceinline__ void sad_rows_block(const MeParams &p, int lvl, uint32_t sbi) {
     using C = RowsCfg<NW, ROWS>;
     constexpr int kBlkPitch = 17;  // odd: lane = row reads are conflict free
     __shared__ uint32_t                    blk[ROWS * kBlkPitch];
     __shared__ __align__(16) uint32_t      win[kStWarps][C::kWinW];
     __shared__ __align__(16) SadJob        jobs[kMaxSadJobs];
-    SbState  &s = p.states[blockIdx.x];
+    SbState  &s = p.states[sbi];
+    PH_DECL
     jobs_load_async<SadJob, kMaxSadJobs>(jobs, s.sad_jobs);
     constexpr int n = kMaxSadJobs;  // fixed slots, unused ones have empty windows
     // block geometry as in make_sad_job (me_control.cuh)
     const DevPlane &cp = p.cur.lvl[lvl];
     const uint32_t  aw = (uint32_t)((p.cur.lvl[0].width + 7) & ~7), ah = (uint32_t)((p.cur.lvl[0].height + 7) & ~7);
-    const uint32_t  org_x = (blockIdx.x % p.wb) * 64, org_y = (blockIdx.x / p.wb) * 64;
+    const uint32_t  org_x = (sbi % p.wb) * 64, org_y = (sbi / p.wb) * 64;
     const uint32_t  b64_w = min(64u, aw - org_x), b64_h = min(64u, ah - org_y);
     const int       bw = (int)(b64_w >> lvl), rows = (int)((b64_h >> lvl) >> 1), nw_eff = bw >> 2;  // bw is a multiple of 4
     {   // every second row of the source block (same for every job of the SB)
@@ -670,6 +677,7 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad_rows_kernel(const __grid
         }
     }
     if (!jobs_wait_any(n, [&](int i) { return jobs[i].sa_w > 0 && jobs[i].sa_h > 0; })) return;
+    PH(3, 0)  // job fetch + source block
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint32_t  sreg[NW];
 #pragma unroll
@@ -682,23 +690,35 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad_rows_kernel(const __grid
         else rows_job<NW, ROWS, false>(p, lvl, j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff);
     }
     if (lane == 0 && px) atomicAdd(&s.px, (unsigned long long)px);
+    PH(3, 1)  // this warp's windows
+}
+// The engine kernels are PERSISTENT: a CTA walks the picture's blocks with a grid stride.  The grid is sized to a share
+// of the GPU's CTA slots (launch_me_picture_staged), so that the engines of two pictures in flight on different
+// streams are resident side by side instead of one after the other.
+template <int NW, int ROWS>
+__global__ void __launch_bounds__(kStThreads, NW == 8 ? SVTME_ROWS8_CTAS : 6) st_sad_rows_kernel(const __grid_constant__ MeParams p, int lvl) {
+    PDL_ENTRY();
+    const uint32_t n_sb = p.wb * p.hb;
+    for (uint32_t sbi = blockIdx.x; sbi < n_sb; sbi += gridDim.x) {
+        sad_rows_block<NW, ROWS>(p, lvl, sbi);
+        __syncthreads();  // the shared-memory tables are reused by the next block
+    }
 }
 
 // `lvl`: plane of this phase (2 sixteenth: pre-HME / level 0, 1 quarter: level 1, 0 full: level 2).  The source block is
 // derived from the block index alone, so its staging overlaps the fetch of the job descriptors.
-__global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constant__ MeParams p, int lvl) {
-    PDL_ENTRY();
+__device__ __forceinline__ void sad_block(const MeParams &p, int lvl, uint32_t sbi) {
     __shared__ __align__(16) uint32_t blk[64 * 16];
     __shared__ __align__(16) uint8_t  win[kStWarps][kSadWarpWin];
     __shared__ __align__(16) SadJob   jobs[kMaxSadJobs];
-    SbState  &s = p.states[blockIdx.x];
+    SbState  &s = p.states[sbi];
     jobs_load_async<SadJob, kMaxSadJobs>(jobs, s.sad_jobs);
     constexpr int n = kMaxSadJobs;  // fixed slots, unused ones have empty windows
     // block geometry as in make_sad_job (me_control.cuh)
     const DevPlane &cp   = p.cur.lvl[lvl];
     const bool      full = p.k.hme_search_method == 1;
     const uint32_t  aw = (uint32_t)((p.cur.lvl[0].width + 7) & ~7), ah = (uint32_t)((p.cur.lvl[0].height + 7) & ~7);
-    const uint32_t  org_x = (blockIdx.x % p.wb) * 64, org_y = (blockIdx.x / p.wb) * 64;
+    const uint32_t  org_x = (sbi % p.wb) * 64, org_y = (sbi / p.wb) * 64;
     const uint32_t  b64_w = min(64u, aw - org_x), b64_h = min(64u, ah - org_y);
     const int       bw = (int)(b64_w >> lvl), rows = (int)(full ? (b64_h >> lvl) : ((b64_h >> lvl) >> 1)), nw = (bw + 3) >> 2;
     const int       rstep = full ? 1 : 2;
@@ -738,6 +758,14 @@ __global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constan
     }
     if (lane == 0 && px) atomicAdd(&s.px, px);
 }
+__global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constant__ MeParams p, int lvl) {
+    PDL_ENTRY();
+    const uint32_t n_sb = p.wb * p.hb;
+    for (uint32_t sbi = blockIdx.x; sbi < n_sb; sbi += gridDim.x) {
+        sad_block(p, lvl, sbi);
+        __syncthreads();
+    }
+}
 
 // ---- pre-HME / HME level 0 on the sixteenth plane (16x16 blocks, 8 sub-sampled rows): CTA-wide windows, lane = item ----
 // The windows of a batch of (job, column tile, row strip) sub-windows are staged together by TMA (2-D tiled copies of
@@ -760,10 +788,154 @@ struct S16Sub {
     int32_t items, off, ibase;                      // off / ibase: words / items before this sub-window inside its batch
     int32_t tx, ty;                                 // the sub-window's first byte in the padded plane (TMA coordinates)
     float   inv_ng, inv_nx;
-    int16_t hsel, cls, brows, pad_;                 // hsel 1: odd rows only; cls: descriptor index; brows: rows per box
+    int16_t hsel, cls, brows, ref;                  // hsel 1: odd rows only; cls: descriptor index; brows: rows per box; ref: list * 4 + index
 };
 
 constexpr int kPad16 = kDevPad[2];
+
+// The plan of one block's pre-HME / HME level-0 searches: the job windows cut into sub-windows, laid out in the window
+// buffer and grouped into batches.  It is made by the one-warp light kernel in front of st_sad16_kernel (the step after
+// the control step that makes the jobs) -- inside the engine it was a third of a CTA's life, with three warps and the
+// CTA's registers and 35 KB of shared memory waiting on one warp -- and handed over through HBM/L2.
+struct alignas(16) S16Plan {
+    int32_t n_sub_all, n_batch, generic, pad_;  // generic: the block takes the per-warp path (picture edge, too many sub-windows)
+    int32_t b_start[kS16MaxSub + 1], b_items[kS16MaxSub], b_words[kS16MaxSub];
+    int32_t pad2_[3];
+    S16Sub  subs[kS16MaxSub];
+};
+static_assert(sizeof(S16Plan) % 16 == 0, "plans are copied as 16-byte words");
+
+// one warp (threads 0 .. 31 of the CTA): lane = job.  Sub-windows = (column tile of <= 128 candidates) x (row strip)
+__device__ void s16_plan(const MeParams &p, SbState &s, S16Plan &pl) {
+    const int     lane = threadIdx.x & 31;
+    constexpr int n    = kMaxSadJobs;
+    SadJob       *jobs = s.sad_jobs;
+    const int     bw = (int)(s.b64_w >> 2), rows = (int)((s.b64_h >> 2) >> 1);
+    if (lane == 0) { pl.n_sub_all = 0; pl.n_batch = 0; pl.generic = 0; }
+    __syncwarp();
+    {
+        const int  ji    = lane;
+        const bool valid = ji < n && jobs[ji].sa_w > 0 && jobs[ji].sa_h > 0;
+        int        cnt = 0, nst = 1, ny_cap = 16;
+        uint32_t   px = 0;
+        if (valid) {
+            const int W = jobs[ji].sa_w, H = jobs[ji].sa_h;
+            const int a16  = (int)((uintptr_t)jobs[ji].ref & 15);                          // the same for every tile (x0 = 128 t)
+            const int need = 4 * ((a16 >> 2) + (((a16 & 3) + min(128, W) + 3) >> 2)) + 16;  // bytes of the widest tile's rows
+            const int pmax = need <= 48 ? 12 : need <= 80 ? 20 : need <= 112 ? 28 : need <= 144 ? 36 : 44;  // its row pitch in words
+            // a sub-window (rows rounded up to boxes of 128) fits the buffer and has < 64 K candidates
+            ny_cap = min(448, (kS16BufWords / (128 * pmax)) * 128 - 14) & ~3;
+            nst    = H <= ny_cap ? 1 : (H + ny_cap - 1) / ny_cap;
+            cnt    = ((W + 127) >> 7) * nst;
+            px     = (uint32_t)W * (uint32_t)(jobs[ji].skip_line ? (H >> 1) : H) * (8 * 16);
+        }
+        for (int o = 16; o; o >>= 1) px += __shfl_xor_sync(0xffffffffu, px, o);  // < 2^32: 32 jobs x 400 x 400 x 128
+        if (lane == 0 && px) s.px += (unsigned long long)px;  // the only writer of the shared-memory copy at this point
+        // one sub-window per job in the common case: everything below is then lane-parallel
+        auto fill = [&](S16Sub &u, int x0, int y0, int nx, int ny, int &words) {
+            const SadJob &j = jobs[ji];
+            const int     a16 = (int)((uintptr_t)(j.ref + x0) & 15), a = a16 & 3, wo = a16 >> 2;  // planes and rows are 16-byte aligned
+            const int     ngroups = (a + nx + 3) >> 2, need = 4 * (wo + ngroups) + 16;  // a group reads 5 words: 4 candidates + 15 more bytes
+            const int     cls = need <= 48 ? 0 : need <= 80 ? 1 : need <= 112 ? 2 : need <= 144 ? 3 : 4, P = 12 + 8 * cls;  // kS16BoxBytes[cls] / 4
+            const int     nyp = (ny + 3) & ~3, nrows = nyp + 14, hc = nrows <= 24 ? 0 : nrows <= 96 ? 1 : 2;
+            const int     brows = 8 << (2 * hc), nbox = (nrows + brows - 1) / brows;  // kS16BoxRows[hc]
+            // the sub-window's first byte inside the reference's padded sixteenth plane
+            const DevPlane &rpl = p.refs[j.li][j.ri].lvl[2];
+            const int       offb = (int)((j.ref + (int64_t)y0 * j.raw_stride + x0) - (rpl.org - (int64_t)kPad16 * rpl.stride - kPad16));
+            const int       ty = offb / rpl.stride;
+            u.job = (int16_t)ji; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
+            u.ngroups = (int16_t)ngroups; u.P = (int16_t)P; u.nbox = (int16_t)nbox; u.cls = (int16_t)(cls * kS16HClasses + hc); u.brows = (int16_t)brows;
+            u.a = (int16_t)a; u.wo = (int16_t)wo;
+            u.tx = offb - ty * rpl.stride - a16; u.ty = ty;
+            u.hsel  = j.skip_line ? 1 : 0;
+            u.ref   = (int16_t)(j.li * kMaxRefs + j.ri);
+            u.items = (nyp >> 2) * (j.skip_line ? 1 : 2) * ngroups;
+            u.inv_ng = __fdividef(1.0f, (float)ngroups) * 1.0000001f; u.inv_nx = __fdividef(1.0f, (float)nx) * 1.0000001f;
+            words = nbox * brows * P;
+        };
+        const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+        if (__all_sync(0xffffffffu, cnt <= 1)) {
+            const int S = __popc(vmask), idx = __popc(vmask & ((1u << lane) - 1u));
+            int       words = 0, items = 0;
+            if (valid) { fill(pl.subs[idx], 0, 0, jobs[ji].sa_w, jobs[ji].sa_h, words); items = pl.subs[idx].items; }
+            int cw = words, ci = items;  // inclusive sums over the lanes (invalid lanes contribute 0)
+            for (int o = 1; o < 32; o <<= 1) {
+                const int vw = __shfl_up_sync(0xffffffffu, cw, o), vi = __shfl_up_sync(0xffffffffu, ci, o);
+                if (lane >= o) { cw += vw; ci += vi; }
+            }
+            // greedy batches: a lane whose window would overflow the buffer starts the next batch
+            int base_w = 0, base_i = 0, nb = 0;
+            if (lane == 0) pl.b_start[0] = 0;
+            for (;;) {
+                const unsigned over = __ballot_sync(0xffffffffu, valid && cw - base_w > kS16BufWords);
+                if (!over) break;
+                const int first = __ffs(over) - 1;
+                const int fw = __shfl_sync(0xffffffffu, cw - words, first), fi = __shfl_sync(0xffffffffu, ci - items, first);
+                const int fidx = __shfl_sync(0xffffffffu, idx, first);
+                // items of the batch that ends here = fi - (items before the batch); every lane >= first moves its base
+                const int prev_base_i = __shfl_sync(0xffffffffu, base_i, first), prev_base_w = __shfl_sync(0xffffffffu, base_w, first);
+                if (lane == 0) { pl.b_items[nb] = fi - prev_base_i; pl.b_words[nb] = fw - prev_base_w; pl.b_start[nb + 1] = fidx; }
+                nb++;
+                if (lane >= first) { base_w = fw; base_i = fi; }
+            }
+            if (valid) { pl.subs[idx].off = cw - words - base_w; pl.subs[idx].ibase = ci - items - base_i; }
+            const int tot_i = __shfl_sync(0xffffffffu, ci, 31), last_base_i = __shfl_sync(0xffffffffu, base_i, 31);
+            const int tot_w = __shfl_sync(0xffffffffu, cw, 31), last_base_w = __shfl_sync(0xffffffffu, base_w, 31);
+            if (lane == 0) { pl.b_items[nb] = tot_i - last_base_i; pl.b_words[nb] = tot_w - last_base_w; pl.b_start[nb + 1] = S; pl.n_batch = S ? nb + 1 : 0; pl.n_sub_all = S; }
+        } else {
+            int incl = cnt;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const int S = __shfl_sync(0xffffffffu, incl, 31);
+            if (lane == 0) pl.n_sub_all = S;
+            if (S <= kS16MaxSub && cnt > 0) {
+                const SadJob &j = jobs[ji];
+                for (int local = 0, xt = 0, st = 0; local < cnt; local++) {
+                    const int x0 = xt * 128, y0 = st * ny_cap;
+                    int       words;
+                    fill(pl.subs[incl - cnt + local], x0, y0, min(128, j.sa_w - x0), min(ny_cap, j.sa_h - y0), words);
+                    if (++st == nst) { st = 0; xt++; }
+                }
+            }
+            __syncwarp();
+            // batches: maximal runs of sub-windows that fit the buffer (lane 0; a handful of adds per sub-window)
+            if (lane == 0 && S <= kS16MaxSub) {
+                int nb = 0, used = 0, items = 0;
+                pl.b_start[0] = 0;
+                for (int i = 0; i < S; i++) {
+                    S16Sub   &u = pl.subs[i];
+                    const int w2 = u.nbox * u.brows * u.P;
+                    if (used + w2 > kS16BufWords) { pl.b_items[nb] = items; pl.b_words[nb] = used; pl.b_start[++nb] = i; used = 0; items = 0; }
+                    u.off = used; u.ibase = items;
+                    used += w2; items += u.items;
+                }
+                pl.b_items[nb] = items; pl.b_words[nb] = used; pl.b_start[++nb] = S;
+                pl.n_batch = nb;
+            }
+        }
+
+        __syncwarp();
+        if (lane == 0) {
+            pl.generic = (bw != 16 || rows != 8 || pl.n_sub_all > kS16MaxSub) ? 1 : 0;
+            if (pl.generic) {
+                // the work counter of partial blocks: rows x width of THIS block (the decomposition counted 8 x 16)
+                long long d = 0;
+                for (int q = 0; q < n; q++) {
+                    const SadJob &j = jobs[q];
+                    if (j.sa_w > 0 && j.sa_h > 0) {
+                        const bool skip = j.skip_line && bw == 16 && rows <= 16;
+                        d += (long long)j.sa_w * (skip ? (j.sa_h >> 1) : j.sa_h) * rows * bw;
+                        d -= (long long)j.sa_w * (j.skip_line ? (j.sa_h >> 1) : j.sa_h) * (8 * 16);
+                    }
+                }
+                s.px += (unsigned long long)d;
+            }
+        }
+        __syncwarp();
+    }
+}
 
 // mbarrier / TMA primitives (PTX ISA: mbarrier, cp.async.bulk.tensor)
 SVTME_D void mbar_init(uint32_t mbar, uint32_t count) {
@@ -785,30 +957,26 @@ SVTME_D void tma_load_2d(uint32_t dst, const void *tmap, int x, int y, uint32_t 
                  ::"r"(dst), "l"(tmap), "r"(x), "r"(y), "r"(mbar) : "memory");
 }
 
-__global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_constant__ MeParams p, const __grid_constant__ S16Maps maps) {
-    PDL_ENTRY();
+// `mbar` is initialised once per CTA; `phase` counts the copy batches this CTA has waited for (the barrier's parity)
+__device__ __forceinline__ void sad16_block(const MeParams &p, const S16Maps &maps, uint32_t sbi, uint32_t mbar, uint32_t &phase, int tag) {
     extern __shared__ __align__(128) uint32_t s16_win[];  // kS16BufWords
-    __shared__ __align__(16) SadJob        jobs[kMaxSadJobs];
+    __shared__ __align__(16) S16Plan       pl;  // made by s16_plan in the light kernel in front of this one
     __shared__ unsigned long long          job_key[kMaxSadJobs];
-    __shared__ S16Sub                      subs[kS16MaxSub];
     __shared__ uint32_t                    sub_key[kS16MaxSub];
-    __shared__ int                         n_sub_all, n_batch, b_start[kS16MaxSub + 1], b_items[kS16MaxSub], b_words[kS16MaxSub];
-    __shared__ __align__(8) unsigned long long mbar_store;
-    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&mbar_store);
     PH_DECL
-    SbState  &s = p.states[blockIdx.x];
-    jobs_load_async<SadJob, kMaxSadJobs>(jobs, s.sad_jobs);
+    SbState  &s = p.states[sbi];
+    jobs_load_async<S16Plan, 1>(&pl, static_cast<const S16Plan *>(p.plans16) + sbi);
     {
         if (threadIdx.x < kMaxSadJobs) job_key[threadIdx.x] = ~0ull;
         if (threadIdx.x < kS16MaxSub) sub_key[threadIdx.x] = ~0u;
-        if (threadIdx.x == 0) mbar_init(mbar, 1);
     }
     constexpr int n = kMaxSadJobs;  // fixed slots, unused ones have empty windows
-    static_assert(kMaxSadJobs == 32, "the decomposition below is lane = job");
+    const S16Sub *subs = pl.subs;
+    const int    *b_start = pl.b_start, *b_items = pl.b_items, *b_words = pl.b_words;
     // block geometry as in make_sad_job (me_control.cuh)
     const DevPlane &cp = p.cur.lvl[2];
     const uint32_t  aw = (uint32_t)((p.cur.lvl[0].width + 7) & ~7), ah = (uint32_t)((p.cur.lvl[0].height + 7) & ~7);
-    const uint32_t  org_x = (blockIdx.x % p.wb) * 64, org_y = (blockIdx.x / p.wb) * 64;
+    const uint32_t  org_x = (sbi % p.wb) * 64, org_y = (sbi / p.wb) * 64;
     const uint32_t  b64_w = min(64u, aw - org_x), b64_h = min(64u, ah - org_y);
     const int       bw = (int)(b64_w >> 2), rows = (int)((b64_h >> 2) >> 1);
     const int       warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -821,119 +989,16 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
             sreg[r][0] = v.x; sreg[r][1] = v.y; sreg[r][2] = v.z; sreg[r][3] = v.w;
         }
     }
-    if (!jobs_wait_any(n, [&](int i) { return jobs[i].sa_w > 0 && jobs[i].sa_h > 0; })) return;
-    PH(1, 0)  // job fetch
-    // ---- decomposition by warp 0: lane = job.  Sub-windows = (column tile of <= 128 candidates) x (row strip) ----
-    if (warp == 0) {
-        const int  ji    = lane;
-        const bool valid = ji < n && jobs[ji].sa_w > 0 && jobs[ji].sa_h > 0;
-        int        cnt = 0, nst = 1, ny_cap = 16;
-        uint32_t   px = 0;
-        if (valid) {
-            const int W = jobs[ji].sa_w, H = jobs[ji].sa_h;
-            const int a16  = (int)((uintptr_t)jobs[ji].ref & 15);                          // the same for every tile (x0 = 128 t)
-            const int need = 4 * ((a16 >> 2) + (((a16 & 3) + min(128, W) + 3) >> 2)) + 16;  // bytes of the widest tile's rows
-            const int pmax = need <= 48 ? 12 : need <= 80 ? 20 : need <= 112 ? 28 : need <= 144 ? 36 : 44;  // its row pitch in words
-            // a sub-window (rows rounded up to boxes of 128) fits the buffer and has < 64 K candidates
-            ny_cap = min(448, (kS16BufWords / (128 * pmax)) * 128 - 14) & ~3;
-            nst    = H <= ny_cap ? 1 : (H + ny_cap - 1) / ny_cap;
-            cnt    = ((W + 127) >> 7) * nst;
-            px     = (uint32_t)W * (uint32_t)(jobs[ji].skip_line ? (H >> 1) : H) * (8 * 16);
-        }
-        for (int o = 16; o; o >>= 1) px += __shfl_xor_sync(0xffffffffu, px, o);  // < 2^32: 32 jobs x 400 x 400 x 128
-        if (lane == 0 && px) atomicAdd(&s.px, (unsigned long long)px);
-        // one sub-window per job in the common case: everything below is then lane-parallel
-        auto fill = [&](S16Sub &u, int x0, int y0, int nx, int ny, int &words) {
-            const SadJob &j = jobs[ji];
-            const int     a16 = (int)((uintptr_t)(j.ref + x0) & 15), a = a16 & 3, wo = a16 >> 2;  // planes and rows are 16-byte aligned
-            const int     ngroups = (a + nx + 3) >> 2, need = 4 * (wo + ngroups) + 16;  // a group reads 5 words: 4 candidates + 15 more bytes
-            const int     cls = need <= 48 ? 0 : need <= 80 ? 1 : need <= 112 ? 2 : need <= 144 ? 3 : 4, P = 12 + 8 * cls;  // kS16BoxBytes[cls] / 4
-            const int     nyp = (ny + 3) & ~3, nrows = nyp + 14, hc = nrows <= 24 ? 0 : nrows <= 96 ? 1 : 2;
-            const int     brows = 8 << (2 * hc), nbox = (nrows + brows - 1) / brows;  // kS16BoxRows[hc]
-            // the sub-window's first byte inside the reference's padded sixteenth plane
-            const DevPlane &rpl = p.refs[j.li][j.ri].lvl[2];
-            const int       offb = (int)((j.ref + (int64_t)y0 * j.raw_stride + x0) - (rpl.org - (int64_t)kPad16 * rpl.stride - kPad16));
-            const int       ty = offb / rpl.stride;
-            u.job = (int16_t)ji; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
-            u.ngroups = (int16_t)ngroups; u.P = (int16_t)P; u.nbox = (int16_t)nbox; u.cls = (int16_t)(cls * kS16HClasses + hc); u.brows = (int16_t)brows;
-            u.a = (int16_t)a; u.wo = (int16_t)wo;
-            u.tx = offb - ty * rpl.stride - a16; u.ty = ty;
-            u.hsel  = j.skip_line ? 1 : 0;
-            u.items = (nyp >> 2) * (j.skip_line ? 1 : 2) * ngroups;
-            u.inv_ng = __fdividef(1.0f, (float)ngroups) * 1.0000001f; u.inv_nx = __fdividef(1.0f, (float)nx) * 1.0000001f;
-            words = nbox * brows * P;
-        };
-        const unsigned vmask = __ballot_sync(0xffffffffu, valid);
-        if (__all_sync(0xffffffffu, cnt <= 1)) {
-            const int S = __popc(vmask), idx = __popc(vmask & ((1u << lane) - 1u));
-            int       words = 0, items = 0;
-            if (valid) { fill(subs[idx], 0, 0, jobs[ji].sa_w, jobs[ji].sa_h, words); items = subs[idx].items; }
-            int cw = words, ci = items;  // inclusive sums over the lanes (invalid lanes contribute 0)
-            for (int o = 1; o < 32; o <<= 1) {
-                const int vw = __shfl_up_sync(0xffffffffu, cw, o), vi = __shfl_up_sync(0xffffffffu, ci, o);
-                if (lane >= o) { cw += vw; ci += vi; }
-            }
-            // greedy batches: a lane whose window would overflow the buffer starts the next batch
-            int base_w = 0, base_i = 0, nb = 0;
-            if (lane == 0) b_start[0] = 0;
-            for (;;) {
-                const unsigned over = __ballot_sync(0xffffffffu, valid && cw - base_w > kS16BufWords);
-                if (!over) break;
-                const int first = __ffs(over) - 1;
-                const int fw = __shfl_sync(0xffffffffu, cw - words, first), fi = __shfl_sync(0xffffffffu, ci - items, first);
-                const int fidx = __shfl_sync(0xffffffffu, idx, first);
-                // items of the batch that ends here = fi - (items before the batch); every lane >= first moves its base
-                const int prev_base_i = __shfl_sync(0xffffffffu, base_i, first), prev_base_w = __shfl_sync(0xffffffffu, base_w, first);
-                if (lane == 0) { b_items[nb] = fi - prev_base_i; b_words[nb] = fw - prev_base_w; b_start[nb + 1] = fidx; }
-                nb++;
-                if (lane >= first) { base_w = fw; base_i = fi; }
-            }
-            if (valid) { subs[idx].off = cw - words - base_w; subs[idx].ibase = ci - items - base_i; }
-            const int tot_i = __shfl_sync(0xffffffffu, ci, 31), last_base_i = __shfl_sync(0xffffffffu, base_i, 31);
-            const int tot_w = __shfl_sync(0xffffffffu, cw, 31), last_base_w = __shfl_sync(0xffffffffu, base_w, 31);
-            if (lane == 0) { b_items[nb] = tot_i - last_base_i; b_words[nb] = tot_w - last_base_w; b_start[nb + 1] = S; n_batch = S ? nb + 1 : 0; n_sub_all = S; }
-        } else {
-            int incl = cnt;
-            for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += v;
-            }
-            const int S = __shfl_sync(0xffffffffu, incl, 31);
-            if (lane == 0) n_sub_all = S;
-            if (S <= kS16MaxSub && cnt > 0) {
-                const SadJob &j = jobs[ji];
-                for (int local = 0, xt = 0, st = 0; local < cnt; local++) {
-                    const int x0 = xt * 128, y0 = st * ny_cap;
-                    int       words;
-                    fill(subs[incl - cnt + local], x0, y0, min(128, j.sa_w - x0), min(ny_cap, j.sa_h - y0), words);
-                    if (++st == nst) { st = 0; xt++; }
-                }
-            }
-            __syncwarp();
-            // batches: maximal runs of sub-windows that fit the buffer (lane 0; a handful of adds per sub-window)
-            if (lane == 0 && S <= kS16MaxSub) {
-                int nb = 0, used = 0, items = 0;
-                b_start[0] = 0;
-                for (int i = 0; i < S; i++) {
-                    S16Sub   &u = subs[i];
-                    const int w2 = u.nbox * u.brows * u.P;
-                    if (used + w2 > kS16BufWords) { b_items[nb] = items; b_words[nb] = used; b_start[++nb] = i; used = 0; items = 0; }
-                    u.off = used; u.ibase = items;
-                    used += w2; items += u.items;
-                }
-                b_items[nb] = items; b_words[nb] = used; b_start[++nb] = S;
-                n_batch = nb;
-            }
-        }
-        __syncwarp();
-        // the first batch's bytes are announced before anybody can issue its copies (barrier below)
-        if (lane == 0 && bw == 16 && rows == 8 && n_sub_all > 0 && n_sub_all <= kS16MaxSub && n_batch > 0)
-            mbar_expect_tx(mbar, 4u * (uint32_t)b_words[0]);
-    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
-    const int S = n_sub_all;
-    if (bw != 16 || rows != 8 || S > kS16MaxSub) {
+    PH(tag, 0)  // plan fetch
+    const int S = pl.n_sub_all;
+    if (S == 0 && !pl.generic) return;  // every reference of the block took an early exit
+    if (pl.generic) {
         // generic path: block words in shared memory, one warp per job, warp-private windows carved from the buffer
+        __shared__ __align__(16) SadJob jobs[kMaxSadJobs];
+        for (int i = threadIdx.x; i < (int)(sizeof(jobs) / 16); i += blockDim.x)
+            reinterpret_cast<uint4 *>(jobs)[i] = reinterpret_cast<const uint4 *>(s.sad_jobs)[i];
         uint32_t *blk = s16_win;
         const int nw = (bw + 3) >> 2;
         for (int i = threadIdx.x; i < rows * nw; i += blockDim.x) {
@@ -951,40 +1016,25 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
             if (bw == 16) warp_sad_job<4>(j, s.sad_jobs[ji], blk, w8, lane, rows, bw, 2, kWin);
             else warp_sad_job<0>(j, s.sad_jobs[ji], blk, w8, lane, rows, bw, 2, kWin);
         }
-        {
-            // the work counter of partial blocks: rows x width of THIS block (the decomposition above counted 8 x 16)
-            if (threadIdx.x == 0) {
-                long long px = 0;
-                for (int ji = 0; ji < n; ji++) {
-                    const SadJob &j = jobs[ji];
-                    if (j.sa_w > 0 && j.sa_h > 0) {
-                        const bool skip = j.skip_line && bw == 16 && rows <= 16;
-                        px += (long long)j.sa_w * (skip ? (j.sa_h >> 1) : j.sa_h) * rows * bw;
-                        px -= (long long)j.sa_w * (j.skip_line ? (j.sa_h >> 1) : j.sa_h) * (8 * 16);
-                    }
-                }
-                if (px) atomicAdd(&s.px, (unsigned long long)px);
-            }
-        }
         return;
     }
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(s16_win);
-    PH(1, 1)  // decomposition
-    const int nb = n_batch;
+    const int nb = pl.n_batch;
+    if (threadIdx.x == 0 && nb > 0) mbar_expect_tx(mbar, 4u * (uint32_t)b_words[0]);  // the first batch's bytes
     for (int bi = 0; bi < nb; bi++) {
         const int s_lo = b_start[bi], s_hi = b_start[bi + 1];
         // stage: one warp per sub-window, one lane per box.  Boxes may reach past the window (rounded-up
         // rows, the box class's width) or past the plane (zero fill): never used.
         for (int si = s_lo + warp; si < s_hi; si += kStWarps) {
             const S16Sub  &u = subs[si];
-            const SadJob  &j = jobs[u.job];
-            const unsigned char *tm = maps.m[j.li * kMaxRefs + j.ri][u.cls];
+            const unsigned char *tm = maps.m[u.ref][u.cls];
             const uint32_t box_bytes = 4u * (uint32_t)u.brows * (uint32_t)u.P, dst0 = sbase + 4u * (uint32_t)u.off;
             if (lane < u.nbox) tma_load_2d(dst0 + (uint32_t)lane * box_bytes, tm, u.tx, u.ty + u.brows * lane, mbar);  // <= 4 boxes
         }
-        PH(1, 2)  // copy issue
-        mbar_wait(mbar, (uint32_t)(bi & 1));
-        PH(1, 3)  // copy wait
+        PH(tag, 2)  // copy issue
+        mbar_wait(mbar, phase & 1u);
+        phase++;
+        PH(tag, 3)  // copy wait
         // compute: flat item list of the batch, lane f takes items f, f + 128, ...
         {
             const int T = b_items[bi];
@@ -1046,10 +1096,10 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
             }
             flush();
         }
-        PH(1, 4)  // search (this thread)
+        PH(tag, 4)  // search (this thread)
         if (threadIdx.x == 0 && bi + 1 < nb) mbar_expect_tx(mbar, 4u * (uint32_t)b_words[bi + 1]);
         __syncthreads();  // the windows are reused by the next batch
-        PH(1, 5)  // waiting for the other warps
+        PH(tag, 5)  // waiting for the other warps
     }
     // sub-window minima -> job keys (sad, y, x): raster order inside the job decides ties between sub-windows
     if ((int)threadIdx.x < S && sub_key[threadIdx.x] != ~0u) {
@@ -1067,7 +1117,20 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
             jo.by = (int16_t)((key >> 16) & 0xffff); jo.bx = (int16_t)(key & 0xffff);
         }
     }
-    PH(1, 6)  // results to the block state
+    PH(tag, 6)  // results to the block state
+}
+__global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_constant__ MeParams p, const __grid_constant__ S16Maps maps, int tag) {
+    PDL_ENTRY();
+    __shared__ __align__(8) unsigned long long mbar_store;
+    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&mbar_store);
+    if (threadIdx.x == 0) mbar_init(mbar, 1);
+    __syncthreads();
+    uint32_t       phase = 0;
+    const uint32_t n_sb = p.wb * p.hb;
+    for (uint32_t sbi = blockIdx.x; sbi < n_sb; sbi += gridDim.x) {
+        sad16_block(p, maps, sbi, mbar, phase, tag);
+        __syncthreads();
+    }
 }
 
 // ---- sub-sampled full-pel search (the open-loop hot path): CTA-wide windows, balanced rounds ----
@@ -1094,8 +1157,7 @@ struct FpSub {
 // each reading the plane of parity (e + half) & 1, and one exchange over lane ^ 16 completes the sums: half h ends up
 // with the four candidates of row 4k + e + 2h.
 template <bool FULL>
-__global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_constant__ MeParams p) {
-    PDL_ENTRY();
+__device__ __forceinline__ void fp_sub_block(const MeParams &p, uint32_t sbi) {
     extern __shared__ __align__(16) uint32_t fp_win[];  // kFpBufWords
     __shared__ uint32_t               sub_key[kFpMaxSub][kPus];  // (sad << 12 | candidate) minima of the batch's sub-windows
     __shared__ unsigned long long     fp_key[kMaxFpJobs][kPus];
@@ -1104,7 +1166,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
     __shared__ int                    n_sub, cur_job, cur_xt, cur_st;
     PH_DECL
     __shared__ int                    b_lo[kFpMaxSub + 1], fast_nb;
-    SbState  &s = p.states[blockIdx.x], &tab = s;  // the block's state (HBM/L2): job table in, best-SAD / best-MV tables out
+    SbState  &s = p.states[sbi], &tab = s;  // the block's state (HBM/L2): job table in, best-SAD / best-MV tables out
     jobs_load_async<FpJob, kMaxFpJobs>(jobs, s.fp_jobs);
     {
         for (int i = threadIdx.x; i < kMaxFpJobs * kPus; i += blockDim.x) (&fp_key[0][0])[i] = ~0ull;
@@ -1117,7 +1179,7 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
     uint32_t  sreg[8][4];  // every second row of the lane's 16x16 block, straight from the source picture (sb_init geometry)
     {
         const DevPlane &f   = p.cur.lvl[0];
-        const uint8_t  *sp0 = f.org + (int64_t)((blockIdx.x / p.wb) * 64 + 16 * by) * f.stride + (blockIdx.x % p.wb) * 64 + 16 * bx;
+        const uint8_t  *sp0 = f.org + (int64_t)((sbi / p.wb) * 64 + 16 * by) * f.stride + (sbi % p.wb) * 64 + 16 * bx;
 #pragma unroll
         for (int r = 0; r < 8; r++) {
             const uint4 v = __ldg(reinterpret_cast<const uint4 *>(sp0 + (int64_t)(2 * r + (FULL ? half : 0)) * f.stride));
@@ -1435,6 +1497,89 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
     }
     PH(0, 7)  // results to the block state
 }
+template <bool FULL>
+__global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_constant__ MeParams p) {
+    PDL_ENTRY();
+    const uint32_t n_sb = p.wb * p.hb;
+    for (uint32_t sbi = blockIdx.x; sbi < n_sb; sbi += gridDim.x) {
+        fp_sub_block<FULL>(p, sbi);
+        __syncthreads();
+    }
+}
+
+// the plan goes to HBM/L2 for the engine kernel that follows (all threads of the light CTA)
+__device__ __forceinline__ void s16_plan_store(const MeParams &p, const S16Plan &pl, uint32_t sbi) {
+    const uint4 *l = reinterpret_cast<const uint4 *>(&pl);
+    uint4       *g = reinterpret_cast<uint4 *>(static_cast<S16Plan *>(p.plans16) + sbi);
+    // header + batch tables always; sub-windows up to the number in use
+    const int n_used = pl.generic ? 0 : pl.n_sub_all;
+    const int vecs = (int)(offsetof(S16Plan, subs) + (size_t)n_used * sizeof(S16Sub) + 15) / 16;
+    for (int i = threadIdx.x; i < vecs; i += blockDim.x) g[i] = l[i];
+}
+
+// The tail of a kernel: steps [first, first + count) of the program -- control steps (warp 0) and the light
+// svt_nxm_sad_kernel probes (all warps) -- then, in the picture's last kernel, the results (sb_finish), and the state goes
+// back to HBM/L2.  Called by every thread of the CTA after a barrier; one copy of this code serves all kernels.
+__device__ __forceinline__ void run_tail(const MeParams &p, unsigned char *head, S16Plan &plan, int first, int count, int finish) {
+    SbState &s = *reinterpret_cast<SbState *>(head);
+    bool     planned = false;
+    for (int i = first; i < first + count; i++) {
+        const Step st = p.prog[i];
+        if (st.kind == STEP_CTL) {
+            if (threadIdx.x < 32) ctl_step(p, s, st.op, st.arg);
+        } else if (st.kind == STEP_PLAN16) {
+            if (threadIdx.x < 32) s16_plan(p, s, plan);
+            planned = true;
+        } else if (st.kind == STEP_PROBE) {
+            probe_engine(p, s);
+        } else {
+            nxm_engine(s);
+        }
+        __syncthreads();
+    }
+    if (finish) {
+        StBackend be;
+        sb_finish(be, p, s, blockIdx.x);
+        if (threadIdx.x == 0 && p.px_counter) atomicAdd(p.px_counter, s.px);
+    }
+    head_store(head, s.home);
+    if (planned) s16_plan_store(p, plan, blockIdx.x);  // (a barrier follows every step)
+}
+
+// The steps between two search engines (and the results behind the last one): a light kernel, ONE WARP per block --
+// 32 threads, ~2 K registers and 4.7 KB of shared memory per CTA, so that it slips in beside the six resident CTAs of
+// another picture's search engine instead of displacing one (a 128-thread version cost 5 % of the picture rate)
+constexpr int kLightThreads = 32;
+__global__ void __launch_bounds__(kLightThreads) st_light_kernel(const __grid_constant__ MeParams p, int first, int count, int finish) {
+    PDL_ENTRY();
+    __shared__ __align__(16) unsigned char head[kSbHeadBytes];
+    __shared__ S16Plan plan;
+    head_load_async(head, &p.states[blockIdx.x]);
+    head_wait();
+    run_tail(p, head, plan, first, count, finish);
+}
+
+// First kernel of a picture: init_me_hme_data for every block, then the steps in front of the first search engine
+#ifndef SVTME_INIT_THREADS
+#define SVTME_INIT_THREADS 32
+#endif
+__global__ void __launch_bounds__(kStThreads) st_init_kernel(const __grid_constant__ MeParams p, int count, int finish) {
+    PDL_ENTRY();
+    __shared__ __align__(16) unsigned char head[kSbHeadBytes];
+    __shared__ S16Plan plan;
+    SbState *home = &p.states[blockIdx.x];
+    for (int i = threadIdx.x; i < kHeadVecs; i += blockDim.x) reinterpret_cast<uint4 *>(head)[i] = make_uint4(0u, 0u, 0u, 0u);
+    // the result tables: unsearched references report MAX_SAD_VALUE (convention of include/svtme_cuda.h), p_sb_best_mv = 0
+    for (int i = threadIdx.x; i < kMaxLists * kMaxRefs * kPus; i += blockDim.x) {
+        (&home->best_sad[0][0][0])[i] = SVTME_MAX_SAD_VALUE;
+        (&home->best_mv[0][0][0])[i]  = 0u;
+    }
+    for (int i = threadIdx.x; i < kPus; i += blockDim.x) home->me_distortion[i] = 0u;
+    __syncthreads();
+    if (threadIdx.x == 0) sb_init_head(p, *reinterpret_cast<SbState *>(head), home, blockIdx.x);
+    __syncthreads();
+    run_tail(p, head, plan, 0, count, finish);
+}
 
 // ---- host: run the program of one picture as a stream-ordered sequence of picture-wide kernels ----
 // One kernel per ENGINE step (pre-HME / HME level 0 / 1 / 2 searches, the 1x1 probe, the full-pel scan) plus the first
@@ -1448,8 +1593,13 @@ cudaError_t staged_set_attributes() {  // per device: call with the device curre
     return e;
 }
 
-cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, cudaStream_t st, int *n_launches) {
+cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, int sm_count, cudaStream_t st, int *n_launches) {
     const int n_sb = (int)(p.wb * p.hb);
+#ifdef SVTME_DIAG
+    static const int engine_ctas = getenv("SVTME_ENGINE_CTAS") ? atoi(getenv("SVTME_ENGINE_CTAS")) : SVTME_ENGINE_CTAS;
+#else
+    constexpr int engine_ctas = SVTME_ENGINE_CTAS;
+#endif
     int       nl   = 0;
 #ifdef SVTME_DIAG
     // diagnostics build only: SVTME_TRACE=1 prints per-kernel device times of every picture on stderr (serialises the
@@ -1468,12 +1618,14 @@ cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, cud
     };
     mark("start");
     cudaError_t err = cudaSuccess;
-    int threads = kStThreads;
+    int threads = kStThreads, grid = n_sb;
+    // persistent engine kernels: a share of the CTA slots of the GPU (engine_ctas per SM), see st_sad_rows_kernel
+    const int engine_grid = engine_ctas > 0 ? (n_sb < sm_count * engine_ctas ? n_sb : sm_count * engine_ctas) : n_sb;
     auto launch = [&](auto kern, size_t smem, auto... args) {
         if (err != cudaSuccess) return;  // the chain stops at the first failed launch
         cudaLaunchConfig_t   cfg = {};
         cudaLaunchAttribute  at[1];
-        cfg.gridDim = dim3((unsigned)n_sb); cfg.blockDim = dim3((unsigned)threads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+        cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)threads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
         cfg.attrs = at; cfg.numAttrs = 1;
@@ -1483,22 +1635,32 @@ cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, cud
     auto is_engine = [&](int i) { return p.prog[i].kind == STEP_SAD || p.prog[i].kind == STEP_FP; };
     int i = 0;
     while (i < p.n_steps && !is_engine(i)) i++;
+    threads = SVTME_INIT_THREADS;
     launch(st_init_kernel, 0, p, i, i == p.n_steps ? 1 : 0); mark("init");
+    threads = kStThreads;
     while (i < p.n_steps) {
         int j = i + 1;
         while (j < p.n_steps && !is_engine(j)) j++;
         const int tf = i + 1, tc = j - i - 1, fin = j == p.n_steps ? 1 : 0;
+        grid = engine_grid;
         if (p.prog[i].kind == STEP_SAD) {
             const int lvl = (int)p.prog[i].arg;
             if (lvl == 1 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<8, 16>, 0, p, lvl); mark("rows8"); }
             else if (lvl == 0 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<16, 32>, 0, p, lvl); mark("rows16"); }
-            else if (lvl == 2 && p.k.hme_search_method == 0) { launch(st_sad16_kernel, (size_t)kS16BufWords * 4, p, maps); mark("sad16"); }
+            else if (lvl == 2 && p.k.hme_search_method == 0) {
+                // (diagnostics) 1: pre-HME windows, 2: HME level-0 quadrants -- by the control step that made the jobs
+                int tag = 2;
+                for (int q = i - 1; q >= 0; q--)
+                    if (p.prog[q].kind == STEP_CTL && (p.prog[q].op == C_PREHME_MAKE || p.prog[q].op == C_L0_MAKE)) { tag = p.prog[q].op == C_PREHME_MAKE ? 1 : 2; break; }
+                launch(st_sad16_kernel, (size_t)kS16BufWords * 4, p, maps, tag); mark(tag == 1 ? "prehme" : "hme0");
+            }
             else { launch(st_sad_kernel, 0, p, lvl); mark("sadg"); }
         } else {
             if (p.k.me_search_method == 0) launch(st_fp_sub_kernel<false>, (size_t)kFpBufWords * 4, p);
             else launch(st_fp_sub_kernel<true>, (size_t)kFpBufWords * 4, p);
             mark("fp");
         }
+        grid = n_sb;
         if (tc > 0 || fin) { threads = kLightThreads; launch(st_light_kernel, 0, p, tf, tc, fin); threads = kStThreads; mark("light"); }
         i = j;
     }
@@ -1513,27 +1675,33 @@ cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, cud
             fprintf(stderr, " %s %.1f", nm[q], ms * 1e3f);
         }
         fprintf(stderr, " | total %.1f us\n", tot * 1e3f);
-#ifdef SVTME_PHASES
-        {
-            unsigned long long ph[2][12];
-            cudaMemcpyFromSymbol(ph, g_phase, sizeof(ph));
-            for (int k = 0; k < 2; k++) {
-                unsigned long long sum = 0;
-                for (int q = 0; q < 12; q++) sum += ph[k][q];
-                fprintf(stderr, "[svtme phases] %s:", k == 0 ? "fp_sub" : "sad16");
-                for (int q = 0; q < 12; q++) if (ph[k][q]) fprintf(stderr, " p%d %.1f%%", q, 100.0 * (double)ph[k][q] / (double)sum);
-                fprintf(stderr, " | %.1f kclk per CTA\n", (double)sum / 1e3 / (double)(n_sb * (k == 0 ? 2 : 2)));
-            }
-            memset(ph, 0, sizeof(ph));
-            cudaMemcpyToSymbol(g_phase, ph, sizeof(ph));
-        }
-#endif
     }
     for (int q = 0; q < ne; q++) cudaEventDestroy(ev[q]);
     if (n_launches) *n_launches = nl;
     return err != cudaSuccess ? err : cudaGetLastError();
 }
 
-size_t staged_state_bytes(uint32_t n_sb) { return (size_t)n_sb * sizeof(SbState); }
+// -DSVTME_PHASES: where thread 0 of the engine CTAs spent its clocks since the last call (svtme_destroy prints it)
+void staged_print_phases() {
+#ifdef SVTME_PHASES
+    unsigned long long ph[4][12];
+    if (cudaMemcpyFromSymbol(ph, g_phase, sizeof(ph)) != cudaSuccess) return;
+    static const char *nm[4] = {"fp_sub", "sad16 pre-HME", "sad16 HME-L0", "sad_rows"};
+    for (int k = 0; k < 4; k++) {
+        unsigned long long sum = 0;
+        for (int q = 0; q < 12; q++) sum += ph[k][q];
+        if (!sum) continue;
+        fprintf(stderr, "[svtme phases] %-14s:", nm[k]);
+        for (int q = 0; q < 12; q++) if (ph[k][q]) fprintf(stderr, " p%d %.1f%%", q, 100.0 * (double)ph[k][q] / (double)sum);
+        fprintf(stderr, " | %.1f Mclk\n", (double)sum / 1e6);
+    }
+    memset(ph, 0, sizeof(ph));
+    cudaMemcpyToSymbol(g_phase, ph, sizeof(ph));
+#endif
+}
+
+// block states, then the sixteenth-plane plans
+size_t staged_plan_offset(uint32_t n_sb) { return ((size_t)n_sb * sizeof(SbState) + 255) & ~size_t(255); }
+size_t staged_state_bytes(uint32_t n_sb) { return staged_plan_offset(n_sb) + (size_t)n_sb * sizeof(S16Plan); }
 
 }  // namespace svtme

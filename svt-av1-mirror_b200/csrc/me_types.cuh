@@ -90,6 +90,7 @@ struct MeParams {
     uint32_t  *work_counter;  // persistent-CTA SB queue
     unsigned long long *px_counter;  // optional: algorithmic pixel-compares of the picture (roofline numerator)
     SbState   *states;        // staged pipeline: one SbState per 64x64 block in HBM/L2
+    void      *plans16;       // one S16Plan per block (me_staged.cu): the sixteenth-plane searches' sub-windows and batches
     int32_t    n_steps;
     Step       prog[kMaxSteps];
 };
