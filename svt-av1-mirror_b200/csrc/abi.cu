@@ -353,6 +353,8 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     p.px_counter = reinterpret_cast<unsigned long long *>(sl->d_counter + 2);
     p.states = reinterpret_cast<SbState *>(sl->d_states);
     p.plans16 = sl->d_states + staged_plan_offset(n_b64);
+    p.q_units = reinterpret_cast<uint32_t *>(sl->d_states + staged_queue_offset(n_b64));
+    p.q_ctr   = sl->d_counter + 16;  // behind the work / pixel counters
     uint8_t *d = sl->d_res;
     const ResultLayout &L = sl->lay;
     p.out.me_mv = (uint32_t *)(d + L.off[R_MV]); p.out.me_cand = d + L.off[R_CAND]; p.out.total_me_candidate_index = d + L.off[R_COUNT];
@@ -374,7 +376,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     cudaError_t  e  = cudaStreamWaitEvent(st, cur->ready, 0);
     for (int l = 0; l < knobs->num_of_list_to_search && e == cudaSuccess; l++)
         for (int r = 0; r < knobs->num_of_ref_pic_to_search[l] && e == cudaSuccess; r++) e = cudaStreamWaitEvent(st, refs[l][r]->ready, 0);
-    if (e == cudaSuccess) e = cudaMemsetAsync(sl->d_counter, 0, 16, st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(sl->d_counter, 0, 64 + kQueueCounterBytes, st);
     if (e == cudaSuccess && p.out.tf_blk_counts) e = cudaMemsetAsync(p.out.tf_blk_counts, 0, 8, st);
     if (e == cudaSuccess && p.out.picture_sums) e = cudaMemsetAsync(p.out.picture_sums, 0, L.bytes[R_PSUM], st);
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_start, st);
@@ -451,7 +453,7 @@ int32_t svtme_init(const SvtMeDeviceCfg *cfg, SvtMeHandle **out) {
         if (e == cudaSuccess) e = cudaEventCreate(&s.ev_start);
         if (e == cudaSuccess) e = cudaEventCreate(&s.ev_kernel);
         if (e == cudaSuccess) e = cudaEventCreate(&s.ev_done);
-        if (e == cudaSuccess) e = cudaMalloc(&s.d_counter, 256);
+        if (e == cudaSuccess) e = cudaMalloc(&s.d_counter, 64 + kQueueCounterBytes);
         if (e == cudaSuccess) e = cudaMallocHost(&s.h_px, 64);
     }
     h->up_streams.resize(std::max<uint32_t>(2, inflight));

@@ -946,7 +946,8 @@ SVTME_HD void gm_detection(const MeParams &p, const SbState &s, const SbOut &o, 
 // STEP_FP, but light enough to run beside the control steps instead of in a search-engine kernel
 // STEP_PLAN16: cut the sixteenth-plane jobs just made into sub-windows and batches for st_sad16_kernel (device only: the
 // host emulation's searches need no plan)
-enum StepKind : uint8_t { STEP_CTL = 0, STEP_NXM = 1, STEP_SAD = 2, STEP_FP = 3, STEP_PROBE = 4, STEP_PLAN16 = 5 };
+// STEP_KEYS16: read the minima the engine's warps folded into that plan back into the job table
+enum StepKind : uint8_t { STEP_CTL = 0, STEP_NXM = 1, STEP_SAD = 2, STEP_FP = 3, STEP_PROBE = 4, STEP_PLAN16 = 5, STEP_KEYS16 = 6 };
 enum CtlOp : uint8_t {
     C_ZZ_MAKE, C_ZZ_FOLD, C_PREHME_MAKE, C_SAD_FOLD, C_PREHME_FINAL, C_L0_MAKE, C_L0_FOLD, C_L1_MAKE, C_L2_MAKE,
     C_FINAL_CENTRE, C_IS_A, C_IS_B, C_IS_C, C_PRUNE
@@ -963,7 +964,9 @@ SVTME_HDX int build_program(const SvtMeKnobs &k, Step *st) {
         for (int pass = 0; pass < (split ? 2 : 1); pass++) {
             ctl(C_PREHME_MAKE, (uint8_t)(split ? pass : 2));
             if (k.hme_search_method == 0) eng(STEP_PLAN16);
-            eng(STEP_SAD, 2); ctl(C_SAD_FOLD, 0);
+            eng(STEP_SAD, 2);
+            if (k.hme_search_method == 0) eng(STEP_KEYS16);
+            ctl(C_SAD_FOLD, 0);
         }
         ctl(C_PREHME_FINAL, 0);
     }
@@ -974,7 +977,9 @@ SVTME_HDX int build_program(const SvtMeKnobs &k, Step *st) {
             for (int pass = 0; pass < (dep ? 2 : 1); pass++) {
                 ctl(C_L0_MAKE, (uint8_t)(dep ? pass : 2));
                 if (k.hme_search_method == 0) eng(STEP_PLAN16);
-                eng(STEP_SAD, 2); ctl(C_L0_FOLD, 0);
+                eng(STEP_SAD, 2);
+                if (k.hme_search_method == 0) eng(STEP_KEYS16);
+                ctl(C_L0_FOLD, 0);
             }
         }
         if (k.enable_hme_level1_flag) { ctl(C_L1_MAKE, 0); eng(STEP_SAD, 1); ctl(C_SAD_FOLD, 0); }
@@ -1108,7 +1113,7 @@ SVTME_HD void me_sb(B &be, const MeParams &p, SbState &s, uint32_t b64_index) {
         case STEP_CTL: ctl_step(p, s, st.op, st.arg); break;  // a warp on the device, 32 sequential lanes on the host
         case STEP_NXM: be.run_nxm(s); break;
         case STEP_SAD: be.run_sad(s); break;
-        case STEP_PLAN16: break;
+        case STEP_PLAN16: case STEP_KEYS16: break;
         default: be.run_fullpel(s); break;
         }
         be.sync();

@@ -23,6 +23,8 @@ cudaError_t staged_set_attributes();  // per device, with the device current
 void        staged_print_phases();    // -DSVTME_PHASES builds only
 size_t      staged_state_bytes(uint32_t n_sb);
 size_t      staged_plan_offset(uint32_t n_sb);
+size_t      staged_queue_offset(uint32_t n_sb);
+constexpr int kQueueCounterBytes = 2 * 4 * kMaxSteps;  // [count, head] per program step
 // dynamic-GOP detector HME level 0 (me_dg.cu): picture-level sums accumulated by the kernel (zero them first)
 struct DgSums {
     unsigned long long tot_dist;

@@ -51,6 +51,9 @@ __device__ __forceinline__ void check_src(const MeParams &p, int lvl, int li, in
 #define CHECK_SRC(p, lvl, li, ri, g, bytes, site)
 #endif
 
+#ifndef SVTME_S16_CTAS
+#define SVTME_S16_CTAS 6  // CTAs per SM of the persistent sixteenth-plane engine
+#endif
 #ifndef SVTME_ENGINE_CTAS
 #define SVTME_ENGINE_CTAS 0  // 0: one CTA per block
 #endif
@@ -767,175 +770,36 @@ __global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constan
     }
 }
 
-// ---- pre-HME / HME level 0 on the sixteenth plane (16x16 blocks, 8 sub-sampled rows): CTA-wide windows, lane = item ----
-// The windows of a batch of (job, column tile, row strip) sub-windows are staged together by TMA (2-D tiled copies of
-// the reference's padded sixteenth plane: boxes of 8 rows x 48 .. 176 bytes, one instruction per box, completion on
-// one mbarrier -- nothing of the copy is executed by the SM's own pipes), and ALL their items form one flat list dealt
-// to the 128 lanes -- HME level 0 has ~20 tiny windows per block (8x8 candidates when the reference is close), which
-// per-warp or per-window scheduling leaves mostly idle.  A box must start on a 16-byte boundary of the plane (the
-// TMA unit raises an illegal-instruction error otherwise: tools/microbench/tma_u8.cu), so candidate 0 sits at byte
-// 4 * wo + a of a staged row: groups start at word wo, candidates are shifted by a bytes.
-// An item = 4 x-adjacent candidates on the two candidate rows y and y + 2, which share 7 of their 8 reference rows:
-// 9 window rows (45 LDS, 108 SHF) per 256 SADs.  With prehme_skip_search_line only odd candidate rows exist
-// (y = 4k + 1 and 4k + 3).  The row pitch is 4 x odd words (8 consecutive rows fall on 8 different bank quads).  A lane
-// keeps the minimum of its current sub-window as (sad << 16 | candidate index) and folds it into the job's 64-bit key
-// (sad, y, x) when it moves on.  Blocks cut by the picture edge take the generic per-warp path.
-constexpr int kS16BufWords = 7 * 1024;
-constexpr int kS16MaxSub   = 64;
-struct S16Sub {
+// ---- pre-HME / HME level 0 on the sixteenth plane (16x16 blocks, 8 sub-sampled rows): WARP-autonomous, lane = item ----
+// The job windows of a block are cut into SUB-WINDOWS (a column tile of <= 128 candidates x a row strip) that fit a
+// warp's private window buffer; the cut (the "plan") is made by the one-warp light kernel in front of this engine, which
+// also appends one UNIT per sub-window to the picture's unit queue.  Here every warp of a persistent grid pulls units
+// from that queue: it stages the sub-window by TMA (2-D tiled copies of the reference's padded sixteenth plane: boxes of
+// 8 or 32 rows x 48 .. 176 bytes, one instruction per box, completion on the warp's own mbarrier -- nothing of the copy
+// is executed by the SM's own pipes), walks its items, reduces the minimum over its lanes and folds it into the job's
+// 64-bit key (sad, y, x) in HBM/L2 with one atomic.  No CTA-wide barrier, plan or batch exists in this kernel: a warp
+// that waits for its copy leaves the SM to the other warps, and blocks with much work and blocks with little are dealt
+// to the warps by the queue.  (The CTA-per-block version of this kernel spent 40-50 % of a CTA's life outside the
+// search: plan, copy issue and wait, batch barriers -- with the registers and shared memory of four warps held.)
+// A box must start on a 16-byte boundary of the plane (the TMA unit raises an illegal-instruction error otherwise:
+// tools/microbench/tma_u8.cu), so candidate 0 sits at byte 4 * wo + a of a staged row: groups start at word wo,
+// candidates are shifted by a bytes.  An item = 4 x-adjacent candidates on the two candidate rows y and y + 2, which
+// share 7 of their 8 reference rows: 9 window rows (45 LDS, 108 SHF) per 256 SADs.  With prehme_skip_search_line only odd
+// candidate rows exist (y = 4k + 1 and 4k + 3).  The row pitch is 4 x odd words (8 consecutive rows fall on 8 different
+// bank quads).  Blocks cut by the picture edge take the generic per-warp path, one unit per job.
+constexpr int kS16BufWords = 2304;  // per warp: 9 KB
+constexpr int kS16MaxSub   = 96;
+struct alignas(16) S16Sub {
     int16_t job, x0, y0, nx, ny, ngroups, P, nbox;  // P: row pitch in words = box bytes / 4; nbox: boxes of `brows` rows
     int16_t a, wo;                                  // candidate 0 at byte 4 * wo + a of a staged row
-    int32_t items, off, ibase;                      // off / ibase: words / items before this sub-window inside its batch
+    int32_t items;
     int32_t tx, ty;                                 // the sub-window's first byte in the padded plane (TMA coordinates)
     float   inv_ng, inv_nx;
     int16_t hsel, cls, brows, ref;                  // hsel 1: odd rows only; cls: descriptor index; brows: rows per box; ref: list * 4 + index
 };
+static_assert(sizeof(S16Sub) == 48, "a sub-window descriptor is fetched as three 16-byte words");
 
 constexpr int kPad16 = kDevPad[2];
-
-// The plan of one block's pre-HME / HME level-0 searches: the job windows cut into sub-windows, laid out in the window
-// buffer and grouped into batches.  It is made by the one-warp light kernel in front of st_sad16_kernel (the step after
-// the control step that makes the jobs) -- inside the engine it was a third of a CTA's life, with three warps and the
-// CTA's registers and 35 KB of shared memory waiting on one warp -- and handed over through HBM/L2.
-struct alignas(16) S16Plan {
-    int32_t n_sub_all, n_batch, generic, pad_;  // generic: the block takes the per-warp path (picture edge, too many sub-windows)
-    int32_t b_start[kS16MaxSub + 1], b_items[kS16MaxSub], b_words[kS16MaxSub];
-    int32_t pad2_[3];
-    S16Sub  subs[kS16MaxSub];
-};
-static_assert(sizeof(S16Plan) % 16 == 0, "plans are copied as 16-byte words");
-
-// one warp (threads 0 .. 31 of the CTA): lane = job.  Sub-windows = (column tile of <= 128 candidates) x (row strip)
-__device__ void s16_plan(const MeParams &p, SbState &s, S16Plan &pl) {
-    const int     lane = threadIdx.x & 31;
-    constexpr int n    = kMaxSadJobs;
-    SadJob       *jobs = s.sad_jobs;
-    const int     bw = (int)(s.b64_w >> 2), rows = (int)((s.b64_h >> 2) >> 1);
-    if (lane == 0) { pl.n_sub_all = 0; pl.n_batch = 0; pl.generic = 0; }
-    __syncwarp();
-    {
-        const int  ji    = lane;
-        const bool valid = ji < n && jobs[ji].sa_w > 0 && jobs[ji].sa_h > 0;
-        int        cnt = 0, nst = 1, ny_cap = 16;
-        uint32_t   px = 0;
-        if (valid) {
-            const int W = jobs[ji].sa_w, H = jobs[ji].sa_h;
-            const int a16  = (int)((uintptr_t)jobs[ji].ref & 15);                          // the same for every tile (x0 = 128 t)
-            const int need = 4 * ((a16 >> 2) + (((a16 & 3) + min(128, W) + 3) >> 2)) + 16;  // bytes of the widest tile's rows
-            const int pmax = need <= 48 ? 12 : need <= 80 ? 20 : need <= 112 ? 28 : need <= 144 ? 36 : 44;  // its row pitch in words
-            // a sub-window (rows rounded up to boxes of 128) fits the buffer and has < 64 K candidates
-            ny_cap = min(448, (kS16BufWords / (128 * pmax)) * 128 - 14) & ~3;
-            nst    = H <= ny_cap ? 1 : (H + ny_cap - 1) / ny_cap;
-            cnt    = ((W + 127) >> 7) * nst;
-            px     = (uint32_t)W * (uint32_t)(jobs[ji].skip_line ? (H >> 1) : H) * (8 * 16);
-        }
-        for (int o = 16; o; o >>= 1) px += __shfl_xor_sync(0xffffffffu, px, o);  // < 2^32: 32 jobs x 400 x 400 x 128
-        if (lane == 0 && px) s.px += (unsigned long long)px;  // the only writer of the shared-memory copy at this point
-        // one sub-window per job in the common case: everything below is then lane-parallel
-        auto fill = [&](S16Sub &u, int x0, int y0, int nx, int ny, int &words) {
-            const SadJob &j = jobs[ji];
-            const int     a16 = (int)((uintptr_t)(j.ref + x0) & 15), a = a16 & 3, wo = a16 >> 2;  // planes and rows are 16-byte aligned
-            const int     ngroups = (a + nx + 3) >> 2, need = 4 * (wo + ngroups) + 16;  // a group reads 5 words: 4 candidates + 15 more bytes
-            const int     cls = need <= 48 ? 0 : need <= 80 ? 1 : need <= 112 ? 2 : need <= 144 ? 3 : 4, P = 12 + 8 * cls;  // kS16BoxBytes[cls] / 4
-            const int     nyp = (ny + 3) & ~3, nrows = nyp + 14, hc = nrows <= 24 ? 0 : nrows <= 96 ? 1 : 2;
-            const int     brows = 8 << (2 * hc), nbox = (nrows + brows - 1) / brows;  // kS16BoxRows[hc]
-            // the sub-window's first byte inside the reference's padded sixteenth plane
-            const DevPlane &rpl = p.refs[j.li][j.ri].lvl[2];
-            const int       offb = (int)((j.ref + (int64_t)y0 * j.raw_stride + x0) - (rpl.org - (int64_t)kPad16 * rpl.stride - kPad16));
-            const int       ty = offb / rpl.stride;
-            u.job = (int16_t)ji; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
-            u.ngroups = (int16_t)ngroups; u.P = (int16_t)P; u.nbox = (int16_t)nbox; u.cls = (int16_t)(cls * kS16HClasses + hc); u.brows = (int16_t)brows;
-            u.a = (int16_t)a; u.wo = (int16_t)wo;
-            u.tx = offb - ty * rpl.stride - a16; u.ty = ty;
-            u.hsel  = j.skip_line ? 1 : 0;
-            u.ref   = (int16_t)(j.li * kMaxRefs + j.ri);
-            u.items = (nyp >> 2) * (j.skip_line ? 1 : 2) * ngroups;
-            u.inv_ng = __fdividef(1.0f, (float)ngroups) * 1.0000001f; u.inv_nx = __fdividef(1.0f, (float)nx) * 1.0000001f;
-            words = nbox * brows * P;
-        };
-        const unsigned vmask = __ballot_sync(0xffffffffu, valid);
-        if (__all_sync(0xffffffffu, cnt <= 1)) {
-            const int S = __popc(vmask), idx = __popc(vmask & ((1u << lane) - 1u));
-            int       words = 0, items = 0;
-            if (valid) { fill(pl.subs[idx], 0, 0, jobs[ji].sa_w, jobs[ji].sa_h, words); items = pl.subs[idx].items; }
-            int cw = words, ci = items;  // inclusive sums over the lanes (invalid lanes contribute 0)
-            for (int o = 1; o < 32; o <<= 1) {
-                const int vw = __shfl_up_sync(0xffffffffu, cw, o), vi = __shfl_up_sync(0xffffffffu, ci, o);
-                if (lane >= o) { cw += vw; ci += vi; }
-            }
-            // greedy batches: a lane whose window would overflow the buffer starts the next batch
-            int base_w = 0, base_i = 0, nb = 0;
-            if (lane == 0) pl.b_start[0] = 0;
-            for (;;) {
-                const unsigned over = __ballot_sync(0xffffffffu, valid && cw - base_w > kS16BufWords);
-                if (!over) break;
-                const int first = __ffs(over) - 1;
-                const int fw = __shfl_sync(0xffffffffu, cw - words, first), fi = __shfl_sync(0xffffffffu, ci - items, first);
-                const int fidx = __shfl_sync(0xffffffffu, idx, first);
-                // items of the batch that ends here = fi - (items before the batch); every lane >= first moves its base
-                const int prev_base_i = __shfl_sync(0xffffffffu, base_i, first), prev_base_w = __shfl_sync(0xffffffffu, base_w, first);
-                if (lane == 0) { pl.b_items[nb] = fi - prev_base_i; pl.b_words[nb] = fw - prev_base_w; pl.b_start[nb + 1] = fidx; }
-                nb++;
-                if (lane >= first) { base_w = fw; base_i = fi; }
-            }
-            if (valid) { pl.subs[idx].off = cw - words - base_w; pl.subs[idx].ibase = ci - items - base_i; }
-            const int tot_i = __shfl_sync(0xffffffffu, ci, 31), last_base_i = __shfl_sync(0xffffffffu, base_i, 31);
-            const int tot_w = __shfl_sync(0xffffffffu, cw, 31), last_base_w = __shfl_sync(0xffffffffu, base_w, 31);
-            if (lane == 0) { pl.b_items[nb] = tot_i - last_base_i; pl.b_words[nb] = tot_w - last_base_w; pl.b_start[nb + 1] = S; pl.n_batch = S ? nb + 1 : 0; pl.n_sub_all = S; }
-        } else {
-            int incl = cnt;
-            for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += v;
-            }
-            const int S = __shfl_sync(0xffffffffu, incl, 31);
-            if (lane == 0) pl.n_sub_all = S;
-            if (S <= kS16MaxSub && cnt > 0) {
-                const SadJob &j = jobs[ji];
-                for (int local = 0, xt = 0, st = 0; local < cnt; local++) {
-                    const int x0 = xt * 128, y0 = st * ny_cap;
-                    int       words;
-                    fill(pl.subs[incl - cnt + local], x0, y0, min(128, j.sa_w - x0), min(ny_cap, j.sa_h - y0), words);
-                    if (++st == nst) { st = 0; xt++; }
-                }
-            }
-            __syncwarp();
-            // batches: maximal runs of sub-windows that fit the buffer (lane 0; a handful of adds per sub-window)
-            if (lane == 0 && S <= kS16MaxSub) {
-                int nb = 0, used = 0, items = 0;
-                pl.b_start[0] = 0;
-                for (int i = 0; i < S; i++) {
-                    S16Sub   &u = pl.subs[i];
-                    const int w2 = u.nbox * u.brows * u.P;
-                    if (used + w2 > kS16BufWords) { pl.b_items[nb] = items; pl.b_words[nb] = used; pl.b_start[++nb] = i; used = 0; items = 0; }
-                    u.off = used; u.ibase = items;
-                    used += w2; items += u.items;
-                }
-                pl.b_items[nb] = items; pl.b_words[nb] = used; pl.b_start[++nb] = S;
-                pl.n_batch = nb;
-            }
-        }
-
-        __syncwarp();
-        if (lane == 0) {
-            pl.generic = (bw != 16 || rows != 8 || pl.n_sub_all > kS16MaxSub) ? 1 : 0;
-            if (pl.generic) {
-                // the work counter of partial blocks: rows x width of THIS block (the decomposition counted 8 x 16)
-                long long d = 0;
-                for (int q = 0; q < n; q++) {
-                    const SadJob &j = jobs[q];
-                    if (j.sa_w > 0 && j.sa_h > 0) {
-                        const bool skip = j.skip_line && bw == 16 && rows <= 16;
-                        d += (long long)j.sa_w * (skip ? (j.sa_h >> 1) : j.sa_h) * rows * bw;
-                        d -= (long long)j.sa_w * (j.skip_line ? (j.sa_h >> 1) : j.sa_h) * (8 * 16);
-                    }
-                }
-                s.px += (unsigned long long)d;
-            }
-        }
-        __syncwarp();
-    }
-}
 
 // mbarrier / TMA primitives (PTX ISA: mbarrier, cp.async.bulk.tensor)
 SVTME_D void mbar_init(uint32_t mbar, uint32_t count) {
@@ -957,179 +821,263 @@ SVTME_D void tma_load_2d(uint32_t dst, const void *tmap, int x, int y, uint32_t 
                  ::"r"(dst), "l"(tmap), "r"(x), "r"(y), "r"(mbar) : "memory");
 }
 
-// `mbar` is initialised once per CTA; `phase` counts the copy batches this CTA has waited for (the barrier's parity)
-__device__ __forceinline__ void sad16_block(const MeParams &p, const S16Maps &maps, uint32_t sbi, uint32_t mbar, uint32_t &phase, int tag) {
-    extern __shared__ __align__(128) uint32_t s16_win[];  // kS16BufWords
-    __shared__ __align__(16) S16Plan       pl;  // made by s16_plan in the light kernel in front of this one
-    __shared__ unsigned long long          job_key[kMaxSadJobs];
-    __shared__ uint32_t                    sub_key[kS16MaxSub];
-    PH_DECL
-    SbState  &s = p.states[sbi];
-    jobs_load_async<S16Plan, 1>(&pl, static_cast<const S16Plan *>(p.plans16) + sbi);
-    {
-        if (threadIdx.x < kMaxSadJobs) job_key[threadIdx.x] = ~0ull;
-        if (threadIdx.x < kS16MaxSub) sub_key[threadIdx.x] = ~0u;
+// The plan of one block's pre-HME / HME level-0 searches, made by the light kernel in front of the engine (s16_plan) and
+// handed over through HBM/L2; the engine's warps fold their minima into job_key, the light kernel behind it reads them.
+struct alignas(16) S16Plan {
+    unsigned long long job_key[kMaxSadJobs];  // (sad << 32 | y << 16 | x) minimum of each job's window, ~0: nothing found
+    int32_t n_sub_all, generic, pad_[2];      // generic: the block takes the generic path (picture edge, too many sub-windows)
+    S16Sub  subs[kS16MaxSub];
+};
+static_assert(sizeof(S16Plan) % 16 == 0 && offsetof(S16Plan, subs) % 16 == 0, "plans are copied as 16-byte words");
+
+// unit of the queue: block index << 8 | generic << 7 | sub-window index (generic: job slot)
+// one warp (threads 0 .. 31 of the CTA): lane = job.  Sub-windows = (column tile of <= 128 candidates) x (row strip)
+__device__ void s16_plan(const MeParams &p, SbState &s, S16Plan &pl) {
+    const int     lane = threadIdx.x & 31;
+    constexpr int n    = kMaxSadJobs;
+    static_assert(kMaxSadJobs == 32, "lane = job");
+    SadJob       *jobs = s.sad_jobs;
+    const int     bw = (int)(s.b64_w >> 2), rows = (int)((s.b64_h >> 2) >> 1);
+    pl.job_key[lane] = ~0ull;
+    if (lane == 0) { pl.n_sub_all = 0; pl.generic = 0; }
+    const int  ji    = lane;
+    const bool valid = jobs[ji].sa_w > 0 && jobs[ji].sa_h > 0;
+    int        cnt = 0, nst = 1, ny_cap = 16;
+    uint32_t   px = 0;
+    if (valid) {
+        const int W = jobs[ji].sa_w, H = jobs[ji].sa_h;
+        const int a16  = (int)((uintptr_t)jobs[ji].ref & 15);                          // the same for every tile (x0 = 128 t)
+        const int need = 4 * ((a16 >> 2) + (((a16 & 3) + min(128, W) + 3) >> 2)) + 16;  // bytes of the widest tile's rows
+        const int pmax = need <= 48 ? 12 : need <= 80 ? 20 : need <= 112 ? 28 : need <= 144 ? 36 : 44;  // its row pitch in words
+        // rows of a strip: whole boxes of 32 or of 8 rows that fit the buffer, minus the 14 rows below the last candidate
+        const int fit = kS16BufWords / pmax;
+        ny_cap = max((fit / 32) * 32, (fit / 8) * 8) - 14;
+        ny_cap = min(448, ny_cap) & ~3;
+        nst    = H <= ny_cap ? 1 : (H + ny_cap - 1) / ny_cap;
+        cnt    = ((W + 127) >> 7) * nst;
+        px     = (uint32_t)W * (uint32_t)(jobs[ji].skip_line ? (H >> 1) : H) * (8 * 16);
     }
-    constexpr int n = kMaxSadJobs;  // fixed slots, unused ones have empty windows
-    const S16Sub *subs = pl.subs;
-    const int    *b_start = pl.b_start, *b_items = pl.b_items, *b_words = pl.b_words;
-    // block geometry as in make_sad_job (me_control.cuh)
-    const DevPlane &cp = p.cur.lvl[2];
-    const uint32_t  aw = (uint32_t)((p.cur.lvl[0].width + 7) & ~7), ah = (uint32_t)((p.cur.lvl[0].height + 7) & ~7);
-    const uint32_t  org_x = (sbi % p.wb) * 64, org_y = (sbi / p.wb) * 64;
-    const uint32_t  b64_w = min(64u, aw - org_x), b64_h = min(64u, ah - org_y);
-    const int       bw = (int)(b64_w >> 2), rows = (int)((b64_h >> 2) >> 1);
-    const int       warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint8_t  *b0 = cp.org + (int64_t)(org_y >> 2) * cp.stride + (org_x >> 2);
-    uint32_t        sreg[8][4];  // rows 0, 2, .. 14 of the 16x16 block (same for every lane: broadcast loads), in flight early
-    if (bw == 16 && rows == 8) {
-#pragma unroll
-        for (int r = 0; r < 8; r++) {
-            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(b0 + (int64_t)(2 * r) * cp.stride));
-            sreg[r][0] = v.x; sreg[r][1] = v.y; sreg[r][2] = v.z; sreg[r][3] = v.w;
+    for (int o = 16; o; o >>= 1) px += __shfl_xor_sync(0xffffffffu, px, o);  // < 2^32: 32 jobs x 400 x 400 x 128
+    if (lane == 0 && px) s.px += (unsigned long long)px;  // the only writer of the shared-memory copy at this point
+    int incl = cnt;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    const int S = __shfl_sync(0xffffffffu, incl, 31);
+    if (S <= kS16MaxSub && cnt > 0) {
+        const SadJob &j = jobs[ji];
+        for (int local = 0, xt = 0, st = 0; local < cnt; local++) {
+            const int x0 = xt * 128, y0 = st * ny_cap, nx = min(128, j.sa_w - x0), ny = min(ny_cap, j.sa_h - y0);
+            S16Sub   &u = pl.subs[incl - cnt + local];
+            const int a16 = (int)((uintptr_t)(j.ref + x0) & 15), a = a16 & 3, wo = a16 >> 2;  // planes and rows are 16-byte aligned
+            const int ngroups = (a + nx + 3) >> 2, need = 4 * (wo + ngroups) + 16;  // a group reads 5 words: 4 candidates + 15 more bytes
+            const int cls = need <= 48 ? 0 : need <= 80 ? 1 : need <= 112 ? 2 : need <= 144 ? 3 : 4, P = 12 + 8 * cls;  // kS16BoxBytes[cls] / 4
+            const int nyp = (ny + 3) & ~3, nrows = nyp + 14;
+            // boxes of 32 rows when they fit the buffer (fewer copies), else of 8
+            const int hc = (nrows > 24 && ((nrows + 31) & ~31) * P <= kS16BufWords) ? 1 : 0;
+            const int brows = 8 << (2 * hc), nbox = (nrows + brows - 1) / brows;  // kS16BoxRows[hc]
+            // the sub-window's first byte inside the reference's padded sixteenth plane (rows of j.raw_stride bytes)
+            const DevPlane &rpl = p.refs[j.li][j.ri].lvl[2];
+            const int       offb = (int)((j.ref + (int64_t)y0 * j.raw_stride + x0) - (rpl.org - (int64_t)kPad16 * rpl.stride - kPad16));
+            const int       ty = offb / rpl.stride;
+            u.job = (int16_t)ji; u.x0 = (int16_t)x0; u.y0 = (int16_t)y0; u.nx = (int16_t)nx; u.ny = (int16_t)ny;
+            u.ngroups = (int16_t)ngroups; u.P = (int16_t)P; u.nbox = (int16_t)nbox; u.cls = (int16_t)(cls * kS16HClasses + hc); u.brows = (int16_t)brows;
+            u.a = (int16_t)a; u.wo = (int16_t)wo;
+            u.tx = offb - ty * rpl.stride - a16; u.ty = ty;
+            u.hsel  = j.skip_line ? 1 : 0;
+            u.ref   = (int16_t)(j.li * kMaxRefs + j.ri);
+            u.items = (nyp >> 2) * (j.skip_line ? 1 : 2) * ngroups;
+            u.inv_ng = __fdividef(1.0f, (float)ngroups) * 1.0000001f; u.inv_nx = __fdividef(1.0f, (float)nx) * 1.0000001f;
+            if (++st == nst) { st = 0; xt++; }
         }
     }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncthreads();
-    PH(tag, 0)  // plan fetch
-    const int S = pl.n_sub_all;
-    if (S == 0 && !pl.generic) return;  // every reference of the block took an early exit
-    if (pl.generic) {
-        // generic path: block words in shared memory, one warp per job, warp-private windows carved from the buffer
-        __shared__ __align__(16) SadJob jobs[kMaxSadJobs];
-        for (int i = threadIdx.x; i < (int)(sizeof(jobs) / 16); i += blockDim.x)
-            reinterpret_cast<uint4 *>(jobs)[i] = reinterpret_cast<const uint4 *>(s.sad_jobs)[i];
-        uint32_t *blk = s16_win;
-        const int nw = (bw + 3) >> 2;
-        for (int i = threadIdx.x; i < rows * nw; i += blockDim.x) {
-            const int      r = i / nw, c = i - r * nw;
-            const uint8_t *sp = b0 + (int64_t)r * (cp.stride * 2) + 4 * c;
-            uint32_t       a = 0;
-            for (int q = 0; q < min(4, bw - 4 * c); q++) a |= (uint32_t)sp[q] << (8 * q);
-            blk[r * 16 + c] = a;
-        }
-        __syncthreads();
-        for (int ji = warp; ji < n; ji += kStWarps) {
-            const SadJob &j = jobs[ji];
-            constexpr int kWin = (kS16BufWords - 1024) / kStWarps * 4;  // bytes per warp
-            uint8_t      *w8   = reinterpret_cast<uint8_t *>(s16_win + 1024) + warp * kWin;
-            if (bw == 16) warp_sad_job<4>(j, s.sad_jobs[ji], blk, w8, lane, rows, bw, 2, kWin);
-            else warp_sad_job<0>(j, s.sad_jobs[ji], blk, w8, lane, rows, bw, 2, kWin);
-        }
-        return;
-    }
-    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(s16_win);
-    const int nb = pl.n_batch;
-    if (threadIdx.x == 0 && nb > 0) mbar_expect_tx(mbar, 4u * (uint32_t)b_words[0]);  // the first batch's bytes
-    for (int bi = 0; bi < nb; bi++) {
-        const int s_lo = b_start[bi], s_hi = b_start[bi + 1];
-        // stage: one warp per sub-window, one lane per box.  Boxes may reach past the window (rounded-up
-        // rows, the box class's width) or past the plane (zero fill): never used.
-        for (int si = s_lo + warp; si < s_hi; si += kStWarps) {
-            const S16Sub  &u = subs[si];
-            const unsigned char *tm = maps.m[u.ref][u.cls];
-            const uint32_t box_bytes = 4u * (uint32_t)u.brows * (uint32_t)u.P, dst0 = sbase + 4u * (uint32_t)u.off;
-            if (lane < u.nbox) tma_load_2d(dst0 + (uint32_t)lane * box_bytes, tm, u.tx, u.ty + u.brows * lane, mbar);  // <= 4 boxes
-        }
-        PH(tag, 2)  // copy issue
-        mbar_wait(mbar, phase & 1u);
-        phase++;
-        PH(tag, 3)  // copy wait
-        // compute: flat item list of the batch, lane f takes items f, f + 128, ...
-        {
-            const int T = b_items[bi];
-            int       si = s_lo - 1, next_base = 0;  // items [ibase, next_base) belong to sub-window si
-            uint32_t  best = ~0u;
-            int       u_ng = 1, u_nx = 1, u_ny = 0, u_P = 1, u_a = 0, u_hsel = 0, u_ibase = 0;
-            float     u_inv_ng = 1.f;
-            const uint32_t *u_win = s16_win;
-            auto flush = [&]() {
-                if (best != ~0u) { atomicMin(&sub_key[si], best); best = ~0u; }
-            };
-            for (int f = threadIdx.x; f < T; f += kStThreads) {
-                if (f >= next_base) {
-                    flush();
-                    do { si++; next_base = subs[si].ibase + subs[si].items; } while (f >= next_base);
-                    const S16Sub &u = subs[si];
-                    u_ng = u.ngroups; u_nx = u.nx; u_ny = u.ny; u_P = u.P; u_a = u.a; u_hsel = u.hsel; u_ibase = u.ibase;
-                    u_inv_ng = u.inv_ng; u_win = s16_win + u.off + u.wo;
-                }
-                const int item = f - u_ibase;
-                const int kh = (int)(((float)item + 0.5f) * u_inv_ng), g = item - kh * u_ng;
-                const int k = u_hsel ? kh : (kh >> 1), h = u_hsel ? 1 : (kh & 1);
-                const int yy = 4 * k + h;
-                uint32_t  acc[2][4];
-#pragma unroll
-                for (int c = 0; c < 4; c++) acc[0][c] = acc[1][c] = 0;
-                const uint32_t *rowp = u_win + yy * u_P + g;  // window rows yy, yy + 2, .. yy + 16
-#pragma unroll
-                for (int rr = 0; rr < 9; rr++) {
-                    const uint32_t *rp = rowp + rr * (2 * u_P);
-                    uint32_t        w[5];
-#pragma unroll
-                    for (int c = 0; c < 5; c++) w[c] = rp[c];
-#pragma unroll
-                    for (int c = 0; c < 4; c++) {
-                        const uint32_t s0 = w[c], s1 = fsr(w[c], w[c + 1], 1), s2 = fsr(w[c], w[c + 1], 2), s3 = fsr(w[c], w[c + 1], 3);
-                        if (rr < 8) {
-                            const uint32_t sw = sreg[rr][c];
-                            acc[0][0] = sad4(s0, sw, acc[0][0]); acc[0][1] = sad4(s1, sw, acc[0][1]);
-                            acc[0][2] = sad4(s2, sw, acc[0][2]); acc[0][3] = sad4(s3, sw, acc[0][3]);
-                        }
-                        if (rr >= 1) {
-                            const uint32_t sw = sreg[rr - 1][c];
-                            acc[1][0] = sad4(s0, sw, acc[1][0]); acc[1][1] = sad4(s1, sw, acc[1][1]);
-                            acc[1][2] = sad4(s2, sw, acc[1][2]); acc[1][3] = sad4(s3, sw, acc[1][3]);
-                        }
-                    }
-                }
-                const int xb = 4 * g - u_a;
-#pragma unroll
-                for (int y2 = 0; y2 < 2; y2++) {
-                    const int  y = yy + 2 * y2;
-                    const bool yok = y < u_ny;
-                    const uint32_t ybase = (uint32_t)(y * u_nx + xb);
-#pragma unroll
-                    for (int c = 0; c < 4; c++)
-                        if (yok && (uint32_t)(xb + c) < (uint32_t)u_nx) best = min(best, acc[y2][c] * 65536u + ybase + (uint32_t)c);
+    if (lane == 0) {
+        pl.n_sub_all = S;
+        pl.generic   = (bw != 16 || rows != 8 || S > kS16MaxSub) ? 1 : 0;
+        if (pl.generic) {
+            // the work counter of partial blocks: rows x width of THIS block (the sum above counted 8 x 16)
+            long long d = 0;
+            for (int q = 0; q < n; q++) {
+                const SadJob &j = jobs[q];
+                if (j.sa_w > 0 && j.sa_h > 0) {
+                    const bool skip = j.skip_line && bw == 16 && rows <= 16;
+                    d += (long long)j.sa_w * (skip ? (j.sa_h >> 1) : j.sa_h) * rows * bw;
+                    d -= (long long)j.sa_w * (j.skip_line ? (j.sa_h >> 1) : j.sa_h) * (8 * 16);
                 }
             }
-            flush();
-        }
-        PH(tag, 4)  // search (this thread)
-        if (threadIdx.x == 0 && bi + 1 < nb) mbar_expect_tx(mbar, 4u * (uint32_t)b_words[bi + 1]);
-        __syncthreads();  // the windows are reused by the next batch
-        PH(tag, 5)  // waiting for the other warps
-    }
-    // sub-window minima -> job keys (sad, y, x): raster order inside the job decides ties between sub-windows
-    if ((int)threadIdx.x < S && sub_key[threadIdx.x] != ~0u) {
-        const S16Sub  &u = subs[threadIdx.x];
-        const uint32_t key = sub_key[threadIdx.x], sad = key >> 16, ord = key & 0xffffu;
-        const uint32_t y = (uint32_t)(((float)ord + 0.5f) * u.inv_nx), x = ord - y * (uint32_t)u.nx;
-        atomicMin(&job_key[u.job], ((unsigned long long)sad << 32) | ((uint32_t)(u.y0 + y) << 16) | (uint32_t)(u.x0 + x));
-    }
-    __syncthreads();
-    if ((int)threadIdx.x < n) {
-        const unsigned long long key = job_key[threadIdx.x];
-        if (key != ~0ull && (uint32_t)(key >> 32) < 0xffffffu) {  // strict '<' against the 0xffffff start value
-            SadJob &jo = s.sad_jobs[threadIdx.x];
-            jo.found = 1; jo.best_sad = (uint32_t)(key >> 32);
-            jo.by = (int16_t)((key >> 16) & 0xffff); jo.bx = (int16_t)(key & 0xffff);
+            s.px += (unsigned long long)d;
         }
     }
-    PH(tag, 6)  // results to the block state
+    __syncwarp();
 }
-__global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_constant__ MeParams p, const __grid_constant__ S16Maps maps, int tag) {
+
+// The plan goes to HBM/L2 and its units into the picture's queue (counter pair `qi`: [count, head]) for the engine kernel
+// that follows.  One warp.
+__device__ __forceinline__ void s16_plan_store(const MeParams &p, const SbState &s, const S16Plan &pl, uint32_t sbi, int qi) {
+    const int    lane = threadIdx.x & 31;
+    const uint4 *l = reinterpret_cast<const uint4 *>(&pl);
+    uint4       *g = reinterpret_cast<uint4 *>(static_cast<S16Plan *>(p.plans16) + sbi);
+    const int    n_used = pl.generic ? 0 : pl.n_sub_all;
+    const int    vecs = (int)(offsetof(S16Plan, subs) + (size_t)n_used * sizeof(S16Sub)) / 16;
+    for (int i = lane; i < vecs; i += 32) g[i] = l[i];
+    // units: sub-windows, or (generic blocks) job slots with a non-empty window
+    const bool     gjob = pl.generic && s.sad_jobs[lane].sa_w > 0 && s.sad_jobs[lane].sa_h > 0;
+    const unsigned gm   = __ballot_sync(0xffffffffu, gjob);
+    const int      nu   = pl.generic ? __popc(gm) : pl.n_sub_all;
+    uint32_t       base = 0;
+    if (lane == 0 && nu) base = atomicAdd(&p.q_ctr[2 * qi], (uint32_t)nu);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (pl.generic) {
+        if (gjob) p.q_units[base + __popc(gm & ((1u << lane) - 1u))] = (sbi << 8) | 128u | (uint32_t)lane;
+    } else {
+        for (int i = lane; i < nu; i += 32) p.q_units[base + i] = (sbi << 8) | (uint32_t)i;
+    }
+}
+
+// the minima of a block's jobs, as the engine's warps left them in the plan -> the job table (control part of the
+// state, in shared memory): what st_sad_kernel's warps write directly.  One warp, lane = job.
+__device__ __forceinline__ void s16_keys(const MeParams &p, SbState &s, uint32_t sbi) {
+    const int      lane = threadIdx.x & 31;
+    const S16Plan &pl = static_cast<const S16Plan *>(p.plans16)[sbi];
+    if (pl.generic) return;  // the generic path has written the job results itself
+    const unsigned long long key = pl.job_key[lane];
+    if (key != ~0ull && (uint32_t)(key >> 32) < 0xffffffu) {  // strict '<' against the 0xffffff start value
+        SadJob &jo = s.sad_jobs[lane];
+        jo.found = 1; jo.best_sad = (uint32_t)(key >> 32);
+        jo.by = (int16_t)((key >> 16) & 0xffff); jo.bx = (int16_t)(key & 0xffff);
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_constant__ MeParams p, const __grid_constant__ S16Maps maps, int qi, int tag) {
     PDL_ENTRY();
-    __shared__ __align__(8) unsigned long long mbar_store;
-    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&mbar_store);
-    if (threadIdx.x == 0) mbar_init(mbar, 1);
-    __syncthreads();
-    uint32_t       phase = 0;
-    const uint32_t n_sb = p.wb * p.hb;
-    for (uint32_t sbi = blockIdx.x; sbi < n_sb; sbi += gridDim.x) {
-        sad16_block(p, maps, sbi, mbar, phase, tag);
-        __syncthreads();
+    extern __shared__ __align__(128) uint32_t s16_win_all[];  // kStWarps x kS16BufWords
+    __shared__ __align__(8) unsigned long long mbar_store[kStWarps];
+    const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t      *win = s16_win_all + warp * kS16BufWords;
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(win);
+    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&mbar_store[warp]);
+    if (lane == 0) mbar_init(mbar, 1);
+    __syncwarp();
+    uint32_t        phase = 0;
+    uint32_t       *ctr = p.q_ctr + 2 * qi;
+    const uint32_t  count = ctr[0];
+    const DevPlane &cp = p.cur.lvl[2];
+    S16Plan        *plans = static_cast<S16Plan *>(p.plans16);
+    uint32_t        last_sb = 0xffffffffu;
+    uint32_t        sreg[8][4];  // rows 0, 2, .. 14 of the block's 16x16 sixteenth-plane block (the same for every lane)
+    (void)tag;
+    for (;;) {
+        uint32_t ui = 0;
+        if (lane == 0) ui = atomicAdd(&ctr[1], 1u);
+        ui = __shfl_sync(0xffffffffu, ui, 0);
+        if (ui >= count) break;
+        const uint32_t unit = p.q_units[ui], sbi = unit >> 8, idx = unit & 127u;
+        SbState       &s = p.states[sbi];
+        const uint32_t org_x = (sbi % p.wb) * 64, org_y = (sbi / p.wb) * 64;
+        const uint8_t *b0 = cp.org + (int64_t)(org_y >> 2) * cp.stride + (org_x >> 2);
+        if (unit & 128u) {
+            // generic path (blocks cut by the picture edge, or with more sub-windows than a plan holds): one job
+            const uint32_t aw = (uint32_t)((p.cur.lvl[0].width + 7) & ~7), ah = (uint32_t)((p.cur.lvl[0].height + 7) & ~7);
+            const uint32_t b64_w = min(64u, aw - org_x), b64_h = min(64u, ah - org_y);
+            const int      bw = (int)(b64_w >> 2), rows = (int)((b64_h >> 2) >> 1), nw = (bw + 3) >> 2;
+            uint32_t      *blk = win;  // block words, rows of 16
+            for (int i = lane; i < rows * nw; i += 32) {
+                const int      r = i / nw, c = i - r * nw;
+                const uint8_t *sp = b0 + (int64_t)r * (cp.stride * 2) + 4 * c;
+                uint32_t       a = 0;
+                for (int q = 0; q < min(4, bw - 4 * c); q++) a |= (uint32_t)sp[q] << (8 * q);
+                blk[r * 16 + c] = a;
+            }
+            __syncwarp();
+            const SadJob  j = s.sad_jobs[idx];
+            constexpr int kWin = (kS16BufWords - 128) * 4;  // bytes behind the block words
+            uint8_t      *w8 = reinterpret_cast<uint8_t *>(win + 128);
+            if (bw == 16) warp_sad_job<4>(j, s.sad_jobs[idx], blk, w8, lane, rows, bw, 2, kWin);
+            else warp_sad_job<0>(j, s.sad_jobs[idx], blk, w8, lane, rows, bw, 2, kWin);
+            __syncwarp();
+            last_sb = 0xffffffffu;
+            continue;
+        }
+        // the sub-window's descriptor: three broadcast loads
+        S16Sub u;
+        {
+            const uint4 *up = reinterpret_cast<const uint4 *>(&plans[sbi].subs[idx]);
+            uint4       *ud = reinterpret_cast<uint4 *>(&u);
+            ud[0] = up[0]; ud[1] = up[1]; ud[2] = up[2];
+        }
+        if (lane == 0) mbar_expect_tx(mbar, 4u * (uint32_t)(u.nbox * u.brows * u.P));
+        __syncwarp();
+        {
+            const unsigned char *tm = maps.m[u.ref][u.cls];
+            const uint32_t       box_bytes = 4u * (uint32_t)u.brows * (uint32_t)u.P;
+            if (lane < u.nbox) tma_load_2d(sbase + (uint32_t)lane * box_bytes, tm, u.tx, u.ty + u.brows * lane, mbar);  // <= 9 boxes
+        }
+        if (sbi != last_sb) {
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4 *>(b0 + (int64_t)(2 * r) * cp.stride));
+                sreg[r][0] = v.x; sreg[r][1] = v.y; sreg[r][2] = v.z; sreg[r][3] = v.w;
+            }
+            last_sb = sbi;
+        }
+        mbar_wait(mbar, phase & 1u);
+        phase++;
+        uint32_t        best = ~0u;
+        const int       u_ng = u.ngroups, u_nx = u.nx, u_ny = u.ny, u_P = u.P, u_a = u.a, u_hsel = u.hsel;
+        const float     u_inv_ng = u.inv_ng;
+        const uint32_t *u_win = win + u.wo;
+        for (int item = lane; item < u.items; item += 32) {
+            const int kh = (int)(((float)item + 0.5f) * u_inv_ng), g = item - kh * u_ng;
+            const int k = u_hsel ? kh : (kh >> 1), h = u_hsel ? 1 : (kh & 1);
+            const int yy = 4 * k + h;
+            uint32_t  acc[2][4];
+#pragma unroll
+            for (int c = 0; c < 4; c++) acc[0][c] = acc[1][c] = 0;
+            const uint32_t *rowp = u_win + yy * u_P + g;  // window rows yy, yy + 2, .. yy + 16
+#pragma unroll
+            for (int rr = 0; rr < 9; rr++) {
+                const uint32_t *rp = rowp + rr * (2 * u_P);
+                uint32_t        w[5];
+#pragma unroll
+                for (int c = 0; c < 5; c++) w[c] = rp[c];
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    const uint32_t s0 = w[c], s1 = fsr(w[c], w[c + 1], 1), s2 = fsr(w[c], w[c + 1], 2), s3 = fsr(w[c], w[c + 1], 3);
+                    if (rr < 8) {
+                        const uint32_t sw = sreg[rr][c];
+                        acc[0][0] = sad4(s0, sw, acc[0][0]); acc[0][1] = sad4(s1, sw, acc[0][1]);
+                        acc[0][2] = sad4(s2, sw, acc[0][2]); acc[0][3] = sad4(s3, sw, acc[0][3]);
+                    }
+                    if (rr >= 1) {
+                        const uint32_t sw = sreg[rr - 1][c];
+                        acc[1][0] = sad4(s0, sw, acc[1][0]); acc[1][1] = sad4(s1, sw, acc[1][1]);
+                        acc[1][2] = sad4(s2, sw, acc[1][2]); acc[1][3] = sad4(s3, sw, acc[1][3]);
+                    }
+                }
+            }
+            const int xb = 4 * g - u_a;
+#pragma unroll
+            for (int y2 = 0; y2 < 2; y2++) {
+                const int  y = yy + 2 * y2;
+                const bool yok = y < u_ny;
+                const uint32_t ybase = (uint32_t)(y * u_nx + xb);
+#pragma unroll
+                for (int c = 0; c < 4; c++)
+                    if (yok && (uint32_t)(xb + c) < (uint32_t)u_nx) best = min(best, acc[y2][c] * 65536u + ybase + (uint32_t)c);
+            }
+        }
+        // the sub-window's minimum (sad << 16 | raster index) -> the job's key (sad, y, x): raster order inside the job
+        // decides ties between sub-windows
+#pragma unroll
+        for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+        if (lane == 0 && best != ~0u) {
+            const uint32_t sad = best >> 16, ord = best & 0xffffu;
+            const uint32_t y = (uint32_t)(((float)ord + 0.5f) * u.inv_nx), x = ord - y * (uint32_t)u.nx;
+            atomicMin(&plans[sbi].job_key[u.job], ((unsigned long long)sad << 32) | ((uint32_t)(u.y0 + y) << 16) | (uint32_t)(u.x0 + x));
+        }
+        __syncwarp();  // every lane is done with the window before the next unit's copy lands in it
     }
 }
 
@@ -1145,6 +1093,7 @@ __global__ void __launch_bounds__(kStThreads, 6) st_sad16_kernel(const __grid_co
 // Minima: 32-bit keys (sad << 12 | candidate index inside the <= 64 x 64 sub-window); 32x32 / 64x64 sums by a
 // transposing butterfly (8 shuffles for 8 candidates).
 constexpr int kFpBufWords = 8 * 1024;  // 44 KB of windows per CTA
+__device__ __forceinline__ bool fp_job_small(const FpJob &j, int &a, int &ngroups, int &P, int &plane);
 constexpr int kFpMaxSub   = 12;
 struct FpSub {
     int16_t job, x0, y0, nx, ny, a, ngroups, P;
@@ -1157,7 +1106,7 @@ struct FpSub {
 // each reading the plane of parity (e + half) & 1, and one exchange over lane ^ 16 completes the sums: half h ends up
 // with the four candidates of row 4k + e + 2h.
 template <bool FULL>
-__device__ __forceinline__ void fp_sub_block(const MeParams &p, uint32_t sbi) {
+__device__ __forceinline__ void fp_sub_block(const MeParams &p, uint32_t sbi, int big_only) {
     extern __shared__ __align__(16) uint32_t fp_win[];  // kFpBufWords
     __shared__ uint32_t               sub_key[kFpMaxSub][kPus];  // (sad << 12 | candidate) minima of the batch's sub-windows
     __shared__ unsigned long long     fp_key[kMaxFpJobs][kPus];
@@ -1187,6 +1136,16 @@ __device__ __forceinline__ void fp_sub_block(const MeParams &p, uint32_t sbi) {
         }
     }
     constexpr uint32_t kPxPerCand = FULL ? 64u * 64u : 64u * 32u;
+    if (big_only) {
+        // the jobs st_fp_warp_kernel has searched (small windows) are not this kernel's
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x < kMaxFpJobs && jobs[threadIdx.x].w > 0 && jobs[threadIdx.x].h > 0) {
+            int a, ng, P, plane;
+            if (fp_job_small(jobs[threadIdx.x], a, ng, P, plane)) { jobs[threadIdx.x].w = 0; jobs[threadIdx.x].h = 0; }
+        }
+        __syncthreads();
+    }
     if (!jobs_wait_any(n, [&](int i) { return jobs[i].w > 0 && jobs[i].h > 0; })) return;
     // the running best SADs this thread will compare against at the end: requested now, needed last
     constexpr int kFoldPer = (kMaxFpJobs * kPus + kStThreads - 1) / kStThreads;
@@ -1497,24 +1456,226 @@ __device__ __forceinline__ void fp_sub_block(const MeParams &p, uint32_t sbi) {
     }
     PH(0, 7)  // results to the block state
 }
+// big_only: behind st_fp_warp_kernel, for the jobs that kernel left (counter word `qi` != 0 when there are any)
 template <bool FULL>
-__global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_constant__ MeParams p) {
+__global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_constant__ MeParams p, int big_only, int qi) {
     PDL_ENTRY();
+    if (big_only && p.q_ctr[2 * qi] == 0) return;
     const uint32_t n_sb = p.wb * p.hb;
     for (uint32_t sbi = blockIdx.x; sbi < n_sb; sbi += gridDim.x) {
-        fp_sub_block<FULL>(p, sbi);
+        fp_sub_block<FULL>(p, sbi, big_only);
         __syncthreads();
     }
 }
 
-// the plan goes to HBM/L2 for the engine kernel that follows (all threads of the light CTA)
-__device__ __forceinline__ void s16_plan_store(const MeParams &p, const S16Plan &pl, uint32_t sbi) {
-    const uint4 *l = reinterpret_cast<const uint4 *>(&pl);
-    uint4       *g = reinterpret_cast<uint4 *>(static_cast<S16Plan *>(p.plans16) + sbi);
-    // header + batch tables always; sub-windows up to the number in use
-    const int n_used = pl.generic ? 0 : pl.n_sub_all;
-    const int vecs = (int)(offsetof(S16Plan, subs) + (size_t)n_used * sizeof(S16Sub) + 15) / 16;
-    for (int i = threadIdx.x; i < vecs; i += blockDim.x) g[i] = l[i];
+// ---- the same search for SMALL windows (what preset M6 and faster produce: a few dozen candidates per reference), one
+// WARP per 64x64 block.  The CTA-wide kernel above spends two thirds of a CTA's life outside the search when the windows
+// are small (job fetch, plan, copy issue, key fold, results: phases of one warp with the others at a barrier); here a
+// warp owns its block -- jobs, window buffer, minima, results -- and never meets a barrier, so the four warps of a CTA
+// (four blocks) overlap each other's copies and searches.  A job whose window does not fit the warp's buffer is left to
+// the CTA-wide kernel, which then runs behind this one for those jobs only (`big` flag in the step's counter pair).
+constexpr int kFpWBufWords = 3584;  // 14 KB per warp: windows up to 64 x 32 candidates
+#ifndef SVTME_FPW_SPLIT
+#define SVTME_FPW_SPLIT 2
+#endif
+__device__ __forceinline__ bool fp_job_small(const FpJob &j, int &a, int &ngroups, int &P, int &plane) {
+    a       = (int)((uintptr_t)j.ref & 3);
+    ngroups = (a + j.w + 3) >> 2;
+    P       = (ngroups + 16 + 3) & ~3;
+    const int nyp = (j.h + 3) & ~3, PR = ((nyp + 62 + 7) & ~7) >> 1;  // staged in groups of 8 rows
+    plane   = PR * P + (PR >> 3) + 1;
+    plane   = ((plane + 15) & ~31) + 16;  // = 16 mod 32
+    return j.w <= 64 && j.h <= 64 && 2 * plane <= kFpWBufWords;
+}
+
+__global__ void __launch_bounds__(kStThreads, 4) st_fp_warp_kernel(const __grid_constant__ MeParams p, int qi) {
+    PDL_ENTRY();
+    extern __shared__ __align__(16) uint32_t fpw_all[];  // kStWarps x kFpWBufWords
+    const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // SVTME_FPW_SPLIT warps share a block: warp `part` takes every SVTME_FPW_SPLIT-th job of it
+    constexpr int  kSplit = SVTME_FPW_SPLIT;
+    const uint32_t sbi = blockIdx.x * (kStWarps / kSplit) + warp / kSplit;
+    const int      part = warp % kSplit;
+    if (sbi >= p.wb * p.hb) return;
+    uint32_t      *win = fpw_all + warp * kFpWBufWords;
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(win);
+    SbState       &s = p.states[sbi];
+    const int      b = lane & 15, half = lane >> 4;
+    const int      bx = ((b >> 2) & 1) * 2 + (b & 1), by = (b >> 3) * 2 + ((b >> 1) & 1);
+    uint32_t       sreg[8][4];  // every second row of the lane's 16x16 block, straight from the source picture
+    {
+        const DevPlane &f   = p.cur.lvl[0];
+        const uint8_t  *sp0 = f.org + (int64_t)((sbi / p.wb) * 64 + 16 * by) * f.stride + (sbi % p.wb) * 64 + 16 * bx;
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(sp0 + (int64_t)(2 * r) * f.stride));
+            sreg[r][0] = v.x; sreg[r][1] = v.y; sreg[r][2] = v.z; sreg[r][3] = v.w;
+        }
+    }
+    uint32_t px = 0;
+    bool     any_big = false;
+    int      ordinal = 0;
+    for (int ji = 0; ji < kMaxFpJobs; ji++) {
+        const FpJob j = s.fp_jobs[ji];  // the same for every lane: broadcast loads
+        if (j.w <= 0 || j.h <= 0) continue;
+        int a, ngroups, P, plane;
+        if (!fp_job_small(j, a, ngroups, P, plane)) { any_big = true; continue; }
+        if ((ordinal++) % kSplit != part) continue;
+        px += (uint32_t)(j.w * j.h) * (64u * 32u);
+        const int nx = j.w, ny = j.h, nyp = (ny + 3) & ~3;
+        uint32_t *bs = s.best_sad[j.li][j.ri], *bm = s.best_mv[j.li][j.ri];
+        // the running bests this lane will compare against at the end: requested now, needed last
+        const int      pu8 = 21 + 4 * b + 2 * half;
+        const uint32_t prev8a = bs[pu8], prev8b = bs[pu8 + 1], prev16 = bs[5 + b], prev32 = bs[1 + (b >> 2)], prev64 = bs[0];
+        // stage: lane = word of the row; rows go in groups of 8 (inside a group the skew (i >> 3) is constant).  The rows
+        // past the window (< 8 + 3) are inside the plane's physical padding (96 rows against the 72 a search uses).
+        {
+            const int      ngrp = (nyp + 62 + 7) >> 3, nwords = ngroups + 16, raw = j.ref_stride;
+            const uint8_t *g0 = j.ref - a;
+            __syncwarp();  // the previous job's window is no longer read
+            for (int wd = lane; wd < nwords; wd += 32) {
+                const uint8_t *g = g0 + 4 * wd;
+                for (int G = 0; G < ngrp; G++) {
+                    // rows 8G + r8: plane r8 & 1, plane row i = 4G + (r8 >> 1), skew i >> 3 = G >> 1
+                    const uint32_t sa0 = sbase + 4u * (uint32_t)((4 * G) * P + (G >> 1) + wd);
+#pragma unroll
+                    for (int r8 = 0; r8 < 8; r8++, g += raw) {
+                        CHECK_SRC(p, 0, j.li, j.ri, g, 4, 4);
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa0 + 4u * (uint32_t)((r8 & 1) * plane + (r8 >> 1) * P)), "l"(g));
+                    }
+                }
+            }
+            asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+            __syncwarp();
+        }
+        // search: a round = one group of 4 x-adjacent candidates for the candidate rows 4k .. 4k + 3 (half-warp `half` takes
+        // rows 4k + half and 4k + half + 2); the rounds of the window one after the other
+        uint32_t        best8[4] = {~0u, ~0u, ~0u, ~0u}, best16 = ~0u, best32 = ~0u, best64 = ~0u;
+        const uint32_t *wbase = win + 4 * bx + (8 * by) * P + by + half * plane;
+        const int       rounds = (nyp >> 2) * ngroups;
+        for (int local = 0, k = 0, g = 0; local < rounds; local++) {
+            const int  yy = 4 * k + half, i0 = 2 * k;
+            const bool active = yy < ny;
+            uint32_t   acc[2][4][4];
+#pragma unroll
+            for (int y2 = 0; y2 < 2; y2++)
+#pragma unroll
+                for (int c = 0; c < 4; c++) acc[y2][c][0] = acc[y2][c][1] = acc[y2][c][2] = acc[y2][c][3] = 0;
+            if (active) {
+                const uint32_t *rowp = wbase + g;
+#pragma unroll
+                for (int rr = 0; rr < 9; rr++) {
+                    const int       i  = i0 + rr;  // + 8 * by is in wbase, and (i + 8 by) >> 3 = by + (i >> 3)
+                    const uint32_t *rp = rowp + i * P + (i >> 3);
+                    uint32_t        w[5];
+#pragma unroll
+                    for (int c = 0; c < 5; c++) w[c] = rp[c];
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const uint32_t s0 = w[c], s1 = fsr(w[c], w[c + 1], 1), s2 = fsr(w[c], w[c + 1], 2), s3 = fsr(w[c], w[c + 1], 3);
+                        if (rr < 8) {
+                            const int      q  = (rr >> 2) * 2 + (c >> 1);
+                            const uint32_t sw = sreg[rr][c];
+                            acc[0][0][q] = sad4(s0, sw, acc[0][0][q]); acc[0][1][q] = sad4(s1, sw, acc[0][1][q]);
+                            acc[0][2][q] = sad4(s2, sw, acc[0][2][q]); acc[0][3][q] = sad4(s3, sw, acc[0][3][q]);
+                        }
+                        if (rr >= 1) {
+                            const int      q  = ((rr - 1) >> 2) * 2 + (c >> 1);
+                            const uint32_t sw = sreg[rr - 1][c];
+                            acc[1][0][q] = sad4(s0, sw, acc[1][0][q]); acc[1][1][q] = sad4(s1, sw, acc[1][1][q]);
+                            acc[1][2][q] = sad4(s2, sw, acc[1][2][q]); acc[1][3][q] = sad4(s3, sw, acc[1][3][q]);
+                        }
+                    }
+                }
+            }
+            const int xb = 4 * g - a;
+            uint32_t  s16[8];
+#pragma unroll
+            for (int y2 = 0; y2 < 2; y2++)
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    const int      xx = xb + c, y = yy + 2 * y2;
+                    const bool     valid = y < ny && xx >= 0 && xx < nx;
+                    const uint32_t ord = (uint32_t)(y * nx + xx);  // < 4096
+                    uint32_t       t = 0;
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        if (valid) best8[q] = min(best8[q], acc[y2][c][q] * 4096u + ord);
+                        t += acc[y2][c][q];
+                    }
+                    if (valid) best16 = min(best16, t * 4096u + ord);
+                    s16[y2 * 4 + c] = t;
+                }
+            // transposing butterfly over the 4 lanes of a 32x32 block, then over the 4 blocks: candidate e = y2 * 4 + c
+            uint32_t t4[4], t2[2], t1;
+            {
+                const bool up = b & 1;  // keeps y2 = b0
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const uint32_t send = up ? s16[i] : s16[4 + i], keep = up ? s16[4 + i] : s16[i];
+                    t4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+                }
+            }
+            {
+                const bool up = b & 2;  // keeps c >> 1 = b1
+#pragma unroll
+                for (int i = 0; i < 2; i++) {
+                    const uint32_t send = up ? t4[i] : t4[2 + i], keep = up ? t4[2 + i] : t4[i];
+                    t2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+                }
+            }
+            const int  y32 = yy + 2 * (b & 1), x32 = xb + (b & 2);
+            const bool yok = y32 < ny;
+#pragma unroll
+            for (int i = 0; i < 2; i++) {
+                const int xx = x32 + i;
+                if (yok && xx >= 0 && xx < nx) best32 = min(best32, t2[i] * 4096u + (uint32_t)(y32 * nx + xx));
+            }
+            {
+                const bool     up   = b & 4;  // keeps c & 1 = b2
+                const uint32_t send = up ? t2[0] : t2[1], keep = up ? t2[1] : t2[0];
+                t1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+            }
+            t1 += __shfl_xor_sync(0xffffffffu, t1, 8);
+            {
+                const int xx = x32 + ((b >> 2) & 1);
+                if (yok && xx >= 0 && xx < nx) best64 = min(best64, t1 * 4096u + (uint32_t)(y32 * nx + xx));
+            }
+            if (++g == ngroups) { g = 0; k++; }
+        }
+        // the window's minima: the two half-warps hold different candidate rows; the 32x32 / 64x64 sums of different
+        // candidates sit in different lanes of the block group.  Keys are (sad << 12 | raster index): min = first in raster order
+#pragma unroll
+        for (int q = 0; q < 4; q++) best8[q] = min(best8[q], __shfl_xor_sync(0xffffffffu, best8[q], 16));
+        best16 = min(best16, __shfl_xor_sync(0xffffffffu, best16, 16));
+        best32 = min(best32, __shfl_xor_sync(0xffffffffu, best32, 1));
+        best32 = min(best32, __shfl_xor_sync(0xffffffffu, best32, 2));
+        best32 = min(best32, __shfl_xor_sync(0xffffffffu, best32, 16));
+        best64 = min(best64, __shfl_xor_sync(0xffffffffu, best64, 1));
+        best64 = min(best64, __shfl_xor_sync(0xffffffffu, best64, 2));
+        best64 = min(best64, __shfl_xor_sync(0xffffffffu, best64, 4));
+        best64 = min(best64, __shfl_xor_sync(0xffffffffu, best64, 16));
+        // fold into the running best of the reference (strict '<': earlier results win ties); SAD doubled (sub-sampled rows)
+        auto fold = [&](int pu, uint32_t key, uint32_t prev) {
+            if (key == ~0u) return;
+            const uint32_t sad = (key >> 12) << 1, ord = key & 4095u;
+            if (sad < prev) {
+                const uint32_t y = ord / (uint32_t)nx, x = ord - y * (uint32_t)nx;
+                bs[pu] = sad;
+                bm[pu] = ((uint32_t)((int32_t)y + j.yo) << 16) | (uint16_t)((int32_t)x + j.xo);
+            }
+        };
+        fold(pu8, half ? best8[2] : best8[0], prev8a);
+        fold(pu8 + 1, half ? best8[3] : best8[1], prev8b);
+        if (half == 0) fold(5 + b, best16, prev16);
+        if (half == 0 && (b & 3) == 0) fold(1 + (b >> 2), best32, prev32);
+        if (lane == 0) fold(0, best64, prev64);
+    }
+    for (int o = 16; o; o >>= 1) any_big |= (bool)__shfl_xor_sync(0xffffffffu, (int)any_big, o);  // (uniform anyway)
+    if (lane == 0) {
+        if (px) atomicAdd(&s.px, (unsigned long long)px);
+        if (any_big) atomicOr(&p.q_ctr[2 * qi], 1u);  // the CTA-wide kernel behind this one has work
+    }
 }
 
 // The tail of a kernel: steps [first, first + count) of the program -- control steps (warp 0) and the light
@@ -1522,14 +1683,18 @@ __device__ __forceinline__ void s16_plan_store(const MeParams &p, const S16Plan 
 // back to HBM/L2.  Called by every thread of the CTA after a barrier; one copy of this code serves all kernels.
 __device__ __forceinline__ void run_tail(const MeParams &p, unsigned char *head, S16Plan &plan, int first, int count, int finish) {
     SbState &s = *reinterpret_cast<SbState *>(head);
-    bool     planned = false;
     for (int i = first; i < first + count; i++) {
         const Step st = p.prog[i];
         if (st.kind == STEP_CTL) {
             if (threadIdx.x < 32) ctl_step(p, s, st.op, st.arg);
         } else if (st.kind == STEP_PLAN16) {
-            if (threadIdx.x < 32) s16_plan(p, s, plan);
-            planned = true;
+            // the sixteenth-plane jobs just made -> sub-windows; the plan and its units go to HBM/L2 for the engine
+            if (threadIdx.x < 32) {
+                s16_plan(p, s, plan);
+                s16_plan_store(p, s, plan, blockIdx.x, i);
+            }
+        } else if (st.kind == STEP_KEYS16) {
+            if (threadIdx.x < 32) s16_keys(p, s, blockIdx.x);
         } else if (st.kind == STEP_PROBE) {
             probe_engine(p, s);
         } else {
@@ -1543,7 +1708,6 @@ __device__ __forceinline__ void run_tail(const MeParams &p, unsigned char *head,
         if (threadIdx.x == 0 && p.px_counter) atomicAdd(p.px_counter, s.px);
     }
     head_store(head, s.home);
-    if (planned) s16_plan_store(p, plan, blockIdx.x);  // (a barrier follows every step)
 }
 
 // The steps between two search engines (and the results behind the last one): a light kernel, ONE WARP per block --
@@ -1587,8 +1751,9 @@ __global__ void __launch_bounds__(kStThreads) st_init_kernel(const __grid_consta
 // results (candidates, statistics) in the tail of the last kernel: 7 launches per picture at preset M6 where the first
 // version of this pipeline needed 21.
 cudaError_t staged_set_attributes() {  // per device: call with the device current (svtme_init)
-    cudaError_t e = cudaFuncSetAttribute(st_sad16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kS16BufWords * 4);
+    cudaError_t e = cudaFuncSetAttribute(st_sad16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStWarps * kS16BufWords * 4);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_sub_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpBufWords * 4);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStWarps * kFpWBufWords * 4);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(st_fp_sub_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpBufWords * 4);
     return e;
 }
@@ -1649,16 +1814,32 @@ cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, int
             else if (lvl == 0 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<16, 32>, 0, p, lvl); mark("rows16"); }
             else if (lvl == 2 && p.k.hme_search_method == 0) {
                 // (diagnostics) 1: pre-HME windows, 2: HME level-0 quadrants -- by the control step that made the jobs
-                int tag = 2;
-                for (int q = i - 1; q >= 0; q--)
+                int tag = 2, qi = -1;
+                for (int q = i - 1; q >= 0; q--) {
+                    if (qi < 0 && p.prog[q].kind == STEP_PLAN16) qi = q;  // the plan step in front of this engine names the unit queue
                     if (p.prog[q].kind == STEP_CTL && (p.prog[q].op == C_PREHME_MAKE || p.prog[q].op == C_L0_MAKE)) { tag = p.prog[q].op == C_PREHME_MAKE ? 1 : 2; break; }
-                launch(st_sad16_kernel, (size_t)kS16BufWords * 4, p, maps, tag); mark(tag == 1 ? "prehme" : "hme0");
+                }
+                // persistent warps that pull units from the queue: every CTA slot of the GPU, whatever the picture size
+#ifdef SVTME_DIAG
+                static const int s16_ctas = getenv("SVTME_S16_CTAS") ? atoi(getenv("SVTME_S16_CTAS")) : SVTME_S16_CTAS;
+#else
+                constexpr int s16_ctas = SVTME_S16_CTAS;
+#endif
+                grid = sm_count * s16_ctas;
+                launch(st_sad16_kernel, (size_t)kStWarps * kS16BufWords * 4, p, maps, qi, tag); mark(tag == 1 ? "prehme" : "hme0");
+                grid = engine_grid;
             }
             else { launch(st_sad_kernel, 0, p, lvl); mark("sadg"); }
         } else {
-            if (p.k.me_search_method == 0) launch(st_fp_sub_kernel<false>, (size_t)kFpBufWords * 4, p);
-            else launch(st_fp_sub_kernel<true>, (size_t)kFpBufWords * 4, p);
-            mark("fp");
+            if (p.k.me_search_method == 0) {
+                // small windows: one warp per block; the CTA-wide kernel behind it takes the jobs that did not fit a warp
+                grid = (n_sb + kStWarps / SVTME_FPW_SPLIT - 1) / (kStWarps / SVTME_FPW_SPLIT);
+                launch(st_fp_warp_kernel, (size_t)kStWarps * kFpWBufWords * 4, p, i); mark("fpw");
+                grid = engine_grid;
+                launch(st_fp_sub_kernel<false>, (size_t)kFpBufWords * 4, p, 1, i); mark("fp");
+            } else {
+                launch(st_fp_sub_kernel<true>, (size_t)kFpBufWords * 4, p, 0, i); mark("fp");
+            }
         }
         grid = n_sb;
         if (tc > 0 || fin) { threads = kLightThreads; launch(st_light_kernel, 0, p, tf, tc, fin); threads = kStThreads; mark("light"); }
@@ -1700,8 +1881,9 @@ void staged_print_phases() {
 #endif
 }
 
-// block states, then the sixteenth-plane plans
+// block states, then the sixteenth-plane plans, then the unit queue of the sixteenth-plane engine
 size_t staged_plan_offset(uint32_t n_sb) { return ((size_t)n_sb * sizeof(SbState) + 255) & ~size_t(255); }
-size_t staged_state_bytes(uint32_t n_sb) { return staged_plan_offset(n_sb) + (size_t)n_sb * sizeof(S16Plan); }
+size_t staged_queue_offset(uint32_t n_sb) { return (staged_plan_offset(n_sb) + (size_t)n_sb * sizeof(S16Plan) + 255) & ~size_t(255); }
+size_t staged_state_bytes(uint32_t n_sb) { return staged_queue_offset(n_sb) + (size_t)n_sb * kS16MaxSub * sizeof(uint32_t); }
 
 }  // namespace svtme

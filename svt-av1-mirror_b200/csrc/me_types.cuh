@@ -90,7 +90,9 @@ struct MeParams {
     uint32_t  *work_counter;  // persistent-CTA SB queue
     unsigned long long *px_counter;  // optional: algorithmic pixel-compares of the picture (roofline numerator)
     SbState   *states;        // staged pipeline: one SbState per 64x64 block in HBM/L2
-    void      *plans16;       // one S16Plan per block (me_staged.cu): the sixteenth-plane searches' sub-windows and batches
+    void      *plans16;       // one S16Plan per block (me_staged.cu): the sixteenth-plane searches' sub-windows
+    uint32_t  *q_units;       // unit queue of the sixteenth-plane engine: one entry per sub-window of the picture
+    uint32_t  *q_ctr;         // [count, head] per program step (zeroed when the search is submitted)
     int32_t    n_steps;
     Step       prog[kMaxSteps];
 };
