@@ -1,10 +1,13 @@
 #!/usr/bin/env python
 """bench.py -- open-loop ME pictures/s at 4K (BASELINE.json configs[2]: 3840x2160 8-bit, preset 6).
 
-One STEP = the hot path over one mini-GOP per GPU: every picture of the mini-GOP is decimated (quarter + sixteenth
-planes + padding) and every non-intra picture is searched against its reference lists (pre-HME, HME L0/L1/L2, full-pel
-64x64 search, pruning, candidates, per-SB statistics).  Pictures are independent objects: with N GPUs every rank runs
-its own mini-GOPs (weak scaling, no data-path collective).
+One STEP = the hot path over --gops-per-step mini-GOPs per GPU, streamed without draining the pipeline in between
+(about 0.1 s of device time): every picture is decimated (quarter + sixteenth planes + padding) and every non-intra
+picture is searched against its reference lists (pre-HME, HME L0/L1/L2, full-pel 64x64 search, pruning, candidates,
+per-SB statistics).  Pictures are independent objects: with N GPUs every rank runs its own mini-GOPs (weak scaling, no
+data-path collective; the default line).  --scaling strong deals the pictures of ONE clip round-robin over the GPUs and
+replicates decimated reference planes to the GPUs that need them (svtme_picture_export_planes -> NCCL ->
+svtme_picture_import_planes).  --config 1..5 selects a BASELINE.json configuration (3 = the default).
 
   value     device-resident: luma planes already in HBM, results stay in HBM
   e2e       through the public C ABI with HOST buffers: H2D of every luma plane and D2H of every result inside the
@@ -48,7 +51,25 @@ def parse():
                     help="me: the headline open-loop ME workload; tf: the temporal-filter (ME_MCTF) searches of the same "
                          "mini-GOP -- a secondary measurement of SURVEY section 8(f) rank 2, not the headline metric")
     ap.add_argument("--tf-window", type=int, default=3, help="tf mode: neighbouring pictures searched on each side of a centre")
-    return ap.parse_args()
+    ap.add_argument("--config", type=int, default=0, choices=[0, 1, 2, 3, 4, 5],
+                    help="BASELINE.json configs[N-1]: 1 = 1080p M10, 2 = 1080p M4 (7 references), 3 = 4K M6 (the default "
+                         "workload), 4 = 4K 10-bit input (ME on the 8-bit MSB plane), 5 = 8K M8; 0 = the flags as given")
+    ap.add_argument("--gops-per-step", type=int, default=0, help="mini-GOPs streamed per step and GPU (0: about 0.1 s of device time)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--bit-depth", type=int, default=8, choices=[8, 10])
+    a = ap.parse_args()
+    if a.config:
+        cfg = {1: dict(width=1920, height=1080, preset=10, hier_levels=4), 2: dict(width=1920, height=1080, preset=4, hier_levels=5),
+               3: dict(width=3840, height=2160, preset=6, hier_levels=5), 4: dict(width=3840, height=2160, preset=6, hier_levels=5, bit_depth=10),
+               5: dict(width=7680, height=4320, preset=8, hier_levels=4)}[a.config]
+        for k, v in cfg.items():
+            setattr(a, k, v)
+    if a.gops_per_step <= 0:  # ~0.1 s of device time per step at the rates of DESIGN.md section 8
+        px = a.width * a.height * (1 << a.hier_levels)
+        a.gops_per_step = max(1, min(64, int(round(12 * (3840 * 2160 * 32) / px * (0.35 if a.preset <= 4 else 1.0)))))
+        if a.mode != "me":
+            a.gops_per_step = 1
+    return a
 
 
 SUBMIT_THREADS = int(os.environ.get("SVTME_BENCH_THREADS", "1"))  # host threads submitting searches in the device-resident step
@@ -57,26 +78,31 @@ SUBMIT_THREADS = int(os.environ.get("SVTME_BENCH_THREADS", "1"))  # host threads
 class Workload:
     """A synthetic 8-bit clip of one mini-GOP (+ its leading base picture) and its prediction structure."""
 
-    def __init__(self, args, seed, minigop=0):
-        from svtme import api, synth
+    def __init__(self, args, seed, minigop=0, derive=None, derive_tf=None):
+        from svtme import synth  # numpy only
+        if derive is None:
+            from svtme import api
+            derive, derive_tf = api.derive_knobs, api.derive_tf_knobs
         self.w, self.h, self.hl = args.width, args.height, args.hier_levels
         self.gop = 1 << self.hl
         self.n_frames = self.gop + 1
         # mini-GOP `minigop` of the clip: its 2^levels pictures plus the leading base picture it shares with its predecessor
         self.frames = synth.make_clip(self.w, self.h, self.n_frames, seed=seed, kind="pan", first=minigop * self.gop)
-        k0 = api.derive_knobs(enc_mode=args.preset, qp=35, frame_rate_q16=60 * Q16, width=self.w, height=self.h,
+        k0 = derive(enc_mode=args.preset, qp=35, frame_rate_q16=60 * Q16, width=self.w, height=self.h,
                               hierarchical_levels=self.hl, picture_number=1, temporal_layer_index=1, is_ref=1, slice_type_b=1)
         self.pics = []  # decode order
         for e in synth.minigop_structure(self.n_frames, self.hl, k0.max_l0, max(1, k0.max_refs - k0.max_l0)):
-            k = api.derive_knobs(enc_mode=args.preset, qp=35, frame_rate_q16=60 * Q16, width=self.w, height=self.h,
+            k = derive(enc_mode=args.preset, qp=35, frame_rate_q16=60 * Q16, width=self.w, height=self.h,
                                  hierarchical_levels=self.hl, picture_number=e["poc"], temporal_layer_index=e["temporal_layer"],
                                  is_ref=e["is_ref"], slice_type_b=1, ref_list0_count_try=len(e["list0"]),
                                  ref_list1_count_try=len(e["list1"]))
             l0 = e["list0"][:k.num_of_ref_pic_to_search[0]]
             l1 = e["list1"][:k.num_of_ref_pic_to_search[1]]
             self.pics.append((e["poc"], k, l0, l1))
-        self.name = "%dx%d 8-bit 4:2:0 synthetic, preset M%d, mini-GOP %d (hier. levels %d), refs<=%d+%d" % (
-            self.w, self.h, args.preset, self.gop, self.hl, k0.max_l0, k0.max_refs - k0.max_l0)
+        self.bit_depth = args.bit_depth
+        self.name = "%dx%d %d-bit 4:2:0 synthetic%s, preset M%d, mini-GOP %d (hier. levels %d), refs<=%d+%d" % (
+            self.w, self.h, args.bit_depth, " (ME on the 8-bit MSB plane)" if args.bit_depth == 10 else "", args.preset, self.gop, self.hl,
+            k0.max_l0, k0.max_refs - k0.max_l0)
         self.units, self.unit, self.extended = self.gop, "pictures", False
         self.metric = "ME pictures/sec at 4K"
         self.needed = list(range(self.n_frames))  # pictures a step uploads: the whole mini-GOP + its leading base picture
@@ -87,7 +113,7 @@ class Workload:
             # hme_me_level 2, me_exit_th 0, qp_opt 1.
             self.pics = []
             for c in (0, self.gop // 2, self.gop):
-                k = api.derive_tf_knobs(hme_me_level=2, qp_opt=1, me_exit_th=0, qp=35, width=self.w, height=self.h,
+                k = derive_tf(hme_me_level=2, qp_opt=1, me_exit_th=0, qp=35, width=self.w, height=self.h,
                                         picture_number=c, temporal_layer_index=0 if c != self.gop // 2 else 1, is_ref=1)
                 for d in range(1, args.tf_window + 1):
                     for nb in (c - d, c + d):
@@ -133,97 +159,123 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def run_step_device(dev, wl, d_luma, inflight, handoff=None):
-    """Device-resident step: register every picture from HBM-resident luma, search in decode order, results stay in HBM.
-    With several ranks the leading base picture first arrives from the previous rank (handoff)."""
+def run_step_device(dev, wl, d_luma, inflight, gops, handoff=None):
+    """Device-resident step: `gops` mini-GOPs streamed back to back -- every picture registered from HBM-resident luma
+    (copy, pad, decimate), searched in decode order with `inflight` searches in flight across the mini-GOP boundaries;
+    results stay in HBM.  With several ranks the leading base picture of the step arrives from the previous rank."""
     w, h = wl.w, wl.h
     first = handoff() if handoff else None
-    pics = {i: dev.register_device((first if (i == 0 and first) else d_luma.data_ptr() + i * w * h), w, w, h, i)
-            for i in range(wl.n_frames)}
-    def submit(items, window):
-        pending = []
+    pending, live = [], []
+
+    def submit(items, pics, window):
         for poc, k, l0, l1 in items:
             refs = {(0, i): pics[p] for i, p in enumerate(l0)}
             refs.update({(1, i): pics[p] for i, p in enumerate(l1)})
             if len(pending) >= window:
                 dev.wait(pending.pop(0))
             pending.append(dev.search_device_async(k, pics[poc], refs))
-        for t in pending:
-            dev.wait(t)
 
-    nt = SUBMIT_THREADS
-    if nt <= 1:
-        submit(wl.pics, inflight)
-    else:  # the encoder's ME kernel threads submit concurrently (me_process.c); the library is thread-safe
-        th = [threading.Thread(target=submit, args=(wl.pics[i::nt], max(1, inflight // nt))) for i in range(nt)]
-        for t in th:
-            t.start()
-        for t in th:
-            t.join()
-    for p in pics.values():
-        p.release()
-
-
-def run_step_host(dev, wl, h_luma, outs, inflight, handoff=None):
-    """End-to-end step through the C ABI with host buffers: H2D of each luma plane, D2H of each picture's results.
-    Pictures are registered (uploaded + decimated, asynchronously) in the order the searches need them, so the uploads
-    of later pictures overlap the searches of earlier ones; every picture of the step is uploaded exactly once."""
-    w, h = wl.w, wl.h
-    base = h_luma.data_ptr()
-    pics = {}
-    first = handoff() if handoff else None  # the shared base picture comes over NVLink, not over the host link
-    if first:
-        pics[0] = dev.register_device(first, w, w, h, 0)
-
-    def pic(i):
-        if i not in pics:
-            pics[i] = dev.register_ptr(base + i * w * h, w, w, h, i)
-        return pics[i]
-
-    pending = []
-    for n, (poc, k, l0, l1) in enumerate(wl.pics):
-        refs = {(0, i): pic(p) for i, p in enumerate(l0)}
-        refs.update({(1, i): pic(p) for i, p in enumerate(l1)})
-        cur = pic(poc)
-        if len(pending) >= inflight:
-            dev.wait(pending.pop(0))
-        pending.append(dev.search_async(k, cur, refs, out=outs[n])[0])
-    for i in wl.needed:  # a picture of the workload that no search touched still counts as uploaded
-        pic(i)
+    for g in range(gops):
+        pics = {i: dev.register_device((first if (g == 0 and i == 0 and first) else d_luma.data_ptr() + i * w * h), w, w, h, i)
+                for i in range(wl.n_frames)}
+        live.append(pics)
+        nt = SUBMIT_THREADS
+        if nt <= 1:
+            submit(wl.pics, pics, inflight)
+        else:  # the encoder's ME kernel threads submit concurrently (me_process.c); the library is thread-safe
+            th = [threading.Thread(target=submit, args=(wl.pics[i::nt], pics, max(1, inflight // nt))) for i in range(nt)]
+            for t in th:
+                t.start()
+            for t in th:
+                t.join()
+        if len(live) > 1:  # the mini-GOP before this one: its last searches may still run -- the release waits for them on the device
+            for q in live.pop(0).values():
+                q.release()
     for t in pending:
         dev.wait(t)
-    for p in pics.values():
-        p.release()
+    for pics in live:
+        for q in pics.values():
+            q.release()
 
 
-def reference_arm(wl, n_pictures, steps, warmup, seconds=None):
-    """The reference's own CPU ME (oracle/_ref/libsvtref.so: its unmodified C sources + AVX2 twins) on the host cores.
-    One step = decimation + ME of `n_pictures` pictures of the workload (all of the mini-GOP by default, else spread
-    over the temporal layers).  With `seconds` the steps repeat until about that much time has been spent."""
+def run_step_host(dev, wl, h_luma, outs, inflight, gops, handoff=None):
+    """End-to-end step through the C ABI with host buffers: H2D of each luma plane, D2H of each picture's results.
+    Pictures are registered (uploaded + decimated, asynchronously) in the order the searches need them, so the uploads
+    of later pictures overlap the searches of earlier ones; every picture of a mini-GOP is uploaded exactly once, and
+    the next mini-GOP's uploads start while the last searches of this one are in flight."""
+    w, h = wl.w, wl.h
+    base = h_luma.data_ptr()
+    bps = 2 if wl.bit_depth == 10 else 1
+    first = handoff() if handoff else None  # the shared base picture comes over NVLink, not over the host link
+    pending, live = [], []
+    for g in range(gops):
+        pics = {}
+        live.append(pics)
+        if g == 0 and first:
+            pics[0] = dev.register_device(first, w, w, h, 0)
+
+        def pic(i):
+            if i not in pics:
+                pics[i] = (dev.register_ptr16 if bps == 2 else dev.register_ptr)(base + i * w * h * bps, w, w, h, i)
+            return pics[i]
+
+        for n, (poc, k, l0, l1) in enumerate(wl.pics):
+            refs = {(0, i): pic(p) for i, p in enumerate(l0)}
+            refs.update({(1, i): pic(p) for i, p in enumerate(l1)})
+            cur = pic(poc)
+            if len(pending) >= inflight:
+                dev.wait(pending.pop(0))
+            pending.append(dev.search_async(k, cur, refs, out=outs[(g & 1) * len(wl.pics) + n])[0])  # two sets of result buffers alternate
+        for i in wl.needed:  # a picture of the workload that no search touched still counts as uploaded
+            pic(i)
+        if len(live) > 1:
+            for q in live.pop(0).values():
+                q.release()
+    for t in pending:
+        dev.wait(t)
+    for pics in live:
+        for q in pics.values():
+            q.release()
+
+
+def config_dict(wl, args, world):
+    """The `config` object of the JSON line: the same keys and values in both arms."""
+    return {"workload": wl.name, "%s_per_step_per_gpu" % wl.unit.replace(" ", "_"): wl.units * args.gops_per_step,
+            "mini_gops_per_step_per_gpu": args.gops_per_step, "scaling": args.scaling,
+            "parallelism": ("pictures of one clip dealt round-robin over %d rank(s), decimated reference planes replicated by NCCL p2p" % world)
+                           if args.scaling == "strong" else "pictures sharded by mini-GOP, %d rank(s)" % world,
+            "l2": "inputs larger than L2 (%.0f MB of planes per mini-GOP)" % (wl.n_frames * wl.w * wl.h * 1.55 / 1e6), "inflight": args.inflight}
+
+
+def reference_arm(wl, steps, warmup, seconds=None, threads=None, one_core=True):
+    """The reference's own CPU ME (oracle/_ref/libsvtref.so: its unmodified C sources with the SIMD twins its RTCD would
+    bind on this host -- AVX2, and the AVX-512 svt_sad_loop_kernel where the CPU has it) on the host cores, parallelised
+    the way the encoder is: one pool of ME threads pulls (picture, 6 x 8 segment) items of the whole mini-GOP, the
+    decimation of its pictures runs on the same pool first (oracle/ref_harness.c: svtref_me_minigop).  One step = one
+    mini-GOP of the workload (a bounded sample of the GPU arm's step, which streams several).  With `seconds` the steps
+    repeat until about that much time has been spent.  Nothing of the product is loaded here."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import refbind
     kind = "reference"
-    if refbind.have_reference():
-        ref = refbind.Reference()
-        isa = ref.set_isa(1)
-        what = "reference C sources compiled by oracle/Makefile, %s kernels" % ("AVX2" if isa == 1 else "C")
-    else:
-        ref, kind, what = refbind.Oracle(), "port", "oracle restatement (oracle/_ref not built)"
-    cores = os.cpu_count() or 1
-    # sample: evenly spaced entries of the decode-order list (covers base, middle and top temporal layers)
-    idx = sorted(set(int(round(i * (len(wl.pics) - 1) / max(1, n_pictures - 1))) for i in range(n_pictures)))
-    sample = [wl.pics[i] for i in idx]
-    need = sorted(set(p for poc, k, l0, l1 in sample for p in [poc] + l0 + l1))
-    padded = {p: refbind.PaddedPicture(wl.frames[p], p) for p in need}
-    for p in need:
-        ref.build_planes(padded[p], 1)
+    if not refbind.have_reference():
+        raise SystemExit("oracle/_ref/libsvtref.so is not built")
+    ref = refbind.Reference()
+    isa = ref.set_isa(2)
+    what = "reference C sources compiled by oracle/Makefile, %s kernels" % {0: "C", 1: "AVX2", 2: "AVX2 + AVX-512 svt_sad_loop_kernel"}[isa]
+    cores = threads or os.cpu_count() or 1
+    padded = {p: refbind.PaddedPicture(wl.frames[p], p) for p in wl.needed}
+    items = []
+    for poc, k, l0, l1 in wl.pics:
+        refs = {(0, i): padded[p] for i, p in enumerate(l0)}
+        refs.update({(1, i): padded[p] for i, p in enumerate(l1)})
+        items.append((k, padded[poc], refs))
+    build = [padded[p] for p in wl.needed]
+    n_b64 = ((wl.w + 63) // 64) * ((wl.h + 63) // 64)
+    from svtme import abi  # ctypes mirror of the result structs (pure Python)
+    outs = [abi.ResultBuffers(n_b64, k, extended=wl.extended) for k, _, _ in items]
 
-    def step():
-        for poc, k, l0, l1 in sample:
-            ref.build_planes(padded[poc], 1)  # decimation of the current picture is part of the path
-            refs = {(0, i): padded[p] for i, p in enumerate(l0)}
-            refs.update({(1, i): padded[p] for i, p in enumerate(l1)})
-            ref.me_picture(k, padded[poc], refs, n_threads=cores, extended=wl.extended)
+    def step(n=cores, its=items, bld=build, o=outs):
+        ref.me_minigop(its, bld, n, outs=o[:len(its)])
 
     for _ in range(warmup):
         step()
@@ -234,10 +286,16 @@ def reference_arm(wl, n_pictures, steps, warmup, seconds=None):
         done += 1
     steps = done
     dt = time.perf_counter() - t0
-    pps = len(sample) * steps / dt
-    return {"value": pps, "unit": wl.unit + "/s", "cores": cores, "kind": kind,
-            "sample": "%d searches (decode-order %s) of the workload x %d steps = %.1f s, %s, %d threads" % (
-                len(sample), "all" if len(sample) == len(wl.pics) else idx, steps, dt, what, cores)}, dt
+    pps = len(items) * steps / dt
+    cb = {"value": pps, "unit": wl.unit + "/s", "cores": cores, "kind": kind,
+          "sample": "%d mini-GOP(s) of the workload (%d searches + %d decimations each) in %.1f s, %s, %d threads on one work queue" % (
+              steps, len(items), len(build), dt, what, cores)}
+    if one_core:  # the same code on ONE host thread, on a few searches spread over the temporal layers
+        idx = sorted(set(int(round(i * (len(items) - 1) / 3)) for i in range(4)))
+        t1 = time.perf_counter()
+        step(1, [items[i] for i in idx], [items[i][1] for i in idx])
+        cb["one_core"] = {"value": len(idx) / (time.perf_counter() - t1), "unit": wl.unit + "/s", "sample": "searches %s of the mini-GOP" % idx}
+    return cb, dt, steps
 
 
 DG_PAIRS = lambda gop: [(gop, 0), (gop, gop // 2), (gop // 2, 0)]  # noqa: E731  eval_sub_mini_gop (pd_process.c:682-705): (end, start), (end, mid), (mid, start)
@@ -369,6 +427,143 @@ def main_dg(args, rank, local_rank, world):
     return 0
 
 
+def main_strong(args, rank, local_rank, world, dist, wl):
+    """--scaling strong: ONE clip on `world` GPUs.  The pictures of every mini-GOP are dealt round-robin (decode order)
+    over the ranks; a picture is uploaded and decimated once, by the rank that searches it (the leading base picture by
+    rank 0), and its three padded planes go to the ranks whose searches reference it: svtme_picture_export_planes ->
+    NCCL point-to-point over NVLink -> svtme_picture_import_planes (no decimation on the receiver).  No collective runs
+    inside the searches.  Before the timed region every rank checks one of its searches against the same search with
+    all references decimated locally (the single-GPU path, itself pinned to the oracle by the GPU tests)."""
+    import torch
+    from svtme import abi, api, shard
+    w, h, nf, G = wl.w, wl.h, wl.n_frames, args.gops_per_step
+    dev = api.MeDevice(device=local_rank, max_inflight=args.inflight, max_pictures=3 * nf)
+    h_luma = torch.empty((nf, h, w), dtype=torch.uint8).pin_memory()
+    h_luma.numpy()[:] = np.stack(wl.frames)
+    d_luma = h_luma.cuda()
+    n_b64 = ((w + 63) // 64) * ((h + 63) // 64)
+    keep = []
+
+    def pinned(shape, dt):
+        t = torch.zeros(tuple(shape), dtype=getattr(torch, np.dtype(dt).name)).pin_memory()
+        keep.append(t)
+        return t.numpy()
+
+    owner = {0: 0}
+    for n, (poc, _, _, _) in enumerate(wl.pics):
+        owner[poc] = n % world
+    mine = [(n, e) for n, e in enumerate(wl.pics) if n % world == rank]
+    outs = {n: abi.ResultBuffers(n_b64, e[1], extended=False, pinned_alloc=pinned) for n, e in mine}
+    # (picture, source rank, destination rank) of every plane set that crosses GPUs in a mini-GOP, the same list on every rank
+    transfers = sorted(set((p, owner[p], n % world) for n, (_, _, l0, l1) in enumerate(wl.pics) for p in l0 + l1 if owner[p] != n % world))
+    nbytes = api.MeDevice.planes_bytes(w, h)
+    sendbuf = {t: torch.empty(nbytes, dtype=torch.uint8, device="cuda") for t in transfers if t[1] == rank}
+    recvbuf = {t: torch.empty(nbytes, dtype=torch.uint8, device="cuda") for t in transfers if t[2] == rank}
+    moved = sum(nbytes for t in transfers if t[2] == rank)
+
+    def gop(host, pending, exchange=True):
+        src = (lambda i: dev.register_ptr(h_luma.data_ptr() + i * w * h, w, w, h, i)) if host else \
+              (lambda i: dev.register_device(d_luma.data_ptr() + i * w * h, w, w, h, i))
+        pics = {p: src(p) for p in owner if owner[p] == rank}  # uploaded / decimated here
+        if exchange and world > 1:
+            ops = []
+            for t in transfers:
+                if t[1] == rank:
+                    dev.export_planes(pics[t[0]], sendbuf[t].data_ptr(), nbytes)
+                    ops.append(dist.P2POp(dist.isend, sendbuf[t], t[2]))
+                elif t[2] == rank:
+                    ops.append(dist.P2POp(dist.irecv, recvbuf[t], t[1]))
+            if ops:
+                for r in dist.batch_isend_irecv(ops):
+                    r.wait()
+            torch.cuda.current_stream().synchronize()
+            for t in transfers:
+                if t[2] == rank and t[0] not in pics:
+                    pics[t[0]] = dev.import_planes(recvbuf[t].data_ptr(), w, h, t[0])
+        else:
+            for _, (_, _, l0, l1) in mine:
+                for p_ in l0 + l1:
+                    if p_ not in pics:
+                        pics[p_] = src(p_)
+        for n, (poc, k, l0, l1) in mine:
+            refs = {(0, i): pics[p_] for i, p_ in enumerate(l0)}
+            refs.update({(1, i): pics[p_] for i, p_ in enumerate(l1)})
+            if len(pending) >= args.inflight:
+                dev.wait(pending.pop(0))
+            pending.append(dev.search_async(k, pics[poc], refs, out=outs[n])[0] if host else dev.search_device_async(k, pics[poc], refs))
+        return pics
+
+    def step(host):
+        pending, prev = [], None
+        for _ in range(G):
+            pics = gop(host, pending)
+            if prev:
+                for q in prev.values():
+                    q.release()
+            prev = pics
+        for t in pending:
+            dev.wait(t)
+        for q in prev.values():
+            q.release()
+
+    # the multi-GPU path against the single-GPU path, on this rank's first picture
+    if mine:
+        n0 = mine[0][0]
+        for exchange in (True, False):
+            pend = []
+            pics = gop(True, pend, exchange)
+            for t in pend:
+                dev.wait(t)
+            for q in pics.values():
+                q.release()
+            got = {f: np.array(getattr(outs[n0], f)) for f in ("me_mv", "me_cand", "total_me_candidate_index", "me_8x8_distortion")}
+            if exchange:
+                first = got
+            elif any(not np.array_equal(first[f], got[f]) for f in got):
+                raise SystemExit("rank %d: the search over replicated reference planes differs from the local one" % rank)
+
+    def timed(host, steps):
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step(host)
+        torch.cuda.synchronize()
+        e1.record()
+        torch.cuda.synchronize()
+        return shard.reduce_job(len(mine) * G * steps, e0.elapsed_time(e1), dist, device="cuda")
+
+    for _ in range(max(3, args.warmup)):
+        step(False)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    l0 = dev.launch_count()
+    pictures, ms_dev = timed(False, args.steps)
+    launches = dev.launch_count() - l0
+    clocks = sampler.stop()
+    step(True)
+    _, ms_host = timed(True, args.steps)
+    if rank != 0:
+        return 0
+    line = {"metric": wl.metric, "value": pictures / (ms_dev * 1e-3), "unit": wl.unit + "/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config_dict(wl, args, world),
+            "e2e": {"value": pictures / (ms_host * 1e-3), "unit": wl.unit + "/s",
+                    "h2d_bytes_per_step": sum(1 for p in owner if owner[p] == 0) * w * h * G,
+                    "d2h_bytes_per_step": sum(o.nbytes() for o in outs.values()) * G, "ms_per_step": ms_host / args.steps,
+                    "nvlink_bytes_received_per_step_rank0": moved * G},
+            "gpu_launches": launches, "clocks": clocks,
+            "verified": "every rank: one search over replicated planes == the same search with locally decimated references"}
+    print(json.dumps(line))
+    dev.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -380,13 +575,16 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return 0
-        wl = Workload(args, seed=100)
-        steps, warmup = max(1, min(args.steps, 40)), min(args.warmup, 2)  # a step = the whole mini-GOP, ~0.2 s on 16 cores
-        cb, dt = reference_arm(wl, args.cpu_sample, steps, warmup)
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import refbind
+        ref = refbind.Reference()  # the knobs come from the reference's own svt_aom_sig_deriv_me: the product is not loaded
+        wl = Workload(args, seed=100, derive=ref.derive_knobs, derive_tf=ref.derive_tf_knobs)
+        steps, warmup = max(1, min(args.steps, 40)), max(3, args.warmup)  # a step = one mini-GOP on every host core
+        cb, dt, steps = reference_arm(wl, steps, warmup)
         line = {"impl": "reference", "metric": wl.metric, "value": cb["value"], "unit": wl.unit + "/s",
                 "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": {"workload": wl.name, "l2": "inputs larger than L2"},
+                "scaling": args.scaling, "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": config_dict(wl, args, args.gpus),
                 "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": wl.unit + "/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         print(json.dumps(line))
         return 0
@@ -403,12 +601,20 @@ def main():
 
     # weak scaling: one mini-GOP per rank and step; rank r owns mini-GOP r of the job (svtme/shard.py), its own clip
     my_gops = list(shard.shard_minigops(world, rank, world))
-    wl = Workload(args, seed=100, minigop=my_gops[0])
-    dev = api.MeDevice(device=local_rank, max_inflight=args.inflight, max_pictures=2 * wl.n_frames)
-    w, h, nf = wl.w, wl.h, wl.n_frames
-    h_luma = torch.empty((nf, h, w), dtype=torch.uint8).pin_memory()
-    h_luma.numpy()[:] = np.stack(wl.frames)
-    d_luma = h_luma.cuda(non_blocking=False)
+    wl = Workload(args, seed=100, minigop=0 if args.scaling == "strong" else my_gops[0])
+    if args.scaling == "strong" and args.mode == "me":
+        return main_strong(args, rank, local_rank, world, dist, wl)
+    dev = api.MeDevice(device=local_rank, max_inflight=args.inflight, max_pictures=3 * wl.n_frames)
+    w, h, nf, G = wl.w, wl.h, wl.n_frames, args.gops_per_step
+    h_luma8 = torch.empty((nf, h, w), dtype=torch.uint8).pin_memory()
+    h_luma8.numpy()[:] = np.stack(wl.frames)
+    d_luma = h_luma8.cuda(non_blocking=False)
+    if wl.bit_depth == 10:  # 10-bit samples whose 8-bit MSB plane is the 8-bit clip (svt_unpack_and_2bcompress keeps in16 >> 2)
+        h_luma = torch.empty((nf, h, w), dtype=torch.int16).pin_memory()
+        rng = np.random.default_rng(7)
+        h_luma.numpy().view(np.uint16)[:] = (np.stack(wl.frames).astype(np.uint16) << 2) | rng.integers(0, 4, (nf, h, w), dtype=np.uint16)
+    else:
+        h_luma = h_luma8
     n_b64 = ((w + 63) // 64) * ((h + 63) // 64)
     keep = []
 
@@ -418,9 +624,10 @@ def main():
         return t.numpy()
 
     # temporal-filter mode: the compact [b64][85] outputs (all the filter reads) instead of the full [2][4][85] tables
-    outs = [abi.ResultBuffers(n_b64, k, extended=wl.extended, pinned_alloc=pinned, tf_compact=(args.mode == "tf")) for _, k, _, _ in wl.pics]
-    d2h = sum(o.nbytes() for o in outs)
-    h2d = len(wl.needed) * w * h
+    outs = [abi.ResultBuffers(n_b64, k, extended=wl.extended, pinned_alloc=pinned, tf_compact=(args.mode == "tf"))
+            for _ in range(2) for _, k, _, _ in wl.pics]  # two sets: consecutive mini-GOPs of a step alternate
+    d2h = sum(o.nbytes() for o in outs[:len(wl.pics)]) * G
+    h2d = len(wl.needed) * w * h * (2 if wl.bit_depth == 10 else 1) * G
 
     def barrier():
         torch.cuda.synchronize()
@@ -440,7 +647,7 @@ def main():
         ms = e0.elapsed_time(e1)
         barrier()
         # whole job: SUM of the pictures of all ranks, MAX of their device times (svtme/shard.py)
-        return shard.reduce_job(wl.units * steps, ms, dist, device="cuda")
+        return shard.reduce_job(wl.units * G * steps, ms, dist, device="cuda")
 
     # the picture consecutive mini-GOPs share (last of rank r = leading base picture of rank r + 1) moves GPU to GPU
     # every step: NCCL point-to-point over NVLink; the receiver decimates it locally
@@ -452,8 +659,8 @@ def main():
         return d_recv.data_ptr() if got else None
 
     hand = handoff if world > 1 else None
-    step_dev = lambda: run_step_device(dev, wl, d_luma, args.inflight, hand)  # noqa: E731
-    step_host = lambda: run_step_host(dev, wl, h_luma, outs, args.inflight, hand)  # noqa: E731
+    step_dev = lambda: run_step_device(dev, wl, d_luma, args.inflight, G, hand)  # noqa: E731
+    step_host = lambda: run_step_host(dev, wl, h_luma, outs, args.inflight, G, hand)  # noqa: E731
     if world > 1:
         handoff()
         if rank > 0 and not torch.equal(d_recv, d_luma[0]):
@@ -471,14 +678,14 @@ def main():
     _, ms_host = timed(step_host, args.steps)
     # context for the end-to-end number: what the host link alone sustains for one step's uploads (pinned -> HBM)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    scratch = torch.empty_like(d_luma)
+    scratch = torch.empty_like(h_luma, device="cuda")
     scratch.copy_(h_luma, non_blocking=True)
     torch.cuda.synchronize()
     e0.record()
     scratch.copy_(h_luma, non_blocking=True)
     e1.record()
     torch.cuda.synchronize()
-    h2d_only_ms = e0.elapsed_time(e1) * len(wl.needed) / nf  # scaled to the pictures a step uploads
+    h2d_only_ms = e0.elapsed_time(e1) * len(wl.needed) / nf * G  # scaled to the pictures a step uploads
     del scratch
 
     # per-launch view: one picture's search at a time, CUDA events on its stream around it (svtme_search_elapsed_ms)
@@ -524,11 +731,11 @@ def main():
     # launches run alone (events on its own stream) -- the latency view, and what the ncu launch list adds up to.
     ach_ser = px_total / (ms_total * 1e-3) / 1e12
     ach = (px_total / n_launch) * (value / world) / 1e12
-    roofline = {"bound": "int", "kernel": "picture search = st_init/ctl/nxm/sad16/sad_rows/fp_sub/finish kernels (me_staged.cu)", "achieved": ach, "peak": sad_peak, "unit": "Tpx-compares/s",
+    roofline = {"bound": "int", "kernel": "picture search = st_init / st_light / st_sad16 / st_sad_rows / st_fp_warp / st_fp_sub kernels (me_staged.cu)", "achieved": ach, "peak": sad_peak, "unit": "Tpx-compares/s",
                 "frac": ach / sad_peak, "traffic": traffic,
                 "peak_source": "VABSDIFF4.U8.ACC issue rate measured in this run (svtme_measure_sad_peak) x 4 px",
                 "px_compares_per_launch": px_total / n_launch, "avg_launch_ms": ms_dev / pictures * world,
-                "launch": "one picture's search (~21 stream-ordered kernels); duration = device time of the timed region / pictures searched in it (%d searches in flight)" % args.inflight,
+                "launch": "one picture's search (14 stream-ordered kernels at preset M6); duration = device time of the timed region / pictures searched in it (%d searches in flight)" % args.inflight,
                 "serialised": {"achieved": ach_ser, "frac": ach_ser / sad_peak, "avg_launch_ms": ms_total / n_launch,
                                "launch": "the same search launched alone, CUDA events on its stream"},
                 "hbm": {"achieved": alg_bytes / (ms_dev / pictures * world * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
@@ -537,15 +744,13 @@ def main():
     line = {"metric": wl.metric, "value": value, "unit": wl.unit + "/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": wl.name, "%s_per_step_per_gpu" % wl.unit.replace(" ", "_"): wl.units, "parallelism": "pictures sharded by mini-GOP, %d rank(s)%s" % (
-                           world, "; shared base picture handed rank r -> r+1 by NCCL p2p every step (verified equal)" if world > 1 else ""),
-                       "l2": "inputs larger than L2 (%.0f MB of planes per step)" % (nf * w * h * 1.55 / 1e6), "inflight": args.inflight},
+            "config": config_dict(wl, args, world),
             "e2e": {"value": e2e, "unit": wl.unit + "/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_host / args.steps, "h2d_copy_alone_ms_per_step": h2d_only_ms,
                     "h2d_link_gbs": h2d / h2d_only_ms / 1e6},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline}
     if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"], _ = reference_arm(wl, args.cpu_sample, 1, 1, seconds=args.cpu_seconds)
+        line["cpu_baseline"], _, _ = reference_arm(wl, 1, 1, seconds=args.cpu_seconds)
     print(json.dumps(line))
     dev.close()
     if dist is not None:

@@ -288,6 +288,24 @@ int32_t svtme_picture_register16(SvtMeHandle *h, uint64_t picture_number, const 
 /* Same, from a luma plane that is already in device memory (device pointer). */
 int32_t svtme_picture_register_device(SvtMeHandle *h, uint64_t picture_number, const void *d_luma, uint32_t stride,
                                       uint32_t width, uint32_t height, SvtMePic **out);
+/*
+ * Reference planes across GPUs (no counterpart in the single-process, single-memory reference:
+ * there every ME thread reads the same EbPaReferenceObject, reference_object.c:217-345).  A picture is uploaded and
+ * decimated ONCE, on the GPU that owns it; the GPUs whose searches reference it get a copy of its three padded planes
+ * (one allocation of svtme_picture_planes_bytes(width, height) bytes, the same layout on every device).
+ *  - one process driving several GPUs (the encoder is one process, enc_handle.c:2245-2307): svtme_picture_replicate
+ *    copies `pic` of src_h into a new picture of dst_h with cudaMemcpyPeerAsync (NVLink when the devices are peers).
+ *    Asynchronous; `pic` may be released right away (its release waits for the copy).
+ *  - one process per GPU (torch.distributed / NCCL): svtme_picture_export_planes copies the planes into a device buffer
+ *    of the caller (synchronous: ready to send when it returns), the caller moves the bytes (ncclSend / ncclBroadcast),
+ *    svtme_picture_import_planes builds a picture from the received bytes (asynchronous: d_src must stay valid until
+ *    svtme_picture_wait).  No decimation runs on the receiving GPU.
+ */
+int32_t svtme_picture_planes_bytes(uint32_t width, uint32_t height, uint64_t *bytes);
+int32_t svtme_picture_replicate(SvtMeHandle *src_h, SvtMePic *pic, SvtMeHandle *dst_h, SvtMePic **out);
+int32_t svtme_picture_export_planes(SvtMeHandle *h, SvtMePic *pic, void *d_dst, uint64_t dst_bytes);
+int32_t svtme_picture_import_planes(SvtMeHandle *h, uint64_t picture_number, const void *d_src, uint32_t width, uint32_t height,
+                                    SvtMePic **out);
 /* Wait until the planes of `pic` are built. */
 int32_t svtme_picture_wait(SvtMeHandle *h, SvtMePic *pic);
 /* Copy a padded plane back (level 0 = full, 1 = quarter, 2 = sixteenth) for the

@@ -47,6 +47,12 @@ void svt_sad_loop_kernel_avx2_intrin(uint8_t *src, uint32_t src_stride, uint8_t 
 static int g_isa = 0;
 
 /* Bind the eight RTCD rows of the hot path (aom_dsp_rtcd.c:501,509-515). */
+void svt_aom_downsample_2d_avx2(uint8_t *input_samples, uint32_t input_stride, uint32_t input_area_width,
+                                uint32_t input_area_height, uint8_t *decim_samples, uint32_t decim_stride, uint32_t decim_step);
+void svt_sad_loop_kernel_avx512_intrin(uint8_t *src, uint32_t src_stride, uint8_t *ref, uint32_t ref_stride, uint32_t block_height,
+                                       uint32_t block_width, uint64_t *best_sad, int16_t *x_search_center, int16_t *y_search_center,
+                                       uint32_t src_stride_raw, uint8_t skip_search_line, int16_t search_area_width,
+                                       int16_t search_area_height);
 int svtref_set_isa(int isa) {
     svt_sad_loop_kernel                       = svt_sad_loop_kernel_c;
     downsample_2d                             = svt_aom_downsample_2d_c;
@@ -59,14 +65,17 @@ int svtref_set_isa(int isa) {
     svt_memcpy                                = svt_memcpy_c;
     g_isa                                     = 0;
 #ifdef SVTREF_HAVE_AVX2
-    if (isa == 1 && __builtin_cpu_supports("avx2")) {
+    if (isa >= 1 && __builtin_cpu_supports("avx2")) {
         svt_sad_loop_kernel                       = svt_sad_loop_kernel_avx2_intrin;
-        /* downsample_2d stays on the C twin: ASM_AVX2/transforms_intrin_avx2.c is not part of this build */
+        downsample_2d                             = svt_aom_downsample_2d_avx2; /* aom_dsp_rtcd.c:509 */
+        /* isa 2: what the RTCD binds on an AVX-512 host (aom_dsp_rtcd.c:501) */
+        if (isa == 2 && __builtin_cpu_supports("avx512f") && __builtin_cpu_supports("avx512bw"))
+            svt_sad_loop_kernel                   = svt_sad_loop_kernel_avx512_intrin;
         svt_ext_sad_calculation_8x8_16x16         = svt_ext_sad_calculation_8x8_16x16_avx2_intrin;
         svt_ext_all_sad_calculation_8x8_16x16     = svt_ext_all_sad_calculation_8x8_16x16_avx2;
         svt_ext_eight_sad_calculation_32x32_64x64 = svt_ext_eight_sad_calculation_32x32_64x64_avx2;
         svt_nxm_sad_kernel                        = svt_nxm_sad_kernel_helper_avx2;
-        g_isa                                     = 1;
+        g_isa                                     = svt_sad_loop_kernel == svt_sad_loop_kernel_avx512_intrin ? 2 : 1;
     }
 #else
     (void)isa;
@@ -399,13 +408,18 @@ static void desc_from_plane(EbPictureBufferDesc *d, const SvtRefPlane *p) {
     d->max_height = d->height;
 }
 
-static void *ref_worker(void *arg) {
-    RefJob                  *job = (RefJob *)arg;
-    const SvtMeKnobs        *k   = job->k;
-    PictureParentControlSet *pcs = job->pcs;
-    SvtMePictureResults     *out = job->out;
-    MeContext               *ctx = (MeContext *)calloc(1, sizeof(MeContext));
-    EbPictureBufferDesc      cur_d[3], ref_d[2][4][3];
+/* one ME thread's view of one picture: its MeContext and the buffer descriptors it points into */
+typedef struct RefThread {
+    MeContext          *ctx;
+    EbPictureBufferDesc cur_d[3], ref_d[2][4][3];
+} RefThread;
+
+static void ref_thread_setup(RefThread *t, const RefJob *job) {
+    const SvtMeKnobs    *k = job->k;
+    MeContext           *ctx = t->ctx;
+    EbPictureBufferDesc *cur_d = t->cur_d;
+    EbPictureBufferDesc (*ref_d)[4][3] = t->ref_d;
+    memset(ctx, 0, sizeof(*ctx));
     ctx_from_knobs(ctx, k);
     for (int l = 0; l < 3; l++) desc_from_plane(&cur_d[l], &job->cur->lvl[l]);
     for (int li = 0; li < k->num_of_list_to_search; li++)
@@ -418,11 +432,17 @@ static void *ref_worker(void *arg) {
             ctx->me_ds_ref_array[li][ri].sixteenth_picture_ptr = &ref_d[li][ri][2];
             ctx->me_ds_ref_array[li][ri].picture_number        = rp->picture_number;
         }
-    const uint32_t total = job->pic_w_b64 * job->pic_h_b64;
+}
+
+/* one 64x64 block: the body of the SB loop of me_process.c:174-290 */
+static void ref_thread_sb(RefThread *t, RefJob *job, uint32_t sb) {
+    const SvtMeKnobs        *k   = job->k;
+    PictureParentControlSet *pcs = job->pcs;
+    SvtMePictureResults     *out = job->out;
+    MeContext               *ctx = t->ctx;
+    EbPictureBufferDesc     *cur_d = t->cur_d;
     const uint32_t pus = out->pu_count, mr = k->max_refs, mc = k->max_cand;
-    for (;;) {
-        uint32_t sb = __sync_fetch_and_add(&job->next_sb, 1);
-        if (sb >= total) break;
+    {
         uint32_t x = (sb % job->pic_w_b64) * 64, y = (sb / job->pic_w_b64) * 64;
         /* me_process.c:183-214 */
         ctx->b64_src_ptr    = cur_d[0].buffer_y + (cur_d[0].org_y + y) * cur_d[0].stride_y + cur_d[0].org_x + x;
@@ -469,11 +489,31 @@ static void *ref_worker(void *arg) {
                 }
             }
     }
+}
+
+static void ref_thread_done(RefThread *t, RefJob *job) {
+    SvtMePictureResults *out = job->out;
+    MeContext           *ctx = t->ctx;
     if (out->tf_blk_counts) { /* temporal_filtering.c:4224-4227: per-segment counters summed into the centre pcs */
         __sync_fetch_and_add(&out->tf_blk_counts[0], ctx->tf_tot_horz_blks);
         __sync_fetch_and_add(&out->tf_blk_counts[1], ctx->tf_tot_vert_blks);
+        ctx->tf_tot_horz_blks = ctx->tf_tot_vert_blks = 0;
     }
-    free(ctx);
+}
+
+static void *ref_worker(void *arg) {
+    RefJob   *job = (RefJob *)arg;
+    RefThread t;
+    t.ctx = (MeContext *)malloc(sizeof(MeContext));
+    ref_thread_setup(&t, job);
+    const uint32_t total = job->pic_w_b64 * job->pic_h_b64;
+    for (;;) {
+        uint32_t sb = __sync_fetch_and_add(&job->next_sb, 1);
+        if (sb >= total) break;
+        ref_thread_sb(&t, job, sb);
+    }
+    ref_thread_done(&t, job);
+    free(t.ctx);
     return NULL;
 }
 
@@ -491,8 +531,7 @@ static void picture_sums(const SvtMeKnobs *k, SvtMePictureResults *out, uint32_t
     out->picture_sums[0] = dist; out->picture_sums[1] = me_sad; out->picture_sums[2] = stat; out->picture_sums[3] = gm;
 }
 
-int svtref_me_picture(const SvtMeKnobs *k, const SvtRefPic *cur, const SvtRefPic *refs, SvtMePictureResults *out,
-                      int n_threads) {
+static int ref_job_open(RefJob *job, const SvtMeKnobs *k, const SvtRefPic *cur, const SvtRefPic *refs, SvtMePictureResults *out) {
     const uint32_t W = cur->lvl[0].width, H = cur->lvl[0].height;
     const uint32_t wb = (W + 63) / 64, hb = (H + 63) / 64, total = wb * hb;
     if (out->b64_total_count < total) return -2;
@@ -544,23 +583,107 @@ int svtref_me_picture(const SvtMeKnobs *k, const SvtRefPic *cur, const SvtRefPic
     pcs->rc_me_allow_gm              = out->rc_me_allow_gm;
 
     if (out->tf_blk_counts) out->tf_blk_counts[0] = out->tf_blk_counts[1] = 0;
+    memset(job, 0, sizeof(*job));
+    job->k = k; job->cur = cur; job->refs = refs; job->out = out; job->pcs = pcs;
+    job->pic_w_b64 = wb; job->pic_h_b64 = hb;
+    return 0;
+}
+
+static void ref_job_close(RefJob *job) {
+    PictureParentControlSet *pcs = job->pcs;
+    MotionEstimationData    *med = pcs->pa_me_data;
+    picture_sums(job->k, job->out, job->pic_w_b64 * job->pic_h_b64);
+    free(pcs->b64_geom);
+    free(med->me_results[0]);
+    free(med->me_results);
+    free(med);
+    free(pcs->scs);
+    free(pcs);
+}
+
+int svtref_me_picture(const SvtMeKnobs *k, const SvtRefPic *cur, const SvtRefPic *refs, SvtMePictureResults *out,
+                      int n_threads) {
     RefJob job;
-    memset(&job, 0, sizeof(job));
-    job.k = k; job.cur = cur; job.refs = refs; job.out = out; job.pcs = pcs;
-    job.pic_w_b64 = wb; job.pic_h_b64 = hb;
+    int    rc = ref_job_open(&job, k, cur, refs, out);
+    if (rc) return rc;
     if (n_threads < 1) n_threads = 1;
     if (n_threads > 256) n_threads = 256;
     pthread_t th[256];
     for (int t = 1; t < n_threads; t++) pthread_create(&th[t], NULL, ref_worker, &job);
     ref_worker(&job);
     for (int t = 1; t < n_threads; t++) pthread_join(th[t], NULL);
-    picture_sums(k, out, wb * hb);
-    free(pcs->b64_geom);
-    free(sbr);
-    free(med->me_results);
-    free(med);
-    free(pcs);
-    free(scs);
+    ref_job_close(&job);
+    return 0;
+}
+
+void svtref_build_planes(const SvtRefPic *pic, int hme_level1);
+
+/* ---- a mini-GOP at a time, parallelised the way the encoder is (enc_handle.c:395-398, 706-773; me_process.c:147-157):
+ * a pool of ME threads pulls (picture, segment) items -- 6 x 8 segments per picture, several pictures in flight -- from
+ * one queue; the decimation of the pictures (the Picture Analysis kernel's share of the path) runs on the same pool
+ * first, one picture per item.  Used by bench.py's CPU arms; results are the same bytes as svtref_me_picture's. ---- */
+typedef struct RefPool {
+    RefJob            *jobs;
+    int                n_jobs;
+    const SvtRefPic  **build;
+    int                n_build, hme_level1;
+    volatile uint32_t  next_build, next_item;
+    pthread_barrier_t  bar;
+} RefPool;
+enum { kSegW = 6, kSegH = 8 };
+
+static void *pool_worker(void *arg) {
+    RefPool *pl = (RefPool *)arg;
+    for (;;) {  /* phase 1: decimation + padding, one picture per item */
+        uint32_t i = __sync_fetch_and_add(&pl->next_build, 1);
+        if (i >= (uint32_t)pl->n_build) break;
+        svtref_build_planes(pl->build[i], pl->hme_level1);
+    }
+    pthread_barrier_wait(&pl->bar);
+    RefThread t;
+    t.ctx = (MeContext *)malloc(sizeof(MeContext));
+    int cur_job = -1;
+    for (;;) {  /* phase 2: (picture, segment) items in decode order */
+        uint32_t it = __sync_fetch_and_add(&pl->next_item, 1);
+        if (it >= (uint32_t)pl->n_jobs * kSegW * kSegH) break;
+        const int ji = (int)(it / (kSegW * kSegH)), seg = (int)(it % (kSegW * kSegH));
+        RefJob   *job = &pl->jobs[ji];
+        if (ji != cur_job) {
+            if (cur_job >= 0) ref_thread_done(&t, &pl->jobs[cur_job]);
+            ref_thread_setup(&t, job);  /* the encoder re-derives the knobs per message as well (me_process.c:121) */
+            cur_job = ji;
+        }
+        const uint32_t wb = job->pic_w_b64, hb = job->pic_h_b64, sx = seg % kSegW, sy = seg / kSegW;
+        const uint32_t x0 = sx * wb / kSegW, x1 = (sx + 1) * wb / kSegW, y0 = sy * hb / kSegH, y1 = (sy + 1) * hb / kSegH;
+        for (uint32_t y = y0; y < y1; y++)
+            for (uint32_t x = x0; x < x1; x++) ref_thread_sb(&t, job, y * wb + x);
+    }
+    if (cur_job >= 0) ref_thread_done(&t, &pl->jobs[cur_job]);
+    free(t.ctx);
+    return NULL;
+}
+
+int svtref_me_minigop(int n_pics, const SvtMeKnobs *const *k, const SvtRefPic *const *cur, const SvtRefPic *const *refs,
+                      SvtMePictureResults *const *out, int n_build, const SvtRefPic *const *build, int hme_level1,
+                      int n_threads) {
+    RefPool pl;
+    memset(&pl, 0, sizeof(pl));
+    pl.jobs = (RefJob *)calloc((size_t)n_pics, sizeof(RefJob));
+    for (int i = 0; i < n_pics; i++) {
+        int rc = ref_job_open(&pl.jobs[i], k[i], cur[i], refs[i], out[i]);
+        if (rc) return rc;
+    }
+    pl.n_jobs = n_pics; pl.build = (const SvtRefPic **)build; pl.n_build = n_build; pl.hme_level1 = hme_level1;
+    if (n_threads < 1) n_threads = 1;
+    if (n_threads > 256) n_threads = 256;
+    pthread_barrier_init(&pl.bar, NULL, (unsigned)n_threads);
+    pthread_t th[256];
+    for (int t = 1; t < n_threads; t++) pthread_create(&th[t], NULL, pool_worker, &pl);
+    pool_worker(&pl);
+    for (int t = 1; t < n_threads; t++) pthread_join(th[t], NULL);
+    pthread_barrier_destroy(&pl.bar);
+    for (int i = 0; i < n_pics; i++) ref_job_close(&pl.jobs[i]);
+    free(pl.jobs);
     return 0;
 }
 

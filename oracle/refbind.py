@@ -172,9 +172,40 @@ class Reference(_Binding):
     def __init__(self):
         super().__init__(_load(os.path.join(HERE, "_ref", "libsvtref.so"), "compiled reference"), "svtref_")
         self.lib.svtref_set_isa.argtypes = [C.c_int]
+        if hasattr(self.lib, "svtref_me_minigop"):
+            pp = C.POINTER(C.c_void_p)
+            self.lib.svtref_me_minigop.argtypes = [C.c_int, pp, pp, pp, pp, C.c_int, pp, C.c_int, C.c_int]
 
     def set_isa(self, isa):
+        """0: C kernels, 1: AVX2 twins, 2: AVX2 + the AVX-512 svt_sad_loop_kernel where the host has it (what the
+        encoder's RTCD would bind).  Returns what was bound."""
         return self.lib.svtref_set_isa(isa)
+
+    def me_minigop(self, items, build, n_threads, hme_level1=1, extended=False, outs=None):
+        """The encoder's parallelisation of the path (oracle/ref_harness.c: svtref_me_minigop): `build` pictures are
+        decimated + padded, then `items` = [(knobs, cur, {(list, idx): PaddedPicture})] are searched, all on one pool of
+        `n_threads` ME threads pulling (picture, 6 x 8 segment) items.  Returns the result buffers."""
+        n = len(items)
+        if outs is None:
+            outs = [abi.ResultBuffers(((c.width + 63) // 64) * ((c.height + 63) // 64), k, extended=extended) for k, c, _ in items]
+        arrs = []
+        for _, _, refs in items:
+            arr = (RefPic * 8)()
+            for (li, ri), p in refs.items():
+                arr[li * 4 + ri] = p.struct
+            arrs.append(arr)
+        vp = C.c_void_p
+        ks = (vp * n)(*[C.addressof(k) for k, _, _ in items])
+        cs = (vp * n)(*[C.addressof(c.struct) for _, c, _ in items])
+        rs = (vp * n)(*[C.addressof(a) for a in arrs])
+        os_ = (vp * n)(*[C.addressof(o.struct) for o in outs])
+        bs = (vp * max(1, len(build)))(*[C.addressof(b.struct) for b in build])
+        rc = self.lib.svtref_me_minigop(n, ks, cs, rs, os_, len(build), bs, hme_level1, n_threads)
+        if rc != 0:
+            raise RuntimeError("me_minigop failed: %d" % rc)
+        for o, a in zip(outs, arrs):
+            o._keep = a
+        return outs
 
 
 class Oracle(_Binding):

@@ -59,6 +59,7 @@ struct SvtMePic {
     uint16_t   *staging16;
     uint64_t    reader_slots;  // search slots whose streams have read this picture (bit = slot index; guarded by the handle's mutex)
     bool        dg_reader;     // the dynamic-GOP detector / statistics stream has read it
+    std::vector<cudaEvent_t> peer_reads;  // copies of this picture to other handles / devices still in flight (svtme_picture_replicate)
 };
 
 namespace {
@@ -546,6 +547,78 @@ int32_t svtme_picture_register16(SvtMeHandle *h, uint64_t picture_number, const 
     return SVTME_OK;
 }
 
+// ---- reference planes across GPUs: a picture is decimated once, on the GPU that owns it, and
+// its three padded planes -- one allocation, the same layout for a given picture size on every device -- are copied to
+// the GPUs whose searches reference it ----
+int32_t svtme_picture_planes_bytes(uint32_t width, uint32_t height, uint64_t *bytes) {
+    if (!bytes || width == 0 || height == 0 || (width & 7) || (height & 7)) return SVTME_ERR_BAD_PARAMETER;
+    PlaneGeom g[3];
+    size_t    total;
+    plane_geometry(width, height, g, &total);
+    *bytes = total;
+    return SVTME_OK;
+}
+
+int32_t svtme_picture_replicate(SvtMeHandle *src_h, SvtMePic *pic, SvtMeHandle *dst_h, SvtMePic **out) {
+    if (!src_h || !pic || !dst_h || !out) return fail(dst_h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    SvtMePic *p = nullptr;
+    int rc = make_pic(dst_h, pic->picture_number, pic->width, pic->height, &p);  // makes dst_h's device current
+    if (rc) return rc;
+    size_t total;
+    PlaneGeom g[3];
+    plane_geometry(pic->width, pic->height, g, &total);
+    const int sd = src_h->cfg.device, dd = dst_h->cfg.device;
+    cudaError_t e = cudaSuccess;
+    if (sd != dd) {  // direct NVLink path when the devices are peers (an "already enabled" answer is fine)
+        int can = 0;
+        if (cudaDeviceCanAccessPeer(&can, dd, sd) == cudaSuccess && can) {
+            e = cudaDeviceEnablePeerAccess(sd, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) { (void)cudaGetLastError(); e = cudaSuccess; }
+        }
+    }
+    // the copy runs on the new picture's stream, behind the source's decimation
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(p->stream, pic->ready, 0);
+    if (e == cudaSuccess) e = cudaMemcpyPeerAsync(p->buf.base, dd, pic->buf.base, sd, total, p->stream);
+    cudaEvent_t done = nullptr;
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&done, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventRecord(done, p->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(p->ready, p->stream);
+    if (e != cudaSuccess) { if (done) cudaEventDestroy(done); svtme_picture_release(dst_h, p); return fail(dst_h, SVTME_ERR_UNDEFINED, "svtme_picture_replicate", e); }
+    { std::lock_guard<std::mutex> lk(src_h->mu); pic->peer_reads.push_back(done); }  // the source's release waits for the copy
+    *out = p;
+    return SVTME_OK;
+}
+
+int32_t svtme_picture_export_planes(SvtMeHandle *h, SvtMePic *pic, void *d_dst, uint64_t dst_bytes) {
+    if (!h || !pic || !d_dst) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    size_t total;
+    PlaneGeom g[3];
+    plane_geometry(pic->width, pic->height, g, &total);
+    if (dst_bytes < total) return fail(h, SVTME_ERR_BAD_PARAMETER, "destination smaller than svtme_picture_planes_bytes");
+    int rc = set_device(h);
+    if (rc) return rc;
+    CK(cudaStreamWaitEvent(pic->stream, pic->ready, 0));
+    CK(cudaMemcpyAsync(d_dst, pic->buf.base, total, cudaMemcpyDeviceToDevice, pic->stream));
+    CK(cudaStreamSynchronize(pic->stream));  // the bytes are in d_dst when the call returns (the caller's NCCL send comes next)
+    return SVTME_OK;
+}
+
+int32_t svtme_picture_import_planes(SvtMeHandle *h, uint64_t picture_number, const void *d_src, uint32_t width, uint32_t height,
+                                    SvtMePic **out) {
+    if (!d_src) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    SvtMePic *p = nullptr;
+    int rc = make_pic(h, picture_number, width, height, &p);
+    if (rc) return rc;
+    size_t total;
+    PlaneGeom g[3];
+    plane_geometry(width, height, g, &total);
+    cudaError_t e = cudaMemcpyAsync(p->buf.base, d_src, total, cudaMemcpyDeviceToDevice, p->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(p->ready, p->stream);
+    if (e != cudaSuccess) { svtme_picture_release(h, p); return fail(h, SVTME_ERR_UNDEFINED, "svtme_picture_import_planes", e); }
+    *out = p;
+    return SVTME_OK;
+}
+
 int32_t svtme_picture_wait(SvtMeHandle *h, SvtMePic *pic) {
     if (!h || !pic) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
     CK(cudaEventSynchronize(pic->ready));
@@ -577,6 +650,7 @@ int32_t svtme_picture_release(SvtMeHandle *h, SvtMePic *pic) {
         for (size_t i = 0; i < h->slots.size(); i++)
             if (pic->reader_slots & (1ull << i)) cudaStreamWaitEvent(pic->stream, h->slots[i].ev_done, 0);
         if (pic->dg_reader && h->dg_done) cudaStreamWaitEvent(pic->stream, h->dg_done, 0);
+        for (cudaEvent_t ev : pic->peer_reads) { cudaStreamWaitEvent(pic->stream, ev, 0); cudaEventDestroy(ev); }
         cudaEventRecord(pic->buf.free_ev, pic->stream);
         pic->buf.recycled = true;
         if (h->free_bufs.size() < h->cfg.max_pictures) h->free_bufs.push_back(pic->buf);

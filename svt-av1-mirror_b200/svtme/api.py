@@ -23,7 +23,8 @@ EXPORTS = [
     "svtme_picture_search", "svtme_search_wait", "svtme_picture_search_device", "svtme_search_elapsed_ms",
     "svtme_search_px_compares", "svtme_measure_sad_peak", "svtme_launch_count", "svtme_last_error", "svtme_cuda_sad_loop_kernel", "svtme_cuda_downsample_2d",
     "svtme_cuda_nxm_sad_kernel", "svtme_cuda_fullpel_search_sblock", "svtme_dg_detector_hme_level0",
-    "svtme_picture_statistics", "svtme_cuda_nxm_sad_kernel_noalloc",
+    "svtme_picture_statistics", "svtme_cuda_nxm_sad_kernel_noalloc", "svtme_picture_planes_bytes", "svtme_picture_replicate",
+    "svtme_picture_export_planes", "svtme_picture_import_planes",
 ]
 
 
@@ -61,6 +62,10 @@ def load_library():
     lib.svtme_picture_register16.argtypes = [vp, u64, u8p, u32, u32, u32, C.POINTER(vp)]
     lib.svtme_picture_register_device.argtypes = [vp, u64, vp, u32, u32, u32, C.POINTER(vp)]
     lib.svtme_picture_wait.argtypes = [vp, vp]
+    lib.svtme_picture_planes_bytes.argtypes = [u32, u32, C.POINTER(u64)]
+    lib.svtme_picture_replicate.argtypes = [vp, vp, vp, C.POINTER(vp)]
+    lib.svtme_picture_export_planes.argtypes = [vp, vp, vp, u64]
+    lib.svtme_picture_import_planes.argtypes = [vp, u64, vp, u32, u32, C.POINTER(vp)]
     lib.svtme_picture_read_plane.argtypes = [vp, vp, i32, u32, u8p, u32]
     lib.svtme_picture_release.argtypes = [vp, vp]
     lib.svtme_picture_search.argtypes = [vp, vp, refs_t, C.POINTER(abi.Knobs), C.POINTER(abi.PictureResults),
@@ -180,11 +185,41 @@ class MeDevice:
                     "svtme_picture_register")
         return Picture(self, ptr, picture_number, width, height, keep=keep)
 
+    def register_ptr16(self, host_ptr, stride, width, height, picture_number, keep=None):
+        """10-bit samples in uint16 at `host_ptr` (stride in samples): the 8-bit MSB plane is what ME sees."""
+        ptr = C.c_void_p()
+        self._check(self.lib.svtme_picture_register16(self.h, picture_number, host_ptr, stride, width, height, C.byref(ptr)),
+                    "svtme_picture_register16")
+        return Picture(self, ptr, picture_number, width, height, keep=keep)
+
     def register_device(self, dev_ptr, stride, width, height, picture_number):
         ptr = C.c_void_p()
         self._check(self.lib.svtme_picture_register_device(self.h, picture_number, dev_ptr, stride, width, height, C.byref(ptr)),
                     "svtme_picture_register_device")
         return Picture(self, ptr, picture_number, width, height)
+
+    # ---- reference planes across GPUs ----
+    @staticmethod
+    def planes_bytes(width, height):
+        n = C.c_uint64(0)
+        if load_library().svtme_picture_planes_bytes(width, height, C.byref(n)) != 0:
+            raise SvtMeError("svtme_picture_planes_bytes: bad size")
+        return n.value
+
+    def replicate_to(self, pic, dst):
+        """Copy `pic` (of this handle) into a new picture of handle `dst` (another GPU of this process): peer copy."""
+        ptr = C.c_void_p()
+        dst._check(self.lib.svtme_picture_replicate(self.h, pic.ptr, dst.h, C.byref(ptr)), "svtme_picture_replicate")
+        return Picture(dst, ptr, pic.picture_number, pic.width, pic.height)
+
+    def export_planes(self, pic, d_dst, nbytes):
+        self._check(self.lib.svtme_picture_export_planes(self.h, pic.ptr, d_dst, nbytes), "svtme_picture_export_planes")
+
+    def import_planes(self, d_src, width, height, picture_number, keep=None):
+        ptr = C.c_void_p()
+        self._check(self.lib.svtme_picture_import_planes(self.h, picture_number, d_src, width, height, C.byref(ptr)),
+                    "svtme_picture_import_planes")
+        return Picture(self, ptr, picture_number, width, height, keep=keep)
 
     def wait_picture(self, pic):
         self._check(self.lib.svtme_picture_wait(self.h, pic.ptr), "svtme_picture_wait")
