@@ -516,7 +516,7 @@ def main_strong(args, rank, local_rank, world, dist, wl):
                 dev.wait(t)
             for q in pics.values():
                 q.release()
-            got = {f: np.array(getattr(outs[n0], f)) for f in ("me_mv", "me_cand", "total_me_candidate_index", "me_8x8_distortion")}
+            got = {f: np.array(outs[n0][f]) for f in ("me_mv", "me_cand", "total_me_candidate_index", "me_8x8_distortion")}
             if exchange:
                 first = got
             elif any(not np.array_equal(first[f], got[f]) for f in got):
