@@ -1,0 +1,71 @@
+#!/usr/bin/env python3
+"""TEST INFRASTRUCTURE ONLY.  Writes build-time copies of two reference files with the dump hooks inserted.
+
+    make_overlay.py <reference root> <out dir>
+
+Reads  <ref>/Source/Lib/Codec/me_process.c  and  <ref>/Source/Lib/Codec/global_me.c, inserts the calls into
+oracle/enc_overlay/me_dump.c listed in HOOKS below, and writes the results into <out dir> (oracle/_ref/enc/, git-ignored).
+The copies exist only there; no reference source is committed.  Every anchor must match exactly once, else the script
+fails: a reference update that moves the code is noticed instead of silently dumping nothing.
+"""
+import pathlib
+import sys
+
+DECLS = (
+    "\n/* svtme dump hooks (oracle/enc_overlay/me_dump.c) */\n"
+    "struct SequenceControlSet; struct PictureParentControlSet; struct MeContext; struct EbPictureBufferDesc;\n"
+    "void svtme_dump_pre_sb(struct PictureParentControlSet *pcs, unsigned b64);\n"
+    "void svtme_dump_gm_level(struct PictureParentControlSet *pcs, unsigned char level);\n"
+    "void svtme_dump_picture(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs, struct MeContext *ctx,\n"
+    "                        struct EbPictureBufferDesc *input_pic);\n"
+)
+
+# (file, anchor, text, where): `text` goes before/after the single line that contains `anchor`
+HOOKS = [
+    # me_process.c:263 -- before the per-block search
+    ("me_process.c", "svt_aom_motion_estimation_b64(pcs,", "svtme_dump_pre_sb(pcs, b64_index);\n", "before"),
+    # me_process.c:282 -- the memset of the `else` branch is the last statement of the last-SB hook; the dump goes after
+    # the closing brace of that else, i.e. two lines further down
+    ("me_process.c", "memset(pcs->is_global_motion, false, MAX_NUM_OF_REF_PIC_LIST * REF_LIST_MAX_DEPTH);",
+     "svtme_dump_picture(scs, pcs, me_context_ptr->me_ctx, input_pic);\n", "after_closing_brace"),
+    # global_me.c:206 -- after the bypass test, before the level is used
+    ("global_me.c", "if (global_motion_estimation_level) {", "svtme_dump_gm_level(pcs, global_motion_estimation_level);\n",
+     "before"),
+]
+
+
+def patch(name, text):
+    lines = text.splitlines(keepends=True)
+    for fname, anchor, ins, where in HOOKS:
+        if fname != name:
+            continue
+        hits = [i for i, l in enumerate(lines) if anchor in l]
+        if len(hits) != 1:
+            sys.exit(f"{name}: anchor {anchor!r} matched {len(hits)} times, expected 1")
+        i = hits[0]
+        if where == "before":
+            lines.insert(i, ins)
+        elif where == "after_closing_brace":
+            j = i + 1
+            while lines[j].strip() != "}":
+                j += 1
+            lines.insert(j + 1, ins)
+        else:
+            sys.exit(f"bad hook placement {where}")
+    # declarations after the last #include
+    last_inc = max(i for i, l in enumerate(lines) if l.startswith("#include"))
+    lines.insert(last_inc + 1, DECLS)
+    return "".join(lines)
+
+
+def main():
+    ref, out = pathlib.Path(sys.argv[1]), pathlib.Path(sys.argv[2])
+    out.mkdir(parents=True, exist_ok=True)
+    for name in ("me_process.c", "global_me.c"):
+        src = (ref / "Source/Lib/Codec" / name).read_text()
+        (out / name).write_text(patch(name, src))
+        print(f"overlay {out / name}")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,127 @@
+/*
+ * me_dump.c -- TEST INFRASTRUCTURE ONLY.  Linked into the C-only reference encoder that oracle/Makefile target `enc`
+ * builds into oracle/_ref/SvtAv1EncApp_dump, and called from the three one-line hooks make_overlay.py inserts into a
+ * build-time copy of Source/Lib/Codec/me_process.c and global_me.c.  With SVTME_DUMP=<file> set, every open-loop ME
+ * picture of the encode is serialised there: the planes ME read, the knob block extracted from the encoder's own
+ * MeContext/pcs by the shim (integration/svtme_shim.c), the reference lists, and what the reference's ME wrote.
+ *
+ * Record = a sequence of chunks { char tag[4]; uint32 bytes; payload }, closed by an "END " chunk:
+ *   HEAD  uint64 picture_number, uint32 width, height, b64_total_count, pu_count, slice_type, hme_level1_planes,
+ *         temporal_layer_index, sizeof(SvtMeKnobs)
+ *   KNOB  SvtMeKnobs (include/svtme_cuda.h)
+ *   REFS  uint64 picture_number[2][4] (~0 where unused)
+ *   CUR0/CUR1/CUR2  full / quarter / sixteenth luma of the source picture, tight rows (no padding)
+ *   R<l><i>0        full luma of reference (list l, index i)
+ *   RES   the flat result buffers in svtme_shim_results_layout order, tight
+ *   GMC   the pcs/scs fields the last-SB gate reads (gm_ctrls, gm_pp_detected, pic_avg_variance, input size)
+ *   GATE  uint8 ran (svt_aom_global_motion_estimation was called), level, downsample_level (0xff when it did not run)
+ *         -- `level`/`downsample_level` come from the hook inside global_me.c, i.e. the reference's own locals
+ */
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include "svtme_shim.h"
+#include "reference_object.h"
+
+static FILE *g_f;
+static int   g_tried;
+static int   g_gm_level = -1, g_gm_ds = -1;
+
+static FILE *dump_file(void) {
+    if (!g_tried) {
+        g_tried        = 1;
+        const char *fn = getenv("SVTME_DUMP");
+        if (fn && *fn) g_f = fopen(fn, "wb");
+    }
+    return g_f;
+}
+
+static void chunk(const char *tag, const void *p, uint32_t n) {
+    fwrite(tag, 1, 4, g_f);
+    fwrite(&n, 4, 1, g_f);
+    if (n) fwrite(p, 1, n, g_f);
+}
+
+static void plane_chunk(const char *tag, const EbPictureBufferDesc *d, uint32_t w, uint32_t h) {
+    uint8_t *tight = (uint8_t *)malloc((size_t)w * h);
+    for (uint32_t y = 0; y < h; y++)
+        memcpy(tight + (size_t)y * w, d->buffer_y + (size_t)(d->org_y + y) * d->stride_y + d->org_x, w);
+    chunk(tag, tight, w * h);
+    free(tight);
+}
+
+/* before each svt_aom_motion_estimation_b64: clear what the pooled MeSbResults still holds from an earlier picture, so
+ * that entries the search leaves unwritten (MVs of pruned references, candidates past the count) read 0 as in the flat ABI */
+void svtme_dump_pre_sb(PictureParentControlSet *pcs, uint32_t b64) {
+    if (!dump_file()) return;
+    const MotionEstimationData *med = pcs->pa_me_data;
+    const uint32_t              pus = svtme_shim_pu_count(pcs);
+    MeSbResults                *r   = med->me_results[b64];
+    memset(r->me_mv_array, 0, sizeof(MvCandidate) * pus * med->max_refs);
+    memset(r->me_candidate_array, 0, sizeof(MeCandidate) * pus * med->max_cand);
+    memset(r->total_me_candidate_index, 0, pus);
+}
+
+/* inside svt_aom_global_motion_estimation, after the bypass test (global_me.c:205) */
+void svtme_dump_gm_level(PictureParentControlSet *pcs, uint8_t level) {
+    g_gm_level = level;
+    g_gm_ds    = pcs->gm_downsample_level;
+}
+
+/* at the end of the last-SB hook (me_process.c:287), still under me_processed_b64_mutex */
+void svtme_dump_picture(SequenceControlSet *scs, PictureParentControlSet *pcs, MeContext *ctx, EbPictureBufferDesc *input_pic) {
+    if (!dump_file()) return;
+    SvtMeKnobs k;
+    svtme_shim_knobs_from_me_context(scs, pcs, ctx, &k);
+    const uint32_t W = pcs->aligned_width, H = pcs->aligned_height, pus = svtme_shim_pu_count(pcs);
+    struct {
+        uint64_t picture_number;
+        uint32_t width, height, b64_total_count, pu_count, slice_type, hme_level1_planes, temporal_layer_index, knob_bytes;
+    } head = {pcs->picture_number, W, H, pcs->b64_total_count, pus, (uint32_t)pcs->slice_type,
+              (uint32_t)(pcs->enable_hme_level1_flag || pcs->tf_enable_hme_level1_flag), pcs->temporal_layer_index,
+              (uint32_t)sizeof(SvtMeKnobs)};
+    chunk("HEAD", &head, sizeof(head));
+    chunk("KNOB", &k, sizeof(k));
+
+    uint64_t refs[2][4];
+    memset(refs, 0xff, sizeof(refs));
+    const EbPaReferenceObject *cur = (const EbPaReferenceObject *)pcs->pa_ref_pic_wrapper->object_ptr;
+    plane_chunk("CUR0", cur->input_padded_pic, W, H);
+    plane_chunk("CUR1", cur->quarter_downsampled_picture_ptr, W >> 1, H >> 1);
+    plane_chunk("CUR2", cur->sixteenth_downsampled_picture_ptr, W >> 2, H >> 2);
+    for (int li = 0; li < k.num_of_list_to_search; li++)
+        for (int ri = 0; ri < k.num_of_ref_pic_to_search[li]; ri++) {
+            const EbPaReferenceObject *ro = (const EbPaReferenceObject *)pcs->ref_pa_pic_ptr_array[li][ri]->object_ptr;
+            char                       tag[5];
+            snprintf(tag, sizeof(tag), "R%d%d0", li, ri);
+            refs[li][ri] = ro->picture_number;
+            plane_chunk(tag, ro->input_padded_pic, W, H);
+        }
+    chunk("REFS", refs, sizeof(refs));
+
+    SvtMePictureResults res;
+    const size_t        bytes = svtme_shim_results_layout(&res, pcs->b64_total_count, pus, k.max_refs, k.max_cand, NULL);
+    void               *mem   = calloc(1, bytes);
+    svtme_shim_results_layout(&res, pcs->b64_total_count, pus, k.max_refs, k.max_cand, mem);
+    svtme_shim_gather_results(pcs, &res);
+    chunk("RES ", mem, (uint32_t)bytes);
+
+    /* the inputs of the last-SB gate (me_process.c:276, global_me.c:162-205), so that a test can rebuild a pcs for the shim */
+    struct {
+        uint8_t  enabled, pp_enabled, gm_pp_detected, downsample_level, bypass_based_on_me, use_stationary_block,
+            calculate_variance, pad;
+        uint32_t pic_avg_variance, input_width, input_height;
+    } c = {pcs->gm_ctrls.enabled, pcs->gm_ctrls.pp_enabled, pcs->gm_pp_detected, pcs->gm_ctrls.downsample_level,
+           pcs->gm_ctrls.bypass_based_on_me, pcs->gm_ctrls.use_stationary_block, scs->calculate_variance, 0,
+           pcs->pic_avg_variance, input_pic->width, input_pic->height};
+    chunk("GMC ", &c, sizeof(c));
+    /* what the reference did: did svt_aom_global_motion_estimation run, and its two locals after the bypass test */
+    struct {
+        uint8_t ran, level, downsample_level, pad;
+    } g = {(uint8_t)(g_gm_level >= 0), (uint8_t)(g_gm_level < 0 ? 0xff : g_gm_level), (uint8_t)(g_gm_ds < 0 ? 0xff : g_gm_ds), 0};
+    chunk("GATE", &g, sizeof(g));
+    chunk("END ", NULL, 0);
+    fflush(g_f);
+    free(mem);
+    g_gm_level = g_gm_ds = -1;
+}

@@ -1,0 +1,243 @@
+"""Encoder-level replay (BASELINE.json config 1 as written: "ME results dumped from the reference CPU path").
+
+tests/golden/enc_m10.npz / enc_m4.npz hold what the C-only reference encoder (SvtAv1EncApp --preset 10 / 4, built by
+`make -C oracle enc` with the dump hooks of oracle/enc_overlay/) did for every picture its ME kernel searched: the planes, the
+knob block taken from the encoder's own MeContext/pcs by the shim, the real reference lists, and the MeSbResults + eight pcs
+arrays.  Generator: tests/golden/make_enc_golden.py.
+
+CPU (`-m "not gpu"`): the oracle restatement and, where present, the compiled reference harness replay every picture
+bit-exactly; the encoder-side shim (integration/svtme_shim.c, compiled against the reference's headers into
+oracle/_ref/libsvtme_shim.so) round-trips knobs and results and reproduces the last-SB global-motion gate.
+GPU (`-m gpu`): the CUDA path replays every picture through svtme_picture_search, and once more through the compiled shim
+driver (svtme_shim_me_picture: the call me_process.c would make), which scatters into a real PictureParentControlSet.
+"""
+import ctypes as C
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import refbind
+from svtme import abi, api
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+SHIM_SO = os.path.join(ROOT, "oracle", "_ref", "libsvtme_shim.so")
+FIXTURES = ["enc_m10", "enc_m4"]
+FIELDS = (["me_mv", "me_cand", "total_me_candidate_index"] + list(abi.ResultBuffers.SCALARS32) +
+          list(abi.ResultBuffers.SCALARS8) + ["picture_sums"])
+
+
+def parse_res(buf, n, pus, mr, mc):
+    """The flat layout of svtme_shim_results_layout (integration/svtme_shim.c): fields in order, each 16-byte aligned."""
+    off, out = 0, {}
+
+    def field(name, dt, shape):
+        nonlocal off
+        off = (off + 15) & ~15
+        a = np.frombuffer(buf, dt, int(np.prod(shape)), off).reshape(shape)
+        off += a.nbytes
+        out[name] = a
+
+    field("me_mv", np.uint32, (n, pus, mr))
+    field("me_cand", np.uint8, (n, pus, mc))
+    field("total_me_candidate_index", np.uint8, (n, pus))
+    for s in abi.ResultBuffers.SCALARS32:
+        field(s, np.uint32, (n,))
+    for s in abi.ResultBuffers.SCALARS8:
+        field(s, np.uint8, (n,))
+    field("picture_sums", np.uint64, (4,))
+    return out, off
+
+
+class Fixture:
+    def __init__(self, name):
+        self.z = np.load(os.path.join(GOLD, name + ".npz"))
+        self.meta = json.loads(bytes(self.z["meta"]))
+        self.n = self.meta["pictures"]
+        self.luma = self.z["luma"]
+
+    def pic(self, i):
+        z = self.z
+        head = [int(v) for v in z[f"pic_{i}_head"]]
+        d = dict(zip(("poc", "W", "H", "n_b64", "pus", "slice_type", "hme_l1", "tl", "knob_bytes"), head))
+        assert d["knob_bytes"] == C.sizeof(abi.Knobs), "fixture made with another SvtMeKnobs layout: regenerate"
+        d["knobs"] = abi.Knobs.from_buffer_copy(bytes(z[f"pic_{i}_knobs"]))
+        d["refs"] = z[f"pic_{i}_refs"]
+        d["planes"] = z[f"pic_{i}_planes"]
+        d["res_bytes"] = bytes(z[f"pic_{i}_res"])
+        d["res"], used = parse_res(d["res_bytes"], d["n_b64"], d["pus"], d["knobs"].max_refs, d["knobs"].max_cand)
+        assert used == len(d["res_bytes"])
+        d["gmc"] = bytes(z[f"pic_{i}_gmc"])
+        d["gate"] = [int(v) for v in z[f"pic_{i}_gate"]]
+        d["cur1"], d["cur2"] = z[f"pic_{i}_cur1"], z[f"pic_{i}_cur2"]
+        return d
+
+
+@pytest.fixture(scope="module", params=FIXTURES)
+def fx(request):
+    return Fixture(request.param)
+
+
+def test_fixture_is_a_real_encode(fx):
+    """The fixture carries what a synthetic harness cannot: the encoder's own prediction structure."""
+    pics = [fx.pic(i) for i in range(fx.n)]
+    assert fx.n >= 16, "at least two mini-GOPs"
+    assert {p["slice_type"] for p in pics} <= {0, 1}  # B_SLICE / P_SLICE (definitions.h): no I picture is searched
+    shapes = {(p["knobs"].num_of_list_to_search, tuple(p["knobs"].num_of_ref_pic_to_search)) for p in pics}
+    assert len(shapes) >= 2, "reference list shapes vary over the hierarchy: %s" % shapes
+    assert len({p["tl"] for p in pics}) >= 3
+    for p in pics:  # every reference of every picture is a plane of the fixture
+        k = p["knobs"]
+        for li in range(k.num_of_list_to_search):
+            for ri in range(k.num_of_ref_pic_to_search[li]):
+                assert p["planes"][1 + li * 4 + ri] >= 0 and p["refs"][li, ri] >= 0
+        assert p["res"]["total_me_candidate_index"].max() >= 1
+
+
+def _replay_cpu(binding, fx):
+    for i in range(fx.n):
+        p = fx.pic(i)
+
+        def padded(idx, num):
+            pp = refbind.PaddedPicture(fx.luma[idx], num)
+            binding.build_planes(pp, p["hme_l1"])
+            return pp
+
+        cur = padded(p["planes"][0], p["poc"])
+        # the encoder's own decimated planes of this picture == ours (pic_analysis_process.c:1945-2002)
+        assert np.array_equal(cur.interior(1), p["cur1"]) and np.array_equal(cur.interior(2), p["cur2"])
+        refs = {(li, ri): padded(p["planes"][1 + li * 4 + ri], int(p["refs"][li, ri]))
+                for li in range(2) for ri in range(4) if p["planes"][1 + li * 4 + ri] >= 0}
+        out = binding.me_picture(p["knobs"], cur, refs, extended=False)
+        bad = [f for f in FIELDS if not np.array_equal(p["res"][f], out[f])]
+        assert not bad, "picture %d (poc %d): %s differ from the encoder's dump" % (i, p["poc"], bad)
+
+
+def test_oracle_replays_encoder_dump(oracle, fx):
+    _replay_cpu(oracle, fx)
+
+
+def test_reference_harness_replays_encoder_dump(reference, fx):
+    """The harness (oracle/ref_harness.c) around the unmodified motion_estimation.c fed with the dumped knobs gives what the
+    encoder gave: the harness' pcs/MeContext filling is complete."""
+    _replay_cpu(reference, fx)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# the encoder-side shim, compiled against the reference's headers
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def shim():
+    if os.path.exists("/root/reference/Source/Lib/Codec/me_process.c"):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "shim"], stdout=subprocess.DEVNULL)
+    if not os.path.exists(SHIM_SO):
+        pytest.skip("oracle/_ref/libsvtme_shim.so not available (built where /root/reference exists)")
+    api.load_library()
+    C.CDLL(api.LIB_PATH, mode=C.RTLD_GLOBAL)  # the shim driver's svtme_* symbols resolve against the product library
+    lib = C.CDLL(SHIM_SO)
+    lib.shimtb_results_bytes.restype = C.c_size_t
+    lib.shimtb_results_bytes.argtypes = [C.c_uint32] * 4
+    lib.shimtb_roundtrip.argtypes = [C.POINTER(abi.Knobs), C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_char_p,
+                                     C.POINTER(abi.Knobs), C.c_void_p, C.c_void_p]
+    lib.shimtb_open.argtypes = [C.c_uint32, C.c_uint32, C.c_int, C.c_uint32, C.c_int, C.POINTER(C.c_void_p)]
+    lib.shimtb_me_picture.argtypes = [C.c_void_p, C.POINTER(abi.Knobs), C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                      C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_void_p, C.c_void_p]
+    lib.svtme_shim_close.argtypes = [C.c_void_p]
+    lib.svtme_shim_close.restype = None
+    lib.svtme_shim_last_error.argtypes = [C.c_void_p]
+    lib.svtme_shim_last_error.restype = C.c_char_p
+    return lib
+
+
+def _check_gate(p, gate):
+    """gate = (run_gm, level, downsample_level) from the shim; p["gate"] = (ran, level, downsample_level) of the encoder."""
+    ran, level, ds = p["gate"][:3]
+    assert gate[0] == ran, "me_process.c:276 decision differs"
+    if ran:
+        assert (gate[1], gate[2]) == (level, ds), "global_me.c:171-205 gate differs: shim %s, encoder %s" % (gate, p["gate"])
+
+
+def test_shim_roundtrip_and_gm_gate(shim, fx):
+    """knobs -> scs/pcs/MeContext -> svtme_shim_knobs_from_me_context gives the knobs back; results scatter into
+    MeSbResults + pcs arrays and gather back byte-identical; the gate computed from the gathered sums is the encoder's."""
+    ran_any = False
+    for i in range(fx.n):
+        p = fx.pic(i)
+        k = p["knobs"]
+        assert shim.shimtb_results_bytes(p["n_b64"], p["pus"], k.max_refs, k.max_cand) == len(p["res_bytes"])
+        k_back = abi.Knobs()
+        res_back = np.zeros(len(p["res_bytes"]), np.uint8)
+        gate = np.zeros(3, np.uint8)
+        rc = shim.shimtb_roundtrip(C.byref(k), p["gmc"], p["W"], p["H"], p["slice_type"], p["res_bytes"], C.byref(k_back),
+                                   res_back.ctypes.data, gate.ctypes.data)
+        assert rc == 0
+        assert bytes(k_back) == bytes(k), "knob block does not survive the trip through MeContext/pcs"
+        assert res_back.tobytes() == p["res_bytes"]
+        _check_gate(p, [int(v) for v in gate])
+        ran_any |= bool(p["gate"][0])
+    if fx.meta["preset"] <= 4:
+        assert ran_any, "global motion runs at this preset: the gate must have been exercised"
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# GPU
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+def test_cuda_replays_encoder_dump(fx):
+    p0 = fx.pic(0)
+    dev = api.MeDevice(device=0, max_inflight=4, sixteenth_from_full=0 if p0["hme_l1"] else 1)
+    try:
+        resident = {}
+
+        def plane(idx, num):
+            if idx not in resident:
+                resident[idx] = dev.register(np.ascontiguousarray(fx.luma[idx]), num)
+            return resident[idx]
+
+        for i in range(fx.n):
+            p = fx.pic(i)
+            cur = plane(p["planes"][0], p["poc"])
+            assert np.array_equal(dev.read_plane(cur, 1, 0), p["cur1"]) and np.array_equal(dev.read_plane(cur, 2, 0), p["cur2"])
+            refs = {(li, ri): plane(p["planes"][1 + li * 4 + ri], int(p["refs"][li, ri]))
+                    for li in range(2) for ri in range(4) if p["planes"][1 + li * 4 + ri] >= 0}
+            out = dev.me_picture(p["knobs"], cur, refs, extended=False)
+            bad = [f for f in FIELDS if not np.array_equal(p["res"][f], out[f])]
+            assert not bad, "picture %d (poc %d): %s differ from the encoder's dump" % (i, p["poc"], bad)
+    finally:
+        dev.close()
+
+
+@pytest.mark.gpu
+def test_cuda_through_compiled_shim(shim, fx):
+    """svtme_shim_me_picture -- upload, search, scatter into a PictureParentControlSet, gate -- gives the pcs contents the
+    reference encoder had after its own ME of the same picture."""
+    p0 = fx.pic(0)
+    h = C.c_void_p()
+    assert shim.shimtb_open(p0["W"], p0["H"], 0, 32, p0["hme_l1"], C.byref(h)) == 0
+    try:
+        for i in range(fx.n):
+            p = fx.pic(i)
+            k = p["knobs"]
+            cur = np.ascontiguousarray(fx.luma[p["planes"][0]])
+            keep, ptrs, nums = [], (C.c_void_p * 8)(), (C.c_uint64 * 8)()
+            for s in range(8):
+                idx = p["planes"][1 + s]
+                if idx >= 0:
+                    a = np.ascontiguousarray(fx.luma[idx])
+                    keep.append(a)
+                    ptrs[s] = a.ctypes.data
+                    nums[s] = int(p["refs"][s // 4, s % 4])
+            res = np.zeros(len(p["res_bytes"]), np.uint8)
+            gate = np.zeros(3, np.uint8)
+            rc = shim.shimtb_me_picture(h, C.byref(k), p["gmc"], p["W"], p["H"], p["slice_type"], cur.ctypes.data, ptrs, nums,
+                                        res.ctypes.data, gate.ctypes.data)
+            assert rc == 0, shim.svtme_shim_last_error(h)
+            got, _ = parse_res(res.tobytes(), p["n_b64"], p["pus"], k.max_refs, k.max_cand)
+            bad = [f for f in FIELDS if not np.array_equal(p["res"][f], got[f])]
+            assert not bad, "picture %d (poc %d): %s differ from the encoder's pcs" % (i, p["poc"], bad)
+            _check_gate(p, [int(v) for v in gate])
+    finally:
+        shim.svtme_shim_close(h)
