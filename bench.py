@@ -57,10 +57,13 @@ def parse():
     ap.add_argument("--gops-per-step", type=int, default=0, help="mini-GOPs streamed per step and GPU (0: about 0.1 s of device time)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--bit-depth", type=int, default=8, choices=[8, 10])
+    ap.add_argument("--tpl", action="store_true",
+                    help="fuse the TPL source-based search (src_ops_process.c:608-884) behind every picture's ME: the lookahead "
+                         "consumer of the ME results reads them in HBM (BASELINE.json configs[3])")
     a = ap.parse_args()
     if a.config:
         cfg = {1: dict(width=1920, height=1080, preset=10, hier_levels=4), 2: dict(width=1920, height=1080, preset=4, hier_levels=5),
-               3: dict(width=3840, height=2160, preset=6, hier_levels=5), 4: dict(width=3840, height=2160, preset=6, hier_levels=5, bit_depth=10),
+               3: dict(width=3840, height=2160, preset=6, hier_levels=5), 4: dict(width=3840, height=2160, preset=6, hier_levels=5, bit_depth=10, tpl=True),
                5: dict(width=7680, height=4320, preset=8, hier_levels=4)}[a.config]
         for k, v in cfg.items():
             setattr(a, k, v)
@@ -105,6 +108,22 @@ class Workload:
             k0.max_l0, k0.max_refs - k0.max_l0)
         self.units, self.unit, self.extended = self.gop, "pictures", False
         self.metric = "ME pictures/sec at 4K"
+        self.tpl = bool(getattr(args, "tpl", False)) and args.mode == "me"
+        if self.tpl:
+            # TPL controls of the preset: level 4 up to M8 (16x16 blocks), level 5 above (32x32 blocks); both SAD / FULL_PEL / DC
+            # (get_tpl_params_level + set_tpl_params, initial_rc_process.c:279-374).  Every reference lies in the TPL group.
+            from svtme import abi
+            self.tpl_cfgs = []
+            for poc, k, l0, l1 in self.pics:
+                c = abi.TplCfg()
+                c.dispenser_search_level = 0 if args.preset <= 8 else 1
+                c.use_sad_in_src_search = c.subpel_full_pel = c.intra_dc_only = 1
+                c.disable_intra_pred = int(k.temporal_layer_index == self.hl)  # disable_intra_pred_nref, src_ops_process.c:567
+                for li, lst in enumerate((l0, l1)):
+                    for ri, q in enumerate(lst):
+                        c.ref_poc[li][ri] = q
+                self.tpl_cfgs.append(c)
+            self.name += ", TPL source-based search fused behind each picture's ME"
         self.needed = list(range(self.n_frames))  # pictures a step uploads: the whole mini-GOP + its leading base picture
         if args.mode == "tf":
             # The temporal filter's motion searches in this mini-GOP: the filtered (centre) pictures are the leading
@@ -159,7 +178,7 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def run_step_device(dev, wl, d_luma, inflight, gops, handoff=None):
+def run_step_device(dev, wl, d_luma, inflight, gops, handoff=None, tpl_bufs=None):
     """Device-resident step: `gops` mini-GOPs streamed back to back -- every picture registered from HBM-resident luma
     (copy, pad, decimate), searched in decode order with `inflight` searches in flight across the mini-GOP boundaries;
     results stay in HBM.  With several ranks the leading base picture of the step arrives from the previous rank."""
@@ -167,21 +186,25 @@ def run_step_device(dev, wl, d_luma, inflight, gops, handoff=None):
     first = handoff() if handoff else None
     pending, live = [], []
 
-    def submit(items, pics, window):
-        for poc, k, l0, l1 in items:
+    def submit(items, pics, window, g=0):
+        for n, (poc, k, l0, l1) in enumerate(items):
             refs = {(0, i): pics[p] for i, p in enumerate(l0)}
             refs.update({(1, i): pics[p] for i, p in enumerate(l1)})
             if len(pending) >= window:
                 dev.wait(pending.pop(0))
-            pending.append(dev.search_device_async(k, pics[poc], refs))
+            if wl.tpl:  # ME results stay in HBM; the (small) TPL decisions come back: they are what the lookahead reads
+                pending.append(dev.search_tpl_async(k, pics[poc], refs, wl.tpl_cfgs[n], want_me=False,
+                                                    tpl=tpl_bufs[(g & 1) * len(wl.pics) + n])[0])
+            else:
+                pending.append(dev.search_device_async(k, pics[poc], refs))
 
     for g in range(gops):
         pics = {i: dev.register_device((first if (g == 0 and i == 0 and first) else d_luma.data_ptr() + i * w * h), w, w, h, i)
                 for i in range(wl.n_frames)}
         live.append(pics)
         nt = SUBMIT_THREADS
-        if nt <= 1:
-            submit(wl.pics, pics, inflight)
+        if nt <= 1 or wl.tpl:
+            submit(wl.pics, pics, inflight, g)
         else:  # the encoder's ME kernel threads submit concurrently (me_process.c); the library is thread-safe
             th = [threading.Thread(target=submit, args=(wl.pics[i::nt], pics, max(1, inflight // nt))) for i in range(nt)]
             for t in th:
@@ -198,7 +221,7 @@ def run_step_device(dev, wl, d_luma, inflight, gops, handoff=None):
             q.release()
 
 
-def run_step_host(dev, wl, h_luma, outs, inflight, gops, handoff=None):
+def run_step_host(dev, wl, h_luma, outs, inflight, gops, handoff=None, tpl_bufs=None):
     """End-to-end step through the C ABI with host buffers: H2D of each luma plane, D2H of each picture's results.
     Pictures are registered (uploaded + decimated, asynchronously) in the order the searches need them, so the uploads
     of later pictures overlap the searches of earlier ones; every picture of a mini-GOP is uploaded exactly once, and
@@ -225,7 +248,11 @@ def run_step_host(dev, wl, h_luma, outs, inflight, gops, handoff=None):
             cur = pic(poc)
             if len(pending) >= inflight:
                 dev.wait(pending.pop(0))
-            pending.append(dev.search_async(k, cur, refs, out=outs[(g & 1) * len(wl.pics) + n])[0])  # two sets of result buffers alternate
+            slot = (g & 1) * len(wl.pics) + n  # two sets of result buffers alternate
+            if wl.tpl:
+                pending.append(dev.search_tpl_async(k, cur, refs, wl.tpl_cfgs[n], out=outs[slot], tpl=tpl_bufs[slot])[0])
+            else:
+                pending.append(dev.search_async(k, cur, refs, out=outs[slot])[0])
         for i in wl.needed:  # a picture of the workload that no search touched still counts as uploaded
             pic(i)
         if len(live) > 1:
@@ -290,6 +317,8 @@ def reference_arm(wl, steps, warmup, seconds=None, threads=None, one_core=True):
     cb = {"value": pps, "unit": wl.unit + "/s", "cores": cores, "kind": kind,
           "sample": "%d mini-GOP(s) of the workload (%d searches + %d decimations each) in %.1f s, %s, %d threads on one work queue" % (
               steps, len(items), len(build), dt, what, cores)}
+    if wl.tpl:  # the compiled reference has no stand-alone TPL entry: the CPU figure is ME alone, i.e. LESS work than the GPU arm does
+        cb["sample"] += "; ME only -- the TPL source-based search the GPU arm adds is not in this CPU figure"
     if one_core:  # the same code on ONE host thread, on a few searches spread over the temporal layers
         idx = sorted(set(int(round(i * (len(items) - 1) / 3)) for i in range(4)))
         t1 = time.perf_counter()
@@ -627,6 +656,10 @@ def main():
     outs = [abi.ResultBuffers(n_b64, k, extended=wl.extended, pinned_alloc=pinned, tf_compact=(args.mode == "tf"))
             for _ in range(2) for _, k, _, _ in wl.pics]  # two sets: consecutive mini-GOPs of a step alternate
     d2h = sum(o.nbytes() for o in outs[:len(wl.pics)]) * G
+    tpl_bufs = None
+    if wl.tpl:
+        tpl_bufs = [abi.TplBuffers(w, h, alloc=pinned) for _ in range(2) for _ in wl.pics]
+        d2h += sum(t.nbytes() for t in tpl_bufs[:len(wl.pics)]) * G
     h2d = len(wl.needed) * w * h * (2 if wl.bit_depth == 10 else 1) * G
 
     def barrier():
@@ -659,8 +692,8 @@ def main():
         return d_recv.data_ptr() if got else None
 
     hand = handoff if world > 1 else None
-    step_dev = lambda: run_step_device(dev, wl, d_luma, args.inflight, G, hand)  # noqa: E731
-    step_host = lambda: run_step_host(dev, wl, h_luma, outs, args.inflight, G, hand)  # noqa: E731
+    step_dev = lambda: run_step_device(dev, wl, d_luma, args.inflight, G, hand, tpl_bufs)  # noqa: E731
+    step_host = lambda: run_step_host(dev, wl, h_luma, outs, args.inflight, G, hand, tpl_bufs)  # noqa: E731
     if world > 1:
         handoff()
         if rank > 0 and not torch.equal(d_recv, d_luma[0]):

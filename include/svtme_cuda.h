@@ -370,6 +370,63 @@ typedef struct SvtMePicStats {
 } SvtMePicStats;
 int32_t svtme_picture_statistics(SvtMeHandle *h, SvtMePic *pic, uint32_t regions_per_width, uint32_t regions_per_height,
                                  uint32_t decim_step, SvtMePicStats *out);
+/*
+ * TPL source-based search.  Replaces: the `tpl_src_data_ready == 0` decision of
+ * tpl_mc_flow_dispenser_sb_generic (src_ops_process.c:608-884) for every TPL block of a picture -- the direct consumer of
+ * me_mv_array / me_candidate_array:
+ *   intra: the DC predictor of the block from its source neighbours (intra_dc_sad_path, :623-660: get_neighbor_samples_dc /
+ *          svt_aom_update_neighbor_samples_array_open_loop_mb with the 127 / 129 fill outside the picture,
+ *          svt_aom_dc_pred[x > 0][y > 0], intra_prediction.c:1034-1073, 2588) and its SAD against the source;
+ *   inter: every single-reference ME candidate of the co-located ME block (:759-772), full-pel MV clamped so that the block
+ *          stays within TPL_PADX / TPL_PADY = 32 pixels of the reference (:792-802), svt_nxm_sad_kernel against the
+ *          reference's source plane (:851-858), first-best-wins (:874-883);
+ *   decision: NEWMV when best_inter_cost < best_intra_cost, else DC_PRED (:886-887).
+ * Blocks are 16x16 / 32x32 / 64x64 (dispenser_search_level 0 / 1 / 2) inside complete 64x64 blocks and 16x16 inside incomplete
+ * ones (:2048-2050); a block less than half inside the picture is skipped (:584-586).  Results are indexed like the
+ * reference's tpl_src_stats_buffer: cell (y >> 4) * grid_width + (x >> 4) of the block origin, grid_width =
+ * (width + 15) >> 4 (:561, 603-604).
+ *
+ * Supported controls: use_sad_in_src_search = 1, subpel_depth = FULL_PEL, intra_mode_end = DC_PRED, in_loop_ois = 1 -- TPL
+ * levels 4 and 5 of set_tpl_params (initial_rc_process.c:351-374), i.e. presets M3..M13 of v3.0.2 (get_tpl_params_level,
+ * :279-292).  Anything else (SATD cost, sub-pel refinement, the PAETH intra sweep of M0-M2) is refused with an error, never
+ * approximated.  The transform / quantisation that follows the decision (srcrf_dist, :888-956) stays on the host: one block
+ * per decision instead of one per candidate.
+ */
+#define SVTME_TPL_DC_PRED 0   /* PredictionMode DC_PRED (definitions.h:1127) */
+#define SVTME_TPL_NEWMV  16   /* PredictionMode NEWMV   (definitions.h:1143) */
+typedef struct SvtMeTplCfg {
+    uint8_t  dispenser_search_level;  /* tpl_ctrls.dispenser_search_level */
+    uint8_t  use_sad_in_src_search;   /* must be 1 */
+    uint8_t  subpel_full_pel;         /* must be 1: tpl_ctrls.subpel_depth == FULL_PEL */
+    uint8_t  intra_dc_only;           /* must be 1: tpl_ctrls.intra_mode_end == DC_PRED && scs->in_loop_ois */
+    uint8_t  disable_intra_pred;      /* tpl_ctrls.disable_intra_pred_nref && temporal_layer_index == hierarchical_levels (:567) */
+    uint8_t  slice_type_i;            /* pcs->slice_type == I_SLICE: no inter candidates (:767) */
+    uint8_t  ref_excluded[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST]; /* ref_tpl_group_idx > 0 && !base_pcs->tpl_valid_pic[idx] (:783-785) */
+    uint64_t ref_poc[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST];      /* tpl_ref_ds_ptr_array[l][r].picture_number (:879) */
+} SvtMeTplCfg;
+typedef struct SvtMeTplResults {
+    uint32_t  grid_width;       /* in: capacity check, (width + 15) >> 4 */
+    uint32_t  grid_height;      /* in: (height + 15) >> 4 */
+    uint8_t  *block_size;       /* [cell] 16 / 32 / 64 where a searched block starts, else 0 (the other arrays are 0 there) */
+    uint8_t  *best_mode;        /* [cell] SVTME_TPL_DC_PRED / SVTME_TPL_NEWMV      -> TplSrcStats.best_mode */
+    int8_t   *best_rf_idx;      /* [cell] list * 4 + index of the winner, -1: none -> TplSrcStats.best_rf_idx */
+    int16_t  *mv;               /* [cell][2] row, col in 1/8 pel                   -> TplSrcStats.mv */
+    uint64_t *ref_frame_poc;    /* [cell]                                          -> TplSrcStats.ref_frame_poc */
+    uint32_t *best_inter_cost;  /* [cell] 0xFFFFFFFF: no candidate (INT64_MAX in the reference) */
+    uint32_t *best_intra_cost;  /* [cell] 0xFFFFFFFF: intra prediction disabled */
+} SvtMeTplResults;
+/* Open-loop ME of the picture (exactly svtme_picture_search) followed, on the same stream, by the TPL source-based search over
+ * the ME results while they are still in HBM: TPL's references are the ME references (tpl_regular_setup_me_refs,
+ * src_ops_process.c:111-144 links the same EbPaReferenceObject.input_padded_pic).  `out` may be NULL when only the TPL
+ * decisions are wanted.  Asynchronous; both result sets are filled when svtme_search_wait() returns. */
+int32_t svtme_picture_search_tpl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
+                                 const SvtMeKnobs *knobs, SvtMePictureResults *out, const SvtMeTplCfg *tpl, SvtMeTplResults *tpl_out,
+                                 uint64_t *ticket);
+/* The same search over ME results the caller already holds (`me`: me_mv, me_cand, total_me_candidate_index of a finished
+ * svtme_picture_search with the same knobs; they are uploaded).  For a TPL pass that runs long after ME.  Asynchronous. */
+int32_t svtme_tpl_src_search(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
+                             const SvtMeKnobs *knobs, const SvtMePictureResults *me, const SvtMeTplCfg *tpl, SvtMeTplResults *tpl_out,
+                             uint64_t *ticket);
 /* Diagnostic: measured peak issue rate of the packed-byte SAD instruction (VABSDIFF4.U8.ACC, 4 pixel-compares per
  * lane) on this device, in 1e9 instructions per second; the INT-roofline denominator of DESIGN.md. */
 int32_t svtme_measure_sad_peak(SvtMeHandle *h, double *gsad4_per_s);

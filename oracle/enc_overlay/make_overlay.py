@@ -3,7 +3,7 @@
 
     make_overlay.py <reference root> <out dir>
 
-Reads  <ref>/Source/Lib/Codec/me_process.c  and  <ref>/Source/Lib/Codec/global_me.c, inserts the calls into
+Reads  <ref>/Source/Lib/Codec/{me_process.c, global_me.c, src_ops_process.c}, inserts the calls into
 oracle/enc_overlay/me_dump.c listed in HOOKS below, and writes the results into <out dir> (oracle/_ref/enc/, git-ignored).
 The copies exist only there; no reference source is committed.  Every anchor must match exactly once, else the script
 fails: a reference update that moves the code is noticed instead of silently dumping nothing.
@@ -16,6 +16,7 @@ DECLS = (
     "struct SequenceControlSet; struct PictureParentControlSet; struct MeContext; struct EbPictureBufferDesc;\n"
     "void svtme_dump_pre_sb(struct PictureParentControlSet *pcs, unsigned b64);\n"
     "void svtme_dump_gm_level(struct PictureParentControlSet *pcs, unsigned char level);\n"
+    "void svtme_dump_tpl(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs);\n"
     "void svtme_dump_picture(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs, struct MeContext *ctx,\n"
     "                        struct EbPictureBufferDesc *input_pic);\n"
 )
@@ -31,6 +32,8 @@ HOOKS = [
     # global_me.c:206 -- after the bypass test, before the level is used
     ("global_me.c", "if (global_motion_estimation_level) {", "svtme_dump_gm_level(pcs, global_motion_estimation_level);\n",
      "before"),
+    # src_ops_process.c:1396 -- every SB of the picture went through tpl_mc_flow_dispenser_sb_generic
+    ("src_ops_process.c", "svt_block_on_semaphore(pcs->tpl_disp_done_semaphore);", "svtme_dump_tpl(scs, pcs);\n", "after"),
 ]
 
 
@@ -45,6 +48,8 @@ def patch(name, text):
         i = hits[0]
         if where == "before":
             lines.insert(i, ins)
+        elif where == "after":
+            lines.insert(i + 1, ins)
         elif where == "after_closing_brace":
             j = i + 1
             while lines[j].strip() != "}":
@@ -61,7 +66,7 @@ def patch(name, text):
 def main():
     ref, out = pathlib.Path(sys.argv[1]), pathlib.Path(sys.argv[2])
     out.mkdir(parents=True, exist_ok=True)
-    for name in ("me_process.c", "global_me.c"):
+    for name in ("me_process.c", "global_me.c", "src_ops_process.c"):
         src = (ref / "Source/Lib/Codec" / name).read_text()
         (out / name).write_text(patch(name, src))
         print(f"overlay {out / name}")

@@ -125,3 +125,113 @@ void svtme_dump_picture(SequenceControlSet *scs, PictureParentControlSet *pcs, M
     free(mem);
     g_gm_level = g_gm_ds = -1;
 }
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * TPL source-based search (src_ops_process.c:608-968): with SVTME_DUMP_TPL=<file>, every picture whose source path was
+ * just computed (tpl_src_data_ready == 0) is serialised after its last SB (hook behind the tpl_disp_done_semaphore wait
+ * of tpl_mc_flow_dispenser, src_ops_process.c:1396).  Record:
+ *   THDR  uint64 picture_number; uint32 width, height (enhanced_pic), aligned_width, b64_total_count, pu_count, slice_type,
+ *         temporal_layer_index, hierarchical_levels, enable_me_16x16, max_cand, max_refs, max_l0, dispenser_search_level,
+ *         disable_intra_pred_nref, intra_mode_end, use_sad_in_src_search, subpel_depth, subsample_tx, tpl_lad_mg, in_loop_ois,
+ *         ref_list0_count_try, ref_list1_count_try
+ *   TREF  per [2][4]: uint64 picture_number, int32 ref_tpl_group_idx, uint32 excluded (src_ops_process.c:783-785),
+ *         uint32 present, uint32 max_width, max_height
+ *   TCUR / T<l><i>0   luma of pcs->enhanced_pic / of tpl_ref_ds_ptr_array[l][i].picture_ptr, tight rows
+ *   TME   the picture's ME results, flat (svtme_shim_results_layout)
+ *   TSRC  per 16x16 grid cell [(height+15)/16][(aligned_width+15)/16]: int16 mv_row, mv_col; int32 best_rf_idx;
+ *         uint64 ref_frame_poc; uint8 best_mode, best_intra_mode, pad[2]   (TplSrcStats, coding_unit.h:323-331)
+ */
+static FILE *g_tf;
+static int   g_ttried;
+
+static void tchunk(const char *tag, const void *p, uint32_t n) {
+    fwrite(tag, 1, 4, g_tf);
+    fwrite(&n, 4, 1, g_tf);
+    if (n) fwrite(p, 1, n, g_tf);
+}
+static void tplane(const char *tag, const EbPictureBufferDesc *d, uint32_t w, uint32_t h) {
+    uint8_t *tight = (uint8_t *)malloc((size_t)w * h);
+    for (uint32_t y = 0; y < h; y++)
+        memcpy(tight + (size_t)y * w, d->buffer_y + (size_t)(d->org_y + y) * d->stride_y + d->org_x, w);
+    tchunk(tag, tight, w * h);
+    free(tight);
+}
+
+void svtme_dump_tpl(SequenceControlSet *scs, PictureParentControlSet *pcs) {
+    if (!g_ttried) {
+        g_ttried       = 1;
+        const char *fn = getenv("SVTME_DUMP_TPL");
+        if (fn && *fn) g_tf = fopen(fn, "wb");
+    }
+    if (!g_tf || pcs->tpl_src_data_ready || scs->tpl_lad_mg == 0) return;
+    const EbPictureBufferDesc *in  = pcs->enhanced_pic;
+    const uint32_t             pus = svtme_shim_pu_count(pcs);
+    struct {
+        uint64_t picture_number;
+        uint32_t v[23];
+    } h = {pcs->picture_number,
+           {in->width, in->height, pcs->aligned_width, pcs->b64_total_count, pus, (uint32_t)pcs->slice_type,
+            pcs->temporal_layer_index, pcs->hierarchical_levels, pcs->enable_me_16x16, pcs->pa_me_data->max_cand,
+            pcs->pa_me_data->max_refs, pcs->pa_me_data->max_l0, pcs->tpl_ctrls.dispenser_search_level,
+            pcs->tpl_ctrls.disable_intra_pred_nref, (uint32_t)pcs->tpl_ctrls.intra_mode_end, pcs->tpl_ctrls.use_sad_in_src_search,
+            (uint32_t)pcs->tpl_ctrls.subpel_depth, pcs->tpl_ctrls.subsample_tx, scs->tpl_lad_mg, scs->in_loop_ois,
+            pcs->ref_list0_count_try, pcs->ref_list1_count_try, 0}};
+    tchunk("THDR", &h, sizeof(h));
+    struct {
+        uint64_t picture_number;
+        int32_t  group_idx;
+        uint32_t excluded, present, max_width, max_height, pad;
+    } r[2][4];
+    memset(r, 0, sizeof(r));
+    tplane("TCUR", in, in->width, in->height);
+    const uint32_t n_list = pcs->slice_type == I_SLICE ? 0 : 2;
+    for (uint32_t li = 0; li < n_list; li++) {
+        const uint32_t cnt = li == 0 ? pcs->ref_list0_count_try : (pcs->slice_type == B_SLICE ? pcs->ref_list1_count_try : 0);
+        for (uint32_t ri = 0; ri < cnt && ri < 4; ri++) {
+            const EbPictureBufferDesc *d = (const EbPictureBufferDesc *)pcs->tpl_data.tpl_ref_ds_ptr_array[li][ri].picture_ptr;
+            const int32_t              g = pcs->tpl_data.ref_tpl_group_idx[li][ri];
+            r[li][ri].picture_number     = pcs->tpl_data.tpl_ref_ds_ptr_array[li][ri].picture_number;
+            r[li][ri].group_idx          = g;
+            r[li][ri].excluded           = g > 0 && pcs->tpl_data.base_pcs->tpl_valid_pic[g] == 0;
+            r[li][ri].present            = d != NULL;
+            if (d) {
+                char tag[5];
+                snprintf(tag, sizeof(tag), "T%u%u0", li, ri);
+                r[li][ri].max_width  = d->max_width;
+                r[li][ri].max_height = d->max_height;
+                tplane(tag, d, in->width, in->height);
+            }
+        }
+    }
+    tchunk("TREF", r, sizeof(r));
+    if (pcs->slice_type != I_SLICE) {
+        SvtMePictureResults res;
+        const size_t bytes = svtme_shim_results_layout(&res, pcs->b64_total_count, pus, pcs->pa_me_data->max_refs,
+                                                       pcs->pa_me_data->max_cand, NULL);
+        void        *mem   = calloc(1, bytes);
+        svtme_shim_results_layout(&res, pcs->b64_total_count, pus, pcs->pa_me_data->max_refs, pcs->pa_me_data->max_cand, mem);
+        svtme_shim_gather_results(pcs, &res);
+        tchunk("TME ", mem, (uint32_t)bytes);
+        free(mem);
+    }
+    const uint32_t gw = (pcs->aligned_width + 15) >> 4, gh = (in->height + 15) >> 4;
+    struct Cell {
+        int16_t  mv_row, mv_col;
+        int32_t  best_rf_idx;
+        uint64_t ref_frame_poc;
+        uint8_t  best_mode, best_intra_mode, pad[6];
+    } *cells = (struct Cell *)calloc((size_t)gw * gh, sizeof(struct Cell));
+    for (uint32_t i = 0; i < gw * gh; i++) {
+        const TplSrcStats *s   = &pcs->pa_me_data->tpl_src_stats_buffer[i];
+        cells[i].mv_row        = s->mv.row;
+        cells[i].mv_col        = s->mv.col;
+        cells[i].best_rf_idx   = s->best_rf_idx;
+        cells[i].ref_frame_poc = s->ref_frame_poc;
+        cells[i].best_mode     = s->best_mode;
+        cells[i].best_intra_mode = (uint8_t)s->best_intra_mode;
+    }
+    tchunk("TSRC", cells, (uint32_t)((size_t)gw * gh * sizeof(struct Cell)));
+    tchunk("END ", NULL, 0);
+    fflush(g_tf);
+    free(cells);
+}

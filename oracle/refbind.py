@@ -213,6 +213,23 @@ class Oracle(_Binding):
         super().__init__(_load(os.path.join(HERE, "libsvtme_oracle.so"), "oracle restatement"), "svtorc_")
         self.lib.svtorc_last_px_compares.restype = C.c_uint64
 
+    def tpl_src_search(self, cfg, knobs, cur, refs, me):
+        """cfg: abi.TplCfg, me: abi.ResultBuffers of this picture's ME (None for an I picture).  Returns abi.TplBuffers."""
+        f = self.lib.svtorc_tpl_src_search
+        f.argtypes = [C.POINTER(abi.TplCfg), C.POINTER(abi.Knobs), C.POINTER(RefPic), C.POINTER(RefPic),
+                      C.POINTER(abi.PictureResults), C.POINTER(abi.TplResults)]
+        out = abi.TplBuffers(cur.width, cur.height)
+        arr = (RefPic * 8)()
+        for (li, ri), p in refs.items():
+            arr[li * 4 + ri] = p.struct
+        if me is None:
+            n_b64 = ((cur.width + 63) // 64) * ((cur.height + 63) // 64)
+            me = abi.ResultBuffers(n_b64, knobs, extended=False)
+        rc = f(C.byref(cfg), C.byref(knobs), C.byref(cur.struct), arr, C.byref(me.struct), C.byref(out.struct))
+        if rc != 0:
+            raise RuntimeError("tpl_src_search failed: %d" % rc)
+        return out
+
     def last_px_compares(self):
         """Pixel-compares of the last me_picture call (the algorithmic work C_alg of SURVEY.md section 8d)."""
         return int(self.lib.svtorc_last_px_compares())

@@ -42,6 +42,8 @@ struct PicBuffer {
     size_t      bytes = 0;
     uint32_t    w = 0, h = 0;
     cudaEvent_t free_ev = nullptr;  // recorded at release, after every reader of the previous owner: the next owner waits on it
+    uint16_t   *staging16 = nullptr;  // 10-bit uploads land here before the unpack kernel; allocated on the first such upload
+                                      // and kept with the buffer (a cudaMalloc / cudaFree pair per picture serialises the device)
     bool        recycled = false;
     unsigned char (*maps)[kTmapBytes] = nullptr;  // host: the kS16Classes x kS16HClasses CUtensorMaps of the sixteenth plane (64-byte aligned)
 };
@@ -89,7 +91,27 @@ struct Inflight {
     float               ms = 0.f;
     unsigned long long *h_px = nullptr;  // pinned
     unsigned long long  px = 0;
+    // TPL source-based search of the same picture (svtme_picture_search_tpl / svtme_tpl_src_search)
+    uint8_t            *d_tpl = nullptr, *h_tpl = nullptr;
+    size_t              tpl_cap = 0, tpl_cells = 0;
+    SvtMeTplResults     tpl_user{};
+    bool                tpl_to_host = false;
 };
+
+// device / pinned arena of one picture's TPL decisions: the seven SvtMeTplResults arrays, each 16-byte aligned
+struct TplLayout {
+    size_t off[7], bytes[7], total;
+};
+inline void tpl_layout(size_t cells, TplLayout *L) {
+    const size_t elem[7] = {1, 1, 1, 4, 8, 4, 4};  // block_size, best_mode, best_rf_idx, mv[2], ref_frame_poc, inter, intra
+    size_t off = 0;
+    for (int i = 0; i < 7; i++) {
+        off = (off + 15) & ~size_t(15);
+        L->off[i] = off; L->bytes[i] = elem[i] * cells;
+        off += L->bytes[i];
+    }
+    L->total = (off + 15) & ~size_t(15);
+}
 
 }  // namespace
 
@@ -282,14 +304,32 @@ int validate_knobs(SvtMeHandle *h, const SvtMeKnobs *k, uint32_t pu_count) {
 }
 
 int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
-                const SvtMeKnobs *knobs, SvtMePictureResults *out, uint32_t pu_count_dev, bool extended, uint64_t *ticket) {
+                const SvtMeKnobs *knobs, SvtMePictureResults *out, uint32_t pu_count_dev, bool extended, uint64_t *ticket,
+                const SvtMeTplCfg *tpl = nullptr, SvtMeTplResults *tpl_out = nullptr, const SvtMePictureResults *me_in = nullptr) {
     if (!h || !cur || !refs || !knobs || !ticket) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    if (tpl) {  // the controls this kernel restates (include/svtme_cuda.h); anything else is refused, not approximated
+        if (!tpl_out) return fail(h, SVTME_ERR_BAD_PARAMETER, "tpl_out is NULL");
+        if (knobs->me_type == SVTME_ME_MCTF) return fail(h, SVTME_ERR_BAD_PARAMETER, "TPL search needs open-loop ME results");
+        if (!tpl->use_sad_in_src_search || !tpl->subpel_full_pel || !tpl->intra_dc_only)
+            return fail(h, SVTME_ERR_BAD_PARAMETER, "TPL source search supports use_sad_in_src_search = 1, subpel_depth = FULL_PEL, intra_mode_end = DC_PRED only");
+        if (tpl->dispenser_search_level > 2 || (tpl->dispenser_search_level == 2 && !knobs->enable_me_16x16))
+            return fail(h, SVTME_ERR_BAD_PARAMETER, "TPL dispenser_search_level");
+        if (tpl_out->grid_width < ((cur->width + 15) >> 4) || tpl_out->grid_height < ((cur->height + 15) >> 4))
+            return fail(h, SVTME_ERR_BAD_PARAMETER, "TPL result grid too small");
+        if (!tpl_out->block_size || !tpl_out->best_mode || !tpl_out->best_rf_idx || !tpl_out->mv || !tpl_out->ref_frame_poc ||
+            !tpl_out->best_inter_cost || !tpl_out->best_intra_cost)
+            return fail(h, SVTME_ERR_BAD_PARAMETER, "TPL result arrays");
+        if (me_in && (!me_in->me_mv || !me_in->me_cand || !me_in->total_me_candidate_index))
+            return fail(h, SVTME_ERR_BAD_PARAMETER, "ME results to search over");
+    }
     const uint32_t wb = (cur->width + 63) / 64, hb = (cur->height + 63) / 64, n_b64 = wb * hb;
-    const uint32_t pu_count = out ? out->pu_count : pu_count_dev;
-    int rc = validate_knobs(h, knobs, pu_count);
+    const uint32_t pu_count = me_in ? me_in->pu_count : out ? out->pu_count : pu_count_dev;
+    const bool intra_only_tpl = tpl && me_in && tpl->slice_type_i;  // an I picture: no lists, no candidates, nothing of ME is read
+    int rc = intra_only_tpl ? SVTME_OK : validate_knobs(h, knobs, pu_count);
     if (rc) return rc;
     if (out && out->b64_total_count < n_b64) return fail(h, SVTME_ERR_BAD_PARAMETER, "b64_total_count too small");
-    for (int l = 0; l < knobs->num_of_list_to_search; l++)
+    const int n_lists = intra_only_tpl ? 0 : knobs->num_of_list_to_search;
+    for (int l = 0; l < n_lists; l++)
         for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) {
             if (!refs[l][r]) return fail(h, SVTME_ERR_BAD_PARAMETER, "missing reference picture");
             if (refs[l][r]->width != cur->width || refs[l][r]->height != cur->height) return fail(h, SVTME_ERR_BAD_PARAMETER, "reference size differs");
@@ -339,12 +379,26 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
         if (e != cudaSuccess) return release_slot(fail(h, SVTME_ERR_INSUFFICIENT, "block state arena", e));
         sl->states_cap = staged_state_bytes(n_b64);
     }
+    TplLayout TL{};
+    if (tpl) {
+        sl->tpl_cells = (size_t)tpl_out->grid_width * tpl_out->grid_height;
+        tpl_layout(sl->tpl_cells, &TL);
+        if (sl->tpl_cap < TL.total) {
+            if (sl->d_tpl) cudaFree(sl->d_tpl);
+            if (sl->h_tpl) cudaFreeHost(sl->h_tpl);
+            sl->d_tpl = nullptr; sl->h_tpl = nullptr; sl->tpl_cap = 0;
+            cudaError_t e = cudaMalloc(&sl->d_tpl, TL.total);
+            if (e == cudaSuccess) e = cudaMallocHost(&sl->h_tpl, TL.total);
+            if (e != cudaSuccess) return release_slot(fail(h, SVTME_ERR_INSUFFICIENT, "TPL result arena", e));
+            sl->tpl_cap = TL.total;
+        }
+    }
     MeParams p;
     memset(&p, 0, sizeof(p));
     S16Maps *maps = &sl->maps;  // unused entries keep whatever they held: the kernel only reads the maps of the picture's references
     p.k   = *knobs;
     p.cur = cur->dev;
-    for (int l = 0; l < knobs->num_of_list_to_search; l++)
+    for (int l = 0; l < n_lists; l++)
         for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) {
             p.refs[l][r] = refs[l][r]->dev;
             memcpy(maps->m[l * kMaxRefs + r], refs[l][r]->buf.maps, sizeof(maps->m[0]));
@@ -375,15 +429,61 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
     }
     cudaStream_t st = sl->stream;
     cudaError_t  e  = cudaStreamWaitEvent(st, cur->ready, 0);
-    for (int l = 0; l < knobs->num_of_list_to_search && e == cudaSuccess; l++)
+    for (int l = 0; l < n_lists && e == cudaSuccess; l++)
         for (int r = 0; r < knobs->num_of_ref_pic_to_search[l] && e == cudaSuccess; r++) e = cudaStreamWaitEvent(st, refs[l][r]->ready, 0);
     if (e == cudaSuccess) e = cudaMemsetAsync(sl->d_counter, 0, 64 + kQueueCounterBytes, st);
     if (e == cudaSuccess && p.out.tf_blk_counts) e = cudaMemsetAsync(p.out.tf_blk_counts, 0, 8, st);
     if (e == cudaSuccess && p.out.picture_sums) e = cudaMemsetAsync(p.out.picture_sums, 0, L.bytes[R_PSUM], st);
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_start, st);
     int n_launch = 0;
-    if (e == cudaSuccess) e = launch_me_picture_staged(p, *maps, h->sm_count, st, &n_launch);
+    if (intra_only_tpl) {
+    } else if (me_in) {  // TPL over ME results the caller holds: they take the place the search kernels would have written
+        const size_t nb = n_b64;
+        if (e == cudaSuccess) e = cudaMemcpyAsync(p.out.me_mv, me_in->me_mv, nb * pu_count * knobs->max_refs * 4, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(p.out.me_cand, me_in->me_cand, nb * pu_count * knobs->max_cand, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(p.out.total_me_candidate_index, me_in->total_me_candidate_index, nb * pu_count, cudaMemcpyHostToDevice, st);
+    } else if (e == cudaSuccess) e = launch_me_picture_staged(p, *maps, h->sm_count, st, &n_launch);
+    sl->tpl_to_host = false;
+    if (tpl && e == cudaSuccess) {
+        svtme::TplParams t;
+        memset(&t, 0, sizeof(t));
+        t.cur = cur->dev;
+        for (int l = 0; l < n_lists; l++)
+            for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) {
+                t.refs[l][r] = refs[l][r]->dev;
+                if (tpl->ref_excluded[l][r]) t.ref_excluded |= 1u << (l * 4 + r);
+                t.ref_poc[l * 4 + r] = tpl->ref_poc[l][r];
+            }
+        t.me_mv = p.out.me_mv; t.me_cand = p.out.me_cand; t.me_count = p.out.total_me_candidate_index;
+        t.pus = pu_count; t.max_refs = knobs->max_refs; t.max_cand = knobs->max_cand; t.max_l0 = knobs->max_l0;
+        t.wb = wb; t.hb = hb; t.grid_width = tpl_out->grid_width;
+        t.level = tpl->dispenser_search_level; t.disable_intra_pred = tpl->disable_intra_pred;
+        t.slice_type_i = tpl->slice_type_i; t.enable_me_16x16 = knobs->enable_me_16x16;
+        uint8_t *b = sl->d_tpl;
+        t.block_size = b + TL.off[0]; t.best_mode = b + TL.off[1]; t.best_rf_idx = (int8_t *)(b + TL.off[2]);
+        t.mv = (int16_t *)(b + TL.off[3]); t.ref_frame_poc = (uint64_t *)(b + TL.off[4]);
+        t.best_inter_cost = (uint32_t *)(b + TL.off[5]); t.best_intra_cost = (uint32_t *)(b + TL.off[6]);
+        e = cudaMemsetAsync(sl->d_tpl, 0, TL.total, st);
+        if (e == cudaSuccess) e = svtme::launch_tpl_src(t, st);
+        n_launch += 1;
+        sl->tpl_user = *tpl_out;
+    }
     if (e == cudaSuccess) e = cudaEventRecord(sl->ev_kernel, st);
+    if (tpl && e == cudaSuccess) {
+        // caller buffers laid out like the arena (one block, fields 16-byte aligned in order) and page-locked: one copy
+        // straight into them; otherwise through the slot's pinned arena, scattered by svtme_search_wait
+        uint8_t *base = tpl_out->block_size;
+        const void *dst[7] = {tpl_out->block_size, tpl_out->best_mode, tpl_out->best_rf_idx, tpl_out->mv, tpl_out->ref_frame_poc,
+                              tpl_out->best_inter_cost, tpl_out->best_intra_cost};
+        bool direct = true;
+        for (int i = 0; i < 7; i++) direct = direct && dst[i] == base + TL.off[i];
+        if (direct) {
+            cudaPointerAttributes pa;
+            if (!(cudaPointerGetAttributes(&pa, base) == cudaSuccess && pa.type == cudaMemoryTypeHost)) { (void)cudaGetLastError(); direct = false; }
+        }
+        sl->tpl_to_host = !direct;
+        e = cudaMemcpyAsync(direct ? base : sl->h_tpl, sl->d_tpl, direct ? TL.off[6] + TL.bytes[6] : TL.total, cudaMemcpyDeviceToHost, st);
+    }
     if (e == cudaSuccess) e = cudaMemcpyAsync(sl->h_px, sl->d_counter + 2, 8, cudaMemcpyDeviceToHost, st);
     sl->to_host = out != nullptr;
     if (out) {
@@ -415,7 +515,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
         std::lock_guard<std::mutex> lk(h->mu);
         const uint64_t bit = 1ull << (sl - h->slots.data());
         cur->reader_slots |= bit;
-        for (int l = 0; l < knobs->num_of_list_to_search; l++)
+        for (int l = 0; l < n_lists; l++)
             for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) refs[l][r]->reader_slots |= bit;
         h->launches += (uint64_t)n_launch;
     }
@@ -483,13 +583,15 @@ void svtme_destroy(SvtMeHandle *h) {
         if (s.ev_done) cudaEventDestroy(s.ev_done);
         if (s.d_res) cudaFree(s.d_res);
         if (s.h_res) cudaFreeHost(s.h_res);
+        if (s.d_tpl) cudaFree(s.d_tpl);
+        if (s.h_tpl) cudaFreeHost(s.h_tpl);
         if (s.d_counter) cudaFree(s.d_counter);
         if (s.d_states) cudaFree(s.d_states);
         if (s.h_px) cudaFreeHost(s.h_px);
     }
     for (auto &s : h->up_streams)
         if (s) cudaStreamDestroy(s);
-    for (auto &b : h->free_bufs) { cudaFree(b.base); cudaEventDestroy(b.free_ev); free(b.maps); }
+    for (auto &b : h->free_bufs) { cudaFree(b.base); cudaFree(b.staging16); cudaEventDestroy(b.free_ev); free(b.maps); }
     if (h->d_scratch) cudaFree(h->d_scratch);
     if (h->d_small) cudaFree(h->d_small);
     if (h->dg_stream) { cudaStreamDestroy(h->dg_stream); cudaEventDestroy(h->dg_e0); cudaEventDestroy(h->dg_e1); cudaEventDestroy(h->dg_done); }
@@ -534,7 +636,9 @@ int32_t svtme_picture_register16(SvtMeHandle *h, uint64_t picture_number, const 
     SvtMePic *p = nullptr;
     int rc = make_pic(h, picture_number, width, height, &p);
     if (rc) return rc;
-    cudaError_t e = cudaMalloc(&p->staging16, (size_t)width * height * 2);
+    cudaError_t e = cudaSuccess;
+    if (!p->buf.staging16) e = cudaMalloc(&p->buf.staging16, (size_t)width * height * 2);  // buffers are pooled per (width, height)
+    p->staging16 = p->buf.staging16;
     if (e == cudaSuccess)
         e = cudaMemcpy2DAsync(p->staging16, (size_t)width * 2, luma16, (size_t)stride * 2, (size_t)width * 2, height, cudaMemcpyHostToDevice, p->stream);
     if (e == cudaSuccess)
@@ -640,7 +744,6 @@ int32_t svtme_picture_read_plane(SvtMeHandle *h, SvtMePic *pic, int32_t level, u
 int32_t svtme_picture_release(SvtMeHandle *h, SvtMePic *pic) {
     if (!h || !pic) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
     cudaSetDevice(h->cfg.device);
-    if (pic->staging16) { cudaEventSynchronize(pic->ready); cudaFree(pic->staging16); }
     // The buffer goes back to the pool while work that reads it may still be in flight.  The picture's own stream (its
     // upload and decimation are already in it) waits for the last thing recorded on the stream of every search slot that
     // read the picture and on the detector stream, then `free_ev` is recorded behind all of that; the buffer's next owner
@@ -654,7 +757,7 @@ int32_t svtme_picture_release(SvtMeHandle *h, SvtMePic *pic) {
         cudaEventRecord(pic->buf.free_ev, pic->stream);
         pic->buf.recycled = true;
         if (h->free_bufs.size() < h->cfg.max_pictures) h->free_bufs.push_back(pic->buf);
-        else { cudaEventSynchronize(pic->buf.free_ev); cudaFree(pic->buf.base); cudaEventDestroy(pic->buf.free_ev); free(pic->buf.maps); }
+        else { cudaEventSynchronize(pic->buf.free_ev); cudaFree(pic->buf.base); cudaFree(pic->buf.staging16); cudaEventDestroy(pic->buf.free_ev); free(pic->buf.maps); }
     }
     cudaEventDestroy(pic->ready);
     delete pic;
@@ -688,6 +791,30 @@ static Inflight *find_slot(SvtMeHandle *h, uint64_t ticket) {
     for (auto &s : h->slots)
         if (s.ticket == ticket) return &s;
     return nullptr;
+}
+
+int32_t svtme_picture_search_tpl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
+                                 const SvtMeKnobs *knobs, SvtMePictureResults *out, const SvtMeTplCfg *tpl, SvtMeTplResults *tpl_out,
+                                 uint64_t *ticket) {
+    if (!tpl || !tpl_out || !knobs) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    const bool extended = out && (out->sb_best_sad || out->sb_best_mv || out->do_ref || out->hme_sc);
+    const uint32_t pus = knobs->enable_me_16x16 ? (knobs->enable_me_8x8 ? 85u : 21u) : 5u;  // pcs.c:106-110
+    return search_impl(h, cur, refs, knobs, out, pus, extended, ticket, tpl, tpl_out, nullptr);
+}
+
+int32_t svtme_tpl_src_search(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST],
+                             const SvtMeKnobs *knobs, const SvtMePictureResults *me, const SvtMeTplCfg *tpl, SvtMeTplResults *tpl_out,
+                             uint64_t *ticket) {
+    if (!tpl || !tpl_out || !knobs) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    if (!me && !tpl->slice_type_i) return fail(h, SVTME_ERR_BAD_PARAMETER, "ME results are needed unless the picture is an I slice");
+    SvtMePictureResults none;
+    memset(&none, 0, sizeof(none));
+    static const uint8_t zero = 0;  // an I picture has no candidates: nothing of `me` is read by the kernel
+    if (!me) {
+        none.pu_count = knobs->enable_me_16x16 ? (knobs->enable_me_8x8 ? 85u : 21u) : 5u;
+        none.me_mv = (uint32_t *)&zero; none.me_cand = (uint8_t *)&zero; none.total_me_candidate_index = (uint8_t *)&zero;
+    }
+    return search_impl(h, cur, refs, knobs, nullptr, 0, false, ticket, tpl, tpl_out, me ? me : &none);
 }
 
 int32_t svtme_search_wait(SvtMeHandle *h, uint64_t ticket) {
@@ -725,6 +852,14 @@ int32_t svtme_search_wait(SvtMeHandle *h, uint64_t ticket) {
                     }
                 } else memcpy(dst[i], sl->h_res + L.off[i], L.bytes[i]);
             }
+    }
+    if (sl->tpl_to_host) {
+        TplLayout TL;
+        tpl_layout(sl->tpl_cells, &TL);
+        const SvtMeTplResults &u = sl->tpl_user;
+        void *dst[7] = {u.block_size, u.best_mode, u.best_rf_idx, u.mv, u.ref_frame_poc, u.best_inter_cost, u.best_intra_cost};
+        for (int i = 0; i < 7; i++) memcpy(dst[i], sl->h_tpl + TL.off[i], TL.bytes[i]);
+        sl->tpl_to_host = false;
     }
     {
         std::lock_guard<std::mutex> lk(h->mu);

@@ -25,6 +25,8 @@ size_t      staged_state_bytes(uint32_t n_sb);
 size_t      staged_plan_offset(uint32_t n_sb);
 size_t      staged_queue_offset(uint32_t n_sb);
 constexpr int kQueueCounterBytes = 2 * 4 * kMaxSteps;  // [count, head] per program step
+// TPL source-based search over the ME results in HBM (me_tpl.cu); the output arrays must be zeroed first
+cudaError_t launch_tpl_src(const TplParams &p, cudaStream_t st);
 // dynamic-GOP detector HME level 0 (me_dg.cu): picture-level sums accumulated by the kernel (zero them first)
 struct DgSums {
     unsigned long long tot_dist;

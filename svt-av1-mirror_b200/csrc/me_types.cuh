@@ -41,6 +41,25 @@ struct DevPic {
     uint64_t picture_number;
 };
 
+// Parameters of the TPL source-based search kernel (me_tpl.cu), passed by value.
+struct TplParams {
+    DevPic          cur;
+    DevPic          refs[kMaxLists][kMaxRefs];
+    const uint32_t *me_mv;     // [b64][pus][max_refs] of the picture's ME results, in HBM
+    const uint8_t  *me_cand;   // [b64][pus][max_cand]
+    const uint8_t  *me_count;  // [b64][pus]
+    uint32_t        pus, max_refs, max_cand, max_l0;
+    uint32_t        wb, hb, grid_width;
+    uint8_t         level, disable_intra_pred, slice_type_i, enable_me_16x16;
+    uint32_t        ref_excluded;  // bit list * 4 + index
+    uint64_t        ref_poc[kMaxLists * kMaxRefs];
+    uint8_t        *block_size, *best_mode;
+    int8_t         *best_rf_idx;
+    int16_t        *mv;
+    uint64_t       *ref_frame_poc;
+    uint32_t       *best_inter_cost, *best_intra_cost;
+};
+
 // Device result buffers of one picture (same layout as SvtMePictureResults).
 struct DevResults {
     uint32_t *me_mv;

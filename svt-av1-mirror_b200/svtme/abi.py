@@ -192,6 +192,24 @@ class DeviceCfg(C.Structure):
     ]
 
 
+TPL_DC_PRED = 0   # SVTME_TPL_DC_PRED
+TPL_NEWMV = 16    # SVTME_TPL_NEWMV
+
+
+class TplCfg(C.Structure):
+    """SvtMeTplCfg: the controls of the TPL source-based search (src_ops_process.c:519-884)."""
+    _fields_ = [("dispenser_search_level", C.c_uint8), ("use_sad_in_src_search", C.c_uint8), ("subpel_full_pel", C.c_uint8),
+                ("intra_dc_only", C.c_uint8), ("disable_intra_pred", C.c_uint8), ("slice_type_i", C.c_uint8),
+                ("ref_excluded", (C.c_uint8 * MAX_REFS_PER_LIST) * MAX_LISTS), ("ref_poc", (C.c_uint64 * MAX_REFS_PER_LIST) * MAX_LISTS)]
+
+
+class TplResults(C.Structure):
+    _fields_ = [("grid_width", C.c_uint32), ("grid_height", C.c_uint32), ("block_size", C.POINTER(C.c_uint8)),
+                ("best_mode", C.POINTER(C.c_uint8)), ("best_rf_idx", C.POINTER(C.c_int8)), ("mv", C.POINTER(C.c_int16)),
+                ("ref_frame_poc", C.POINTER(C.c_uint64)), ("best_inter_cost", C.POINTER(C.c_uint32)),
+                ("best_intra_cost", C.POINTER(C.c_uint32))]
+
+
 def pu_count_of(knobs):
     """Number of PUs stored per SB (pcs.c:106-110)."""
     if not knobs.enable_me_16x16:
@@ -259,3 +277,39 @@ class ResultBuffers:
             if n in other.arrays and not np.array_equal(self.arrays[n], other.arrays[n]):
                 bad.append(n)
         return bad
+
+
+class TplBuffers:
+    """Caller-owned host buffers of one picture's TPL source-based decisions (SvtMeTplResults) backed by numpy arrays."""
+    FIELDS = (("block_size", np.uint8, ()), ("best_mode", np.uint8, ()), ("best_rf_idx", np.int8, ()), ("mv", np.int16, (2,)),
+              ("ref_frame_poc", np.uint64, ()), ("best_inter_cost", np.uint32, ()), ("best_intra_cost", np.uint32, ()))
+
+    def __init__(self, width, height, alloc=None):
+        self.gw, self.gh = (width + 15) >> 4, (height + 15) >> 4
+        alloc = alloc or (lambda shape, dt: np.zeros(shape, dt))
+        # one arena, the arrays in SvtMeTplResults order, each 16-byte aligned: the library's own layout, so that page-locked
+        # buffers receive the whole picture's decisions in one device-to-host copy
+        cells, off, offs = self.gw * self.gh, 0, []
+        for n, dt, tail in self.FIELDS:
+            off = (off + 15) & ~15
+            offs.append(off)
+            off += cells * np.dtype(dt).itemsize * (tail[0] if tail else 1)
+        self.arena = alloc(((off + 15) & ~15,), np.uint8)
+        self.arrays = {}
+        for (n, dt, tail), o in zip(self.FIELDS, offs):
+            cnt = cells * (tail[0] if tail else 1)
+            self.arrays[n] = self.arena[o:o + cnt * np.dtype(dt).itemsize].view(dt).reshape((self.gh, self.gw) + tail)
+        s = TplResults()
+        s.grid_width, s.grid_height = self.gw, self.gh
+        for n, a in self.arrays.items():
+            setattr(s, n, a.ctypes.data_as(dict(TplResults._fields_)[n]))
+        self.struct = s
+
+    def __getitem__(self, k):
+        return self.arrays[k]
+
+    def nbytes(self):
+        return sum(a.nbytes for a in self.arrays.values())
+
+    def diff(self, other):
+        return [n for n in self.arrays if not np.array_equal(self.arrays[n], other.arrays[n])]

@@ -24,7 +24,7 @@ EXPORTS = [
     "svtme_search_px_compares", "svtme_measure_sad_peak", "svtme_launch_count", "svtme_last_error", "svtme_cuda_sad_loop_kernel", "svtme_cuda_downsample_2d",
     "svtme_cuda_nxm_sad_kernel", "svtme_cuda_fullpel_search_sblock", "svtme_dg_detector_hme_level0",
     "svtme_picture_statistics", "svtme_cuda_nxm_sad_kernel_noalloc", "svtme_picture_planes_bytes", "svtme_picture_replicate",
-    "svtme_picture_export_planes", "svtme_picture_import_planes",
+    "svtme_picture_export_planes", "svtme_picture_import_planes", "svtme_picture_search_tpl", "svtme_tpl_src_search",
 ]
 
 
@@ -93,6 +93,10 @@ def load_library():
     lib.svtme_dg_detector_hme_level0.argtypes = [vp, vp, vp, u32, C.POINTER(abi.DgMetrics), vp, vp, C.POINTER(C.c_float),
                                                  C.POINTER(u64)]
     lib.svtme_picture_statistics.argtypes = [vp, vp, u32, u32, u32, C.POINTER(abi.PicStats)]
+    lib.svtme_picture_search_tpl.argtypes = [vp, vp, refs_t, C.POINTER(abi.Knobs), C.POINTER(abi.PictureResults),
+                                             C.POINTER(abi.TplCfg), C.POINTER(abi.TplResults), C.POINTER(u64)]
+    lib.svtme_tpl_src_search.argtypes = [vp, vp, refs_t, C.POINTER(abi.Knobs), C.POINTER(abi.PictureResults),
+                                         C.POINTER(abi.TplCfg), C.POINTER(abi.TplResults), C.POINTER(u64)]
     _lib = lib
     return lib
 
@@ -281,6 +285,40 @@ class MeDevice:
         out.px_compares = self.px_compares(t)
         out.kernel_ms = self.elapsed_ms(t)
         return out
+
+    # ---- TPL source-based search (src_ops_process.c:608-884) ----
+    def search_tpl_async(self, knobs, cur, refs, tpl_cfg, out=None, want_me=True, alloc=None, tpl=None):
+        """ME of the picture + the TPL source-based decisions over the ME results still in HBM.
+        Returns (ticket, ResultBuffers | None, TplBuffers)."""
+        n_b64 = ((cur.width + 63) // 64) * ((cur.height + 63) // 64)
+        if out is None and want_me:
+            out = abi.ResultBuffers(n_b64, knobs, extended=False, pinned_alloc=alloc)
+        if tpl is None:
+            tpl = abi.TplBuffers(cur.width, cur.height, alloc=alloc)
+        arr = self._refs_array(refs)
+        ticket = C.c_uint64()
+        self._check(self.lib.svtme_picture_search_tpl(self.h, cur.ptr, C.byref(arr), C.byref(knobs),
+                                                      C.byref(out.struct) if out is not None else None, C.byref(tpl_cfg),
+                                                      C.byref(tpl.struct), C.byref(ticket)), "svtme_picture_search_tpl")
+        self._pending[ticket.value] = ((out, tpl), arr, knobs, tpl_cfg)
+        return ticket.value, out, tpl
+
+    def me_tpl_picture(self, knobs, cur, refs, tpl_cfg):
+        t, out, tpl = self.search_tpl_async(knobs, cur, refs, tpl_cfg)
+        self.wait(t)
+        return out, tpl
+
+    def tpl_src_search(self, knobs, cur, refs, tpl_cfg, me):
+        """The TPL source-based decisions over ME results the caller holds (`me`: ResultBuffers, None for an I picture)."""
+        tpl = abi.TplBuffers(cur.width, cur.height)
+        arr = self._refs_array(refs)
+        ticket = C.c_uint64()
+        self._check(self.lib.svtme_tpl_src_search(self.h, cur.ptr, C.byref(arr), C.byref(knobs),
+                                                  C.byref(me.struct) if me is not None else None, C.byref(tpl_cfg),
+                                                  C.byref(tpl.struct), C.byref(ticket)), "svtme_tpl_src_search")
+        self._pending[ticket.value] = (tpl, arr, knobs, tpl_cfg, me)
+        self.wait(ticket.value)
+        return tpl
 
     def dg_hme_level0(self, src, ref, input_resolution, per_block=True):
         """Dynamic-GOP detector HME level 0 of picture `src` against `ref` (dg_detector_hme_level0, pd_process.c:493):

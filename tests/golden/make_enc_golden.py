@@ -4,7 +4,7 @@
 
 Runs HERE only (needs /root/reference):
     make -C oracle enc                      # oracle/_ref/SvtAv1EncApp_dump: the C-only reference encoder + dump hooks
-    python tests/golden/make_enc_golden.py  # writes tests/golden/enc_m10.npz, enc_m4.npz
+    python tests/golden/make_enc_golden.py  # writes tests/golden/enc_m10.npz, enc_m4.npz, enc_m6.npz
 
 For each fixture a deterministic synthetic 4:2:0 clip (global pan + a moving patch + noise) is encoded with
 `--preset P --lp 1`; the hooks of oracle/enc_overlay/ serialise, for every picture the ME kernel searched, the planes it
@@ -21,6 +21,13 @@ npz keys:
   pic_<i>_cur1/_cur2   the encoder's own quarter / sixteenth planes of the source picture (decimation parity)
   pic_<i>_res          uint8[...] flat results in svtme_shim_results_layout order
   pic_<i>_gmc / _gate  inputs and outcome of the last-SB global-motion gate
+TPL source-based search (src_ops_process.c:608-968), one record per picture whose source path the encoder computed:
+  tpl_<i>_head         uint64[24]: picture_number, then the 23 uint32 of the THDR chunk (oracle/enc_overlay/me_dump.c)
+  tpl_<i>_refs         uint8 raw TREF chunk: per [2][4] {uint64 poc; int32 group_idx; uint32 excluded, present, max_w, max_h, pad}
+  tpl_<i>_planes       int32[9] index into `luma` of the source and of tpl_ref_ds_ptr_array[l][r] (-1)
+  tpl_<i>_me           int32: index of the pic_<j> record holding this picture's ME results (-1 for an I picture)
+  tpl_<i>_src          uint8 raw TSRC chunk: per 16x16 cell {int16 mv_row, mv_col; int32 best_rf_idx; uint64 ref_frame_poc;
+                       uint8 best_mode, best_intra_mode, pad[6]}
 """
 import hashlib
 import json
@@ -80,11 +87,13 @@ def build(name, preset, w, h, frames, extra=()):
         synth_clip(clip, w, h, frames, seed=1234 + preset)
         cmd = [str(ENC), "-i", clip, "-w", str(w), "-h", str(h), "--fps", "30", "-n", str(frames), "--preset", str(preset),
                "--lp", "1", "-b", os.path.join(td, "out.ivf"), *extra]
-        env = dict(os.environ, SVTME_DUMP=dump)
+        tdump = os.path.join(td, "tpl.dump")
+        env = dict(os.environ, SVTME_DUMP=dump, SVTME_DUMP_TPL=tdump)
         r = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if r.returncode != 0:
             sys.exit(f"encoder failed:\n{r.stdout[-2000:]}")
         recs = parse_dump(dump)
+        trecs = parse_dump(tdump)
     lumas, index, out = [], {}, {}
 
     def plane_id(buf, W, H):
@@ -114,14 +123,33 @@ def build(name, preset, w, h, frames, extra=()):
         out[f"pic_{i}_res"] = np.frombuffer(r["RES"], np.uint8)
         out[f"pic_{i}_gmc"] = np.frombuffer(r["GMC"], np.uint8)
         out[f"pic_{i}_gate"] = np.frombuffer(r["GATE"], np.uint8)
-    meta = dict(preset=preset, width=w, height=h, frames=frames, pictures=len(recs),
+    poc_to_pic = {int(out[f"pic_{i}_head"][0]): i for i in range(len(recs))}
+    trecs.sort(key=lambda r: struct.unpack_from("<Q", r["THDR"])[0])
+    for i, r in enumerate(trecs):
+        head = struct.unpack("<Q23I4x", r["THDR"])
+        W, H = head[1], head[2]
+        out[f"tpl_{i}_head"] = np.array(head, np.uint64)
+        out[f"tpl_{i}_refs"] = np.frombuffer(r["TREF"], np.uint8)
+        planes = np.full(9, -1, np.int32)
+        planes[0] = plane_id(r["TCUR"], W, H)
+        for li in range(2):
+            for ri in range(4):
+                if f"T{li}{ri}0" in r:
+                    planes[1 + li * 4 + ri] = plane_id(r[f"T{li}{ri}0"], W, H)
+        out[f"tpl_{i}_planes"] = planes
+        j = poc_to_pic.get(head[0], -1)
+        if "TME" in r:  # the ME results TPL read are the ones ME wrote: keep them once
+            assert j >= 0 and bytes(out[f"pic_{j}_res"]) == r["TME"], "TPL saw other ME results than ME dumped"
+        out[f"tpl_{i}_me"] = np.array(j if "TME" in r else -1, np.int32)
+        out[f"tpl_{i}_src"] = np.frombuffer(r["TSRC"], np.uint8)
+    meta = dict(tpl_pictures=len(trecs), preset=preset, width=w, height=h, frames=frames, pictures=len(recs),
                 command=" ".join(["SvtAv1EncApp", *cmd[1:]]).replace(os.path.dirname(clip), "<tmp>"),
                 reference="SVT-AV1 v3.0.2, C-only build (oracle/Makefile target enc)")
     out["meta"] = np.frombuffer(json.dumps(meta).encode(), np.uint8)
     out["luma"] = np.stack(lumas)
     dst = ROOT / "tests/golden" / f"{name}.npz"
     np.savez_compressed(dst, **out)
-    print(f"{dst}: {len(recs)} pictures, {len(lumas)} distinct planes, {dst.stat().st_size / 1024:.0f} KiB")
+    print(f"{dst}: {len(recs)} ME pictures, {len(trecs)} TPL pictures, {len(lumas)} distinct planes, {dst.stat().st_size / 1024:.0f} KiB")
 
 
 if __name__ == "__main__":
@@ -129,3 +157,4 @@ if __name__ == "__main__":
         sys.exit("build the dump encoder first: make -C oracle enc")
     build("enc_m10", 10, 320, 192, 17)
     build("enc_m4", 4, 192, 128, 17)
+    build("enc_m6", 6, 200, 136, 17)  # incomplete 64x64 blocks on the right and bottom edges

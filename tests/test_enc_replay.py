@@ -25,7 +25,7 @@ from svtme import abi, api
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GOLD = os.path.join(ROOT, "tests", "golden")
 SHIM_SO = os.path.join(ROOT, "oracle", "_ref", "libsvtme_shim.so")
-FIXTURES = ["enc_m10", "enc_m4"]
+FIXTURES = ["enc_m10", "enc_m4", "enc_m6"]
 FIELDS = (["me_mv", "me_cand", "total_me_candidate_index"] + list(abi.ResultBuffers.SCALARS32) +
           list(abi.ResultBuffers.SCALARS8) + ["picture_sums"])
 
@@ -124,6 +124,94 @@ def test_reference_harness_replays_encoder_dump(reference, fx):
     """The harness (oracle/ref_harness.c) around the unmodified motion_estimation.c fed with the dumped knobs gives what the
     encoder gave: the harness' pcs/MeContext filling is complete."""
     _replay_cpu(reference, fx)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# TPL source-based search (src_ops_process.c:608-884): TplSrcStats as the encoder's own dispenser wrote them
+# ---------------------------------------------------------------------------------------------------------------------
+THDR = ("poc W H aligned_w n_b64 pus slice_type tl hl me16 max_cand max_refs max_l0 dispenser_level disable_intra_nref "
+        "intra_mode_end use_sad subpel_depth subsample_tx tpl_lad_mg in_loop_ois l0 l1 pad").split()
+TREF_DT = np.dtype([("poc", "<u8"), ("group_idx", "<i4"), ("excluded", "<u4"), ("present", "<u4"), ("max_w", "<u4"),
+                    ("max_h", "<u4"), ("pad", "<u4")])
+TSRC_DT = np.dtype([("mv_row", "<i2"), ("mv_col", "<i2"), ("best_rf_idx", "<i4"), ("ref_frame_poc", "<u8"), ("best_mode", "u1"),
+                    ("best_intra_mode", "u1"), ("pad", "u1", (6,))])
+FULL_PEL = 3  # SUBPEL_FORCE_STOP (definitions.h): EIGHTH_PEL, QUARTER_PEL, HALF_PEL, FULL_PEL
+I_SLICE = 2
+
+
+def tpl_case(fx, i):
+    """One TPL record of the fixture -> (head dict, abi.TplCfg, abi.Knobs, plane indices, abi.ResultBuffers | None, expected)."""
+    z = fx.z
+    hd = dict(zip(THDR, [int(v) for v in z[f"tpl_{i}_head"]]))
+    refs = np.frombuffer(bytes(z[f"tpl_{i}_refs"]), TREF_DT).reshape(2, 4)
+    cfg = abi.TplCfg()
+    cfg.dispenser_search_level = hd["dispenser_level"]
+    cfg.use_sad_in_src_search = hd["use_sad"]
+    cfg.subpel_full_pel = int(hd["subpel_depth"] == FULL_PEL)
+    cfg.intra_dc_only = int(hd["intra_mode_end"] == 0 and hd["in_loop_ois"] == 1)
+    cfg.disable_intra_pred = int(hd["disable_intra_nref"] and hd["tl"] == hd["hl"])
+    cfg.slice_type_i = int(hd["slice_type"] == I_SLICE)
+    for li in range(2):
+        for ri in range(4):
+            cfg.ref_excluded[li][ri] = int(refs[li, ri]["excluded"])
+            cfg.ref_poc[li][ri] = int(refs[li, ri]["poc"])
+            if refs[li, ri]["present"]:  # the MV clamp uses ref_pic_ptr->max_width / max_height: the picture size here
+                assert (refs[li, ri]["max_w"], refs[li, ri]["max_h"]) == (hd["W"], hd["H"])
+    j = int(z[f"tpl_{i}_me"])
+    if j >= 0:
+        p = fx.pic(j)
+        k = p["knobs"]
+        me = abi.ResultBuffers(p["n_b64"], k, extended=False)
+        for f in ("me_mv", "me_cand", "total_me_candidate_index"):
+            me[f][...] = p["res"][f]
+    else:
+        k = abi.Knobs()
+        k.enable_me_16x16, k.enable_me_8x8 = hd["me16"], int(hd["pus"] == 85)
+        k.max_cand, k.max_refs, k.max_l0 = hd["max_cand"], hd["max_refs"], hd["max_l0"]
+        me = None
+    assert (k.enable_me_16x16, k.max_cand, k.max_refs, k.max_l0) == (hd["me16"], hd["max_cand"], hd["max_refs"], hd["max_l0"])
+    gw, gh = (hd["aligned_w"] + 15) >> 4, (hd["H"] + 15) >> 4
+    want = np.frombuffer(bytes(z[f"tpl_{i}_src"]), TSRC_DT).reshape(gh, gw)
+    return hd, cfg, k, z[f"tpl_{i}_planes"], me, want
+
+
+def check_tpl(hd, got, want):
+    """Every block the dispenser searched: mode, winner, vector and POC equal the encoder's TplSrcStats."""
+    live = got["block_size"] > 0
+    assert live.any()
+    sizes = set(np.unique(got["block_size"][live]).tolist())
+    assert sizes <= {16, 32, 64}
+    for name, a, b in (("best_mode", got["best_mode"], want["best_mode"]), ("best_rf_idx", got["best_rf_idx"], want["best_rf_idx"]),
+                       ("mv_row", got["mv"][..., 0], want["mv_row"]), ("mv_col", got["mv"][..., 1], want["mv_col"]),
+                       ("ref_frame_poc", got["ref_frame_poc"], want["ref_frame_poc"])):
+        bad = np.argwhere(live & (a.astype(np.int64) != b.astype(np.int64)))
+        assert len(bad) == 0, "poc %d: %s differs at cells %s: %s vs %s" % (
+            hd["poc"], name, bad[:4].tolist(), [a[tuple(c)] for c in bad[:4]], [b[tuple(c)] for c in bad[:4]])
+    return sizes
+
+
+def test_oracle_tpl_src_search_matches_encoder(oracle, fx):
+    n, sizes, newmv = fx.meta["tpl_pictures"], set(), 0
+    assert n >= 5
+    for i in range(n):
+        hd, cfg, k, planes, me, want = tpl_case(fx, i)
+
+        def padded(idx, num):
+            pp = refbind.PaddedPicture(fx.luma[idx], num)
+            oracle.build_planes(pp, 1)
+            return pp
+
+        cur = padded(planes[0], hd["poc"])
+        refs = {(li, ri): padded(planes[1 + li * 4 + ri], int(cfg.ref_poc[li][ri]))
+                for li in range(2) for ri in range(4) if planes[1 + li * 4 + ri] >= 0}
+        got = oracle.tpl_src_search(cfg, k, cur, refs, me)
+        sizes |= check_tpl(hd, got, want)
+        newmv += int((got["best_mode"] == abi.TPL_NEWMV).sum())
+    assert newmv > 0
+    if fx.meta["preset"] >= 10:
+        assert 32 in sizes  # dispenser_search_level 1 (TPL level 5)
+    if fx.meta["width"] % 64:
+        assert sizes == {16} or 16 in sizes  # incomplete 64x64 blocks fall back to 16x16
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -241,3 +329,58 @@ def test_cuda_through_compiled_shim(shim, fx):
             _check_gate(p, [int(v) for v in gate])
     finally:
         shim.svtme_shim_close(h)
+
+
+@pytest.mark.gpu
+def test_cuda_tpl_src_search_matches_encoder(oracle, fx):
+    """The TPL source-based decisions of the CUDA path -- standalone over the dumped ME results, and fused behind the picture's
+    own ME search -- equal the encoder's TplSrcStats; costs equal the oracle's."""
+    dev = api.MeDevice(device=0, max_inflight=4)
+    try:
+        resident = {}
+
+        def plane(idx, num):
+            if idx not in resident:
+                resident[idx] = dev.register(np.ascontiguousarray(fx.luma[idx]), num)
+            return resident[idx]
+
+        for i in range(fx.meta["tpl_pictures"]):
+            hd, cfg, k, planes, me, want = tpl_case(fx, i)
+            cur = plane(planes[0], hd["poc"])
+            refs = {(li, ri): plane(planes[1 + li * 4 + ri], int(cfg.ref_poc[li][ri]))
+                    for li in range(2) for ri in range(4) if planes[1 + li * 4 + ri] >= 0}
+            got = dev.tpl_src_search(k, cur, refs, cfg, me)
+            check_tpl(hd, got, want)
+
+            def padded(idx, num):
+                pp = refbind.PaddedPicture(fx.luma[idx], num)
+                oracle.build_planes(pp, 1)
+                return pp
+
+            orc = oracle.tpl_src_search(cfg, k, padded(planes[0], hd["poc"]),
+                                        {key: padded(planes[1 + key[0] * 4 + key[1]], 0) for key in refs}, me)
+            assert not got.diff(orc), "poc %d: %s differ from the oracle" % (hd["poc"], got.diff(orc))
+            if me is not None:  # fused: ME on the device, TPL over its results in HBM
+                me2, fused = dev.me_tpl_picture(k, cur, refs, cfg)
+                assert not me2.diff(me, names=["me_mv", "me_cand", "total_me_candidate_index"])
+                assert not fused.diff(got), "poc %d: fused differs from standalone: %s" % (hd["poc"], fused.diff(got))
+    finally:
+        dev.close()
+
+
+@pytest.mark.gpu
+def test_tpl_refuses_unsupported_controls():
+    dev = api.MeDevice(device=0)
+    try:
+        f = np.zeros((64, 64), np.uint8)
+        a, b = dev.register(f, 0), dev.register(f, 1)
+        k = api.derive_knobs(enc_mode=6, qp=35, frame_rate_q16=30 << 16, width=64, height=64, hierarchical_levels=3,
+                             picture_number=1, temporal_layer_index=0, is_ref=1, slice_type_b=0)
+        for field in ("use_sad_in_src_search", "subpel_full_pel", "intra_dc_only"):
+            cfg = abi.TplCfg()
+            cfg.use_sad_in_src_search = cfg.subpel_full_pel = cfg.intra_dc_only = 1
+            setattr(cfg, field, 0)
+            with pytest.raises(api.SvtMeError):
+                dev.me_tpl_picture(k, a, {(0, 0): b}, cfg)
+    finally:
+        dev.close()

@@ -1,5 +1,5 @@
 """Randomised parity sweep (run on the GPU box): random picture sizes, presets, temporal layers, clip kinds, reference
-lists and modes (open-loop ME, temporal filter, dynamic-GOP detector, picture statistics) -- every output of the CUDA
+lists and modes (open-loop ME, TPL source-based search, temporal filter, dynamic-GOP detector, picture statistics) -- every output of the CUDA
 path against the oracle.  python tools/fuzz_parity.py [iterations] [seed]"""
 import os
 import sys
@@ -30,9 +30,9 @@ def run(iters=40, seed=1234, verbose=True):
         try:
             pd = [dev.register(f, i) for i, f in enumerate(frames)]
             cur = int(rng.integers(0, n))
-            mode = str(rng.choice(["me", "me", "me", "tf", "dg", "stats"]))
+            mode = str(rng.choice(["me", "me", "me", "tf", "dg", "stats", "tpl"]))
             what = "%dx%d %s n=%d seed=%d cur=%d %s" % (w, h, kind, n, seed, cur, mode)
-            if mode == "me":
+            if mode in ("me", "tpl"):
                 em = int(rng.integers(-1, 14))
                 hl = int(rng.integers(2, 6))
                 tl = int(rng.integers(0, hl + 1))
@@ -53,6 +53,23 @@ def run(iters=40, seed=1234, verbose=True):
                 b = dev.me_picture(k, pd[cur], H.refs_dict(pd, l0, l1), extended=True)
                 H.assert_same(a, b, what)
                 assert b.px_compares == px, what
+                if mode == "tpl":  # the TPL source-based decisions over those ME results: fused on the device vs the oracle
+                    from svtme import abi
+                    c = abi.TplCfg()
+                    c.use_sad_in_src_search = c.subpel_full_pel = c.intra_dc_only = 1
+                    c.dispenser_search_level = int(rng.integers(0, 3)) if k.enable_me_16x16 else int(rng.integers(0, 2))
+                    c.disable_intra_pred = int(rng.random() < 0.3)
+                    for li, lst in enumerate((l0, l1)):
+                        for ri, q in enumerate(lst):
+                            c.ref_poc[li][ri] = q
+                            c.ref_excluded[li][ri] = int(rng.random() < 0.15)
+                    what += " tpl level %d nointra %d" % (c.dispenser_search_level, c.disable_intra_pred)
+                    t0 = oracle.tpl_src_search(c, k, po[cur], H.refs_dict(po, l0, l1), a)
+                    me1, t1 = dev.me_tpl_picture(k, pd[cur], H.refs_dict(pd, l0, l1), c)
+                    assert not t1.diff(t0), (what, t1.diff(t0))
+                    assert not me1.diff(a, names=["me_mv", "me_cand", "total_me_candidate_index"]), what
+                    t2 = dev.tpl_src_search(k, pd[cur], H.refs_dict(pd, l0, l1), c, a)
+                    assert not t2.diff(t0), (what, "standalone", t2.diff(t0))
             elif mode == "tf":
                 nb = int(rng.choice([i for i in range(n) if i != cur]))
                 k = api.derive_tf_knobs(hme_me_level=int(rng.integers(0, 5)), qp_opt=int(rng.integers(0, 2)),
