@@ -1515,8 +1515,26 @@ __global__ void __launch_bounds__(kStThreads, 4) st_fp_warp_kernel(const __grid_
     uint32_t px = 0;
     bool     any_big = false;
     int      ordinal = 0;
+    // the block's job table (8 x 24 bytes) in ONE round trip: lane = word of the table, a job's fields come by shuffle
+    static_assert(sizeof(FpJob) == 24 && kMaxFpJobs * 6 <= 64, "job table = 48 words");
+    const uint32_t *jt  = reinterpret_cast<const uint32_t *>(s.fp_jobs);
+    const uint32_t  jt0 = jt[lane], jt1 = lane < kMaxFpJobs * 6 - 32 ? jt[32 + lane] : 0u;
     for (int ji = 0; ji < kMaxFpJobs; ji++) {
-        const FpJob j = s.fp_jobs[ji];  // the same for every lane: broadcast loads
+        FpJob j;
+        {
+            uint32_t f[6];
+#pragma unroll
+            for (int q = 0; q < 6; q++) {
+                const int      idx = 6 * ji + q;
+                const uint32_t v0 = __shfl_sync(0xffffffffu, jt0, idx & 31), v1 = __shfl_sync(0xffffffffu, jt1, idx & 31);
+                f[q] = idx < 32 ? v0 : v1;
+            }
+            j.ref = reinterpret_cast<const uint8_t *>(((unsigned long long)f[1] << 32) | f[0]);
+            j.ref_stride = (int32_t)f[2];
+            j.xo = (int16_t)(f[3] & 0xffff); j.yo = (int16_t)(f[3] >> 16);
+            j.w = (int16_t)(f[4] & 0xffff); j.h = (int16_t)(f[4] >> 16);
+            j.li = (uint8_t)(f[5] & 0xff); j.ri = (uint8_t)((f[5] >> 8) & 0xff);
+        }
         if (j.w <= 0 || j.h <= 0) continue;
         int a, ngroups, P, plane;
         if (!fp_job_small(j, a, ngroups, P, plane)) { any_big = true; continue; }
@@ -1596,7 +1614,7 @@ __global__ void __launch_bounds__(kStThreads, 4) st_fp_warp_kernel(const __grid_
                 for (int c = 0; c < 4; c++) {
                     const int      xx = xb + c, y = yy + 2 * y2;
                     const bool     valid = y < ny && xx >= 0 && xx < nx;
-                    const uint32_t ord = (uint32_t)(y * nx + xx);  // < 4096
+                    const uint32_t ord = (uint32_t)(y * 64 + xx);  // < 4096; the same order as y * nx + xx (nx <= 64)
                     uint32_t       t = 0;
 #pragma unroll
                     for (int q = 0; q < 4; q++) {
@@ -1629,7 +1647,7 @@ __global__ void __launch_bounds__(kStThreads, 4) st_fp_warp_kernel(const __grid_
 #pragma unroll
             for (int i = 0; i < 2; i++) {
                 const int xx = x32 + i;
-                if (yok && xx >= 0 && xx < nx) best32 = min(best32, t2[i] * 4096u + (uint32_t)(y32 * nx + xx));
+                if (yok && xx >= 0 && xx < nx) best32 = min(best32, t2[i] * 4096u + (uint32_t)(y32 * 64 + xx));
             }
             {
                 const bool     up   = b & 4;  // keeps c & 1 = b2
@@ -1639,7 +1657,7 @@ __global__ void __launch_bounds__(kStThreads, 4) st_fp_warp_kernel(const __grid_
             t1 += __shfl_xor_sync(0xffffffffu, t1, 8);
             {
                 const int xx = x32 + ((b >> 2) & 1);
-                if (yok && xx >= 0 && xx < nx) best64 = min(best64, t1 * 4096u + (uint32_t)(y32 * nx + xx));
+                if (yok && xx >= 0 && xx < nx) best64 = min(best64, t1 * 4096u + (uint32_t)(y32 * 64 + xx));
             }
             if (++g == ngroups) { g = 0; k++; }
         }
@@ -1660,7 +1678,7 @@ __global__ void __launch_bounds__(kStThreads, 4) st_fp_warp_kernel(const __grid_
             if (key == ~0u) return;
             const uint32_t sad = (key >> 12) << 1, ord = key & 4095u;
             if (sad < prev) {
-                const uint32_t y = ord / (uint32_t)nx, x = ord - y * (uint32_t)nx;
+                const uint32_t y = ord >> 6, x = ord & 63u;
                 bs[pu] = sad;
                 bm[pu] = ((uint32_t)((int32_t)y + j.yo) << 16) | (uint16_t)((int32_t)x + j.xo);
             }
