@@ -8,7 +8,7 @@ for r in rows[1:]:
     k = r[ki].split('(')[0]
     per[k] += float(r[vi].replace(',', '')) * mult.get(r[ui], 1)
     if r[ni] == 'dram__bytes_read.sum': cnt[k] += 1
-npic = max(1, cnt.get('st_finish_kernel', 1))
+npic = max(1, cnt.get('st_finish_kernel', cnt.get('st_init_kernel', 1)))  # one st_init_kernel per picture search
 search = sum(v for k, v in per.items() if k.split('<')[0].split()[-1].startswith('st_'))
 out = {"search_dram_bytes_per_picture": search / npic, "pictures": npic,
        "per_kernel_bytes_per_picture": {k: v / npic for k, v in sorted(per.items(), key=lambda kv: -kv[1])},
