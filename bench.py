@@ -456,6 +456,13 @@ def main_dg(args, rank, local_rank, world):
     return 0
 
 
+class _DeviceBytes:
+    """A device allocation of the library as a __cuda_array_interface__ object (torch.as_tensor wraps it without a copy)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}  # never written through this view
+
+
 def main_strong(args, rank, local_rank, world, dist, wl):
     """--scaling strong: ONE clip on `world` GPUs.  The pictures of every mini-GOP are dealt round-robin (decode order)
     over the ranks; a picture is uploaded and decimated once, by the rank that searches it (the leading base picture by
@@ -466,7 +473,7 @@ def main_strong(args, rank, local_rank, world, dist, wl):
     import torch
     from svtme import abi, api, shard
     w, h, nf, G = wl.w, wl.h, wl.n_frames, args.gops_per_step
-    dev = api.MeDevice(device=local_rank, max_inflight=args.inflight, max_pictures=3 * nf)
+    dev = api.MeDevice(device=local_rank, max_inflight=args.inflight, max_pictures=5 * nf)  # three mini-GOPs alive + one in preparation
     h_luma = torch.empty((nf, h, w), dtype=torch.uint8).pin_memory()
     h_luma.numpy()[:] = np.stack(wl.frames)
     d_luma = h_luma.cuda()
@@ -486,34 +493,55 @@ def main_strong(args, rank, local_rank, world, dist, wl):
     # (picture, source rank, destination rank) of every plane set that crosses GPUs in a mini-GOP, the same list on every rank
     transfers = sorted(set((p, owner[p], n % world) for n, (_, _, l0, l1) in enumerate(wl.pics) for p in l0 + l1 if owner[p] != n % world))
     nbytes = api.MeDevice.planes_bytes(w, h)
-    sendbuf = {t: torch.empty(nbytes, dtype=torch.uint8, device="cuda") for t in transfers if t[1] == rank}
-    recvbuf = {t: torch.empty(nbytes, dtype=torch.uint8, device="cuda") for t in transfers if t[2] == rank}
+    # two sets of exchange buffers: the planes of mini-GOP g + 1 move while mini-GOP g is searched
+    recvbuf = [{t: torch.empty(nbytes, dtype=torch.uint8, device="cuda") for t in transfers if t[2] == rank} for _ in range(2)]
     moved = sum(nbytes for t in transfers if t[2] == rank)
+    xstream = torch.cuda.Stream()  # the NCCL point-to-point operations: never on the stream the host synchronises
+    imported = [[], []]  # pictures whose planes are still being copied out of recvbuf[slot]
 
-    def gop(host, pending, exchange=True):
+    def prepare(host, slot, exchange=True):
+        """Upload + decimate this rank's pictures of a mini-GOP and start moving the plane sets other ranks need (and
+        receiving the ones this rank needs).  Returns the state `launch` completes."""
         src = (lambda i: dev.register_ptr(h_luma.data_ptr() + i * w * h, w, w, h, i)) if host else \
               (lambda i: dev.register_device(d_luma.data_ptr() + i * w * h, w, w, h, i))
         pics = {p: src(p) for p in owner if owner[p] == rank}  # uploaded / decimated here
+        works, done = [], None
         if exchange and world > 1:
-            ops = []
+            for q in imported[slot]:  # the previous user of these receive buffers has copied its planes out
+                if q.ptr:  # (a released picture has: its release waited for the copy)
+                    dev.wait_picture(q)
+            imported[slot] = []
+            ops, views = [], {}
             for t in transfers:
-                if t[1] == rank:
-                    dev.export_planes(pics[t[0]], sendbuf[t].data_ptr(), nbytes)
-                    ops.append(dist.P2POp(dist.isend, sendbuf[t], t[2]))
+                if t[1] == rank:  # straight out of the picture's plane allocation (no staging copy); it outlives the send
+                    if t[0] not in views:
+                        views[t[0]] = torch.as_tensor(_DeviceBytes(*dev.planes_device(pics[t[0]])), device="cuda")
+                    ops.append(dist.P2POp(dist.isend, views[t[0]], t[2]))
                 elif t[2] == rank:
-                    ops.append(dist.P2POp(dist.irecv, recvbuf[t], t[1]))
+                    ops.append(dist.P2POp(dist.irecv, recvbuf[slot][t], t[1]))
             if ops:
-                for r in dist.batch_isend_irecv(ops):
-                    r.wait()
-            torch.cuda.current_stream().synchronize()
-            for t in transfers:
-                if t[2] == rank and t[0] not in pics:
-                    pics[t[0]] = dev.import_planes(recvbuf[t].data_ptr(), w, h, t[0])
-        else:
+                with torch.cuda.stream(xstream):
+                    works = dist.batch_isend_irecv(ops)
+                    for r in works:
+                        r.wait()  # orders xstream behind the transfers; the host does not block here
+                    done = torch.cuda.Event()
+                    done.record(xstream)
+        elif not exchange:
             for _, (_, _, l0, l1) in mine:
                 for p_ in l0 + l1:
                     if p_ not in pics:
                         pics[p_] = src(p_)
+        return pics, done, slot
+
+    def launch(host, state, pending):
+        """The received plane sets become pictures (no decimation here), then this rank's searches of the mini-GOP."""
+        pics, done, slot = state
+        if done is not None:
+            done.synchronize()  # the transfers had a whole mini-GOP of searches to complete
+            for t in transfers:
+                if t[2] == rank and t[0] not in pics:
+                    pics[t[0]] = dev.import_planes(recvbuf[slot][t].data_ptr(), w, h, t[0])
+                    imported[slot].append(pics[t[0]])
         for n, (poc, k, l0, l1) in mine:
             refs = {(0, i): pics[p_] for i, p_ in enumerate(l0)}
             refs.update({(1, i): pics[p_] for i, p_ in enumerate(l1)})
@@ -522,18 +550,25 @@ def main_strong(args, rank, local_rank, world, dist, wl):
             pending.append(dev.search_async(k, pics[poc], refs, out=outs[n])[0] if host else dev.search_device_async(k, pics[poc], refs))
         return pics
 
+    def gop(host, pending, exchange=True):
+        return launch(host, prepare(host, 0, exchange), pending)
+
     def step(host):
-        pending, prev = [], None
-        for _ in range(G):
-            pics = gop(host, pending)
-            if prev:
-                for q in prev.values():
+        pending, live = [], []
+        state = prepare(host, 0)
+        for g in range(G):
+            nxt = prepare(host, (g + 1) & 1) if g + 1 < G else None  # mini-GOP g + 1's planes start moving now
+            pics = launch(host, state, pending)
+            live.append(pics)
+            if len(live) > 2:  # its imports have long been copied out of the exchange buffers that are about to be reused
+                for q in live.pop(0).values():
                     q.release()
-            prev = pics
+            state = nxt
         for t in pending:
             dev.wait(t)
-        for q in prev.values():
-            q.release()
+        for pics in live:
+            for q in pics.values():
+                q.release()
 
     # the multi-GPU path against the single-GPU path, on this rank's first picture
     if mine:

@@ -306,6 +306,10 @@ int32_t svtme_picture_replicate(SvtMeHandle *src_h, SvtMePic *pic, SvtMeHandle *
 int32_t svtme_picture_export_planes(SvtMeHandle *h, SvtMePic *pic, void *d_dst, uint64_t dst_bytes);
 int32_t svtme_picture_import_planes(SvtMeHandle *h, uint64_t picture_number, const void *d_src, uint32_t width, uint32_t height,
                                     SvtMePic **out);
+/* Zero-copy form of the export: the device address of the picture's plane allocation (svtme_picture_planes_bytes bytes, the
+ * layout svtme_picture_import_planes expects), for a send straight out of it.  Returns when the planes are built.  Read-only;
+ * valid until the picture is released, so release it only after the send has completed. */
+int32_t svtme_picture_planes_device(SvtMeHandle *h, SvtMePic *pic, const void **d_planes, uint64_t *bytes);
 /* Wait until the planes of `pic` are built. */
 int32_t svtme_picture_wait(SvtMeHandle *h, SvtMePic *pic);
 /* Copy a padded plane back (level 0 = full, 1 = quarter, 2 = sixteenth) for the

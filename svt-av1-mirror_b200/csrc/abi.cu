@@ -707,6 +707,19 @@ int32_t svtme_picture_export_planes(SvtMeHandle *h, SvtMePic *pic, void *d_dst, 
     return SVTME_OK;
 }
 
+int32_t svtme_picture_planes_device(SvtMeHandle *h, SvtMePic *pic, const void **d_planes, uint64_t *bytes) {
+    if (!h || !pic || !d_planes) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");
+    size_t total;
+    PlaneGeom g[3];
+    plane_geometry(pic->width, pic->height, g, &total);
+    int rc = set_device(h);
+    if (rc) return rc;
+    CK(cudaEventSynchronize(pic->ready));  // the planes are built when the call returns
+    *d_planes = pic->buf.base;
+    if (bytes) *bytes = total;
+    return SVTME_OK;
+}
+
 int32_t svtme_picture_import_planes(SvtMeHandle *h, uint64_t picture_number, const void *d_src, uint32_t width, uint32_t height,
                                     SvtMePic **out) {
     if (!d_src) return fail(h, SVTME_ERR_BAD_PARAMETER, "null argument");

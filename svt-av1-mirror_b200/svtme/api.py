@@ -24,7 +24,7 @@ EXPORTS = [
     "svtme_search_px_compares", "svtme_measure_sad_peak", "svtme_launch_count", "svtme_last_error", "svtme_cuda_sad_loop_kernel", "svtme_cuda_downsample_2d",
     "svtme_cuda_nxm_sad_kernel", "svtme_cuda_fullpel_search_sblock", "svtme_dg_detector_hme_level0",
     "svtme_picture_statistics", "svtme_cuda_nxm_sad_kernel_noalloc", "svtme_picture_planes_bytes", "svtme_picture_replicate",
-    "svtme_picture_export_planes", "svtme_picture_import_planes", "svtme_picture_search_tpl", "svtme_tpl_src_search",
+    "svtme_picture_export_planes", "svtme_picture_import_planes", "svtme_picture_search_tpl", "svtme_tpl_src_search", "svtme_picture_planes_device",
 ]
 
 
@@ -66,6 +66,7 @@ def load_library():
     lib.svtme_picture_replicate.argtypes = [vp, vp, vp, C.POINTER(vp)]
     lib.svtme_picture_export_planes.argtypes = [vp, vp, vp, u64]
     lib.svtme_picture_import_planes.argtypes = [vp, u64, vp, u32, u32, C.POINTER(vp)]
+    lib.svtme_picture_planes_device.argtypes = [vp, vp, C.POINTER(vp), C.POINTER(u64)]
     lib.svtme_picture_read_plane.argtypes = [vp, vp, i32, u32, u8p, u32]
     lib.svtme_picture_release.argtypes = [vp, vp]
     lib.svtme_picture_search.argtypes = [vp, vp, refs_t, C.POINTER(abi.Knobs), C.POINTER(abi.PictureResults),
@@ -218,6 +219,12 @@ class MeDevice:
 
     def export_planes(self, pic, d_dst, nbytes):
         self._check(self.lib.svtme_picture_export_planes(self.h, pic.ptr, d_dst, nbytes), "svtme_picture_export_planes")
+
+    def planes_device(self, pic):
+        """(device address, bytes) of the picture's plane allocation, once built: a send buffer without a copy."""
+        ptr, n = C.c_void_p(), C.c_uint64()
+        self._check(self.lib.svtme_picture_planes_device(self.h, pic.ptr, C.byref(ptr), C.byref(n)), "svtme_picture_planes_device")
+        return ptr.value, n.value
 
     def import_planes(self, d_src, width, height, picture_number, keep=None):
         ptr = C.c_void_p()

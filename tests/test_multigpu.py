@@ -72,3 +72,25 @@ def test_export_import_round_trip(oracle):
         owner.export_planes(cur, keep[0].data_ptr(), nbytes - 1) if dst_dev == 0 else other.export_planes(cur, keep[0].data_ptr(), nbytes - 1)
     owner.close()
     other.close()
+
+
+def test_planes_device_is_the_export_without_the_copy(oracle):
+    """svtme_picture_planes_device hands out the plane allocation itself: the same bytes svtme_picture_export_planes copies."""
+    import ctypes as C
+    import torch
+    frames, _, _, _, _ = _case(oracle)
+    dev = api.MeDevice(device=0)
+    pic = dev.register(frames[2], 2)
+    nbytes = api.MeDevice.planes_bytes(W, HH)
+    ptr, n = dev.planes_device(pic)
+    assert n == nbytes and ptr
+    buf = torch.empty(nbytes, dtype=torch.uint8, device="cuda:0")
+    dev.export_planes(pic, buf.data_ptr(), nbytes)
+
+    class Raw:
+        __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+    view = torch.as_tensor(Raw(), device="cuda:0")
+    assert view.data_ptr() == ptr and torch.equal(view, buf)
+    pic.release()
+    dev.close()
