@@ -236,7 +236,7 @@ int make_pic(SvtMeHandle *h, uint64_t picture_number, uint32_t width, uint32_t h
         const PlaneGeom &g = p->geom[2];
         static_assert(sizeof(CUtensorMap) == kTmapBytes, "CUtensorMap is 128 bytes");
         void *mem = nullptr;
-        if (posix_memalign(&mem, 64, (size_t)kS16Classes * kS16HClasses * kTmapBytes) != 0) { cudaEventDestroy(p->ready); return give_back(fail(h, SVTME_ERR_INSUFFICIENT, "tensor maps")); }
+        if (posix_memalign(&mem, 64, (size_t)svtme::kMapsPerPic * kTmapBytes) != 0) { cudaEventDestroy(p->ready); return give_back(fail(h, SVTME_ERR_INSUFFICIENT, "tensor maps")); }
         p->buf.maps = reinterpret_cast<unsigned char (*)[kTmapBytes]>(mem);
         for (int c = 0; c < kS16Classes * kS16HClasses; c++) {
             const cuuint64_t gdim[2] = {(cuuint64_t)g.stride, (cuuint64_t)(g.h + 2 * g.pad)}, gstr[1] = {(cuuint64_t)g.stride};
@@ -245,6 +245,18 @@ int make_pic(SvtMeHandle *h, uint64_t picture_number, uint32_t width, uint32_t h
                 reinterpret_cast<CUtensorMap *>(p->buf.maps[c]), CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, p->buf.base + g.offset, gdim, gstr, box, estr,
                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
             if (r != CUDA_SUCCESS) { cudaEventDestroy(p->ready); return give_back(fail(h, SVTME_ERR_UNDEFINED, "cuTensorMapEncodeTiled")); }
+        }
+        for (int q = 0; q < svtme::kRowsTmaMaps; q++) {  // rows of parity q of the padded full plane (HME level-2 windows)
+            const int        par = q;
+            const PlaneGeom &f = p->geom[0];
+            const cuuint64_t rows = (cuuint64_t)(f.h + 2 * f.pad);
+            const cuuint64_t gdim[2] = {(cuuint64_t)f.stride, (rows - par + 1) / 2}, gstr[1] = {(cuuint64_t)f.stride * 2};
+            const cuuint32_t box[2] = {(cuuint32_t)svtme::kRowsTmaBoxW, (cuuint32_t)svtme::kRowsTmaBoxH}, estr[2] = {1, 1};
+            const CUresult   r = reinterpret_cast<EncodeFn>(h->encode_tiled)(
+                reinterpret_cast<CUtensorMap *>(p->buf.maps[kS16Classes * kS16HClasses + q]), CU_TENSOR_MAP_DATA_TYPE_UINT8, 2,
+                p->buf.base + f.offset + (size_t)par * f.stride, gdim, gstr, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) { cudaEventDestroy(p->ready); return give_back(fail(h, SVTME_ERR_UNDEFINED, "cuTensorMapEncodeTiled (parity planes)")); }
         }
     }
     *out = p;

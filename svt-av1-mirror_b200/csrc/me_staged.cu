@@ -503,6 +503,26 @@ __device__ void warp_sad_job_fast(const SadJob &j, SadJob &jout, const uint32_t 
     }
 }
 
+// mbarrier / TMA primitives (PTX ISA: mbarrier, cp.async.bulk.tensor)
+SVTME_D void mbar_init(uint32_t mbar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\nfence.mbarrier_init.release.cluster;" ::"r"(mbar), "r"(count) : "memory");
+}
+SVTME_D void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+SVTME_D void mbar_wait(uint32_t mbar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(mbar), "r"(parity) : "memory");
+    } while (!done);
+}
+// one box of a 2-D tiled tensor map -> shared memory (dst 128-byte aligned), completion counted on `mbar`
+SVTME_D void tma_load_2d(uint32_t dst, const void *tmap, int x, int y, uint32_t mbar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(tmap), "r"(x), "r"(y), "r"(mbar) : "memory");
+}
+
 // ---- HME level 1 / 2 refinement windows (8x3 candidates on 32x16 / 64x32 sub-sampled blocks): lane = one block row ----
 // The search job is tiny (24 candidates) but every candidate touches the whole block, and each window row is used by
 // at most two candidate rows -- so shared memory is only the transposer between coalesced global rows and "one row
@@ -523,7 +543,8 @@ struct RowsCfg {
     static constexpr int kExtY    = (ROWS - 1) * 2;
     static constexpr int kNy      = 4;                            // candidate rows per staged chunk
     static constexpr int kRowsPad = (kNy + kExtY + 7) & ~7;       // staged in groups of 8 rows
-    static constexpr int kPlaneW  = (kRowsPad / 2) * kS;          // words per parity plane
+    static constexpr int kPlaneW  = ((kRowsPad / 2) * kS + 31) & ~31;  // words per parity plane, a multiple of 128 bytes: the odd
+                                                                  // plane is a legal TMA destination
     static constexpr int kWinW    = 2 * kPlaneW;
     static_assert(kRowsPad % kRpi == 0 && kRpi % 2 == 0, "copy groups");
 };
@@ -604,7 +625,8 @@ __device__ __forceinline__ void rows_unit(const uint32_t (&sreg)[NW], const uint
 
 template <int NW, int ROWS, bool FULLW>
 __device__ __forceinline__ void rows_job(const MeParams &p, int lvl, const SadJob &j, SadJob &jout, const uint32_t (&sreg)[NW],
-                                         uint32_t *win, int lane, int rows, int nw_eff) {
+                                         uint32_t *win, int lane, int rows, int nw_eff, const S16Maps *maps = nullptr, uint32_t mbar = 0,
+                                         uint32_t *phase = nullptr) {
     using C = RowsCfg<NW, ROWS>;
     const int W = j.sa_w, H = j.sa_h;
     if (W <= 0 || H <= 0) return;
@@ -621,6 +643,27 @@ __device__ __forceinline__ void rows_job(const MeParams &p, int lvl, const SadJo
             const int      ny = min(H - y0, C::kNy);
             const uint8_t *g0 = ref + (int64_t)y0 * (int64_t)raw + x0 - a16 + 16 * lc;
             __syncwarp();
+            if (maps) {
+                // the two parity planes of the window as two TMA boxes (kS * 4 bytes x kRowsPad / 2 rows of the same-parity rows of
+                // the padded plane, from the picture's parity-view descriptors); completion on this warp's mbarrier.  Rows or bytes
+                // beyond the plane's allocation are zero-filled by the TMA unit; they belong to no candidate.
+                constexpr int L = 0;  // the full plane: only the HME level-2 kernel is given descriptors
+                static_assert(NW != 16 || (C::kS * 4 == kRowsTmaBoxW && C::kRowsPad / 2 == kRowsTmaBoxH), "box = one parity plane");
+                const DevPlane &rpl = p.refs[j.li][j.ri].lvl[L];
+                const uint8_t  *row0 = ref + (int64_t)y0 * (int64_t)raw + x0 - a16;  // 16-byte aligned
+                constexpr int   kPadL = kDevPad[L], kBoxBytes = C::kS * 4 * (C::kRowsPad / 2);
+                const int       offb = (int)(row0 - (rpl.org - (int64_t)kPadL * rpl.stride - kPadL));
+                const int       ty = offb / rpl.stride, tx = offb - ty * rpl.stride;
+                if (lane == 0) mbar_expect_tx(mbar, 2u * (uint32_t)kBoxBytes);
+                __syncwarp();
+                if (lane < 2) {  // window rows of parity `lane` = plane rows of parity (ty + lane) & 1, from row (ty + lane) >> 1 of that view
+                    const int pr = ty + lane;
+                    tma_load_2d(sbase + (uint32_t)lane * (uint32_t)(C::kPlaneW * 4),
+                                maps->m[j.li * kMaxRefs + j.ri][kS16Classes * kS16HClasses + (pr & 1)], tx, pr >> 1, mbar);
+                }
+                mbar_wait(mbar, *phase & 1u);
+                (*phase)++;
+            } else
             // always the full kRowsPad rows: the few rows below a short window are inside the plane's physical padding
             // (96 / 48 rows against the 72 / 32 the search may touch), and the copy loop unrolls to immediates
             if (lc < C::kChunks) {
@@ -656,11 +699,12 @@ __device__ __forceinline__ void rows_job(const MeParams &p, int lvl, const SadJo
 #define SVTME_ROWS8_CTAS 6
 #endif
 template <int NW, int ROWS>
-__device__ __forceinline__ void sad_rows_block(const MeParams &p, int lvl, uint32_t sbi) {
+__device__ __forceinline__ void sad_rows_block(const MeParams &p, int lvl, uint32_t sbi, const S16Maps *maps = nullptr, uint32_t mbar = 0,
+                                               uint32_t *phase = nullptr) {
     using C = RowsCfg<NW, ROWS>;
     constexpr int kBlkPitch = 17;  // odd: lane = row reads are conflict free
     __shared__ uint32_t                    blk[ROWS * kBlkPitch];
-    __shared__ __align__(16) uint32_t      win[kStWarps][C::kWinW];
+    __shared__ __align__(128) uint32_t     win[kStWarps][C::kWinW];
     __shared__ __align__(16) SadJob        jobs[kMaxSadJobs];
     SbState  &s = p.states[sbi];
     PH_DECL
@@ -689,8 +733,8 @@ __device__ __forceinline__ void sad_rows_block(const MeParams &p, int lvl, uint3
     for (int ji = warp; ji < n; ji += kStWarps) {
         const SadJob &j = jobs[ji];
         if (j.sa_w > 0 && j.sa_h > 0) px += (uint32_t)(j.sa_w * j.sa_h) * (uint32_t)(rows * bw);
-        if (nw_eff == NW) rows_job<NW, ROWS, true>(p, lvl, j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff);
-        else rows_job<NW, ROWS, false>(p, lvl, j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff);
+        if (nw_eff == NW) rows_job<NW, ROWS, true>(p, lvl, j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff, maps, mbar, phase);
+        else rows_job<NW, ROWS, false>(p, lvl, j, s.sad_jobs[ji], sreg, win[warp], lane, rows, nw_eff, maps, mbar, phase);
     }
     if (lane == 0 && px) atomicAdd(&s.px, (unsigned long long)px);
     PH(3, 1)  // this warp's windows
@@ -699,11 +743,17 @@ __device__ __forceinline__ void sad_rows_block(const MeParams &p, int lvl, uint3
 // of the GPU's CTA slots (launch_me_picture_staged), so that the engines of two pictures in flight on different
 // streams are resident side by side instead of one after the other.
 template <int NW, int ROWS>
-__global__ void __launch_bounds__(kStThreads, NW == 8 ? SVTME_ROWS8_CTAS : 6) st_sad_rows_kernel(const __grid_constant__ MeParams p, int lvl) {
+__global__ void __launch_bounds__(kStThreads, NW == 8 ? SVTME_ROWS8_CTAS : 6) st_sad_rows_kernel(const __grid_constant__ MeParams p, const __grid_constant__ S16Maps maps, int lvl) {
     PDL_ENTRY();
+    __shared__ __align__(8) unsigned long long mbar_store[kStWarps];  // one mbarrier per warp: a warp stages and searches its own windows
+    const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t mbar = (uint32_t)__cvta_generic_to_shared(&mbar_store[warp]);
+    if (lane == 0) mbar_init(mbar, 1);
+    __syncthreads();
+    uint32_t       phase = 0;
     const uint32_t n_sb = p.wb * p.hb;
     for (uint32_t sbi = blockIdx.x; sbi < n_sb; sbi += gridDim.x) {
-        sad_rows_block<NW, ROWS>(p, lvl, sbi);
+        sad_rows_block<NW, ROWS>(p, lvl, sbi, NW == 16 ? &maps : nullptr, mbar, &phase);  // HME level 1 keeps its cp.async copies
         __syncthreads();  // the shared-memory tables are reused by the next block
     }
 }
@@ -800,26 +850,6 @@ struct alignas(16) S16Sub {
 static_assert(sizeof(S16Sub) == 48, "a sub-window descriptor is fetched as three 16-byte words");
 
 constexpr int kPad16 = kDevPad[2];
-
-// mbarrier / TMA primitives (PTX ISA: mbarrier, cp.async.bulk.tensor)
-SVTME_D void mbar_init(uint32_t mbar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\nfence.mbarrier_init.release.cluster;" ::"r"(mbar), "r"(count) : "memory");
-}
-SVTME_D void mbar_expect_tx(uint32_t mbar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
-}
-SVTME_D void mbar_wait(uint32_t mbar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
-                     : "=r"(done) : "r"(mbar), "r"(parity) : "memory");
-    } while (!done);
-}
-// one box of a 2-D tiled tensor map -> shared memory (dst 128-byte aligned), completion counted on `mbar`
-SVTME_D void tma_load_2d(uint32_t dst, const void *tmap, int x, int y, uint32_t mbar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                 ::"r"(dst), "l"(tmap), "r"(x), "r"(y), "r"(mbar) : "memory");
-}
 
 // The plan of one block's pre-HME / HME level-0 searches, made by the light kernel in front of the engine (s16_plan) and
 // handed over through HBM/L2; the engine's warps fold their minima into job_key, the light kernel behind it reads them.
@@ -1828,8 +1858,8 @@ cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, int
         grid = engine_grid;
         if (p.prog[i].kind == STEP_SAD) {
             const int lvl = (int)p.prog[i].arg;
-            if (lvl == 1 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<8, 16>, 0, p, lvl); mark("rows8"); }
-            else if (lvl == 0 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<16, 32>, 0, p, lvl); mark("rows16"); }
+            if (lvl == 1 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<8, 16>, 0, p, maps, lvl); mark("rows8"); }
+            else if (lvl == 0 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<16, 32>, 0, p, maps, lvl); mark("rows16"); }
             else if (lvl == 2 && p.k.hme_search_method == 0) {
                 // (diagnostics) 1: pre-HME windows, 2: HME level-0 quadrants -- by the control step that made the jobs
                 int tag = 2, qi = -1;

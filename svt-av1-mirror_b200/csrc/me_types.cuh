@@ -118,11 +118,18 @@ struct MeParams {
 
 // TMA descriptors of every reference picture's padded sixteenth plane: kS16Classes x kS16HClasses CUtensorMaps (128 bytes
 // each), box = kS16BoxBytes[class] x kS16BoxRows[height class]; st_sad16_kernel stages its search windows with them.
-// Passed to that kernel BY VALUE as a __grid_constant__ parameter (15 KB of the 32 KB a launch may carry): descriptors
+// Passed to the kernels BY VALUE as a __grid_constant__ parameter (17 KB of the 32 KB a launch may carry): descriptors
 // in parameter space need no proxy fence before the TMA unit fetches them, unlike descriptors read from global memory
 // (a fence.proxy.tensormap per CTA was measured at -8 % of the picture rate).
+// Two more descriptors per picture for the HME level-2 windows (st_sad_rows_kernel<16, 32>): the even and the odd rows of the
+// padded full plane as two tensors of doubled row pitch; box = one parity plane of a window (112 bytes x 36 rows).  Index
+// kS16Classes * kS16HClasses + parity.  (The same for the quarter plane / HME level 1 -- 80 bytes x 20 rows -- was measured
+// 0.5 % slower than that kernel's 16-byte cp.async copies and is not built.)
+constexpr int kRowsTmaMaps = 2;
+constexpr int kMapsPerPic  = kS16Classes * kS16HClasses + kRowsTmaMaps;
+constexpr int kRowsTmaBoxW = 112, kRowsTmaBoxH = 36;
 struct alignas(64) S16Maps {
-    unsigned char m[kMaxLists * kMaxRefs][kS16Classes * kS16HClasses][kTmapBytes];
+    unsigned char m[kMaxLists * kMaxRefs][kMapsPerPic][kTmapBytes];
 };
 
 // ---- work descriptors produced by the per-SB control code and consumed by the search engines ----
