@@ -87,6 +87,7 @@ struct Inflight {
     std::thread::id     owner;  // the thread that submitted the search in flight
     bool                direct[32] = {};  // result array i went straight into the caller's (page-locked) buffer
     S16Maps             maps;             // launch parameter of st_sad16_kernel: the references' TMA descriptors
+    svtme::RowsMaps     rmaps;            // launch parameter of st_sad_rows_kernel<16, 32>
     uint64_t            ticket = 0;
     float               ms = 0.f;
     unsigned long long *h_px = nullptr;  // pinned
@@ -414,6 +415,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
         for (int r = 0; r < knobs->num_of_ref_pic_to_search[l]; r++) {
             p.refs[l][r] = refs[l][r]->dev;
             memcpy(maps->m[l * kMaxRefs + r], refs[l][r]->buf.maps, sizeof(maps->m[0]));
+            memcpy(sl->rmaps.m[l * kMaxRefs + r], refs[l][r]->buf.maps[kS16Classes * kS16HClasses], sizeof(sl->rmaps.m[0]));
         }
     p.n_steps = build_program(p.k, p.prog);
     p.wb = wb; p.hb = hb; p.pu_count = pu_count; p.work_counter = sl->d_counter;
@@ -454,7 +456,7 @@ int search_impl(SvtMeHandle *h, SvtMePic *cur, SvtMePic *const refs[SVTME_MAX_LI
         if (e == cudaSuccess) e = cudaMemcpyAsync(p.out.me_mv, me_in->me_mv, nb * pu_count * knobs->max_refs * 4, cudaMemcpyHostToDevice, st);
         if (e == cudaSuccess) e = cudaMemcpyAsync(p.out.me_cand, me_in->me_cand, nb * pu_count * knobs->max_cand, cudaMemcpyHostToDevice, st);
         if (e == cudaSuccess) e = cudaMemcpyAsync(p.out.total_me_candidate_index, me_in->total_me_candidate_index, nb * pu_count, cudaMemcpyHostToDevice, st);
-    } else if (e == cudaSuccess) e = launch_me_picture_staged(p, *maps, h->sm_count, st, &n_launch);
+    } else if (e == cudaSuccess) e = launch_me_picture_staged(p, *maps, sl->rmaps, h->sm_count, st, &n_launch);
     sl->tpl_to_host = false;
     if (tpl && e == cudaSuccess) {
         svtme::TplParams t;

@@ -18,7 +18,7 @@ cudaError_t launch_sad_peak(uint32_t *d_out, int grid, int iters, cudaStream_t s
 }  // namespace svtme
 namespace svtme {
 // staged (picture-wide kernels) execution of the step program; p.states must hold staged_state_bytes(n_sb) bytes
-cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, int sm_count, cudaStream_t st, int *n_launches);
+cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, const RowsMaps &rmaps, int sm_count, cudaStream_t st, int *n_launches);
 cudaError_t staged_set_attributes();  // per device, with the device current
 void        staged_print_phases();    // -DSVTME_PHASES builds only
 size_t      staged_state_bytes(uint32_t n_sb);

@@ -625,7 +625,7 @@ __device__ __forceinline__ void rows_unit(const uint32_t (&sreg)[NW], const uint
 
 template <int NW, int ROWS, bool FULLW>
 __device__ __forceinline__ void rows_job(const MeParams &p, int lvl, const SadJob &j, SadJob &jout, const uint32_t (&sreg)[NW],
-                                         uint32_t *win, int lane, int rows, int nw_eff, const S16Maps *maps = nullptr, uint32_t mbar = 0,
+                                         uint32_t *win, int lane, int rows, int nw_eff, const RowsMaps *maps = nullptr, uint32_t mbar = 0,
                                          uint32_t *phase = nullptr) {
     using C = RowsCfg<NW, ROWS>;
     const int W = j.sa_w, H = j.sa_h;
@@ -659,7 +659,7 @@ __device__ __forceinline__ void rows_job(const MeParams &p, int lvl, const SadJo
                 if (lane < 2) {  // window rows of parity `lane` = plane rows of parity (ty + lane) & 1, from row (ty + lane) >> 1 of that view
                     const int pr = ty + lane;
                     tma_load_2d(sbase + (uint32_t)lane * (uint32_t)(C::kPlaneW * 4),
-                                maps->m[j.li * kMaxRefs + j.ri][kS16Classes * kS16HClasses + (pr & 1)], tx, pr >> 1, mbar);
+                                maps->m[j.li * kMaxRefs + j.ri][pr & 1], tx, pr >> 1, mbar);
                 }
                 mbar_wait(mbar, *phase & 1u);
                 (*phase)++;
@@ -699,7 +699,7 @@ __device__ __forceinline__ void rows_job(const MeParams &p, int lvl, const SadJo
 #define SVTME_ROWS8_CTAS 6
 #endif
 template <int NW, int ROWS>
-__device__ __forceinline__ void sad_rows_block(const MeParams &p, int lvl, uint32_t sbi, const S16Maps *maps = nullptr, uint32_t mbar = 0,
+__device__ __forceinline__ void sad_rows_block(const MeParams &p, int lvl, uint32_t sbi, const RowsMaps *maps = nullptr, uint32_t mbar = 0,
                                                uint32_t *phase = nullptr) {
     using C = RowsCfg<NW, ROWS>;
     constexpr int kBlkPitch = 17;  // odd: lane = row reads are conflict free
@@ -743,7 +743,7 @@ __device__ __forceinline__ void sad_rows_block(const MeParams &p, int lvl, uint3
 // of the GPU's CTA slots (launch_me_picture_staged), so that the engines of two pictures in flight on different
 // streams are resident side by side instead of one after the other.
 template <int NW, int ROWS>
-__global__ void __launch_bounds__(kStThreads, NW == 8 ? SVTME_ROWS8_CTAS : 6) st_sad_rows_kernel(const __grid_constant__ MeParams p, const __grid_constant__ S16Maps maps, int lvl) {
+__global__ void __launch_bounds__(kStThreads, NW == 8 ? SVTME_ROWS8_CTAS : 6) st_sad_rows_kernel(const __grid_constant__ MeParams p, const __grid_constant__ RowsMaps maps, int lvl) {
     PDL_ENTRY();
     __shared__ __align__(8) unsigned long long mbar_store[kStWarps];  // one mbarrier per warp: a warp stages and searches its own windows
     const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -1806,7 +1806,7 @@ cudaError_t staged_set_attributes() {  // per device: call with the device curre
     return e;
 }
 
-cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, int sm_count, cudaStream_t st, int *n_launches) {
+cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, const RowsMaps &rmaps, int sm_count, cudaStream_t st, int *n_launches) {
     const int n_sb = (int)(p.wb * p.hb);
 #ifdef SVTME_DIAG
     static const int engine_ctas = getenv("SVTME_ENGINE_CTAS") ? atoi(getenv("SVTME_ENGINE_CTAS")) : SVTME_ENGINE_CTAS;
@@ -1858,8 +1858,8 @@ cudaError_t launch_me_picture_staged(const MeParams &p, const S16Maps &maps, int
         grid = engine_grid;
         if (p.prog[i].kind == STEP_SAD) {
             const int lvl = (int)p.prog[i].arg;
-            if (lvl == 1 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<8, 16>, 0, p, maps, lvl); mark("rows8"); }
-            else if (lvl == 0 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<16, 32>, 0, p, maps, lvl); mark("rows16"); }
+            if (lvl == 1 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<8, 16>, 0, p, rmaps, lvl); mark("rows8"); }
+            else if (lvl == 0 && p.k.hme_search_method == 0) { launch(st_sad_rows_kernel<16, 32>, 0, p, rmaps, lvl); mark("rows16"); }
             else if (lvl == 2 && p.k.hme_search_method == 0) {
                 // (diagnostics) 1: pre-HME windows, 2: HME level-0 quadrants -- by the control step that made the jobs
                 int tag = 2, qi = -1;

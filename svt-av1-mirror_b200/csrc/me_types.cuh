@@ -129,7 +129,12 @@ constexpr int kRowsTmaMaps = 2;
 constexpr int kMapsPerPic  = kS16Classes * kS16HClasses + kRowsTmaMaps;
 constexpr int kRowsTmaBoxW = 112, kRowsTmaBoxH = 36;
 struct alignas(64) S16Maps {
-    unsigned char m[kMaxLists * kMaxRefs][kMapsPerPic][kTmapBytes];
+    unsigned char m[kMaxLists * kMaxRefs][kS16Classes * kS16HClasses][kTmapBytes];
+};
+// the parity-view descriptors of the references' full planes, for st_sad_rows_kernel<16, 32> (2 KB: a launch copies its
+// parameters, and at 1080p M10 the pipeline is bound by launches)
+struct alignas(64) RowsMaps {
+    unsigned char m[kMaxLists * kMaxRefs][kRowsTmaMaps][kTmapBytes];
 };
 
 // ---- work descriptors produced by the per-SB control code and consumed by the search engines ----
