@@ -485,13 +485,10 @@ def main_strong(args, rank, local_rank, world, dist, wl):
         keep.append(t)
         return t.numpy()
 
-    owner = {0: 0}
-    for n, (poc, _, _, _) in enumerate(wl.pics):
-        owner[poc] = n % world
+    # who uploads which picture, and the (picture, source rank, destination rank) plane sets that cross GPUs in a mini-GOP
+    owner, transfers = shard.strong_plan(wl.pics, world)
     mine = [(n, e) for n, e in enumerate(wl.pics) if n % world == rank]
     outs = {n: abi.ResultBuffers(n_b64, e[1], extended=False, pinned_alloc=pinned) for n, e in mine}
-    # (picture, source rank, destination rank) of every plane set that crosses GPUs in a mini-GOP, the same list on every rank
-    transfers = sorted(set((p, owner[p], n % world) for n, (_, _, l0, l1) in enumerate(wl.pics) for p in l0 + l1 if owner[p] != n % world))
     nbytes = api.MeDevice.planes_bytes(w, h)
     # two sets of exchange buffers: the planes of mini-GOP g + 1 move while mini-GOP g is searched
     recvbuf = [{t: torch.empty(nbytes, dtype=torch.uint8, device="cuda") for t in transfers if t[2] == rank} for _ in range(2)]

@@ -51,3 +51,19 @@ def reduce_job(pictures_local, ms_local, dist=None, device="cpu"):
     dist.all_reduce(t, op=dist.ReduceOp.SUM)
     dist.all_reduce(m, op=dist.ReduceOp.MAX)
     return int(round(t.item())), float(m.item())
+
+
+def strong_plan(pics, world):
+    """--scaling strong: ONE clip over `world` ranks.  `pics` = the searches of a mini-GOP in decode order, each
+    (picture, knobs, list0, list1); search n goes to rank n % world, the leading base picture (0) is uploaded by rank 0.
+    Returns (owner, transfers): owner[picture] = the rank that uploads and decimates it; transfers = the sorted list of
+    (picture, source rank, destination rank) plane sets that cross GPUs -- the same list on every rank, so that the
+    point-to-point operations of all ranks pair up."""
+    if world <= 0:
+        raise ValueError("bad world: %r" % (world,))
+    owner = {0: 0}
+    for n, e in enumerate(pics):
+        owner[e[0]] = n % world
+    transfers = sorted(set((p, owner[p], n % world) for n, e in enumerate(pics) for p in list(e[2]) + list(e[3])
+                           if owner[p] != n % world))
+    return owner, transfers

@@ -91,3 +91,71 @@ def test_two_ranks_over_gloo_equal_one_process(oracle):
     assert merged.keys() == want.keys() and all(merged[k] == want[k] for k in want)
     for g in got:  # every rank sees the whole-job numbers: SUM of pictures, MAX of times
         assert g["pictures"] == GOP * NGOP and g["ms"] == 20.0
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# strong scaling: ONE clip over the ranks, reference planes replicated (bench.py --scaling strong)
+# ---------------------------------------------------------------------------------------------------------------------
+def _minigop(levels=4, n0=3, n1=2):
+    n = (1 << levels) + 1
+    return [(e["poc"], None, e["list0"][:n0], e["list1"][:n1]) for e in synth.minigop_structure(n, levels, n0, n1)]
+
+
+def test_strong_plan_covers_every_reference():
+    pics = _minigop()
+    for world in (1, 2, 3, 4, 8):
+        owner, transfers = shard.strong_plan(pics, world)
+        assert set(owner) == {0} | {e[0] for e in pics} and set(owner.values()) <= set(range(world))
+        assert transfers == sorted(set(transfers)) and all(s != d and owner[p] == s for p, s, d in transfers)
+        for n, (poc, _, l0, l1) in enumerate(pics):
+            r = n % world
+            assert owner[poc] == r  # a picture is uploaded and decimated by the rank that searches it
+            for p in l0 + l1:  # every reference is on the searching rank: its own, or received exactly once
+                assert owner[p] == r or (p, owner[p], r) in transfers
+        used = {(p, n % world) for n, (_, _, l0, l1) in enumerate(pics) for p in l0 + l1}
+        assert all((p, d) in used for p, _, d in transfers), "a plane set moves to a rank that never reads it"
+        if world == 1:
+            assert not transfers
+    with pytest.raises(ValueError):
+        shard.strong_plan(pics, 0)
+
+
+def _strong_worker(rank, world, port, outdir):
+    for p in (os.path.join(ROOT, "svt-av1-mirror_b200"), os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        pics = _minigop(levels=3, n0=2, n1=2)
+        owner, transfers = shard.strong_plan(pics, world)
+        # stand-in for a picture's plane set: bytes that only its owner can produce
+        planes = {p: torch.full((64,), (7 * p + 3) % 251, dtype=torch.uint8) for p in owner if owner[p] == rank}
+        recv = {t: torch.zeros(64, dtype=torch.uint8) for t in transfers if t[2] == rank}
+        ops = []
+        for t in transfers:  # the same order on every rank: the operations pair up
+            if t[1] == rank:
+                ops.append(dist.P2POp(dist.isend, planes[t[0]], t[2]))
+            elif t[2] == rank:
+                ops.append(dist.P2POp(dist.irecv, recv[t], t[1]))
+        for r in (dist.batch_isend_irecv(ops) if ops else []):
+            r.wait()
+        have = dict(planes)
+        have.update({t[0]: b for t, b in recv.items()})
+        ok = all(int(have[p][0]) == (7 * p + 3) % 251 and bool((have[p] == have[p][0]).all())
+                 for n, (_, _, l0, l1) in enumerate(pics) if n % world == rank for p in l0 + l1)
+        with open(os.path.join(outdir, "strong%d.pkl" % rank), "wb") as f:
+            pickle.dump({"ok": ok, "searches": [n for n in range(len(pics)) if n % world == rank], "received": len(recv)}, f)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_strong_exchange_over_gloo():
+    world = 2
+    port = 31500 + (os.getpid() % 2000)
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(_strong_worker, args=(world, port, d), nprocs=world, join=True)
+        got = [pickle.load(open(os.path.join(d, "strong%d.pkl" % r), "rb")) for r in range(world)]
+    assert all(g["ok"] for g in got), "a rank searched against planes it does not hold"
+    assert sorted(got[0]["searches"] + got[1]["searches"]) == list(range(8))
+    assert got[0]["received"] + got[1]["received"] > 0
