@@ -17,12 +17,20 @@ DECLS = (
     "void svtme_dump_pre_sb(struct PictureParentControlSet *pcs, unsigned b64);\n"
     "void svtme_dump_gm_level(struct PictureParentControlSet *pcs, unsigned char level);\n"
     "void svtme_dump_tpl(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs);\n"
+    "int svtme_gpu_me_picture(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs, struct MeContext *ctx,\n"
+    "                         struct EbPictureBufferDesc *input_pic, unsigned segment_index);\n"
     "void svtme_dump_picture(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs, struct MeContext *ctx,\n"
     "                        struct EbPictureBufferDesc *input_pic);\n"
 )
 
 # (file, anchor, text, where): `text` goes before/after the single line that contains `anchor`
 HOOKS = [
+    # me_process.c:173 -- in front of the 64x64 block loop of a TASK_PAME segment: with SVTME_GPU_ME=1 the whole picture is
+    # searched by libsvtme_cuda.so through the encoder-side shim (segment 0 does it, the other segments have nothing left to
+    # do), and the loop below runs over an empty range
+    ("me_process.c", "// 64x64 Block Loop",
+     "if (svtme_gpu_me_picture(scs, pcs, me_context_ptr->me_ctx, input_pic, segment_index)) y_b64_end_index = y_b64_start_index;\n",
+     "before"),
     # me_process.c:263 -- before the per-block search
     ("me_process.c", "svt_aom_motion_estimation_b64(pcs,", "svtme_dump_pre_sb(pcs, b64_index);\n", "before"),
     # me_process.c:282 -- the memset of the `else` branch is the last statement of the last-SB hook; the dump goes after

@@ -384,3 +384,41 @@ def test_tpl_refuses_unsupported_controls():
                 dev.me_tpl_picture(k, a, {(0, 0): b}, cfg)
     finally:
         dev.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# the drop-in, end to end: the reference encoder with its open-loop ME on the GPU writes the same bitstream
+# ---------------------------------------------------------------------------------------------------------------------
+ENC_BIN = os.path.join(ROOT, "oracle", "_ref", "SvtAv1EncApp_dump")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("preset,w,h", [(10, 320, 192), (6, 200, 136), (4, 192, 128)])
+def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h):
+    """oracle/_ref/SvtAv1EncApp_dump = the unmodified C-only reference encoder + one hook in front of me_process.c's 64x64
+    block loop (oracle/enc_overlay/).  SVTME_GPU_ME=1 sends every picture's open-loop ME through the compiled shim to
+    libsvtme_cuda.so; mode decision, TPL, rate control and entropy coding then run on those results.  The AV1 bitstream must
+    be the one the CPU ME gives, byte for byte, and the GPU run's own ME dump must equal the CPU run's."""
+    if not os.path.exists(ENC_BIN):
+        pytest.skip("oracle/_ref/SvtAv1EncApp_dump not built (make -C oracle enc, where /root/reference exists)")
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_enc_golden", os.path.join(GOLD, "make_enc_golden.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    clip = str(tmp_path / "clip.yuv")
+    gen.synth_clip(clip, w, h, 17, seed=4321 + preset)
+    outs = {}
+    for mode in ("cpu", "gpu"):
+        ivf, dump = str(tmp_path / (mode + ".ivf")), str(tmp_path / (mode + ".dump"))
+        env = dict(os.environ, SVTME_DUMP=dump)
+        if mode == "gpu":
+            env["SVTME_GPU_ME"] = "1"
+        else:
+            env.pop("SVTME_GPU_ME", None)
+        r = subprocess.run([ENC_BIN, "-i", clip, "-w", str(w), "-h", str(h), "--fps", "30", "-n", "17", "--preset", str(preset),
+                            "--lp", "1", "-b", ivf], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        assert r.returncode == 0, "%s encode failed:\n%s" % (mode, r.stdout[-1500:])
+        outs[mode] = (open(ivf, "rb").read(), os.path.getsize(dump) if os.path.exists(dump) else 0)
+    assert len(outs["cpu"][0]) > 1000
+    assert outs["cpu"][1] > 0 and outs["gpu"][1] == 0, "the GPU run must not have gone through the CPU block loop (its dump hooks sit there)"
+    assert outs["gpu"][0] == outs["cpu"][0], "bitstreams differ: %d vs %d bytes" % (len(outs["gpu"][0]), len(outs["cpu"][0]))
