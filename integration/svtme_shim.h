@@ -72,6 +72,12 @@ void    svtme_shim_close(SvtMeShim *s);
  * of every reference that is not resident yet, searches, scatters the results into `pcs`, evaluates the GM gate. */
 int32_t svtme_shim_me_picture(SvtMeShim *s, const SequenceControlSet *scs, PictureParentControlSet *pcs, const MeContext *ctx,
                               const EbPictureBufferDesc *input_pic, SvtMeShimGmGate *gate);
+/* TPL source-based search of one picture (the `tpl_src_data_ready == 0` decision of tpl_mc_flow_dispenser_sb_generic,
+ * src_ops_process.c:608-887) over the ME results `pcs` holds; to be called once per picture before its dispenser tasks are
+ * posted (src_ops_process.c:1378).  `out`: arrays laid out by svtme_shim_tpl_layout(out, pcs->enhanced_pic->width, height, mem).
+ * Returns 1 when the picture's TPL controls are outside what the library restates (the CPU path stays), 0 on success. */
+size_t  svtme_shim_tpl_layout(SvtMeTplResults *res, uint32_t width, uint32_t height, void *mem);
+int32_t svtme_shim_tpl_picture(SvtMeShim *s, const SequenceControlSet *scs, PictureParentControlSet *pcs, SvtMeTplResults *out);
 /* To be called where the encoder releases a PA reference object (pic_mgr / pd_process release of pa_ref_pic_wrapper). */
 void svtme_shim_forget(SvtMeShim *s, uint64_t picture_number);
 const char *svtme_shim_last_error(SvtMeShim *s);

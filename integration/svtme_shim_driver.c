@@ -75,7 +75,7 @@ void svtme_shim_forget(SvtMeShim *s, uint64_t picture_number) {
 
 /* The device planes of one PA reference object: resident already, or uploaded from its padded 8-bit luma
  * (EbPaReferenceObject.input_padded_pic, reference_object.h; the planes ME reads at me_process.c:139-143, 248-262). */
-static SvtMePic *shim_resident(SvtMeShim *s, const EbPaReferenceObject *obj, uint64_t picture_number) {
+static SvtMePic *shim_resident_desc(SvtMeShim *s, const EbPictureBufferDesc *d, uint64_t picture_number) {
     ShimPic *free_slot = NULL, *oldest = NULL;
     for (uint32_t i = 0; i < s->n_pics; i++) {
         ShimPic *p = &s->pics[i];
@@ -93,7 +93,6 @@ static SvtMePic *shim_resident(SvtMeShim *s, const EbPaReferenceObject *obj, uin
         oldest->pic = NULL;
         free_slot   = oldest;
     }
-    const EbPictureBufferDesc *d    = obj->input_padded_pic;
     const uint8_t             *luma = d->buffer_y + (size_t)d->org_y * d->stride_y + d->org_x;
     /* the ME planes are multiples of 8 wide/high (pcs->aligned_width/height): the padded picture holds them */
     const uint32_t w = (d->width + 7u) & ~7u, h = (d->height + 7u) & ~7u;
@@ -103,6 +102,10 @@ static SvtMePic *shim_resident(SvtMeShim *s, const EbPaReferenceObject *obj, uin
     free_slot->picture_number = picture_number;
     free_slot->last_use       = ++s->clock;
     return pic;
+}
+
+static SvtMePic *shim_resident(SvtMeShim *s, const EbPaReferenceObject *obj, uint64_t picture_number) {
+    return shim_resident_desc(s, obj->input_padded_pic, picture_number);
 }
 
 int32_t svtme_shim_me_picture(SvtMeShim *s, const SequenceControlSet *scs, PictureParentControlSet *pcs, const MeContext *ctx,
@@ -144,5 +147,88 @@ int32_t svtme_shim_me_picture(SvtMeShim *s, const SequenceControlSet *scs, Pictu
     svtme_shim_scatter_results(pcs, &res);
     pcs->me_processed_b64_count = pcs->b64_total_count; /* me_process.c:273 */
     svtme_shim_gm_gate(pcs, input_pic, res.picture_sums, gate);
+    return 0;
+}
+
+/* ---- TPL source-based search (src_ops_process.c:608-887) over the ME results the pcs holds ---- */
+
+size_t svtme_shim_tpl_layout(SvtMeTplResults *res, uint32_t width, uint32_t height, void *mem) {
+    const uint32_t gw = (width + 15) >> 4, gh = (height + 15) >> 4;
+    const size_t   cells = (size_t)gw * gh, elem[7] = {1, 1, 1, 4, 8, 4, 4};
+    size_t         off = 0, at[7];
+    for (int i = 0; i < 7; i++) {
+        off   = (off + 15) & ~(size_t)15;
+        at[i] = off;
+        off += elem[i] * cells;
+    }
+    if (mem) {
+        uint8_t *b = (uint8_t *)mem;
+        memset(res, 0, sizeof(*res));
+        res->grid_width = gw; res->grid_height = gh;
+        res->block_size = b + at[0]; res->best_mode = b + at[1]; res->best_rf_idx = (int8_t *)(b + at[2]);
+        res->mv = (int16_t *)(b + at[3]); res->ref_frame_poc = (uint64_t *)(b + at[4]);
+        res->best_inter_cost = (uint32_t *)(b + at[5]); res->best_intra_cost = (uint32_t *)(b + at[6]);
+    }
+    return (off + 15) & ~(size_t)15;
+}
+
+/* 1: the picture's TPL controls are outside what the library restates (keep the CPU path); 0: `out` is filled; < 0: error */
+int32_t svtme_shim_tpl_picture(SvtMeShim *s, const SequenceControlSet *scs, PictureParentControlSet *pcs, SvtMeTplResults *out) {
+    const TplControls *tc = &pcs->tpl_ctrls;
+    if (!tc->use_sad_in_src_search || tc->subpel_depth != FULL_PEL || tc->intra_mode_end != DC_PRED || scs->in_loop_ois == 0) return 1;
+    SvtMeTplCfg c;
+    memset(&c, 0, sizeof(c));
+    c.dispenser_search_level = tc->dispenser_search_level;
+    c.use_sad_in_src_search = c.subpel_full_pel = c.intra_dc_only = 1;
+    c.disable_intra_pred = tc->disable_intra_pred_nref && pcs->temporal_layer_index == pcs->hierarchical_levels; /* :567 */
+    c.slice_type_i       = pcs->slice_type == I_SLICE;                                                           /* :767 */
+    /* the pcs / scs part of the knob block (the search kernels do not run: only list shapes and array strides are read) */
+    SvtMeKnobs k;
+    memset(&k, 0, sizeof(k));
+    k.picture_number           = pcs->picture_number;
+    k.enable_me_8x8            = pcs->enable_me_8x8;
+    k.enable_me_16x16          = pcs->enable_me_16x16;
+    k.max_number_of_pus_per_sb = pcs->max_number_of_pus_per_sb;
+    k.max_cand                 = pcs->pa_me_data->max_cand;
+    k.max_refs                 = pcs->pa_me_data->max_refs;
+    k.max_l0                   = pcs->pa_me_data->max_l0;
+    k.num_of_list_to_search    = pcs->slice_type == P_SLICE ? 1 : 2;
+    k.num_of_ref_pic_to_search[0] = pcs->ref_list0_count_try;
+    k.num_of_ref_pic_to_search[1] = pcs->slice_type == B_SLICE ? pcs->ref_list1_count_try : 0;
+    k.num_hme_sa_w = k.num_hme_sa_h = 2;
+    k.me_type      = SVTME_ME_OPEN_LOOP;
+
+    SvtMePic *cur = shim_resident_desc(s, pcs->enhanced_pic, pcs->picture_number);
+    if (!cur) return shim_fail(s, "register source picture (TPL)");
+    SvtMePic *refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST];
+    memset(refs, 0, sizeof(refs));
+    if (!c.slice_type_i)
+        for (int li = 0; li < k.num_of_list_to_search; li++)
+            for (int ri = 0; ri < k.num_of_ref_pic_to_search[li]; ri++) {
+                const EbDownScaledBufDescPtrArray *r = &pcs->tpl_data.tpl_ref_ds_ptr_array[li][ri]; /* :111-144 */
+                const int32_t                      g = pcs->tpl_data.ref_tpl_group_idx[li][ri];
+                c.ref_poc[li][ri]      = r->picture_number;
+                c.ref_excluded[li][ri] = g > 0 && pcs->tpl_data.base_pcs->tpl_valid_pic[g] == 0;   /* :783-785 */
+                refs[li][ri]           = shim_resident_desc(s, (const EbPictureBufferDesc *)r->picture_ptr, r->picture_number);
+                if (!refs[li][ri]) return shim_fail(s, "register reference picture (TPL)");
+            }
+    SvtMePictureResults me;
+    memset(&me, 0, sizeof(me));
+    if (!c.slice_type_i) {
+        const uint32_t pus  = svtme_shim_pu_count(pcs);
+        const size_t   need = svtme_shim_results_layout(&me, pcs->b64_total_count, pus, k.max_refs, k.max_cand, NULL);
+        if (need > s->res_bytes) {
+            free(s->res_mem);
+            s->res_mem   = malloc(need);
+            s->res_bytes = s->res_mem ? need : 0;
+            if (!s->res_mem) return -1;
+        }
+        svtme_shim_results_layout(&me, pcs->b64_total_count, pus, k.max_refs, k.max_cand, s->res_mem);
+        svtme_shim_gather_results(pcs, &me);
+    }
+    uint64_t ticket = 0;
+    if (svtme_tpl_src_search(s->h, cur, (SvtMePic * const(*)[SVTME_MAX_REFS_PER_LIST]) refs, &k, c.slice_type_i ? NULL : &me, &c, out, &ticket) != 0)
+        return shim_fail(s, "svtme_tpl_src_search");
+    if (svtme_search_wait(s->h, ticket) != 0) return shim_fail(s, "svtme_search_wait (TPL)");
     return 0;
 }

@@ -17,6 +17,9 @@ DECLS = (
     "void svtme_dump_pre_sb(struct PictureParentControlSet *pcs, unsigned b64);\n"
     "void svtme_dump_gm_level(struct PictureParentControlSet *pcs, unsigned char level);\n"
     "void svtme_dump_tpl(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs);\n"
+    "void svtme_gpu_tpl_prepare(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs);\n"
+    "int svtme_gpu_tpl_block(struct PictureParentControlSet *pcs, unsigned x, unsigned y, unsigned char *best_mode, int *best_rf_idx,\n"
+    "                        void *final_best_mv, unsigned long long *best_ref_poc);\n"
     "int svtme_gpu_me_picture(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs, struct MeContext *ctx,\n"
     "                         struct EbPictureBufferDesc *input_pic, unsigned segment_index);\n"
     "void svtme_dump_picture(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs, struct MeContext *ctx,\n"
@@ -40,6 +43,14 @@ HOOKS = [
     # global_me.c:206 -- after the bypass test, before the level is used
     ("global_me.c", "if (global_motion_estimation_level) {", "svtme_dump_gm_level(pcs, global_motion_estimation_level);\n",
      "before"),
+    # src_ops_process.c:1378 -- before the picture's dispenser tasks are posted: with SVTME_GPU_ME=1 the source-based decisions of
+    # all its TPL blocks come from the GPU (svtme_shim_tpl_picture) ...
+    ("src_ops_process.c", "pcs->tpl_disp_coded_sb_count = 0;", "svtme_gpu_tpl_prepare(scs, pcs);\n", "after"),
+    # ... and src_ops_process.c:612-887, the intra + inter source search of one block, is skipped when its decision is there
+    ("src_ops_process.c", "            if (!disable_intra_pred) {",
+     "if (!svtme_gpu_tpl_block(pcs, mb_origin_x, mb_origin_y, &best_mode, &best_rf_idx, &final_best_mv, (unsigned long long *)&best_ref_poc)) {\n",
+     "before"),
+    ("src_ops_process.c", "                best_mode = NEWMV;", "}\n", "after"),
     # src_ops_process.c:1396 -- every SB of the picture went through tpl_mc_flow_dispenser_sb_generic
     ("src_ops_process.c", "svt_block_on_semaphore(pcs->tpl_disp_done_semaphore);", "svtme_dump_tpl(scs, pcs);\n", "after"),
 ]

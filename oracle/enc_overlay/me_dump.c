@@ -168,14 +168,14 @@ void svtme_dump_tpl(SequenceControlSet *scs, PictureParentControlSet *pcs) {
     const uint32_t             pus = svtme_shim_pu_count(pcs);
     struct {
         uint64_t picture_number;
-        uint32_t v[23];
+        uint32_t v[24]; /* 23 used; the 24th keeps the record free of uninitialised padding */
     } h = {pcs->picture_number,
            {in->width, in->height, pcs->aligned_width, pcs->b64_total_count, pus, (uint32_t)pcs->slice_type,
             pcs->temporal_layer_index, pcs->hierarchical_levels, pcs->enable_me_16x16, pcs->pa_me_data->max_cand,
             pcs->pa_me_data->max_refs, pcs->pa_me_data->max_l0, pcs->tpl_ctrls.dispenser_search_level,
             pcs->tpl_ctrls.disable_intra_pred_nref, (uint32_t)pcs->tpl_ctrls.intra_mode_end, pcs->tpl_ctrls.use_sad_in_src_search,
             (uint32_t)pcs->tpl_ctrls.subpel_depth, pcs->tpl_ctrls.subsample_tx, scs->tpl_lad_mg, scs->in_loop_ois,
-            pcs->ref_list0_count_try, pcs->ref_list1_count_try, 0}};
+            pcs->ref_list0_count_try, pcs->ref_list1_count_try, 0, 0}};
     tchunk("THDR", &h, sizeof(h));
     struct {
         uint64_t picture_number;

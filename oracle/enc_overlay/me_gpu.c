@@ -16,6 +16,16 @@
 static SvtMeShim      *g_shim;
 static int             g_state; /* 0: not looked at, 1: CPU ME, 2: GPU ME */
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
+/* what went through the GPU, written to $SVTME_GPU_STATS at exit (the test checks that the GPU paths were really taken) */
+static unsigned long long g_n_me, g_n_tpl_pics, g_n_tpl_blocks;
+static void               write_stats(void) {
+    const char *fn = getenv("SVTME_GPU_STATS");
+    FILE       *f  = fn ? fopen(fn, "w") : NULL;
+    if (f) {
+        fprintf(f, "{\"me_pictures\": %llu, \"tpl_pictures\": %llu, \"tpl_blocks\": %llu}\n", g_n_me, g_n_tpl_pics, g_n_tpl_blocks);
+        fclose(f);
+    }
+}
 
 /* returns 1 when the picture's ME is (being) done on the GPU: the caller skips its 64x64 block loop */
 int svtme_gpu_me_picture(SequenceControlSet *scs, PictureParentControlSet *pcs, MeContext *ctx, EbPictureBufferDesc *input_pic,
@@ -24,6 +34,7 @@ int svtme_gpu_me_picture(SequenceControlSet *scs, PictureParentControlSet *pcs, 
     if (g_state == 0) {
         const char *v = getenv("SVTME_GPU_ME");
         g_state       = (v && v[0] == '1') ? 2 : 1;
+        atexit(write_stats);
         if (g_state == 2 &&
             svtme_shim_open(scs, 0, 64, pcs->enable_hme_level1_flag || pcs->tf_enable_hme_level1_flag, &g_shim) != 0) {
             fprintf(stderr, "svtme: SVTME_GPU_ME=1 but the CUDA library could not be brought up -- no CPU fallback\n");
@@ -41,9 +52,58 @@ int svtme_gpu_me_picture(SequenceControlSet *scs, PictureParentControlSet *pcs, 
             abort();
         }
         /* the last-SB hook, me_process.c:272-287 (svt_aom_global_motion_estimation re-derives the same level from the arrays) */
+        g_n_me++;
         if (gate.run_gm) svt_aom_global_motion_estimation(pcs, input_pic);
         else memset(pcs->is_global_motion, false, MAX_NUM_OF_REF_PIC_LIST * REF_LIST_MAX_DEPTH);
     }
     pthread_mutex_unlock(&g_mu);
+    return 1;
+}
+
+/* ---- the TPL source-based decisions of one picture from the GPU (hooks in src_ops_process.c, see make_overlay.py) ----
+ * tpl_mc_flow_dispenser handles one picture at a time (it blocks on tpl_disp_done_semaphore), so one result set is enough;
+ * the per-block hook only reads it (several dispenser threads). */
+static uint64_t        g_tpl_poc = ~0ull;
+static SvtMeTplResults g_tpl;
+static void           *g_tpl_mem;
+static size_t          g_tpl_bytes;
+
+void svtme_gpu_tpl_prepare(SequenceControlSet *scs, PictureParentControlSet *pcs) {
+    g_tpl_poc = ~0ull;
+    if (g_state != 2 || pcs->tpl_src_data_ready) return; /* CPU ME, or the source path of this picture is already known */
+    pthread_mutex_lock(&g_mu);
+    const size_t need = svtme_shim_tpl_layout(&g_tpl, pcs->enhanced_pic->width, pcs->enhanced_pic->height, NULL);
+    if (need > g_tpl_bytes) {
+        free(g_tpl_mem);
+        g_tpl_mem   = malloc(need);
+        g_tpl_bytes = need;
+    }
+    svtme_shim_tpl_layout(&g_tpl, pcs->enhanced_pic->width, pcs->enhanced_pic->height, g_tpl_mem);
+    const int32_t rc = svtme_shim_tpl_picture(g_shim, scs, pcs, &g_tpl);
+    if (rc < 0) {
+        fprintf(stderr, "svtme: %s\n", svtme_shim_last_error(g_shim));
+        abort();
+    }
+    if (rc == 0) g_n_tpl_pics++;
+    if (rc == 0) g_tpl_poc = pcs->picture_number; /* rc == 1: controls the library does not restate -> the CPU search runs */
+    pthread_mutex_unlock(&g_mu);
+}
+
+/* 1: the decision of the block at (x, y) is filled in and the caller skips its intra + inter source search */
+int svtme_gpu_tpl_block(PictureParentControlSet *pcs, unsigned x, unsigned y, unsigned char *best_mode, int *best_rf_idx,
+                        void *final_best_mv, unsigned long long *best_ref_poc) {
+    if (g_tpl_poc != pcs->picture_number) return 0;
+    const uint32_t cell = (y >> 4) * g_tpl.grid_width + (x >> 4);
+    if (!g_tpl.block_size[cell]) {
+        fprintf(stderr, "svtme: TPL block (%u, %u) of picture %llu has no decision\n", x, y, (unsigned long long)pcs->picture_number);
+        abort();
+    }
+    __sync_fetch_and_add(&g_n_tpl_blocks, 1ull);
+    MV *mv        = (MV *)final_best_mv;
+    *best_mode    = g_tpl.best_mode[cell];
+    *best_rf_idx  = g_tpl.best_rf_idx[cell];
+    mv->row       = g_tpl.mv[2 * cell];
+    mv->col       = g_tpl.mv[2 * cell + 1];
+    *best_ref_poc = g_tpl.ref_frame_poc[cell];
     return 1;
 }

@@ -397,7 +397,8 @@ ENC_BIN = os.path.join(ROOT, "oracle", "_ref", "SvtAv1EncApp_dump")
 def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h):
     """oracle/_ref/SvtAv1EncApp_dump = the unmodified C-only reference encoder + one hook in front of me_process.c's 64x64
     block loop (oracle/enc_overlay/).  SVTME_GPU_ME=1 sends every picture's open-loop ME through the compiled shim to
-    libsvtme_cuda.so; mode decision, TPL, rate control and entropy coding then run on those results.  The AV1 bitstream must
+    libsvtme_cuda.so, and every picture's TPL source-based decisions come from tpl_src_kernel (svtme_shim_tpl_picture); mode
+    decision, the rest of TPL, rate control and entropy coding then run on those results.  The AV1 bitstream must
     be the one the CPU ME gives, byte for byte, and the GPU run's own ME dump must equal the CPU run's."""
     if not os.path.exists(ENC_BIN):
         pytest.skip("oracle/_ref/SvtAv1EncApp_dump not built (make -C oracle enc, where /root/reference exists)")
@@ -410,15 +411,21 @@ def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h):
     outs = {}
     for mode in ("cpu", "gpu"):
         ivf, dump = str(tmp_path / (mode + ".ivf")), str(tmp_path / (mode + ".dump"))
-        env = dict(os.environ, SVTME_DUMP=dump)
+        tdump = str(tmp_path / (mode + ".tpl"))
+        env = dict(os.environ, SVTME_DUMP=dump, SVTME_DUMP_TPL=tdump)
         if mode == "gpu":
             env["SVTME_GPU_ME"] = "1"
+            env["SVTME_GPU_STATS"] = str(tmp_path / "gpu_stats.json")
         else:
             env.pop("SVTME_GPU_ME", None)
         r = subprocess.run([ENC_BIN, "-i", clip, "-w", str(w), "-h", str(h), "--fps", "30", "-n", "17", "--preset", str(preset),
                             "--lp", "1", "-b", ivf], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         assert r.returncode == 0, "%s encode failed:\n%s" % (mode, r.stdout[-1500:])
-        outs[mode] = (open(ivf, "rb").read(), os.path.getsize(dump) if os.path.exists(dump) else 0)
+        outs[mode] = (open(ivf, "rb").read(), os.path.getsize(dump) if os.path.exists(dump) else 0, open(tdump, "rb").read())
     assert len(outs["cpu"][0]) > 1000
+    stats = json.load(open(str(tmp_path / "gpu_stats.json")))
+    assert stats["me_pictures"] == 16 and stats["tpl_pictures"] >= 5 and stats["tpl_blocks"] >= 5 * (w // 32) * (h // 32), stats
     assert outs["cpu"][1] > 0 and outs["gpu"][1] == 0, "the GPU run must not have gone through the CPU block loop (its dump hooks sit there)"
+    # TplSrcStats of every picture (+ the planes and ME results TPL read): the GPU run took them from tpl_src_kernel
+    assert len(outs["cpu"][2]) > 1000 and outs["gpu"][2] == outs["cpu"][2], "TPL source-based decisions differ"
     assert outs["gpu"][0] == outs["cpu"][0], "bitstreams differ: %d vs %d bytes" % (len(outs["gpu"][0]), len(outs["cpu"][0]))
