@@ -393,8 +393,8 @@ ENC_BIN = os.path.join(ROOT, "oracle", "_ref", "SvtAv1EncApp_dump")
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("preset,w,h", [(10, 320, 192), (6, 200, 136), (4, 192, 128)])
-def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h):
+@pytest.mark.parametrize("preset,w,h,frames", [(10, 320, 192, 17), (6, 200, 136, 17), (4, 192, 128, 17), (10, 1280, 720, 9)])
+def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h, frames):
     """oracle/_ref/SvtAv1EncApp_dump = the unmodified C-only reference encoder + one hook in front of me_process.c's 64x64
     block loop (oracle/enc_overlay/).  SVTME_GPU_ME=1 sends every picture's open-loop ME through the compiled shim to
     libsvtme_cuda.so, and every picture's TPL source-based decisions come from tpl_src_kernel (svtme_shim_tpl_picture); mode
@@ -407,7 +407,7 @@ def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h):
     gen = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(gen)
     clip = str(tmp_path / "clip.yuv")
-    gen.synth_clip(clip, w, h, 17, seed=4321 + preset)
+    gen.synth_clip(clip, w, h, frames, seed=4321 + preset)
     outs = {}
     for mode in ("cpu", "gpu"):
         ivf, dump = str(tmp_path / (mode + ".ivf")), str(tmp_path / (mode + ".dump"))
@@ -418,13 +418,13 @@ def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h):
             env["SVTME_GPU_STATS"] = str(tmp_path / "gpu_stats.json")
         else:
             env.pop("SVTME_GPU_ME", None)
-        r = subprocess.run([ENC_BIN, "-i", clip, "-w", str(w), "-h", str(h), "--fps", "30", "-n", "17", "--preset", str(preset),
+        r = subprocess.run([ENC_BIN, "-i", clip, "-w", str(w), "-h", str(h), "--fps", "30", "-n", str(frames), "--preset", str(preset),
                             "--lp", "1", "-b", ivf], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         assert r.returncode == 0, "%s encode failed:\n%s" % (mode, r.stdout[-1500:])
         outs[mode] = (open(ivf, "rb").read(), os.path.getsize(dump) if os.path.exists(dump) else 0, open(tdump, "rb").read())
     assert len(outs["cpu"][0]) > 1000
     stats = json.load(open(str(tmp_path / "gpu_stats.json")))
-    assert stats["me_pictures"] == 16 and stats["tpl_pictures"] >= 5 and stats["tpl_blocks"] >= 5 * (w // 32) * (h // 32), stats
+    assert stats["me_pictures"] == frames - 1 and stats["tpl_pictures"] >= 3 and stats["tpl_blocks"] >= 3 * (w // 32) * (h // 32), stats
     assert outs["cpu"][1] > 0 and outs["gpu"][1] == 0, "the GPU run must not have gone through the CPU block loop (its dump hooks sit there)"
     # TplSrcStats of every picture (+ the planes and ME results TPL read): the GPU run took them from tpl_src_kernel
     assert len(outs["cpu"][2]) > 1000 and outs["gpu"][2] == outs["cpu"][2], "TPL source-based decisions differ"
