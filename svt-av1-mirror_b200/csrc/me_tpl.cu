@@ -10,8 +10,8 @@
 // kernel slots in beside the search kernels of the pictures in flight.  A lane holds one source row of the block in registers
 // for all candidates (16-pixel blocks: each half-warp holds the 16 rows and the two halves cost two candidates per pass), reads
 // the matching reference row as aligned words funnel-shifted into place, packed-byte SAD (VABSDIFF4) per word, a (half-)warp
-// add-reduction per candidate, the running best in lane-uniform registers.  The kernel is bound by L2 sector traffic of the
-// reference rows (16 bytes of a 32-byte sector per row), not by arithmetic: ~5 candidates x 256 bytes per 16x16 block.
+// add-reduction per candidate, the running best in lane-uniform registers.  The kernel is bound by L1 wavefronts of the reference
+// rows (ncu: l1tex throughput 87 % of peak with word loads), not by arithmetic: ~5 candidates x 256 bytes per 16x16 block.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -48,17 +48,27 @@ struct Row {
         for (int i = 0; i < RW; i++) a = __vsadu4(w[i], dc4) + a;
         return a;
     }
-    // against RW * 4 bytes at any alignment: RW + 1 aligned words (all within the row's 32-byte sectors), funnel-shifted
+    // against RW * 4 bytes at any alignment: the RW / 4 + 1 aligned 16-byte chunks that cover them (128-bit loads: the kernel is
+    // bound by L1 wavefronts -- one row per lane means one cache line per lane and load instruction -- so a row costs 2 / 3 / 5
+    // load instructions instead of 5 / 9 / 17 word loads), rotated by the word offset with two select stages, then
+    // funnel-shifted by the byte offset.  The bytes read beyond the row are inside the plane's physical padding.
     __device__ __forceinline__ uint32_t sad_ref(const uint8_t *ref) const {
-        const uint32_t  mis = (uint32_t)(reinterpret_cast<uintptr_t>(ref) & 3);
-        const uint32_t *q   = reinterpret_cast<const uint32_t *>(ref - mis);
-        uint32_t a = 0, lo = q[0];
+        constexpr int   NV = RW / 4 + 1;
+        const uint32_t  m = (uint32_t)(reinterpret_cast<uintptr_t>(ref) & 15), wi = m >> 2, sh = (m & 3) * 8;
+        const uint4    *q4 = reinterpret_cast<const uint4 *>(ref - m);
+        uint32_t        q[4 * NV];
 #pragma unroll
-        for (int i = 0; i < RW; i++) {
-            const uint32_t hi = (i + 1 < RW || mis) ? q[i + 1] : 0u;
-            a  = __vsadu4(w[i], __funnelshift_r(lo, hi, mis * 8)) + a;
-            lo = hi;
+        for (int v = 0; v < NV; v++) {
+            const uint4 t = q4[v];
+            q[4 * v] = t.x; q[4 * v + 1] = t.y; q[4 * v + 2] = t.z; q[4 * v + 3] = t.w;
         }
+#pragma unroll
+        for (int i = 0; i + 1 < 4 * NV; i++) q[i] = (wi & 1) ? q[i + 1] : q[i];
+#pragma unroll
+        for (int i = 0; i + 2 < 4 * NV; i++) q[i] = (wi & 2) ? q[i + 2] : q[i];
+        uint32_t a = 0;
+#pragma unroll
+        for (int i = 0; i < RW; i++) a = __vsadu4(w[i], __funnelshift_r(q[i], q[i + 1], sh)) + a;
         return a;
     }
 };
