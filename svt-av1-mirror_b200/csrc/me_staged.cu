@@ -837,6 +837,9 @@ __global__ void __launch_bounds__(kStThreads) st_sad_kernel(const __grid_constan
 // share 7 of their 8 reference rows: 9 window rows (45 LDS, 108 SHF) per 256 SADs.  With prehme_skip_search_line only odd
 // candidate rows exist (y = 4k + 1 and 4k + 3).  The row pitch is 4 x odd words (8 consecutive rows fall on 8 different
 // bank quads).  Blocks cut by the picture edge take the generic per-warp path, one unit per job.
+#ifndef SVTME_S16_NYCAP
+#define SVTME_S16_NYCAP 448  // candidate rows of a sub-window at most (a unit is searched by ONE warp)
+#endif
 constexpr int kS16BufWords = 2304;  // per warp: 9 KB
 constexpr int kS16MaxSub   = 96;
 struct alignas(16) S16Sub {
@@ -882,7 +885,7 @@ __device__ void s16_plan(const MeParams &p, SbState &s, S16Plan &pl) {
         // rows of a strip: whole boxes of 32 or of 8 rows that fit the buffer, minus the 14 rows below the last candidate
         const int fit = kS16BufWords / pmax;
         ny_cap = max((fit / 32) * 32, (fit / 8) * 8) - 14;
-        ny_cap = min(448, ny_cap) & ~3;
+        ny_cap = min(SVTME_S16_NYCAP, ny_cap) & ~3;
         nst    = H <= ny_cap ? 1 : (H + ny_cap - 1) / ny_cap;
         cnt    = ((W + 127) >> 7) * nst;
         px     = (uint32_t)W * (uint32_t)(jobs[ji].skip_line ? (H >> 1) : H) * (8 * 16);
