@@ -1507,7 +1507,10 @@ __global__ void __launch_bounds__(kStThreads, 5) st_fp_sub_kernel(const __grid_c
 // warp owns its block -- jobs, window buffer, minima, results -- and never meets a barrier, so the four warps of a CTA
 // (four blocks) overlap each other's copies and searches.  A job whose window does not fit the warp's buffer is left to
 // the CTA-wide kernel, which then runs behind this one for those jobs only (`big` flag in the step's counter pair).
-constexpr int kFpWBufWords = 3584;  // 14 KB per warp: windows up to 64 x 32 candidates
+#ifndef SVTME_FPW_BUF_WORDS
+#define SVTME_FPW_BUF_WORDS 3584
+#endif
+constexpr int kFpWBufWords = SVTME_FPW_BUF_WORDS;  // 14 KB per warp: windows up to 64 x 32 candidates
 #ifndef SVTME_FPW_SPLIT
 #define SVTME_FPW_SPLIT 2
 #endif
@@ -1521,7 +1524,10 @@ __device__ __forceinline__ bool fp_job_small(const FpJob &j, int &a, int &ngroup
     return j.w <= 64 && j.h <= 64 && 2 * plane <= kFpWBufWords;
 }
 
-__global__ void __launch_bounds__(kStThreads, 4) st_fp_warp_kernel(const __grid_constant__ MeParams p, int qi) {
+#ifndef SVTME_FPW_CTAS
+#define SVTME_FPW_CTAS 4  // resident CTAs per SM the register budget is set for (128 registers)
+#endif
+__global__ void __launch_bounds__(kStThreads, SVTME_FPW_CTAS) st_fp_warp_kernel(const __grid_constant__ MeParams p, int qi) {
     PDL_ENTRY();
     extern __shared__ __align__(16) uint32_t fpw_all[];  // kStWarps x kFpWBufWords
     const int      warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
