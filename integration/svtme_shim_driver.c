@@ -40,7 +40,7 @@ int32_t svtme_shim_open(const SequenceControlSet *scs, int32_t device, uint32_t 
     cfg.device       = device;
     cfg.max_width    = scs->max_input_luma_width;
     cfg.max_height   = scs->max_input_luma_height;
-    cfg.max_pictures = pictures;
+    cfg.max_pictures = pictures && pictures < 9 ? 9 : pictures;
     cfg.max_inflight = 4;
     /* pic_analysis_process.c:1968-1992: the sixteenth plane is decimated from the quarter plane when the HME level 1
      * planes exist (step 2), from the full plane otherwise (step 4) */
@@ -49,7 +49,9 @@ int32_t svtme_shim_open(const SequenceControlSet *scs, int32_t device, uint32_t 
         free(s);
         return -1;
     }
-    s->n_pics = pictures ? pictures : 64;
+    /* at least one search's worth (source + 2 x 4 references): the least recently used picture is recycled when the cache is
+     * full, and that must never be one this very search has just collected */
+    s->n_pics = pictures ? (pictures < 9 ? 9 : pictures) : 64;
     s->pics   = (ShimPic *)calloc(s->n_pics, sizeof(ShimPic));
     *out      = s;
     return 0;

@@ -299,12 +299,13 @@ def test_cuda_replays_encoder_dump(fx):
 
 
 @pytest.mark.gpu
-def test_cuda_through_compiled_shim(shim, fx):
+@pytest.mark.parametrize("cache", [32, 4])  # 4 is raised to 9 by the shim: every search recycles least-recently-used pictures
+def test_cuda_through_compiled_shim(shim, fx, cache):
     """svtme_shim_me_picture -- upload, search, scatter into a PictureParentControlSet, gate -- gives the pcs contents the
     reference encoder had after its own ME of the same picture."""
     p0 = fx.pic(0)
     h = C.c_void_p()
-    assert shim.shimtb_open(p0["W"], p0["H"], 0, 32, p0["hme_l1"], C.byref(h)) == 0
+    assert shim.shimtb_open(p0["W"], p0["H"], 0, cache, p0["hme_l1"], C.byref(h)) == 0
     try:
         for i in range(fx.n):
             p = fx.pic(i)
