@@ -78,6 +78,12 @@ int32_t svtme_shim_me_picture(SvtMeShim *s, const SequenceControlSet *scs, Pictu
  * Returns 1 when the picture's TPL controls are outside what the library restates (the CPU path stays), 0 on success. */
 size_t  svtme_shim_tpl_layout(SvtMeTplResults *res, uint32_t width, uint32_t height, void *mem);
 int32_t svtme_shim_tpl_picture(SvtMeShim *s, const SequenceControlSet *scs, PictureParentControlSet *pcs, SvtMeTplResults *out);
+/* Dynamic-GOP detector (TASK_DG_DETECTOR_HME, me_process.c:327-329): the level-0 search of dg_detector_hme_level0
+ * (pd_process.c:492-590) for ALL segments of `ppcs` against ppcs->dg_detector->ref_pic, added into
+ * ppcs->dg_detector->metrics (the caller holds metrics_mutex or is the only segment doing work; seg_completed and the
+ * frame_done semaphore stay with the caller).  Both pictures are uploaded for this call only and not cached: the detector
+ * runs in picture decision, BEFORE temporal filtering rewrites the source planes ME will read later. */
+int32_t svtme_shim_dg_picture(SvtMeShim *s, PictureParentControlSet *ppcs);
 /* To be called where the encoder releases a PA reference object (pic_mgr / pd_process release of pa_ref_pic_wrapper). */
 void svtme_shim_forget(SvtMeShim *s, uint64_t picture_number);
 const char *svtme_shim_last_error(SvtMeShim *s);

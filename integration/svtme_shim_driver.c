@@ -40,7 +40,8 @@ int32_t svtme_shim_open(const SequenceControlSet *scs, int32_t device, uint32_t 
     cfg.device       = device;
     cfg.max_width    = scs->max_input_luma_width;
     cfg.max_height   = scs->max_input_luma_height;
-    cfg.max_pictures = pictures && pictures < 9 ? 9 : pictures;
+    /* + 2: the dynamic-GOP detector's uncached pair (svtme_shim_dg_picture) */
+    cfg.max_pictures = pictures ? (pictures < 9 ? 9 : pictures) + 2 : 0;
     cfg.max_inflight = 4;
     /* pic_analysis_process.c:1968-1992: the sixteenth plane is decimated from the quarter plane when the HME level 1
      * planes exist (step 2), from the full plane otherwise (step 4) */
@@ -150,6 +151,38 @@ int32_t svtme_shim_me_picture(SvtMeShim *s, const SequenceControlSet *scs, Pictu
     pcs->me_processed_b64_count = pcs->b64_total_count; /* me_process.c:273 */
     svtme_shim_gm_gate(pcs, input_pic, res.picture_sums, gate);
     return 0;
+}
+
+/* ---- dynamic-GOP detector, HME level 0 (pd_process.c:492-590) ---- */
+
+static SvtMePic *shim_upload_once(SvtMeShim *s, const PictureParentControlSet *p) {
+    const EbPictureBufferDesc *d    = ((const EbPaReferenceObject *)p->pa_ref_pic_wrapper->object_ptr)->input_padded_pic;
+    const uint8_t             *luma = d->buffer_y + (size_t)d->org_y * d->stride_y + d->org_x;
+    SvtMePic                  *pic  = NULL;
+    if (svtme_picture_register(s->h, p->picture_number, luma, d->stride_y, (d->width + 7u) & ~7u, (d->height + 7u) & ~7u, &pic) != 0)
+        return NULL;
+    return pic;
+}
+
+int32_t svtme_shim_dg_picture(SvtMeShim *s, PictureParentControlSet *ppcs) {
+    SvtMePic *src = shim_upload_once(s, ppcs);
+    SvtMePic *ref = src ? shim_upload_once(s, ppcs->dg_detector->ref_pic) : NULL;
+    int32_t   rc  = -1;
+    if (src && ref) {
+        SvtMeDgMetrics m;
+        rc = svtme_dg_detector_hme_level0(s->h, src, ref, ppcs->input_resolution, &m, NULL, NULL, NULL, NULL);
+        if (rc == 0) { /* pd_process.c:543-580, summed over the picture */
+            DGDetectorMetrics *dst = &ppcs->dg_detector->metrics;
+            dst->tot_dist += m.tot_dist;
+            dst->tot_cplx += m.tot_cplx;
+            dst->tot_active += m.tot_active;
+            dst->sum_in_vectors += m.sum_in_vectors;
+        }
+    }
+    if (rc != 0) shim_fail(s, "svtme_dg_detector_hme_level0");
+    if (src) svtme_picture_release(s->h, src);
+    if (ref) svtme_picture_release(s->h, ref);
+    return rc;
 }
 
 /* ---- TPL source-based search (src_ops_process.c:608-887) over the ME results the pcs holds ---- */

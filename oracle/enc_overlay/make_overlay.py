@@ -22,6 +22,8 @@ DECLS = (
     "                        void *final_best_mv, unsigned long long *best_ref_poc);\n"
     "int svtme_gpu_me_picture(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs, struct MeContext *ctx,\n"
     "                         struct EbPictureBufferDesc *input_pic, unsigned segment_index);\n"
+    "int svtme_gpu_dg_picture(struct PictureParentControlSet *ppcs, unsigned seg_idx);\n"
+    "void svtme_dump_dg(struct PictureParentControlSet *src_pcs);\n"
     "void svtme_dump_picture(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs, struct MeContext *ctx,\n"
     "                        struct EbPictureBufferDesc *input_pic);\n"
 )
@@ -43,6 +45,12 @@ HOOKS = [
     # global_me.c:206 -- after the bypass test, before the level is used
     ("global_me.c", "if (global_motion_estimation_level) {", "svtme_dump_gm_level(pcs, global_motion_estimation_level);\n",
      "before"),
+    # pd_process.c:517 -- in front of the block loop of a TASK_DG_DETECTOR_HME segment (dg_detector_hme_level0): with
+    # SVTME_GPU_ME=1 segment 0 has the whole picture searched by svtme_dg_detector_hme_level0 and the loop runs over nothing
+    ("pd_process.c", "for (uint32_t y_b64_idx = y_b64_start_idx; y_b64_idx < y_b64_end_idx; ++y_b64_idx) {",
+     "if (svtme_gpu_dg_picture(ppcs, seg_idx)) y_b64_end_idx = y_b64_start_idx;\n", "before"),
+    # pd_process.c:624 -- early_hme has every segment's metrics of one (source, reference) pair
+    ("pd_process.c", "svt_block_on_semaphore(src_pcs->dg_detector->frame_done_sem);", "svtme_dump_dg(src_pcs);\n", "after"),
     # src_ops_process.c:1378 -- before the picture's dispenser tasks are posted: with SVTME_GPU_ME=1 the source-based decisions of
     # all its TPL blocks come from the GPU (svtme_shim_tpl_picture) ...
     ("src_ops_process.c", "pcs->tpl_disp_coded_sb_count = 0;", "svtme_gpu_tpl_prepare(scs, pcs);\n", "after"),
@@ -85,7 +93,7 @@ def patch(name, text):
 def main():
     ref, out = pathlib.Path(sys.argv[1]), pathlib.Path(sys.argv[2])
     out.mkdir(parents=True, exist_ok=True)
-    for name in ("me_process.c", "global_me.c", "src_ops_process.c"):
+    for name in ("me_process.c", "global_me.c", "src_ops_process.c", "pd_process.c"):
         src = (ref / "Source/Lib/Codec" / name).read_text()
         (out / name).write_text(patch(name, src))
         print(f"overlay {out / name}")

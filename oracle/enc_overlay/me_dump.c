@@ -235,3 +235,20 @@ void svtme_dump_tpl(SequenceControlSet *scs, PictureParentControlSet *pcs) {
     fflush(g_tf);
     free(cells);
 }
+
+/* ---- dynamic-GOP detector: one text line per early_hme (pd_process.c:592-634) pair, after all its segments ---- */
+void svtme_dump_dg(PictureParentControlSet *src_pcs) {
+    static FILE *f;
+    static int   tried;
+    if (!tried) {
+        tried          = 1;
+        const char *fn = getenv("SVTME_DUMP_DG");
+        if (fn && *fn) f = fopen(fn, "w");
+    }
+    if (!f) return;
+    const DGDetectorMetrics *m = &src_pcs->dg_detector->metrics;
+    fprintf(f, "%llu %llu %llu %u %u %d\n", (unsigned long long)src_pcs->picture_number,
+            (unsigned long long)src_pcs->dg_detector->ref_pic->picture_number, (unsigned long long)m->tot_dist, m->tot_cplx,
+            m->tot_active, m->sum_in_vectors);
+    fflush(f);
+}

@@ -17,24 +17,25 @@ static SvtMeShim      *g_shim;
 static int             g_state; /* 0: not looked at, 1: CPU ME, 2: GPU ME */
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
 /* what went through the GPU, written to $SVTME_GPU_STATS at exit (the test checks that the GPU paths were really taken) */
-static unsigned long long g_n_me, g_n_tpl_pics, g_n_tpl_blocks;
+static unsigned long long g_n_me, g_n_tpl_pics, g_n_tpl_blocks, g_n_dg;
 static void               write_stats(void) {
     const char *fn = getenv("SVTME_GPU_STATS");
     FILE       *f  = fn ? fopen(fn, "w") : NULL;
     if (f) {
-        fprintf(f, "{\"me_pictures\": %llu, \"tpl_pictures\": %llu, \"tpl_blocks\": %llu}\n", g_n_me, g_n_tpl_pics, g_n_tpl_blocks);
+        fprintf(f, "{\"me_pictures\": %llu, \"tpl_pictures\": %llu, \"tpl_blocks\": %llu, \"dg_pictures\": %llu}\n", g_n_me, g_n_tpl_pics,
+                g_n_tpl_blocks, g_n_dg);
         fclose(f);
     }
 }
 
-/* returns 1 when the picture's ME is (being) done on the GPU: the caller skips its 64x64 block loop */
-int svtme_gpu_me_picture(SequenceControlSet *scs, PictureParentControlSet *pcs, MeContext *ctx, EbPictureBufferDesc *input_pic,
-                         unsigned segment_index) {
+/* first call: reads SVTME_GPU_ME and brings the library up.  Returns with g_mu HELD when the GPU path is on. */
+static int gpu_me_enabled(SequenceControlSet *scs, PictureParentControlSet *pcs) {
     pthread_mutex_lock(&g_mu);
     if (g_state == 0) {
         const char *v = getenv("SVTME_GPU_ME");
         g_state       = (v && v[0] == '1') ? 2 : 1;
         atexit(write_stats);
+        /* the two flags are set by picture analysis (pic_analysis_process.c:1968), so they are valid in every later kernel */
         if (g_state == 2 &&
             svtme_shim_open(scs, 0, 64, pcs->enable_hme_level1_flag || pcs->tf_enable_hme_level1_flag, &g_shim) != 0) {
             fprintf(stderr, "svtme: SVTME_GPU_ME=1 but the CUDA library could not be brought up -- no CPU fallback\n");
@@ -45,6 +46,13 @@ int svtme_gpu_me_picture(SequenceControlSet *scs, PictureParentControlSet *pcs, 
         pthread_mutex_unlock(&g_mu);
         return 0;
     }
+    return 1;
+}
+
+/* returns 1 when the picture's ME is (being) done on the GPU: the caller skips its 64x64 block loop */
+int svtme_gpu_me_picture(SequenceControlSet *scs, PictureParentControlSet *pcs, MeContext *ctx, EbPictureBufferDesc *input_pic,
+                         unsigned segment_index) {
+    if (!gpu_me_enabled(scs, pcs)) return 0;
     if (segment_index == 0) { /* one call per picture; the shim's picture cache is not thread-safe: under the lock */
         SvtMeShimGmGate gate;
         if (svtme_shim_me_picture(g_shim, scs, pcs, ctx, input_pic, &gate) != 0) {
@@ -55,6 +63,24 @@ int svtme_gpu_me_picture(SequenceControlSet *scs, PictureParentControlSet *pcs, 
         g_n_me++;
         if (gate.run_gm) svt_aom_global_motion_estimation(pcs, input_pic);
         else memset(pcs->is_global_motion, false, MAX_NUM_OF_REF_PIC_LIST * REF_LIST_MAX_DEPTH);
+    }
+    pthread_mutex_unlock(&g_mu);
+    return 1;
+}
+
+/* TASK_DG_DETECTOR_HME (hook in front of the block loop of dg_detector_hme_level0, pd_process.c:517): segment 0 searches the
+ * whole picture on the GPU and adds the picture's metrics; every segment then falls through to the reference's own
+ * seg_completed / frame_done_sem bookkeeping with an empty block range. */
+int svtme_gpu_dg_picture(PictureParentControlSet *ppcs, unsigned seg_idx) {
+    if (!gpu_me_enabled(ppcs->scs, ppcs)) return 0;
+    if (seg_idx == 0) {
+        svt_block_on_mutex(ppcs->dg_detector->metrics_mutex);
+        if (svtme_shim_dg_picture(g_shim, ppcs) != 0) {
+            fprintf(stderr, "svtme: %s\n", svtme_shim_last_error(g_shim));
+            abort();
+        }
+        svt_release_mutex(ppcs->dg_detector->metrics_mutex);
+        g_n_dg++;
     }
     pthread_mutex_unlock(&g_mu);
     return 1;

@@ -394,7 +394,9 @@ ENC_BIN = os.path.join(ROOT, "oracle", "_ref", "SvtAv1EncApp_dump")
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("preset,w,h,frames", [(10, 320, 192, 17), (6, 200, 136, 17), (4, 192, 128, 17), (10, 1280, 720, 9)])
+@pytest.mark.parametrize("preset,w,h,frames", [(10, 320, 192, 17), (6, 200, 136, 17), (4, 192, 128, 17), (10, 1280, 720, 9),
+                                                    # 33+ frames below M8: picture decision runs the dynamic-GOP detector
+                                                    (6, 200, 136, 40), (7, 640, 496, 34), (7, 896, 744, 34)])
 def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h, frames):
     """oracle/_ref/SvtAv1EncApp_dump = the unmodified C-only reference encoder + one hook in front of me_process.c's 64x64
     block loop (oracle/enc_overlay/).  SVTME_GPU_ME=1 sends every picture's open-loop ME through the compiled shim to
@@ -413,7 +415,8 @@ def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h, frames)
     for mode in ("cpu", "gpu"):
         ivf, dump = str(tmp_path / (mode + ".ivf")), str(tmp_path / (mode + ".dump"))
         tdump = str(tmp_path / (mode + ".tpl"))
-        env = dict(os.environ, SVTME_DUMP=dump, SVTME_DUMP_TPL=tdump)
+        dgdump = str(tmp_path / (mode + ".dg"))
+        env = dict(os.environ, SVTME_DUMP=dump, SVTME_DUMP_TPL=tdump, SVTME_DUMP_DG=dgdump)
         if mode == "gpu":
             env["SVTME_GPU_ME"] = "1"
             env["SVTME_GPU_STATS"] = str(tmp_path / "gpu_stats.json")
@@ -422,10 +425,15 @@ def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h, frames)
         r = subprocess.run([ENC_BIN, "-i", clip, "-w", str(w), "-h", str(h), "--fps", "30", "-n", str(frames), "--preset", str(preset),
                             "--lp", "1", "-b", ivf], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         assert r.returncode == 0, "%s encode failed:\n%s" % (mode, r.stdout[-1500:])
-        outs[mode] = (open(ivf, "rb").read(), os.path.getsize(dump) if os.path.exists(dump) else 0, open(tdump, "rb").read())
+        outs[mode] = (open(ivf, "rb").read(), os.path.getsize(dump) if os.path.exists(dump) else 0, open(tdump, "rb").read(),
+                      open(dgdump).read())
     assert len(outs["cpu"][0]) > 1000
     stats = json.load(open(str(tmp_path / "gpu_stats.json")))
     assert stats["me_pictures"] == frames - 1 and stats["tpl_pictures"] >= 3 and stats["tpl_blocks"] >= 3 * (w // 32) * (h // 32), stats
+    # DGDetectorMetrics of every (source, reference) pair picture decision evaluated
+    n_dg = len(outs["cpu"][3].splitlines())
+    assert n_dg == (3 * ((frames - 1) // 32) if preset < 8 else 0) and stats["dg_pictures"] == n_dg, (n_dg, stats)
+    assert outs["gpu"][3] == outs["cpu"][3], "dynamic-GOP detector metrics differ:\n%s\nvs\n%s" % (outs["gpu"][3], outs["cpu"][3])
     assert outs["cpu"][1] > 0 and outs["gpu"][1] == 0, "the GPU run must not have gone through the CPU block loop (its dump hooks sit there)"
     # TplSrcStats of every picture (+ the planes and ME results TPL read): the GPU run took them from tpl_src_kernel
     assert len(outs["cpu"][2]) > 1000 and outs["gpu"][2] == outs["cpu"][2], "TPL source-based decisions differ"
