@@ -14,31 +14,9 @@ static void area_mm_of(SvtMeAreaMinMax *d, const SearchAreaMinMax *s) {
     area_of(&d->sa_max, &s->sa_max);
 }
 
-void svtme_shim_knobs_from_me_context(const SequenceControlSet *scs, const PictureParentControlSet *pcs, const MeContext *c,
-                                      SvtMeKnobs *k) {
-    memset(k, 0, sizeof(*k));
-    /* (c) what motion_estimation.c reads from pcs / scs directly */
-    k->picture_number                  = pcs->picture_number;
-    k->hierarchical_levels             = pcs->hierarchical_levels;
-    k->similar_brightness_refs         = pcs->similar_brightness_refs;
-    k->input_resolution                = (uint8_t)scs->input_resolution;
-    k->enable_me_8x8                   = pcs->enable_me_8x8;
-    k->enable_me_16x16                 = pcs->enable_me_16x16;
-    k->max_number_of_pus_per_sb        = pcs->max_number_of_pus_per_sb;
-    k->gm_enabled                      = pcs->gm_ctrls.enabled;
-    k->gm_use_distance_based_active_th = pcs->gm_ctrls.use_distance_based_active_th;
-    k->only_l_bwd                      = scs->mrp_ctrls.only_l_bwd;
-    k->max_cand                        = pcs->pa_me_data->max_cand;
-    k->max_refs                        = pcs->pa_me_data->max_refs;
-    k->max_l0                          = pcs->pa_me_data->max_l0;
-    /* (b) what the SB loop copies into MeContext per message, me_process.c:216-227 */
-    k->num_of_list_to_search       = pcs->slice_type == P_SLICE ? 1 : 2;
-    k->num_of_ref_pic_to_search[0] = pcs->ref_list0_count_try;
-    k->num_of_ref_pic_to_search[1] = pcs->slice_type == B_SLICE ? pcs->ref_list1_count_try : 0;
-    k->temporal_layer_index        = pcs->temporal_layer_index;
-    k->is_ref                      = pcs->is_ref;
-    k->me_type                     = SVTME_ME_OPEN_LOOP;
-    /* (a) the block svt_aom_sig_deriv_me wrote, enc_mode_config.c:671-808 */
+/* the block svt_aom_sig_deriv_me (open loop, enc_mode_config.c:671-808) or svt_aom_sig_deriv_me_tf (temporal filter, :814-854)
+ * wrote into the MeContext */
+static void knobs_from_ctx(const MeContext *c, SvtMeKnobs *k) {
     k->hme_search_method      = c->hme_search_method;
     k->me_search_method       = c->me_search_method;
     k->enable_hme_flag        = c->enable_hme_flag;
@@ -85,6 +63,58 @@ void svtme_shim_knobs_from_me_context(const SequenceControlSet *scs, const Pictu
     k->me_safe_limit_zz_th         = c->me_safe_limit_zz_th;
     k->prev_me_stage_based_exit_th = c->prev_me_stage_based_exit_th;
     k->tf_me_exit_th               = 0;
+}
+
+void svtme_shim_knobs_from_me_context(const SequenceControlSet *scs, const PictureParentControlSet *pcs, const MeContext *c,
+                                      SvtMeKnobs *k) {
+    memset(k, 0, sizeof(*k));
+    /* (c) what motion_estimation.c reads from pcs / scs directly */
+    k->picture_number                  = pcs->picture_number;
+    k->hierarchical_levels             = pcs->hierarchical_levels;
+    k->similar_brightness_refs         = pcs->similar_brightness_refs;
+    k->input_resolution                = (uint8_t)scs->input_resolution;
+    k->enable_me_8x8                   = pcs->enable_me_8x8;
+    k->enable_me_16x16                 = pcs->enable_me_16x16;
+    k->max_number_of_pus_per_sb        = pcs->max_number_of_pus_per_sb;
+    k->gm_enabled                      = pcs->gm_ctrls.enabled;
+    k->gm_use_distance_based_active_th = pcs->gm_ctrls.use_distance_based_active_th;
+    k->only_l_bwd                      = scs->mrp_ctrls.only_l_bwd;
+    k->max_cand                        = pcs->pa_me_data->max_cand;
+    k->max_refs                        = pcs->pa_me_data->max_refs;
+    k->max_l0                          = pcs->pa_me_data->max_l0;
+    /* (b) what the SB loop copies into MeContext per message, me_process.c:216-227 */
+    k->num_of_list_to_search       = pcs->slice_type == P_SLICE ? 1 : 2;
+    k->num_of_ref_pic_to_search[0] = pcs->ref_list0_count_try;
+    k->num_of_ref_pic_to_search[1] = pcs->slice_type == B_SLICE ? pcs->ref_list1_count_try : 0;
+    k->temporal_layer_index        = pcs->temporal_layer_index;
+    k->is_ref                      = pcs->is_ref;
+    k->me_type                     = SVTME_ME_OPEN_LOOP;
+    knobs_from_ctx(c, k);
+}
+
+/* Temporal-filter searches (produce_temporally_filtered_pic, temporal_filtering.c:3129-3174): `c` is the MeContext of the TF
+ * segment thread after create_me_context_and_picture_control (:296, 316), the per-pair lines :3140-3164 and
+ * set_hme_search_params_mctf (:2759-2767), i.e. as svt_aom_motion_estimation_b64 would see it. */
+void svtme_shim_tf_knobs_from_me_context(const SequenceControlSet *scs, const PictureParentControlSet *centre_pcs, const MeContext *c,
+                                         SvtMeKnobs *k) {
+    memset(k, 0, sizeof(*k));
+    k->picture_number          = centre_pcs->picture_number;
+    k->hierarchical_levels     = centre_pcs->hierarchical_levels;
+    k->similar_brightness_refs = centre_pcs->similar_brightness_refs;
+    k->input_resolution        = (uint8_t)scs->input_resolution;
+    /* read by the candidate / statistics stage only, which ME_MCTF skips (motion_estimation.c:3126); pa_me_data is not
+     * assigned yet when picture decision runs the filter */
+    k->enable_me_8x8 = k->enable_me_16x16 = 1;
+    k->max_number_of_pus_per_sb = SQUARE_PU_COUNT;
+    k->max_cand = k->max_refs = k->max_l0 = 1;
+    knobs_from_ctx(c, k);
+    k->me_type                     = SVTME_ME_MCTF;
+    k->num_of_list_to_search       = 1;
+    k->num_of_ref_pic_to_search[0] = 1;
+    k->num_of_ref_pic_to_search[1] = 0;
+    k->temporal_layer_index        = c->temporal_layer_index;
+    k->is_ref                      = c->is_ref;
+    k->tf_me_exit_th               = c->tf_me_exit_th;
 }
 
 uint32_t svtme_shim_pu_count(const PictureParentControlSet *pcs) {

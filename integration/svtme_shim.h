@@ -33,6 +33,9 @@ extern "C" {
  * (me_process.c:121), `pcs` / `scs` as the SB loop reads them (me_process.c:216-227, motion_estimation.c passim). */
 void svtme_shim_knobs_from_me_context(const SequenceControlSet *scs, const PictureParentControlSet *pcs, const MeContext *ctx,
                                       SvtMeKnobs *k);
+/* The same for one temporal-filter search (ME_MCTF): `ctx` as svt_aom_motion_estimation_b64 sees it at temporal_filtering.c:3169 */
+void svtme_shim_tf_knobs_from_me_context(const SequenceControlSet *scs, const PictureParentControlSet *centre_pcs, const MeContext *ctx,
+                                         SvtMeKnobs *k);
 
 /* 85 / 21 / 5 square PUs per 64x64 block, as MeSbResults is allocated (pcs.c:106-110). */
 uint32_t svtme_shim_pu_count(const PictureParentControlSet *pcs);
@@ -84,6 +87,17 @@ int32_t svtme_shim_tpl_picture(SvtMeShim *s, const SequenceControlSet *scs, Pict
  * frame_done semaphore stay with the caller).  Both pictures are uploaded for this call only and not cached: the detector
  * runs in picture decision, BEFORE temporal filtering rewrites the source planes ME will read later. */
 int32_t svtme_shim_dg_picture(SvtMeShim *s, PictureParentControlSet *ppcs);
+/* Temporal-filter ME (produce_temporally_filtered_pic, temporal_filtering.c:3129-3174).  Replaces the call of
+ * svt_aom_motion_estimation_b64 at :3169 for block `b64_index` of `centre_pcs` against `ref_pcs`: the first request of a
+ * (centre, reference) pair searches the WHOLE picture on the GPU (ME_MCTF mode of svtme_picture_search) and keeps the pair's
+ * results until the next centre picture; every request then puts the block's outputs where the filter reads them:
+ * ctx->p_sb_best_sad / p_sb_best_mv [0][0] with the p_best_* pointers on them, search_results[0][0].hme_sc_x / y,
+ * tf_use_pred_64x64_only_th = 0xFF when the HME SAD was under tf_me_exit_th (motion_estimation.c:3109-3113), and
+ * tf_tot_horz_blks / tf_tot_vert_blks (:2469-2474).  The centre picture is uploaded at its first request -- before any block
+ * of it has been filtered in place -- and the neighbours per pair; neither goes into the open-loop picture cache.
+ * Not thread-safe: TF segment threads call it under one lock. */
+int32_t svtme_shim_tf_b64(SvtMeShim *s, const SequenceControlSet *scs, PictureParentControlSet *centre_pcs,
+                          PictureParentControlSet *ref_pcs, MeContext *ctx, uint32_t b64_index);
 /* To be called where the encoder releases a PA reference object (pic_mgr / pd_process release of pa_ref_pic_wrapper). */
 void svtme_shim_forget(SvtMeShim *s, uint64_t picture_number);
 const char *svtme_shim_last_error(SvtMeShim *s);

@@ -15,8 +15,24 @@ typedef struct ShimPic {
     SvtMePic *pic; /* NULL: free slot */
 } ShimPic;
 
+/* temporal filter: the results of one (centre, neighbour) pair, whole picture */
+#define SHIM_TF_PAIRS ALTREF_MAX_NFRAMES /* definitions.h: 33 */
+typedef struct ShimTfPair {
+    uint64_t  ref_picture_number;
+    int       valid;
+    void     *mem;
+    size_t    bytes;
+    uint32_t *best_sad, *best_mv; /* [b64][85] */
+    int16_t  *hme_sc;             /* [b64][2][4][2] */
+    uint8_t  *exit_sb;            /* [b64] */
+    uint32_t  blk_counts[2];
+} ShimTfPair;
+
 struct SvtMeShim {
     SvtMeHandle *h;
+    uint64_t     tf_centre_number;
+    SvtMePic    *tf_centre;
+    ShimTfPair   tf_pairs[SHIM_TF_PAIRS];
     ShimPic     *pics;
     uint32_t     n_pics;
     uint64_t     clock;
@@ -40,8 +56,8 @@ int32_t svtme_shim_open(const SequenceControlSet *scs, int32_t device, uint32_t 
     cfg.device       = device;
     cfg.max_width    = scs->max_input_luma_width;
     cfg.max_height   = scs->max_input_luma_height;
-    /* + 2: the dynamic-GOP detector's uncached pair (svtme_shim_dg_picture) */
-    cfg.max_pictures = pictures ? (pictures < 9 ? 9 : pictures) + 2 : 0;
+    /* + 2: the uncached pictures of svtme_shim_dg_picture (2) / svtme_shim_tf_b64 (centre + 1) */
+    cfg.max_pictures = pictures ? (pictures < 9 ? 9 : pictures) + 3 : 0;
     cfg.max_inflight = 4;
     /* pic_analysis_process.c:1968-1992: the sixteenth plane is decimated from the quarter plane when the HME level 1
      * planes exist (step 2), from the full plane otherwise (step 4) */
@@ -62,6 +78,8 @@ void svtme_shim_close(SvtMeShim *s) {
     if (!s) return;
     for (uint32_t i = 0; i < s->n_pics; i++)
         if (s->pics[i].pic) svtme_picture_release(s->h, s->pics[i].pic);
+    if (s->tf_centre) svtme_picture_release(s->h, s->tf_centre);
+    for (int i = 0; i < SHIM_TF_PAIRS; i++) free(s->tf_pairs[i].mem);
     svtme_destroy(s->h);
     free(s->pics);
     free(s->res_mem);
@@ -183,6 +201,101 @@ int32_t svtme_shim_dg_picture(SvtMeShim *s, PictureParentControlSet *ppcs) {
     if (src) svtme_picture_release(s->h, src);
     if (ref) svtme_picture_release(s->h, ref);
     return rc;
+}
+
+/* ---- temporal-filter ME (temporal_filtering.c:3129-3174) ---- */
+
+static ShimTfPair *shim_tf_pair(SvtMeShim *s, const SequenceControlSet *scs, PictureParentControlSet *centre,
+                                PictureParentControlSet *ref_pcs, const MeContext *ctx) {
+    if (!s->tf_centre || s->tf_centre_number != centre->picture_number) { /* a new centre picture: drop the previous one */
+        if (s->tf_centre) svtme_picture_release(s->h, s->tf_centre);
+        for (int i = 0; i < SHIM_TF_PAIRS; i++) s->tf_pairs[i].valid = 0;
+        s->tf_centre = shim_upload_once(s, centre);
+        if (!s->tf_centre) {
+            shim_fail(s, "register the temporal filter's centre picture");
+            return NULL;
+        }
+        s->tf_centre_number = centre->picture_number;
+    }
+    ShimTfPair *p = NULL;
+    for (int i = 0; i < SHIM_TF_PAIRS; i++) {
+        if (s->tf_pairs[i].valid && s->tf_pairs[i].ref_picture_number == ref_pcs->picture_number) return &s->tf_pairs[i];
+        if (!p && !s->tf_pairs[i].valid) p = &s->tf_pairs[i];
+    }
+    if (!p) {
+        snprintf(s->err, sizeof(s->err), "more than %d neighbours of one temporal-filter centre picture", SHIM_TF_PAIRS);
+        return NULL;
+    }
+    SvtMeKnobs k;
+    svtme_shim_tf_knobs_from_me_context(scs, centre, ctx, &k);
+    const EbPictureBufferDesc *d     = ((const EbPaReferenceObject *)centre->pa_ref_pic_wrapper->object_ptr)->input_padded_pic;
+    const uint32_t             w = (d->width + 7u) & ~7u, h = (d->height + 7u) & ~7u;
+    const size_t               n_b64 = (size_t)((w + 63) / 64) * ((h + 63) / 64);
+    const size_t               at_mv = n_b64 * 85 * 4, at_sc = 2 * at_mv, at_exit = at_sc + n_b64 * 16 * 2, need = at_exit + n_b64;
+    if (need > p->bytes) {
+        free(p->mem);
+        p->mem   = malloc(need);
+        p->bytes = p->mem ? need : 0;
+        if (!p->mem) {
+            snprintf(s->err, sizeof(s->err), "out of host memory for %zu temporal-filter result bytes", need);
+            return NULL;
+        }
+    }
+    p->best_sad = (uint32_t *)p->mem;
+    p->best_mv  = (uint32_t *)((uint8_t *)p->mem + at_mv);
+    p->hme_sc   = (int16_t *)((uint8_t *)p->mem + at_sc);
+    p->exit_sb  = (uint8_t *)p->mem + at_exit;
+
+    SvtMePic *ref = shim_upload_once(s, ref_pcs);
+    if (!ref) {
+        shim_fail(s, "register a temporal-filter neighbour");
+        return NULL;
+    }
+    SvtMePic *refs[SVTME_MAX_LISTS][SVTME_MAX_REFS_PER_LIST];
+    memset(refs, 0, sizeof(refs));
+    refs[0][0] = ref;
+    SvtMePictureResults res;
+    memset(&res, 0, sizeof(res));
+    res.b64_total_count = (uint32_t)n_b64;
+    res.pu_count        = SQUARE_PU_COUNT;
+    res.tf_best_sad     = p->best_sad;
+    res.tf_best_mv      = p->best_mv;
+    res.hme_sc          = p->hme_sc;
+    res.tf_exit_sb      = p->exit_sb;
+    res.tf_blk_counts   = p->blk_counts;
+    uint64_t ticket     = 0;
+    int32_t  rc = svtme_picture_search(s->h, s->tf_centre, (SvtMePic * const(*)[SVTME_MAX_REFS_PER_LIST]) refs, &k, &res, &ticket);
+    if (rc == 0) rc = svtme_search_wait(s->h, ticket);
+    if (rc != 0) shim_fail(s, "temporal-filter search");
+    svtme_picture_release(s->h, ref);
+    if (rc != 0) return NULL;
+    p->ref_picture_number = ref_pcs->picture_number;
+    p->valid              = 1;
+    return p;
+}
+
+int32_t svtme_shim_tf_b64(SvtMeShim *s, const SequenceControlSet *scs, PictureParentControlSet *centre_pcs,
+                          PictureParentControlSet *ref_pcs, MeContext *ctx, uint32_t b64_index) {
+    const ShimTfPair *p = shim_tf_pair(s, scs, centre_pcs, ref_pcs, ctx);
+    if (!p) return -1;
+    memcpy(ctx->p_sb_best_sad[0][0], p->best_sad + (size_t)b64_index * SQUARE_PU_COUNT, SQUARE_PU_COUNT * sizeof(uint32_t));
+    memcpy(ctx->p_sb_best_mv[0][0], p->best_mv + (size_t)b64_index * SQUARE_PU_COUNT, SQUARE_PU_COUNT * sizeof(uint32_t));
+    /* motion_estimation.c:1368-1384 */
+    ctx->p_best_sad_64x64 = &ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_64x64];
+    ctx->p_best_sad_32x32 = &ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_32x32_0];
+    ctx->p_best_sad_16x16 = &ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_16x16_0];
+    ctx->p_best_sad_8x8   = &ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_8x8_0];
+    ctx->p_best_mv64x64   = &ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_64x64];
+    ctx->p_best_mv32x32   = &ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_32x32_0];
+    ctx->p_best_mv16x16   = &ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_16x16_0];
+    ctx->p_best_mv8x8     = &ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_8x8_0];
+    const int16_t sc_x = p->hme_sc[(size_t)b64_index * 16], sc_y = p->hme_sc[(size_t)b64_index * 16 + 1];
+    ctx->search_results[0][0].hme_sc_x = sc_x;
+    ctx->search_results[0][0].hme_sc_y = sc_y;
+    if (abs(sc_x) > abs(sc_y)) ctx->tf_tot_horz_blks++; /* :2469-2474 */
+    else ctx->tf_tot_vert_blks++;
+    if (p->exit_sb[b64_index]) ctx->tf_use_pred_64x64_only_th = (uint8_t)~0; /* :3109-3113 */
+    return 0;
 }
 
 /* ---- TPL source-based search (src_ops_process.c:608-887) over the ME results the pcs holds ---- */

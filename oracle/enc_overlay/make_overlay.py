@@ -24,6 +24,10 @@ DECLS = (
     "                         struct EbPictureBufferDesc *input_pic, unsigned segment_index);\n"
     "int svtme_gpu_dg_picture(struct PictureParentControlSet *ppcs, unsigned seg_idx);\n"
     "void svtme_dump_dg(struct PictureParentControlSet *src_pcs);\n"
+    "int svtme_gpu_tf_b64(struct PictureParentControlSet *centre_pcs, struct PictureParentControlSet *ref_pcs, struct MeContext *ctx,\n"
+    "                     unsigned b64_index);\n"
+    "void svtme_dump_tf_b64(struct PictureParentControlSet *centre_pcs, struct PictureParentControlSet *ref_pcs, struct MeContext *ctx,\n"
+    "                       unsigned b64_index);\n"
     "void svtme_dump_picture(struct SequenceControlSet *scs, struct PictureParentControlSet *pcs, struct MeContext *ctx,\n"
     "                        struct EbPictureBufferDesc *input_pic);\n"
 )
@@ -51,6 +55,13 @@ HOOKS = [
      "if (svtme_gpu_dg_picture(ppcs, seg_idx)) y_b64_end_idx = y_b64_start_idx;\n", "before"),
     # pd_process.c:624 -- early_hme has every segment's metrics of one (source, reference) pair
     ("pd_process.c", "svt_block_on_semaphore(src_pcs->dg_detector->frame_done_sem);", "svtme_dump_dg(src_pcs);\n", "after"),
+    # temporal_filtering.c:3169 -- the ME call of produce_temporally_filtered_pic becomes conditional: with SVTME_GPU_ME=1 the
+    # block's outputs come from the whole-picture ME_MCTF search of the (centre, neighbour) pair (svtme_shim_tf_b64) ...
+    ("temporal_filtering.c", "svt_aom_motion_estimation_b64(centre_pcs,",
+     "if (!svtme_gpu_tf_b64(centre_pcs, pcs_list[frame_index], ctx, (uint32_t)blk_row * blk_cols + blk_col))\n", "before"),
+    # ... and :3174, after the call: what the filter is about to read from the MeContext
+    ("temporal_filtering.c", "input_picture_ptr_central); // source picture",
+     "svtme_dump_tf_b64(centre_pcs, pcs_list[frame_index], ctx, (uint32_t)blk_row * blk_cols + blk_col);\n", "after"),
     # src_ops_process.c:1378 -- before the picture's dispenser tasks are posted: with SVTME_GPU_ME=1 the source-based decisions of
     # all its TPL blocks come from the GPU (svtme_shim_tpl_picture) ...
     ("src_ops_process.c", "pcs->tpl_disp_coded_sb_count = 0;", "svtme_gpu_tpl_prepare(scs, pcs);\n", "after"),
@@ -93,7 +104,7 @@ def patch(name, text):
 def main():
     ref, out = pathlib.Path(sys.argv[1]), pathlib.Path(sys.argv[2])
     out.mkdir(parents=True, exist_ok=True)
-    for name in ("me_process.c", "global_me.c", "src_ops_process.c", "pd_process.c"):
+    for name in ("me_process.c", "global_me.c", "src_ops_process.c", "pd_process.c", "temporal_filtering.c"):
         src = (ref / "Source/Lib/Codec" / name).read_text()
         (out / name).write_text(patch(name, src))
         print(f"overlay {out / name}")

@@ -252,3 +252,25 @@ void svtme_dump_dg(PictureParentControlSet *src_pcs) {
             m->tot_active, m->sum_in_vectors);
     fflush(f);
 }
+
+/* ---- temporal-filter ME: one text line per (centre, neighbour, block) with what the filter reads from the MeContext ---- */
+void svtme_dump_tf_b64(PictureParentControlSet *centre_pcs, PictureParentControlSet *ref_pcs, MeContext *ctx, unsigned b64_index) {
+    static FILE *f;
+    static int   tried;
+    if (!tried) {
+        tried          = 1;
+        const char *fn = getenv("SVTME_DUMP_TF");
+        if (fn && *fn) f = fopen(fn, "w");
+    }
+    if (!f) return;
+    const int exited = ctx->tf_use_pred_64x64_only_th == (uint8_t)~0;
+    uint64_t  hs = 1469598103934665603ull, hm = hs; /* FNV-1a over the 85 SADs / 85 MVs; stale when the search exited early */
+    if (!exited)
+        for (int i = 0; i < SQUARE_PU_COUNT; i++) {
+            hs = (hs ^ ctx->p_sb_best_sad[0][0][i]) * 1099511628211ull;
+            hm = (hm ^ ctx->p_sb_best_mv[0][0][i]) * 1099511628211ull;
+        }
+    fprintf(f, "%llu %llu %u %d %d %d %016llx %016llx\n", (unsigned long long)centre_pcs->picture_number,
+            (unsigned long long)ref_pcs->picture_number, b64_index, exited, ctx->search_results[0][0].hme_sc_x,
+            ctx->search_results[0][0].hme_sc_y, (unsigned long long)hs, (unsigned long long)hm);
+}

@@ -17,13 +17,13 @@ static SvtMeShim      *g_shim;
 static int             g_state; /* 0: not looked at, 1: CPU ME, 2: GPU ME */
 static pthread_mutex_t g_mu = PTHREAD_MUTEX_INITIALIZER;
 /* what went through the GPU, written to $SVTME_GPU_STATS at exit (the test checks that the GPU paths were really taken) */
-static unsigned long long g_n_me, g_n_tpl_pics, g_n_tpl_blocks, g_n_dg;
+static unsigned long long g_n_me, g_n_tpl_pics, g_n_tpl_blocks, g_n_dg, g_n_tf_blocks;
 static void               write_stats(void) {
     const char *fn = getenv("SVTME_GPU_STATS");
     FILE       *f  = fn ? fopen(fn, "w") : NULL;
     if (f) {
-        fprintf(f, "{\"me_pictures\": %llu, \"tpl_pictures\": %llu, \"tpl_blocks\": %llu, \"dg_pictures\": %llu}\n", g_n_me, g_n_tpl_pics,
-                g_n_tpl_blocks, g_n_dg);
+        fprintf(f, "{\"me_pictures\": %llu, \"tpl_pictures\": %llu, \"tpl_blocks\": %llu, \"dg_pictures\": %llu, \"tf_blocks\": %llu}\n", g_n_me,
+                g_n_tpl_pics, g_n_tpl_blocks, g_n_dg, g_n_tf_blocks);
         fclose(f);
     }
 }
@@ -82,6 +82,19 @@ int svtme_gpu_dg_picture(PictureParentControlSet *ppcs, unsigned seg_idx) {
         svt_release_mutex(ppcs->dg_detector->metrics_mutex);
         g_n_dg++;
     }
+    pthread_mutex_unlock(&g_mu);
+    return 1;
+}
+
+/* Temporal-filter ME (hook in front of the svt_aom_motion_estimation_b64 call of produce_temporally_filtered_pic,
+ * temporal_filtering.c:3169): 1 = the block's ME outputs are in `ctx`, taken from the whole-picture GPU search of the pair. */
+int svtme_gpu_tf_b64(PictureParentControlSet *centre_pcs, PictureParentControlSet *ref_pcs, MeContext *ctx, unsigned b64_index) {
+    if (!gpu_me_enabled(centre_pcs->scs, centre_pcs)) return 0;
+    if (svtme_shim_tf_b64(g_shim, centre_pcs->scs, centre_pcs, ref_pcs, ctx, b64_index) != 0) {
+        fprintf(stderr, "svtme: %s\n", svtme_shim_last_error(g_shim));
+        abort();
+    }
+    g_n_tf_blocks++;
     pthread_mutex_unlock(&g_mu);
     return 1;
 }

@@ -416,7 +416,8 @@ def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h, frames)
         ivf, dump = str(tmp_path / (mode + ".ivf")), str(tmp_path / (mode + ".dump"))
         tdump = str(tmp_path / (mode + ".tpl"))
         dgdump = str(tmp_path / (mode + ".dg"))
-        env = dict(os.environ, SVTME_DUMP=dump, SVTME_DUMP_TPL=tdump, SVTME_DUMP_DG=dgdump)
+        tfdump = str(tmp_path / (mode + ".tf"))
+        env = dict(os.environ, SVTME_DUMP=dump, SVTME_DUMP_TPL=tdump, SVTME_DUMP_DG=dgdump, SVTME_DUMP_TF=tfdump)
         if mode == "gpu":
             env["SVTME_GPU_ME"] = "1"
             env["SVTME_GPU_STATS"] = str(tmp_path / "gpu_stats.json")
@@ -424,17 +425,34 @@ def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h, frames)
             env.pop("SVTME_GPU_ME", None)
         r = subprocess.run([ENC_BIN, "-i", clip, "-w", str(w), "-h", str(h), "--fps", "30", "-n", str(frames), "--preset", str(preset),
                             "--lp", "1", "-b", ivf], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
-        assert r.returncode == 0, "%s encode failed:\n%s" % (mode, r.stdout[-1500:])
+        assert r.returncode == 0, "%s encode failed:\n%s" % (mode, r.stdout[-400:])
         outs[mode] = (open(ivf, "rb").read(), os.path.getsize(dump) if os.path.exists(dump) else 0, open(tdump, "rb").read(),
-                      open(dgdump).read())
+                      open(dgdump).read() if os.path.exists(dgdump) else "",  # written at the first detector call only
+                      open(tfdump).read().splitlines() if os.path.exists(tfdump) else [])
     assert len(outs["cpu"][0]) > 1000
     stats = json.load(open(str(tmp_path / "gpu_stats.json")))
-    assert stats["me_pictures"] == frames - 1 and stats["tpl_pictures"] >= 3 and stats["tpl_blocks"] >= 3 * (w // 32) * (h // 32), stats
+    cpu, gpu, problems = outs["cpu"], outs["gpu"], []
+    if not (stats["me_pictures"] == frames - 1 and stats["tpl_pictures"] >= 3 and stats["tpl_blocks"] >= 3 * (w // 32) * (h // 32)):
+        problems.append("GPU paths not taken: %s" % stats)
     # DGDetectorMetrics of every (source, reference) pair picture decision evaluated
-    n_dg = len(outs["cpu"][3].splitlines())
-    assert n_dg == (3 * ((frames - 1) // 32) if preset < 8 else 0) and stats["dg_pictures"] == n_dg, (n_dg, stats)
-    assert outs["gpu"][3] == outs["cpu"][3], "dynamic-GOP detector metrics differ:\n%s\nvs\n%s" % (outs["gpu"][3], outs["cpu"][3])
-    assert outs["cpu"][1] > 0 and outs["gpu"][1] == 0, "the GPU run must not have gone through the CPU block loop (its dump hooks sit there)"
+    n_dg = len(cpu[3].splitlines())
+    if not (n_dg == (3 * ((frames - 1) // 32) if preset < 8 else 0) and stats["dg_pictures"] == n_dg):
+        problems.append("dynamic-GOP detector pairs: %d in the CPU run, stats %s" % (n_dg, stats))
+    if gpu[3] != cpu[3]:
+        problems.append("dynamic-GOP detector metrics differ:\n%s\nvs\n%s" % (gpu[3], cpu[3]))
+    # temporal filter: per (centre, neighbour, block) the early-exit flag, the HME centre and the 85 SADs / MVs the filter reads
+    tf = [{tuple(l.split()[:3]): l for l in o[4]} for o in (cpu, gpu)]
+    if not (len(tf[0]) >= (w // 64) * (h // 64) and stats["tf_blocks"] == len(cpu[4]) and tf[0].keys() == tf[1].keys()):
+        problems.append("temporal-filter blocks: %d in the CPU run, %d in the GPU run, stats %s" % (len(cpu[4]), len(gpu[4]), stats))
+    bad = [(tf[0][k], tf[1][k]) for k in sorted(tf[0]) if k in tf[1] and tf[0][k] != tf[1][k]]
+    if bad:
+        problems.append("temporal-filter ME differs in %d of %d blocks, exited %d; first (cpu, gpu): %s" %
+                        (len(bad), len(tf[0]), sum(l.split()[3] == "1" for l in cpu[4]), bad[:3]))
+    if not (cpu[1] > 0 and gpu[1] == 0):
+        problems.append("the GPU run must not have gone through the CPU block loop (its dump hooks sit there)")
     # TplSrcStats of every picture (+ the planes and ME results TPL read): the GPU run took them from tpl_src_kernel
-    assert len(outs["cpu"][2]) > 1000 and outs["gpu"][2] == outs["cpu"][2], "TPL source-based decisions differ"
-    assert outs["gpu"][0] == outs["cpu"][0], "bitstreams differ: %d vs %d bytes" % (len(outs["gpu"][0]), len(outs["cpu"][0]))
+    if not (len(cpu[2]) > 1000 and gpu[2] == cpu[2]):
+        problems.append("TPL source-based decisions differ")
+    if gpu[0] != cpu[0]:
+        problems.append("bitstreams differ: %d vs %d bytes" % (len(gpu[0]), len(cpu[0])))
+    assert not problems, "\n".join(problems)
