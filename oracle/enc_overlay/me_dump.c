@@ -262,6 +262,26 @@ void svtme_dump_tf_b64(PictureParentControlSet *centre_pcs, PictureParentControl
         const char *fn = getenv("SVTME_DUMP_TF");
         if (fn && *fn) f = fopen(fn, "w");
     }
+    /* the knob block of the pair (first block only) next to the TfControls fields svtme_derive_tf_knobs takes */
+    static FILE *fk;
+    static int   ktried;
+    if (!ktried) {
+        ktried         = 1;
+        const char *fn = getenv("SVTME_DUMP_TF_KNOBS");
+        if (fn && *fn) fk = fopen(fn, "wb");
+    }
+    if (fk && b64_index == 0) {
+        SvtMeKnobs k;
+        svtme_shim_tf_knobs_from_me_context(centre_pcs->scs, centre_pcs, ctx, &k);
+        const EbPictureBufferDesc *d = ((const EbPaReferenceObject *)centre_pcs->pa_ref_pic_wrapper->object_ptr)->input_padded_pic;
+        const uint64_t hdr[12] = {centre_pcs->picture_number, ref_pcs->picture_number, (d->width + 7u) & ~7u, (d->height + 7u) & ~7u,
+                                  centre_pcs->tf_ctrls.hme_me_level, centre_pcs->tf_ctrls.qp_opt, centre_pcs->tf_ctrls.me_exit_th,
+                                  centre_pcs->scs->static_config.qp, centre_pcs->temporal_layer_index, centre_pcs->is_ref,
+                                  centre_pcs->scs->static_config.enc_mode, sizeof(k)};
+        fwrite(hdr, sizeof(hdr), 1, fk);
+        fwrite(&k, sizeof(k), 1, fk);
+        fflush(fk);
+    }
     if (!f) return;
     const int exited = ctx->tf_use_pred_64x64_only_th == (uint8_t)~0;
     uint64_t  hs = 1469598103934665603ull, hm = hs; /* FNV-1a over the 85 SADs / 85 MVs; stale when the search exited early */

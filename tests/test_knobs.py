@@ -51,3 +51,22 @@ def test_bad_preset_rejected():
         api.derive_knobs(enc_mode=14, width=64, height=64)
     with pytest.raises(api.SvtMeError):
         api.derive_knobs(enc_mode=3, width=0, height=64)
+
+
+def test_tf_knobs_match_the_encoder():
+    """svtme_derive_tf_knobs against the knob block of the temporal filter's ME in the reference ENCODER: the fixture
+    (tests/golden/make_tf_knobs_golden.py) holds, per preset / size / qp / layer, what svtme_shim_tf_knobs_from_me_context
+    read out of the live MeContext at temporal_filtering.c:3169 -- stale open-loop fields of the thread's context included."""
+    import json
+    import os
+    from svtme import abi
+    recs = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "enc_tf_knobs.json")))["records"]
+    assert len(recs) >= 10 and {r["hme_me_level"] for r in recs} >= {1, 2, 3} and {r["me_exit_th"] for r in recs} >= {0, 256}
+    for r in recs:
+        assert r["knobs_bytes"] == C.sizeof(abi.Knobs), "SvtMeKnobs changed: regenerate the fixture"
+        enc = abi.Knobs.from_buffer_copy(bytes.fromhex(r["knobs"]))
+        ours = api.derive_tf_knobs(**{k: r[k] for k in ("hme_me_level", "qp_opt", "me_exit_th", "qp", "width", "height", "picture_number",
+                                                        "temporal_layer_index", "is_ref")})
+        d = _diff(enc, ours)
+        d.pop("hierarchical_levels", None)  # read only when two lists are searched (motion_estimation.c:2419): never in ME_MCTF; the derivation leaves it 0
+        assert not d, "%s: %s" % ({k: v for k, v in r.items() if k != "knobs"}, d)
