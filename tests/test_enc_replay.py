@@ -394,10 +394,12 @@ ENC_BIN = os.path.join(ROOT, "oracle", "_ref", "SvtAv1EncApp_dump")
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("preset,w,h,frames", [(10, 320, 192, 17), (6, 200, 136, 17), (4, 192, 128, 17), (10, 1280, 720, 9),
-                                                    # 33+ frames below M8: picture decision runs the dynamic-GOP detector
-                                                    (6, 200, 136, 40), (7, 640, 496, 34), (7, 896, 744, 34)])
-def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h, frames):
+@pytest.mark.parametrize("preset,w,h,frames,depth", [(10, 320, 192, 17, 8), (6, 200, 136, 17, 8), (4, 192, 128, 17, 8), (10, 1280, 720, 9, 8),
+                                                          # 33+ frames below M8: picture decision runs the dynamic-GOP detector
+                                                          (6, 200, 136, 40, 8), (7, 640, 496, 34, 8), (7, 896, 744, 34, 8),
+                                                          # 10-bit input: ME, TPL and the filter's ME read the 8 MSB planes
+                                                          (8, 320, 192, 17, 10), (4, 192, 128, 17, 10)])
+def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h, frames, depth):
     """oracle/_ref/SvtAv1EncApp_dump = the unmodified C-only reference encoder + one hook in front of me_process.c's 64x64
     block loop (oracle/enc_overlay/).  SVTME_GPU_ME=1 sends every picture's open-loop ME through the compiled shim to
     libsvtme_cuda.so, and every picture's TPL source-based decisions come from tpl_src_kernel (svtme_shim_tpl_picture); mode
@@ -411,6 +413,11 @@ def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h, frames)
     spec.loader.exec_module(gen)
     clip = str(tmp_path / "clip.yuv")
     gen.synth_clip(clip, w, h, frames, seed=4321 + preset)
+    depth_args = []
+    if depth == 10:  # the same clip with two random low bits, 16-bit little-endian samples
+        a = np.fromfile(clip, np.uint8).astype(np.uint16)
+        ((a << 2) | np.random.default_rng(preset).integers(0, 4, size=a.shape, dtype=np.uint16)).astype("<u2").tofile(clip)
+        depth_args = ["--input-depth", "10"]
     outs = {}
     for mode in ("cpu", "gpu"):
         ivf, dump = str(tmp_path / (mode + ".ivf")), str(tmp_path / (mode + ".dump"))
@@ -424,7 +431,7 @@ def test_encoder_bitstream_identical_with_gpu_me(tmp_path, preset, w, h, frames)
         else:
             env.pop("SVTME_GPU_ME", None)
         r = subprocess.run([ENC_BIN, "-i", clip, "-w", str(w), "-h", str(h), "--fps", "30", "-n", str(frames), "--preset", str(preset),
-                            "--lp", "1", "-b", ivf], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+                            "--lp", "1", "-b", ivf, *depth_args], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         assert r.returncode == 0, "%s encode failed:\n%s" % (mode, r.stdout[-400:])
         outs[mode] = (open(ivf, "rb").read(), os.path.getsize(dump) if os.path.exists(dump) else 0, open(tdump, "rb").read(),
                       open(dgdump).read() if os.path.exists(dgdump) else "",  # written at the first detector call only
