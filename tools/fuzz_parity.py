@@ -1,6 +1,7 @@
 """Randomised parity sweep (run on the GPU box): random picture sizes, presets, temporal layers, clip kinds, reference
 lists and modes (open-loop ME, TPL source-based search, temporal filter, dynamic-GOP detector, picture statistics) -- every output of the CUDA
-path against the oracle.  python tools/fuzz_parity.py [iterations] [seed]"""
+path against the oracle.  python tools/fuzz_parity.py [iterations] [seed] [min_w/8 max_w/8 min_h/8 max_h/8]
+(default sizes 64..712 x 64..472; e.g. `60 4242 120 481 68 271` draws 960x544 .. 3840x2160)"""
 import os
 import sys
 
@@ -14,14 +15,14 @@ import refbind  # noqa: E402
 from svtme import api  # noqa: E402
 
 
-def run(iters=40, seed=1234, verbose=True):
+def run(iters=40, seed=1234, verbose=True, w8=(8, 90), h8=(8, 60), n_threads=8):
     """Returns the list of failure messages (empty = every output of every case bit-exact)."""
     rng = np.random.default_rng(seed)
     oracle = refbind.Oracle()
     bad = []
     for it in range(iters):
-        w = int(rng.integers(8, 90)) * 8
-        h = int(rng.integers(8, 60)) * 8
+        w = int(rng.integers(*w8)) * 8
+        h = int(rng.integers(*h8)) * 8
         kind = str(rng.choice(["pan", "pan", "noise", "static", "zero"]))
         n = int(rng.integers(8, 10))  # enough pictures for 4 + 3 references
         seed = int(rng.integers(0, 1 << 30))
@@ -48,7 +49,7 @@ def run(iters=40, seed=1234, verbose=True):
                 l0, l1 = H.ref_lists(cur, n, k.num_of_ref_pic_to_search[0], k.num_of_ref_pic_to_search[1])
                 assert len(l0) == k.num_of_ref_pic_to_search[0] and len(l1) == k.num_of_ref_pic_to_search[1]
                 what += " M%d hl%d tl%d qp%d %s refs %s %s" % (em, hl, tl, qp, extra, l0, l1)
-                a = oracle.me_picture(k, po[cur], H.refs_dict(po, l0, l1), n_threads=8)
+                a = oracle.me_picture(k, po[cur], H.refs_dict(po, l0, l1), n_threads=n_threads)
                 px = oracle.last_px_compares()
                 b = dev.me_picture(k, pd[cur], H.refs_dict(pd, l0, l1), extended=True)
                 H.assert_same(a, b, what)
@@ -75,7 +76,7 @@ def run(iters=40, seed=1234, verbose=True):
                 k = api.derive_tf_knobs(hme_me_level=int(rng.integers(0, 5)), qp_opt=int(rng.integers(0, 2)),
                                         me_exit_th=int(rng.choice([0, 256, 4000])), qp=35, width=w, height=h, picture_number=cur,
                                         temporal_layer_index=0, is_ref=1)
-                a = oracle.me_picture(k, po[cur], {(0, 0): po[nb]}, n_threads=8)
+                a = oracle.me_picture(k, po[cur], {(0, 0): po[nb]}, n_threads=n_threads)
                 b = dev.me_picture(k, pd[cur], {(0, 0): pd[nb]})
                 for name in ("sb_best_sad", "sb_best_mv", "hme_sc", "do_ref", "tf_exit_sb", "tf_blk_counts"):
                     assert np.array_equal(a[name], b[name]), (what, name)
@@ -103,4 +104,6 @@ def run(iters=40, seed=1234, verbose=True):
 
 
 if __name__ == "__main__":
-    sys.exit(1 if run(int(sys.argv[1]) if len(sys.argv) > 1 else 40, int(sys.argv[2]) if len(sys.argv) > 2 else 1234) else 0)
+    a = [int(v) for v in sys.argv[1:]]
+    size = dict(w8=(a[2], a[3]), h8=(a[4], a[5]), n_threads=min(64, os.cpu_count() or 8)) if len(a) >= 6 else {}
+    sys.exit(1 if run(a[0] if len(a) > 0 else 40, a[1] if len(a) > 1 else 1234, **size) else 0)
