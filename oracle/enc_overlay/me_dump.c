@@ -50,6 +50,35 @@ static void plane_chunk(const char *tag, const EbPictureBufferDesc *d, uint32_t 
     free(tight);
 }
 
+/* ---- $SVTME_DUMP_PAIRS: the planes + knobs of every dynamic-GOP detector pair and temporal-filter pair (fixture enc_pairs.npz) */
+#include <pthread.h>
+static FILE           *g_pf;
+static int             g_ptried;
+static pthread_mutex_t g_pmu = PTHREAD_MUTEX_INITIALIZER;
+static FILE           *pairs_file(void) {
+    if (!g_ptried) {
+        g_ptried       = 1;
+        const char *fn = getenv("SVTME_DUMP_PAIRS");
+        if (fn && *fn) g_pf = fopen(fn, "wb");
+    }
+    return g_pf;
+}
+static void pchunk(const char *tag, const void *p, uint32_t n) {
+    fwrite(tag, 1, 4, g_pf);
+    fwrite(&n, 4, 1, g_pf);
+    if (n) fwrite(p, 1, n, g_pf);
+}
+static void pplane(const char *tag, const EbPictureBufferDesc *d, uint32_t w, uint32_t h) {
+    uint8_t *tight = (uint8_t *)malloc((size_t)w * h);
+    for (uint32_t y = 0; y < h; y++)
+        memcpy(tight + (size_t)y * w, d->buffer_y + (size_t)(d->org_y + y) * d->stride_y + d->org_x, w);
+    pchunk(tag, tight, w * h);
+    free(tight);
+}
+static const EbPaReferenceObject *pa_of(const PictureParentControlSet *p) {
+    return (const EbPaReferenceObject *)p->pa_ref_pic_wrapper->object_ptr;
+}
+
 /* before each svt_aom_motion_estimation_b64: clear what the pooled MeSbResults still holds from an earlier picture, so
  * that entries the search leaves unwritten (MVs of pruned references, candidates past the count) read 0 as in the flat ABI */
 void svtme_dump_pre_sb(PictureParentControlSet *pcs, uint32_t b64) {
@@ -245,6 +274,23 @@ void svtme_dump_dg(PictureParentControlSet *src_pcs) {
         const char *fn = getenv("SVTME_DUMP_DG");
         if (fn && *fn) f = fopen(fn, "w");
     }
+    if (pairs_file()) {
+        pthread_mutex_lock(&g_pmu);
+        const PictureParentControlSet *rp = src_pcs->dg_detector->ref_pic;
+        const DGDetectorMetrics       *dm = &src_pcs->dg_detector->metrics;
+        const uint32_t W = src_pcs->aligned_width, H = src_pcs->aligned_height;
+        const uint64_t hd[10] = {src_pcs->picture_number, rp->picture_number, W, H, src_pcs->input_resolution,
+                                 (uint64_t)(src_pcs->enable_hme_level1_flag || src_pcs->tf_enable_hme_level1_flag), dm->tot_dist,
+                                 dm->tot_cplx, dm->tot_active, (uint64_t)(int64_t)dm->sum_in_vectors};
+        pchunk("DGHD", hd, sizeof(hd));
+        pplane("DGS0", pa_of(src_pcs)->input_padded_pic, W, H);
+        pplane("DGR0", pa_of(rp)->input_padded_pic, W, H);
+        pplane("DGS2", pa_of(src_pcs)->sixteenth_downsampled_picture_ptr, W >> 2, H >> 2);
+        pplane("DGR2", pa_of(rp)->sixteenth_downsampled_picture_ptr, W >> 2, H >> 2);
+        pchunk("END ", NULL, 0);
+        fflush(g_pf);
+        pthread_mutex_unlock(&g_pmu);
+    }
     if (!f) return;
     const DGDetectorMetrics *m = &src_pcs->dg_detector->metrics;
     fprintf(f, "%llu %llu %llu %u %u %d\n", (unsigned long long)src_pcs->picture_number,
@@ -261,6 +307,33 @@ void svtme_dump_tf_b64(PictureParentControlSet *centre_pcs, PictureParentControl
         tried          = 1;
         const char *fn = getenv("SVTME_DUMP_TF");
         if (fn && *fn) f = fopen(fn, "w");
+    }
+    if (pairs_file()) {
+        static uint64_t seen_centre = ~0ull, seen_refs[ALTREF_MAX_NFRAMES];
+        static int      n_seen;
+        pthread_mutex_lock(&g_pmu); /* a second TF thread waits here until the centre plane is on file, then may filter */
+        const int new_centre = seen_centre != centre_pcs->picture_number;
+        if (new_centre) {
+            seen_centre = centre_pcs->picture_number;
+            n_seen      = 0;
+        }
+        int known = 0;
+        for (int i = 0; i < n_seen; i++) known |= seen_refs[i] == ref_pcs->picture_number;
+        if (!known && n_seen < ALTREF_MAX_NFRAMES) {
+            seen_refs[n_seen++] = ref_pcs->picture_number;
+            SvtMeKnobs k;
+            svtme_shim_tf_knobs_from_me_context(centre_pcs->scs, centre_pcs, ctx, &k);
+            const uint32_t W = centre_pcs->aligned_width, H = centre_pcs->aligned_height;
+            const uint64_t hd[6] = {centre_pcs->picture_number, ref_pcs->picture_number, W, H,
+                                    (uint64_t)(centre_pcs->enable_hme_level1_flag || centre_pcs->tf_enable_hme_level1_flag), sizeof(k)};
+            pchunk("TFHD", hd, sizeof(hd));
+            pchunk("TFKN", &k, sizeof(k));
+            if (new_centre) pplane("TFC0", pa_of(centre_pcs)->input_padded_pic, W, H);
+            pplane("TFR0", pa_of(ref_pcs)->input_padded_pic, W, H);
+            pchunk("END ", NULL, 0);
+            fflush(g_pf);
+        }
+        pthread_mutex_unlock(&g_pmu);
     }
     /* the knob block of the pair (first block only) next to the TfControls fields svtme_derive_tf_knobs takes */
     static FILE *fk;

@@ -44,8 +44,9 @@ ROOT = pathlib.Path(__file__).resolve().parents[2]
 ENC = ROOT / "oracle/_ref/SvtAv1EncApp_dump"
 
 
-def synth_clip(path, w, h, n, seed):
-    """Textured background panning (2,1) px/frame, a patch moving the other way, a flash at frame 9, +-2 noise."""
+def synth_clip(path, w, h, n, seed, pan=(2, 1), noise=2):
+    """Textured background panning (2,1) px/frame, a patch moving the other way, a flash at frame 9, +-2 noise.
+    pan=(0, 0), noise=0: a still background (the temporal filter's ME leaves early on such blocks)."""
     rng = np.random.default_rng(seed)
     big = rng.integers(0, 256, size=(h // 4 + 64, w // 4 + 64), dtype=np.uint8)
     big = np.kron(big, np.ones((4, 4), dtype=np.uint8)).astype(np.int32)
@@ -54,13 +55,13 @@ def synth_clip(path, w, h, n, seed):
     patch = rng.integers(0, 256, size=(48, 64)).astype(np.int32)
     with open(path, "wb") as f:
         for t in range(n):
-            ox, oy = 40 + 2 * t, 30 + t
+            ox, oy = 40 + pan[0] * t, 30 + pan[1] * t
             y = big[oy:oy + h, ox:ox + w].copy()
             px, py = (w - 80 - 3 * t) % (w - 64), (20 + 2 * t) % (h - 48)
             y[py:py + 48, px:px + 64] = patch
             if t == 9:
                 y = y + 12
-            y = np.clip(y + rng.integers(-2, 3, size=y.shape), 0, 255).astype(np.uint8)
+            y = np.clip(y + rng.integers(-noise, noise + 1, size=y.shape), 0, 255).astype(np.uint8)
             f.write(y.tobytes())
             f.write(np.full((h // 2, w // 2), 128, np.uint8).tobytes() * 2)
 

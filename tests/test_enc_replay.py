@@ -388,6 +388,111 @@ def test_tpl_refuses_unsupported_controls():
 
 
 # ---------------------------------------------------------------------------------------------------------------------
+# dynamic-GOP detector and temporal-filter ME against what the encoder's own picture decision / filter searched
+# (tests/golden/enc_pairs.npz, generator make_pairs_golden.py)
+# ---------------------------------------------------------------------------------------------------------------------
+def _pairs():
+    z = np.load(os.path.join(GOLD, "enc_pairs.npz"))
+    return z, json.loads(bytes(z["meta"]).decode())
+
+
+def _fnv(words):
+    h = 1469598103934665603
+    for v in words:
+        h = ((h ^ int(v)) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+def _dg_cases(z, meta, binding):
+    for i in range(meta["dg_pairs"]):
+        hd = [int(v) for v in z["dg_%d_head" % i]]
+        luma = z["luma_%dx%d" % (hd[2], hd[3])]
+        pics = []
+        for idx, num, s16 in ((z["dg_%d_planes" % i][0], hd[0], z["dg_%d_s16" % i]), (z["dg_%d_planes" % i][1], hd[1], z["dg_%d_r16" % i])):
+            pp = refbind.PaddedPicture(luma[idx], num)
+            binding.build_planes(pp, hd[5])
+            assert np.array_equal(pp.interior(2), s16), "sixteenth plane of picture %d differs from the encoder's" % num
+            pics.append(pp)
+        yield hd, luma, pics, dict(tot_dist=hd[6], tot_cplx=hd[7], tot_active=hd[8], sum_in_vectors=hd[9])
+
+
+def _tf_cases(z, meta):
+    from svtme import abi
+    for i in range(meta["tf_pairs"]):
+        hd = [int(v) for v in z["tf_%d_head" % i]]
+        k = abi.Knobs.from_buffer_copy(bytes(z["tf_%d_knobs" % i]))
+        assert k.me_type == 1 and k.num_of_list_to_search == 1 and k.picture_number == hd[0]
+        yield hd, z["luma_%dx%d" % (hd[2], hd[3])], z["tf_%d_planes" % i], k, z["tf_%d_blocks" % i], z["tf_%d_hash" % i]
+
+
+def _check_tf(hd, out, blocks, hashes):
+    """what the filter reads after svt_aom_motion_estimation_b64: exit flag, HME centre, the 85 SADs / MVs of [0][0]"""
+    n = len(blocks)
+    sad = np.asarray(out["sb_best_sad"]).reshape(n, 2, 4, 85)[:, 0, 0]
+    mv = np.asarray(out["sb_best_mv"]).reshape(n, 2, 4, 85)[:, 0, 0]
+    sc = np.asarray(out["hme_sc"]).reshape(n, 2, 4, 2)[:, 0, 0]
+    ex = np.asarray(out["tf_exit_sb"]).reshape(n)
+    for b in range(n):
+        what = "centre %d neighbour %d block %d" % (hd[0], hd[1], b)
+        assert int(ex[b]) == blocks[b][0] and (int(sc[b][0]), int(sc[b][1])) == (blocks[b][1], blocks[b][2]), what
+        if not blocks[b][0]:
+            assert (_fnv(sad[b]), _fnv(mv[b])) == (int(hashes[b][0]), int(hashes[b][1])), what
+    horz = int(np.sum(np.abs(sc[:, 0].astype(np.int64)) > np.abs(sc[:, 1].astype(np.int64))))
+    assert [int(v) for v in out["tf_blk_counts"]] == [horz, n - horz]  # motion_estimation.c:2469-2474
+
+
+def _replay_pairs_cpu(binding):
+    z, meta = _pairs()
+    assert meta["dg_pairs"] >= 3 and meta["tf_pairs"] >= 15 and meta["tf_early_exits"] >= 100
+    for hd, _, (src, ref), want in _dg_cases(z, meta, binding):
+        got = binding.dg_hme_level0(src, ref, hd[4])[0]
+        assert {k: int(got[k]) for k in want} == want, "detector pair %d / %d" % (hd[0], hd[1])
+    for hd, luma, planes, k, blocks, hashes in _tf_cases(z, meta):
+        pics = []
+        for idx, num in ((planes[0], hd[0]), (planes[1], hd[1])):
+            pp = refbind.PaddedPicture(luma[idx], num)
+            binding.build_planes(pp, hd[4])
+            pics.append(pp)
+        _check_tf(hd, binding.me_picture(k, pics[0], {(0, 0): pics[1]}), blocks, hashes)
+
+
+def test_oracle_dg_and_tf_match_the_encoder(oracle):
+    _replay_pairs_cpu(oracle)
+
+
+def test_reference_harness_dg_and_tf_match_the_encoder(reference):
+    _replay_pairs_cpu(reference)
+
+
+@pytest.mark.gpu
+def test_cuda_dg_and_tf_match_the_encoder():
+    from svtme import api
+    z, meta = _pairs()
+    for hl1 in (0, 1):
+        dev = api.MeDevice(device=0, sixteenth_from_full=0 if hl1 else 1)
+        try:
+            for i in range(meta["dg_pairs"]):
+                hd = [int(v) for v in z["dg_%d_head" % i]]
+                if hd[5] != hl1:
+                    continue
+                luma, pl = z["luma_%dx%d" % (hd[2], hd[3])], z["dg_%d_planes" % i]
+                src, ref = dev.register(luma[pl[0]], hd[0]), dev.register(luma[pl[1]], hd[1])
+                m = dev.dg_hme_level0(src, ref, hd[4])[0]
+                assert [int(m[k]) for k in ("tot_dist", "tot_cplx", "tot_active", "sum_in_vectors")] == hd[6:10], hd
+                src.release()
+                ref.release()
+            for hd, luma, planes, k, blocks, hashes in _tf_cases(z, meta):
+                if hd[4] != hl1:
+                    continue
+                cur, nb = dev.register(luma[planes[0]], hd[0]), dev.register(luma[planes[1]], hd[1])
+                _check_tf(hd, dev.me_picture(k, cur, {(0, 0): nb}), blocks, hashes)
+                cur.release()
+                nb.release()
+        finally:
+            dev.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
 # the drop-in, end to end: the reference encoder with its open-loop ME on the GPU writes the same bitstream
 # ---------------------------------------------------------------------------------------------------------------------
 ENC_BIN = os.path.join(ROOT, "oracle", "_ref", "SvtAv1EncApp_dump")
