@@ -70,3 +70,29 @@ def test_tf_knobs_match_the_encoder():
         d = _diff(enc, ours)
         d.pop("hierarchical_levels", None)  # read only when two lists are searched (motion_estimation.c:2419): never in ME_MCTF; the derivation leaves it 0
         assert not d, "%s: %s" % ({k: v for k, v in r.items() if k != "knobs"}, d)
+
+
+@pytest.mark.parametrize("name", ["enc_m10", "enc_m4", "enc_m6"])
+def test_knobs_match_the_encoder(name):
+    """svtme_derive_knobs against the knob block the shim read out of the reference ENCODER's live MeContext / pcs for every
+    picture of the encoder-level fixtures (tests/golden/make_enc_golden.py; presets 10 / 4 / 6, all temporal layers, P and B
+    slices).  Two fields are not derivable from the preset: similar_brightness_refs comes from the picture's content
+    (pd_process.c), and the reference counts are picture decision's ref_list{0,1}_count_try (what the DPB holds at that point of
+    the sequence, pruned per layer): the derivation gives their upper bound."""
+    import json
+    import os
+    import numpy as np
+    from svtme import abi
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", name + ".npz"))
+    meta = json.loads(bytes(z["meta"]))
+    for i in range(meta["pictures"]):
+        head = [int(v) for v in z["pic_%d_head" % i]]
+        enc = abi.Knobs.from_buffer_copy(bytes(z["pic_%d_knobs" % i]))
+        ours = api.derive_knobs(enc_mode=meta["preset"], qp=35, frame_rate_q16=30 * Q16, width=head[1], height=head[2],
+                                hierarchical_levels=enc.hierarchical_levels, picture_number=head[0], temporal_layer_index=head[7],
+                                is_ref=enc.is_ref, slice_type_b=1 if head[5] == 0 else 0)
+        d = _diff(enc, ours)
+        d.pop("similar_brightness_refs", None)
+        got, cap = d.pop("num_of_ref_pic_to_search", (None, None))
+        assert not d, "picture %d: %s" % (head[0], d)
+        assert got is None or all(g <= c for g, c in zip(got, cap)), (head[0], got, cap)
