@@ -1,12 +1,13 @@
 #!/usr/bin/env python3
-"""TEST INFRASTRUCTURE ONLY.  Writes build-time copies of two reference files with the dump hooks inserted.
+"""TEST INFRASTRUCTURE ONLY.  Prints one reference source file with the dump / GPU hooks inserted, for the compiler to read.
 
-    make_overlay.py <reference root> <out dir>
+    make_overlay.py <reference root> <file name>  > <temporary translation unit>
 
-Reads  <ref>/Source/Lib/Codec/{me_process.c, global_me.c, src_ops_process.c}, inserts the calls into
-oracle/enc_overlay/me_dump.c listed in HOOKS below, and writes the results into <out dir> (oracle/_ref/enc/, git-ignored).
-The copies exist only there; no reference source is committed.  Every anchor must match exactly once, else the script
-fails: a reference update that moves the code is noticed instead of silently dumping nothing.
+Reads <ref>/Source/Lib/Codec/<file name> (me_process.c, global_me.c, src_ops_process.c, pd_process.c, temporal_filtering.c)
+and inserts the calls into oracle/enc_overlay/me_dump.c / me_gpu.c listed in HOOKS below.  oracle/Makefile compiles the output
+and deletes it in the same recipe: no copy of a reference source stays on disk, let alone in the repository -- only the object
+file under oracle/_ref/enc/.  Every anchor must match exactly once, else the script fails: a reference update that moves the
+code is noticed instead of silently hooking nothing.
 """
 import pathlib
 import sys
@@ -102,12 +103,8 @@ def patch(name, text):
 
 
 def main():
-    ref, out = pathlib.Path(sys.argv[1]), pathlib.Path(sys.argv[2])
-    out.mkdir(parents=True, exist_ok=True)
-    for name in ("me_process.c", "global_me.c", "src_ops_process.c", "pd_process.c", "temporal_filtering.c"):
-        src = (ref / "Source/Lib/Codec" / name).read_text()
-        (out / name).write_text(patch(name, src))
-        print(f"overlay {out / name}")
+    ref, name = pathlib.Path(sys.argv[1]), sys.argv[2]
+    sys.stdout.write(patch(name, (ref / "Source/Lib/Codec" / name).read_text()))
 
 
 if __name__ == "__main__":
