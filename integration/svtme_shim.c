@@ -117,6 +117,29 @@ void svtme_shim_tf_knobs_from_me_context(const SequenceControlSet *scs, const Pi
     k->tf_me_exit_th               = c->tf_me_exit_th;
 }
 
+/* What svt_aom_motion_estimation_b64 leaves in the MeContext for the temporal filter (ME_MCTF), from one block's row of a
+ * whole-picture search: p_sb_best_sad / p_sb_best_mv [0][0] with the p_best_* pointers on them (motion_estimation.c:1368-1384),
+ * the HME centre (:2465), the horizontal / vertical block count (:2469-2474) and the early-exit mark (:3109-3113). */
+void svtme_shim_tf_fill_b64(MeContext *ctx, const uint32_t *best_sad, const uint32_t *best_mv, int16_t hme_sc_x, int16_t hme_sc_y,
+                            int exited) {
+    memcpy(ctx->p_sb_best_sad[0][0], best_sad, SQUARE_PU_COUNT * sizeof(uint32_t));
+    memcpy(ctx->p_sb_best_mv[0][0], best_mv, SQUARE_PU_COUNT * sizeof(uint32_t));
+    ctx->p_best_sad_64x64 = &ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_64x64];
+    ctx->p_best_sad_32x32 = &ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_32x32_0];
+    ctx->p_best_sad_16x16 = &ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_16x16_0];
+    ctx->p_best_sad_8x8   = &ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_8x8_0];
+    ctx->p_best_mv64x64   = &ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_64x64];
+    ctx->p_best_mv32x32   = &ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_32x32_0];
+    ctx->p_best_mv16x16   = &ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_16x16_0];
+    ctx->p_best_mv8x8     = &ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_8x8_0];
+    ctx->search_results[0][0].hme_sc_x = hme_sc_x;
+    ctx->search_results[0][0].hme_sc_y = hme_sc_y;
+    const int ax = hme_sc_x < 0 ? -hme_sc_x : hme_sc_x, ay = hme_sc_y < 0 ? -hme_sc_y : hme_sc_y;
+    if (ax > ay) ctx->tf_tot_horz_blks++;
+    else ctx->tf_tot_vert_blks++;
+    if (exited) ctx->tf_use_pred_64x64_only_th = (uint8_t)~0;
+}
+
 uint32_t svtme_shim_pu_count(const PictureParentControlSet *pcs) {
     return pcs->enable_me_16x16 ? (pcs->enable_me_8x8 ? SQUARE_PU_COUNT : MAX_SB64_PU_COUNT_NO_8X8) : MAX_SB64_PU_COUNT_WO_16X16;
 }

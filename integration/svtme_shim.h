@@ -96,6 +96,9 @@ int32_t svtme_shim_dg_picture(SvtMeShim *s, PictureParentControlSet *ppcs);
  * tf_tot_horz_blks / tf_tot_vert_blks (:2469-2474).  The centre picture is uploaded at its first request -- before any block
  * of it has been filtered in place -- and the neighbours per pair; neither goes into the open-loop picture cache.
  * Not thread-safe: TF segment threads call it under one lock. */
+/* the pure-host half of svtme_shim_tf_b64: one block's row of the pair's results into the MeContext */
+void svtme_shim_tf_fill_b64(MeContext *ctx, const uint32_t *best_sad, const uint32_t *best_mv, int16_t hme_sc_x, int16_t hme_sc_y,
+                            int exited);
 int32_t svtme_shim_tf_b64(SvtMeShim *s, const SequenceControlSet *scs, PictureParentControlSet *centre_pcs,
                           PictureParentControlSet *ref_pcs, MeContext *ctx, uint32_t b64_index);
 /* To be called where the encoder releases a PA reference object (pic_mgr / pd_process release of pa_ref_pic_wrapper). */

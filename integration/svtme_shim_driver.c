@@ -278,23 +278,8 @@ int32_t svtme_shim_tf_b64(SvtMeShim *s, const SequenceControlSet *scs, PicturePa
                           PictureParentControlSet *ref_pcs, MeContext *ctx, uint32_t b64_index) {
     const ShimTfPair *p = shim_tf_pair(s, scs, centre_pcs, ref_pcs, ctx);
     if (!p) return -1;
-    memcpy(ctx->p_sb_best_sad[0][0], p->best_sad + (size_t)b64_index * SQUARE_PU_COUNT, SQUARE_PU_COUNT * sizeof(uint32_t));
-    memcpy(ctx->p_sb_best_mv[0][0], p->best_mv + (size_t)b64_index * SQUARE_PU_COUNT, SQUARE_PU_COUNT * sizeof(uint32_t));
-    /* motion_estimation.c:1368-1384 */
-    ctx->p_best_sad_64x64 = &ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_64x64];
-    ctx->p_best_sad_32x32 = &ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_32x32_0];
-    ctx->p_best_sad_16x16 = &ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_16x16_0];
-    ctx->p_best_sad_8x8   = &ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_8x8_0];
-    ctx->p_best_mv64x64   = &ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_64x64];
-    ctx->p_best_mv32x32   = &ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_32x32_0];
-    ctx->p_best_mv16x16   = &ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_16x16_0];
-    ctx->p_best_mv8x8     = &ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_8x8_0];
-    const int16_t sc_x = p->hme_sc[(size_t)b64_index * 16], sc_y = p->hme_sc[(size_t)b64_index * 16 + 1];
-    ctx->search_results[0][0].hme_sc_x = sc_x;
-    ctx->search_results[0][0].hme_sc_y = sc_y;
-    if (abs(sc_x) > abs(sc_y)) ctx->tf_tot_horz_blks++; /* :2469-2474 */
-    else ctx->tf_tot_vert_blks++;
-    if (p->exit_sb[b64_index]) ctx->tf_use_pred_64x64_only_th = (uint8_t)~0; /* :3109-3113 */
+    svtme_shim_tf_fill_b64(ctx, p->best_sad + (size_t)b64_index * SQUARE_PU_COUNT, p->best_mv + (size_t)b64_index * SQUARE_PU_COUNT,
+                           p->hme_sc[(size_t)b64_index * 16], p->hme_sc[(size_t)b64_index * 16 + 1], p->exit_sb[b64_index]);
     return 0;
 }
 

@@ -286,3 +286,43 @@ size_t shimtb_results_bytes(uint32_t n_b64, uint32_t pus, uint32_t max_refs, uin
     SvtMePictureResults r;
     return svtme_shim_results_layout(&r, n_b64, pus, max_refs, max_cand, NULL);
 }
+
+/*
+ * CPU-only, temporal filter: put the TF knob block `k` where the filter's MeContext / centre pcs keep it (pa_me_data is not
+ * assigned yet when picture decision runs the filter: NULL here), read it back through svtme_shim_tf_knobs_from_me_context
+ * (-> k_back), then hand one block's results to svtme_shim_tf_fill_b64 and report what the filter would read:
+ * out[0..84] SADs through p_best_sad_64x64 / 32x32 / 16x16 / 8x8, out[85..169] MVs through p_best_mv*, out[170..171] the HME
+ * centre, out[172] tf_use_pred_64x64_only_th, out[173..174] tf_tot_horz_blks / tf_tot_vert_blks.
+ */
+int shimtb_tf_roundtrip(const SvtMeKnobs *k, uint32_t W, uint32_t H, const uint32_t *best_sad, const uint32_t *best_mv, int sc_x,
+                        int sc_y, int exited, uint8_t th_before, SvtMeKnobs *k_back, int64_t out[175]) {
+    static const ShimTbGmc no_gm;
+    ShimTb *t = tb_new(k, &no_gm, W, H, 1);
+    if (!t) return -1;
+    t->pcs.pa_me_data           = NULL;
+    t->ctx.me_type              = ME_MCTF;
+    t->ctx.temporal_layer_index = k->temporal_layer_index;
+    t->ctx.is_ref               = k->is_ref;
+    t->ctx.tf_me_exit_th        = (uint16_t)k->tf_me_exit_th;
+    svtme_shim_tf_knobs_from_me_context(&t->scs, &t->pcs, &t->ctx, k_back);
+    MeContext *c                 = &t->ctx;
+    c->tf_use_pred_64x64_only_th = th_before;
+    c->tf_tot_horz_blks          = 100;
+    c->tf_tot_vert_blks          = 200;
+    svtme_shim_tf_fill_b64(c, best_sad, best_mv, (int16_t)sc_x, (int16_t)sc_y, exited);
+    out[0] = c->p_best_sad_64x64[0];
+    for (int i = 0; i < 4; i++) out[1 + i] = c->p_best_sad_32x32[i];
+    for (int i = 0; i < 16; i++) out[5 + i] = c->p_best_sad_16x16[i];
+    for (int i = 0; i < 64; i++) out[21 + i] = c->p_best_sad_8x8[i];
+    out[85] = c->p_best_mv64x64[0];
+    for (int i = 0; i < 4; i++) out[86 + i] = c->p_best_mv32x32[i];
+    for (int i = 0; i < 16; i++) out[90 + i] = c->p_best_mv16x16[i];
+    for (int i = 0; i < 64; i++) out[106 + i] = c->p_best_mv8x8[i];
+    out[170] = c->search_results[0][0].hme_sc_x;
+    out[171] = c->search_results[0][0].hme_sc_y;
+    out[172] = c->tf_use_pred_64x64_only_th;
+    out[173] = c->tf_tot_horz_blks;
+    out[174] = c->tf_tot_vert_blks;
+    tb_free(t);
+    return 0;
+}

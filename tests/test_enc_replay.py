@@ -464,6 +464,47 @@ def test_reference_harness_dg_and_tf_match_the_encoder(reference):
     _replay_pairs_cpu(reference)
 
 
+def test_shim_tf_knobs_and_fill(shim, oracle):
+    """The pure-host half of the temporal-filter shim on the reference's own structs (oracle/shim_testbed.c): the knob block of
+    every fixture pair survives MeContext / pcs -> svtme_shim_tf_knobs_from_me_context (with pa_me_data NULL, as in picture
+    decision), and svtme_shim_tf_fill_b64 leaves in the MeContext what the encoder's filter read after its own ME call."""
+    z, meta = _pairs()
+    shim.shimtb_tf_roundtrip.argtypes = [C.POINTER(abi.Knobs), C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                         C.c_int, C.c_uint8, C.POINTER(abi.Knobs), C.c_void_p]
+    seen = set()
+    for hd, luma, planes, k, blocks, hashes in _tf_cases(z, meta):
+        if (hd[0], hd[2]) in seen:  # one pair per centre picture is enough here
+            continue
+        seen.add((hd[0], hd[2]))
+        pics = []
+        for idx, num in ((planes[0], hd[0]), (planes[1], hd[1])):
+            pp = refbind.PaddedPicture(luma[idx], num)
+            oracle.build_planes(pp, hd[4])
+            pics.append(pp)
+        out = oracle.me_picture(k, pics[0], {(0, 0): pics[1]})
+        n = len(blocks)
+        sad = np.ascontiguousarray(np.asarray(out["sb_best_sad"]).reshape(n, 2, 4, 85)[:, 0, 0], np.uint32)
+        mv = np.ascontiguousarray(np.asarray(out["sb_best_mv"]).reshape(n, 2, 4, 85)[:, 0, 0], np.uint32)
+        sc = np.asarray(out["hme_sc"]).reshape(n, 2, 4, 2)[:, 0, 0]
+        horz = vert = 0
+        for b in range(n):
+            k_back, got = abi.Knobs(), np.zeros(175, np.int64)
+            th = 0 if b % 3 == 0 else 35
+            assert shim.shimtb_tf_roundtrip(C.byref(k), hd[2], hd[3], sad[b].ctypes.data, mv[b].ctypes.data, int(sc[b][0]), int(sc[b][1]),
+                                            int(blocks[b][0]), th, C.byref(k_back), got.ctypes.data) == 0
+            assert bytes(k_back) == bytes(k), (hd, {f: (a, c) for (f, a), (_, c) in zip(k.as_dict().items(), k_back.as_dict().items()) if a != c})
+            what = "centre %d block %d" % (hd[0], b)
+            assert (int(got[170]), int(got[171])) == (blocks[b][1], blocks[b][2]), what  # the encoder's own HME centre
+            assert int(got[172]) == (255 if blocks[b][0] else th), what
+            if not blocks[b][0]:  # tier-zero order: 64x64, 4 x 32x32, 16 x 16x16, 64 x 8x8 (me_context.h:52-138)
+                assert (_fnv(got[0:85]), _fnv(got[85:170])) == (int(hashes[b][0]), int(hashes[b][1])), what
+            horz += int(got[173]) - 100
+            vert += int(got[174]) - 200
+            assert (int(got[173]) - 100) + (int(got[174]) - 200) == 1
+        assert [horz, vert] == [int(v) for v in out["tf_blk_counts"]]
+    assert len(seen) >= 6
+
+
 @pytest.mark.gpu
 def test_cuda_dg_and_tf_match_the_encoder():
     from svtme import api
