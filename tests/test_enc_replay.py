@@ -464,6 +464,16 @@ def test_reference_harness_dg_and_tf_match_the_encoder(reference):
     _replay_pairs_cpu(reference)
 
 
+def test_shim_library_exports_its_header(shim):
+    """Every function integration/svtme_shim.h declares is defined by the compiled shim (svtme_shim.c + svtme_shim_driver.c)."""
+    import re
+    text = open(os.path.join(ROOT, "integration", "svtme_shim.h")).read()
+    names = sorted(set(re.findall(r"\b(svtme_shim_[a-z0-9_]+)\s*\(", text)))
+    assert len(names) >= 15, names
+    missing = [n for n in names if not hasattr(shim, n)]
+    assert not missing, missing
+
+
 def test_shim_tf_knobs_and_fill(shim, oracle):
     """The pure-host half of the temporal-filter shim on the reference's own structs (oracle/shim_testbed.c): the knob block of
     every fixture pair survives MeContext / pcs -> svtme_shim_tf_knobs_from_me_context (with pa_me_data NULL, as in picture
